@@ -1,0 +1,198 @@
+/*
+ * prometheus_b200.h -- C ABI of libprometheus_b200.so
+ *
+ * B200 (sm_100a) implementation of the PROMETHEUS transit forward-model hot path.
+ * The reference has no FFI layer: its seam is the Python method
+ *     Transit.sumOverChords(self, max_memory_gb=2.0) -> ndarray (n_orb, n_wav)
+ * (reference: pythonScripts/gasProperties.py:1160-1258) and the methods it calls.  Each entry
+ * point below names the reference method it stands in for; the ctypes binding a maintainer
+ * adds on the reference side is shown in INTEGRATION.md.
+ *
+ * Conventions
+ *   - plain C: pointers + sizes, float64 everywhere (the reference computes in float64).
+ *   - every function returns PB200_OK (0) or a negative pb200_status; the text of the last
+ *     failure is available from pb200_last_error().
+ *   - host pointers are caller-owned and only read during the call; device memory is owned
+ *     by the context.  One context per GPU; a context is not thread-safe.
+ *   - there is no CPU fallback: without a usable CUDA device pb200_create fails.
+ *   - chord order is the reference's: flat chord index c = (i_phi*n_rho + i_rho)*n_orb + i_orb
+ *     (reference: pythonScripts/geometryHandler.py:188-208, meshgrid 'ij' + flatten).
+ */
+#ifndef PROMETHEUS_B200_H
+#define PROMETHEUS_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PB200_ABI_VERSION 1
+
+typedef enum {
+    PB200_OK = 0,
+    PB200_ERR_INVALID = -1,      /* bad argument / inconsistent scene                    */
+    PB200_ERR_CUDA = -2,         /* CUDA runtime error (text in pb200_last_error)        */
+    PB200_ERR_NO_DEVICE = -3,    /* no CUDA device: there is no CPU fallback             */
+    PB200_ERR_UNSUPPORTED = -4,  /* scenario / constituent kind not implemented          */
+    PB200_ERR_NO_SCENE = -5,     /* pb200_run & co. called before pb200_set_scene        */
+    PB200_ERR_BOUNDS = -6        /* tabulated density queried outside its grid (the
+                                    reference raises ValueError there, gasProperties.py:600) */
+} pb200_status;
+
+/* density scenarios -- reference classes in pythonScripts/gasProperties.py */
+typedef enum {
+    PB200_SCN_BAROMETRIC = 0,    /* BarometricAtmosphere   :122-161  p = {n0, R, H}          */
+    PB200_SCN_HYDROSTATIC = 1,   /* HydrostaticAtmosphere  :164-204  p = {n0, R, G*mu*M, kB*T} */
+    PB200_SCN_POWERLAW = 2,      /* PowerLawAtmosphere :207-244, PowerLawExosphere :291-330,
+                                    MoonExosphere :333-374, TidallyHeatedMoon :377-461
+                                                                      p = {n0, R, q}          */
+    PB200_SCN_TORUS = 3,         /* TorusExosphere         :464-516  p = {n0, a_torus, H_torus} */
+    PB200_SCN_SERPENS = 4        /* SerpensExosphere       :519-601  trilinear table          */
+} pb200_scenario_type;
+
+typedef struct {
+    int32_t type;                /* pb200_scenario_type                                      */
+    int32_t n_constituents;      /* constituents [first, first+n) belong to this scenario    */
+    int32_t first_constituent;
+    int32_t reserved;
+    double T;                    /* temperature for P = n*kB*T (molecular lookups), :927     */
+    double p[8];                 /* scenario parameters, see pb200_scenario_type             */
+    /* per-phase arrays, length n_orb, evaluated by the host code with the reference's own
+       expressions (celestialBodies.py:370-397, :499-550; constants.py:31-45)                */
+    const double* centre_x;      /* x of the density centre (planet or moon)                 */
+    const double* centre_y;      /* y of the density centre                                  */
+    const double* shift;         /* Doppler factor of the absorber frame, :916               */
+    const double* amplitude;     /* NULL or per-phase multiplier of n0 (TidallyHeatedMoon)   */
+    /* serpens only: trilinear table on (gx, gy, gz), values C-ordered [ix][iy][iz], :580    */
+    const double* gx; const double* gy; const double* gz; const double* values;
+    int32_t dims[3];
+    int32_t reserved2;
+} pb200_scenario;
+
+typedef struct {
+    int32_t kind;                /* 0 = atom/ion (AtmosphericConstituent :609-735),
+                                    1 = molecule (MolecularConstituent :738-818)             */
+    int32_t reserved;
+    double chi;                  /* mixing ratio (1 for evaporative scenarios, :274)         */
+    double offset;               /* lookupOffset, 1e-50 (:638, :761)                         */
+    /* atoms: log10(sigma+offset) on a sorted wavelength table (interp1d .x/.y, :713)        */
+    const double* tab_x; const double* tab_y; int64_t n_tab;
+    /* molecules: log10(sigma+offset) on (P, T, lambda), C-ordered [iP][iT][iw] (:779)       */
+    const double* grid_P; const double* grid_T; const double* grid_w; const double* values;
+    int32_t dims[3];
+    int32_t reserved2;
+    double fill;                 /* RegularGridInterpolator fill_value = log10(offset)       */
+} pb200_constituent;
+
+typedef struct {
+    int32_t abi_version;         /* PB200_ABI_VERSION                                        */
+    int32_t n_x, n_rho, n_phi, n_orb;
+    int32_t n_scenarios, n_constituents, n_moons;
+    int64_t n_wav;
+    /* axes as produced by the host code (Grid.construct*Axis, geometryHandler.py:112-186;
+       WavelengthGrid.constructWavelengthGrid, gasProperties.py:1050-1071)                  */
+    const double* x;             /* [n_x]   line-of-sight midpoints                          */
+    const double* rho;           /* [n_rho]                                                  */
+    const double* sin_phi;       /* [n_phi] sin / cos of the phi midpoints                   */
+    const double* cos_phi;       /* [n_phi]                                                  */
+    const double* cos_phi_rot;   /* [n_phi] cos(phi - phiStarrot), gasProperties.py:1182     */
+    const double* wavelength;    /* [n_wav] cm, ascending                                    */
+    double delta_x;              /* Grid.getDeltaX, geometryHandler.py:88-94                 */
+    /* star (celestialBodies.py:59-74) */
+    double star_R, clv_u1, clv_u2, vsini;
+    const double* fstar_x; const double* fstar_y; int64_t n_fstar;   /* NULL/0: F* == 1     */
+    /* opaque bodies (gasProperties.py:1224-1230) */
+    double planet_R;
+    const double* planet_y;      /* [n_orb] a*sin(orbphase)                                  */
+    const double* moon_R;        /* [n_moons]                                                */
+    const double* moon_y;        /* [n_moons*n_orb]                                          */
+    const pb200_scenario* scenarios;
+    const pb200_constituent* constituents;
+} pb200_scene;
+
+typedef struct {
+    double upload_ms;            /* H2D of the scene (pb200_set_scene)                       */
+    double column_ms;            /* kernel (a'): density + column density                    */
+    double transit_ms;           /* kernel (c'): tau + exp(-tau) + disk sum                  */
+    double finalize_ms;          /* split reduction + division                               */
+    double download_ms;          /* D2H of R                                                 */
+    int64_t launches;            /* kernels launched by the call                             */
+    int64_t samples;             /* chord*lambda samples of the call (nominal)               */
+} pb200_timing;
+
+typedef struct pb200_ctx pb200_ctx;
+
+/* ---- life cycle ------------------------------------------------------------------------ */
+int pb200_abi_version(void);
+int pb200_device_count(void);
+int pb200_create(int device, pb200_ctx** out);
+void pb200_destroy(pb200_ctx* ctx);
+const char* pb200_last_error(pb200_ctx* ctx);          /* ctx may be NULL (create errors)   */
+/* run all work of this context on an existing cudaStream_t (e.g. torch's current stream). */
+int pb200_set_stream(pb200_ctx* ctx, void* cuda_stream);
+int64_t pb200_launch_count(pb200_ctx* ctx);            /* kernels launched since create     */
+
+/* ---- scene ------------------------------------------------------------------------------ */
+/* Uploads everything Transit.sumOverChords reads through `self`.             */
+int pb200_set_scene(pb200_ctx* ctx, const pb200_scene* scene);
+
+/* ---- Transit.sumOverChords (gasProperties.py:1160-1258) ---------------------------------
+ * R[(p-phase_lo)*(wav_hi-wav_lo) + (w-wav_lo)] for p in [phase_lo,phase_hi), w in [wav_lo,wav_hi).
+ * pb200_run writes to host memory; pb200_run_device leaves the tile in device memory
+ * (R_dev is a device pointer, e.g. a torch tensor) and does not synchronise.               */
+int pb200_run(pb200_ctx* ctx, int phase_lo, int phase_hi, int64_t wav_lo, int64_t wav_hi,
+              double* R_host, pb200_timing* timing);
+int pb200_run_device(pb200_ctx* ctx, int phase_lo, int phase_hi, int64_t wav_lo, int64_t wav_hi,
+                     double* R_dev, pb200_timing* timing);
+/* timing record of the last pb200_run / pb200_voigt_sigma call of this context */
+int pb200_last_timing(pb200_ctx* ctx, pb200_timing* timing);
+
+/* ---- inner seams, same arithmetic as the fused path, materialised ------------------------ */
+/* <Scenario>.calculateNumberDensity on the whole chord grid -> out[n_c*n_x] (chord-major)   */
+int pb200_number_density(pb200_ctx* ctx, int scenario, double* n_host);
+/* same for caller-supplied chords: y,z = rho*sin(phi), rho*cos(phi); cx,cy = density centre;
+   amp = NULL or per-chord multiplier.  out[n*n_x]                                           */
+int pb200_number_density_chords(pb200_ctx* ctx, int scenario, int64_t n, const double* y,
+                                const double* z, const double* cx, const double* cy,
+                                const double* amp, double* n_host);
+/* column density sum_x(n*chi)*delta_x of every atomic constituent (gasProperties.py:940),
+   out[n_atoms*n_c] in constituent order, chord order as the reference                       */
+int pb200_column_density(pb200_ctx* ctx, double* ncol_host);
+/* blocked mask (gasProperties.py:1224-1230) out[n_c] (1 = blocked) and
+   flux weights rho*clv (gasProperties.py:1178-1180, :1232) out[n_c]                         */
+int pb200_chord_masks(pb200_ctx* ctx, uint8_t* blocked_host, double* weight_host);
+/* Atmosphere.getLOSopticalDepth_Batch on the whole chord grid (gasProperties.py:885-956):
+   tau[n_c*(wav_hi-wav_lo)], blocked chords included (the reference evaluates only active
+   chords; their rows are simply not used).  Testing / bandwidth probe, memory-hungry.       */
+int pb200_optical_depth(pb200_ctx* ctx, int64_t wav_lo, int64_t wav_hi, double* tau_host);
+
+/* ---- cross sections --------------------------------------------------------------------- */
+/* n_interp_log (gasProperties.py:34-51) == AtmosphericConstituent.getSigmaAbs (:727-735):
+   out[i] = 10**interp(wl[i]; tab_x, tab_y) - offset, np.interp end clamping                 */
+int pb200_sigma_lookup(pb200_ctx* ctx, const double* tab_x, const double* tab_y, int64_t n_tab,
+                       double offset, const double* wl, int64_t n, double* out_host);
+/* AtmosphericConstituent.calculateVoigtProfile (:672-692): sigma(wl) = sum over lines of
+   pi e^2/(m_e c) f V(c/wl - c/wl0; sigma_v/wl0, gamma);  if out_log10 != NULL it also gets
+   log10(sigma + offset), the table constructLookupFunction stores (:713-714)                */
+int pb200_voigt_sigma(pb200_ctx* ctx, const double* line_wl, const double* line_gamma,
+                      const double* line_f, int64_t n_lines, double sigma_v, const double* wl,
+                      int64_t n, double offset, double* out_sigma, double* out_log10);
+/* scipy.special.voigt_profile(x, sigma, gamma) element-wise (validation of the Faddeeva code) */
+int pb200_voigt_profile(pb200_ctx* ctx, const double* x, const double* sigma,
+                        const double* gamma, int64_t n, double* out_host);
+/* MolecularConstituent.getSigmaAbs (:789-818): P[n_c*n_x] (clipped at 1e-4 inside), scalar T,
+   wl[n_c*n_wav] -> out[n_c*n_x*n_wav]                                                       */
+int pb200_molecular_sigma(pb200_ctx* ctx, const double* grid_P, const double* grid_T,
+                          const double* grid_w, const double* values, const int32_t dims[3],
+                          double fill, double offset, const double* P, double T, const double* wl,
+                          int64_t n_c, int64_t n_x, int64_t n_wav, double* out_host);
+
+/* ---- machine probes (roofline denominators that MEASURED_PEAKS.json does not hold) ------- */
+/* DFMA-chain FP64 peak [TFLOP/s] and fp64 exp throughput [G exp/s] on this context's GPU    */
+int pb200_probe_fp64(pb200_ctx* ctx, double* dfma_tflops, double* exp_gops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PROMETHEUS_B200_H */

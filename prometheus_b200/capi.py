@@ -1,0 +1,252 @@
+"""ctypes binding of libprometheus_b200.so (include/prometheus_b200.h).
+
+This is the only door from Python to the compute path.  If the shared library is missing
+or no CUDA device is usable the calls raise: there is no CPU implementation to fall back on.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libprometheus_b200.so")
+ABI_VERSION = 1
+
+c_double_p = C.POINTER(C.c_double)
+
+# every symbol include/prometheus_b200.h declares (checked by tests/test_abi.py)
+EXPORTS = [
+    "pb200_abi_version", "pb200_device_count", "pb200_create", "pb200_destroy", "pb200_last_error",
+    "pb200_set_stream", "pb200_launch_count", "pb200_set_scene", "pb200_run", "pb200_run_device",
+    "pb200_last_timing", "pb200_number_density", "pb200_number_density_chords", "pb200_column_density",
+    "pb200_chord_masks", "pb200_optical_depth", "pb200_sigma_lookup", "pb200_voigt_sigma",
+    "pb200_voigt_profile", "pb200_molecular_sigma", "pb200_probe_fp64",
+]
+
+SCN_BAROMETRIC, SCN_HYDROSTATIC, SCN_POWERLAW, SCN_TORUS, SCN_SERPENS = range(5)
+
+STATUS = {0: "PB200_OK", -1: "PB200_ERR_INVALID", -2: "PB200_ERR_CUDA", -3: "PB200_ERR_NO_DEVICE",
+          -4: "PB200_ERR_UNSUPPORTED", -5: "PB200_ERR_NO_SCENE", -6: "PB200_ERR_BOUNDS"}
+
+
+class Scenario(C.Structure):
+    _fields_ = [
+        ("type", C.c_int32), ("n_constituents", C.c_int32), ("first_constituent", C.c_int32),
+        ("reserved", C.c_int32), ("T", C.c_double), ("p", C.c_double * 8),
+        ("centre_x", c_double_p), ("centre_y", c_double_p), ("shift", c_double_p), ("amplitude", c_double_p),
+        ("gx", c_double_p), ("gy", c_double_p), ("gz", c_double_p), ("values", c_double_p),
+        ("dims", C.c_int32 * 3), ("reserved2", C.c_int32),
+    ]
+
+
+class Constituent(C.Structure):
+    _fields_ = [
+        ("kind", C.c_int32), ("reserved", C.c_int32), ("chi", C.c_double), ("offset", C.c_double),
+        ("tab_x", c_double_p), ("tab_y", c_double_p), ("n_tab", C.c_int64),
+        ("grid_P", c_double_p), ("grid_T", c_double_p), ("grid_w", c_double_p), ("values", c_double_p),
+        ("dims", C.c_int32 * 3), ("reserved2", C.c_int32), ("fill", C.c_double),
+    ]
+
+
+class Scene(C.Structure):
+    _fields_ = [
+        ("abi_version", C.c_int32),
+        ("n_x", C.c_int32), ("n_rho", C.c_int32), ("n_phi", C.c_int32), ("n_orb", C.c_int32),
+        ("n_scenarios", C.c_int32), ("n_constituents", C.c_int32), ("n_moons", C.c_int32),
+        ("n_wav", C.c_int64),
+        ("x", c_double_p), ("rho", c_double_p), ("sin_phi", c_double_p), ("cos_phi", c_double_p),
+        ("cos_phi_rot", c_double_p), ("wavelength", c_double_p),
+        ("delta_x", C.c_double),
+        ("star_R", C.c_double), ("clv_u1", C.c_double), ("clv_u2", C.c_double), ("vsini", C.c_double),
+        ("fstar_x", c_double_p), ("fstar_y", c_double_p), ("n_fstar", C.c_int64),
+        ("planet_R", C.c_double),
+        ("planet_y", c_double_p), ("moon_R", c_double_p), ("moon_y", c_double_p),
+        ("scenarios", C.POINTER(Scenario)), ("constituents", C.POINTER(Constituent)),
+    ]
+
+
+class Timing(C.Structure):
+    _fields_ = [("upload_ms", C.c_double), ("column_ms", C.c_double), ("transit_ms", C.c_double),
+                ("finalize_ms", C.c_double), ("download_ms", C.c_double),
+                ("launches", C.c_int64), ("samples", C.c_int64)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+class Pb200Error(RuntimeError):
+    def __init__(self, code: int, text: str):
+        super().__init__(f"{STATUS.get(code, code)}: {text}")
+        self.code = code
+
+
+_lib = None
+
+
+def library_path() -> str:
+    return LIB_PATH
+
+
+def load():
+    """dlopen the shared library and declare the prototypes.  Raises if it is not built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: build it with `python -m prometheus_b200.build` "
+            "(needs nvcc; there is no CPU fallback for the transit hot path)")
+    lib = C.CDLL(LIB_PATH)
+    vp, i32, i64, dbl = C.c_void_p, C.c_int, C.c_int64, C.c_double
+    sig = {
+        "pb200_abi_version": (C.c_int, []),
+        "pb200_device_count": (C.c_int, []),
+        "pb200_create": (C.c_int, [i32, C.POINTER(vp)]),
+        "pb200_destroy": (None, [vp]),
+        "pb200_last_error": (C.c_char_p, [vp]),
+        "pb200_set_stream": (C.c_int, [vp, vp]),
+        "pb200_launch_count": (i64, [vp]),
+        "pb200_set_scene": (C.c_int, [vp, C.POINTER(Scene)]),
+        "pb200_run": (C.c_int, [vp, i32, i32, i64, i64, c_double_p, C.POINTER(Timing)]),
+        "pb200_run_device": (C.c_int, [vp, i32, i32, i64, i64, vp, C.POINTER(Timing)]),
+        "pb200_last_timing": (C.c_int, [vp, C.POINTER(Timing)]),
+        "pb200_number_density": (C.c_int, [vp, i32, c_double_p]),
+        "pb200_number_density_chords": (C.c_int, [vp, i32, i64] + [c_double_p] * 6),
+        "pb200_column_density": (C.c_int, [vp, c_double_p]),
+        "pb200_chord_masks": (C.c_int, [vp, C.POINTER(C.c_uint8), c_double_p]),
+        "pb200_optical_depth": (C.c_int, [vp, i64, i64, c_double_p]),
+        "pb200_sigma_lookup": (C.c_int, [vp, c_double_p, c_double_p, i64, dbl, c_double_p, i64, c_double_p]),
+        "pb200_voigt_sigma": (C.c_int, [vp, c_double_p, c_double_p, c_double_p, i64, dbl, c_double_p, i64, dbl,
+                                        c_double_p, c_double_p]),
+        "pb200_voigt_profile": (C.c_int, [vp, c_double_p, c_double_p, c_double_p, i64, c_double_p]),
+        "pb200_molecular_sigma": (C.c_int, [vp, c_double_p, c_double_p, c_double_p, c_double_p,
+                                            C.POINTER(C.c_int32), dbl, dbl, c_double_p, dbl, c_double_p,
+                                            i64, i64, i64, c_double_p]),
+        "pb200_probe_fp64": (C.c_int, [vp, c_double_p, c_double_p]),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(lib, name)
+        fn.restype, fn.argtypes = res, args
+    if lib.pb200_abi_version() != ABI_VERSION:
+        raise ImportError(f"{LIB_PATH}: ABI {lib.pb200_abi_version()} != binding {ABI_VERSION}; rebuild")
+    _lib = lib
+    return lib
+
+
+def as_f64(a) -> np.ndarray:
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+def dptr(a: np.ndarray):
+    return a.ctypes.data_as(c_double_p)
+
+
+class Context:
+    """One pb200_ctx: one GPU, one stream.  Not thread-safe (mirrors the C contract)."""
+
+    def __init__(self, device: int = 0):
+        self.lib = load()
+        h = C.c_void_p()
+        rc = self.lib.pb200_create(int(device), C.byref(h))
+        if rc != 0:
+            raise Pb200Error(rc, self.lib.pb200_last_error(None).decode())
+        self.handle = h
+        self.device = device
+        self._keep = None   # numpy arrays referenced by the last scene struct
+
+    def check(self, rc: int):
+        if rc != 0:
+            raise Pb200Error(rc, self.lib.pb200_last_error(self.handle).decode())
+
+    def close(self):
+        if getattr(self, "handle", None):
+            self.lib.pb200_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    # ---- thin wrappers ---------------------------------------------------------------------------
+    def set_stream(self, cuda_stream: int):
+        self.check(self.lib.pb200_set_stream(self.handle, C.c_void_p(cuda_stream)))
+
+    def launch_count(self) -> int:
+        return int(self.lib.pb200_launch_count(self.handle))
+
+    def set_scene(self, scene: Scene, keep):
+        self._keep = keep
+        self.check(self.lib.pb200_set_scene(self.handle, C.byref(scene)))
+
+    def run(self, phase_lo, phase_hi, wav_lo, wav_hi, out: np.ndarray | None = None):
+        n = (phase_hi - phase_lo, wav_hi - wav_lo)
+        if out is None:
+            out = np.empty(n, dtype=np.float64)
+        assert out.shape == n and out.dtype == np.float64 and out.flags.c_contiguous
+        t = Timing()
+        self.check(self.lib.pb200_run(self.handle, phase_lo, phase_hi, wav_lo, wav_hi, dptr(out), C.byref(t)))
+        return out, t.as_dict()
+
+    def run_device(self, phase_lo, phase_hi, wav_lo, wav_hi, dev_ptr: int, want_timing=False):
+        t = Timing()
+        self.check(self.lib.pb200_run_device(self.handle, phase_lo, phase_hi, wav_lo, wav_hi, C.c_void_p(dev_ptr),
+                                             C.byref(t) if want_timing else None))
+        return t.as_dict() if want_timing else None
+
+    def last_timing(self) -> dict:
+        t = Timing()
+        self.check(self.lib.pb200_last_timing(self.handle, C.byref(t)))
+        return t.as_dict()
+
+    def probe_fp64(self):
+        a, b = C.c_double(), C.c_double()
+        self.check(self.lib.pb200_probe_fp64(self.handle, C.byref(a), C.byref(b)))
+        return {"dfma_tflops": a.value, "exp_gops": b.value}
+
+    def sigma_lookup(self, tab_x, tab_y, offset, wl):
+        tab_x, tab_y = as_f64(tab_x), as_f64(tab_y)
+        wl = as_f64(wl)
+        out = np.empty(wl.shape, dtype=np.float64)
+        self.check(self.lib.pb200_sigma_lookup(self.handle, dptr(tab_x), dptr(tab_y), tab_x.size, float(offset),
+                                               dptr(wl), wl.size, dptr(out)))
+        return out
+
+    def voigt_sigma(self, line_wl, line_gamma, line_f, sigma_v, wl, offset=1e-50, want_log=False):
+        lw, lg, lf, wl = as_f64(line_wl), as_f64(line_gamma), as_f64(line_f), as_f64(wl)
+        sig = np.empty(wl.shape, dtype=np.float64)
+        lg10 = np.empty(wl.shape, dtype=np.float64) if want_log else None
+        self.check(self.lib.pb200_voigt_sigma(self.handle, dptr(lw), dptr(lg), dptr(lf), lw.size, float(sigma_v),
+                                              dptr(wl), wl.size, float(offset), dptr(sig),
+                                              dptr(lg10) if want_log else None))
+        return (sig, lg10) if want_log else sig
+
+    def voigt_profile(self, x, sigma, gamma):
+        x = as_f64(x)
+        sigma = as_f64(np.broadcast_to(sigma, x.shape))
+        gamma = as_f64(np.broadcast_to(gamma, x.shape))
+        out = np.empty(x.shape, dtype=np.float64)
+        self.check(self.lib.pb200_voigt_profile(self.handle, dptr(x), dptr(sigma), dptr(gamma), x.size, dptr(out)))
+        return out
+
+    def molecular_sigma(self, grid, values, fill, offset, P, T, wl):
+        gP, gT, gW = (as_f64(g) for g in grid)
+        values = as_f64(values)
+        P, wl = as_f64(P), as_f64(wl)
+        n_c, n_x = P.shape
+        n_wav = wl.shape[1]
+        dims = (C.c_int32 * 3)(gP.size, gT.size, gW.size)
+        out = np.empty((n_c, n_x, n_wav), dtype=np.float64)
+        self.check(self.lib.pb200_molecular_sigma(self.handle, dptr(gP), dptr(gT), dptr(gW), dptr(values), dims,
+                                                  float(fill), float(offset), dptr(P), float(T), dptr(wl),
+                                                  n_c, n_x, n_wav, dptr(out)))
+        return out

@@ -1,0 +1,779 @@
+// pb200_api.cu -- the C ABI of include/prometheus_b200.h: context, scene upload, orchestration.
+// All compute is in the kernels of pb200_density.cu / pb200_sigma.cu / pb200_transit.cu /
+// pb200_molecular.cu; there is no host fallback for any of it.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "pb200_internal.cuh"
+#include "pb200_molecule.cuh"
+
+namespace pb200 {
+
+
+// launchers implemented in the kernel translation units
+void launch_sky_cells(const DevScene*, int Mp, cudaStream_t);
+void launch_fout_scalar(const DevScene*, cudaStream_t);
+void launch_column(const DevScene*, int Mp, int phase_lo, int n_phase, int* oob, int sm_count, cudaStream_t);
+void launch_number_density_grid(const DevScene*, int64_t n_chords, int scenario, double* out, int* oob, int sm_count,
+                                cudaStream_t);
+void launch_number_density_chords(const DevScene*, int scenario, int64_t n, const double* y, const double* z,
+                                  const double* cx, const double* cy, const double* amp, double* out, int* oob,
+                                  int sm_count, cudaStream_t);
+cudaError_t launch_transit(const DevScene*, int n_atoms, const TransitParams&, cudaStream_t);
+cudaError_t launch_transit_general(const DevScene*, const DevScene& host_copy, const TransitParams&, int sm_count,
+                                   cudaStream_t, int* n_launch);
+int transit_wpt_for(int n_atoms);
+void launch_finalize(const DevScene*, const TransitParams&, int sm_count, cudaStream_t);
+void launch_sigma_lookup(const double*, const double*, int64_t, double, const double*, int64_t, double*, int,
+                         cudaStream_t);
+void launch_sigma_u(const DevScene*, int n_atoms, int n_orb, int64_t wav_lo, int64_t n_wav_sel, double* out, int,
+                    cudaStream_t);
+void launch_voigt_sigma(const double*, const double*, const double*, int64_t, double, const double*, int64_t, double,
+                        double*, double*, cudaStream_t);
+void launch_voigt_profile(const double*, const double*, const double*, int64_t, double*, int, cudaStream_t);
+void launch_molecular_sigma(const MolTable&, double offset, const double* P, double T, const double* wl, int64_t n_c,
+                            int64_t n_x, int64_t n_wav, double* out, int sm_count, cudaStream_t);
+void launch_optical_depth(const DevScene*, const double* sigma_u, int64_t n_chords, int64_t wav_lo, int64_t n_wav_sel,
+                          double* tau, cudaStream_t);
+void launch_probe_dfma(double* out, int blocks, int iters, cudaStream_t);
+void launch_probe_exp(double* out, int blocks, int iters, cudaStream_t);
+
+}  // namespace pb200
+
+using namespace pb200;
+
+static thread_local std::string g_create_error;
+
+struct pb200_ctx {
+    int device = 0;
+    int sm_count = 148;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    std::string err;
+    int64_t launches = 0;
+    bool has_scene = false;
+    bool general_path = false;   // molecules or a per-chord F* table: transit_general kernels
+    DevScene h_scene;            // host copy, pointers are device pointers
+    DevScene* d_scene = nullptr;
+    void* arena = nullptr;       // one allocation holding every uploaded array
+    size_t arena_bytes = 0;
+    void* stage = nullptr;       // pinned host staging buffer for the upload
+    size_t stage_bytes = 0;
+    std::vector<void*> derived;  // w_out, w_in, ncol, density..., freed with the scene
+    double* scratch = nullptr;   // partial sums / R tile / temporary outputs
+    size_t scratch_bytes = 0;
+    int* d_oob = nullptr;
+    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    pb200_timing last = {};
+    double upload_ms = 0.0;
+};
+
+static int fail(pb200_ctx* c, int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (c) c->err = buf; else g_create_error = buf;
+    return code;
+}
+
+#define PB_CUDA(c, call)                                                                          \
+    do {                                                                                          \
+        cudaError_t e_ = (call);                                                                  \
+        if (e_ != cudaSuccess)                                                                    \
+            return fail((c), PB200_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), \
+                        __FILE__, __LINE__);                                                      \
+    } while (0)
+
+static int ensure_scratch(pb200_ctx* c, size_t bytes) {
+    if (bytes <= c->scratch_bytes) return PB200_OK;
+    if (c->scratch) { PB_CUDA(c, cudaStreamSynchronize(c->stream)); PB_CUDA(c, cudaFree(c->scratch)); c->scratch = nullptr; c->scratch_bytes = 0; }
+    PB_CUDA(c, cudaMalloc((void**)&c->scratch, bytes));
+    c->scratch_bytes = bytes;
+    return PB200_OK;
+}
+
+static void free_scene(pb200_ctx* c) {
+    for (void* p : c->derived) cudaFree(p);
+    c->derived.clear();
+    if (c->arena) { cudaFree(c->arena); c->arena = nullptr; c->arena_bytes = 0; }
+    c->has_scene = false;
+}
+
+extern "C" {
+
+int pb200_abi_version(void) { return PB200_ABI_VERSION; }
+
+int pb200_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+const char* pb200_last_error(pb200_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+int pb200_create(int device, pb200_ctx** out) {
+    if (!out) return fail(nullptr, PB200_ERR_INVALID, "pb200_create: out == NULL");
+    *out = nullptr;
+    int n = pb200_device_count();
+    if (n <= 0) return fail(nullptr, PB200_ERR_NO_DEVICE, "no CUDA device visible; libprometheus_b200 has no CPU fallback");
+    if (device < 0 || device >= n) return fail(nullptr, PB200_ERR_INVALID, "device %d out of range [0, %d)", device, n);
+    pb200_ctx* c = new pb200_ctx();
+    c->device = device;
+    cudaError_t e = cudaSetDevice(device);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) { c->own_stream = true; e = cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device); }
+    for (int i = 0; i < 6 && e == cudaSuccess; ++i) e = cudaEventCreate(&c->ev[i]);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_scene, sizeof(DevScene));
+    if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_oob, sizeof(int));
+    if (e == cudaSuccess) e = cudaMemset(c->d_oob, 0, sizeof(int));
+    if (e != cudaSuccess) {
+        int rc = fail(nullptr, PB200_ERR_CUDA, "pb200_create: %s", cudaGetErrorString(e));
+        delete c;
+        return rc;
+    }
+    memset(&c->h_scene, 0, sizeof(DevScene));
+    *out = c;
+    return PB200_OK;
+}
+
+void pb200_destroy(pb200_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    free_scene(c);
+    if (c->scratch) cudaFree(c->scratch);
+    if (c->stage) cudaFreeHost(c->stage);
+    if (c->d_scene) cudaFree(c->d_scene);
+    if (c->d_oob) cudaFree(c->d_oob);
+    for (auto& e : c->ev) if (e) cudaEventDestroy(e);
+    if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int pb200_set_stream(pb200_ctx* c, void* cuda_stream) {
+    if (!c) return PB200_ERR_INVALID;
+    PB_CUDA(c, cudaSetDevice(c->device));
+    PB_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (c->own_stream && c->stream) { cudaStreamDestroy(c->stream); c->own_stream = false; }
+    c->stream = (cudaStream_t)cuda_stream;
+    return PB200_OK;
+}
+
+int64_t pb200_launch_count(pb200_ctx* c) { return c ? c->launches : 0; }
+
+}  // extern "C"
+
+// =================================================================================================
+// scene upload
+// =================================================================================================
+namespace {
+
+struct ArenaPlan {
+    struct Item { const void* src; size_t bytes; size_t offset; };
+    std::vector<Item> items;
+    size_t total = 0;
+    // returns the offset (in bytes) the array will have inside the arena
+    size_t add(const void* src, size_t bytes) {
+        const size_t off = total;
+        items.push_back({src, bytes, off});
+        total += (bytes + 255) & ~size_t(255);   // 256-byte alignment: TMA bulk copies need 16
+        return off;
+    }
+};
+
+template <typename T>
+const T* at(void* base, size_t off) { return reinterpret_cast<const T*>(static_cast<char*>(base) + off); }
+
+}  // namespace
+
+extern "C" int pb200_set_scene(pb200_ctx* c, const pb200_scene* s) {
+    if (!c || !s) return PB200_ERR_INVALID;
+    if (s->abi_version != PB200_ABI_VERSION)
+        return fail(c, PB200_ERR_INVALID, "scene abi_version %d != library %d", s->abi_version, PB200_ABI_VERSION);
+    if (s->n_x <= 0 || s->n_rho <= 0 || s->n_phi <= 0 || s->n_orb <= 0 || s->n_wav <= 0)
+        return fail(c, PB200_ERR_INVALID, "empty axis: n_x=%d n_rho=%d n_phi=%d n_orb=%d n_wav=%lld", s->n_x, s->n_rho,
+                    s->n_phi, s->n_orb, (long long)s->n_wav);
+    if (s->n_scenarios <= 0 || s->n_scenarios > kMaxScenarios)
+        return fail(c, PB200_ERR_INVALID, "n_scenarios=%d outside [1, %d]", s->n_scenarios, kMaxScenarios);
+    if (s->n_constituents < 0 || s->n_constituents > kMaxConstituents)
+        return fail(c, PB200_ERR_INVALID, "n_constituents=%d outside [0, %d]", s->n_constituents, kMaxConstituents);
+    if (s->n_moons < 0 || s->n_moons > kMaxMoons)
+        return fail(c, PB200_ERR_INVALID, "n_moons=%d outside [0, %d]", s->n_moons, kMaxMoons);
+    if (!s->x || !s->rho || !s->sin_phi || !s->cos_phi || !s->cos_phi_rot || !s->wavelength || !s->planet_y ||
+        !s->scenarios || (s->n_constituents && !s->constituents) || (s->n_moons && (!s->moon_R || !s->moon_y)))
+        return fail(c, PB200_ERR_INVALID, "scene has NULL array pointers");
+    if ((int64_t)s->n_phi * s->n_rho > (int64_t)1 << 30) return fail(c, PB200_ERR_INVALID, "sky grid too large");
+
+    PB_CUDA(c, cudaSetDevice(c->device));
+    PB_CUDA(c, cudaStreamSynchronize(c->stream));
+    free_scene(c);
+    PB_CUDA(c, cudaEventRecord(c->ev[0], c->stream));
+
+    DevScene& h = c->h_scene;
+    memset(&h, 0, sizeof h);
+    h.n_x = s->n_x; h.n_rho = s->n_rho; h.n_phi = s->n_phi; h.n_orb = s->n_orb; h.n_wav = s->n_wav;
+    h.n_scen = s->n_scenarios; h.n_cons = s->n_constituents; h.n_moons = s->n_moons;
+    h.M = s->n_phi * s->n_rho;
+    h.Mp = ((h.M + kChordTile - 1) / kChordTile) * kChordTile;
+    h.delta_x = s->delta_x; h.star_R = s->star_R; h.clv_u1 = s->clv_u1; h.clv_u2 = s->clv_u2; h.vsini = s->vsini;
+    h.planet_R = s->planet_R;
+    h.n_fstar = (s->fstar_x && s->fstar_y) ? s->n_fstar : 0;
+
+    // ---- plan the arena --------------------------------------------------------------------------
+    ArenaPlan plan;
+    const size_t D = sizeof(double);
+    const size_t o_x = plan.add(s->x, s->n_x * D), o_rho = plan.add(s->rho, s->n_rho * D);
+    const size_t o_sin = plan.add(s->sin_phi, s->n_phi * D), o_cos = plan.add(s->cos_phi, s->n_phi * D);
+    const size_t o_rot = plan.add(s->cos_phi_rot, s->n_phi * D), o_wav = plan.add(s->wavelength, s->n_wav * D);
+    const size_t o_py = plan.add(s->planet_y, s->n_orb * D);
+    size_t o_fx = 0, o_fy = 0, o_mR = 0, o_my = 0;
+    if (h.n_fstar) { o_fx = plan.add(s->fstar_x, h.n_fstar * D); o_fy = plan.add(s->fstar_y, h.n_fstar * D); }
+    if (s->n_moons) { o_mR = plan.add(s->moon_R, s->n_moons * D); o_my = plan.add(s->moon_y, (size_t)s->n_moons * s->n_orb * D); }
+
+    struct ScnOff { size_t cx, cy, sh, amp, gx, gy, gz, val; };
+    struct ConOff { size_t tx, ty, gP, gT, gW, val; };
+    std::vector<ScnOff> so(s->n_scenarios);
+    std::vector<ConOff> co(s->n_constituents);
+    int n_atoms = 0, n_mols = 0, n_density = 0, covered = 0;
+    for (int i = 0; i < s->n_scenarios; ++i) {
+        const pb200_scenario& q = s->scenarios[i];
+        if (q.type < PB200_SCN_BAROMETRIC || q.type > PB200_SCN_SERPENS)
+            return fail(c, PB200_ERR_UNSUPPORTED, "scenario %d: unknown type %d", i, q.type);
+        if (!q.shift) return fail(c, PB200_ERR_INVALID, "scenario %d: shift array is NULL", i);
+        if (q.type != PB200_SCN_SERPENS && (!q.centre_x || !q.centre_y))
+            return fail(c, PB200_ERR_INVALID, "scenario %d: centre arrays are NULL", i);
+        if (q.first_constituent != covered || q.n_constituents < 0 || covered + q.n_constituents > s->n_constituents)
+            return fail(c, PB200_ERR_INVALID, "scenario %d: constituent range [%d,+%d) is not contiguous", i,
+                        q.first_constituent, q.n_constituents);
+        covered += q.n_constituents;
+        so[i].cx = q.centre_x ? plan.add(q.centre_x, s->n_orb * D) : 0;
+        so[i].cy = q.centre_y ? plan.add(q.centre_y, s->n_orb * D) : 0;
+        so[i].sh = plan.add(q.shift, s->n_orb * D);
+        so[i].amp = q.amplitude ? plan.add(q.amplitude, s->n_orb * D) : 0;
+        if (q.type == PB200_SCN_SERPENS) {
+            if (!q.gx || !q.gy || !q.gz || !q.values || q.dims[0] < 2 || q.dims[1] < 2 || q.dims[2] < 2)
+                return fail(c, PB200_ERR_INVALID, "scenario %d: serpens table missing", i);
+            so[i].gx = plan.add(q.gx, q.dims[0] * D); so[i].gy = plan.add(q.gy, q.dims[1] * D);
+            so[i].gz = plan.add(q.gz, q.dims[2] * D);
+            so[i].val = plan.add(q.values, (size_t)q.dims[0] * q.dims[1] * q.dims[2] * D);
+        }
+    }
+    if (covered != s->n_constituents) return fail(c, PB200_ERR_INVALID, "constituents not covered by the scenarios");
+    for (int k = 0; k < s->n_constituents; ++k) {
+        const pb200_constituent& q = s->constituents[k];
+        if (q.kind == 0) {
+            if (!q.tab_x || !q.tab_y || q.n_tab < 1) return fail(c, PB200_ERR_INVALID, "constituent %d: sigma table missing", k);
+            co[k].tx = plan.add(q.tab_x, q.n_tab * D); co[k].ty = plan.add(q.tab_y, q.n_tab * D);
+        } else if (q.kind == 1) {
+            if (!q.grid_P || !q.grid_T || !q.grid_w || !q.values || q.dims[0] < 2 || q.dims[1] < 2 || q.dims[2] < 2)
+                return fail(c, PB200_ERR_INVALID, "constituent %d: molecular table missing", k);
+            co[k].gP = plan.add(q.grid_P, q.dims[0] * D); co[k].gT = plan.add(q.grid_T, q.dims[1] * D);
+            co[k].gW = plan.add(q.grid_w, q.dims[2] * D);
+            co[k].val = plan.add(q.values, (size_t)q.dims[0] * q.dims[1] * q.dims[2] * D);
+        } else {
+            return fail(c, PB200_ERR_UNSUPPORTED, "constituent %d: unknown kind %d", k, q.kind);
+        }
+    }
+
+    // ---- stage + one H2D copy --------------------------------------------------------------------
+    if (plan.total > c->stage_bytes) {
+        if (c->stage) cudaFreeHost(c->stage);
+        c->stage = nullptr; c->stage_bytes = 0;
+        PB_CUDA(c, cudaMallocHost(&c->stage, plan.total));
+        c->stage_bytes = plan.total;
+    }
+    for (const auto& it : plan.items) memcpy(static_cast<char*>(c->stage) + it.offset, it.src, it.bytes);
+    PB_CUDA(c, cudaMalloc(&c->arena, plan.total));
+    c->arena_bytes = plan.total;
+    PB_CUDA(c, cudaMemcpyAsync(c->arena, c->stage, plan.total, cudaMemcpyHostToDevice, c->stream));
+
+    void* A = c->arena;
+    h.x = at<double>(A, o_x); h.rho = at<double>(A, o_rho); h.sin_phi = at<double>(A, o_sin);
+    h.cos_phi = at<double>(A, o_cos); h.cos_phi_rot = at<double>(A, o_rot); h.wavelength = at<double>(A, o_wav);
+    h.planet_y = at<double>(A, o_py);
+    if (h.n_fstar) { h.fstar_x = at<double>(A, o_fx); h.fstar_y = at<double>(A, o_fy); }
+    if (s->n_moons) { h.moon_R = at<double>(A, o_mR); h.moon_y = at<double>(A, o_my); }
+    for (int i = 0; i < s->n_scenarios; ++i) {
+        const pb200_scenario& q = s->scenarios[i];
+        DevScenario& d = h.scen[i];
+        d.type = q.type; d.n_cons = q.n_constituents; d.first_cons = q.first_constituent; d.T = q.T;
+        memcpy(d.p, q.p, sizeof d.p);
+        d.centre_x = q.centre_x ? at<double>(A, so[i].cx) : nullptr;
+        d.centre_y = q.centre_y ? at<double>(A, so[i].cy) : nullptr;
+        d.shift = at<double>(A, so[i].sh);
+        d.amplitude = q.amplitude ? at<double>(A, so[i].amp) : nullptr;
+        d.density_slot = -1;
+        if (q.type == PB200_SCN_SERPENS) {
+            d.gx = at<double>(A, so[i].gx); d.gy = at<double>(A, so[i].gy); d.gz = at<double>(A, so[i].gz);
+            d.values = at<double>(A, so[i].val);
+            memcpy(d.dims, q.dims, sizeof d.dims);
+        }
+        for (int k = q.first_constituent; k < q.first_constituent + q.n_constituents; ++k) {
+            const pb200_constituent& qc = s->constituents[k];
+            DevConstituent& dc = h.cons[k];
+            dc.kind = qc.kind; dc.scenario = i; dc.chi = qc.chi; dc.offset = qc.offset; dc.fill = qc.fill;
+            dc.atom_index = dc.mol_index = -1;
+            if (qc.kind == 0) {
+                dc.atom_index = n_atoms++;
+                dc.tab_x = at<double>(A, co[k].tx); dc.tab_y = at<double>(A, co[k].ty); dc.n_tab = qc.n_tab;
+            } else {
+                dc.mol_index = n_mols++;
+                d.has_molecule = 1;
+                dc.grid_P = at<double>(A, co[k].gP); dc.grid_T = at<double>(A, co[k].gT);
+                dc.grid_w = at<double>(A, co[k].gW); dc.values = at<double>(A, co[k].val);
+                memcpy(dc.dims, qc.dims, sizeof dc.dims);
+            }
+        }
+        if (d.has_molecule) d.density_slot = n_density++;
+    }
+    h.n_atoms = n_atoms; h.n_mols = n_mols;
+
+    // ---- derived device arrays -------------------------------------------------------------------
+    auto dalloc = [&](double** p, size_t n) -> cudaError_t {
+        cudaError_t e = cudaMalloc((void**)p, (n ? n : 1) * sizeof(double));
+        if (e == cudaSuccess) c->derived.push_back(*p);
+        return e;
+    };
+    PB_CUDA(c, dalloc(&h.w_out, h.Mp));
+    PB_CUDA(c, dalloc(&h.star_shift, h.Mp));
+    PB_CUDA(c, dalloc(&h.w_in, (size_t)h.n_orb * h.Mp));
+    PB_CUDA(c, dalloc(&h.ncol, (size_t)n_atoms * h.n_orb * h.Mp));
+    for (int i = 0; i < s->n_scenarios; ++i)
+        if (h.scen[i].density_slot >= 0)
+            PB_CUDA(c, dalloc(&h.density[h.scen[i].density_slot], (size_t)h.n_orb * h.M * h.n_x));
+    const bool fstar_per_chord = h.n_fstar > 0 && h.vsini != 0.0;
+    PB_CUDA(c, dalloc(&h.fout, fstar_per_chord ? (size_t)h.n_wav : 1));
+    c->general_path = (n_mols > 0) || fstar_per_chord;
+    h.fout_per_wav = fstar_per_chord ? 1 : 0;
+
+    PB_CUDA(c, cudaMemcpyAsync(c->d_scene, &h, sizeof(DevScene), cudaMemcpyHostToDevice, c->stream));
+    // phase-independent prologue: flux weights and stellar surface shifts
+    launch_sky_cells(c->d_scene, h.Mp, c->stream);
+    launch_fout_scalar(c->d_scene, c->stream);
+    c->launches += 2;
+    PB_CUDA(c, cudaGetLastError());
+    PB_CUDA(c, cudaEventRecord(c->ev[1], c->stream));
+    PB_CUDA(c, cudaStreamSynchronize(c->stream));   // h (stack of this ctx) and stage are reused afterwards
+    float ms = 0.f;
+    PB_CUDA(c, cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]));
+    c->upload_ms = ms;
+    c->has_scene = true;
+    return PB200_OK;
+}
+
+// =================================================================================================
+// Transit.sumOverChords
+// =================================================================================================
+namespace {
+
+int check_scene(pb200_ctx* c) {
+    if (!c) return PB200_ERR_INVALID;
+    if (!c->has_scene) return fail(c, PB200_ERR_NO_SCENE, "no scene: call pb200_set_scene first");
+    cudaError_t e = cudaSetDevice(c->device);
+    if (e != cudaSuccess) return fail(c, PB200_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e));
+    return PB200_OK;
+}
+
+// enqueue kernels (a') and (c') for the tile; R_dev receives [n_phase][n_wav_sel]
+int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_t wav_hi, double* R_dev,
+                bool R_in_scratch) {
+    const DevScene& h = c->h_scene;
+    if (phase_lo < 0 || phase_hi > h.n_orb || phase_lo >= phase_hi || wav_lo < 0 || wav_hi > h.n_wav || wav_lo >= wav_hi)
+        return fail(c, PB200_ERR_INVALID, "tile [%d,%d) x [%lld,%lld) outside the (%d, %lld) grid", phase_lo, phase_hi,
+                    (long long)wav_lo, (long long)wav_hi, h.n_orb, (long long)h.n_wav);
+    const int n_phase = phase_hi - phase_lo;
+    const int64_t n_wav_sel = wav_hi - wav_lo;
+    const int64_t n_out = (int64_t)n_phase * n_wav_sel;
+    const int64_t launches0 = c->launches;
+
+    TransitParams prm;
+    prm.phase_lo = phase_lo; prm.n_phase = n_phase; prm.wav_lo = wav_lo; prm.n_wav_sel = n_wav_sel;
+    const int n_tiles = h.Mp / kChordTile;
+    const int wpt = c->general_path ? 1 : transit_wpt_for(h.n_atoms);
+    const int64_t ctas = ((n_wav_sel + 128 * wpt - 1) / (128 * wpt)) * n_phase;
+    int64_t want = ((int64_t)c->sm_count * 8 + ctas - 1) / ctas;   // aim at >= 8 CTAs per SM
+    if (want < 1) want = 1;
+    if (want > n_tiles) want = n_tiles;
+    prm.tiles_per_split = (int)((n_tiles + want - 1) / want);
+    prm.n_split = (n_tiles + prm.tiles_per_split - 1) / prm.tiles_per_split;
+
+    const size_t r_bytes = R_in_scratch ? (size_t)((n_out * sizeof(double) + 255) & ~255ll) : 0;
+    const size_t part_bytes = prm.n_split > 1 ? (size_t)prm.n_split * n_out * sizeof(double) : 0;
+    int rc = ensure_scratch(c, r_bytes + part_bytes + 256);
+    if (rc) return rc;
+    prm.R = R_in_scratch ? c->scratch : R_dev;
+    prm.partial = reinterpret_cast<double*>(reinterpret_cast<char*>(c->scratch) + r_bytes);
+
+    PB_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
+    launch_column(c->d_scene, h.Mp, phase_lo, n_phase, c->d_oob, c->sm_count, c->stream);
+    c->launches += 1;
+    PB_CUDA(c, cudaGetLastError());
+    PB_CUDA(c, cudaEventRecord(c->ev[3], c->stream));
+    if (c->general_path) {
+        int n_launch = 0;
+        cudaError_t e = launch_transit_general(c->d_scene, h, prm, c->sm_count, c->stream, &n_launch);
+        if (e == cudaErrorInvalidValue)
+            return fail(c, PB200_ERR_UNSUPPORTED, "molecular tables need more shared memory than one SM has (pressure nodes x molecules > 64)");
+        if (e != cudaSuccess) return fail(c, PB200_ERR_CUDA, "transit (general) launch: %s", cudaGetErrorString(e));
+        c->launches += n_launch;
+    } else {
+        if (h.n_atoms < 1) return fail(c, PB200_ERR_INVALID, "scene has no absorbing constituent");
+        cudaError_t e = launch_transit(c->d_scene, h.n_atoms, prm, c->stream);
+        if (e == cudaErrorInvalidValue && h.n_atoms > 12)
+            return fail(c, PB200_ERR_UNSUPPORTED, "%d atomic constituents; kernel (c') is compiled for <= 12", h.n_atoms);
+        if (e != cudaSuccess) return fail(c, PB200_ERR_CUDA, "transit launch: %s", cudaGetErrorString(e));
+        c->launches += 1;
+    }
+    PB_CUDA(c, cudaEventRecord(c->ev[4], c->stream));
+    if (prm.n_split > 1) {
+        launch_finalize(c->d_scene, prm, c->sm_count, c->stream);
+        c->launches += 1;
+        PB_CUDA(c, cudaGetLastError());
+    }
+    PB_CUDA(c, cudaEventRecord(c->ev[5], c->stream));
+    c->last = pb200_timing{};
+    c->last.upload_ms = c->upload_ms;
+    c->last.launches = c->launches - launches0;
+    c->last.samples = (int64_t)n_phase * h.M * n_wav_sel;
+    return PB200_OK;
+}
+
+int collect_timing(pb200_ctx* c) {
+    float a = 0, b = 0, d = 0;
+    PB_CUDA(c, cudaEventElapsedTime(&a, c->ev[2], c->ev[3]));
+    PB_CUDA(c, cudaEventElapsedTime(&b, c->ev[3], c->ev[4]));
+    PB_CUDA(c, cudaEventElapsedTime(&d, c->ev[4], c->ev[5]));
+    c->last.column_ms = a; c->last.transit_ms = b; c->last.finalize_ms = d;
+    return PB200_OK;
+}
+
+int check_oob(pb200_ctx* c) {
+    int flag = 0;
+    PB_CUDA(c, cudaMemcpyAsync(&flag, c->d_oob, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    PB_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (flag) {
+        PB_CUDA(c, cudaMemsetAsync(c->d_oob, 0, sizeof(int), c->stream));
+        return fail(c, PB200_ERR_BOUNDS, "tabulated density queried outside its grid (the reference raises ValueError)");
+    }
+    return PB200_OK;
+}
+
+}  // namespace
+
+extern "C" int pb200_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_t wav_hi, double* R_host,
+                         pb200_timing* timing) {
+    int rc = check_scene(c);
+    if (rc) return rc;
+    if (!R_host) return fail(c, PB200_ERR_INVALID, "R_host == NULL");
+    rc = enqueue_run(c, phase_lo, phase_hi, wav_lo, wav_hi, nullptr, true);
+    if (rc) return rc;
+    const size_t bytes = (size_t)(phase_hi - phase_lo) * (size_t)(wav_hi - wav_lo) * sizeof(double);
+    cudaEvent_t e0 = c->ev[0], e1 = c->ev[1];
+    PB_CUDA(c, cudaEventRecord(e0, c->stream));
+    PB_CUDA(c, cudaMemcpyAsync(R_host, c->scratch, bytes, cudaMemcpyDeviceToHost, c->stream));
+    PB_CUDA(c, cudaEventRecord(e1, c->stream));
+    rc = check_oob(c);   // synchronises the stream
+    if (rc) return rc;
+    PB_CUDA(c, cudaGetLastError());
+    rc = collect_timing(c);
+    if (rc) return rc;
+    float ms = 0;
+    PB_CUDA(c, cudaEventElapsedTime(&ms, e0, e1));
+    c->last.download_ms = ms;
+    if (timing) *timing = c->last;
+    return PB200_OK;
+}
+
+extern "C" int pb200_run_device(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_t wav_hi,
+                                double* R_dev, pb200_timing* timing) {
+    int rc = check_scene(c);
+    if (rc) return rc;
+    if (!R_dev) return fail(c, PB200_ERR_INVALID, "R_dev == NULL");
+    rc = enqueue_run(c, phase_lo, phase_hi, wav_lo, wav_hi, R_dev, false);
+    if (rc) return rc;
+    if (timing) {   // the caller asked for timings: this needs a synchronisation
+        rc = check_oob(c);
+        if (rc) return rc;
+        rc = collect_timing(c);
+        if (rc) return rc;
+        *timing = c->last;
+    }
+    return PB200_OK;
+}
+
+// =================================================================================================
+// inner seams (materialised) -- API parity with the methods sumOverChords calls
+// =================================================================================================
+namespace {
+
+// temporary device buffers for host-pointer entry points
+struct DevBuf {
+    void* p = nullptr;
+    ~DevBuf() { if (p) cudaFree(p); }
+    cudaError_t alloc(size_t bytes) { return cudaMalloc(&p, bytes ? bytes : 8); }
+    template <typename T> T* as() { return static_cast<T*>(p); }
+};
+
+int upload(pb200_ctx* c, DevBuf& b, const void* src, size_t bytes) {
+    PB_CUDA(c, b.alloc(bytes));
+    PB_CUDA(c, cudaMemcpyAsync(b.p, src, bytes, cudaMemcpyHostToDevice, c->stream));
+    return PB200_OK;
+}
+
+int download(pb200_ctx* c, void* dst, const void* src, size_t bytes) {
+    PB_CUDA(c, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, c->stream));
+    PB_CUDA(c, cudaStreamSynchronize(c->stream));
+    PB_CUDA(c, cudaGetLastError());
+    return PB200_OK;
+}
+
+int need_ctx(pb200_ctx* c) {
+    if (!c) return PB200_ERR_INVALID;
+    cudaError_t e = cudaSetDevice(c->device);
+    if (e != cudaSuccess) return fail(c, PB200_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e));
+    return PB200_OK;
+}
+
+}  // namespace
+
+extern "C" int pb200_number_density(pb200_ctx* c, int scenario, double* n_host) {
+    int rc = check_scene(c);
+    if (rc) return rc;
+    const DevScene& h = c->h_scene;
+    if (scenario < 0 || scenario >= h.n_scen || !n_host) return fail(c, PB200_ERR_INVALID, "bad scenario index %d", scenario);
+    const int64_t n_c = (int64_t)h.M * h.n_orb;
+    DevBuf out;
+    PB_CUDA(c, out.alloc((size_t)n_c * h.n_x * sizeof(double)));
+    launch_number_density_grid(c->d_scene, n_c, scenario, out.as<double>(), c->d_oob, c->sm_count, c->stream);
+    c->launches += 1;
+    PB_CUDA(c, cudaGetLastError());
+    rc = check_oob(c);
+    if (rc) return rc;
+    return download(c, n_host, out.p, (size_t)n_c * h.n_x * sizeof(double));
+}
+
+extern "C" int pb200_number_density_chords(pb200_ctx* c, int scenario, int64_t n, const double* y, const double* z,
+                                           const double* cx, const double* cy, const double* amp, double* n_host) {
+    int rc = check_scene(c);
+    if (rc) return rc;
+    const DevScene& h = c->h_scene;
+    if (scenario < 0 || scenario >= h.n_scen || n < 0 || !y || !z || !n_host)
+        return fail(c, PB200_ERR_INVALID, "pb200_number_density_chords: bad arguments");
+    if (n == 0) return PB200_OK;
+    const bool serp = h.scen[scenario].type == PB200_SCN_SERPENS;
+    if (!serp && (!cx || !cy)) return fail(c, PB200_ERR_INVALID, "centre arrays required");
+    DevBuf dy, dz, dcx, dcy, damp, out;
+    const size_t nb = (size_t)n * sizeof(double);
+    if ((rc = upload(c, dy, y, nb)) || (rc = upload(c, dz, z, nb))) return rc;
+    if (cx && (rc = upload(c, dcx, cx, nb))) return rc;
+    if (cy && (rc = upload(c, dcy, cy, nb))) return rc;
+    if (amp && (rc = upload(c, damp, amp, nb))) return rc;
+    PB_CUDA(c, out.alloc(nb * h.n_x));
+    launch_number_density_chords(c->d_scene, scenario, n, dy.as<double>(), dz.as<double>(), dcx.as<double>(),
+                                 dcy.as<double>(), amp ? damp.as<double>() : nullptr, out.as<double>(), c->d_oob,
+                                 c->sm_count, c->stream);
+    c->launches += 1;
+    PB_CUDA(c, cudaGetLastError());
+    rc = check_oob(c);
+    if (rc) return rc;
+    return download(c, n_host, out.p, nb * h.n_x);
+}
+
+// phase-major device rows -> the reference's chord order c = m*n_orb + p
+static void to_chord_order(const double* src, int n_orb, int M, int Mp, double* dst) {
+    for (int p = 0; p < n_orb; ++p)
+        for (int m = 0; m < M; ++m) dst[(int64_t)m * n_orb + p] = src[(int64_t)p * Mp + m];
+}
+
+extern "C" int pb200_column_density(pb200_ctx* c, double* ncol_host) {
+    int rc = check_scene(c);
+    if (rc) return rc;
+    const DevScene& h = c->h_scene;
+    if (!ncol_host) return fail(c, PB200_ERR_INVALID, "ncol_host == NULL");
+    launch_column(c->d_scene, h.Mp, 0, h.n_orb, c->d_oob, c->sm_count, c->stream);
+    c->launches += 1;
+    PB_CUDA(c, cudaGetLastError());
+    rc = check_oob(c);
+    if (rc) return rc;
+    const size_t per_atom = (size_t)h.n_orb * h.Mp;
+    std::vector<double> tmp(per_atom * (h.n_atoms ? h.n_atoms : 1));
+    rc = download(c, tmp.data(), h.ncol, per_atom * h.n_atoms * sizeof(double));
+    if (rc) return rc;
+    for (int a = 0; a < h.n_atoms; ++a)
+        to_chord_order(tmp.data() + a * per_atom, h.n_orb, h.M, h.Mp, ncol_host + (size_t)a * h.n_orb * h.M);
+    return PB200_OK;
+}
+
+extern "C" int pb200_chord_masks(pb200_ctx* c, uint8_t* blocked_host, double* weight_host) {
+    int rc = check_scene(c);
+    if (rc) return rc;
+    const DevScene& h = c->h_scene;
+    launch_column(c->d_scene, h.Mp, 0, h.n_orb, c->d_oob, c->sm_count, c->stream);
+    c->launches += 1;
+    PB_CUDA(c, cudaGetLastError());
+    std::vector<double> w_in((size_t)h.n_orb * h.Mp), w_out(h.Mp);
+    if ((rc = download(c, w_in.data(), h.w_in, w_in.size() * sizeof(double)))) return rc;
+    if ((rc = download(c, w_out.data(), h.w_out, w_out.size() * sizeof(double)))) return rc;
+    for (int p = 0; p < h.n_orb; ++p)
+        for (int m = 0; m < h.M; ++m) {
+            const int64_t cidx = (int64_t)m * h.n_orb + p;
+            // every rho midpoint is > 0 and clv > 0 for physical u1,u2, so w_in == 0 <=> blocked
+            if (blocked_host) blocked_host[cidx] = (w_in[(size_t)p * h.Mp + m] == 0.0 && w_out[m] != 0.0) ? 1 : 0;
+            if (weight_host) weight_host[cidx] = w_out[m];
+        }
+    return PB200_OK;
+}
+
+extern "C" int pb200_optical_depth(pb200_ctx* c, int64_t wav_lo, int64_t wav_hi, double* tau_host) {
+    int rc = check_scene(c);
+    if (rc) return rc;
+    const DevScene& h = c->h_scene;
+    if (wav_lo < 0 || wav_hi > h.n_wav || wav_lo >= wav_hi || !tau_host) return fail(c, PB200_ERR_INVALID, "bad wavelength range");
+    const int64_t n_wav_sel = wav_hi - wav_lo, n_c = (int64_t)h.M * h.n_orb;
+    DevBuf sig, tau;
+    PB_CUDA(c, sig.alloc((size_t)(h.n_atoms ? h.n_atoms : 1) * h.n_orb * n_wav_sel * sizeof(double)));
+    PB_CUDA(c, tau.alloc((size_t)n_c * n_wav_sel * sizeof(double)));
+    launch_column(c->d_scene, h.Mp, 0, h.n_orb, c->d_oob, c->sm_count, c->stream);
+    if (h.n_atoms) launch_sigma_u(c->d_scene, h.n_atoms, h.n_orb, wav_lo, n_wav_sel, sig.as<double>(), c->sm_count, c->stream);
+    launch_optical_depth(c->d_scene, sig.as<double>(), n_c, wav_lo, n_wav_sel, tau.as<double>(), c->stream);
+    c->launches += 2 + (h.n_atoms ? 1 : 0);
+    PB_CUDA(c, cudaGetLastError());
+    rc = check_oob(c);
+    if (rc) return rc;
+    return download(c, tau_host, tau.p, (size_t)n_c * n_wav_sel * sizeof(double));
+}
+
+// =================================================================================================
+// cross sections
+// =================================================================================================
+extern "C" int pb200_sigma_lookup(pb200_ctx* c, const double* tab_x, const double* tab_y, int64_t n_tab, double offset,
+                                  const double* wl, int64_t n, double* out_host) {
+    int rc = need_ctx(c);
+    if (rc) return rc;
+    if (!tab_x || !tab_y || n_tab < 1 || n < 0 || (n && (!wl || !out_host))) return fail(c, PB200_ERR_INVALID, "pb200_sigma_lookup: bad arguments");
+    if (n == 0) return PB200_OK;
+    DevBuf tx, ty, dw, out;
+    if ((rc = upload(c, tx, tab_x, n_tab * sizeof(double))) || (rc = upload(c, ty, tab_y, n_tab * sizeof(double))) ||
+        (rc = upload(c, dw, wl, n * sizeof(double))))
+        return rc;
+    PB_CUDA(c, out.alloc(n * sizeof(double)));
+    launch_sigma_lookup(tx.as<double>(), ty.as<double>(), n_tab, offset, dw.as<double>(), n, out.as<double>(), c->sm_count, c->stream);
+    c->launches += 1;
+    PB_CUDA(c, cudaGetLastError());
+    return download(c, out_host, out.p, n * sizeof(double));
+}
+
+extern "C" int pb200_voigt_sigma(pb200_ctx* c, const double* line_wl, const double* line_gamma, const double* line_f,
+                                 int64_t n_lines, double sigma_v, const double* wl, int64_t n, double offset,
+                                 double* out_sigma, double* out_log10) {
+    int rc = need_ctx(c);
+    if (rc) return rc;
+    if (n_lines < 0 || n < 0 || (n_lines && (!line_wl || !line_gamma || !line_f)) || (n && !wl))
+        return fail(c, PB200_ERR_INVALID, "pb200_voigt_sigma: bad arguments");
+    if (n == 0) return PB200_OK;
+    DevBuf lw, lg, lf, dw, os, ol;
+    const size_t lb = (size_t)n_lines * sizeof(double), nb = (size_t)n * sizeof(double);
+    if ((rc = upload(c, lw, line_wl, lb)) || (rc = upload(c, lg, line_gamma, lb)) || (rc = upload(c, lf, line_f, lb)) ||
+        (rc = upload(c, dw, wl, nb)))
+        return rc;
+    PB_CUDA(c, os.alloc(nb));
+    PB_CUDA(c, ol.alloc(nb));
+    PB_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
+    launch_voigt_sigma(lw.as<double>(), lg.as<double>(), lf.as<double>(), n_lines, sigma_v, dw.as<double>(), n, offset,
+                       os.as<double>(), ol.as<double>(), c->stream);
+    PB_CUDA(c, cudaEventRecord(c->ev[3], c->stream));
+    c->launches += 1;
+    PB_CUDA(c, cudaGetLastError());
+    if (out_sigma && (rc = download(c, out_sigma, os.p, nb))) return rc;
+    if (out_log10 && (rc = download(c, out_log10, ol.p, nb))) return rc;
+    PB_CUDA(c, cudaStreamSynchronize(c->stream));
+    float ms = 0;
+    PB_CUDA(c, cudaEventElapsedTime(&ms, c->ev[2], c->ev[3]));
+    c->last = pb200_timing{};
+    c->last.transit_ms = ms;   // kernel (b2) time, read back through pb200_last_timing
+    c->last.launches = 1;
+    c->last.samples = n * n_lines;
+    return PB200_OK;
+}
+
+extern "C" int pb200_voigt_profile(pb200_ctx* c, const double* x, const double* sigma, const double* gamma, int64_t n,
+                                   double* out_host) {
+    int rc = need_ctx(c);
+    if (rc) return rc;
+    if (n < 0 || (n && (!x || !sigma || !gamma || !out_host))) return fail(c, PB200_ERR_INVALID, "pb200_voigt_profile: bad arguments");
+    if (n == 0) return PB200_OK;
+    DevBuf dx, ds, dg, out;
+    const size_t nb = (size_t)n * sizeof(double);
+    if ((rc = upload(c, dx, x, nb)) || (rc = upload(c, ds, sigma, nb)) || (rc = upload(c, dg, gamma, nb))) return rc;
+    PB_CUDA(c, out.alloc(nb));
+    launch_voigt_profile(dx.as<double>(), ds.as<double>(), dg.as<double>(), n, out.as<double>(), c->sm_count, c->stream);
+    c->launches += 1;
+    PB_CUDA(c, cudaGetLastError());
+    return download(c, out_host, out.p, nb);
+}
+
+extern "C" int pb200_molecular_sigma(pb200_ctx* c, const double* grid_P, const double* grid_T, const double* grid_w,
+                                     const double* values, const int32_t dims[3], double fill, double offset,
+                                     const double* P, double T, const double* wl, int64_t n_c, int64_t n_x,
+                                     int64_t n_wav, double* out_host) {
+    int rc = need_ctx(c);
+    if (rc) return rc;
+    if (!grid_P || !grid_T || !grid_w || !values || !dims || dims[0] < 2 || dims[1] < 2 || dims[2] < 2 || !P || !wl ||
+        !out_host || n_c < 0 || n_x < 0 || n_wav < 0)
+        return fail(c, PB200_ERR_INVALID, "pb200_molecular_sigma: bad arguments");
+    if (n_c * n_x * n_wav == 0) return PB200_OK;
+    DevBuf gP, gT, gW, val, dP, dw, out;
+    const size_t D = sizeof(double);
+    if ((rc = upload(c, gP, grid_P, dims[0] * D)) || (rc = upload(c, gT, grid_T, dims[1] * D)) ||
+        (rc = upload(c, gW, grid_w, dims[2] * D)) || (rc = upload(c, val, values, (size_t)dims[0] * dims[1] * dims[2] * D)) ||
+        (rc = upload(c, dP, P, (size_t)n_c * n_x * D)) || (rc = upload(c, dw, wl, (size_t)n_c * n_wav * D)))
+        return rc;
+    PB_CUDA(c, out.alloc((size_t)n_c * n_x * n_wav * D));
+    MolTable t;
+    t.gP = gP.as<double>(); t.gT = gT.as<double>(); t.gW = gW.as<double>(); t.values = val.as<double>();
+    t.nP = dims[0]; t.nT = dims[1]; t.nW = dims[2]; t.fill = fill;
+    launch_molecular_sigma(t, offset, dP.as<double>(), T, dw.as<double>(), n_c, n_x, n_wav, out.as<double>(), c->sm_count, c->stream);
+    c->launches += 1;
+    PB_CUDA(c, cudaGetLastError());
+    return download(c, out_host, out.p, (size_t)n_c * n_x * n_wav * D);
+}
+
+extern "C" int pb200_last_timing(pb200_ctx* c, pb200_timing* t) {
+    if (!c || !t) return PB200_ERR_INVALID;
+    *t = c->last;
+    return PB200_OK;
+}
+
+// =================================================================================================
+// machine probes
+// =================================================================================================
+extern "C" int pb200_probe_fp64(pb200_ctx* c, double* dfma_tflops, double* exp_gops) {
+    int rc = need_ctx(c);
+    if (rc) return rc;
+    const int blocks = c->sm_count * 8, iters = 1 << 15;
+    DevBuf out;
+    PB_CUDA(c, out.alloc((size_t)blocks * 256 * sizeof(double)));
+    float best_f = 1e30f, best_e = 1e30f;
+    for (int rep = 0; rep < 4; ++rep) {
+        PB_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
+        launch_probe_dfma(out.as<double>(), blocks, iters, c->stream);
+        PB_CUDA(c, cudaEventRecord(c->ev[3], c->stream));
+        launch_probe_exp(out.as<double>(), blocks, iters / 8, c->stream);
+        PB_CUDA(c, cudaEventRecord(c->ev[4], c->stream));
+        PB_CUDA(c, cudaStreamSynchronize(c->stream));
+        float a, b;
+        PB_CUDA(c, cudaEventElapsedTime(&a, c->ev[2], c->ev[3]));
+        PB_CUDA(c, cudaEventElapsedTime(&b, c->ev[3], c->ev[4]));
+        if (rep > 0) { best_f = a < best_f ? a : best_f; best_e = b < best_e ? b : best_e; }
+    }
+    c->launches += 8;
+    const double n_thr = (double)blocks * 256;
+    if (dfma_tflops) *dfma_tflops = n_thr * iters * 8 * 2 / (best_f * 1e-3) / 1e12;
+    if (exp_gops) *exp_gops = n_thr * (iters / 8) * 4 / (best_e * 1e-3) / 1e9;
+    return PB200_OK;
+}

@@ -1,0 +1,214 @@
+// pb200_density.cu -- kernels (a)/(a'): chord weights, blocking mask, number density and
+// column density on the chord grid.  SURVEY 8(a) rows a2, a4, a6, a7, a8 (column part).
+//
+// Work decomposition: one warp per chord (phase p, sky cell m = i_phi*n_rho + i_rho); the 32 lanes
+// stride over the line-of-sight axis x and are reduced with warp shuffles in fp64.  Chord axes are a
+// few hundred doubles and live in L1; the only HBM traffic is the coalesced store of the result.
+#include "pb200_internal.cuh"
+
+namespace pb200 {
+
+// ---- a2 + a4: per sky cell weights, per (phase, cell) blocking ---------------------------------
+// w_out[m] = rho*clv (gasProperties.py:1179-1180, :1232 with F* = 1); star_shift[m] (:1182-1183)
+__global__ void sky_cell_kernel(const DevScene* __restrict__ scp) {
+    const DevScene& sc = *scp;
+    const int m = blockIdx.x * blockDim.x + threadIdx.x;
+    if (m >= sc.Mp) return;
+    if (m >= sc.M) { sc.w_out[m] = 0.0; sc.star_shift[m] = 1.0; return; }
+    const int iphi = m / sc.n_rho, irho = m - iphi * sc.n_rho;
+    const double rho = sc.rho[irho];
+    // mu = sqrt(clip(1 - rho^2/R^2, 0, 1)); clv = 1 - u1 (1-mu) - u2 (1-mu)^2, no FMA contraction
+    double q = __dsub_rn(1.0, __ddiv_rn(__dmul_rn(rho, rho), __dmul_rn(sc.star_R, sc.star_R)));
+    q = fmin(fmax(q, 0.0), 1.0);
+    const double om = __dsub_rn(1.0, __dsqrt_rn(q));
+    const double clv = __dsub_rn(__dsub_rn(1.0, __dmul_rn(sc.clv_u1, om)),
+                                 __dmul_rn(sc.clv_u2, __dmul_rn(om, om)));
+    sc.w_out[m] = __dmul_rn(rho, clv);
+    const double v = __dmul_rn(__ddiv_rn(__dmul_rn(sc.vsini, rho), sc.star_R), sc.cos_phi_rot[iphi]);
+    const double beta = __ddiv_rn(v, kLightSpeed);
+    sc.star_shift[m] = __dsqrt_rn(__ddiv_rn(__dsub_rn(1.0, beta), __dadd_rn(1.0, beta)));
+}
+
+// blocked(p, m): planet disk sqrt((y-y_p)^2 + z^2) < R_p, moon disks (y-y_m)^2 + z^2 < R_m^2
+// (gasProperties.py:1224-1230).  Same operation order as numpy, round-to-nearest, no FMA.
+__device__ __forceinline__ bool pb_blocked(const DevScene& sc, int p, double y, double z) {
+    const double z2 = __dmul_rn(z, z);
+    const double dyp = __dsub_rn(y, sc.planet_y[p]);
+    bool blocked = __dsqrt_rn(__dadd_rn(__dmul_rn(dyp, dyp), z2)) < sc.planet_R;
+    for (int k = 0; k < sc.n_moons; ++k) {
+        const double dym = __dsub_rn(y, sc.moon_y[k * sc.n_orb + p]);
+        const double Rm = sc.moon_R[k];
+        blocked |= __dadd_rn(__dmul_rn(dym, dym), z2) < __dmul_rn(Rm, Rm);
+    }
+    return blocked;
+}
+
+// ---- a6 + a7 + a8: density and column density, one warp per chord -----------------------------
+// WRITE_DENSITY: also store n(c, x) of scenarios that carry molecules (needed by kernel (m)).
+__global__ void __launch_bounds__(256)
+column_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, int* __restrict__ oob_flag) {
+    const DevScene& sc = *scp;
+    const int lane = threadIdx.x & 31;
+    const int warps_per_block = blockDim.x >> 5;
+    const int64_t n_chords = (int64_t)n_phase * sc.Mp;
+    for (int64_t cid = (int64_t)blockIdx.x * warps_per_block + (threadIdx.x >> 5); cid < n_chords;
+         cid += (int64_t)gridDim.x * warps_per_block) {
+        const int p = phase_lo + (int)(cid / sc.Mp);
+        const int m = (int)(cid % sc.Mp);
+        const int64_t row = (int64_t)p * sc.Mp + m;
+        if (m >= sc.M) {   // padding of the phase-major rows: zero weight, zero column
+            if (lane == 0) {
+                sc.w_in[row] = 0.0;
+                for (int a = 0; a < sc.n_atoms; ++a) sc.ncol[(int64_t)a * sc.n_orb * sc.Mp + row] = 0.0;
+            }
+            continue;
+        }
+        const int iphi = m / sc.n_rho, irho = m - iphi * sc.n_rho;
+        const double rho = sc.rho[irho];
+        const double y = __dmul_rn(rho, sc.sin_phi[iphi]);
+        const double z = __dmul_rn(rho, sc.cos_phi[iphi]);
+        const bool blocked = pb_blocked(sc, p, y, z);
+        if (lane == 0) sc.w_in[row] = blocked ? 0.0 : sc.w_out[m];
+        for (int s = 0; s < sc.n_scen; ++s) {
+            const DevScenario& S = sc.scen[s];
+            double sum = 0.0;
+            // the reference evaluates only unblocked chords (gasProperties.py:1235-1240)
+            if (!blocked) {
+                const double amp = S.amplitude ? S.amplitude[p] : 1.0;
+                double* dens = (S.density_slot >= 0)
+                                   ? sc.density[S.density_slot] + ((int64_t)p * sc.M + m) * sc.n_x
+                                   : nullptr;
+                if (S.type == PB200_SCN_SERPENS) {
+                    int oob = 0;
+                    for (int ix = lane; ix < sc.n_x; ix += 32) {
+                        const double n = pb_trilinear(S, sc.x[ix], y, z, &oob) * amp;
+                        if (dens) dens[ix] = n;
+                        sum += n;
+                    }
+                    if (oob) *oob_flag = 1;
+                } else {
+                    const double dy = y - S.centre_y[p];
+                    const double cx = S.centre_x[p];
+                    for (int ix = lane; ix < sc.n_x; ix += 32) {
+                        const double n = pb_density(S, amp, sc.x[ix] - cx, dy, z);
+                        if (dens) dens[ix] = n;
+                        sum += n;
+                    }
+                }
+                sum = pb_warp_sum(sum);
+            } else if (S.density_slot >= 0) {
+                double* dens = sc.density[S.density_slot] + ((int64_t)p * sc.M + m) * sc.n_x;
+                for (int ix = lane; ix < sc.n_x; ix += 32) dens[ix] = 0.0;
+            }
+            if (lane == 0) {
+                for (int k = S.first_cons; k < S.first_cons + S.n_cons; ++k) {
+                    const DevConstituent& C = sc.cons[k];
+                    if (C.kind == 0)   // col = sum_x(n*chi) * delta_x, gasProperties.py:940
+                        sc.ncol[(int64_t)C.atom_index * sc.n_orb * sc.Mp + row] = (sum * C.chi) * sc.delta_x;
+                }
+            }
+        }
+    }
+}
+
+// ---- calculateNumberDensity materialised (chord-major, reference chord order) ------------------
+// out[c*n_x + ix], c = m*n_orb + p.  One warp per chord: rows are written as coalesced 8-byte stores.
+__global__ void __launch_bounds__(256)
+number_density_grid_kernel(const DevScene* __restrict__ scp, int scenario, double* __restrict__ out,
+                           int* __restrict__ oob_flag) {
+    const DevScene& sc = *scp;
+    const DevScenario& S = sc.scen[scenario];
+    const int lane = threadIdx.x & 31;
+    const int warps_per_block = blockDim.x >> 5;
+    const int64_t n_chords = (int64_t)sc.M * sc.n_orb;
+    for (int64_t c = (int64_t)blockIdx.x * warps_per_block + (threadIdx.x >> 5); c < n_chords;
+         c += (int64_t)gridDim.x * warps_per_block) {
+        const int m = (int)(c / sc.n_orb), p = (int)(c % sc.n_orb);
+        const int iphi = m / sc.n_rho, irho = m - iphi * sc.n_rho;
+        const double rho = sc.rho[irho];
+        const double y = __dmul_rn(rho, sc.sin_phi[iphi]);
+        const double z = __dmul_rn(rho, sc.cos_phi[iphi]);
+        const double amp = S.amplitude ? S.amplitude[p] : 1.0;
+        double* row = out + c * sc.n_x;
+        if (S.type == PB200_SCN_SERPENS) {
+            int oob = 0;
+            for (int ix = lane; ix < sc.n_x; ix += 32) row[ix] = pb_trilinear(S, sc.x[ix], y, z, &oob) * amp;
+            if (oob) *oob_flag = 1;
+        } else {
+            const double dy = y - S.centre_y[p], cx = S.centre_x[p];
+            for (int ix = lane; ix < sc.n_x; ix += 32) row[ix] = pb_density(S, amp, sc.x[ix] - cx, dy, z);
+        }
+    }
+}
+
+// same for caller-supplied chords (API parity with <Scenario>.calculateNumberDensity(x, phi, rho, orb))
+__global__ void __launch_bounds__(256)
+number_density_chords_kernel(const DevScene* __restrict__ scp, int scenario, int64_t n,
+                             const double* __restrict__ y, const double* __restrict__ z,
+                             const double* __restrict__ cx, const double* __restrict__ cy,
+                             const double* __restrict__ amp, double* __restrict__ out,
+                             int* __restrict__ oob_flag) {
+    const DevScene& sc = *scp;
+    const DevScenario& S = sc.scen[scenario];
+    const int lane = threadIdx.x & 31;
+    const int warps_per_block = blockDim.x >> 5;
+    for (int64_t c = (int64_t)blockIdx.x * warps_per_block + (threadIdx.x >> 5); c < n;
+         c += (int64_t)gridDim.x * warps_per_block) {
+        const double a = amp ? amp[c] : 1.0;
+        double* row = out + c * sc.n_x;
+        if (S.type == PB200_SCN_SERPENS) {
+            int oob = 0;
+            for (int ix = lane; ix < sc.n_x; ix += 32) row[ix] = pb_trilinear(S, sc.x[ix], y[c], z[c], &oob) * a;
+            if (oob) *oob_flag = 1;
+        } else {
+            const double dy = y[c] - cy[c];
+            for (int ix = lane; ix < sc.n_x; ix += 32) row[ix] = pb_density(S, a, sc.x[ix] - cx[c], dy, z[c]);
+        }
+    }
+}
+
+// ---- F_out for F* == 1: sum_m rho*clv, one block, fixed order (deterministic) -------------------
+__global__ void __launch_bounds__(1024) fout_scalar_kernel(const DevScene* __restrict__ scp) {
+    const DevScene& sc = *scp;
+    __shared__ double part[32];
+    double s = 0.0;
+    for (int m = threadIdx.x; m < sc.M; m += blockDim.x) s += sc.w_out[m];
+    s = pb_warp_sum(s);
+    if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        double t = (threadIdx.x < (blockDim.x >> 5)) ? part[threadIdx.x] : 0.0;
+        t = pb_warp_sum(t);
+        if (threadIdx.x == 0) sc.fout[0] = t;
+    }
+}
+
+// ---- host-callable launchers ---------------------------------------------------------------------
+static inline int grid_for_warps(int64_t n_warp_items, int sm_count) {
+    const int64_t blocks = (n_warp_items + 7) / 8;   // 8 warps per 256-thread block
+    const int64_t cap = (int64_t)sm_count * 8;       // 8 resident blocks per SM, grid-stride beyond
+    return (int)(blocks < cap ? (blocks > 0 ? blocks : 1) : cap);
+}
+
+void launch_sky_cells(const DevScene* d_scene, int Mp, cudaStream_t st) {
+    sky_cell_kernel<<<(Mp + 255) / 256, 256, 0, st>>>(d_scene);
+}
+void launch_fout_scalar(const DevScene* d_scene, cudaStream_t st) {
+    fout_scalar_kernel<<<1, 1024, 0, st>>>(d_scene);
+}
+void launch_column(const DevScene* d_scene, int Mp, int phase_lo, int n_phase, int* oob, int sm_count,
+                   cudaStream_t st) {
+    column_kernel<<<grid_for_warps((int64_t)n_phase * Mp, sm_count), 256, 0, st>>>(d_scene, phase_lo, n_phase, oob);
+}
+void launch_number_density_grid(const DevScene* d_scene, int64_t n_chords, int scenario, double* out,
+                                int* oob, int sm_count, cudaStream_t st) {
+    number_density_grid_kernel<<<grid_for_warps(n_chords, sm_count), 256, 0, st>>>(d_scene, scenario, out, oob);
+}
+void launch_number_density_chords(const DevScene* d_scene, int scenario, int64_t n, const double* y,
+                                  const double* z, const double* cx, const double* cy, const double* amp,
+                                  double* out, int* oob, int sm_count, cudaStream_t st) {
+    number_density_chords_kernel<<<grid_for_warps(n, sm_count), 256, 0, st>>>(d_scene, scenario, n, y, z, cx,
+                                                                              cy, amp, out, oob);
+}
+
+}  // namespace pb200

@@ -1,0 +1,138 @@
+// pb200_internal.cuh -- device-side scene description shared by the kernels and the C ABI.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/prometheus_b200.h"
+#include "pb200_math.cuh"
+
+namespace pb200 {
+
+constexpr int kMaxScenarios = 8;
+constexpr int kMaxConstituents = 32;
+constexpr int kMaxMoons = 8;
+constexpr int kChordTile = 256;   // chords per shared-memory tile of kernel (c'); rows are padded to it
+
+struct DevScenario {
+    int type, n_cons, first_cons, has_molecule;
+    double T;
+    double p[8];
+    const double* centre_x;
+    const double* centre_y;
+    const double* shift;
+    const double* amplitude;
+    const double* gx; const double* gy; const double* gz; const double* values;
+    int dims[3];
+    int density_slot;   // index into DevScene::density (molecular scenarios) or -1
+};
+
+struct DevConstituent {
+    int kind, scenario, atom_index, mol_index;
+    double chi, offset, fill;
+    const double* tab_x; const double* tab_y; int64_t n_tab;
+    const double* grid_P; const double* grid_T; const double* grid_w; const double* values;
+    int dims[3];
+    int pad;
+};
+
+struct DevScene {
+    int n_x, n_rho, n_phi, n_orb;
+    int n_scen, n_cons, n_moons, n_atoms, n_mols;
+    int M;            // chords per phase  = n_phi * n_rho
+    int Mp;           // M padded to a multiple of kChordTile
+    int fout_per_wav; // 1: fout is [n_wav] (per-chord F* table with stellar rotation), 0: fout is [1]
+    int64_t n_wav;
+    double delta_x, star_R, clv_u1, clv_u2, vsini, planet_R;
+    const double* x; const double* rho; const double* sin_phi; const double* cos_phi;
+    const double* cos_phi_rot; const double* wavelength;
+    const double* fstar_x; const double* fstar_y; int64_t n_fstar;
+    const double* planet_y; const double* moon_R; const double* moon_y;
+    DevScenario scen[kMaxScenarios];
+    DevConstituent cons[kMaxConstituents];
+    // derived, device-resident, phase-major ("m" = i_phi*n_rho + i_rho):
+    double* w_out;        // [Mp]            rho*clv, 0 in the padding
+    double* star_shift;   // [Mp]            Doppler factor of the stellar surface element
+    double* w_in;         // [n_orb][Mp]     rho*clv, 0 where blocked by planet/moon or padding
+    double* ncol;         // [n_atoms][n_orb][Mp]  column densities
+    double* density[kMaxScenarios];  // [n_orb][M][n_x] number density of molecular scenarios
+    double* fout;         // [1] or [n_wav]  sum of unattenuated flux
+};
+
+// launch parameters of kernel (c') and its variants
+struct TransitParams {
+    int phase_lo, n_phase;
+    int64_t wav_lo, n_wav_sel;
+    int n_split;          // chord-axis splits (gridDim.z)
+    int tiles_per_split;  // kChordTile-chord tiles per split
+    double* partial;      // [n_split][n_phase][n_wav_sel] sums of w_in*exp(-tau)  (n_split > 1)
+    double* R;            // [n_phase][n_wav_sel] final ratio
+};
+
+// ---------------------------------------------------------------------------------------------
+// number density of one scenario at offsets (dx, dy, z) from its centre -- SURVEY 8(a) row a7
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ double pb_heaviside1(double u) { return (u < 0.0) ? 0.0 : 1.0; }
+
+__device__ __forceinline__ double pb_density(const DevScenario& s, double amp, double dx, double dy,
+                                             double z) {
+    switch (s.type) {
+        case PB200_SCN_BAROMETRIC: {   // gasProperties.py:155-160
+            const double r = sqrt(dx * dx + dy * dy + z * z);
+            return s.p[0] * amp * exp((s.p[1] - r) / s.p[2]) * pb_heaviside1(r - s.p[1]);
+        }
+        case PB200_SCN_HYDROSTATIC: {  // gasProperties.py:197-203 (non-zero inside the planet)
+            const double r = sqrt(dx * dx + dy * dy + z * z);
+            const double jeans0 = s.p[2] / (s.p[3] * s.p[1]);
+            const double jeans = s.p[2] / (s.p[3] * r) * pb_heaviside1(r - s.p[1]);
+            return s.p[0] * amp * exp(jeans - jeans0);
+        }
+        case PB200_SCN_POWERLAW: {     // gasProperties.py:240-243, :326-329, :371-373, :453-460
+            const double r = sqrt(dx * dx + dy * dy + z * z);
+            return s.p[0] * amp * pow(s.p[1] / r, s.p[2]) * pb_heaviside1(r - s.p[1]);
+        }
+        case PB200_SCN_TORUS: {        // gasProperties.py:506-515, celestialBodies.py:438-470
+            const double a = sqrt(dx * dx + dy * dy);
+            const double qa = (a - s.p[1]) / (4.0 * s.p[2]);
+            const double qz = z / s.p[2];
+            return s.p[0] * amp * (exp(-(qa * qa)) * exp(-(qz * qz)));
+        }
+        default:
+            return 0.0;
+    }
+}
+
+// trilinear interpolation on a regular grid (scipy RegularGridInterpolator, method='linear'),
+// used by the serpens scenario (gasProperties.py:580-600).  *oob is set when the point lies
+// outside the grid (the reference raises there).
+__device__ __forceinline__ int pb_grid_cell(const double* __restrict__ g, int n, double v, double* frac,
+                                            int* oob) {
+    if (v < g[0] || v > g[n - 1]) *oob = 1;
+    int lo = 0, hi = n - 1;
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (g[mid] <= v) lo = mid; else hi = mid;
+    }
+    // scipy: interval with g[i] <= v < g[i+1], clipped to [0, n-2]
+    *frac = (v - g[lo]) / (g[lo + 1] - g[lo]);
+    return lo;
+}
+
+__device__ __forceinline__ double pb_trilinear(const DevScenario& s, double px, double py, double pz,
+                                               int* oob) {
+    double fx, fy, fz;
+    const int ix = pb_grid_cell(s.gx, s.dims[0], px, &fx, oob);
+    const int iy = pb_grid_cell(s.gy, s.dims[1], py, &fy, oob);
+    const int iz = pb_grid_cell(s.gz, s.dims[2], pz, &fz, oob);
+    const int64_t sy = s.dims[2], sx = (int64_t)s.dims[1] * s.dims[2];
+    const double* v = s.values + ix * sx + iy * sy + iz;
+    double acc = 0.0;
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+        const int bx = (c >> 2) & 1, by = (c >> 1) & 1, bz = c & 1;
+        const double wgt = (bx ? fx : 1.0 - fx) * (by ? fy : 1.0 - fy) * (bz ? fz : 1.0 - fz);
+        acc += v[bx * sx + by * sy + bz] * wgt;
+    }
+    return acc;
+}
+
+}  // namespace pb200

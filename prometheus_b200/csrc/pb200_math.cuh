@@ -1,0 +1,192 @@
+// pb200_math.cuh -- fp64 device math of the transit hot path (sm_100a).
+//
+//   pb_exp_neg      exp(-t), t >= 0        inner loop of kernel (c'): Beer-Lambert, gasProperties.py:1241
+//   pb_interp_log   np.interp + 10**v - offset   == n_interp_log, gasProperties.py:34-51
+//   pb_faddeeva_re  Re w(x+iy)             == scipy.special.wofz(...).real inside voigt_profile
+//   pb_voigt        scipy.special.voigt_profile(x, sigma, gamma), call site gasProperties.py:687-688
+#pragma once
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
+
+namespace pb200 {
+
+// constants of the reference (pythonScripts/constants.py:13-17); mirrored in constants.py
+constexpr double kElemCharge = 4.803e-10;
+constexpr double kElectronMass = 9.109e-28;
+constexpr double kLightSpeed = 2.998e10;
+constexpr double kBoltzmann = 1.381e-16;
+constexpr double kPi = 3.141592653589793;
+
+// ---------------------------------------------------------------------------------------------
+// exp(-t) for t >= 0.  Cody-Waite reduction t = -k ln2 + r, |r| <= ln2/2, degree-11 polynomial
+// (max relative error 2e-17 before rounding, measured against long double), exponent patched
+// in with integer adds.  t is clamped at 700 (exp(-700) = 1e-304 stands in for "0"), which
+// keeps the result normal and the code branch-free.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ double pb_exp_neg(double t) {
+    t = fmin(t, 700.0);
+    const double kMagic = 6755399441055744.0;  // 1.5 * 2^52: rint() through the adder
+    double kd = fma(t, -1.4426950408889634, kMagic);
+    const int k = __double2loint(kd);
+    kd -= kMagic;
+    double r = fma(kd, -6.93147180369123816490e-01, -t);
+    r = fma(kd, -1.90821492927058770002e-10, r);
+    double p = 0x1.af354eec9216ep-26;
+    p = fma(p, r, 0x1.28917965df995p-22);
+    p = fma(p, r, 0x1.71de0fd1838abp-19);
+    p = fma(p, r, 0x1.a019b9189c259p-16);
+    p = fma(p, r, 0x1.a01a01a6cffcap-13);
+    p = fma(p, r, 0x1.6c16c178884cep-10);
+    p = fma(p, r, 0x1.1111111110c74p-7);
+    p = fma(p, r, 0x1.5555555553d6fp-5);
+    p = fma(p, r, 0x1.5555555555555p-3);
+    p = fma(p, r, 0x1.0000000000001p-1);
+    p = fma(p, r * r, r);
+    p += 1.0;
+    return __hiloint2double(__double2hiint(p) + (k << 20), __double2loint(p));
+}
+
+// exp(a) for |a| <= 700 (same kernel as pb_exp_neg, two-sided); used for 10**v = exp(v ln10) of the
+// molecular tables, where |v| <= 50 keeps the extra rounding of v*ln10 below 1e-14 relative.
+__device__ __forceinline__ double pb_exp(double a) {
+    a = fmax(fmin(a, 700.0), -700.0);
+    const double kMagic = 6755399441055744.0;
+    double kd = fma(a, 1.4426950408889634, kMagic);
+    const int k = __double2loint(kd);
+    kd -= kMagic;
+    double r = fma(kd, -6.93147180369123816490e-01, a);
+    r = fma(kd, -1.90821492927058770002e-10, r);
+    double p = 0x1.af354eec9216ep-26;
+    p = fma(p, r, 0x1.28917965df995p-22);
+    p = fma(p, r, 0x1.71de0fd1838abp-19);
+    p = fma(p, r, 0x1.a019b9189c259p-16);
+    p = fma(p, r, 0x1.a01a01a6cffcap-13);
+    p = fma(p, r, 0x1.6c16c178884cep-10);
+    p = fma(p, r, 0x1.1111111110c74p-7);
+    p = fma(p, r, 0x1.5555555553d6fp-5);
+    p = fma(p, r, 0x1.5555555555555p-3);
+    p = fma(p, r, 0x1.0000000000001p-1);
+    p = fma(p, r * r, r);
+    p += 1.0;
+    return __hiloint2double(__double2hiint(p) + (k << 20), __double2loint(p));
+}
+
+// ---------------------------------------------------------------------------------------------
+// np.interp semantics on a sorted table (numba's implementation follows numpy's
+// compiled_base.c): clamp to the end values outside [x0, x_{n-1}], otherwise
+// slope*(x - x_j) + y_j with j = largest index with x_j <= x.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ int64_t pb_search_le(const double* __restrict__ xs, int64_t n, double x) {
+    // largest j in [0, n-2] with xs[j] <= x  (x is inside (xs[0], xs[n-1]))
+    int64_t lo = 0, hi = n - 1;
+    while (hi - lo > 1) {
+        const int64_t mid = (lo + hi) >> 1;
+        if (__ldg(xs + mid) <= x) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
+__device__ __forceinline__ double pb_interp(const double* __restrict__ xs,
+                                            const double* __restrict__ ys, int64_t n, double x) {
+    if (!(x == x)) return x;  // NaN passes through
+    if (n == 1) return __ldg(ys);
+    if (x <= __ldg(xs)) return __ldg(ys);
+    if (x >= __ldg(xs + n - 1)) return __ldg(ys + n - 1);
+    const int64_t j = pb_search_le(xs, n, x);
+    const double x0 = __ldg(xs + j), x1 = __ldg(xs + j + 1);
+    const double y0 = __ldg(ys + j), y1 = __ldg(ys + j + 1);
+    const double slope = (y1 - y0) / (x1 - x0);
+    return slope * (x - x0) + y0;
+}
+
+__device__ __forceinline__ double pb_interp_log(const double* __restrict__ xs,
+                                                const double* __restrict__ ys, int64_t n, double x,
+                                                double offset) {
+    return exp10(pb_interp(xs, ys, n, x)) - offset;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Re w(x + iy), y >= 0 (Faddeeva function).  Own two-region algorithm, validated against
+// scipy.special.wofz to <= 3e-14 relative over |x| <= 1e5, 1e-8 <= y <= 10 (tests/test_voigt.py):
+//   |z|^2 >= 100 : asymptotic series  w ~ i/(sqrt(pi) z) * sum_k (2k-1)!!/2^k z^-2k, 2..12 terms
+//   otherwise    : trapezoid rule for (i/pi) int e^{-t^2}/(z-t) dt with step h = 1/2 on nodes
+//                  t_n = x + (n+1/2)h that straddle x symmetrically; every term is positive and
+//                  the pole correction 2 e^{-z^2}/(1 + e^{2 pi y/h}) is free of cancellation
+//                  (residual error e^{-pi^2/h^2} = 7e-18).
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ double pb_faddeeva_re_far(double x, double y, double r2) {
+    // u = 1/z^2 = conj(z)^2 / |z|^4
+    const double inv = 1.0 / r2;
+    const double ur = (x * x - y * y) * inv * inv;
+    const double ui = -2.0 * x * y * inv * inv;
+    int nt;
+    if (r2 >= 1e8) nt = 2; else if (r2 >= 1e6) nt = 3; else if (r2 >= 1e5) nt = 4;
+    else if (r2 >= 1e4) nt = 5; else if (r2 >= 1e3) nt = 6; else if (r2 >= 400.0) nt = 8;
+    else if (r2 >= 256.0) nt = 9; else if (r2 >= 144.0) nt = 10; else nt = 12;
+    // c_k = (2k-1)!!/2^k
+    const double c[12] = {1.0, 0.5, 0.75, 1.875, 6.5625, 29.53125, 162.421875, 1055.7421875,
+                          7918.06640625, 67303.564453125, 639383.8623046875, 6713530.554199219};
+    double sr = 0.0, si = 0.0;
+#pragma unroll 1
+    for (int k = nt - 1; k >= 0; --k) {
+        const double tr = fma(sr, ur, -si * ui) + c[k];
+        si = fma(sr, ui, si * ur);
+        sr = tr;
+    }
+    // w = i/(sqrt(pi) z) * s ;  i/z = (y + i x)/|z|^2  ->  Re = (y*sr - x*si)/(sqrt(pi)|z|^2)
+    return 0.5641895835477563 * (y * sr - x * si) * inv;
+}
+
+static __device__ __noinline__ double pb_faddeeva_re_near(double x, double y) {
+    const double h = 0.5, T = 6.3;
+    const double ax = fabs(x);
+    // nodes t = ax + (n + 1/2) h with |t| < T
+    const int n_lo = (int)ceil((-T - ax) / h - 0.5);
+    const int n_hi = (int)floor((T - ax) / h - 0.5);
+    const double y2 = y * y;
+    double s = 0.0;
+    for (int n = n_lo; n <= n_hi; ++n) {
+        const double u = (n + 0.5) * h;
+        const double t = ax + u;
+        s += exp(-t * t) / fma(u, u, y2);
+    }
+    s *= h * y / kPi;
+    if (y < 5.0) {
+        const double g = 2.0 * exp(y2 - ax * ax) * cos(2.0 * ax * y) / (1.0 + exp(2.0 * kPi * y / h));
+        s += g;
+    }
+    return s;
+}
+
+__device__ __forceinline__ double pb_faddeeva_re(double x, double y) {
+    const double r2 = fma(x, x, y * y);
+    if (r2 >= 100.0) return pb_faddeeva_re_far(x, y, r2);
+    return pb_faddeeva_re_near(x, y);
+}
+
+// scipy.special.voigt_profile(x, sigma, gamma) incl. its degenerate branches
+__device__ __forceinline__ double pb_voigt(double x, double sigma, double gamma) {
+    const double kInvSqrt2 = 0.7071067811865476;
+    const double kSqrt2Pi = 2.5066282746310002;
+    if (sigma == 0.0) {
+        if (gamma == 0.0) return (x == 0.0) ? INFINITY : 0.0;
+        return gamma / kPi / (x * x + gamma * gamma);
+    }
+    if (gamma == 0.0) {
+        const double q = x / sigma;
+        return 1.0 / kSqrt2Pi / sigma * exp(-0.5 * q * q);
+    }
+    const double zr = x / sigma * kInvSqrt2;
+    const double zi = gamma / sigma * kInvSqrt2;
+    return pb_faddeeva_re(zr, zi) / sigma / kSqrt2Pi;
+}
+
+// warp-level fp64 sum, result in every lane
+__device__ __forceinline__ double pb_warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+}  // namespace pb200

@@ -1,0 +1,197 @@
+// pb200_sigma.cu -- kernels (b1)/(b2): cross-section lookup and Voigt line synthesis, the
+// materialised optical depth, and the FP64 machine probes.  SURVEY 8(a) rows a8-a11.
+#include "pb200_internal.cuh"
+#include "pb200_molecule.cuh"
+
+namespace pb200 {
+
+// ---- (b1) n_interp_log (gasProperties.py:34-51): out = 10**interp(wl) - offset ------------------
+__global__ void sigma_lookup_kernel(const double* __restrict__ tab_x, const double* __restrict__ tab_y,
+                                    int64_t n_tab, double offset, const double* __restrict__ wl, int64_t n,
+                                    double* __restrict__ out) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        out[i] = pb_interp_log(tab_x, tab_y, n_tab, wl[i], offset);
+}
+
+// sigma_u[a][p][w] = sigma_a(shift_a(p) * lambda_w): the reference's cached per-unique-shift table
+// (gasProperties.py:941-953), materialised only for pb200_optical_depth.
+__global__ void sigma_u_kernel(const DevScene* __restrict__ scp, int64_t wav_lo, int64_t n_wav_sel,
+                               double* __restrict__ out) {
+    const DevScene& sc = *scp;
+    const int a = blockIdx.z, p = blockIdx.y;
+    int k = 0;
+    for (; k < sc.n_cons; ++k)
+        if (sc.cons[k].kind == 0 && sc.cons[k].atom_index == a) break;
+    const DevConstituent& C = sc.cons[k];
+    const double shift = sc.scen[C.scenario].shift[p];
+    for (int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; w < n_wav_sel; w += (int64_t)gridDim.x * blockDim.x)
+        out[((int64_t)a * sc.n_orb + p) * n_wav_sel + w] =
+            pb_interp_log(C.tab_x, C.tab_y, C.n_tab, shift * sc.wavelength[wav_lo + w], C.offset);
+}
+
+// ---- (b2) Voigt synthesis: sigma(wl) = sum_lines K f V(c/wl - c/wl0; sigma_v/wl0, gamma) -------
+// One thread per wavelength, line parameters staged through shared memory in chunks, the line sum
+// lives in a register; one coalesced store per wavelength.  (gasProperties.py:672-692)
+constexpr int kLineChunk = 1024;
+
+__global__ void __launch_bounds__(256)
+voigt_sigma_kernel(const double* __restrict__ line_wl, const double* __restrict__ line_gamma,
+                   const double* __restrict__ line_f, int64_t n_lines, double sigma_v,
+                   const double* __restrict__ wl, int64_t n, double offset, double* __restrict__ out_sigma,
+                   double* __restrict__ out_log10) {
+    __shared__ double s_nu0[kLineChunk], s_rs[kLineChunk], s_zi[kLineChunk], s_amp[kLineChunk];
+    const double kInvSqrt2 = 0.7071067811865476, kSqrt2Pi = 2.5066282746310002;
+    // np.pi * e**2 / (m_e * c), evaluated left to right as the reference does (:689-690)
+    const double K = (kPi * (kElemCharge * kElemCharge)) / (kElectronMass * kLightSpeed);
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const double nu = (i < n) ? kLightSpeed / wl[i] : 0.0;
+    double acc = 0.0;
+    for (int64_t l0 = 0; l0 < n_lines; l0 += kLineChunk) {
+        const int cnt = (int)((n_lines - l0 < kLineChunk) ? n_lines - l0 : kLineChunk);
+        __syncthreads();
+        for (int l = threadIdx.x; l < cnt; l += blockDim.x) {
+            const double w0 = line_wl[l0 + l];
+            const double sig_nu = sigma_v / w0;           // :688
+            const double rs = 1.0 / sig_nu;
+            s_nu0[l] = kLightSpeed / w0;
+            s_rs[l] = rs * kInvSqrt2;
+            s_zi[l] = line_gamma[l0 + l] * rs * kInvSqrt2;
+            s_amp[l] = K * line_f[l0 + l] * (rs / kSqrt2Pi);
+        }
+        __syncthreads();
+        if (i < n) {
+            for (int l = 0; l < cnt; ++l) {
+                const double zr = (nu - s_nu0[l]) * s_rs[l];
+                acc = fma(s_amp[l], pb_faddeeva_re(zr, s_zi[l]), acc);
+            }
+        }
+    }
+    if (i < n) {
+        if (out_sigma) out_sigma[i] = acc;
+        if (out_log10) out_log10[i] = log10(acc + offset);   // :713-714
+    }
+}
+
+__global__ void voigt_profile_kernel(const double* __restrict__ x, const double* __restrict__ sigma,
+                                     const double* __restrict__ gamma, int64_t n, double* __restrict__ out) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        out[i] = pb_voigt(x[i], sigma[i], gamma[i]);
+}
+
+// ---- MolecularConstituent.getSigmaAbs materialised (gasProperties.py:789-818) -------------------
+__global__ void molecular_sigma_kernel(MolTable tab, double offset, const double* __restrict__ P, double T,
+                                       const double* __restrict__ wl, int64_t n_c, int64_t n_x, int64_t n_wav,
+                                       double* __restrict__ out) {
+    const int64_t total = n_c * n_x * n_wav;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t w = i % n_wav, cx = i / n_wav, c = cx / n_x;
+        const double Pc = fmax(P[cx], 1e-4);    // np.clip(P, a_min=1e-4) :805
+        out[i] = exp10(pb_mol_log_sigma(tab, Pc, T, wl[c * n_wav + w])) - offset;   // :814
+    }
+}
+
+// ---- getLOSopticalDepth_Batch materialised (gasProperties.py:885-956) ---------------------------
+// tau[c][w], c = m*n_orb + p (reference chord order).  One CTA per (chord, wavelength tile).
+__global__ void __launch_bounds__(256)
+optical_depth_kernel(const DevScene* __restrict__ scp, const double* __restrict__ sigma_u, int64_t wav_lo,
+                     int64_t n_wav_sel, int64_t chord0, double* __restrict__ tau) {
+    const DevScene& sc = *scp;
+    const int64_t c = chord0 + blockIdx.y;
+    const int m = (int)(c / sc.n_orb), p = (int)(c % sc.n_orb);
+    const int64_t row = (int64_t)p * sc.Mp + m;
+    for (int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; w < n_wav_sel; w += (int64_t)gridDim.x * blockDim.x) {
+        double t = 0.0;
+        for (int k = 0; k < sc.n_cons; ++k) {
+            const DevConstituent& C = sc.cons[k];
+            const DevScenario& S = sc.scen[C.scenario];
+            if (C.kind == 0) {
+                const double N = sc.ncol[(int64_t)C.atom_index * sc.n_orb * sc.Mp + row];
+                t += N * sigma_u[((int64_t)C.atom_index * sc.n_orb + p) * n_wav_sel + w];     // :954
+            } else {
+                MolTable tab = pb_mol_table(C);
+                const double lam = S.shift[p] * sc.wavelength[wav_lo + w];
+                const double* dens = sc.density[S.density_slot] + ((int64_t)p * sc.M + m) * sc.n_x;
+                double s = 0.0;
+                for (int ix = 0; ix < sc.n_x; ++ix) {
+                    const double n = dens[ix];
+                    const double Pc = fmax(n * kBoltzmann * S.T, 1e-4);                       // :927, :805
+                    const double sg = exp10(pb_mol_log_sigma(tab, Pc, S.T, lam)) - C.offset;
+                    s = fma(n * C.chi, sg, s);                                                // :932-936
+                }
+                t += s * sc.delta_x;
+            }
+        }
+        tau[c * n_wav_sel + w] = t;
+    }
+}
+
+// ---- FP64 probes: DFMA chain and exp throughput --------------------------------------------------
+__global__ void __launch_bounds__(256) probe_dfma_kernel(double* out, int iters) {
+    double a0 = threadIdx.x * 1e-9, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
+    const double b = 1.0000001, c = 1e-9;
+    for (int i = 0; i < iters; ++i) {
+        a0 = fma(a0, b, c); a1 = fma(a1, b, c); a2 = fma(a2, b, c); a3 = fma(a3, b, c);
+        a4 = fma(a4, b, c); a5 = fma(a5, b, c); a6 = fma(a6, b, c); a7 = fma(a7, b, c);
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+}
+__global__ void __launch_bounds__(256) probe_exp_kernel(double* out, int iters) {
+    double t0 = 1e-3 * (threadIdx.x + 1), t1 = t0 * 1.5, t2 = t0 * 2.5, t3 = t0 * 3.5;
+    double s0 = 0, s1 = 0, s2 = 0, s3 = 0;
+    for (int i = 0; i < iters; ++i) {
+        s0 = fma(0.5, pb_exp_neg(t0), s0); s1 = fma(0.5, pb_exp_neg(t1), s1);
+        s2 = fma(0.5, pb_exp_neg(t2), s2); s3 = fma(0.5, pb_exp_neg(t3), s3);
+        t0 += 1e-7; t1 += 1e-7; t2 += 1e-7; t3 += 1e-7;
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s0 + s1 + s2 + s3;
+}
+
+// ---- launchers ------------------------------------------------------------------------------------
+static inline unsigned blocks_for(int64_t n, int threads, int sm_count) {
+    int64_t b = (n + threads - 1) / threads;
+    const int64_t cap = (int64_t)sm_count * 16;
+    if (b > cap) b = cap;
+    return (unsigned)(b > 0 ? b : 1);
+}
+void launch_sigma_lookup(const double* tx, const double* ty, int64_t n_tab, double offset, const double* wl,
+                         int64_t n, double* out, int sm_count, cudaStream_t st) {
+    sigma_lookup_kernel<<<blocks_for(n, 256, sm_count), 256, 0, st>>>(tx, ty, n_tab, offset, wl, n, out);
+}
+void launch_sigma_u(const DevScene* d_scene, int n_atoms, int n_orb, int64_t wav_lo, int64_t n_wav_sel,
+                    double* out, int sm_count, cudaStream_t st) {
+    dim3 grid(blocks_for(n_wav_sel, 256, sm_count), n_orb, n_atoms);
+    sigma_u_kernel<<<grid, 256, 0, st>>>(d_scene, wav_lo, n_wav_sel, out);
+}
+void launch_voigt_sigma(const double* lw, const double* lg, const double* lf, int64_t n_lines, double sigma_v,
+                        const double* wl, int64_t n, double offset, double* out_sigma, double* out_log10,
+                        cudaStream_t st) {
+    voigt_sigma_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(lw, lg, lf, n_lines, sigma_v, wl, n, offset,
+                                                                    out_sigma, out_log10);
+}
+void launch_voigt_profile(const double* x, const double* s, const double* g, int64_t n, double* out, int sm_count,
+                          cudaStream_t st) {
+    voigt_profile_kernel<<<blocks_for(n, 256, sm_count), 256, 0, st>>>(x, s, g, n, out);
+}
+void launch_molecular_sigma(const MolTable& tab, double offset, const double* P, double T, const double* wl,
+                            int64_t n_c, int64_t n_x, int64_t n_wav, double* out, int sm_count, cudaStream_t st) {
+    molecular_sigma_kernel<<<blocks_for(n_c * n_x * n_wav, 256, sm_count), 256, 0, st>>>(tab, offset, P, T, wl, n_c,
+                                                                                         n_x, n_wav, out);
+}
+void launch_optical_depth(const DevScene* d_scene, const double* sigma_u, int64_t n_chords, int64_t wav_lo,
+                          int64_t n_wav_sel, double* tau, cudaStream_t st) {
+    unsigned bx = (unsigned)((n_wav_sel + 255) / 256);
+    if (bx > 64) bx = 64;
+    // gridDim.y is limited to 65535: chunk the chord axis
+    for (int64_t c0 = 0; c0 < n_chords; c0 += 65535) {
+        const unsigned by = (unsigned)((n_chords - c0 < 65535) ? n_chords - c0 : 65535);
+        optical_depth_kernel<<<dim3(bx, by), 256, 0, st>>>(d_scene, sigma_u, wav_lo, n_wav_sel, c0, tau);
+    }
+}
+void launch_probe_dfma(double* out, int blocks, int iters, cudaStream_t st) {
+    probe_dfma_kernel<<<blocks, 256, 0, st>>>(out, iters);
+}
+void launch_probe_exp(double* out, int blocks, int iters, cudaStream_t st) {
+    probe_exp_kernel<<<blocks, 256, 0, st>>>(out, iters);
+}
+
+}  // namespace pb200

@@ -1,0 +1,192 @@
+"""Flattens a Transit object graph into the pb200_scene POD of the C ABI.
+
+Works on anything that quacks like the reference's objects ("state read through the
+seam"): the reference's own `Transit` (drop-in use) or the host mirror in
+`prometheus_b200.host`.  Only O(axis) host work happens here -- axes, per-phase body positions and
+Doppler factors are evaluated by the objects' own methods, so chord/grid indexing is bit-exact with
+whatever host code produced them.  Everything O(chords) and above runs on the GPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+
+import numpy as np
+
+from . import capi
+from . import constants as const
+
+_PLANET_CENTRED = {"BarometricAtmosphere", "HydrostaticAtmosphere", "PowerLawAtmosphere",
+                   "PowerLawExosphere", "TorusExosphere"}
+_MOON_CENTRED = {"MoonExosphere", "TidallyHeatedMoon"}
+
+
+def _kind(obj) -> str:
+    """Scenario class name; subclasses of the reference classes resolve through the MRO."""
+    for klass in type(obj).__mro__:
+        if klass.__name__ in _PLANET_CENTRED or klass.__name__ in _MOON_CENTRED or klass.__name__ == "SerpensExosphere":
+            return klass.__name__
+    raise capi.Pb200Error(-4, f"unsupported density scenario {type(obj).__name__}")
+
+
+def scenario_parameters(dist) -> tuple[int, list[float]]:
+    """(pb200_scenario_type, p[8]) -- the scalar part of SURVEY 8(a) row a7."""
+    name = _kind(dist)
+    kB, G = const.k_B, const.G
+    if name == "BarometricAtmosphere":          # gasProperties.py:156-158
+        pl = dist.planet
+        n0 = dist.P_0 / (kB * dist.T)
+        H = kB * dist.T * pl.R ** 2 / (G * dist.mu * pl.M)
+        return capi.SCN_BAROMETRIC, [n0, pl.R, H]
+    if name == "HydrostaticAtmosphere":         # gasProperties.py:198-202
+        pl = dist.planet
+        n0 = dist.P_0 / (kB * dist.T)
+        return capi.SCN_HYDROSTATIC, [n0, pl.R, G * dist.mu * pl.M, kB * dist.T]
+    if name == "PowerLawAtmosphere":            # gasProperties.py:241-242
+        pl = dist.planet
+        return capi.SCN_POWERLAW, [dist.P_0 / (kB * dist.T), pl.R, dist.q]
+    if name == "PowerLawExosphere":             # gasProperties.py:327
+        pl = dist.planet
+        return capi.SCN_POWERLAW, [(dist.q - 3.0) / (4.0 * np.pi * pl.R ** 3) * dist.N, pl.R, dist.q]
+    if name == "MoonExosphere":                 # gasProperties.py:372
+        mo = dist.moon
+        return capi.SCN_POWERLAW, [(dist.q - 3.0) / (4.0 * np.pi * mo.R ** 3) * dist.N, mo.R, dist.q]
+    if name == "TidallyHeatedMoon":             # gasProperties.py:459 (N enters per phase)
+        mo = dist.moon
+        return capi.SCN_POWERLAW, [(dist.q - 3.0) / (4.0 * np.pi * mo.R ** 3), mo.R, dist.q]
+    if name == "TorusExosphere":                # gasProperties.py:507-514
+        pl = dist.planet
+        v_orbit = np.sqrt(G * pl.M / dist.a_torus)
+        H = dist.a_torus * dist.v_ej / v_orbit
+        term1 = 8.0 * H ** 2 * np.exp(-dist.a_torus ** 2 / (16.0 * H ** 2))
+        term2 = 2.0 * np.sqrt(np.pi) * dist.a_torus * H * (math.erf(dist.a_torus / (4.0 * H)) + 1.0)
+        n0 = 1.0 / (2.0 * np.pi ** 1.5 * H * (term1 + term2)) * dist.N
+        return capi.SCN_TORUS, [n0, dist.a_torus, H]
+    if name == "SerpensExosphere":
+        return capi.SCN_SERPENS, []
+    raise capi.Pb200Error(-4, f"unsupported density scenario {name}")
+
+
+class SceneBuilder:
+    """Collects numpy arrays (kept alive for the duration of pb200_set_scene) and fills the structs."""
+
+    def __init__(self):
+        self.keep = []
+
+    def arr(self, a) -> np.ndarray:
+        a = capi.as_f64(a)
+        self.keep.append(a)
+        return a
+
+    def ptr(self, a):
+        return capi.dptr(self.arr(a))
+
+    def per_phase(self, v, n_orb):
+        return self.ptr(np.broadcast_to(np.asarray(v, dtype=np.float64), (n_orb,)))
+
+
+def flatten(transit, wavelength=None) -> tuple[capi.Scene, list, dict]:
+    """Transit-like object -> (pb200_scene, keep-alive list, info)."""
+    b = SceneBuilder()
+    grid = transit.spatialGrid
+    atmos = transit.atmosphere
+    dists = list(atmos.densityDistributionList)
+    planet = getattr(transit, "planet", None) or dists[0].planet
+    star = planet.hostStar
+    if wavelength is None:
+        wavelength = transit.wavelength
+    wavelength = np.asarray(wavelength, dtype=np.float64)
+
+    x = np.asarray(grid.constructXaxis(), dtype=np.float64)
+    rho = np.asarray(grid.constructRhoAxis(), dtype=np.float64)
+    phi = np.asarray(grid.constructPhiAxis(), dtype=np.float64)
+    phase = np.asarray(grid.constructOrbphaseAxis(), dtype=np.float64)
+    n_orb = phase.size
+
+    sc = capi.Scene()
+    sc.abi_version = capi.ABI_VERSION
+    sc.n_x, sc.n_rho, sc.n_phi, sc.n_orb, sc.n_wav = x.size, rho.size, phi.size, n_orb, wavelength.size
+    sc.x, sc.rho = b.ptr(x), b.ptr(rho)
+    sc.sin_phi, sc.cos_phi = b.ptr(np.sin(phi)), b.ptr(np.cos(phi))            # geometryHandler.py:84-85
+    sc.cos_phi_rot = b.ptr(np.cos(phi - star.phiStarrot))                        # gasProperties.py:1182
+    sc.wavelength = b.ptr(wavelength)
+    sc.delta_x = float(grid.getDeltaX())
+    sc.star_R, sc.clv_u1, sc.clv_u2 = float(star.R), float(star.CLV_u1), float(star.CLV_u2)
+    sc.vsini = float(star.vsiniStarrot)
+    fstar = getattr(star, "Fstar_function", None)
+    if fstar is not None:
+        sc.fstar_x, sc.fstar_y, sc.n_fstar = b.ptr(fstar.x), b.ptr(fstar.y), int(np.size(fstar.x))
+    sc.planet_R = float(planet.R)
+    sc.planet_y = b.ptr(planet.a * np.sin(phase))                                # gasProperties.py:1224
+
+    moons_R, moons_y = [], []
+    for dist in dists:
+        if getattr(dist, "hasMoon", False):                                      # gasProperties.py:1226-1230
+            moons_R.append(float(dist.moon.R))
+            moons_y.append(np.broadcast_to(np.asarray(dist.moon.getPosition(phase)[1], dtype=np.float64), (n_orb,)))
+    sc.n_moons = len(moons_R)
+    if moons_R:
+        sc.moon_R = b.ptr(np.array(moons_R))
+        sc.moon_y = b.ptr(np.concatenate(moons_y))
+
+    scn_arr = (capi.Scenario * len(dists))()
+    cons_list = []
+    for i, dist in enumerate(dists):
+        q = scn_arr[i]
+        q.type, params = scenario_parameters(dist)
+        for j, v in enumerate(params):
+            q.p[j] = float(v)
+        q.T = float(getattr(dist, "T", 0.0) or 0.0)
+        has_moon = bool(getattr(dist, "hasMoon", False))
+        body = dist.moon if has_moon else dist.planet
+        if q.type != capi.SCN_SERPENS:
+            cx, cy = body.getPosition(phase)                                     # celestialBodies.py:370-383, :518-531
+            q.centre_x, q.centre_y = b.per_phase(cx, n_orb), b.per_phase(cy, n_orb)
+        else:
+            tab = dist.InterpolatedDensity
+            gx, gy, gz = tab.grid
+            q.gx, q.gy, q.gz = b.ptr(gx), b.ptr(gy), b.ptr(gz)
+            vals = np.asarray(tab.values, dtype=np.float64)
+            q.values = b.ptr(vals)
+            q.dims[0], q.dims[1], q.dims[2] = vals.shape
+        if atmos.hasOrbitalDopplerShift:                                         # gasProperties.py:908-916
+            v_los = body.getLOSvelocity(phase)
+        else:
+            v_los = np.zeros(n_orb)
+        q.shift = b.per_phase(const.calculateDopplerShift(-np.asarray(v_los, dtype=np.float64)), n_orb)
+        if _kind(dist) == "TidallyHeatedMoon":                                   # gasProperties.py:425-436
+            q.amplitude = b.per_phase(dist.calculateAbsorberNumber(phase), n_orb)
+        q.first_constituent = len(cons_list)
+        q.n_constituents = len(dist.constituents)
+        for con in dist.constituents:
+            cons_list.append((con, dist))
+
+    cons_arr = (capi.Constituent * max(len(cons_list), 1))()
+    n_atoms = n_mols = 0
+    for k, (con, dist) in enumerate(cons_list):
+        q = cons_arr[k]
+        q.chi, q.offset = float(con.chi), float(con.lookupOffset)
+        lf = con.lookupFunction
+        if con.isMolecule:
+            q.kind = 1
+            gP, gT, gW = lf.grid                                                 # gasProperties.py:779
+            vals = np.asarray(lf.values, dtype=np.float64)
+            q.grid_P, q.grid_T, q.grid_w, q.values = b.ptr(gP), b.ptr(gT), b.ptr(gW), b.ptr(vals)
+            q.dims[0], q.dims[1], q.dims[2] = vals.shape
+            fill = getattr(lf, "fill_value", None)
+            q.fill = float(fill) if fill is not None else float("nan")
+            n_mols += 1
+        else:
+            q.kind = 0
+            q.tab_x, q.tab_y, q.n_tab = b.ptr(lf.x), b.ptr(lf.y), int(np.size(lf.x))   # gasProperties.py:730-735
+            n_atoms += 1
+    sc.n_scenarios, sc.n_constituents = len(dists), len(cons_list)
+    sc.scenarios = C.cast(scn_arr, C.POINTER(capi.Scenario))
+    sc.constituents = C.cast(cons_arr, C.POINTER(capi.Constituent))
+    b.keep += [scn_arr, cons_arr]
+
+    h2d = sum(a.nbytes for a in b.keep if isinstance(a, np.ndarray))
+    info = {"n_x": x.size, "n_rho": rho.size, "n_phi": phi.size, "n_orb": n_orb, "n_wav": wavelength.size,
+            "n_chords": rho.size * phi.size * n_orb, "n_atoms": n_atoms, "n_mols": n_mols,
+            "h2d_bytes": int(h2d)}
+    return sc, b.keep, info

@@ -1,0 +1,148 @@
+"""Generates the golden fixtures in tests/golden/ by running the UNMODIFIED reference.
+
+Run in the build container only (it needs /root/reference; the GPU box does not have it):
+
+    python tests/golden/make_golden.py [case ...]
+
+For every case of prometheus_b200.workloads.GOLDEN_CASES it builds the reference's own objects
+through the reference's public classes (builder.build_transit with a namespace that points at the
+reference modules), calls the reference's Transit.sumOverChords and friends, and stores inputs and
+outputs as <case>.npz.  h5py / astropy are absent from this image and are never reached on this
+path, so two empty stub modules stand in for them.
+"""
+from __future__ import annotations
+
+import os
+import sys
+import time
+import types
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+
+
+def import_reference():
+    for m in ["h5py", "astropy", "astropy.io", "astropy.io.fits"]:
+        sys.modules.setdefault(m, types.ModuleType(m))
+    sys.modules["astropy"].io = sys.modules["astropy.io"]
+    sys.modules["astropy.io"].fits = sys.modules["astropy.io.fits"]
+    if "/root" not in sys.path:
+        sys.path.insert(0, "/root")
+    import reference.pythonScripts.celestialBodies as bodies
+    import reference.pythonScripts.constants as consts
+    import reference.pythonScripts.gasProperties as gasprop
+    import reference.pythonScripts.geometryHandler as geom
+    return gasprop, bodies, geom, consts
+
+
+class ReferenceNamespace:
+    def __init__(self):
+        from scipy.interpolate import RegularGridInterpolator, interp1d
+        self.gas, self.bodies, self.geom, self.consts = import_reference()
+        self.Species = self.consts.Species
+        self.findSpecies = lambda name: self.consts.AvailableSpecies().findSpecies(name)
+        self._interp1d, self._rgi = interp1d, RegularGridInterpolator
+        self.nist_rows = np.array(self.gas.LINE_LIST, dtype=str)
+
+        # SerpensExosphere.calculateNumberDensity is scalar-only in the reference and raises for the batch
+        # call: evaluate the reference's own scalar method chord by chord.
+        scalar = self.gas.SerpensExosphere.calculateNumberDensity
+
+        def batch(obj, x, phi, rho, orbphase):
+            if np.ndim(phi) == 0:
+                return scalar(obj, x, phi, rho, orbphase)
+            return np.stack([scalar(obj, x, phi[i], rho[i], orbphase[i]) for i in range(len(phi))])
+
+        self.gas.SerpensExosphere.calculateNumberDensity = batch
+
+    def set_line_list(self, rows):
+        self.gas.LINE_LIST = np.asarray(rows, dtype=str)
+
+    def table_1d(self, x, y):
+        return self._interp1d(x, y, kind="linear")
+
+    def table_nd(self, grid, values, fill_value=None, bounds_error=False):
+        if bounds_error:
+            return self._rgi(grid, values)
+        return self._rgi(grid, values, bounds_error=False, fill_value=fill_value)
+
+
+def run_case(ns, name, out_dir=HERE):
+    from prometheus_b200 import builder, workloads
+    spec = workloads.get(name)
+    t0 = time.time()
+    tr = builder.build_transit(spec, ns=ns, nist_rows=ns.nist_rows)
+    t_build = time.time() - t0
+    t0 = time.time()
+    R = tr.sumOverChords(2.0)
+    t_run = time.time() - t0
+
+    # opaque-disk value R0: the reference's own sumOverChords with tau == 0
+    atm = tr.atmosphere
+    real = atm.getLOSopticalDepth_Batch
+    atm.getLOSopticalDepth_Batch = lambda x, phi, rho, orb, wl, dx: np.zeros((len(phi), len(wl)))
+    R0 = tr.sumOverChords(2.0)
+    atm.getLOSopticalDepth_Batch = real
+
+    grid = tr.spatialGrid
+    chords = grid.getChordGrid()
+    phi, rho, orb = chords[:, 0], chords[:, 1], chords[:, 2]
+    x = grid.constructXaxis()
+    n_c = len(chords)
+    # a deterministic subset of chords for the heavier intermediate quantities
+    sub = np.unique(np.linspace(0, n_c - 1, min(n_c, 512, max(32, 100000 // len(tr.wavelength)))).astype(np.int64))
+    out = {
+        "R": R, "R0": R0, "wavelength": tr.wavelength,
+        "x": x, "rho": grid.constructRhoAxis(), "phi": grid.constructPhiAxis(), "orb": grid.constructOrbphaseAxis(),
+        "delta_x": np.float64(grid.getDeltaX()), "chord_subset": sub,
+        "chord_grid_head": chords[:64], "chord_grid_tail": chords[-64:],
+    }
+    # blocking mask exactly as sumOverChords computes it (gasProperties.py:1224-1230)
+    y, z = rho * np.sin(phi), rho * np.cos(phi)
+    blocked = np.sqrt((y - tr.planet.a * np.sin(orb)) ** 2 + z ** 2) < tr.planet.R
+    for dist in atm.densityDistributionList:
+        if dist.hasMoon:
+            blocked |= (y - dist.moon.getPosition(orb)[1]) ** 2 + z ** 2 < dist.moon.R ** 2
+    out["blocked"] = np.packbits(blocked)
+    out["n_blocked"] = np.int64(blocked.sum())
+
+    k = 0
+    for i, dist in enumerate(atm.densityDistributionList):
+        n_sub = dist.calculateNumberDensity(x, phi[sub], rho[sub], orb[sub])
+        out[f"density_{i}"] = n_sub
+        n_all = dist.calculateNumberDensity(x, phi, rho, orb)
+        for con in dist.constituents:
+            if con.isMolecule:
+                continue
+            out[f"ncol_{k}"] = np.sum(n_all * con.chi, axis=1) * grid.getDeltaX()
+            tx, ty = con.lookupFunction.x, con.lookupFunction.y
+            out[f"table_n_{k}"] = np.int64(len(tx))
+            stride = max(1, len(tx) // 20000)
+            out[f"table_stride_{k}"] = np.int64(stride)
+            out[f"table_x_{k}"] = tx[::stride]
+            out[f"table_y_{k}"] = ty[::stride]
+            out[f"table_xsum_{k}"] = np.float64(np.sum(tx))
+            k += 1
+    out["tau_sub"] = atm.getLOSopticalDepth_Batch(x, phi[sub], rho[sub], orb[sub], tr.wavelength, grid.getDeltaX())
+    out["timing"] = np.array([t_build, t_run])
+    path = os.path.join(out_dir, f"{name}.npz")
+    np.savez_compressed(path, **out)
+    print(f"{name}: n_c={n_c} n_wav={len(tr.wavelength)} build {t_build:.1f}s run {t_run:.1f}s "
+          f"R in [{R.min():.6f}, {R.max():.6f}] -> {os.path.getsize(path) / 1e6:.2f} MB", flush=True)
+
+
+def main(argv):
+    from prometheus_b200 import workloads
+    ns = ReferenceNamespace()
+    ll = os.path.join(HERE, "linelist.npz")
+    np.savez_compressed(ll, rows=ns.nist_rows)
+    print("line list rows:", ns.nist_rows.shape)
+    for name in (argv or workloads.GOLDEN_CASES):
+        run_case(ns, name)
+
+
+if __name__ == "__main__":
+    main(sys.argv[1:])
