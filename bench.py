@@ -1,0 +1,440 @@
+#!/usr/bin/env python
+"""bench.py -- chord*lambda samples/s of the transit hot path on N B200s, next to the CPU path.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload C4] [--impl reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port P bench.py --gpus N --steps K --warmup W
+
+One "step" = one complete Transit.sumOverChords of the workload (kernels (a') + (c') [+ split
+reduction]) -> R(phase, lambda).  Workload at N GPUs (weak scaling): the named config with its
+wavelength resolution refined N-fold, so n_wav ~ N x the single-GPU n_wav; rank r owns the r-th
+contiguous wavelength chunk of every orbital phase; the only collective is the final
+all-gather of the R tiles (NCCL).  Prints ONE JSON line on rank 0.
+
+  value      whole-job chord*lambda samples/s, scene resident in HBM, CUDA-event timed, max over ranks
+  e2e        same metric through the host API with HOST buffers: scene flattening + H2D upload from
+             pinned memory + kernels + gather + D2H of R inside the timed region
+  roofline   kernel (c') against the measured HBM peak on the north star's staged-equivalent
+             convention (16 B per chord*lambda sample); plus its FP64-pipe fraction
+  cpu_baseline / --impl reference
+             the CPU restatement of the reference algorithm (oracle/, numpy+scipy like the
+             reference itself) on all host cores via multiprocessing over wavelength chunks, on a
+             bounded contiguous wavelength sample of the same workload
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+BYTES_PER_SAMPLE_STAGED = 16.0      # one f64 tau store + one load (SURVEY 8(d), row (c'))
+
+
+def flops_per_sample(n_atoms: int) -> float:
+    return 2.0 * n_atoms + 29.0     # SURVEY 8(d) convention: S FMA + negate + exp(26) + 1 FMA
+
+
+# ------------------------------------------------------------------------------------------------
+# workload
+# ------------------------------------------------------------------------------------------------
+def scaled_spec(name: str, n_gpus: int) -> dict:
+    from prometheus_b200 import workloads
+    spec = workloads.get(name)
+    if n_gpus > 1:      # weak scaling along the wavelength axis: N-fold finer grid
+        spec["wavelength"][3] /= n_gpus
+        spec["wavelength"][4] /= n_gpus
+        spec["name"] = f"{name}x{n_gpus}"
+    return spec
+
+
+def nist_rows():
+    return np.load(os.path.join(ROOT, "tests", "golden", "linelist.npz"))["rows"]
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks: sampled DURING the timed region (NVML in a thread)
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    REASONS = {0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
+               0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+               0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting"}
+
+    def __init__(self, index: int, period: float = 0.05):
+        self.samples, self.mask, self.max_mhz, self.power = [], 0, None, []
+        self._stop = threading.Event()
+        self._thr = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[index]) if vis and vis.replace(",", "").isdigit() else index
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self.nv = None
+        self.period = period
+
+    def _loop(self):
+        nv = self.nv
+        while not self._stop.is_set():
+            try:
+                self.samples.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+                self.mask |= int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+                self.power.append(nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0)
+            except Exception:
+                pass
+            self._stop.wait(self.period)
+
+    def start(self):
+        if self.nv is not None:
+            self._thr = threading.Thread(target=self._loop, daemon=True)
+            self._thr.start()
+
+    def stop(self) -> dict:
+        if self._thr is not None:
+            self._stop.set()
+            self._thr.join()
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["unavailable"]}
+        reasons = [n for b, n in self.REASONS.items() if self.mask & b and n != "gpu_idle"]
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz, "reasons": reasons,
+                "samples": len(self.samples), "power_w_max": max(self.power) if self.power else None}
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the oracle (numpy/scipy restatement of the reference) on all host cores
+# ------------------------------------------------------------------------------------------------
+_W = {}
+
+
+def _cpu_init(name, n_gpus, tables_path):
+    os.environ.setdefault("OMP_NUM_THREADS", "1")
+    os.environ.setdefault("OPENBLAS_NUM_THREADS", "1")
+    os.environ.setdefault("MKL_NUM_THREADS", "1")
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from helpers import oracle, oracle_inputs
+    spec = scaled_spec(name, n_gpus)
+    inputs = oracle_inputs(spec, nist_rows() if spec.get("linelist", "nist") == "nist" else None)
+    if tables_path:
+        z = np.load(tables_path)
+        inputs["tables"] = {}
+        for key in z.files:
+            if key.startswith("x|"):
+                _, i, sp = key.split("|")
+                inputs["tables"][(int(i), sp)] = (z[key], z["y|" + i + "|" + sp])
+    _W["oracle"] = oracle
+    _W["model"] = oracle.build_model(spec, inputs)
+
+
+def _cpu_chunk(wl):
+    oracle, m = _W["oracle"], _W["model"]
+    if wl.size == 0:
+        return np.empty((len(m.orb), 0))
+    has_mol = any(c.kind == "molecule" for s in m.scenarios for c in s.constituents)
+    n_c = len(m.rho) * len(m.phi) * len(m.orb)
+    bs = oracle.reference_batch_size(n_c, wl.size, len(m.x), has_mol, 2.0)     # memoryHandler.py:55-66
+    return oracle.sum_over_chords(m, batch_size=None if bs >= n_c else bs, wavelength=wl)
+
+
+class CpuArm:
+    """multiprocessing.Pool(P) over wavelength chunks, each worker running the single-process
+    restatement of Transit.sumOverChords with the reference's own RAM-bounded chord batching."""
+
+    def __init__(self, name, n_gpus, tables=None, procs=None):
+        import multiprocessing as mp
+        self.procs = procs or (os.cpu_count() or 1)
+        self.tmp = None
+        if tables:
+            fd, self.tmp = tempfile.mkstemp(suffix=".npz")
+            os.close(fd)
+            flat = {}
+            for (i, sp), (tx, ty) in tables.items():
+                flat[f"x|{i}|{sp}"] = tx
+                flat[f"y|{i}|{sp}"] = ty
+            np.savez(self.tmp, **flat)
+        self.pool = mp.get_context("spawn").Pool(self.procs, initializer=_cpu_init, initargs=(name, n_gpus, self.tmp))
+        self.pool.map(_cpu_chunk, [np.empty(0)] * self.procs)      # wait until every worker is up
+
+    def run(self, wl):
+        t0 = time.perf_counter()
+        parts = self.pool.map(_cpu_chunk, np.array_split(wl, self.procs), chunksize=1)
+        return np.hstack(parts), time.perf_counter() - t0
+
+    def close(self):
+        self.pool.close()
+        self.pool.join()
+        if self.tmp:
+            os.unlink(self.tmp)
+
+
+def calibrate_sample(arm, wl, centre, n_c, seconds):
+    """Two probes -> linear cost model t = a + b*n (a: the wavelength-independent density work) ->
+    wavelength window whose CPU time is ~`seconds`."""
+    n1, n2 = 16 * arm.procs, 64 * arm.procs
+    t1 = arm.run(wl[slice(*pick_sample(wl, centre, n1))])[1]
+    t2 = arm.run(wl[slice(*pick_sample(wl, centre, n2))])[1]
+    b = max((t2 - t1) / (n2 - n1), 1e-9)
+    a = max(t1 - b * n1, 0.0)
+    return pick_sample(wl, centre, int(max(n2, (seconds - a) / b)))
+
+
+def pick_sample(wavelength, centre_index, n):
+    n = int(min(max(n, 1), wavelength.size))
+    lo = int(min(max(centre_index - n // 2, 0), wavelength.size - n))
+    return lo, lo + n
+
+
+# ------------------------------------------------------------------------------------------------
+# reference arm: --impl reference
+# ------------------------------------------------------------------------------------------------
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from prometheus_b200 import builder
+    n_gpus = args.gpus
+    spec = scaled_spec(args.workload, n_gpus)
+    tr = builder.build_transit(spec, nist_rows=nist_rows(), build_tables=False)     # host-only: axes + grid
+    wl = tr.wavelength
+    shape = {"n_chords": int(spec["grid"][4]) * int(spec["grid"][5]) * int(spec["grid"][7])}
+    n_c = shape["n_chords"]
+    arm = CpuArm(args.workload, n_gpus)
+    centre = int(np.argmin(wl)) + wl.size // 2
+    # calibrate, then size a step so that (warmup + steps) steps end within --cpu-seconds
+    budget = args.cpu_seconds / max(args.steps + args.warmup + 1, 1)
+    lo, hi = calibrate_sample(arm, wl, centre, n_c, budget)
+    for _ in range(args.warmup):
+        arm.run(wl[lo:hi])
+    times = [arm.run(wl[lo:hi])[1] for _ in range(args.steps)]
+    arm.close()
+    t = float(np.mean(times))
+    value = n_c * (hi - lo) / t
+    sample = f"{hi - lo} contiguous wavelengths [{lo},{hi}) of {wl.size}, all {n_c} chords, per step"
+    print(json.dumps({
+        "impl": "reference", "metric": "chord*lambda samples/s", "value": value, "unit": "samples/s",
+        "n_gpus": n_gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": t * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args.workload, spec, n_c, wl.size, n_gpus),
+        "cpu_baseline": {"value": value, "unit": "samples/s", "cores": arm.procs, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "full_run_seconds_extrapolated": n_c * wl.size / value,
+    }))
+
+
+def workload_config(name, spec, n_c, n_wav, n_gpus):
+    g = spec["grid"]
+    return {"workload": f"{name}: {spec['title']}", "n_chords": n_c, "n_wav": int(n_wav), "n_x": int(g[2]),
+            "n_orb": int(g[7]), "n_phi": int(g[5]), "n_rho": int(g[4]),
+            "sharding": f"wavelength chunks over {n_gpus} rank(s), replicated scene, one all-gather of R",
+            "weak_scaling_rule": "wavelength resolution refined N-fold at N GPUs",
+            "cache": "L2 flushed between timed steps (512 MiB write)"}
+
+
+# ------------------------------------------------------------------------------------------------
+# B200 arm
+# ------------------------------------------------------------------------------------------------
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def recorded_traffic(workload, kernel="transit_kernel"):
+    """dram bytes per launch of the dominant kernel from the committed ncu capture, or None."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(p):
+        return json.load(open(p)).get(workload, {}).get(kernel)
+    return None
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py: no CUDA device; the transit hot path has no CPU implementation to fall back on")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    import prometheus_b200 as pb
+    from prometheus_b200 import distributed as pbd, host, scene
+
+    host.set_default_device(local)
+    ctx = host.get_context(local)
+    stream = torch.cuda.Stream(dev)
+    spec = scaled_spec(args.workload, world)
+    with torch.cuda.stream(stream):
+        ctx.set_stream(stream.cuda_stream)
+        probe = ctx.probe_fp64() if rank == 0 else None
+        t0 = time.perf_counter()
+        tr = pb.build_transit(spec, nist_rows=nist_rows())            # sigma tables: kernel (b2), set-up time
+        t_setup = time.perf_counter() - t0
+        voigt = ctx.last_timing()
+        sc, keep, info = scene.flatten(tr)
+        ctx.set_scene(sc, keep)
+        n_orb, n_wav, n_c, n_atoms = info["n_orb"], info["n_wav"], info["n_chords"], info["n_atoms"]
+        st = pbd.ShardedTransit(n_orb, n_wav, None, "wavelength", dev)
+        tile_t = []
+
+        def compute_tile(p0, p1, w0, w1, out):
+            tile_t.append(ctx.run_device(p0, p1, w0, w1, out.data_ptr(), want_timing=True))
+        st.compute_tile = compute_tile
+        flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
+        samples_total = float(n_c) * float(n_wav)
+
+        def barrier():
+            if world > 1:
+                dist.barrier()
+            torch.cuda.synchronize(dev)
+
+        # ---- device-resident timing --------------------------------------------------------------
+        for _ in range(args.warmup):
+            st.run_device()
+        barrier()
+        tile_t.clear()
+        launches0 = ctx.launch_count()
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+        clocks = ClockSampler(local)
+        clocks.start()
+        for a, b in ev:
+            flush.zero_()
+            a.record()
+            st.run_device()
+            b.record()
+        barrier()
+        clk = clocks.stop()
+        launches = ctx.launch_count() - launches0
+        step_ms = [a.elapsed_time(b) for a, b in ev]
+        total_ms = torch.tensor([sum(step_ms)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
+        ms_per_step = float(total_ms.item()) / args.steps
+        kernel_ms = float(np.mean([t["transit_ms"] for t in tile_t]))
+        column_ms = float(np.mean([t["column_ms"] for t in tile_t]))
+        finalize_ms = float(np.mean([t["finalize_ms"] for t in tile_t]))
+        R_dev = st.to_host(0)
+
+        # ---- end to end through the host API (host buffers, H2D + D2H inside) ---------------------
+        state = {}
+        e2e_ms = []
+        R_e2e = None
+        for i in range(args.warmup + args.steps):
+            flush.zero_()
+            barrier()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            if world == 1:
+                R_e2e = tr.sumOverChords()                 # the user-facing call: numpy in, numpy out
+            else:
+                R_e2e = pbd.sum_over_chords(tr, None, "wavelength", local, 0, state)
+            b.record()
+            barrier()
+            if i >= args.warmup:
+                e2e_ms.append(a.elapsed_time(b))
+        e2e_total = torch.tensor([sum(e2e_ms)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(e2e_total, op=dist.ReduceOp.MAX)
+        e2e_ms_per_step = float(e2e_total.item()) / args.steps
+    launch_total = torch.tensor([launches], dtype=torch.int64, device=dev)
+    if world > 1:
+        dist.all_reduce(launch_total)
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    assert R_dev.shape == (n_orb, n_wav) and np.all(np.isfinite(R_dev)) and np.array_equal(R_dev, R_e2e)
+
+    hbm_peak, peak_src = measured_peaks()
+    tile_samples = float(n_c) * float(st.samples_tile_shape[1])
+    achieved = BYTES_PER_SAMPLE_STAGED * tile_samples / (kernel_ms * 1e-3) / 1e9
+    fl = flops_per_sample(n_atoms) * tile_samples / (kernel_ms * 1e-3) / 1e12
+    out = {
+        "metric": "chord*lambda samples/s", "value": samples_total / (ms_per_step * 1e-3), "unit": "samples/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args.workload, spec, n_c, n_wav, world),
+        "runs_per_s": 1e3 / ms_per_step,
+        "e2e": {"value": samples_total / (e2e_ms_per_step * 1e-3), "unit": "samples/s", "ms_per_step": e2e_ms_per_step,
+                "h2d_bytes_per_step": int(info["h2d_bytes"]) * world, "d2h_bytes_per_step": int(n_orb * n_wav * 8),
+                "runs_per_s": 1e3 / e2e_ms_per_step},
+        "gpu_launches": int(launch_total.item()),
+        "clocks": clk,
+        "roofline": {"kernel": "transit_kernel (c': tau + exp(-tau) + disk sum)", "bound": "hbm", "achieved": achieved,
+                     "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "peak_source": peak_src,
+                     "convention": "staged-equivalent 16 B per chord*lambda sample (SURVEY 8(d)); the fused kernel's true DRAM traffic is in `traffic`",
+                     "traffic": recorded_traffic(args.workload), "kernel_ms": kernel_ms,
+                     "fp64": {"achieved_tflops": fl, "peak_tflops_dfma_probe": probe["dfma_tflops"],
+                              "frac": fl / probe["dfma_tflops"], "flops_per_sample": flops_per_sample(n_atoms),
+                              "exp_probe_gops": probe["exp_gops"],
+                              "exp_frac": tile_samples / (kernel_ms * 1e-3) / 1e9 / probe["exp_gops"]}},
+        "kernels_ms": {"column": column_ms, "transit": kernel_ms, "finalize": finalize_ms},
+        "setup": {"seconds": t_setup, "voigt_last_table_ms": voigt["transit_ms"], "voigt_last_table_evals": voigt["samples"]},
+    }
+
+    # ---- CPU baseline on the host cores of this box (rank 0, N = 1 only) -----------------------------
+    if world == 1 and args.cpu_seconds > 0:
+        tables = {}
+        for i, d in enumerate(tr.atmosphere.densityDistributionList):
+            for con in d.constituents:
+                if not con.isMolecule:
+                    tables[(i, con.species.name)] = (con.lookupFunction.x, con.lookupFunction.y)
+        arm = CpuArm(args.workload, 1, tables)
+        wl = tr.wavelength
+        centre = wl.size // 2
+        lo, hi = calibrate_sample(arm, wl, centre, n_c, args.cpu_seconds)
+        R_cpu, t_cpu = arm.run(wl[lo:hi])
+        arm.close()
+        err = float(np.max(np.abs(R_cpu - R_dev[:, lo:hi])))
+        out["cpu_baseline"] = {"value": n_c * (hi - lo) / t_cpu, "unit": "samples/s", "cores": arm.procs, "kind": "port",
+                               "sample": f"{hi - lo} contiguous wavelengths [{lo},{hi}) of {wl.size}, all {n_c} chords, "
+                                         f"{t_cpu:.1f} s; multiprocessing over wavelength chunks",
+                               "max_abs_diff_R_gpu_vs_cpu_on_sample": err}
+    print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="C4")
+    ap.add_argument("--cpu-seconds", type=float, default=None,
+                    help="CPU budget: cpu_baseline sample (default 15 s) / whole --impl reference run (default 120 s)")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    if args.cpu_seconds is None:
+        args.cpu_seconds = 15.0 if args.impl == "b200" else 120.0
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "b200" and world != args.gpus:
+        if args.gpus == 1 or world > 1:
+            raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run --nproc-per-node {args.gpus}")
+        # convenience: python bench.py --gpus N re-launches itself under torchrun
+        import subprocess
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", "29517", os.path.abspath(__file__)] + sys.argv[1:]
+        raise SystemExit(subprocess.call(cmd))
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -157,6 +157,7 @@ void pb200_destroy(pb200_ctx* c) {
 
 int pb200_set_stream(pb200_ctx* c, void* cuda_stream) {
     if (!c) return PB200_ERR_INVALID;
+    if (c->stream == (cudaStream_t)cuda_stream && !c->own_stream) return PB200_OK;
     PB_CUDA(c, cudaSetDevice(c->device));
     PB_CUDA(c, cudaStreamSynchronize(c->stream));
     if (c->own_stream && c->stream) { cudaStreamDestroy(c->stream); c->own_stream = false; }

@@ -1,0 +1,137 @@
+"""Multi-GPU Transit.sumOverChords: one process per GPU, R(phase, lambda) tiled over ranks.
+
+R[i_orb, lambda] depends only on the chords of that phase and on that wavelength
+(reference: gasProperties.py:1243-1258), so the output tiles are independent units: there is no
+exchange step on the data path.  This replaces memoryHandler's RAM-bounded chord batching
+(memoryHandler.py:55-66) and the multiprocessing the reference's README advertises.  The one
+collective is the final all-gather of the fp64 R tiles (NCCL over NVLink; gloo in the CPU tests).
+
+Partition: contiguous wavelength chunks of equal padded width (every rank then does the same
+kernel (c') work; kernel (a') -- n_c*n_x, < 1 % of n_c*n_wav -- is replicated), or contiguous
+phase blocks when asked for (`axis="phase"`: partitions kernel (a') as well; useful for dense
+phase sweeps such as C3 where n_orb >> world).
+"""
+from __future__ import annotations
+
+import numpy as np
+
+
+def partition(n: int, world: int) -> list[tuple[int, int]]:
+    """Contiguous [lo, hi) blocks of equal padded width ceil(n/world); trailing blocks may be
+    short or empty."""
+    per = -(-n // world)
+    return [(min(r * per, n), min((r + 1) * per, n)) for r in range(world)]
+
+
+def padded_width(n: int, world: int) -> int:
+    return -(-n // world)
+
+
+def unpack_tiles(flat: np.ndarray, n_orb: int, n_wav: int, world: int, axis: str = "wavelength") -> np.ndarray:
+    """[world][n_orb*per] (axis="wavelength") or [world][per*n_wav] (axis="phase") gathered tile
+    buffers -> (n_orb, n_wav).  Each rank's tile is C-contiguous [n_phase_sel][n_wav_sel] at the
+    start of its slot."""
+    R = np.empty((n_orb, n_wav), dtype=np.float64)
+    if axis == "wavelength":
+        per = padded_width(n_wav, world)
+        flat = flat.reshape(world, n_orb * per)
+        for r, (lo, hi) in enumerate(partition(n_wav, world)):
+            if hi > lo:
+                R[:, lo:hi] = flat[r, : n_orb * (hi - lo)].reshape(n_orb, hi - lo)
+    else:
+        per = padded_width(n_orb, world)
+        flat = flat.reshape(world, per * n_wav)
+        for r, (lo, hi) in enumerate(partition(n_orb, world)):
+            if hi > lo:
+                R[lo:hi, :] = flat[r, : (hi - lo) * n_wav].reshape(hi - lo, n_wav)
+    return R
+
+
+class ShardedTransit:
+    """Keeps the per-rank state of a sharded run: context, tile bounds, gather buffers.
+
+    `compute_tile(phase_lo, phase_hi, wav_lo, wav_hi, out_tensor)` defaults to the CUDA library
+    (pb200_run_device into `out_tensor`'s memory); tests on CPU inject a host function.
+    """
+
+    def __init__(self, n_orb: int, n_wav: int, group=None, axis: str = "wavelength", device=None, compute_tile=None):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist = torch, dist
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.n_orb, self.n_wav, self.axis = int(n_orb), int(n_wav), axis
+        if axis == "wavelength":
+            self.lo, self.hi = partition(self.n_wav, self.world)[self.rank]
+            self.tile = (0, self.n_orb, self.lo, self.hi)
+            self.slot = self.n_orb * padded_width(self.n_wav, self.world)
+        elif axis == "phase":
+            self.lo, self.hi = partition(self.n_orb, self.world)[self.rank]
+            self.tile = (self.lo, self.hi, 0, self.n_wav)
+            self.slot = padded_width(self.n_orb, self.world) * self.n_wav
+        else:
+            raise ValueError("axis must be 'wavelength' or 'phase'")
+        self.device = torch.device(device) if device is not None else torch.device("cpu")
+        self.local = torch.zeros(self.slot, dtype=torch.float64, device=self.device)
+        self.gathered = torch.empty(self.world * self.slot, dtype=torch.float64, device=self.device) if self.world > 1 else self.local
+        self.host = None
+        self.compute_tile = compute_tile
+
+    @property
+    def samples_tile_shape(self):
+        p0, p1, w0, w1 = self.tile
+        return p1 - p0, w1 - w0
+
+    def run_device(self):
+        """Enqueue this rank's tile and the all-gather; returns the gathered device buffer."""
+        p0, p1, w0, w1 = self.tile
+        if p1 > p0 and w1 > w0:
+            self.compute_tile(p0, p1, w0, w1, self.local)
+        if self.world > 1:
+            self.dist.all_gather_into_tensor(self.gathered, self.local, group=self.group)
+        return self.gathered
+
+    def to_host(self, dst: int | None = 0):
+        """D2H of the gathered buffer (on `dst` only, or on every rank if dst is None) -> (n_orb, n_wav)."""
+        torch = self.torch
+        if dst is not None and self.rank != dst:
+            return None
+        if self.device.type == "cuda":
+            if self.host is None:
+                self.host = torch.empty(self.gathered.shape, dtype=torch.float64, pin_memory=True)
+            self.host.copy_(self.gathered, non_blocking=True)
+            torch.cuda.current_stream(self.device).synchronize()
+            flat = self.host.numpy()
+        else:
+            flat = self.gathered.numpy()
+        return unpack_tiles(flat, self.n_orb, self.n_wav, self.world, self.axis)
+
+
+def sum_over_chords(transit, group=None, axis: str = "wavelength", device: int | None = None, dst: int | None = 0,
+                    state: dict | None = None):
+    """Sharded replacement of Transit.sumOverChords: every rank uploads the (replicated) scene,
+    computes its tile on its GPU, the tiles are all-gathered, rank `dst` returns R (n_orb, n_wav).
+
+    Must be called with torch's current CUDA stream being the one the context runs on
+    (pass `state` from a previous call to reuse buffers and the context binding)."""
+    import torch
+    from . import host, scene
+    if device is None:
+        device = torch.cuda.current_device()
+    ctx = host.get_context(device)
+    ctx.set_stream(torch.cuda.current_stream(device).cuda_stream)
+    sc, keep, info = scene.flatten(transit)
+    ctx.set_scene(sc, keep)
+    st = state.get("sharded") if state else None
+    if st is None or (st.n_orb, st.n_wav, st.axis) != (info["n_orb"], info["n_wav"], axis):
+        st = ShardedTransit(info["n_orb"], info["n_wav"], group, axis, torch.device("cuda", device),
+                            compute_tile=lambda p0, p1, w0, w1, out: ctx.run_device(p0, p1, w0, w1, out.data_ptr()))
+        if state is not None:
+            state["sharded"] = st
+    else:
+        st.compute_tile = lambda p0, p1, w0, w1, out: ctx.run_device(p0, p1, w0, w1, out.data_ptr())
+    st.run_device()
+    if state is not None:
+        state["info"] = info
+    return st.to_host(dst)

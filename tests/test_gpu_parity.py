@@ -1,0 +1,263 @@
+"""GPU parity: the CUDA path (through the C ABI) against the committed reference outputs
+(tests/golden/*.npz) and the CPU oracle on the same seeded inputs.
+
+Tolerances (north star / SURVEY 8(c)):
+  * chord/grid indexing and the blocked mask: bit-exact;
+  * excess transit depth E = R0 - R:  |E - E_ref| <= 1e-10 + 1e-6 |E_ref|;
+  * intermediates: Ncol rel 1e-12, density rel 1e-12, sigma lookup rel 1e-12 on an identical
+    table, Voigt table rel 1e-9 where sigma > 1e-40.
+"""
+import numpy as np
+import pytest
+
+from helpers import excess_depth_ok, oracle, oracle_model
+import prometheus_b200 as pb
+from prometheus_b200 import builder, capi, host, workloads
+
+pytestmark = pytest.mark.gpu
+
+CASES = workloads.GOLDEN_CASES
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    return host.get_context(0)
+
+
+@pytest.fixture(scope="module")
+def transits(nist_rows, ctx):
+    """Host-mirror Transit per case; sigma tables built by kernel (b2) on the GPU."""
+    cache = {}
+
+    def get(name):
+        if name not in cache:
+            cache[name] = builder.build_transit(workloads.get(name), nist_rows=nist_rows)
+        return cache[name]
+
+    return get
+
+
+@pytest.fixture(scope="module")
+def models(nist_rows):
+    cache = {}
+
+    def get(name):
+        if name not in cache:
+            cache[name] = oracle_model(name, nist_rows)
+        return cache[name]
+
+    return get
+
+
+def with_oracle_tables(name, nist_rows, model):
+    """Mirror Transit whose atomic sigma tables are the oracle's (scipy-built): isolates kernels
+    (a') and (c') from the Voigt synthesis."""
+    tr = builder.build_transit(workloads.get(name), nist_rows=nist_rows, build_tables=False)
+    for dist, scn in zip(tr.atmosphere.densityDistributionList, model.scenarios):
+        for con, ocon in zip(dist.constituents, scn.constituents):
+            if not con.isMolecule:
+                con.lookupFunction = host.TableFunction1D(ocon.tab_x, ocon.tab_y)
+    return tr
+
+
+# ---- the headline criterion --------------------------------------------------------------------
+@pytest.mark.parametrize("name", CASES)
+def test_R_matches_reference_end_to_end(name, transits, golden):
+    """Transit.sumOverChords with GPU-built Voigt tables against the reference's R."""
+    tr, g = transits(name), golden(name)
+    R = tr.sumOverChords()
+    assert R.shape == g["R"].shape and R.dtype == np.float64 and R.flags.c_contiguous
+    ok, worst = excess_depth_ok(R, g["R"], g["R0"])
+    assert ok, f"{name}: worst excess-depth error / bound = {worst:.3g}"
+    assert tr.last_timing["launches"] >= 2
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_R_with_identical_tables_is_tight(name, nist_rows, models, golden):
+    tr, g = with_oracle_tables(name, nist_rows, models(name)), golden(name)
+    R = tr.sumOverChords()
+    assert np.max(np.abs(R - g["R"])) < 2e-13, float(np.max(np.abs(R - g["R"])))
+
+
+# ---- a1/a4: indexing contract -----------------------------------------------------------------
+@pytest.mark.parametrize("name", CASES)
+def test_blocked_mask_and_weights_bit_exact(name, transits, models, golden):
+    tr, g = transits(name), golden(name)
+    blocked, weight = tr.getChordMasks()
+    assert int(blocked.sum()) == int(g["n_blocked"])
+    assert np.array_equal(np.packbits(blocked), g["blocked"])
+    _, w_ref = oracle.chord_masks(models(name))
+    assert np.array_equal(weight, w_ref)       # rho*clv in the reference's chord order
+
+
+# ---- a6/a7/a8: density and column density --------------------------------------------------------
+@pytest.mark.parametrize("name", CASES)
+def test_number_density_and_column(name, transits, golden):
+    tr, g = transits(name), golden(name)
+    grid = tr.spatialGrid
+    chords = grid.getChordGrid()
+    sub = g["chord_subset"]
+    x = grid.constructXaxis()
+    blocked, _ = tr.getChordMasks()
+    for i, dist in enumerate(tr.atmosphere.densityDistributionList):
+        n = dist.calculateNumberDensity(x, chords[sub, 0], chords[sub, 1], chords[sub, 2])
+        np.testing.assert_allclose(n, g[f"density_{i}"], rtol=1e-12, atol=0)
+        one = dist.calculateNumberDensity(x, chords[sub[3], 0], chords[sub[3], 1], chords[sub[3], 2])
+        assert one.shape == (x.size,)
+        np.testing.assert_allclose(one, g[f"density_{i}"][3], rtol=1e-12, atol=0)
+        n_grid = tr.getNumberDensityGrid(i)
+        np.testing.assert_allclose(n_grid[sub], g[f"density_{i}"], rtol=1e-12, atol=0)
+    ncol = tr.getColumnDensityGrid()
+    act = ~blocked        # the reference evaluates only unblocked chords (gasProperties.py:1235-1240)
+    for k in range(ncol.shape[0]):
+        np.testing.assert_allclose(ncol[k][act], g[f"ncol_{k}"][act], rtol=1e-12, atol=0)
+        assert np.all(ncol[k][~act] == 0.0)
+
+
+# ---- a8-a11: tau ----------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", CASES)
+def test_optical_depth_rows(name, nist_rows, models, golden):
+    tr, g = with_oracle_tables(name, nist_rows, models(name)), golden(name)
+    blocked, _ = tr.getChordMasks()
+    sub = g["chord_subset"]
+    tau = tr.getLOSopticalDepthGrid()
+    keep = ~blocked[sub]
+    np.testing.assert_allclose(tau[sub][keep], g["tau_sub"][keep], rtol=2e-12, atol=1e-300)
+
+
+# ---- a9: sigma lookup (n_interp_log) ---------------------------------------------------------------
+def test_sigma_lookup_matches_np_interp(ctx, models):
+    m = models("C5s")
+    con = m.scenarios[0].constituents[0]
+    rng = np.random.default_rng(5)
+    lo, hi = con.tab_x[0], con.tab_x[-1]
+    wl = np.concatenate([rng.uniform(lo * 0.999, hi * 1.001, 20000), con.tab_x[::37], [lo, hi, lo * 0.5, hi * 2, np.nan]])
+    got = ctx.sigma_lookup(con.tab_x, con.tab_y, 1e-50, wl)
+    ref = oracle.interp_log(wl, con.tab_x, con.tab_y, 1e-50)
+    assert np.isnan(got[-1]) and np.isnan(ref[-1])
+    np.testing.assert_allclose(got[:-1], ref[:-1], rtol=1e-12, atol=1e-60)
+    # empty input and (n_orb, n_wav) shaped input
+    assert ctx.sigma_lookup(con.tab_x, con.tab_y, 1e-50, np.empty(0)).size == 0
+    wl2 = np.outer(np.linspace(0.9999, 1.0001, 7), m.wavelength)
+    np.testing.assert_allclose(ctx.sigma_lookup(con.tab_x, con.tab_y, 1e-50, wl2),
+                               oracle.interp_log(wl2, con.tab_x, con.tab_y, 1e-50), rtol=1e-12, atol=1e-60)
+
+
+# ---- a10: Voigt synthesis ---------------------------------------------------------------------------
+def test_voigt_profile_against_scipy(ctx):
+    from scipy.special import voigt_profile
+    rng = np.random.default_rng(11)
+    n = 200000
+    sigma = 10 ** rng.uniform(8, 10, n)
+    y = 10 ** rng.uniform(-8, 1, n)                    # gamma/(sqrt2 sigma)
+    gamma = y * sigma * np.sqrt(2.0)
+    xs = np.concatenate([rng.uniform(-12, 12, n // 2), np.sign(rng.uniform(-1, 1, n - n // 2)) * 10 ** rng.uniform(-3, 5, n - n // 2)])
+    x = xs * sigma * np.sqrt(2.0)
+    got = ctx.voigt_profile(x, sigma, gamma)
+    ref = voigt_profile(x, sigma, gamma)
+    rel = np.abs(got - ref) / ref
+    assert np.max(rel) < 1e-12, float(np.max(rel))
+    # degenerate branches of scipy.special.voigt_profile
+    xx = np.array([0.0, 1.0, -2.0, 0.5])
+    np.testing.assert_allclose(ctx.voigt_profile(xx, 0.0, 1.5), voigt_profile(xx, 0.0, 1.5), rtol=1e-15)
+    np.testing.assert_allclose(ctx.voigt_profile(xx, 2.0, 0.0), voigt_profile(xx, 2.0, 0.0), rtol=1e-14)
+
+
+@pytest.mark.parametrize("name", ["C1", "C5s", "C2s"])
+def test_voigt_tables_against_reference(name, transits, golden):
+    tr, g = transits(name), golden(name)
+    k = 0
+    for dist in tr.atmosphere.densityDistributionList:
+        for con in dist.constituents:
+            if con.isMolecule:
+                continue
+            lf = con.lookupFunction
+            assert lf.x.size == int(g[f"table_n_{k}"])
+            st = int(g[f"table_stride_{k}"])
+            assert np.array_equal(lf.x[::st], g[f"table_x_{k}"])
+            assert np.sum(lf.x) == float(g[f"table_xsum_{k}"])
+            s_got, s_ref = 10 ** lf.y[::st], 10 ** g[f"table_y_{k}"]
+            big = s_ref > 1e-40
+            assert np.max(np.abs(s_got[big] - s_ref[big]) / s_ref[big]) < 1e-9
+            np.testing.assert_allclose(lf.y[::st], g[f"table_y_{k}"], rtol=0, atol=1e-9)
+            k += 1
+
+
+def test_calculateVoigtProfile_signature(transits, models):
+    tr, m = transits("C1"), models("C1")
+    con = tr.atmosphere.densityDistributionList[0].constituents[0]
+    wl = tr.wavelength
+    got = con.calculateVoigtProfile(wl)
+    el, ion, _ = oracle.SPECIES["NaI"]
+    lam0, gamma, f = oracle.line_parameters(host.LINE_LIST, el, ion, wl)
+    ref = oracle.voigt_sigma(lam0, gamma, f, con.sigma_v, wl)
+    np.testing.assert_allclose(got, ref, rtol=1e-11)
+    np.testing.assert_allclose(con.getSigmaAbs(wl), oracle.interp_log(wl, con.lookupFunction.x, con.lookupFunction.y, 1e-50),
+                               rtol=1e-12)
+
+
+# ---- a11: molecular lookup ----------------------------------------------------------------------------
+def test_molecular_sigma_against_scipy_rgi(ctx, transits, models):
+    tr, m = transits("C2s"), models("C2s")
+    dist = tr.atmosphere.densityDistributionList[0]
+    mol = [c for c in dist.constituents if c.isMolecule][0]
+    omol = [c for c in m.scenarios[0].constituents if c.kind == "molecule"][0]
+    rng = np.random.default_rng(3)
+    n_c, n_x, n_wav = 6, 9, 301
+    P = 10 ** rng.uniform(-6, 9, (n_c, n_x))          # below the clip, inside, above the grid
+    wl = np.sort(rng.uniform(2850e-8, 8150e-8, (n_c, n_wav)), axis=1)
+    got = mol.getSigmaAbs(P, 3000.0, wl)
+    ref = oracle.molecular_sigma(omol, P, 3000.0, wl)
+    assert got.shape == (n_c, n_x, n_wav)
+    np.testing.assert_allclose(got, ref, rtol=1e-11, atol=1e-62)
+
+
+# ---- tiles, chord splits, repeatability ------------------------------------------------------------------
+def test_tiles_equal_full_run(ctx, transits):
+    tr = transits("C3s")
+    R = tr.sumOverChords()
+    n_orb, n_wav = R.shape
+    for (p0, p1, w0, w1) in [(0, 1, 0, n_wav), (2, 7, 5, 133), (n_orb - 1, n_orb, n_wav - 1, n_wav), (0, n_orb, 64, 65)]:
+        tile, _ = ctx.run(p0, p1, w0, w1)
+        np.testing.assert_allclose(tile, R[p0:p1, w0:w1], rtol=0, atol=3e-15)
+    again = tr.sumOverChords()
+    assert np.array_equal(R, again), "the chord reduction must be deterministic"
+
+
+def test_opaque_disk_limit(nist_rows, golden):
+    """tau == 0 (no absorber) => R is the opaque-disk value R0 of the reference."""
+    spec = workloads.get("C3s")
+    for s in spec["scenarios"]:
+        s["N"] = 0.0
+    tr = builder.build_transit(spec, nist_rows=nist_rows)
+    R = tr.sumOverChords()
+    np.testing.assert_allclose(R, golden("C3s")["R0"], rtol=0, atol=2e-15)
+
+
+# ---- error conventions --------------------------------------------------------------------------------
+def test_errors_are_loud(nist_rows):
+    c = capi.Context(0)
+    with pytest.raises(capi.Pb200Error) as ei:
+        c.run(0, 1, 0, 1)
+    assert ei.value.code == -5
+    tr = builder.build_transit(workloads.get("C1"), nist_rows=nist_rows)
+    tr._upload(c)
+    for bad in [(0, 6, 0, 10), (-1, 2, 0, 10), (0, 1, 10, 10), (0, 1, 0, 10 ** 6)]:
+        with pytest.raises(capi.Pb200Error) as ei:
+            c.run(*bad)
+        assert ei.value.code == -1
+    c.close()
+
+
+def test_serpens_out_of_grid_raises(nist_rows):
+    """The reference's RegularGridInterpolator raises ValueError outside the histogram (:600)."""
+    spec = workloads.get("SERs")
+    spec["grid"][1] *= 1.5            # x axis now sticks out of the tabulated box
+    tr = builder.build_transit(spec, nist_rows=nist_rows, build_tables=False)
+    good = builder.build_transit(workloads.get("SERs"), nist_rows=nist_rows)
+    dist, gdist = tr.atmosphere.densityDistributionList[0], good.atmosphere.densityDistributionList[0]
+    dist.InterpolatedDensity = gdist.InterpolatedDensity
+    dist.constituents[0].lookupFunction = gdist.constituents[0].lookupFunction
+    with pytest.raises(capi.Pb200Error) as ei:
+        tr.sumOverChords()
+    assert ei.value.code == -6
