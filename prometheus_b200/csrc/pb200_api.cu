@@ -1,6 +1,7 @@
 // pb200_api.cu -- the C ABI of include/prometheus_b200.h: context, scene upload, orchestration.
 // All compute is in the kernels of pb200_density.cu / pb200_sigma.cu / pb200_transit.cu /
 // pb200_molecular.cu; there is no host fallback for any of it.
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -66,6 +67,7 @@ struct pb200_ctx {
     double* scratch = nullptr;   // partial sums / R tile / temporary outputs
     size_t scratch_bytes = 0;
     int* d_oob = nullptr;
+    double* d_exp_tab = nullptr; // 2^(j/64), j < 64
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     pb200_timing last = {};
     double upload_ms = 0.0;
@@ -131,6 +133,12 @@ int pb200_create(int device, pb200_ctx** out) {
     if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_scene, sizeof(DevScene));
     if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_oob, sizeof(int));
     if (e == cudaSuccess) e = cudaMemset(c->d_oob, 0, sizeof(int));
+    if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_exp_tab, kExpTabEntries * sizeof(double));
+    if (e == cudaSuccess) {
+        double tab[kExpTabEntries];
+        for (int j = 0; j < kExpTabEntries; ++j) tab[j] = pb_exp_tab_entry((double)exp2l((long double)j / kExpTabEntries), j);
+        e = cudaMemcpy(c->d_exp_tab, tab, sizeof tab, cudaMemcpyHostToDevice);
+    }
     if (e != cudaSuccess) {
         int rc = fail(nullptr, PB200_ERR_CUDA, "pb200_create: %s", cudaGetErrorString(e));
         delete c;
@@ -150,6 +158,7 @@ void pb200_destroy(pb200_ctx* c) {
     if (c->stage) cudaFreeHost(c->stage);
     if (c->d_scene) cudaFree(c->d_scene);
     if (c->d_oob) cudaFree(c->d_oob);
+    if (c->d_exp_tab) cudaFree(c->d_exp_tab);
     for (auto& e : c->ev) if (e) cudaEventDestroy(e);
     if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
     delete c;
@@ -344,6 +353,8 @@ extern "C" int pb200_set_scene(pb200_ctx* c, const pb200_scene* s) {
     PB_CUDA(c, dalloc(&h.star_shift, h.Mp));
     PB_CUDA(c, dalloc(&h.w_in, (size_t)h.n_orb * h.Mp));
     PB_CUDA(c, dalloc(&h.ncol, (size_t)n_atoms * h.n_orb * h.Mp));
+    PB_CUDA(c, dalloc(&h.rec, (size_t)(n_atoms + 1) * h.n_orb * h.Mp));
+    h.exp_tab = c->d_exp_tab;
     for (int i = 0; i < s->n_scenarios; ++i)
         if (h.scen[i].density_slot >= 0)
             PB_CUDA(c, dalloc(&h.density[h.scen[i].density_slot], (size_t)h.n_orb * h.M * h.n_x));
@@ -397,9 +408,11 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     const int n_tiles = h.Mp / kChordTile;
     const int wpt = c->general_path ? 1 : transit_wpt_for(h.n_atoms);
     const int64_t ctas = ((n_wav_sel + 128 * wpt - 1) / (128 * wpt)) * n_phase;
-    int64_t want = ((int64_t)c->sm_count * 8 + ctas - 1) / ctas;   // aim at >= 8 CTAs per SM
+    // many more CTAs than resident slots (~10 per SM) so that the last wave is a small fraction of the
+    // run; a CTA keeps at least 4 tiles (1024 chords) to amortise its sigma-lookup prologue
+    int64_t want = ((int64_t)c->sm_count * 80 + ctas - 1) / ctas;
+    if (want > n_tiles / 4) want = n_tiles / 4;
     if (want < 1) want = 1;
-    if (want > n_tiles) want = n_tiles;
     prm.tiles_per_split = (int)((n_tiles + want - 1) / want);
     prm.n_split = (n_tiles + prm.tiles_per_split - 1) / prm.tiles_per_split;
 

@@ -59,7 +59,11 @@ column_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, int* 
         if (m >= sc.M) {   // padding of the phase-major rows: zero weight, zero column
             if (lane == 0) {
                 sc.w_in[row] = 0.0;
-                for (int a = 0; a < sc.n_atoms; ++a) sc.ncol[(int64_t)a * sc.n_orb * sc.Mp + row] = 0.0;
+                sc.rec[row * (sc.n_atoms + 1)] = 0.0;
+                for (int a = 0; a < sc.n_atoms; ++a) {
+                    sc.ncol[(int64_t)a * sc.n_orb * sc.Mp + row] = 0.0;
+                    sc.rec[row * (sc.n_atoms + 1) + 1 + a] = 0.0;
+                }
             }
             continue;
         }
@@ -68,7 +72,11 @@ column_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, int* 
         const double y = __dmul_rn(rho, sc.sin_phi[iphi]);
         const double z = __dmul_rn(rho, sc.cos_phi[iphi]);
         const bool blocked = pb_blocked(sc, p, y, z);
-        if (lane == 0) sc.w_in[row] = blocked ? 0.0 : sc.w_out[m];
+        if (lane == 0) {
+            const double wv = blocked ? 0.0 : sc.w_out[m];
+            sc.w_in[row] = wv;
+            sc.rec[row * (sc.n_atoms + 1)] = wv;
+        }
         for (int s = 0; s < sc.n_scen; ++s) {
             const DevScenario& S = sc.scen[s];
             double sum = 0.0;
@@ -103,8 +111,11 @@ column_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, int* 
             if (lane == 0) {
                 for (int k = S.first_cons; k < S.first_cons + S.n_cons; ++k) {
                     const DevConstituent& C = sc.cons[k];
-                    if (C.kind == 0)   // col = sum_x(n*chi) * delta_x, gasProperties.py:940
-                        sc.ncol[(int64_t)C.atom_index * sc.n_orb * sc.Mp + row] = (sum * C.chi) * sc.delta_x;
+                    if (C.kind == 0) {   // col = sum_x(n*chi) * delta_x, gasProperties.py:940
+                        const double col = (sum * C.chi) * sc.delta_x;
+                        sc.ncol[(int64_t)C.atom_index * sc.n_orb * sc.Mp + row] = col;
+                        sc.rec[row * (sc.n_atoms + 1) + 1 + C.atom_index] = col;
+                    }
                 }
             }
         }

@@ -56,6 +56,10 @@ struct DevScene {
     double* ncol;         // [n_atoms][n_orb][Mp]  column densities
     double* density[kMaxScenarios];  // [n_orb][M][n_x] number density of molecular scenarios
     double* fout;         // [1] or [n_wav]  sum of unattenuated flux
+    // chord records of kernel (c'): [n_orb][Mp][n_atoms+1] = {w_in, Ncol_0 .. Ncol_{S-1}}, one TMA
+    // bulk copy per 256-chord tile
+    double* rec;
+    const double* exp_tab;   // [64] 2^(j/64), correctly rounded (pb_exp_neg_tab)
 };
 
 // launch parameters of kernel (c') and its variants

@@ -47,6 +47,54 @@ __device__ __forceinline__ double pb_exp_neg(double t) {
     return __hiloint2double(__double2hiint(p) + (k << 20), __double2loint(p));
 }
 
+// ---------------------------------------------------------------------------------------------
+// exp(u) for u <= 0 -- the Beer-Lambert inner loop of kernel (c') -- with a 64-entry table:
+//   k = rint(u * 64/ln2) = 64 e + j,  r = u - k ln2/64  (|r| <= ln2/128 = 5.4e-3)
+//   exp(u) = 2^e * T[j] * (1 + r + r^2/2 + r^3/6 + r^4/24),   T[j] = 2^(j/64)
+// 9 FP64-pipe instructions instead of 18 (the FP64 pipe, 64 lanes/SM, is what bounds the kernel);
+// truncation r^5/120 <= 3.9e-14 relative, reduction error <= 1.1e-16 * |k| ln2/64 (4e-15 at u = -40).
+// u is clamped at -700 on its high word (integer pipe), which keeps 2^e * T[j] normal.
+// `tab` points at this lane's column of the table in shared memory, laid out [j][16] so that the
+// 16 lanes of a half-warp hit 16 different bank pairs whatever their j (conflict-free LDS.64).
+// ---------------------------------------------------------------------------------------------
+constexpr int kExpTabEntries = 64;
+constexpr int kExpTabCopies = 16;
+
+// Table entry j as stored: 2^(j/64) with (j << 14) subtracted from its high word, so that adding
+// (k << 14) -- k = 64 e + j -- yields the high word of 2^e * 2^(j/64) in ONE integer op.
+__host__ __device__ inline double pb_exp_tab_entry(double two_pow_j64, int j) {
+    union { double d; uint64_t u; } v;
+    v.d = two_pow_j64;
+    v.u -= (uint64_t)j << (14 + 32);
+    return v.d;
+}
+
+// tab_addr: shared-window byte address of this lane's column, table laid out [j][16] doubles
+__device__ __forceinline__ double pb_exp_neg_tab(double u, uint32_t tab_addr) {
+    const unsigned hi = min((unsigned)__double2hiint(u), 0xC085E000u);   // u >= -700 (and -0.0/+tiny pass)
+    u = __hiloint2double((int)hi, __double2loint(u));
+    const double kMagic = 6755399441055744.0;            // 1.5 * 2^52
+    double kd = fma(u, 92.332482616893656877, kMagic);   // 64 / ln 2
+    const int k = __double2loint(kd);
+    kd -= kMagic;
+    const double r = fma(kd, -1.0830424696249145e-02, u);   // ln2 / 64
+    int t_lo, t_hi;
+    asm("{\n"
+        ".reg .b32 j, a;\n"
+        "and.b32 j, %2, 63;\n"
+        "mad.lo.u32 a, j, 128, %3;\n"
+        "ld.shared.v2.b32 {%0, %1}, [a];\n"
+        "}\n"
+        : "=r"(t_lo), "=r"(t_hi)
+        : "r"(k), "r"(tab_addr));
+    const double T = __hiloint2double(t_hi + (k << 14), t_lo);   // 2^e * 2^(j/64)
+    double p = fma(r, 4.1666666666666664e-02, 1.6666666666666666e-01);
+    p = fma(p, r, 0.5);
+    p = fma(p, r, 1.0);
+    const double q = r * p;
+    return fma(T, q, T);
+}
+
 // exp(a) for |a| <= 700 (same kernel as pb_exp_neg, two-sided); used for 10**v = exp(v ln10) of the
 // molecular tables, where |v| <= 50 keeps the extra rounding of v*ln10 below 1e-14 relative.
 __device__ __forceinline__ double pb_exp(double a) {

@@ -4,14 +4,18 @@
 //
 // restates Transit.sumOverChords (gasProperties.py:1205-1258) together with the atomic branch of
 // Atmosphere.getLOSopticalDepth_Batch (:937-954) without ever materialising tau(chord, lambda):
-//   * a thread owns WPT wavelengths of one orbital phase and keeps sigma_a(p, w) in registers
+//   * a thread owns WPT wavelengths of one orbital phase and keeps -sigma_a(p, w) in registers
 //     (looked up once in the prologue: np.interp + 10**v - offset, i.e. n_interp_log :34-51);
 //   * the chord records {w_in, Ncol_0..Ncol_{S-1}} of the phase stream through shared memory in
-//     256-chord tiles, fetched by 1-D TMA bulk copies (cp.async.bulk + mbarrier, double buffered);
+//     256-chord tiles, one 1-D TMA bulk copy per tile (cp.async.bulk + mbarrier, double buffered);
 //     every thread of the CTA reads the same record, so the LDS is a broadcast;
-//   * fp64 exp, fp64 accumulators; optional split of the chord axis over blockIdx.z for small
-//     (phase x lambda) grids, reduced in a fixed order by finalize_kernel (deterministic).
-// Chord-level early-outs (w_in == 0: blocked/padding; all Ncol == 0: exp(0) = 1) are CTA-uniform.
+//   * fp64 exp (table-driven, pb_exp_neg_tab: the kernel is bound by the FP64 pipe, so the exp is
+//     built to need as few FP64 instructions as possible), fp64 accumulators; the chord axis is
+//     split over blockIdx.z to get many more CTAs than resident slots (tail effect), partial sums
+//     reduced in a fixed order by finalize_kernel (deterministic).
+// The chord-level early-out (w_in == 0: blocked/padding) is CTA-uniform.
+#include <cstdlib>
+
 #include "pb200_internal.cuh"
 
 namespace pb200 {
@@ -54,9 +58,17 @@ template <int S, int WPT>
 __global__ void __launch_bounds__(kTransitThreads)
 transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
     const DevScene& sc = *scp;
-    // stage layout: [stage][row][kChordTile], row 0 = w_in, rows 1..S = Ncol_a
+    // shared memory: exp table [64][16] | stage 0 records | stage 1 records; a record is
+    // {w_in, Ncol_0 .. Ncol_{S-1}}, a stage holds kChordTile records
     extern __shared__ __align__(128) double smem[];
     __shared__ uint64_t full_bar[2];
+    constexpr int R = S + 1;
+    constexpr int kTabDoubles = kExpTabEntries * kExpTabCopies;
+    constexpr int kStageDoubles = R * kChordTile;
+    constexpr uint32_t kStageBytes = kStageDoubles * sizeof(double);
+    double* etab = smem;
+    double* stages = smem + kTabDoubles;
+
     const int tid = threadIdx.x;
     const int p = prm.phase_lo + blockIdx.y;
     const int split = blockIdx.z;
@@ -65,34 +77,27 @@ transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
     int n_tiles = n_tiles_total - tile0;
     if (n_tiles > prm.tiles_per_split) n_tiles = prm.tiles_per_split;
 
-    constexpr uint32_t kRowBytes = kChordTile * sizeof(double);
-    constexpr int kStageDoubles = (S + 1) * kChordTile;
-
     if (tid == 0) {
         mbar_init(&full_bar[0], 1);
         mbar_init(&full_bar[1], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+    for (int i = tid; i < kTabDoubles; i += kTransitThreads) etab[i] = __ldg(sc.exp_tab + (i / kExpTabCopies));
     __syncthreads();
 
-    const double* w_in_row = sc.w_in + (int64_t)p * sc.Mp;
-    const double* ncol_row = sc.ncol + (int64_t)p * sc.Mp;
-    const int64_t atom_stride = (int64_t)sc.n_orb * sc.Mp;
+    const double* rec_row = sc.rec + ((int64_t)p * sc.Mp + (int64_t)tile0 * kChordTile) * R;
     auto issue = [&](int tile, int stage) {
-        double* dst = smem + stage * kStageDoubles;
-        const int64_t off = (int64_t)(tile0 + tile) * kChordTile;
-        mbar_expect_tx(&full_bar[stage], (S + 1) * kRowBytes);
-        tma_bulk_g2s(dst, w_in_row + off, kRowBytes, &full_bar[stage]);
-#pragma unroll
-        for (int a = 0; a < S; ++a)
-            tma_bulk_g2s(dst + (a + 1) * kChordTile, ncol_row + a * atom_stride + off, kRowBytes, &full_bar[stage]);
+        mbar_expect_tx(&full_bar[stage], kStageBytes);
+        tma_bulk_g2s(stages + stage * kStageDoubles, rec_row + (int64_t)tile * kStageDoubles, kStageBytes,
+                     &full_bar[stage]);
     };
     if (tid == 0 && n_tiles > 0) issue(0, 0);
 
-    // ---- prologue: sigma_a(p, w) for this thread's wavelengths (kernel (b1) inlined) ------------
+    // ---- prologue: -sigma_a(p, w) for this thread's wavelengths (kernel (b1) inlined) -----------
     const int64_t w_base = prm.wav_lo + (int64_t)blockIdx.x * (kTransitThreads * WPT) + tid;
-    double sig[S][WPT];
+    double nsig[S][WPT];
     double acc[WPT];
+    bool bad = false;   // NaN cross-section (NaN wavelength): the reference propagates NaN into R
 #pragma unroll
     for (int j = 0; j < WPT; ++j) {
         acc[j] = 0.0;
@@ -107,42 +112,41 @@ transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
             if (live) {
                 const double shift = __ldg(sc.scen[C.scenario].shift + p);
                 v = pb_interp_log(C.tab_x, C.tab_y, C.n_tab, shift * lam, C.offset);   // :917, :950-951
+                bad |= (v != v);
             }
 #pragma unroll
             for (int aa = 0; aa < S; ++aa)
-                if (aa == a) sig[aa][j] = v;
+                if (aa == a) nsig[aa][j] = -v;
             ++a;
         }
     }
 
     // ---- main loop over chord tiles -----------------------------------------------------------
+    const uint32_t tab_lane = smem_u32(etab) + (tid & (kExpTabCopies - 1)) * (uint32_t)sizeof(double);
     for (int t = 0; t < n_tiles; ++t) {
         const int stage = t & 1;
         if (tid == 0 && t + 1 < n_tiles) issue(t + 1, stage ^ 1);
         mbar_wait(&full_bar[stage], (t >> 1) & 1);
-        const double* sw = smem + stage * kStageDoubles;
+        const double* sw = stages + stage * kStageDoubles;
 #pragma unroll 2
         for (int m = 0; m < kChordTile; ++m) {
-            const double wv = sw[m];
-            if (wv == 0.0) continue;   // blocked chord or padding: F_in = 0 (gasProperties.py:1233)
-            double N[S];
-            bool any = false;
+            double wv, N[S];
+            if constexpr (S == 1) {
+                const double2 v = *reinterpret_cast<const double2*>(sw + 2 * m);   // broadcast LDS.128
+                wv = v.x; N[0] = v.y;
+            } else {
+                wv = sw[m * R];
 #pragma unroll
-            for (int a = 0; a < S; ++a) {
-                N[a] = sw[(a + 1) * kChordTile + m];
-                any |= (N[a] != 0.0);
+                for (int a = 0; a < S; ++a) N[a] = sw[m * R + 1 + a];
             }
-            if (!any) {   // tau == 0 exactly
-#pragma unroll
-                for (int j = 0; j < WPT; ++j) acc[j] += wv;
-                continue;
-            }
+            // blocked chord or padding: F_in = 0 (gasProperties.py:1233); CTA-uniform, integer test
+            if ((__double2hiint(wv) | __double2loint(wv)) == 0) continue;
 #pragma unroll
             for (int j = 0; j < WPT; ++j) {
-                double tau = N[0] * sig[0][j];
+                double u = N[0] * nsig[0][j];                                      // -tau, :954
 #pragma unroll
-                for (int a = 1; a < S; ++a) tau = fma(N[a], sig[a][j], tau);   // :954
-                acc[j] = fma(wv, pb_exp_neg(tau), acc[j]);                    // :1241, :1244/:1255
+                for (int a = 1; a < S; ++a) u = fma(N[a], nsig[a][j], u);
+                acc[j] = fma(wv, pb_exp_neg_tab(u, tab_lane), acc[j]);            // :1241, :1244/:1255
             }
         }
         __syncthreads();   // stage may be refilled by the producer in the next iteration
@@ -155,8 +159,14 @@ transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
         const int64_t w = w_base + (int64_t)j * kTransitThreads;
         if (w >= prm.wav_lo + prm.n_wav_sel) continue;
         const int64_t o = (int64_t)blockIdx.y * prm.n_wav_sel + (w - prm.wav_lo);
-        if (prm.n_split == 1) prm.R[o] = acc[j] / fout;                        // :1258
-        else prm.partial[(int64_t)split * prm.n_phase * prm.n_wav_sel + o] = acc[j];
+        double v = acc[j];
+        if (bad) {
+#pragma unroll
+            for (int a = 0; a < S; ++a)
+                if (nsig[a][j] != nsig[a][j]) v = nsig[a][j];
+        }
+        if (prm.n_split == 1) prm.R[o] = v / fout;                             // :1258
+        else prm.partial[(int64_t)split * prm.n_phase * prm.n_wav_sel + o] = v;
     }
 }
 
@@ -174,7 +184,7 @@ __global__ void finalize_kernel(const DevScene* __restrict__ scp, const TransitP
 
 template <int S, int WPT>
 static cudaError_t launch_one(const DevScene* d_scene, const TransitParams& prm, cudaStream_t st) {
-    const size_t smem = 2 * (S + 1) * kChordTile * sizeof(double);
+    const size_t smem = (kExpTabEntries * kExpTabCopies + 2 * (S + 1) * kChordTile) * sizeof(double);
     auto kern = transit_kernel<S, WPT>;
     if (smem > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -186,15 +196,25 @@ static cudaError_t launch_one(const DevScene* d_scene, const TransitParams& prm,
     return cudaGetLastError();
 }
 
-int transit_wpt_for(int n_atoms) { return n_atoms <= 4 ? 4 : 2; }
+static int env_wpt() {
+    static const int v = [] { const char* e = getenv("PB200_WPT"); return e ? atoi(e) : 0; }();
+    return v;
+}
+
+int transit_wpt_for(int n_atoms) {
+    const int forced = env_wpt();
+    if (n_atoms <= 4) return (forced == 4 || forced == 8) ? forced : 8;
+    return 2;
+}
 
 // returns cudaSuccess, or cudaErrorInvalidValue when n_atoms is outside the compiled range
 cudaError_t launch_transit(const DevScene* d_scene, int n_atoms, const TransitParams& prm, cudaStream_t st) {
+    const bool w8 = transit_wpt_for(n_atoms) == 8;
     switch (n_atoms) {
-        case 1: return launch_one<1, 4>(d_scene, prm, st);
-        case 2: return launch_one<2, 4>(d_scene, prm, st);
-        case 3: return launch_one<3, 4>(d_scene, prm, st);
-        case 4: return launch_one<4, 4>(d_scene, prm, st);
+        case 1: return w8 ? launch_one<1, 8>(d_scene, prm, st) : launch_one<1, 4>(d_scene, prm, st);
+        case 2: return w8 ? launch_one<2, 8>(d_scene, prm, st) : launch_one<2, 4>(d_scene, prm, st);
+        case 3: return w8 ? launch_one<3, 8>(d_scene, prm, st) : launch_one<3, 4>(d_scene, prm, st);
+        case 4: return w8 ? launch_one<4, 8>(d_scene, prm, st) : launch_one<4, 4>(d_scene, prm, st);
         case 5: return launch_one<5, 2>(d_scene, prm, st);
         case 6: return launch_one<6, 2>(d_scene, prm, st);
         case 7: return launch_one<7, 2>(d_scene, prm, st);

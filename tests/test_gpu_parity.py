@@ -101,16 +101,16 @@ def test_number_density_and_column(name, transits, golden):
     blocked, _ = tr.getChordMasks()
     for i, dist in enumerate(tr.atmosphere.densityDistributionList):
         n = dist.calculateNumberDensity(x, chords[sub, 0], chords[sub, 1], chords[sub, 2])
-        np.testing.assert_allclose(n, g[f"density_{i}"], rtol=1e-12, atol=0)
+        np.testing.assert_allclose(n, g[f"density_{i}"], rtol=1e-12, atol=1e-300)   # denormal tails
         one = dist.calculateNumberDensity(x, chords[sub[3], 0], chords[sub[3], 1], chords[sub[3], 2])
         assert one.shape == (x.size,)
-        np.testing.assert_allclose(one, g[f"density_{i}"][3], rtol=1e-12, atol=0)
+        np.testing.assert_allclose(one, g[f"density_{i}"][3], rtol=1e-12, atol=1e-300)
         n_grid = tr.getNumberDensityGrid(i)
-        np.testing.assert_allclose(n_grid[sub], g[f"density_{i}"], rtol=1e-12, atol=0)
+        np.testing.assert_allclose(n_grid[sub], g[f"density_{i}"], rtol=1e-12, atol=1e-300)
     ncol = tr.getColumnDensityGrid()
     act = ~blocked        # the reference evaluates only unblocked chords (gasProperties.py:1235-1240)
     for k in range(ncol.shape[0]):
-        np.testing.assert_allclose(ncol[k][act], g[f"ncol_{k}"][act], rtol=1e-12, atol=0)
+        np.testing.assert_allclose(ncol[k][act], g[f"ncol_{k}"][act], rtol=1e-12, atol=1e-290)
         assert np.all(ncol[k][~act] == 0.0)
 
 
@@ -178,7 +178,8 @@ def test_voigt_tables_against_reference(name, transits, golden):
             assert np.sum(lf.x) == float(g[f"table_xsum_{k}"])
             s_got, s_ref = 10 ** lf.y[::st], 10 ** g[f"table_y_{k}"]
             big = s_ref > 1e-40
-            assert np.max(np.abs(s_got[big] - s_ref[big]) / s_ref[big]) < 1e-9
+            if big.any():      # a species without lines in the range has sigma == 0 everywhere
+                assert np.max(np.abs(s_got[big] - s_ref[big]) / s_ref[big]) < 1e-9
             np.testing.assert_allclose(lf.y[::st], g[f"table_y_{k}"], rtol=0, atol=1e-9)
             k += 1
 
