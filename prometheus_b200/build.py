@@ -17,6 +17,9 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libprometheus_b200.so")
 SOURCES = ["pb200_api.cu", "pb200_density.cu", "pb200_sigma.cu", "pb200_transit.cu", "pb200_general.cu"]
 HEADERS = ["pb200_internal.cuh", "pb200_math.cuh", "pb200_molecule.cuh", "../../include/prometheus_b200.h"]
+# per-translation-unit extra flags (none at present; -Xptxas -O1 on pb200_transit.cu was tried to keep a
+# software-interleaved instruction order and made no difference)
+PER_SOURCE_FLAGS = {}
 NVCC_FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
               "-Xcompiler", "-fPIC", "--fmad=true", "-Xptxas", "-v"]
 
@@ -34,6 +37,7 @@ def _digest() -> str:
         with open(os.path.join(CSRC, f), "rb") as fh:
             h.update(fh.read())
     h.update(" ".join(NVCC_FLAGS).encode())
+    h.update(repr(sorted(PER_SOURCE_FLAGS.items())).encode())
     return h.hexdigest()
 
 
@@ -46,7 +50,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     procs = []
     for src in SOURCES:
         obj = os.path.join(CSRC, src.replace(".cu", ".o"))
-        cmd = [_nvcc(), *NVCC_FLAGS, "-c", os.path.join(CSRC, src), "-o", obj]
+        cmd = [_nvcc(), *NVCC_FLAGS, *PER_SOURCE_FLAGS.get(src, []), "-c", os.path.join(CSRC, src), "-o", obj]
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
         objs.append(obj)
     log = []

@@ -115,6 +115,8 @@ column_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, int* 
                         const double col = (sum * C.chi) * sc.delta_x;
                         sc.ncol[(int64_t)C.atom_index * sc.n_orb * sc.Mp + row] = col;
                         sc.rec[row * (sc.n_atoms + 1) + 1 + C.atom_index] = col;
+                        // densities are >= 0, so the bit patterns order like the values
+                        if (col > 0.0) atomicMax(sc.nmax + (int64_t)C.atom_index * sc.n_orb + p, (unsigned long long)__double_as_longlong(col));
                     }
                 }
             }

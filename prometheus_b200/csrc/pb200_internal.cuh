@@ -59,7 +59,8 @@ struct DevScene {
     // chord records of kernel (c'): [n_orb][Mp][n_atoms+1] = {w_in, Ncol_0 .. Ncol_{S-1}}, one TMA
     // bulk copy per 256-chord tile
     double* rec;
-    const double* exp_tab;   // [64] 2^(j/64), correctly rounded (pb_exp_neg_tab)
+    const double* exp_tab;   // [256] 2^(j/256), correctly rounded, high word biased (pb_exp_neg_tab)
+    unsigned long long* nmax;   // [n_atoms][n_orb] bit pattern of max_m Ncol (>= 0), set by kernel (a')
 };
 
 // launch parameters of kernel (c') and its variants

@@ -48,48 +48,63 @@ __device__ __forceinline__ double pb_exp_neg(double t) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// exp(u) for u <= 0 -- the Beer-Lambert inner loop of kernel (c') -- with a 64-entry table:
-//   k = rint(u * 64/ln2) = 64 e + j,  r = u - k ln2/64  (|r| <= ln2/128 = 5.4e-3)
-//   exp(u) = 2^e * T[j] * (1 + r + r^2/2 + r^3/6 + r^4/24),   T[j] = 2^(j/64)
-// 9 FP64-pipe instructions instead of 18 (the FP64 pipe, 64 lanes/SM, is what bounds the kernel);
-// truncation r^5/120 <= 3.9e-14 relative, reduction error <= 1.1e-16 * |k| ln2/64 (4e-15 at u = -40).
-// u is clamped at -700 on its high word (integer pipe), which keeps 2^e * T[j] normal.
-// `tab` points at this lane's column of the table in shared memory, laid out [j][16] so that the
-// 16 lanes of a half-warp hit 16 different bank pairs whatever their j (conflict-free LDS.64).
+// exp(u) for u <= 0 -- the Beer-Lambert inner loop of kernel (c') -- with a 256-entry table:
+//   k = rint(u * 256/ln2) = 256 e + j,  r = u - k ln2/256  (|r| <= ln2/512 = 1.35e-3)
+//   exp(u) = 2^e * T[j] * (1 + r + r^2/2 + r^3/6),   T[j] = 2^(j/256)
+// 8 FP64-pipe instructions (+1 for u = N*sigma, +1 for the accumulate) instead of 18 for a
+// polynomial-only exp: the kernel is bound by the FP64 pipe (64 lanes/SM, 2 cycles per warp
+// instruction) and, to a lesser degree, by the integer instructions issued next to it
+// (profiles/microbench/exp_mix.cu), so both are kept minimal:
+//   * table entry j is stored with (j << 12) subtracted from its high word, so adding (k << 12)
+//     gives the high word of 2^e * 2^(j/256) in one integer op;
+//   * the table is laid out [j][8] in shared memory: a half-warp's 16 lanes hit 8 bank pairs,
+//     at most 2-way conflicts, which the otherwise idle LSU absorbs;
+//   * the clamp u >= -700 (keeps 2^e normal) is only compiled into the CLAMP variant, used by warps
+//     whose largest possible tau can exceed 690.
+// Accuracy: truncation r^4/24 <= 1.4e-13 relative, reduction error <= 1.1e-16 |k| ln2/256.
 // ---------------------------------------------------------------------------------------------
-constexpr int kExpTabEntries = 64;
-constexpr int kExpTabCopies = 16;
+constexpr int kExpTabEntries = 256;
+constexpr int kExpTabCopies = 8;
+constexpr int kExpTabShift = 12;                           // 20 - log2(kExpTabEntries)
+constexpr double kExpMagic = 6755399441055744.0;           // 1.5 * 2^52: rint() through the adder
+constexpr double kExpScale = 369.32993046757462751;        // 256 / ln 2
+constexpr double kExpStep = 2.7076061740622862e-03;        // ln 2 / 256
+constexpr double kExpClampTau = 690.0;
 
-// Table entry j as stored: 2^(j/64) with (j << 14) subtracted from its high word, so that adding
-// (k << 14) -- k = 64 e + j -- yields the high word of 2^e * 2^(j/64) in ONE integer op.
-__host__ __device__ inline double pb_exp_tab_entry(double two_pow_j64, int j) {
+__host__ __device__ inline double pb_exp_tab_entry(double two_pow_frac, int j) {
     union { double d; uint64_t u; } v;
-    v.d = two_pow_j64;
-    v.u -= (uint64_t)j << (14 + 32);
+    v.d = two_pow_frac;
+    v.u -= (uint64_t)j << (kExpTabShift + 32);
     return v.d;
 }
 
-// tab_addr: shared-window byte address of this lane's column, table laid out [j][16] doubles
-__device__ __forceinline__ double pb_exp_neg_tab(double u, uint32_t tab_addr) {
-    const unsigned hi = min((unsigned)__double2hiint(u), 0xC085E000u);   // u >= -700 (and -0.0/+tiny pass)
-    u = __hiloint2double((int)hi, __double2loint(u));
-    const double kMagic = 6755399441055744.0;            // 1.5 * 2^52
-    double kd = fma(u, 92.332482616893656877, kMagic);   // 64 / ln 2
-    const int k = __double2loint(kd);
-    kd -= kMagic;
-    const double r = fma(kd, -1.0830424696249145e-02, u);   // ln2 / 64
+// T = 2^e * 2^(j/256) for k = 256 e + j.  tab_addr: shared-window byte address of this lane's column.
+// AND + IMAD + LDS.64 + IMAD, all off the FP64 pipe.
+__device__ __forceinline__ double pb_exp_tab_load(uint32_t tab_addr, int k) {
     int t_lo, t_hi;
-    asm("{\n"
+    asm volatile("{\n"
         ".reg .b32 j, a;\n"
-        "and.b32 j, %2, 63;\n"
-        "mad.lo.u32 a, j, 128, %3;\n"
+        "and.b32 j, %2, 255;\n"
+        "mad.lo.u32 a, j, 64, %3;\n"
         "ld.shared.v2.b32 {%0, %1}, [a];\n"
         "}\n"
         : "=r"(t_lo), "=r"(t_hi)
         : "r"(k), "r"(tab_addr));
-    const double T = __hiloint2double(t_hi + (k << 14), t_lo);   // 2^e * 2^(j/64)
-    double p = fma(r, 4.1666666666666664e-02, 1.6666666666666666e-01);
-    p = fma(p, r, 0.5);
+    return __hiloint2double(t_hi + (k << kExpTabShift), t_lo);
+}
+
+template <bool CLAMP>
+__device__ __forceinline__ double pb_exp_neg_tab(double u, uint32_t tab_addr) {
+    if (CLAMP) {
+        const unsigned hi = min((unsigned)__double2hiint(u), 0xC085E000u);   // u >= -700 (-0.0/+tiny pass)
+        u = __hiloint2double((int)hi, __double2loint(u));
+    }
+    double kd = fma(u, kExpScale, kExpMagic);
+    const int k = __double2loint(kd);
+    kd -= kExpMagic;
+    const double r = fma(kd, -kExpStep, u);
+    const double T = pb_exp_tab_load(tab_addr, k);
+    double p = fma(r, 1.6666666666666666e-01, 0.5);
     p = fma(p, r, 1.0);
     const double q = r * p;
     return fma(T, q, T);

@@ -135,15 +135,26 @@ __global__ void __launch_bounds__(256) probe_dfma_kernel(double* out, int iters)
     }
     out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
 }
-__global__ void __launch_bounds__(256) probe_exp_kernel(double* out, int iters) {
-    double t0 = 1e-3 * (threadIdx.x + 1), t1 = t0 * 1.5, t2 = t0 * 2.5, t3 = t0 * 3.5;
-    double s0 = 0, s1 = 0, s2 = 0, s3 = 0;
-    for (int i = 0; i < iters; ++i) {
-        s0 = fma(0.5, pb_exp_neg(t0), s0); s1 = fma(0.5, pb_exp_neg(t1), s1);
-        s2 = fma(0.5, pb_exp_neg(t2), s2); s3 = fma(0.5, pb_exp_neg(t3), s3);
-        t0 += 1e-7; t1 += 1e-7; t2 += 1e-7; t3 += 1e-7;
+// exp throughput of the production exp (pb_exp_neg_tab): 8 independent exp per thread and iteration
+__global__ void __launch_bounds__(256) probe_exp_kernel(double* out, int iters, const double* __restrict__ exp_tab) {
+    __shared__ __align__(16) double etab[kExpTabEntries * kExpTabCopies];
+    for (int i = threadIdx.x; i < kExpTabEntries * kExpTabCopies; i += blockDim.x) etab[i] = exp_tab[i / kExpTabCopies];
+    __syncthreads();
+    const uint32_t tab_lane = (uint32_t)__cvta_generic_to_shared(etab) + (threadIdx.x & (kExpTabCopies - 1)) * 8u;
+    double t[8], s[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { t[i] = -1e-3 * (threadIdx.x + 1) * (i + 1); s[i] = 0.0; }
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            s[i] = fma(0.5, pb_exp_neg_tab<false>(t[i], tab_lane), s[i]);
+            t[i] = __hiloint2double(__double2hiint(t[i]), __double2loint(t[i]) + 64);   // next argument: integer pipe
+        }
     }
-    out[blockIdx.x * blockDim.x + threadIdx.x] = s0 + s1 + s2 + s3;
+    double r = 0.0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) r += s[i];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = r;
 }
 
 // ---- launchers ------------------------------------------------------------------------------------
@@ -190,8 +201,8 @@ void launch_optical_depth(const DevScene* d_scene, const double* sigma_u, int64_
 void launch_probe_dfma(double* out, int blocks, int iters, cudaStream_t st) {
     probe_dfma_kernel<<<blocks, 256, 0, st>>>(out, iters);
 }
-void launch_probe_exp(double* out, int blocks, int iters, cudaStream_t st) {
-    probe_exp_kernel<<<blocks, 256, 0, st>>>(out, iters);
+void launch_probe_exp(double* out, int blocks, int iters, const double* exp_tab, cudaStream_t st) {
+    probe_exp_kernel<<<blocks, 256, 0, st>>>(out, iters, exp_tab);
 }
 
 }  // namespace pb200

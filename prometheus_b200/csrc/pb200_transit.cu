@@ -53,6 +53,34 @@ __device__ __forceinline__ void tma_bulk_g2s(void* dst, const void* src, uint32_
 }
 
 
+// One 256-chord tile: acc[j] += w_m * exp(-sum_a N_a(m) sigma_a(j)) for the thread's WPT wavelengths.
+template <int S, int WPT, bool CLAMP>
+__device__ __forceinline__ void transit_tile(const double* __restrict__ sw, const double (&nsig)[S][WPT],
+                                             double (&acc)[WPT], uint32_t tab_lane) {
+    constexpr int R = S + 1;
+#pragma unroll 2
+    for (int m = 0; m < kChordTile; ++m) {
+        double wv, N[S];
+        if constexpr (S == 1) {
+            const double2 v = *reinterpret_cast<const double2*>(sw + 2 * m);   // broadcast LDS.128
+            wv = v.x; N[0] = v.y;
+        } else {
+            wv = sw[m * R];
+#pragma unroll
+            for (int a = 0; a < S; ++a) N[a] = sw[m * R + 1 + a];
+        }
+        // blocked chord or padding: F_in = 0 (gasProperties.py:1233); CTA-uniform, integer test
+        if ((__double2hiint(wv) | __double2loint(wv)) == 0) continue;
+#pragma unroll
+        for (int j = 0; j < WPT; ++j) {
+            double u = N[0] * nsig[0][j];                                          // -tau, :954
+#pragma unroll
+            for (int a = 1; a < S; ++a) u = fma(N[a], nsig[a][j], u);
+            acc[j] = fma(wv, pb_exp_neg_tab<CLAMP>(u, tab_lane), acc[j]);         // :1241, :1244/:1255
+        }
+    }
+}
+
 // S atomic constituents (compile time), WPT wavelengths per thread
 template <int S, int WPT>
 __global__ void __launch_bounds__(kTransitThreads)
@@ -121,6 +149,19 @@ transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
         }
     }
 
+    // A warp needs the clamped exp only if one of its wavelengths can reach tau > 690 on the densest
+    // chord of this phase (warp-uniform choice, so the two loop variants never diverge).
+    bool clamp = false;
+#pragma unroll
+    for (int j = 0; j < WPT; ++j) {
+        double tmax = 0.0;
+#pragma unroll
+        for (int a = 0; a < S; ++a)
+            tmax = fma(__longlong_as_double((long long)__ldg(sc.nmax + (int64_t)a * sc.n_orb + p)), -nsig[a][j], tmax);
+        clamp |= !(tmax < kExpClampTau);   // NaN -> clamped variant (harmless)
+    }
+    clamp = __any_sync(0xffffffffu, clamp);
+
     // ---- main loop over chord tiles -----------------------------------------------------------
     const uint32_t tab_lane = smem_u32(etab) + (tid & (kExpTabCopies - 1)) * (uint32_t)sizeof(double);
     for (int t = 0; t < n_tiles; ++t) {
@@ -128,27 +169,8 @@ transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
         if (tid == 0 && t + 1 < n_tiles) issue(t + 1, stage ^ 1);
         mbar_wait(&full_bar[stage], (t >> 1) & 1);
         const double* sw = stages + stage * kStageDoubles;
-#pragma unroll 2
-        for (int m = 0; m < kChordTile; ++m) {
-            double wv, N[S];
-            if constexpr (S == 1) {
-                const double2 v = *reinterpret_cast<const double2*>(sw + 2 * m);   // broadcast LDS.128
-                wv = v.x; N[0] = v.y;
-            } else {
-                wv = sw[m * R];
-#pragma unroll
-                for (int a = 0; a < S; ++a) N[a] = sw[m * R + 1 + a];
-            }
-            // blocked chord or padding: F_in = 0 (gasProperties.py:1233); CTA-uniform, integer test
-            if ((__double2hiint(wv) | __double2loint(wv)) == 0) continue;
-#pragma unroll
-            for (int j = 0; j < WPT; ++j) {
-                double u = N[0] * nsig[0][j];                                      // -tau, :954
-#pragma unroll
-                for (int a = 1; a < S; ++a) u = fma(N[a], nsig[a][j], u);
-                acc[j] = fma(wv, pb_exp_neg_tab(u, tab_lane), acc[j]);            // :1241, :1244/:1255
-            }
-        }
+        if (clamp) transit_tile<S, WPT, true>(sw, nsig, acc, tab_lane);
+        else transit_tile<S, WPT, false>(sw, nsig, acc, tab_lane);
         __syncthreads();   // stage may be refilled by the producer in the next iteration
     }
 
