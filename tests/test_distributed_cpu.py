@@ -1,0 +1,82 @@
+"""world_size > 1 on CPU (gloo): partitioning, the single all-gather and the unpacking of the R tiles
+(prometheus_b200/distributed.py).  The tile computation is injected (a host function that copies
+the tile out of a known R), so no GPU is needed; the GPU path is the same code with
+compute_tile = pb200_run_device."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from prometheus_b200 import distributed as pbd
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _truth(n_orb, n_wav):
+    return (np.arange(n_orb)[:, None] * 1000.0 + np.arange(n_wav)[None, :] + 0.25)
+
+
+def _worker(rank, world, port, n_orb, n_wav, axis, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        R_true = _truth(n_orb, n_wav)
+        calls = []
+
+        def compute_tile(p0, p1, w0, w1, out):
+            calls.append((p0, p1, w0, w1))
+            tile = np.ascontiguousarray(R_true[p0:p1, w0:w1]).reshape(-1)
+            out[: tile.size] = torch.from_numpy(tile)
+
+        st = pbd.ShardedTransit(n_orb, n_wav, None, axis, "cpu", compute_tile)
+        st.run_device()
+        R0 = st.to_host(0)
+        Rall = st.to_host(None)
+        ok = np.array_equal(Rall, R_true) and ((R0 is None) if rank else np.array_equal(R0, R_true))
+        q.put((rank, bool(ok), calls))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,n_orb,n_wav,axis", [(2, 5, 219, "wavelength"), (2, 5, 219, "phase"),
+                                                    (3, 4, 10, "wavelength"), (3, 2, 7, "phase"), (2, 1, 1, "wavelength")])
+def test_sharded_gather(world, n_orb, n_wav, axis):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, n_orb, n_wav, axis, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=120) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    covered = np.zeros((n_orb, n_wav), dtype=int)
+    for rank, ok, calls in results:
+        assert ok, f"rank {rank}"
+        for p0, p1, w0, w1 in calls:
+            covered[p0:p1, w0:w1] += 1
+    assert np.all(covered == 1), "tiles must partition the output exactly once"
+
+
+def test_partition_properties():
+    for n in (0, 1, 7, 219, 31969, 300306):
+        for world in (1, 2, 3, 4, 8):
+            parts = pbd.partition(n, world)
+            assert len(parts) == world and parts[0][0] == 0 and parts[-1][1] == n
+            assert all(a[1] == b[0] for a, b in zip(parts, parts[1:]))
+            assert all(0 <= hi - lo <= pbd.padded_width(n, world) for lo, hi in parts)
+
+
+def test_unpack_single_rank():
+    R = _truth(3, 11)
+    assert np.array_equal(pbd.unpack_tiles(R.reshape(-1).copy(), 3, 11, 1, "wavelength"), R)
+    assert np.array_equal(pbd.unpack_tiles(R.reshape(-1).copy(), 3, 11, 1, "phase"), R)
