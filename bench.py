@@ -371,6 +371,8 @@ def run_b200(args):
         "e2e": {"value": samples_total / (e2e_ms_per_step * 1e-3), "unit": "samples/s", "ms_per_step": e2e_ms_per_step,
                 "h2d_bytes_per_step": int(info["h2d_bytes"]) * world, "d2h_bytes_per_step": int(n_orb * n_wav * 8),
                 "runs_per_s": 1e3 / e2e_ms_per_step},
+        "e2e_breakdown_ms": ({k: tr.last_timing[k] for k in ("upload_ms", "column_ms", "transit_ms", "finalize_ms", "download_ms")}
+                             if world == 1 and tr.last_timing else None),
         "gpu_launches": int(launch_total.item()),
         "clocks": clk,
         "roofline": {"kernel": "transit_kernel (c': tau + exp(-tau) + disk sum)", "bound": "hbm", "achieved": achieved,

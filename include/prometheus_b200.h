@@ -21,6 +21,7 @@
 #ifndef PROMETHEUS_B200_H
 #define PROMETHEUS_B200_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -132,6 +133,11 @@ const char* pb200_last_error(pb200_ctx* ctx);          /* ctx may be NULL (creat
 /* run all work of this context on an existing cudaStream_t (e.g. torch's current stream). */
 int pb200_set_stream(pb200_ctx* ctx, void* cuda_stream);
 int64_t pb200_launch_count(pb200_ctx* ctx);            /* kernels launched since create     */
+/* page-locked host memory for result arrays: pb200_run writes R at DMA speed into such a buffer,
+   and the caller avoids first-touch page faults on a fresh (n_orb, n_wav) array every call
+   (the reference allocates F_in_sum/F_out_sum afresh per call, gasProperties.py:1202-1203).      */
+int pb200_host_alloc(size_t bytes, void** out);
+int pb200_host_free(void* p);
 
 /* ---- scene ------------------------------------------------------------------------------ */
 /* Uploads everything Transit.sumOverChords reads through `self`.             */

@@ -19,7 +19,7 @@ c_double_p = C.POINTER(C.c_double)
 # every symbol include/prometheus_b200.h declares (checked by tests/test_abi.py)
 EXPORTS = [
     "pb200_abi_version", "pb200_device_count", "pb200_create", "pb200_destroy", "pb200_last_error",
-    "pb200_set_stream", "pb200_launch_count", "pb200_set_scene", "pb200_run", "pb200_run_device",
+    "pb200_set_stream", "pb200_launch_count", "pb200_host_alloc", "pb200_host_free", "pb200_set_scene", "pb200_run", "pb200_run_device",
     "pb200_last_timing", "pb200_number_density", "pb200_number_density_chords", "pb200_column_density",
     "pb200_chord_masks", "pb200_optical_depth", "pb200_sigma_lookup", "pb200_voigt_sigma",
     "pb200_voigt_profile", "pb200_molecular_sigma", "pb200_probe_fp64",
@@ -108,6 +108,8 @@ def load():
         "pb200_last_error": (C.c_char_p, [vp]),
         "pb200_set_stream": (C.c_int, [vp, vp]),
         "pb200_launch_count": (i64, [vp]),
+        "pb200_host_alloc": (C.c_int, [C.c_size_t, C.POINTER(vp)]),
+        "pb200_host_free": (C.c_int, [vp]),
         "pb200_set_scene": (C.c_int, [vp, C.POINTER(Scene)]),
         "pb200_run": (C.c_int, [vp, i32, i32, i64, i64, c_double_p, C.POINTER(Timing)]),
         "pb200_run_device": (C.c_int, [vp, i32, i32, i64, i64, vp, C.POINTER(Timing)]),
@@ -141,6 +143,60 @@ def as_f64(a) -> np.ndarray:
 
 def dptr(a: np.ndarray):
     return a.ctypes.data_as(c_double_p)
+
+
+class _PinnedBlock:
+    """A page-locked host block that goes back to the pool when the last numpy view of it dies."""
+
+    def __init__(self, pool, ptr, nbytes):
+        self.pool, self.ptr, self.nbytes = pool, ptr, nbytes
+        self.__array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 3}
+
+    def __del__(self):
+        pool = self.pool
+        if pool is not None:
+            pool._give_back(self.ptr, self.nbytes)
+
+
+class PinnedPool:
+    """Recycles pinned result buffers: `R = transit.sumOverChords()` in a loop reuses two blocks
+    instead of faulting in a fresh 13 MB array (8 ms of page faults at C4) on every call."""
+
+    GRANULE = 1 << 21
+    MAX_CACHED_BYTES = 1 << 30
+
+    def __init__(self):
+        self.free = {}          # nbytes -> [ptr]
+        self.cached = 0
+
+    def empty(self, shape, dtype=np.float64) -> np.ndarray:
+        n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        nbytes = max(self.GRANULE, -(-n // self.GRANULE) * self.GRANULE)
+        lst = self.free.get(nbytes)
+        if lst:
+            ptr = lst.pop()
+            self.cached -= nbytes
+        else:
+            p = C.c_void_p()
+            rc = load().pb200_host_alloc(nbytes, C.byref(p))
+            if rc != 0:
+                raise Pb200Error(rc, load().pb200_last_error(None).decode())
+            ptr = p.value
+        block = _PinnedBlock(self, ptr, nbytes)
+        return np.asarray(block)[:n].view(dtype).reshape(shape)
+
+    def _give_back(self, ptr, nbytes):
+        try:
+            if self.cached + nbytes <= self.MAX_CACHED_BYTES:
+                self.free.setdefault(nbytes, []).append(ptr)
+                self.cached += nbytes
+            else:
+                load().pb200_host_free(C.c_void_p(ptr))
+        except Exception:
+            pass
+
+
+pinned_pool = PinnedPool()
 
 
 class Context:
@@ -191,7 +247,7 @@ class Context:
     def run(self, phase_lo, phase_hi, wav_lo, wav_hi, out: np.ndarray | None = None):
         n = (phase_hi - phase_lo, wav_hi - wav_lo)
         if out is None:
-            out = np.empty(n, dtype=np.float64)
+            out = pinned_pool.empty(n)
         assert out.shape == n and out.dtype == np.float64 and out.flags.c_contiguous
         t = Timing()
         self.check(self.lib.pb200_run(self.handle, phase_lo, phase_hi, wav_lo, wav_hi, dptr(out), C.byref(t)))

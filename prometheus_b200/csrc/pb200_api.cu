@@ -17,7 +17,7 @@ namespace pb200 {
 // launchers implemented in the kernel translation units
 void launch_sky_cells(const DevScene*, int Mp, cudaStream_t);
 void launch_fout_scalar(const DevScene*, cudaStream_t);
-void launch_column(const DevScene*, int Mp, int phase_lo, int n_phase, int* oob, int sm_count, cudaStream_t);
+void launch_column(const DevScene*, int Mp, int phase_lo, int n_phase, int* oob, int sm_count, cudaStream_t, bool has_molecules);
 void launch_number_density_grid(const DevScene*, int64_t n_chords, int scenario, double* out, int* oob, int sm_count,
                                 cudaStream_t);
 void launch_number_density_chords(const DevScene*, int scenario, int64_t n, const double* y, const double* z,
@@ -63,12 +63,13 @@ struct pb200_ctx {
     size_t arena_bytes = 0;
     void* stage = nullptr;       // pinned host staging buffer for the upload
     size_t stage_bytes = 0;
-    std::vector<void*> derived;  // w_out, w_in, ncol, density..., freed with the scene
+    void* darena = nullptr;      // one allocation holding every derived array (w_out, rec, ncol, ...)
+    size_t darena_bytes = 0;     // both arenas are grow-only: repeated pb200_set_scene calls do not cudaMalloc
     double* scratch = nullptr;   // partial sums / R tile / temporary outputs
     size_t scratch_bytes = 0;
     int* d_oob = nullptr;
     double* d_exp_tab = nullptr; // 2^(j/64), j < 64
-    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // 6,7: scene upload
     pb200_timing last = {};
     double upload_ms = 0.0;
 };
@@ -100,8 +101,7 @@ static int ensure_scratch(pb200_ctx* c, size_t bytes) {
 }
 
 static void free_scene(pb200_ctx* c) {
-    for (void* p : c->derived) cudaFree(p);
-    c->derived.clear();
+    if (c->darena) { cudaFree(c->darena); c->darena = nullptr; c->darena_bytes = 0; }
     if (c->arena) { cudaFree(c->arena); c->arena = nullptr; c->arena_bytes = 0; }
     c->has_scene = false;
 }
@@ -129,7 +129,7 @@ int pb200_create(int device, pb200_ctx** out) {
     cudaError_t e = cudaSetDevice(device);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) { c->own_stream = true; e = cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device); }
-    for (int i = 0; i < 6 && e == cudaSuccess; ++i) e = cudaEventCreate(&c->ev[i]);
+    for (int i = 0; i < 8 && e == cudaSuccess; ++i) e = cudaEventCreate(&c->ev[i]);
     if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_scene, sizeof(DevScene));
     if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_oob, sizeof(int));
     if (e == cudaSuccess) e = cudaMemset(c->d_oob, 0, sizeof(int));
@@ -176,6 +176,21 @@ int pb200_set_stream(pb200_ctx* c, void* cuda_stream) {
 
 int64_t pb200_launch_count(pb200_ctx* c) { return c ? c->launches : 0; }
 
+int pb200_host_alloc(size_t bytes, void** out) {
+    if (!out) return PB200_ERR_INVALID;
+    *out = nullptr;
+    cudaError_t e = cudaMallocHost(out, bytes ? bytes : 1);
+    if (e != cudaSuccess) return fail(nullptr, PB200_ERR_CUDA, "cudaMallocHost(%zu): %s", bytes, cudaGetErrorString(e));
+    return PB200_OK;
+}
+
+int pb200_host_free(void* p) {
+    if (!p) return PB200_OK;
+    cudaError_t e = cudaFreeHost(p);
+    if (e != cudaSuccess) return fail(nullptr, PB200_ERR_CUDA, "cudaFreeHost: %s", cudaGetErrorString(e));
+    return PB200_OK;
+}
+
 }  // extern "C"
 
 // =================================================================================================
@@ -221,8 +236,8 @@ extern "C" int pb200_set_scene(pb200_ctx* c, const pb200_scene* s) {
 
     PB_CUDA(c, cudaSetDevice(c->device));
     PB_CUDA(c, cudaStreamSynchronize(c->stream));
-    free_scene(c);
-    PB_CUDA(c, cudaEventRecord(c->ev[0], c->stream));
+    c->has_scene = false;
+    PB_CUDA(c, cudaEventRecord(c->ev[6], c->stream));
 
     DevScene& h = c->h_scene;
     memset(&h, 0, sizeof h);
@@ -298,8 +313,12 @@ extern "C" int pb200_set_scene(pb200_ctx* c, const pb200_scene* s) {
         c->stage_bytes = plan.total;
     }
     for (const auto& it : plan.items) memcpy(static_cast<char*>(c->stage) + it.offset, it.src, it.bytes);
-    PB_CUDA(c, cudaMalloc(&c->arena, plan.total));
-    c->arena_bytes = plan.total;
+    if (plan.total > c->arena_bytes) {
+        if (c->arena) PB_CUDA(c, cudaFree(c->arena));
+        c->arena = nullptr; c->arena_bytes = 0;
+        PB_CUDA(c, cudaMalloc(&c->arena, plan.total));
+        c->arena_bytes = plan.total;
+    }
     PB_CUDA(c, cudaMemcpyAsync(c->arena, c->stage, plan.total, cudaMemcpyHostToDevice, c->stream));
 
     void* A = c->arena;
@@ -344,28 +363,38 @@ extern "C" int pb200_set_scene(pb200_ctx* c, const pb200_scene* s) {
     h.n_atoms = n_atoms; h.n_mols = n_mols;
 
     // ---- derived device arrays -------------------------------------------------------------------
-    auto dalloc = [&](double** p, size_t n) -> cudaError_t {
-        cudaError_t e = cudaMalloc((void**)p, (n ? n : 1) * sizeof(double));
-        if (e == cudaSuccess) c->derived.push_back(*p);
-        return e;
-    };
-    PB_CUDA(c, dalloc(&h.w_out, h.Mp));
-    PB_CUDA(c, dalloc(&h.star_shift, h.Mp));
-    PB_CUDA(c, dalloc(&h.w_in, (size_t)h.n_orb * h.Mp));
-    PB_CUDA(c, dalloc(&h.ncol, (size_t)n_atoms * h.n_orb * h.Mp));
-    PB_CUDA(c, dalloc(&h.rec, (size_t)(n_atoms + 1) * h.n_orb * h.Mp));
-    h.exp_tab = c->d_exp_tab;
-    {
-        double* nm = nullptr;
-        PB_CUDA(c, dalloc(&nm, (size_t)(n_atoms ? n_atoms : 1) * h.n_orb));
-        h.nmax = reinterpret_cast<unsigned long long*>(nm);
-        PB_CUDA(c, cudaMemsetAsync(nm, 0, (size_t)(n_atoms ? n_atoms : 1) * h.n_orb * sizeof(double), c->stream));
-    }
+    const bool fstar_per_chord = h.n_fstar > 0 && h.vsini != 0.0;
+    struct Want { double** p; size_t n; };
+    std::vector<Want> wants;
+    double* nmax_d = nullptr;
+    wants.push_back({&h.w_out, (size_t)h.Mp});
+    wants.push_back({&h.star_shift, (size_t)h.Mp});
+    wants.push_back({&h.w_in, (size_t)h.n_orb * h.Mp});
+    wants.push_back({&h.ncol, (size_t)n_atoms * h.n_orb * h.Mp});
+    wants.push_back({&h.rec, (size_t)(n_atoms + 1) * h.n_orb * h.Mp});
+    wants.push_back({&nmax_d, (size_t)(n_atoms ? n_atoms : 1) * h.n_orb});
     for (int i = 0; i < s->n_scenarios; ++i)
         if (h.scen[i].density_slot >= 0)
-            PB_CUDA(c, dalloc(&h.density[h.scen[i].density_slot], (size_t)h.n_orb * h.M * h.n_x));
-    const bool fstar_per_chord = h.n_fstar > 0 && h.vsini != 0.0;
-    PB_CUDA(c, dalloc(&h.fout, fstar_per_chord ? (size_t)h.n_wav : 1));
+            wants.push_back({&h.density[h.scen[i].density_slot], (size_t)h.n_orb * h.M * h.n_x});
+    wants.push_back({&h.fout, fstar_per_chord ? (size_t)h.n_wav : 1});
+    size_t need = 0;
+    for (const auto& w : wants) need += ((w.n ? w.n : 1) * sizeof(double) + 255) & ~size_t(255);
+    if (need > c->darena_bytes) {
+        if (c->darena) PB_CUDA(c, cudaFree(c->darena));
+        c->darena = nullptr; c->darena_bytes = 0;
+        PB_CUDA(c, cudaMalloc(&c->darena, need));
+        c->darena_bytes = need;
+    }
+    {
+        size_t off = 0;
+        for (const auto& w : wants) {
+            *w.p = reinterpret_cast<double*>(static_cast<char*>(c->darena) + off);
+            off += ((w.n ? w.n : 1) * sizeof(double) + 255) & ~size_t(255);
+        }
+    }
+    h.exp_tab = c->d_exp_tab;
+    h.nmax = reinterpret_cast<unsigned long long*>(nmax_d);
+    PB_CUDA(c, cudaMemsetAsync(nmax_d, 0, (size_t)(n_atoms ? n_atoms : 1) * h.n_orb * sizeof(double), c->stream));
     c->general_path = (n_mols > 0) || fstar_per_chord;
     h.fout_per_wav = fstar_per_chord ? 1 : 0;
 
@@ -375,11 +404,10 @@ extern "C" int pb200_set_scene(pb200_ctx* c, const pb200_scene* s) {
     launch_fout_scalar(c->d_scene, c->stream);
     c->launches += 2;
     PB_CUDA(c, cudaGetLastError());
-    PB_CUDA(c, cudaEventRecord(c->ev[1], c->stream));
-    PB_CUDA(c, cudaStreamSynchronize(c->stream));   // h (stack of this ctx) and stage are reused afterwards
-    float ms = 0.f;
-    PB_CUDA(c, cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]));
-    c->upload_ms = ms;
+    PB_CUDA(c, cudaEventRecord(c->ev[7], c->stream));
+    // no synchronisation here: the staging buffer is only reused after the synchronize at the top of
+    // the next pb200_set_scene, and the upload time is read back lazily (collect_timing)
+    c->upload_ms = -1.0;
     c->has_scene = true;
     return PB200_OK;
 }
@@ -430,7 +458,7 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     prm.partial = reinterpret_cast<double*>(reinterpret_cast<char*>(c->scratch) + r_bytes);
 
     PB_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
-    launch_column(c->d_scene, h.Mp, phase_lo, n_phase, c->d_oob, c->sm_count, c->stream);
+    launch_column(c->d_scene, h.Mp, phase_lo, n_phase, c->d_oob, c->sm_count, c->stream, h.n_mols > 0);
     c->launches += 1;
     PB_CUDA(c, cudaGetLastError());
     PB_CUDA(c, cudaEventRecord(c->ev[3], c->stream));
@@ -469,6 +497,12 @@ int collect_timing(pb200_ctx* c) {
     PB_CUDA(c, cudaEventElapsedTime(&b, c->ev[3], c->ev[4]));
     PB_CUDA(c, cudaEventElapsedTime(&d, c->ev[4], c->ev[5]));
     c->last.column_ms = a; c->last.transit_ms = b; c->last.finalize_ms = d;
+    if (c->upload_ms < 0.0) {
+        float u = 0;
+        PB_CUDA(c, cudaEventElapsedTime(&u, c->ev[6], c->ev[7]));
+        c->upload_ms = u;
+    }
+    c->last.upload_ms = c->upload_ms;
     return PB200_OK;
 }
 
@@ -615,7 +649,7 @@ extern "C" int pb200_column_density(pb200_ctx* c, double* ncol_host) {
     if (rc) return rc;
     const DevScene& h = c->h_scene;
     if (!ncol_host) return fail(c, PB200_ERR_INVALID, "ncol_host == NULL");
-    launch_column(c->d_scene, h.Mp, 0, h.n_orb, c->d_oob, c->sm_count, c->stream);
+    launch_column(c->d_scene, h.Mp, 0, h.n_orb, c->d_oob, c->sm_count, c->stream, h.n_mols > 0);
     c->launches += 1;
     PB_CUDA(c, cudaGetLastError());
     rc = check_oob(c);
@@ -633,7 +667,7 @@ extern "C" int pb200_chord_masks(pb200_ctx* c, uint8_t* blocked_host, double* we
     int rc = check_scene(c);
     if (rc) return rc;
     const DevScene& h = c->h_scene;
-    launch_column(c->d_scene, h.Mp, 0, h.n_orb, c->d_oob, c->sm_count, c->stream);
+    launch_column(c->d_scene, h.Mp, 0, h.n_orb, c->d_oob, c->sm_count, c->stream, h.n_mols > 0);
     c->launches += 1;
     PB_CUDA(c, cudaGetLastError());
     std::vector<double> w_in((size_t)h.n_orb * h.Mp), w_out(h.Mp);
@@ -658,7 +692,7 @@ extern "C" int pb200_optical_depth(pb200_ctx* c, int64_t wav_lo, int64_t wav_hi,
     DevBuf sig, tau;
     PB_CUDA(c, sig.alloc((size_t)(h.n_atoms ? h.n_atoms : 1) * h.n_orb * n_wav_sel * sizeof(double)));
     PB_CUDA(c, tau.alloc((size_t)n_c * n_wav_sel * sizeof(double)));
-    launch_column(c->d_scene, h.Mp, 0, h.n_orb, c->d_oob, c->sm_count, c->stream);
+    launch_column(c->d_scene, h.Mp, 0, h.n_orb, c->d_oob, c->sm_count, c->stream, h.n_mols > 0);
     if (h.n_atoms) launch_sigma_u(c->d_scene, h.n_atoms, h.n_orb, wav_lo, n_wav_sel, sig.as<double>(), c->sm_count, c->stream);
     launch_optical_depth(c->d_scene, sig.as<double>(), n_c, wav_lo, n_wav_sel, tau.as<double>(), c->stream);
     c->launches += 2 + (h.n_atoms ? 1 : 0);

@@ -124,6 +124,112 @@ column_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, int* 
     }
 }
 
+// ---- (a') fast form for scenes without molecules: one THREAD per chord -------------------------
+// All 32 lanes stay busy whatever n_x is, there are no shuffles, x[ix] is a warp-uniform load, and the
+// per-chord pieces of the formulas are hoisted out of the x loop (torus: exp(-(z/H)^2); power law:
+// (R/r)^q = exp(q (ln R - ln(r^2)/2)) instead of pow: <= 3e-14 relative, Ncol is tested to 1e-12).
+// Four partial sums per thread give ILP and halve the rounding growth of the long sum.
+template <class F>
+__device__ __forceinline__ double pb_sum4(int n, F term) {
+    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+    int ix = 0;
+    for (; ix + 4 <= n; ix += 4) {
+        a0 += term(ix); a1 += term(ix + 1); a2 += term(ix + 2); a3 += term(ix + 3);
+    }
+    for (; ix < n; ++ix) a0 += term(ix);
+    return (a0 + a1) + (a2 + a3);
+}
+
+__device__ __forceinline__ double pb_column_sum(const DevScene& sc, const DevScenario& S, int p, double amp, double y,
+                                                double z, int* oob_flag) {
+    const int n_x = sc.n_x;
+    const double* __restrict__ xs = sc.x;
+    if (S.type == PB200_SCN_SERPENS) {
+        int oob = 0;
+        const double sum = pb_sum4(n_x, [&](int ix) { return pb_trilinear(S, xs[ix], y, z, &oob); });
+        if (oob) *oob_flag = 1;
+        return sum * amp;
+    }
+    const double cx = S.centre_x[p];
+    const double dy = y - S.centre_y[p];
+    const double n0 = S.p[0] * amp;
+    switch (S.type) {
+        case PB200_SCN_BAROMETRIC: {   // n0 exp((R - r)/H) H(r - R), gasProperties.py:155-160
+            const double R = S.p[1], invH = 1.0 / S.p[2], c2 = fma(dy, dy, z * z);
+            return n0 * pb_sum4(n_x, [&](int ix) {
+                const double dx = xs[ix] - cx;
+                const double r = sqrt(fma(dx, dx, c2));
+                return (r < R) ? 0.0 : exp((R - r) * invH);
+            });
+        }
+        case PB200_SCN_HYDROSTATIC: {  // n0 exp(J(r) H(r - R) - J(R)), gasProperties.py:197-203
+            const double R = S.p[1], jc = S.p[2] / S.p[3], j0 = jc / R, c2 = fma(dy, dy, z * z);
+            return n0 * pb_sum4(n_x, [&](int ix) {
+                const double dx = xs[ix] - cx;
+                const double r = sqrt(fma(dx, dx, c2));
+                return exp(((r < R) ? 0.0 : jc / r) - j0);
+            });
+        }
+        case PB200_SCN_POWERLAW: {     // n0 (R/r)^q H(r - R), gasProperties.py:240-243, :326-329, :371-373, :453-460
+            const double R = S.p[1], q = S.p[2], qlogR = q * log(R), hq = -0.5 * q, c2 = fma(dy, dy, z * z);
+            return n0 * pb_sum4(n_x, [&](int ix) {
+                const double dx = xs[ix] - cx;
+                const double r2 = fma(dx, dx, c2);
+                return (sqrt(r2) < R) ? 0.0 : exp(fma(hq, log(r2), qlogR));
+            });
+        }
+        case PB200_SCN_TORUS: {        // n0 exp(-((a - a_t)/4H)^2) exp(-(z/H)^2), gasProperties.py:506-515
+            const double at = S.p[1], inv4H = 1.0 / (4.0 * S.p[2]), qz = z / S.p[2], dy2 = dy * dy;
+            const double ez = exp(-(qz * qz));
+            return (n0 * ez) * pb_sum4(n_x, [&](int ix) {
+                const double dx = xs[ix] - cx;
+                const double qa = (sqrt(fma(dx, dx, dy2)) - at) * inv4H;
+                return exp(-(qa * qa));
+            });
+        }
+        default:
+            return 0.0;
+    }
+}
+
+__global__ void __launch_bounds__(128)
+column_thread_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, int* __restrict__ oob_flag) {
+    const DevScene& sc = *scp;
+    const int64_t cid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (cid >= (int64_t)n_phase * sc.Mp) return;
+    const int p = phase_lo + (int)(cid / sc.Mp);
+    const int m = (int)(cid % sc.Mp);
+    const int64_t row = (int64_t)p * sc.Mp + m;
+    const int R = sc.n_atoms + 1;
+    double* rec = sc.rec + row * R;
+    bool blocked = true;
+    double y = 0.0, z = 0.0, wv = 0.0;
+    if (m < sc.M) {
+        const int iphi = m / sc.n_rho, irho = m - iphi * sc.n_rho;
+        const double rho = sc.rho[irho];
+        y = __dmul_rn(rho, sc.sin_phi[iphi]);
+        z = __dmul_rn(rho, sc.cos_phi[iphi]);
+        blocked = pb_blocked(sc, p, y, z);
+        wv = blocked ? 0.0 : sc.w_out[m];
+    }
+    sc.w_in[row] = wv;
+    rec[0] = wv;
+    for (int s = 0; s < sc.n_scen; ++s) {
+        const DevScenario& S = sc.scen[s];
+        // the reference evaluates only unblocked chords (gasProperties.py:1235-1240)
+        const double sum = blocked ? 0.0 : pb_column_sum(sc, S, p, S.amplitude ? S.amplitude[p] : 1.0, y, z, oob_flag);
+        for (int k = S.first_cons; k < S.first_cons + S.n_cons; ++k) {
+            const DevConstituent& C = sc.cons[k];
+            if (C.kind != 0) continue;
+            const double col = (sum * C.chi) * sc.delta_x;                      // gasProperties.py:940
+            sc.ncol[(int64_t)C.atom_index * sc.n_orb * sc.Mp + row] = col;
+            rec[1 + C.atom_index] = col;
+            if (col > 0.0)
+                atomicMax(sc.nmax + (int64_t)C.atom_index * sc.n_orb + p, (unsigned long long)__double_as_longlong(col));
+        }
+    }
+}
+
 // ---- calculateNumberDensity materialised (chord-major, reference chord order) ------------------
 // out[c*n_x + ix], c = m*n_orb + p.  One warp per chord: rows are written as coalesced 8-byte stores.
 __global__ void __launch_bounds__(256)
@@ -210,8 +316,13 @@ void launch_fout_scalar(const DevScene* d_scene, cudaStream_t st) {
     fout_scalar_kernel<<<1, 1024, 0, st>>>(d_scene);
 }
 void launch_column(const DevScene* d_scene, int Mp, int phase_lo, int n_phase, int* oob, int sm_count,
-                   cudaStream_t st) {
-    column_kernel<<<grid_for_warps((int64_t)n_phase * Mp, sm_count), 256, 0, st>>>(d_scene, phase_lo, n_phase, oob);
+                   cudaStream_t st, bool has_molecules) {
+    if (has_molecules) {   // density rows n(c, x) are needed by kernel (m): warp per chord, coalesced row stores
+        column_kernel<<<grid_for_warps((int64_t)n_phase * Mp, sm_count), 256, 0, st>>>(d_scene, phase_lo, n_phase, oob);
+    } else {
+        const int64_t n = (int64_t)n_phase * Mp;
+        column_thread_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(d_scene, phase_lo, n_phase, oob);
+    }
 }
 void launch_number_density_grid(const DevScene* d_scene, int64_t n_chords, int scenario, double* out,
                                 int* oob, int sm_count, cudaStream_t st) {

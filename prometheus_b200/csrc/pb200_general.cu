@@ -44,11 +44,14 @@ __global__ void __launch_bounds__(kGenThreads)
 transit_general_kernel(const DevScene* __restrict__ scp, const TransitParams prm, int rec_cap) {
     const DevScene& sc = *scp;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    // layout: U[node_total][kGenThreads] | sig[n_atoms][kGenThreads] | rec[2][rec_cap]
+    // layout: exp table [256][8] | U[node_total][kGenThreads] | sig[n_atoms][kGenThreads] | rec[2][rec_cap]
     int node_total = 0;
     for (int k = 0; k < sc.n_cons; ++k)
         if (sc.cons[k].kind == 1) node_total += sc.cons[k].dims[0];
-    double* U = reinterpret_cast<double*>(smem_raw);
+    double* etab = reinterpret_cast<double*>(smem_raw);
+    for (int i = threadIdx.x; i < kExpTabEntries * kExpTabCopies; i += kGenThreads) etab[i] = __ldg(sc.exp_tab + i / kExpTabCopies);
+    const uint32_t tab_lane = (uint32_t)__cvta_generic_to_shared(etab) + (threadIdx.x & (kExpTabCopies - 1)) * 8u;
+    double* U = etab + kExpTabEntries * kExpTabCopies;
     double* sig = U + (size_t)node_total * kGenThreads;
     MolRecord* rec = reinterpret_cast<MolRecord*>(sig + (size_t)sc.n_atoms * kGenThreads);
 
@@ -140,14 +143,14 @@ transit_general_kernel(const DevScene* __restrict__ scp, const TransitParams prm
                 const DevConstituent& C = sc.cons[k];
                 if (C.kind != 1) continue;
                 const double* Uc = U + (size_t)node0 * kGenThreads + tid;
-                const double fill_sigma = pb_exp(C.fill * kLn10) - C.offset;
+                const double fill_sigma = pb_exp_neg_tab<true>(C.fill * kLn10, tab_lane) - C.offset;
                 double s = 0.0;
                 for (int i = 0; i < sc.n_x; ++i) {
                     const MolRecord r = R[r0 + i];
                     const double u0 = Uc[r.j * kGenThreads], u1 = Uc[(r.j + 1) * kGenThreads];
                     double sg;
                     if (r.t < 0.0 || u0 != u0) sg = fill_sigma;
-                    else sg = pb_exp(((1.0 - r.t) * u0 + r.t * u1) * kLn10) - C.offset;      // :814
+                    else sg = pb_exp_neg_tab<true>(((1.0 - r.t) * u0 + r.t * u1) * kLn10, tab_lane) - C.offset;   // :814
                     s = fma(r.coef, sg, s);
                 }
                 tau += s;
@@ -157,7 +160,7 @@ transit_general_kernel(const DevScene* __restrict__ scp, const TransitParams prm
         }
         double f = wv;
         if (per_chord_fstar) f *= pb_interp_log(sc.fstar_x, sc.fstar_y, sc.n_fstar, lam / sc.star_shift[m], 0.0);
-        acc = fma(f, pb_exp_neg(tau), acc);                                                   // :1241
+        acc = fma(f, pb_exp_neg_tab<true>(-tau, tab_lane), acc);                                    // :1241
         buf ^= 1;   // the other record buffer is free: its readers passed the barrier above
     }
 
@@ -180,7 +183,8 @@ cudaError_t launch_transit_general(const DevScene* d_scene, const DevScene& h, c
         ++*n_launch;
     }
     const int rec_cap = n_mol * h.n_x > 0 ? n_mol * h.n_x : 1;
-    const size_t smem = ((size_t)node_total + h.n_atoms) * kGenThreads * sizeof(double) + 2 * (size_t)rec_cap * sizeof(MolRecord);
+    const size_t smem = ((size_t)kExpTabEntries * kExpTabCopies + ((size_t)node_total + h.n_atoms) * kGenThreads) * sizeof(double) +
+                        2 * (size_t)rec_cap * sizeof(MolRecord);
     if (smem > 200 * 1024) return cudaErrorInvalidValue;
     cudaError_t e = cudaFuncSetAttribute(transit_general_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;

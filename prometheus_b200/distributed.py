@@ -92,20 +92,37 @@ class ShardedTransit:
             self.dist.all_gather_into_tensor(self.gathered, self.local, group=self.group)
         return self.gathered
 
+    def unpack_device(self):
+        """Gathered slots -> one contiguous (n_orb, n_wav) device tensor (device-side copies only)."""
+        torch = self.torch
+        if self.world == 1:
+            return self.local[: self.n_orb * self.n_wav].view(self.n_orb, self.n_wav)
+        if getattr(self, "full", None) is None:
+            self.full = torch.empty((self.n_orb, self.n_wav), dtype=torch.float64, device=self.device)
+        slots = self.gathered.view(self.world, self.slot)
+        if self.axis == "wavelength":
+            for r, (lo, hi) in enumerate(partition(self.n_wav, self.world)):
+                if hi > lo:
+                    self.full[:, lo:hi] = slots[r, : self.n_orb * (hi - lo)].view(self.n_orb, hi - lo)
+        else:
+            for r, (lo, hi) in enumerate(partition(self.n_orb, self.world)):
+                if hi > lo:
+                    self.full[lo:hi, :] = slots[r, : (hi - lo) * self.n_wav].view(hi - lo, self.n_wav)
+        return self.full
+
     def to_host(self, dst: int | None = 0):
-        """D2H of the gathered buffer (on `dst` only, or on every rank if dst is None) -> (n_orb, n_wav)."""
+        """D2H of R (on `dst` only, or on every rank if dst is None) -> (n_orb, n_wav) float64.
+        On CUDA the tiles are put in place on the device and land in a pooled page-locked array."""
         torch = self.torch
         if dst is not None and self.rank != dst:
             return None
         if self.device.type == "cuda":
-            if self.host is None:
-                self.host = torch.empty(self.gathered.shape, dtype=torch.float64, pin_memory=True)
-            self.host.copy_(self.gathered, non_blocking=True)
+            from . import capi
+            R = capi.pinned_pool.empty((self.n_orb, self.n_wav))
+            torch.from_numpy(R).copy_(self.unpack_device(), non_blocking=True)
             torch.cuda.current_stream(self.device).synchronize()
-            flat = self.host.numpy()
-        else:
-            flat = self.gathered.numpy()
-        return unpack_tiles(flat, self.n_orb, self.n_wav, self.world, self.axis)
+            return R
+        return unpack_tiles(self.gathered.numpy(), self.n_orb, self.n_wav, self.world, self.axis)
 
 
 def sum_over_chords(transit, group=None, axis: str = "wavelength", device: int | None = None, dst: int | None = 0,
