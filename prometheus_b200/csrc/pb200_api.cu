@@ -438,6 +438,7 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     const int64_t launches0 = c->launches;
 
     TransitParams prm;
+    prm.ec = pb_exp_consts();
     prm.phase_lo = phase_lo; prm.n_phase = n_phase; prm.wav_lo = wav_lo; prm.n_wav_sel = n_wav_sel;
     const int n_tiles = h.Mp / kChordTile;
     const int wpt = c->general_path ? 1 : transit_wpt_for(h.n_atoms);

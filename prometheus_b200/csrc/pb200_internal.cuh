@@ -71,6 +71,7 @@ struct TransitParams {
     int tiles_per_split;  // kChordTile-chord tiles per split
     double* partial;      // [n_split][n_phase][n_wav_sel] sums of w_in*exp(-tau)  (n_split > 1)
     double* R;            // [n_phase][n_wav_sel] final ratio
+    ExpConsts ec;         // constant-bank operands of the exp (pb_exp_neg_tab)
 };
 
 // ---------------------------------------------------------------------------------------------

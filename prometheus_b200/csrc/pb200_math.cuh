@@ -93,21 +93,36 @@ __device__ __forceinline__ double pb_exp_tab_load(uint32_t tab_addr, int k) {
     return __hiloint2double(t_hi + (k << kExpTabShift), t_lo);
 }
 
+// The three constants that do not fit an FP64 immediate (only the high word can be encoded) are
+// taken from kernel parameters by the hot kernels, so that they are constant-bank operands of the
+// DFMAs instead of registers re-materialised with MOVs inside the chord loop.
+struct ExpConsts {
+    double scale;   // 256 / ln 2
+    double step;    // ln 2 / 256
+    double sixth;   // 1 / 6
+};
+__host__ __device__ inline ExpConsts pb_exp_consts() { return ExpConsts{kExpScale, kExpStep, 1.6666666666666666e-01}; }
+
 template <bool CLAMP>
-__device__ __forceinline__ double pb_exp_neg_tab(double u, uint32_t tab_addr) {
+__device__ __forceinline__ double pb_exp_neg_tab(double u, uint32_t tab_addr, const ExpConsts& ec) {
     if (CLAMP) {
         const unsigned hi = min((unsigned)__double2hiint(u), 0xC085E000u);   // u >= -700 (-0.0/+tiny pass)
         u = __hiloint2double((int)hi, __double2loint(u));
     }
-    double kd = fma(u, kExpScale, kExpMagic);
+    double kd = fma(u, ec.scale, kExpMagic);
     const int k = __double2loint(kd);
     kd -= kExpMagic;
-    const double r = fma(kd, -kExpStep, u);
+    const double r = fma(-kd, ec.step, u);
     const double T = pb_exp_tab_load(tab_addr, k);
-    double p = fma(r, 1.6666666666666666e-01, 0.5);
+    double p = fma(r, ec.sixth, 0.5);
     p = fma(p, r, 1.0);
     const double q = r * p;
     return fma(T, q, T);
+}
+
+template <bool CLAMP>
+__device__ __forceinline__ double pb_exp_neg_tab(double u, uint32_t tab_addr) {
+    return pb_exp_neg_tab<CLAMP>(u, tab_addr, pb_exp_consts());
 }
 
 // exp(a) for |a| <= 700 (same kernel as pb_exp_neg, two-sided); used for 10**v = exp(v ln10) of the

@@ -53,21 +53,32 @@ __device__ __forceinline__ void tma_bulk_g2s(void* dst, const void* src, uint32_
 }
 
 
+__device__ __forceinline__ double lds_f64(uint32_t addr) {
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ void lds_v2f64(uint32_t addr, double& a, double& b) {
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(a), "=d"(b) : "r"(addr));
+}
+
 // One 256-chord tile: acc[j] += w_m * exp(-sum_a N_a(m) sigma_a(j)) for the thread's WPT wavelengths.
+// `stage` is the shared-window address of the tile's records (explicit ld.shared: no generic->shared
+// address conversion inside the loop).
 template <int S, int WPT, bool CLAMP>
-__device__ __forceinline__ void transit_tile(const double* __restrict__ sw, const double (&nsig)[S][WPT],
-                                             double (&acc)[WPT], uint32_t tab_lane) {
-    constexpr int R = S + 1;
+__device__ __forceinline__ void transit_tile(uint32_t stage, const double (&nsig)[S][WPT], double (&acc)[WPT],
+                                             uint32_t tab_lane, const ExpConsts& ec) {
+    constexpr uint32_t kRecBytes = (S + 1) * sizeof(double);
 #pragma unroll 2
     for (int m = 0; m < kChordTile; ++m) {
+        const uint32_t rec = stage + m * kRecBytes;
         double wv, N[S];
         if constexpr (S == 1) {
-            const double2 v = *reinterpret_cast<const double2*>(sw + 2 * m);   // broadcast LDS.128
-            wv = v.x; N[0] = v.y;
+            lds_v2f64(rec, wv, N[0]);                                              // broadcast LDS.128
         } else {
-            wv = sw[m * R];
+            wv = lds_f64(rec);
 #pragma unroll
-            for (int a = 0; a < S; ++a) N[a] = sw[m * R + 1 + a];
+            for (int a = 0; a < S; ++a) N[a] = lds_f64(rec + 8 + 8 * a);
         }
         // blocked chord or padding: F_in = 0 (gasProperties.py:1233); CTA-uniform, integer test
         if ((__double2hiint(wv) | __double2loint(wv)) == 0) continue;
@@ -76,7 +87,7 @@ __device__ __forceinline__ void transit_tile(const double* __restrict__ sw, cons
             double u = N[0] * nsig[0][j];                                          // -tau, :954
 #pragma unroll
             for (int a = 1; a < S; ++a) u = fma(N[a], nsig[a][j], u);
-            acc[j] = fma(wv, pb_exp_neg_tab<CLAMP>(u, tab_lane), acc[j]);         // :1241, :1244/:1255
+            acc[j] = fma(wv, pb_exp_neg_tab<CLAMP>(u, tab_lane, ec), acc[j]);     // :1241, :1244/:1255
         }
     }
 }
@@ -164,13 +175,14 @@ transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
 
     // ---- main loop over chord tiles -----------------------------------------------------------
     const uint32_t tab_lane = smem_u32(etab) + (tid & (kExpTabCopies - 1)) * (uint32_t)sizeof(double);
+    const uint32_t stages_addr = smem_u32(stages);
     for (int t = 0; t < n_tiles; ++t) {
         const int stage = t & 1;
         if (tid == 0 && t + 1 < n_tiles) issue(t + 1, stage ^ 1);
         mbar_wait(&full_bar[stage], (t >> 1) & 1);
-        const double* sw = stages + stage * kStageDoubles;
-        if (clamp) transit_tile<S, WPT, true>(sw, nsig, acc, tab_lane);
-        else transit_tile<S, WPT, false>(sw, nsig, acc, tab_lane);
+        const uint32_t sw = stages_addr + stage * kStageBytes;
+        if (clamp) transit_tile<S, WPT, true>(sw, nsig, acc, tab_lane, pb_exp_consts());
+        else transit_tile<S, WPT, false>(sw, nsig, acc, tab_lane, pb_exp_consts());
         __syncthreads();   // stage may be refilled by the producer in the next iteration
     }
 

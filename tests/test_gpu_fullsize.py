@@ -1,0 +1,72 @@
+"""Parity at BASELINE.json's full sizes (C3, C4, C5) through the C ABI.
+
+The oracle cannot do 1e10 chord*lambda samples in seconds, but every wavelength column of R is
+independent (gasProperties.py:1243-1258), so a strided handful of columns computed by the oracle on
+ALL chords is a genuine full-size check of kernels (a') and (c').  Plus size-independent properties:
+the opaque-disk limit, R <= R0, tile independence, determinism."""
+import numpy as np
+import pytest
+
+from helpers import excess_depth_ok, oracle, oracle_inputs
+from prometheus_b200 import builder, host, workloads
+
+pytestmark = pytest.mark.gpu
+
+
+def gpu_tables(tr):
+    out = {}
+    for i, d in enumerate(tr.atmosphere.densityDistributionList):
+        for con in d.constituents:
+            if not con.isMolecule:
+                out[(i, con.species.name)] = (con.lookupFunction.x, con.lookupFunction.y)
+    return out
+
+
+@pytest.mark.parametrize("name,n_cols", [("C3", 12), ("C4", 10), ("C5", 4)])
+def test_full_size_columns_against_oracle(name, n_cols, nist_rows):
+    spec = workloads.get(name)
+    tr = builder.build_transit(spec, nist_rows=nist_rows)
+    R = tr.sumOverChords()
+    n_orb, n_wav = R.shape
+    assert np.all(np.isfinite(R)) and R.max() <= 1.0 + 1e-15 and R.min() > 0.0
+    # columns: the deepest one (a line core), its neighbours, and a strided set
+    core = int(np.argmin(R.min(axis=0)))
+    sel = np.unique(np.clip(np.concatenate([[core - 1, core, core + 1], np.linspace(0, n_wav - 1, n_cols).astype(int)]), 0, n_wav - 1))
+    inputs = oracle_inputs(spec, nist_rows)
+    inputs["tables"] = gpu_tables(tr)          # same sigma tables on both sides: isolates (a') + (c') at full size
+    m = oracle.build_model(spec, inputs)
+    assert np.array_equal(m.wavelength, tr.wavelength)
+    n_c = len(m.rho) * len(m.phi) * len(m.orb)
+    bs = oracle.reference_batch_size(n_c, len(sel), len(m.x), False, 2.0)
+    R_ref = oracle.sum_over_chords(m, batch_size=None if bs >= n_c else bs, wavelength=m.wavelength[sel])
+    R0 = oracle.sum_over_chords(m, batch_size=None if bs >= n_c else bs, wavelength=m.wavelength[sel], opaque_only=True)
+    ok, worst = excess_depth_ok(R[:, sel], R_ref, R0)
+    assert ok, f"{name}: worst err/bound {worst:.3g}"
+    assert np.max(np.abs(R[:, sel] - R_ref)) < 5e-13
+    assert np.all(R[:, sel] <= R0 + 1e-14)
+    assert float((R0 - R[:, sel]).max()) > 1e-4, "the selected columns must see real absorption"
+
+
+def test_c4_properties(nist_rows):
+    ctx = host.get_context(0)
+    tr = builder.build_transit(workloads.get("C4"), nist_rows=nist_rows)
+    R = tr.sumOverChords()
+    again = tr.sumOverChords()
+    assert np.array_equal(R, again)
+    n_orb, n_wav = R.shape
+    # wavelength- and phase-tiles (what the multi-GPU path computes per rank) agree with the full run
+    for (p0, p1, w0, w1) in [(0, n_orb, n_wav // 2, n_wav // 2 + 4000), (7, 19, 0, n_wav), (n_orb - 1, n_orb, n_wav - 3, n_wav)]:
+        tile, _ = ctx.run(p0, p1, w0, w1)
+        np.testing.assert_allclose(tile, R[p0:p1, w0:w1], rtol=0, atol=5e-15)
+    # opaque-disk limit at full size: N -> 0
+    spec0 = workloads.get("C4")
+    spec0["scenarios"][0]["N"] = 0.0
+    tr0 = builder.build_transit(spec0, nist_rows=nist_rows)
+    R0 = tr0.sumOverChords()
+    assert np.all(R0 >= R - 1e-15)
+    assert np.ptp(R0, axis=1).max() < 1e-15, "without absorber R does not depend on wavelength"
+    # doubling the absorber can only deepen the transit
+    spec2 = workloads.get("C4")
+    spec2["scenarios"][0]["N"] *= 2.0
+    R2 = builder.build_transit(spec2, nist_rows=nist_rows).sumOverChords()
+    assert np.all(R2 <= R + 1e-15)
