@@ -259,6 +259,42 @@ def recorded_traffic(workload, kernel="transit_kernel"):
     return None
 
 
+def quick_workload(name, ctx, torch, stream, flush, steps=3, warmup=3):
+    """Device-resident samples/s of another workload on this rank's GPU (3 warm-up + 3 timed steps)."""
+    import prometheus_b200 as pb
+    from prometheus_b200 import scene
+    spec = scaled_spec(name, 1)
+    t0 = time.perf_counter()
+    tr = pb.build_transit(spec, nist_rows=nist_rows())
+    t_setup = time.perf_counter() - t0
+    sc, keep, info = scene.flatten(tr)
+    ctx.set_scene(sc, keep)
+    out = torch.empty(info["n_orb"] * info["n_wav"], dtype=torch.float64, device=flush.device)
+    ms, kern = [], []
+    for i in range(warmup + steps):
+        flush.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        t = ctx.run_device(0, info["n_orb"], 0, info["n_wav"], out.data_ptr(), want_timing=True)
+        b.record()
+        torch.cuda.synchronize()
+        if i >= warmup:
+            ms.append(a.elapsed_time(b))
+            kern.append(t)
+    t0 = time.perf_counter()
+    R = tr.sumOverChords()
+    e2e_ms = (time.perf_counter() - t0) * 1e3
+    samples = float(info["n_chords"]) * info["n_wav"]
+    res = {"title": spec["title"], "n_chords": info["n_chords"], "n_wav": info["n_wav"], "n_x": info["n_x"],
+           "n_atoms": info["n_atoms"], "n_molecules": info["n_mols"], "ms_per_step": float(np.mean(ms)),
+           "samples_per_s": samples / (np.mean(ms) * 1e-3), "e2e_ms_one_call": e2e_ms,
+           "kernels_ms": {k: float(np.mean([t[k] for t in kern])) for k in ("column_ms", "transit_ms", "finalize_ms")},
+           "setup_seconds": t_setup, "R_min": float(R.min()), "R_max": float(R.max())}
+    if info["n_mols"]:
+        res["molecular_lookups_per_s"] = samples * info["n_x"] * info["n_mols"] / (np.mean(ms) * 1e-3)
+    return res
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -286,7 +322,7 @@ def run_b200(args):
         voigt = ctx.last_timing()
         sc, keep, info = scene.flatten(tr)
         ctx.set_scene(sc, keep)
-        n_orb, n_wav, n_c, n_atoms = info["n_orb"], info["n_wav"], info["n_chords"], info["n_atoms"]
+        n_orb, n_wav, n_c, n_atoms, n_mols = info["n_orb"], info["n_wav"], info["n_chords"], info["n_atoms"], info["n_mols"]
         st = pbd.ShardedTransit(n_orb, n_wav, None, "wavelength", dev)
         tile_t = []
 
@@ -381,11 +417,21 @@ def run_b200(args):
                      "traffic": recorded_traffic(args.workload), "kernel_ms": kernel_ms,
                      "fp64": {"achieved_tflops": fl, "peak_tflops_dfma_probe": probe["dfma_tflops"],
                               "frac": fl / probe["dfma_tflops"], "flops_per_sample": flops_per_sample(n_atoms),
+                              "pipe_frac": ((9.0 + n_atoms) * tile_samples / 32.0 * 2.0) /
+                                           (148 * 4 * (clk["sm_mhz"] or 1965.0) * 1e6 * kernel_ms * 1e-3) if n_mols == 0 else None,
+                              "pipe_frac_note": "issued FP64 warp instructions (9+S per sample) x 2 cycles / SMSP cycles: the binding unit",
                               "exp_probe_gops": probe["exp_gops"],
                               "exp_frac": tile_samples / (kernel_ms * 1e-3) / 1e9 / probe["exp_gops"]}},
         "kernels_ms": {"column": column_ms, "transit": kernel_ms, "finalize": finalize_ms},
         "setup": {"seconds": t_setup, "voigt_last_table_ms": voigt["transit_ms"], "voigt_last_table_evals": voigt["samples"]},
     }
+
+    # ---- the other BASELINE configs, device-resident, few steps (N = 1 only; parity is in tests/) -----------
+    if world == 1 and args.others:
+        out["other_workloads"] = {}
+        for name in [w for w in args.others.split(",") if w and w != args.workload]:
+            with torch.cuda.stream(stream):
+                out["other_workloads"][name] = quick_workload(name, ctx, torch, stream, flush)
 
     # ---- CPU baseline on the host cores of this box (rank 0, N = 1 only) -----------------------------
     if world == 1 and args.cpu_seconds > 0:
@@ -417,6 +463,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="C4")
+    ap.add_argument("--others", default="C2,C3,C5", help="other BASELINE configs reported under other_workloads (N=1)")
     ap.add_argument("--cpu-seconds", type=float, default=None,
                     help="CPU budget: cpu_baseline sample (default 15 s) / whole --impl reference run (default 120 s)")
     args = ap.parse_args()

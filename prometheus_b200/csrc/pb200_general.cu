@@ -16,14 +16,26 @@
 namespace pb200 {
 
 constexpr int kGenThreads = 128;
-constexpr int kMaxMolNodes = 64;   // sum over molecules of pressure nodes held in shared memory
+constexpr int kGenWarps = kGenThreads / 32;
+constexpr int kMaxMolNodes = 64;   // sum over molecules of (pressure nodes + 1) held in shared memory
 
-struct MolRecord {
-    double t;     // fractional position inside the pressure interval, or -1: out of grid -> fill
-    double coef;  // n * chi * delta_x
-    int j;        // pressure interval
-    int pad;
+// one (x sample, molecule) of the current chord; records with the same pressure node form runs
+struct __align__(16) MolRecord {
+    double t;      // fractional position inside the pressure interval (0 for the fill node)
+    double coef;   // n * chi * delta_x
 };
+struct MolRun {
+    int joff;      // node index (global over molecules) * 16 B * kGenThreads: byte offset of V/D in shared memory
+    int start;     // first record of the run; the run ends where the next one starts
+};
+
+// coef * sigma of one record for this thread's wavelength: ln sigma = V_j + t (V_{j+1} - V_j), then the
+// table exp (no clamp: ln sigma >= ln(1e-50) = -115).  1 + 8 + 1 FP64 instructions, one broadcast LDS.128.
+__device__ __forceinline__ double mol_term(uint32_t rec_addr, double v, double d, uint32_t tab_lane) {
+    double t, coef;
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(t), "=d"(coef) : "r"(rec_addr));
+    return coef * pb_exp_neg_tab<false>(fma(t, d, v), tab_lane);
+}
 
 // F_out[w] = sum_m rho*clv*F*(lambda_w / shift*(m))   (gasProperties.py:1213-1222, :1232, :1249/:1256)
 __global__ void __launch_bounds__(kGenThreads)
@@ -40,30 +52,51 @@ fout_table_kernel(const DevScene* __restrict__ scp) {
     sc.fout[w] = s;
 }
 
-__global__ void __launch_bounds__(kGenThreads)
-transit_general_kernel(const DevScene* __restrict__ scp, const TransitParams prm, int rec_cap) {
+// named barriers (id 0 is __syncthreads): producer warp <-> 4 consumer warps, two chord buffers
+__device__ __forceinline__ void bar_sync(int id, int count) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory"); }
+__device__ __forceinline__ void bar_arrive(int id, int count) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory"); }
+constexpr int kBarFull = 1, kBarEmpty = 3;
+constexpr int kGenBlock = kGenThreads + 32;   // + one producer warp
+
+// Warp-specialised: warp 4 (producer) walks the chords of this CTA's split, skips blocked ones, and
+// turns each chord's density rows into a shared-memory item
+//     { w_in, star_shift, valid flag | Ncol_a | sum of coef per molecule | records {t_P, n chi dx, node} }
+// (global loads, pressure-interval search and the division happen here, off the consumers' path);
+// warps 0-3 (consumers, one wavelength per thread) wait on the item and sum
+//     tau = sum_a Ncol_a sigma_a + sum_records coef * exp(V_j + t (V_{j+1} - V_j)) - offset * sum coef.
+// Shared memory: exp table [256][8] | VD[node_total][kGenThreads] double2 {V_j, V_{j+1} - V_j} with
+// V = ln sigma at pressure node j (T and lambda already interpolated for this thread's wavelength;
+// every molecule has one extra "fill" node {ln(fill sigma), 0}) | sig[n_atoms][kGenThreads] |
+// pgrid[node_total] | item[2]
+__global__ void __launch_bounds__(kGenBlock)
+transit_general_kernel(const DevScene* __restrict__ scp, const TransitParams prm, int item_doubles, int node_total, int n_mol) {
     const DevScene& sc = *scp;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    // layout: exp table [256][8] | U[node_total][kGenThreads] | sig[n_atoms][kGenThreads] | rec[2][rec_cap]
-    int node_total = 0;
-    for (int k = 0; k < sc.n_cons; ++k)
-        if (sc.cons[k].kind == 1) node_total += sc.cons[k].dims[0];
     double* etab = reinterpret_cast<double*>(smem_raw);
-    for (int i = threadIdx.x; i < kExpTabEntries * kExpTabCopies; i += kGenThreads) etab[i] = __ldg(sc.exp_tab + i / kExpTabCopies);
-    const uint32_t tab_lane = (uint32_t)__cvta_generic_to_shared(etab) + (threadIdx.x & (kExpTabCopies - 1)) * 8u;
-    double* U = etab + kExpTabEntries * kExpTabCopies;
-    double* sig = U + (size_t)node_total * kGenThreads;
-    MolRecord* rec = reinterpret_cast<MolRecord*>(sig + (size_t)sc.n_atoms * kGenThreads);
+    double2* VD = reinterpret_cast<double2*>(etab + kExpTabEntries * kExpTabCopies);
+    double* sig = reinterpret_cast<double*>(VD + (size_t)node_total * kGenThreads);
+    double* pgrid = sig + (size_t)sc.n_atoms * kGenThreads;
+    double* items = pgrid + ((node_total + 1) & ~1);
+    // item layout (doubles): [0] w_in  [1] star_shift  [2] valid (int), n_runs (int)  [4..) Ncol_a  [..) offset * sum coef
+    //                        [run_off..) runs {joff, start} (n_rec + 1 slots)  [rec_off..) records {t, coef}
+    const int n_rec_all = n_mol * sc.n_x;
+    const int hdr = 4 + sc.n_atoms + 1;
+    const int run_off = (hdr + 1) & ~1;
+    const int rec_off = run_off + ((n_rec_all + 1 + 1) & ~1);
 
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const bool producer = tid >= kGenThreads;
+    for (int i = tid; i < kExpTabEntries * kExpTabCopies; i += kGenBlock) etab[i] = __ldg(sc.exp_tab + i / kExpTabCopies);
+    const uint32_t tab_lane = (uint32_t)__cvta_generic_to_shared(etab) + (tid & (kExpTabCopies - 1)) * 8u;
     const int p = prm.phase_lo + blockIdx.y;
     const int64_t w = prm.wav_lo + (int64_t)blockIdx.x * kGenThreads + tid;
-    const bool live = w < prm.wav_lo + prm.n_wav_sel;
+    const bool live = !producer && w < prm.wav_lo + prm.n_wav_sel;
     const double lam = live ? sc.wavelength[w] : sc.wavelength[prm.wav_lo];
     const bool per_chord_fstar = sc.fout_per_wav != 0;
+    const double kLn10 = 2.302585092994046;
 
-    // ---- prologue: atomic sigma and molecular U columns -----------------------------------------
-    {
+    // ---- prologue: atomic sigma and the molecular columns (consumers), pressure grids (producer) ---
+    if (!producer) {
         int node0 = 0;
         for (int k = 0; k < sc.n_cons; ++k) {
             const DevConstituent& C = sc.cons[k];
@@ -73,6 +106,7 @@ transit_general_kernel(const DevScene* __restrict__ scp, const TransitParams prm
                 sig[C.atom_index * kGenThreads + tid] = pb_interp_log(C.tab_x, C.tab_y, C.n_tab, sl, C.offset);
             } else {
                 const MolTable t = pb_mol_table(C);
+                // outside the table in T or lambda: every sample takes the fill value (:779 bounds_error=False)
                 const bool inside = (S.T >= t.gT[0] && S.T <= t.gT[t.nT - 1] && sl >= t.gW[0] && sl <= t.gW[t.nW - 1]);
                 int iT = 0, iW = 0;
                 double fT = 0.0, fW = 0.0;
@@ -81,87 +115,171 @@ transit_general_kernel(const DevScene* __restrict__ scp, const TransitParams prm
                     fT = (S.T - t.gT[iT]) / (t.gT[iT + 1] - t.gT[iT]);
                     fW = (sl - t.gW[iW]) / (t.gW[iW + 1] - t.gW[iW]);
                 }
+                double prev = 0.0;
                 for (int j = 0; j < t.nP; ++j) {
                     double u = t.fill;
                     if (inside) {
                         const double* v = t.values + ((int64_t)j * t.nT + iT) * t.nW + iW;
                         u = (v[0] * (1.0 - fW) + v[1] * fW) * (1.0 - fT) + (v[t.nW] * (1.0 - fW) + v[t.nW + 1] * fW) * fT;
-                    } else {
-                        u = nan("");   // marks "outside in T or lambda": every sample takes the fill value
                     }
-                    U[(node0 + j) * kGenThreads + tid] = u;
+                    u *= kLn10;
+                    VD[(node0 + j) * kGenThreads + tid].x = u;
+                    if (j > 0) VD[(node0 + j - 1) * kGenThreads + tid].y = u - prev;
+                    prev = u;
                 }
-                node0 += t.nP;
+                VD[(node0 + t.nP - 1) * kGenThreads + tid].y = 0.0;
+                VD[(node0 + t.nP) * kGenThreads + tid] = make_double2(t.fill * kLn10, 0.0);     // fill node
+                node0 += t.nP + 1;
             }
         }
+    } else {
+        int node0 = 0;
+        for (int k = 0; k < sc.n_cons; ++k) {
+            const DevConstituent& C = sc.cons[k];
+            if (C.kind != 1) continue;
+            for (int j = lane; j < C.dims[0]; j += 32) pgrid[node0 + j] = C.grid_P[j];
+            node0 += C.dims[0] + 1;
+        }
     }
+    __syncthreads();
 
     const int m_lo = blockIdx.z * prm.tiles_per_split * kChordTile;
     int m_hi = m_lo + prm.tiles_per_split * kChordTile;
     if (m_hi > sc.M) m_hi = sc.M;
     const int64_t atom_stride = (int64_t)sc.n_orb * sc.Mp;
-    const double kLn10 = 2.302585092994046;
-    double acc = 0.0;
-    int buf = 0;
 
-    for (int m = m_lo; m < m_hi; ++m) {
-        const int64_t row = (int64_t)p * sc.Mp + m;
-        const double wv = sc.w_in[row];
-        if (wv == 0.0) continue;   // blocked (CTA-uniform)
-        // ---- cooperative records for this chord ---------------------------------------------------
-        MolRecord* R = rec + (size_t)buf * rec_cap;
-        int n_rec = 0;
-        for (int k = 0; k < sc.n_cons; ++k) {
-            const DevConstituent& C = sc.cons[k];
-            if (C.kind != 1) continue;
-            const DevScenario& S = sc.scen[C.scenario];
-            const double* dens = sc.density[S.density_slot] + ((int64_t)p * sc.M + m) * sc.n_x;
-            for (int ix = tid; ix < sc.n_x; ix += kGenThreads) {
-                const double n = dens[ix];
-                const double P = fmax(n * kBoltzmann * S.T, 1e-4);                            // :927, :805
-                MolRecord r;
-                r.coef = n * C.chi * sc.delta_x;                                              // :932, :936
-                r.pad = 0;
-                if (P >= C.grid_P[0] && P <= C.grid_P[C.dims[0] - 1]) {
-                    r.j = pb_interval(C.grid_P, C.dims[0], P);
-                    r.t = (P - C.grid_P[r.j]) / (C.grid_P[r.j + 1] - C.grid_P[r.j]);
-                } else {
-                    r.j = 0; r.t = -1.0;
-                }
-                R[n_rec + ix] = r;
+    if (producer) {
+        // ======================= producer warp ==================================================
+        int it = 0;
+        for (int m = m_lo; m <= m_hi; ++m) {
+            const bool end = (m == m_hi);
+            int64_t row = 0;
+            double wv = 0.0;
+            if (!end) {
+                row = (int64_t)p * sc.Mp + m;
+                wv = sc.w_in[row];
+                if (wv == 0.0) continue;   // blocked: F_in = 0 (gasProperties.py:1233)
             }
-            n_rec += sc.n_x;
+            const int b = it & 1;
+            if (it >= 2) bar_sync(kBarEmpty + b, kGenBlock);
+            double* item = items + (size_t)b * item_doubles;
+            if (lane == 0) {
+                item[0] = wv;
+                item[1] = (!end && per_chord_fstar) ? sc.star_shift[m] : 1.0;
+                reinterpret_cast<int*>(item + 2)[0] = end ? 0 : 1;
+            }
+            if (!end) {
+                for (int a = lane; a < sc.n_atoms; a += 32) item[4 + a] = sc.ncol[a * atom_stride + row];
+                MolRecord* R = reinterpret_cast<MolRecord*>(item + rec_off);
+                MolRun* runs = reinterpret_cast<MolRun*>(item + run_off);
+                int n_rec = 0, node0 = 0, n_runs = 0, prev_joff = -1;
+                double off_sum = 0.0;
+                for (int k = 0; k < sc.n_cons; ++k) {
+                    const DevConstituent& C = sc.cons[k];
+                    if (C.kind != 1) continue;
+                    const DevScenario& S = sc.scen[C.scenario];
+                    const double* dens = sc.density[S.density_slot] + ((int64_t)p * sc.M + m) * sc.n_x;
+                    const int nP = C.dims[0];
+                    const double* g = pgrid + node0;
+                    const double kT = kBoltzmann * S.T, g0 = g[0], g1 = g[nP - 1];
+                    double part = 0.0;
+                    for (int ix0 = 0; ix0 < sc.n_x; ix0 += 32) {
+                        const int ix = ix0 + lane;
+                        const bool have = ix < sc.n_x;
+                        int joff = -2;
+                        if (have) {
+                            const double n = dens[ix];
+                            const double P = fmax(n * kT, 1e-4);                              // :927, :805
+                            MolRecord r;
+                            r.coef = n * C.chi * sc.delta_x;                                  // :932, :936
+                            if (P >= g0 && P <= g1) {
+                                int lo = 0, hi = nP - 1;
+                                while (hi - lo > 1) {
+                                    const int mid = (lo + hi) >> 1;
+                                    if (g[mid] <= P) lo = mid; else hi = mid;
+                                }
+                                r.t = (P - g[lo]) / (g[lo + 1] - g[lo]);
+                                joff = (node0 + lo) * kGenThreads * 16;
+                            } else {
+                                r.t = 0.0;
+                                joff = (node0 + nP) * kGenThreads * 16;
+                            }
+                            part += r.coef;
+                            R[n_rec + ix] = r;
+                        }
+                        // run boundaries of this 32-record chunk (records are in x order)
+                        int before = __shfl_up_sync(0xffffffffu, joff, 1);
+                        if (lane == 0) before = prev_joff;
+                        const bool head = have && joff != before;
+                        const unsigned heads = __ballot_sync(0xffffffffu, head);
+                        if (head) {
+                            const int idx = n_runs + __popc(heads & ((1u << lane) - 1u));
+                            runs[idx].joff = joff;
+                            runs[idx].start = n_rec + ix;
+                        }
+                        n_runs += __popc(heads);
+                        const int last = min(31, sc.n_x - 1 - ix0);
+                        prev_joff = __shfl_sync(0xffffffffu, joff, last);
+                    }
+                    part = pb_warp_sum(part);                  // fixed order: deterministic
+                    off_sum = fma(C.offset, part, off_sum);
+                    n_rec += sc.n_x;
+                    node0 += nP + 1;
+                    prev_joff = -1;                            // a new molecule always starts a new run
+                }
+                if (lane == 0) {
+                    runs[n_runs].joff = 0;
+                    runs[n_runs].start = n_rec;                // sentinel: end of the last run
+                    item[4 + sc.n_atoms] = off_sum;
+                    reinterpret_cast<int*>(item + 2)[1] = n_runs;
+                }
+            }
+            __threadfence_block();
+            bar_arrive(kBarFull + b, kGenBlock);
+            ++it;
         }
-        __syncthreads();
-        // ---- per-thread optical depth ----------------------------------------------------------------
+        // the consumers' last "empty" arrival has no matching wait yet: drain it so the barrier is idle at exit
+        if (it >= 2) bar_sync(kBarEmpty + ((it - 2) & 1), kGenBlock);
+        return;
+    }
+
+    // ======================= consumer warps =====================================================
+    const uint32_t vd_lane = (uint32_t)__cvta_generic_to_shared(VD) + tid * 16u;
+    double acc = 0.0;
+    for (int it = 0;; ++it) {
+        const int b = it & 1;
+        bar_sync(kBarFull + b, kGenBlock);
+        const double* item = items + (size_t)b * item_doubles;
+        if (reinterpret_cast<const int*>(item + 2)[0] == 0) break;
+        const double wv = item[0];
         double tau = 0.0;
-        for (int a = 0; a < sc.n_atoms; ++a)
-            tau = fma(sc.ncol[a * atom_stride + row], sig[a * kGenThreads + tid], tau);        // :954
+        for (int a = 0; a < sc.n_atoms; ++a) tau = fma(item[4 + a], sig[a * kGenThreads + tid], tau);   // :954
         {
-            int node0 = 0, r0 = 0;
-            for (int k = 0; k < sc.n_cons; ++k) {
-                const DevConstituent& C = sc.cons[k];
-                if (C.kind != 1) continue;
-                const double* Uc = U + (size_t)node0 * kGenThreads + tid;
-                const double fill_sigma = pb_exp_neg_tab<true>(C.fill * kLn10, tab_lane) - C.offset;
-                double s = 0.0;
-                for (int i = 0; i < sc.n_x; ++i) {
-                    const MolRecord r = R[r0 + i];
-                    const double u0 = Uc[r.j * kGenThreads], u1 = Uc[(r.j + 1) * kGenThreads];
-                    double sg;
-                    if (r.t < 0.0 || u0 != u0) sg = fill_sigma;
-                    else sg = pb_exp_neg_tab<true>(((1.0 - r.t) * u0 + r.t * u1) * kLn10, tab_lane) - C.offset;   // :814
-                    s = fma(r.coef, sg, s);
+            const int n_runs = reinterpret_cast<const int*>(item + 2)[1];
+            const MolRun* runs = reinterpret_cast<const MolRun*>(item + run_off);
+            const uint32_t ra = (uint32_t)__cvta_generic_to_shared(item + rec_off);
+            double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+            int start = runs[0].start;
+            for (int q = 0; q < n_runs; ++q) {
+                const int joff = runs[q].joff, stop = runs[q + 1].start;
+                double v, d;   // this thread's V_j and V_{j+1} - V_j: one LDS.128 per run instead of per record
+                asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v), "=d"(d) : "r"(vd_lane + (uint32_t)joff));
+                int i = start;
+                for (; i + 4 <= stop; i += 4) {
+                    s0 += mol_term(ra + i * 16, v, d, tab_lane);
+                    s1 += mol_term(ra + i * 16 + 16, v, d, tab_lane);
+                    s2 += mol_term(ra + i * 16 + 32, v, d, tab_lane);
+                    s3 += mol_term(ra + i * 16 + 48, v, d, tab_lane);
                 }
-                tau += s;
-                node0 += C.dims[0];
-                r0 += sc.n_x;
+                for (; i < stop; ++i) s0 += mol_term(ra + i * 16, v, d, tab_lane);
+                start = stop;
             }
+            tau += ((s0 + s1) + (s2 + s3)) - item[4 + sc.n_atoms];   // sum coef (sigma - offset), :814, :936
         }
         double f = wv;
-        if (per_chord_fstar) f *= pb_interp_log(sc.fstar_x, sc.fstar_y, sc.n_fstar, lam / sc.star_shift[m], 0.0);
-        acc = fma(f, pb_exp_neg_tab<true>(-tau, tab_lane), acc);                                    // :1241
-        buf ^= 1;   // the other record buffer is free: its readers passed the barrier above
+        if (per_chord_fstar) f *= pb_interp_log(sc.fstar_x, sc.fstar_y, sc.n_fstar, lam / item[1], 0.0);
+        bar_arrive(kBarEmpty + b, kGenBlock);   // every read of the item is done
+        acc = fma(f, pb_exp_neg_tab<true>(-tau, tab_lane), acc);                              // :1241
     }
 
     if (!live) return;
@@ -176,20 +294,23 @@ cudaError_t launch_transit_general(const DevScene* d_scene, const DevScene& h, c
     *n_launch = 0;
     int node_total = 0, n_mol = 0;
     for (int k = 0; k < h.n_cons; ++k)
-        if (h.cons[k].kind == 1) { node_total += h.cons[k].dims[0]; ++n_mol; }
+        if (h.cons[k].kind == 1) { node_total += h.cons[k].dims[0] + 1; ++n_mol; }
     if (node_total > kMaxMolNodes) return cudaErrorInvalidValue;
     if (h.fout_per_wav) {
         fout_table_kernel<<<(unsigned)((h.n_wav + kGenThreads - 1) / kGenThreads), kGenThreads, 0, st>>>(d_scene);
         ++*n_launch;
     }
-    const int rec_cap = n_mol * h.n_x > 0 ? n_mol * h.n_x : 1;
-    const size_t smem = ((size_t)kExpTabEntries * kExpTabCopies + ((size_t)node_total + h.n_atoms) * kGenThreads) * sizeof(double) +
-                        2 * (size_t)rec_cap * sizeof(MolRecord);
+    const int n_rec_all = n_mol * h.n_x;
+    const int run_off = ((4 + h.n_atoms + 1) + 1) & ~1;
+    const int item_doubles = run_off + ((n_rec_all + 1 + 1) & ~1) + n_rec_all * (int)(sizeof(MolRecord) / sizeof(double));
+    const size_t smem = (size_t)kExpTabEntries * kExpTabCopies * sizeof(double) +
+                        (size_t)node_total * kGenThreads * sizeof(double2) + (size_t)h.n_atoms * kGenThreads * sizeof(double) +
+                        (size_t)((node_total + 1) & ~1) * sizeof(double) + 2 * (size_t)item_doubles * sizeof(double);
     if (smem > 200 * 1024) return cudaErrorInvalidValue;
     cudaError_t e = cudaFuncSetAttribute(transit_general_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     dim3 grid((unsigned)((prm.n_wav_sel + kGenThreads - 1) / kGenThreads), (unsigned)prm.n_phase, (unsigned)prm.n_split);
-    transit_general_kernel<<<grid, kGenThreads, smem, st>>>(d_scene, prm, rec_cap);
+    transit_general_kernel<<<grid, kGenBlock, smem, st>>>(d_scene, prm, item_doubles, node_total, n_mol);
     ++*n_launch;
     return cudaGetLastError();
 }
