@@ -25,7 +25,7 @@ struct __align__(16) MolRecord {
     double coef;   // n * chi * delta_x
 };
 struct MolRun {
-    int joff;      // node index (global over molecules) * 16 B * kGenThreads: byte offset of V/D in shared memory
+    int joff;      // node index (global over molecules) * 8 B * kGenThreads: byte offset of V_j in shared memory
     int start;     // first record of the run; the run ends where the next one starts
 };
 
@@ -34,7 +34,7 @@ struct MolRun {
 __device__ __forceinline__ double mol_term(uint32_t rec_addr, double v, double d, uint32_t tab_lane) {
     double t, coef;
     asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(t), "=d"(coef) : "r"(rec_addr));
-    return coef * pb_exp_neg_tab<false>(fma(t, d, v), tab_lane);
+    return coef * pb_exp_neg_tab<false, kGenTabCopies>(fma(t, d, v), tab_lane);
 }
 
 // F_out[w] = sum_m rho*clv*F*(lambda_w / shift*(m))   (gasProperties.py:1213-1222, :1232, :1249/:1256)
@@ -57,6 +57,7 @@ __device__ __forceinline__ void bar_sync(int id, int count) { asm volatile("bar.
 __device__ __forceinline__ void bar_arrive(int id, int count) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory"); }
 constexpr int kBarFull = 1, kBarEmpty = 3;
 constexpr int kGenBlock = kGenThreads + 32;   // + one producer warp
+constexpr int kGenTabCopies = 4;              // exp table [256][4]: 8 KB, so that four CTAs fit one SM
 
 // Warp-specialised: warp 4 (producer) walks the chords of this CTA's split, skips blocked ones, and
 // turns each chord's density rows into a shared-memory item
@@ -64,17 +65,17 @@ constexpr int kGenBlock = kGenThreads + 32;   // + one producer warp
 // (global loads, pressure-interval search and the division happen here, off the consumers' path);
 // warps 0-3 (consumers, one wavelength per thread) wait on the item and sum
 //     tau = sum_a Ncol_a sigma_a + sum_records coef * exp(V_j + t (V_{j+1} - V_j)) - offset * sum coef.
-// Shared memory: exp table [256][8] | VD[node_total][kGenThreads] double2 {V_j, V_{j+1} - V_j} with
-// V = ln sigma at pressure node j (T and lambda already interpolated for this thread's wavelength;
-// every molecule has one extra "fill" node {ln(fill sigma), 0}) | sig[n_atoms][kGenThreads] |
+// Shared memory: exp table [256][4] | V[node_total + 1][kGenThreads], V = ln sigma at pressure node j
+// (T and lambda already interpolated for this thread's wavelength; every molecule has one extra
+// "fill" node ln(fill sigma); one zero pad row at the end) | sig[n_atoms][kGenThreads] |
 // pgrid[node_total] | item[2]
 __global__ void __launch_bounds__(kGenBlock)
 transit_general_kernel(const DevScene* __restrict__ scp, const TransitParams prm, int item_doubles, int node_total, int n_mol) {
     const DevScene& sc = *scp;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     double* etab = reinterpret_cast<double*>(smem_raw);
-    double2* VD = reinterpret_cast<double2*>(etab + kExpTabEntries * kExpTabCopies);
-    double* sig = reinterpret_cast<double*>(VD + (size_t)node_total * kGenThreads);
+    double* V = etab + kExpTabEntries * kGenTabCopies;
+    double* sig = V + (size_t)(node_total + 1) * kGenThreads;
     double* pgrid = sig + (size_t)sc.n_atoms * kGenThreads;
     double* items = pgrid + ((node_total + 1) & ~1);
     // item layout (doubles): [0] w_in  [1] star_shift  [2] valid (int), n_runs (int)  [4..) Ncol_a  [..) offset * sum coef
@@ -86,8 +87,8 @@ transit_general_kernel(const DevScene* __restrict__ scp, const TransitParams prm
 
     const int tid = threadIdx.x, lane = tid & 31;
     const bool producer = tid >= kGenThreads;
-    for (int i = tid; i < kExpTabEntries * kExpTabCopies; i += kGenBlock) etab[i] = __ldg(sc.exp_tab + i / kExpTabCopies);
-    const uint32_t tab_lane = (uint32_t)__cvta_generic_to_shared(etab) + (tid & (kExpTabCopies - 1)) * 8u;
+    for (int i = tid; i < kExpTabEntries * kGenTabCopies; i += kGenBlock) etab[i] = __ldg(sc.exp_tab + i / kGenTabCopies);
+    const uint32_t tab_lane = (uint32_t)__cvta_generic_to_shared(etab) + (tid & (kGenTabCopies - 1)) * 8u;
     const int p = prm.phase_lo + blockIdx.y;
     const int64_t w = prm.wav_lo + (int64_t)blockIdx.x * kGenThreads + tid;
     const bool live = !producer && w < prm.wav_lo + prm.n_wav_sel;
@@ -115,7 +116,6 @@ transit_general_kernel(const DevScene* __restrict__ scp, const TransitParams prm
                     fT = (S.T - t.gT[iT]) / (t.gT[iT + 1] - t.gT[iT]);
                     fW = (sl - t.gW[iW]) / (t.gW[iW + 1] - t.gW[iW]);
                 }
-                double prev = 0.0;
                 for (int j = 0; j < t.nP; ++j) {
                     double u = t.fill;
                     if (inside) {
@@ -123,15 +123,13 @@ transit_general_kernel(const DevScene* __restrict__ scp, const TransitParams prm
                         u = (v[0] * (1.0 - fW) + v[1] * fW) * (1.0 - fT) + (v[t.nW] * (1.0 - fW) + v[t.nW + 1] * fW) * fT;
                     }
                     u *= kLn10;
-                    VD[(node0 + j) * kGenThreads + tid].x = u;
-                    if (j > 0) VD[(node0 + j - 1) * kGenThreads + tid].y = u - prev;
-                    prev = u;
+                    V[(node0 + j) * kGenThreads + tid] = u;
                 }
-                VD[(node0 + t.nP - 1) * kGenThreads + tid].y = 0.0;
-                VD[(node0 + t.nP) * kGenThreads + tid] = make_double2(t.fill * kLn10, 0.0);     // fill node
+                V[(node0 + t.nP) * kGenThreads + tid] = t.fill * kLn10;     // fill node (records point at it with t = 0)
                 node0 += t.nP + 1;
             }
         }
+        V[(size_t)node_total * kGenThreads + tid] = 0.0;   // pad row: "V_{j+1}" of the last fill node
     } else {
         int node0 = 0;
         for (int k = 0; k < sc.n_cons; ++k) {
@@ -199,10 +197,10 @@ transit_general_kernel(const DevScene* __restrict__ scp, const TransitParams prm
                                     if (g[mid] <= P) lo = mid; else hi = mid;
                                 }
                                 r.t = (P - g[lo]) / (g[lo + 1] - g[lo]);
-                                joff = (node0 + lo) * kGenThreads * 16;
+                                joff = (node0 + lo) * kGenThreads * 8;
                             } else {
                                 r.t = 0.0;
-                                joff = (node0 + nP) * kGenThreads * 16;
+                                joff = (node0 + nP) * kGenThreads * 8;
                             }
                             part += r.coef;
                             R[n_rec + ix] = r;
@@ -244,7 +242,7 @@ transit_general_kernel(const DevScene* __restrict__ scp, const TransitParams prm
     }
 
     // ======================= consumer warps =====================================================
-    const uint32_t vd_lane = (uint32_t)__cvta_generic_to_shared(VD) + tid * 16u;
+    const uint32_t vd_lane = (uint32_t)__cvta_generic_to_shared(V) + tid * 8u;
     double acc = 0.0;
     for (int it = 0;; ++it) {
         const int b = it & 1;
@@ -262,8 +260,10 @@ transit_general_kernel(const DevScene* __restrict__ scp, const TransitParams prm
             int start = runs[0].start;
             for (int q = 0; q < n_runs; ++q) {
                 const int joff = runs[q].joff, stop = runs[q + 1].start;
-                double v, d;   // this thread's V_j and V_{j+1} - V_j: one LDS.128 per run instead of per record
-                asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v), "=d"(d) : "r"(vd_lane + (uint32_t)joff));
+                double v, d;   // this thread's V_j and V_{j+1} - V_j: loaded once per run instead of per record
+                asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(vd_lane + (uint32_t)joff));
+                asm volatile("ld.shared.f64 %0, [%1];" : "=d"(d) : "r"(vd_lane + (uint32_t)joff + kGenThreads * 8u));
+                d -= v;
                 int i = start;
                 for (; i + 4 <= stop; i += 4) {
                     s0 += mol_term(ra + i * 16, v, d, tab_lane);
@@ -279,7 +279,7 @@ transit_general_kernel(const DevScene* __restrict__ scp, const TransitParams prm
         double f = wv;
         if (per_chord_fstar) f *= pb_interp_log(sc.fstar_x, sc.fstar_y, sc.n_fstar, lam / item[1], 0.0);
         bar_arrive(kBarEmpty + b, kGenBlock);   // every read of the item is done
-        acc = fma(f, pb_exp_neg_tab<true>(-tau, tab_lane), acc);                              // :1241
+        acc = fma(f, pb_exp_neg_tab<true, kGenTabCopies>(-tau, tab_lane), acc);                              // :1241
     }
 
     if (!live) return;
@@ -303,8 +303,8 @@ cudaError_t launch_transit_general(const DevScene* d_scene, const DevScene& h, c
     const int n_rec_all = n_mol * h.n_x;
     const int run_off = ((4 + h.n_atoms + 1) + 1) & ~1;
     const int item_doubles = run_off + ((n_rec_all + 1 + 1) & ~1) + n_rec_all * (int)(sizeof(MolRecord) / sizeof(double));
-    const size_t smem = (size_t)kExpTabEntries * kExpTabCopies * sizeof(double) +
-                        (size_t)node_total * kGenThreads * sizeof(double2) + (size_t)h.n_atoms * kGenThreads * sizeof(double) +
+    const size_t smem = (size_t)kExpTabEntries * kGenTabCopies * sizeof(double) +
+                        (size_t)(node_total + 1) * kGenThreads * sizeof(double) + (size_t)h.n_atoms * kGenThreads * sizeof(double) +
                         (size_t)((node_total + 1) & ~1) * sizeof(double) + 2 * (size_t)item_doubles * sizeof(double);
     if (smem > 200 * 1024) return cudaErrorInvalidValue;
     cudaError_t e = cudaFuncSetAttribute(transit_general_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

@@ -80,16 +80,17 @@ __host__ __device__ inline double pb_exp_tab_entry(double two_pow_frac, int j) {
 
 // T = 2^e * 2^(j/256) for k = 256 e + j.  tab_addr: shared-window byte address of this lane's column.
 // AND + IMAD + LDS.64 + IMAD, all off the FP64 pipe.
+template <int COPIES = kExpTabCopies>
 __device__ __forceinline__ double pb_exp_tab_load(uint32_t tab_addr, int k) {
     int t_lo, t_hi;
     asm volatile("{\n"
         ".reg .b32 j, a;\n"
         "and.b32 j, %2, 255;\n"
-        "mad.lo.u32 a, j, 64, %3;\n"
+        "mad.lo.u32 a, j, %4, %3;\n"
         "ld.shared.v2.b32 {%0, %1}, [a];\n"
         "}\n"
         : "=r"(t_lo), "=r"(t_hi)
-        : "r"(k), "r"(tab_addr));
+        : "r"(k), "r"(tab_addr), "n"(COPIES * 8));
     return __hiloint2double(t_hi + (k << kExpTabShift), t_lo);
 }
 
@@ -103,7 +104,7 @@ struct ExpConsts {
 };
 __host__ __device__ inline ExpConsts pb_exp_consts() { return ExpConsts{kExpScale, kExpStep, 1.6666666666666666e-01}; }
 
-template <bool CLAMP>
+template <bool CLAMP, int COPIES = kExpTabCopies>
 __device__ __forceinline__ double pb_exp_neg_tab(double u, uint32_t tab_addr, const ExpConsts& ec) {
     if (CLAMP) {
         const unsigned hi = min((unsigned)__double2hiint(u), 0xC085E000u);   // u >= -700 (-0.0/+tiny pass)
@@ -113,16 +114,16 @@ __device__ __forceinline__ double pb_exp_neg_tab(double u, uint32_t tab_addr, co
     const int k = __double2loint(kd);
     kd -= kExpMagic;
     const double r = fma(-kd, ec.step, u);
-    const double T = pb_exp_tab_load(tab_addr, k);
+    const double T = pb_exp_tab_load<COPIES>(tab_addr, k);
     double p = fma(r, ec.sixth, 0.5);
     p = fma(p, r, 1.0);
     const double q = r * p;
     return fma(T, q, T);
 }
 
-template <bool CLAMP>
+template <bool CLAMP, int COPIES = kExpTabCopies>
 __device__ __forceinline__ double pb_exp_neg_tab(double u, uint32_t tab_addr) {
-    return pb_exp_neg_tab<CLAMP>(u, tab_addr, pb_exp_consts());
+    return pb_exp_neg_tab<CLAMP, COPIES>(u, tab_addr, pb_exp_consts());
 }
 
 // exp(a) for |a| <= 700 (same kernel as pb_exp_neg, two-sided); used for 10**v = exp(v ln10) of the
