@@ -16,6 +16,7 @@
 namespace pb200 {
 
 constexpr int kGenThreads = 128;
+constexpr int kGenTabCopies = 4;   // exp table [256][4]: 8 KB, so that four CTAs fit one SM
 constexpr int kGenWarps = kGenThreads / 32;
 constexpr int kMaxMolNodes = 64;   // sum over molecules of (pressure nodes + 1) held in shared memory
 
@@ -57,7 +58,6 @@ __device__ __forceinline__ void bar_sync(int id, int count) { asm volatile("bar.
 __device__ __forceinline__ void bar_arrive(int id, int count) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory"); }
 constexpr int kBarFull = 1, kBarEmpty = 3;
 constexpr int kGenBlock = kGenThreads + 32;   // + one producer warp
-constexpr int kGenTabCopies = 4;              // exp table [256][4]: 8 KB, so that four CTAs fit one SM
 
 // Warp-specialised: warp 4 (producer) walks the chords of this CTA's split, skips blocked ones, and
 // turns each chord's density rows into a shared-memory item
