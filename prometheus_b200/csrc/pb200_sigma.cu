@@ -30,45 +30,85 @@ __global__ void sigma_u_kernel(const DevScene* __restrict__ scp, int64_t wav_lo,
 }
 
 // ---- (b2) Voigt synthesis: sigma(wl) = sum_lines K f V(c/wl - c/wl0; sigma_v/wl0, gamma) -------
-// One thread per wavelength, line parameters staged through shared memory in chunks, the line sum
-// lives in a register; one coalesced store per wavelength.  (gasProperties.py:672-692)
-constexpr int kLineChunk = 1024;
+// A thread owns kVoigtWpt refined wavelengths and keeps their line sums in registers; line parameters
+// are staged through shared memory in chunks as three 16-byte records per line (broadcast LDS.128),
+// one coalesced store per wavelength.  (gasProperties.py:672-692)
+//
+// Almost every (wavelength, line) pair is far out in the Lorentzian wing (|z|^2 >= 1e8: the lines
+// span thousands of Angstrom, a Doppler width is ~0.01 A), where the asymptotic series of w(z) needs
+// two terms:  Re w = y/(sqrt(pi) |z|^2) * (1 + (1.5 x^2 - 0.5 y^2)/|z|^4)  (next term 0.75/|z|^4 < 1e-16).
+// That branch is 13 FP64 instructions (reciprocal: MUFU.RCP64H seed + two Newton steps); everything
+// nearer goes through the general pb_faddeeva_re.  FP64-pipe-bound.
+constexpr int kLineChunk = 512;
+constexpr int kVoigtWpt = 2;
+constexpr int kVoigtThreads = 128;
 
-__global__ void __launch_bounds__(256)
+__device__ __forceinline__ double pb_rcp(double a) {   // 1/a for normal a > 0, <= 1 ulp
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(a));
+    double e = fma(-a, r, 1.0);
+    r = fma(r, e, r);
+    e = fma(-a, r, 1.0);
+    return fma(r, e, r);
+}
+
+__global__ void __launch_bounds__(kVoigtThreads)
 voigt_sigma_kernel(const double* __restrict__ line_wl, const double* __restrict__ line_gamma,
                    const double* __restrict__ line_f, int64_t n_lines, double sigma_v,
                    const double* __restrict__ wl, int64_t n, double offset, double* __restrict__ out_sigma,
                    double* __restrict__ out_log10) {
-    __shared__ double s_nu0[kLineChunk], s_rs[kLineChunk], s_zi[kLineChunk], s_amp[kLineChunk];
-    const double kInvSqrt2 = 0.7071067811865476, kSqrt2Pi = 2.5066282746310002;
+    // per line: {nu0, 1/(sigma_nu sqrt2)} {-y^2/2, amp*y/sqrt(pi)} {y, amp},  amp = K f /(sigma_nu sqrt(2 pi))
+    __shared__ double2 s_a[kLineChunk], s_b[kLineChunk], s_c[kLineChunk];
+    const double kInvSqrt2 = 0.7071067811865476, kSqrt2Pi = 2.5066282746310002, kInvSqrtPi = 0.5641895835477563;
     // np.pi * e**2 / (m_e * c), evaluated left to right as the reference does (:689-690)
     const double K = (kPi * (kElemCharge * kElemCharge)) / (kElectronMass * kLightSpeed);
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const double nu = (i < n) ? kLightSpeed / wl[i] : 0.0;
-    double acc = 0.0;
+    const int64_t i0 = (int64_t)blockIdx.x * (kVoigtThreads * kVoigtWpt) + threadIdx.x;
+    double nu[kVoigtWpt], acc[kVoigtWpt];
+#pragma unroll
+    for (int j = 0; j < kVoigtWpt; ++j) {
+        const int64_t i = i0 + (int64_t)j * kVoigtThreads;
+        nu[j] = (i < n) ? kLightSpeed / wl[i] : 1.0;
+        acc[j] = 0.0;
+    }
     for (int64_t l0 = 0; l0 < n_lines; l0 += kLineChunk) {
         const int cnt = (int)((n_lines - l0 < kLineChunk) ? n_lines - l0 : kLineChunk);
         __syncthreads();
-        for (int l = threadIdx.x; l < cnt; l += blockDim.x) {
+        for (int l = threadIdx.x; l < cnt; l += kVoigtThreads) {
             const double w0 = line_wl[l0 + l];
             const double sig_nu = sigma_v / w0;           // :688
             const double rs = 1.0 / sig_nu;
-            s_nu0[l] = kLightSpeed / w0;
-            s_rs[l] = rs * kInvSqrt2;
-            s_zi[l] = line_gamma[l0 + l] * rs * kInvSqrt2;
-            s_amp[l] = K * line_f[l0 + l] * (rs / kSqrt2Pi);
+            const double y = line_gamma[l0 + l] * rs * kInvSqrt2;
+            const double amp = K * line_f[l0 + l] * (rs / kSqrt2Pi);
+            s_a[l] = make_double2(kLightSpeed / w0, rs * kInvSqrt2);
+            s_b[l] = make_double2(-0.5 * y * y, amp * y * kInvSqrtPi);
+            s_c[l] = make_double2(y, amp);
         }
         __syncthreads();
-        if (i < n) {
-            for (int l = 0; l < cnt; ++l) {
-                const double zr = (nu - s_nu0[l]) * s_rs[l];
-                acc = fma(s_amp[l], pb_faddeeva_re(zr, s_zi[l]), acc);
+        for (int l = 0; l < cnt; ++l) {
+            const double2 a = s_a[l], b = s_b[l];
+#pragma unroll
+            for (int j = 0; j < kVoigtWpt; ++j) {
+                const double x = (nu[j] - a.x) * a.y;
+                const double x2 = x * x;
+                const double r2 = fma(-2.0, b.x, x2);
+                if (r2 >= 1e8) {
+                    const double inv = pb_rcp(r2);
+                    const double corr = fma(inv * inv, fma(1.5, x2, b.x), 1.0);
+                    acc[j] = fma(b.y * inv, corr, acc[j]);
+                } else {
+                    const double2 c = s_c[l];
+                    acc[j] = fma(c.y, pb_faddeeva_re(x, c.x), acc[j]);
+                }
             }
         }
     }
-    if (i < n) {
-        if (out_sigma) out_sigma[i] = acc;
-        if (out_log10) out_log10[i] = log10(acc + offset);   // :713-714
+#pragma unroll
+    for (int j = 0; j < kVoigtWpt; ++j) {
+        const int64_t i = i0 + (int64_t)j * kVoigtThreads;
+        if (i < n) {
+            if (out_sigma) out_sigma[i] = acc[j];
+            if (out_log10) out_log10[i] = log10(acc[j] + offset);   // :713-714
+        }
     }
 }
 
@@ -176,8 +216,9 @@ void launch_sigma_u(const DevScene* d_scene, int n_atoms, int n_orb, int64_t wav
 void launch_voigt_sigma(const double* lw, const double* lg, const double* lf, int64_t n_lines, double sigma_v,
                         const double* wl, int64_t n, double offset, double* out_sigma, double* out_log10,
                         cudaStream_t st) {
-    voigt_sigma_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(lw, lg, lf, n_lines, sigma_v, wl, n, offset,
-                                                                    out_sigma, out_log10);
+    const int64_t per = kVoigtThreads * kVoigtWpt;
+    voigt_sigma_kernel<<<(unsigned)((n + per - 1) / per), kVoigtThreads, 0, st>>>(lw, lg, lf, n_lines, sigma_v, wl, n, offset,
+                                                                                 out_sigma, out_log10);
 }
 void launch_voigt_profile(const double* x, const double* s, const double* g, int64_t n, double* out, int sm_count,
                           cudaStream_t st) {
