@@ -385,7 +385,8 @@ def run_b200(args):
         if world > 1:
             dist.all_reduce(e2e_total, op=dist.ReduceOp.MAX)
         e2e_ms_per_step = float(e2e_total.item()) / args.steps
-    launch_total = torch.tensor([launches], dtype=torch.int64, device=dev)
+    h2d_local = state["info"]["h2d_bytes"] if (world > 1 and "info" in state) else info["h2d_bytes"]
+    launch_total = torch.tensor([launches, h2d_local], dtype=torch.int64, device=dev)
     if world > 1:
         dist.all_reduce(launch_total)
     if rank != 0:
@@ -405,11 +406,11 @@ def run_b200(args):
         "config": workload_config(args.workload, spec, n_c, n_wav, world),
         "runs_per_s": 1e3 / ms_per_step,
         "e2e": {"value": samples_total / (e2e_ms_per_step * 1e-3), "unit": "samples/s", "ms_per_step": e2e_ms_per_step,
-                "h2d_bytes_per_step": int(info["h2d_bytes"]) * world, "d2h_bytes_per_step": int(n_orb * n_wav * 8),
+                "h2d_bytes_per_step": int(launch_total[1].item()), "d2h_bytes_per_step": int(n_orb * n_wav * 8),
                 "runs_per_s": 1e3 / e2e_ms_per_step},
         "e2e_breakdown_ms": ({k: tr.last_timing[k] for k in ("upload_ms", "column_ms", "transit_ms", "finalize_ms", "download_ms")}
                              if world == 1 and tr.last_timing else None),
-        "gpu_launches": int(launch_total.item()),
+        "gpu_launches": int(launch_total[0].item()),
         "clocks": clk,
         "roofline": {"kernel": "transit_kernel (c': tau + exp(-tau) + disk sum)", "bound": "hbm", "achieved": achieved,
                      "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "peak_source": peak_src,
@@ -457,6 +458,10 @@ def run_b200(args):
 
 
 def main():
+    # stdout carries exactly ONE JSON line: anything libraries print there (NCCL's version banner) goes to stderr
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real_stdout, "w")
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)

@@ -138,7 +138,10 @@ def sum_over_chords(transit, group=None, axis: str = "wavelength", device: int |
         device = torch.cuda.current_device()
     ctx = host.get_context(device)
     ctx.set_stream(torch.cuda.current_stream(device).cuda_stream)
-    sc, keep, info = scene.flatten(transit)
+    world = torch.distributed.get_world_size(group) if torch.distributed.is_initialized() else 1
+    rank = torch.distributed.get_rank(group) if torch.distributed.is_initialized() else 0
+    wav_range = partition(int(np.size(transit.wavelength)), world)[rank] if (axis == "wavelength" and world > 1) else None
+    sc, keep, info = scene.flatten(transit, wav_range=wav_range)
     ctx.set_scene(sc, keep)
     st = state.get("sharded") if state else None
     if st is None or (st.n_orb, st.n_wav, st.axis) != (info["n_orb"], info["n_wav"], axis):

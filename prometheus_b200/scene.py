@@ -85,8 +85,24 @@ class SceneBuilder:
         return self.ptr(np.broadcast_to(np.asarray(v, dtype=np.float64), (n_orb,)))
 
 
-def flatten(transit, wavelength=None) -> tuple[capi.Scene, list, dict]:
-    """Transit-like object -> (pb200_scene, keep-alive list, info)."""
+def _trim_table(tx, ty, q_lo, q_hi):
+    """Sub-table that answers every np.interp query in [q_lo, q_hi] exactly like the full table:
+    the queries stay strictly inside the kept range unless they were outside the full one."""
+    n = tx.size
+    i0 = max(int(np.searchsorted(tx, q_lo, side="right")) - 2, 0)
+    i1 = min(int(np.searchsorted(tx, q_hi, side="left")) + 2, n)
+    if i1 - i0 < 2:
+        i0, i1 = max(min(i0, n - 2), 0), min(max(i1, i0 + 2), n)
+    return tx[i0:i1], ty[i0:i1]
+
+
+def flatten(transit, wavelength=None, wav_range=None) -> tuple[capi.Scene, list, dict]:
+    """Transit-like object -> (pb200_scene, keep-alive list, info).
+
+    `wav_range = (lo, hi)`: the caller will only run wavelengths [lo, hi) of this scene (one rank of
+    a wavelength-sharded run); the atomic sigma tables are then cut down to the part those
+    wavelengths can reach through any phase's Doppler factor, which divides the upload by the
+    number of ranks without changing a single result bit."""
     b = SceneBuilder()
     grid = transit.spatialGrid
     atmos = transit.atmosphere
@@ -131,6 +147,7 @@ def flatten(transit, wavelength=None) -> tuple[capi.Scene, list, dict]:
 
     scn_arr = (capi.Scenario * len(dists))()
     cons_list = []
+    shifts_of = {}
     for i, dist in enumerate(dists):
         q = scn_arr[i]
         q.type, params = scenario_parameters(dist)
@@ -153,7 +170,9 @@ def flatten(transit, wavelength=None) -> tuple[capi.Scene, list, dict]:
             v_los = body.getLOSvelocity(phase)
         else:
             v_los = np.zeros(n_orb)
-        q.shift = b.per_phase(const.calculateDopplerShift(-np.asarray(v_los, dtype=np.float64)), n_orb)
+        shift = np.broadcast_to(np.asarray(const.calculateDopplerShift(-np.asarray(v_los, dtype=np.float64)), dtype=np.float64), (n_orb,))
+        shifts_of[id(dist)] = shift
+        q.shift = b.per_phase(shift, n_orb)
         if _kind(dist) == "TidallyHeatedMoon":                                   # gasProperties.py:425-436
             q.amplitude = b.per_phase(dist.calculateAbsorberNumber(phase), n_orb)
         q.first_constituent = len(cons_list)
@@ -178,7 +197,13 @@ def flatten(transit, wavelength=None) -> tuple[capi.Scene, list, dict]:
             n_mols += 1
         else:
             q.kind = 0
-            q.tab_x, q.tab_y, q.n_tab = b.ptr(lf.x), b.ptr(lf.y), int(np.size(lf.x))   # gasProperties.py:730-735
+            tx, ty = np.asarray(lf.x), np.asarray(lf.y)                                  # gasProperties.py:730-735
+            if wav_range is not None and tx.size > 4 and wav_range[1] > wav_range[0]:
+                sh = shifts_of[id(dist)]
+                lam_lo, lam_hi = wavelength[wav_range[0]], wavelength[wav_range[1] - 1]
+                cand = np.outer(sh, [lam_lo, lam_hi])
+                tx, ty = _trim_table(tx, ty, float(cand.min()), float(cand.max()))
+            q.tab_x, q.tab_y, q.n_tab = b.ptr(tx), b.ptr(ty), int(tx.size)
             n_atoms += 1
     sc.n_scenarios, sc.n_constituents = len(dists), len(cons_list)
     sc.scenarios = C.cast(scn_arr, C.POINTER(capi.Scenario))

@@ -262,3 +262,21 @@ def test_serpens_out_of_grid_raises(nist_rows):
     with pytest.raises(capi.Pb200Error) as ei:
         tr.sumOverChords()
     assert ei.value.code == -6
+
+
+def test_trimmed_sigma_tables_are_bit_identical(ctx, transits):
+    """A wavelength-sharded rank uploads only the part of each sigma table its wavelengths can reach
+    (scene.flatten(wav_range=...)); the tile it computes must not change by a single bit."""
+    from prometheus_b200 import scene
+    for name in ("C3s", "C5s", "C2s"):
+        tr = transits(name)
+        n_orb, n_wav = len(tr.spatialGrid.constructOrbphaseAxis()), tr.wavelength.size
+        for lo, hi in [(0, n_wav // 3), (n_wav // 3, n_wav - 5), (n_wav - 5, n_wav), (n_wav // 2, n_wav // 2 + 1)]:
+            sc, keep, info = scene.flatten(tr)
+            ctx.set_scene(sc, keep)
+            full, _ = ctx.run(0, n_orb, lo, hi)
+            sc2, keep2, info2 = scene.flatten(tr, wav_range=(lo, hi))
+            assert info2["h2d_bytes"] <= info["h2d_bytes"]
+            ctx.set_scene(sc2, keep2)
+            part, _ = ctx.run(0, n_orb, lo, hi)
+            assert np.array_equal(full, part), (name, lo, hi)
