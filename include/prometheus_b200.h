@@ -194,6 +194,14 @@ int pb200_molecular_sigma(pb200_ctx* ctx, const double* grid_P, const double* gr
                           double fill, double offset, const double* P, double T, const double* wl,
                           int64_t n_c, int64_t n_x, int64_t n_wav, double* out_host);
 
+/* ---- result file ------------------------------------------------------------------------- */
+/* Byte-identical replacement of the reference's writer (prometheus.py:142-156): first row
+   "nan orbphase/(2 pi) ...", then one row per wavelength "lambda R(phase_0, lambda) ...", np.savetxt
+   defaults (fmt %.18e, ' ' delimiter, header lines prefixed "# ").  R is [n_orb][n_wav] as returned by
+   pb200_run.  Host code, n_threads <= 0: all hardware threads.                                   */
+int pb200_write_output(const char* path, const char* header, const double* wavelength,
+                       const double* orbphase, const double* R, int n_orb, int64_t n_wav, int n_threads);
+
 /* ---- machine probes (roofline denominators that MEASURED_PEAKS.json does not hold) ------- */
 /* DFMA-chain FP64 peak [TFLOP/s] and fp64 exp throughput [G exp/s] on this context's GPU    */
 int pb200_probe_fp64(pb200_ctx* ctx, double* dfma_tflops, double* exp_gops);

@@ -22,7 +22,7 @@ EXPORTS = [
     "pb200_set_stream", "pb200_launch_count", "pb200_host_alloc", "pb200_host_free", "pb200_set_scene", "pb200_run", "pb200_run_device",
     "pb200_last_timing", "pb200_number_density", "pb200_number_density_chords", "pb200_column_density",
     "pb200_chord_masks", "pb200_optical_depth", "pb200_sigma_lookup", "pb200_voigt_sigma",
-    "pb200_voigt_profile", "pb200_molecular_sigma", "pb200_probe_fp64",
+    "pb200_voigt_profile", "pb200_molecular_sigma", "pb200_write_output", "pb200_probe_fp64",
 ]
 
 SCN_BAROMETRIC, SCN_HYDROSTATIC, SCN_POWERLAW, SCN_TORUS, SCN_SERPENS = range(5)
@@ -126,6 +126,7 @@ def load():
         "pb200_molecular_sigma": (C.c_int, [vp, c_double_p, c_double_p, c_double_p, c_double_p,
                                             C.POINTER(C.c_int32), dbl, dbl, c_double_p, dbl, c_double_p,
                                             i64, i64, i64, c_double_p]),
+        "pb200_write_output": (C.c_int, [C.c_char_p, C.c_char_p, c_double_p, c_double_p, c_double_p, i32, i64, i32]),
         "pb200_probe_fp64": (C.c_int, [vp, c_double_p, c_double_p]),
     }
     for name, (res, args) in sig.items():

@@ -210,7 +210,8 @@ class AtmosphericConstituent:
         lam0 = rows[mine, 2].astype(float) * 1e-8
         gamma = rows[mine, 3].astype(float) / (4.0 * np.pi)
         f = rows[mine, 4].astype(float)
-        inside = (lam0 > min(wavelength)) & (lam0 < max(wavelength))
+        wavelength = np.asarray(wavelength)
+        inside = (lam0 > wavelength.min()) & (lam0 < wavelength.max())   # the reference uses builtin min/max (0.13 s each at C5)
         return lam0[inside], gamma[inside], f[inside]
 
     def calculateVoigtProfile(self, wavelength):
