@@ -418,9 +418,9 @@ def run_b200(args):
                      "traffic": recorded_traffic(args.workload), "kernel_ms": kernel_ms,
                      "fp64": {"achieved_tflops": fl, "peak_tflops_dfma_probe": probe["dfma_tflops"],
                               "frac": fl / probe["dfma_tflops"], "flops_per_sample": flops_per_sample(n_atoms),
-                              "pipe_frac": ((8.0 + n_atoms) * tile_samples / 32.0 * 2.0) /
+                              "pipe_frac": ((6.0 if n_atoms == 1 else 6.0 + n_atoms) * tile_samples / 32.0 * 2.0) /
                                            (148 * 4 * (clk["sm_mhz"] or 1965.0) * 1e6 * kernel_ms * 1e-3) if n_mols == 0 else None,
-                              "pipe_frac_note": "issued FP64 warp instructions (8+S per sample, nominal sample count) x 2 cycles / SMSP cycles: the binding unit",
+                              "pipe_frac_note": "issued FP64 warp instructions (6 per sample for one absorber, else 6+S; nominal sample count) x 2 cycles / SMSP cycles: the binding unit",
                               "exp_probe_gops": probe["exp_gops"],
                               "exp_frac": tile_samples / (kernel_ms * 1e-3) / 1e9 / probe["exp_gops"]}},
         "kernels_ms": {"column": column_ms, "transit": kernel_ms, "finalize": finalize_ms},

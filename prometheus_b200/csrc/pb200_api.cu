@@ -26,7 +26,8 @@ void launch_number_density_chords(const DevScene*, int scenario, int64_t n, cons
 cudaError_t launch_transit(const DevScene*, int n_atoms, const TransitParams&, cudaStream_t);
 cudaError_t launch_transit_general(const DevScene*, const DevScene& host_copy, const TransitParams&, int sm_count,
                                    cudaStream_t, int* n_launch);
-int transit_wpt_for(int n_atoms);
+int transit_cta_wavelengths(int n_atoms);
+void launch_sigma_phase(const DevScene*, const TransitParams&, cudaStream_t);
 void launch_finalize(const DevScene*, const TransitParams&, int sm_count, cudaStream_t);
 void launch_sigma_lookup(const double*, const double*, int64_t, double, const double*, int64_t, double*, int,
                          cudaStream_t);
@@ -133,11 +134,16 @@ int pb200_create(int device, pb200_ctx** out) {
     if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_scene, sizeof(DevScene));
     if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_oob, sizeof(int));
     if (e == cudaSuccess) e = cudaMemset(c->d_oob, 0, sizeof(int));
-    if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_exp_tab, kExpTabEntries * sizeof(double));
+    if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_exp_tab, (kExpTabEntries + kExpBigEntries) * sizeof(double));
     if (e == cudaSuccess) {
         double tab[kExpTabEntries];
         for (int j = 0; j < kExpTabEntries; ++j) tab[j] = pb_exp_tab_entry((double)exp2l((long double)j / kExpTabEntries), j);
         e = cudaMemcpy(c->d_exp_tab, tab, sizeof tab, cudaMemcpyHostToDevice);
+    }
+    if (e == cudaSuccess) {
+        static double big[kExpBigEntries];
+        for (int j = 0; j < kExpBigEntries; ++j) big[j] = pb_exp_big_entry((double)exp2l((long double)j / kExpBigEntries), j);
+        e = cudaMemcpy(c->d_exp_tab + kExpTabEntries, big, sizeof big, cudaMemcpyHostToDevice);
     }
     if (e != cudaSuccess) {
         int rc = fail(nullptr, PB200_ERR_CUDA, "pb200_create: %s", cudaGetErrorString(e));
@@ -371,7 +377,7 @@ extern "C" int pb200_set_scene(pb200_ctx* c, const pb200_scene* s) {
     wants.push_back({&h.star_shift, (size_t)h.Mp});
     wants.push_back({&h.w_in, (size_t)h.n_orb * h.Mp});
     wants.push_back({&h.ncol, (size_t)n_atoms * h.n_orb * h.Mp});
-    wants.push_back({&h.rec, (size_t)(n_atoms + 1) * h.n_orb * h.Mp});
+    wants.push_back({&h.rec, (size_t)(n_atoms + 3) * h.n_orb * h.Mp});
     wants.push_back({&nmax_d, (size_t)(n_atoms ? n_atoms : 1) * h.n_orb});
     for (int i = 0; i < s->n_scenarios; ++i)
         if (h.scen[i].density_slot >= 0)
@@ -438,11 +444,10 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     const int64_t launches0 = c->launches;
 
     TransitParams prm;
-    prm.ec = pb_exp_consts();
     prm.phase_lo = phase_lo; prm.n_phase = n_phase; prm.wav_lo = wav_lo; prm.n_wav_sel = n_wav_sel;
     const int n_tiles = h.Mp / kChordTile;
-    const int wpt = c->general_path ? 1 : transit_wpt_for(h.n_atoms);
-    const int64_t ctas = ((n_wav_sel + 128 * wpt - 1) / (128 * wpt)) * n_phase;
+    const int cta_wav = c->general_path ? 128 : transit_cta_wavelengths(h.n_atoms);
+    const int64_t ctas = ((n_wav_sel + cta_wav - 1) / cta_wav) * n_phase;
     // many more CTAs than resident slots (~10 per SM) so that the last wave is a small fraction of the
     // run; a CTA keeps at least 4 tiles (1024 chords) to amortise its sigma-lookup prologue
     int64_t want = ((int64_t)c->sm_count * 80 + ctas - 1) / ctas;
@@ -453,10 +458,12 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
 
     const size_t r_bytes = R_in_scratch ? (size_t)((n_out * sizeof(double) + 255) & ~255ll) : 0;
     const size_t part_bytes = prm.n_split > 1 ? (size_t)prm.n_split * n_out * sizeof(double) : 0;
-    int rc = ensure_scratch(c, r_bytes + part_bytes + 256);
+    const size_t nsig_bytes = c->general_path ? 0 : (size_t)h.n_atoms * n_out * sizeof(double);
+    int rc = ensure_scratch(c, r_bytes + part_bytes + nsig_bytes + 256);
     if (rc) return rc;
     prm.R = R_in_scratch ? c->scratch : R_dev;
     prm.partial = reinterpret_cast<double*>(reinterpret_cast<char*>(c->scratch) + r_bytes);
+    prm.nsig = reinterpret_cast<double*>(reinterpret_cast<char*>(c->scratch) + r_bytes + part_bytes);
 
     PB_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
     launch_column(c->d_scene, h.Mp, phase_lo, n_phase, c->d_oob, c->sm_count, c->stream, h.n_mols > 0);
@@ -472,11 +479,12 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
         c->launches += n_launch;
     } else {
         if (h.n_atoms < 1) return fail(c, PB200_ERR_INVALID, "scene has no absorbing constituent");
+        launch_sigma_phase(c->d_scene, prm, c->stream);
         cudaError_t e = launch_transit(c->d_scene, h.n_atoms, prm, c->stream);
         if (e == cudaErrorInvalidValue && h.n_atoms > 12)
             return fail(c, PB200_ERR_UNSUPPORTED, "%d atomic constituents; kernel (c') is compiled for <= 12", h.n_atoms);
         if (e != cudaSuccess) return fail(c, PB200_ERR_CUDA, "transit launch: %s", cudaGetErrorString(e));
-        c->launches += 1;
+        c->launches += 2;
     }
     PB_CUDA(c, cudaEventRecord(c->ev[4], c->stream));
     if (prm.n_split > 1) {

@@ -43,6 +43,14 @@ __device__ __forceinline__ bool pb_blocked(const DevScene& sc, int p, double y, 
     return blocked;
 }
 
+// chord record head for kernel (c'): the weight with the quadratic of the table exp folded in
+// (pb200_math.cuh "Big-table form"): w exp(r c1) ~= w + r (w c1 + r w c2)
+__device__ __forceinline__ void pb_rec_weight(double* rec, double w) {
+    rec[0] = w;
+    rec[1] = w * kExpBigC1;
+    rec[2] = w * kExpBigC2;
+}
+
 // ---- a6 + a7 + a8: density and column density, one warp per chord -----------------------------
 // WRITE_DENSITY: also store n(c, x) of scenarios that carry molecules (needed by kernel (m)).
 __global__ void __launch_bounds__(256)
@@ -59,10 +67,10 @@ column_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, int* 
         if (m >= sc.M) {   // padding of the phase-major rows: zero weight, zero column
             if (lane == 0) {
                 sc.w_in[row] = 0.0;
-                sc.rec[row * (sc.n_atoms + 1)] = 0.0;
+                pb_rec_weight(sc.rec + row * (sc.n_atoms + 3), 0.0);
                 for (int a = 0; a < sc.n_atoms; ++a) {
                     sc.ncol[(int64_t)a * sc.n_orb * sc.Mp + row] = 0.0;
-                    sc.rec[row * (sc.n_atoms + 1) + 1 + a] = 0.0;
+                    sc.rec[row * (sc.n_atoms + 3) + 3 + a] = 0.0;
                 }
             }
             continue;
@@ -75,7 +83,7 @@ column_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, int* 
         if (lane == 0) {
             const double wv = blocked ? 0.0 : sc.w_out[m];
             sc.w_in[row] = wv;
-            sc.rec[row * (sc.n_atoms + 1)] = wv;
+            pb_rec_weight(sc.rec + row * (sc.n_atoms + 3), wv);
         }
         for (int s = 0; s < sc.n_scen; ++s) {
             const DevScenario& S = sc.scen[s];
@@ -114,7 +122,7 @@ column_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, int* 
                     if (C.kind == 0) {   // col = sum_x(n*chi) * delta_x, gasProperties.py:940
                         const double col = (sum * C.chi) * sc.delta_x;
                         sc.ncol[(int64_t)C.atom_index * sc.n_orb * sc.Mp + row] = col;
-                        sc.rec[row * (sc.n_atoms + 1) + 1 + C.atom_index] = col;
+                        sc.rec[row * (sc.n_atoms + 3) + 3 + C.atom_index] = col;
                         // densities are >= 0, so the bit patterns order like the values
                         if (col > 0.0) atomicMax(sc.nmax + (int64_t)C.atom_index * sc.n_orb + p, (unsigned long long)__double_as_longlong(col));
                     }
@@ -200,7 +208,7 @@ column_thread_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase
     const int p = phase_lo + (int)(cid / sc.Mp);
     const int m = (int)(cid % sc.Mp);
     const int64_t row = (int64_t)p * sc.Mp + m;
-    const int R = sc.n_atoms + 1;
+    const int R = sc.n_atoms + 3;
     double* rec = sc.rec + row * R;
     bool blocked = true;
     double y = 0.0, z = 0.0, wv = 0.0;
@@ -213,7 +221,7 @@ column_thread_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase
         wv = blocked ? 0.0 : sc.w_out[m];
     }
     sc.w_in[row] = wv;
-    rec[0] = wv;
+    pb_rec_weight(rec, wv);
     for (int s = 0; s < sc.n_scen; ++s) {
         const DevScenario& S = sc.scen[s];
         // the reference evaluates only unblocked chords (gasProperties.py:1235-1240)
@@ -223,7 +231,7 @@ column_thread_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase
             if (C.kind != 0) continue;
             const double col = (sum * C.chi) * sc.delta_x;                      // gasProperties.py:940
             sc.ncol[(int64_t)C.atom_index * sc.n_orb * sc.Mp + row] = col;
-            rec[1 + C.atom_index] = col;
+            rec[3 + C.atom_index] = col;
             if (col > 0.0)
                 atomicMax(sc.nmax + (int64_t)C.atom_index * sc.n_orb + p, (unsigned long long)__double_as_longlong(col));
         }

@@ -56,10 +56,10 @@ struct DevScene {
     double* ncol;         // [n_atoms][n_orb][Mp]  column densities
     double* density[kMaxScenarios];  // [n_orb][M][n_x] number density of molecular scenarios
     double* fout;         // [1] or [n_wav]  sum of unattenuated flux
-    // chord records of kernel (c'): [n_orb][Mp][n_atoms+1] = {w_in, Ncol_0 .. Ncol_{S-1}}, one TMA
+    // chord records of kernel (c'): [n_orb][Mp][n_atoms+3] = {w_in, w_in c1, w_in c2, Ncol_0 .. Ncol_{S-1}}, one TMA
     // bulk copy per 256-chord tile
     double* rec;
-    const double* exp_tab;   // [256] 2^(j/256), correctly rounded, high word biased (pb_exp_neg_tab)
+    const double* exp_tab;   // [256] 2^(j/256) then [4096] 2^(j/4096), correctly rounded, high words biased (pb200_math.cuh)
     unsigned long long* nmax;   // [n_atoms][n_orb] bit pattern of max_m Ncol (>= 0), set by kernel (a')
 };
 
@@ -71,7 +71,7 @@ struct TransitParams {
     int tiles_per_split;  // kChordTile-chord tiles per split
     double* partial;      // [n_split][n_phase][n_wav_sel] sums of w_in*exp(-tau)  (n_split > 1)
     double* R;            // [n_phase][n_wav_sel] final ratio
-    ExpConsts ec;         // constant-bank operands of the exp (pb_exp_neg_tab)
+    double* nsig;         // [n_atoms][n_phase][n_wav_sel] -sigma_a(p, w) * 4096/ln2 (sigma_phase_kernel)
 };
 
 // ---------------------------------------------------------------------------------------------

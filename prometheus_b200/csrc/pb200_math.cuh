@@ -126,6 +126,48 @@ __device__ __forceinline__ double pb_exp_neg_tab(double u, uint32_t tab_addr) {
     return pb_exp_neg_tab<CLAMP, COPIES>(u, tab_addr, pb_exp_consts());
 }
 
+// ---------------------------------------------------------------------------------------------
+// Big-table form used by kernel (c') (pb200_transit.cu).  The kernel works in SCALED units
+// v = u * 4096/ln2 (the scale is folded into the per-thread -sigma), so
+//     exp(u) = 2^(k/4096) * exp(r ln2/4096),   k = rint(v),  r = v - k,  |r| <= 1/2,
+// with 2^(k/4096) from a 4096-entry shared-memory table (32 KB, one copy: neighbouring lanes hold
+// neighbouring wavelengths, so their k are equal or close and bank conflicts are rare -- ncu) and
+// a QUADRATIC in r: truncation |r^3| (ln2/4096)^3 / 6 <= 1.0e-13, alternating in sign.
+// The chord weight is folded into the polynomial: the record carries {w, w c1, w c2}, so
+//     w exp(u) = T * (w + r (w c1 + r w c2))            2 DFMA + the accumulate DFMA.
+// For one absorber k and r come straight from the product N * nsig:
+//     t = fma(N, nsig, magic); kf = t - magic; r = fma(N, nsig, -kf)    (r exact to 2^-54)
+// => 6 FP64 instructions per chord*lambda sample (S + 6 for S > 1, + 1 integer op when clamped).
+// ---------------------------------------------------------------------------------------------
+constexpr int kExpBigEntries = 4096;
+constexpr int kExpBigShift = 8;                              // 20 - log2(4096)
+constexpr double kExpBigScale = 5909.278887481194;           // 4096 / ln 2
+constexpr double kExpBigC1 = 1.6922538587889289e-04;         // ln 2 / 4096
+constexpr double kExpBigC2 = 1.43186156129301e-08;           // (ln 2 / 4096)^2 / 2
+constexpr unsigned kExpBigClampHi = 0xC14F47D0u;             // high word of -4.1e6 scaled units (tau = 693.8)
+constexpr double kExpBigClampDecision = 690.0 * 5909.278887481194;   // warps that can exceed it take the clamped loop
+
+__host__ __device__ inline double pb_exp_big_entry(double two_pow_frac, int j) {
+    union { double d; uint64_t u; } v;
+    v.d = two_pow_frac;
+    v.u -= (uint64_t)j << (kExpBigShift + 32);
+    return v.d;
+}
+
+// T = 2^(k/4096) = 2^e 2^(j/4096) for k = 4096 e + j >= -4.2e6.  LOP3 + IMAD + LDS.64 + IMAD.
+__device__ __forceinline__ double pb_exp_big_load(uint32_t tab_base, int k) {
+    int t_lo, t_hi;
+    asm volatile("{\n"
+        ".reg .b32 j, a;\n"
+        "and.b32 j, %2, 4095;\n"
+        "mad.lo.u32 a, j, 8, %3;\n"
+        "ld.shared.v2.b32 {%0, %1}, [a];\n"
+        "}\n"
+        : "=r"(t_lo), "=r"(t_hi)
+        : "r"(k), "r"(tab_base));
+    return __hiloint2double(t_hi + (k << kExpBigShift), t_lo);
+}
+
 // exp(a) for |a| <= 700 (same kernel as pb_exp_neg, two-sided); used for 10**v = exp(v ln10) of the
 // molecular tables, where |v| <= 50 keeps the extra rounding of v*ln10 below 1e-14 relative.
 __device__ __forceinline__ double pb_exp(double a) {

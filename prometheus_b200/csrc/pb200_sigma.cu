@@ -175,21 +175,29 @@ __global__ void __launch_bounds__(256) probe_dfma_kernel(double* out, int iters)
     }
     out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
 }
-// exp throughput of the production exp (pb_exp_neg_tab): 8 independent exp per thread and iteration
+// throughput of kernel (c')'s sample (one absorber: 6 FP64 + LOP3 + LEA + LDS.64 + IMAD, see "Big-table
+// form" in pb200_math.cuh) with nothing else around it: 8 independent samples per thread and iteration
 __global__ void __launch_bounds__(256) probe_exp_kernel(double* out, int iters, const double* __restrict__ exp_tab) {
-    __shared__ __align__(16) double etab[kExpTabEntries * kExpTabCopies];
-    for (int i = threadIdx.x; i < kExpTabEntries * kExpTabCopies; i += blockDim.x) etab[i] = exp_tab[i / kExpTabCopies];
+    extern __shared__ __align__(16) double etab[];
+    for (int i = threadIdx.x; i < kExpBigEntries; i += blockDim.x) etab[i] = exp_tab[kExpTabEntries + i];
     __syncthreads();
-    const uint32_t tab_lane = (uint32_t)__cvta_generic_to_shared(etab) + (threadIdx.x & (kExpTabCopies - 1)) * 8u;
-    double t[8], s[8];
+    const uint32_t tab_base = (uint32_t)__cvta_generic_to_shared(etab);
+    double ns[8], s[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) { t[i] = -1e-3 * (threadIdx.x + 1) * (i + 1); s[i] = 0.0; }
+    for (int i = 0; i < 8; ++i) { ns[i] = -1e-3 * (threadIdx.x + 1) * (i + 1); s[i] = 0.0; }
+    double N = 1.0;
+    const double w0 = 0.5, w1 = 0.5 * kExpBigC1, w2 = 0.5 * kExpBigC2;
     for (int it = 0; it < iters; ++it) {
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-            s[i] = fma(0.5, pb_exp_neg_tab<false>(t[i], tab_lane), s[i]);
-            t[i] = __hiloint2double(__double2hiint(t[i]), __double2loint(t[i]) + 64);   // next argument: integer pipe
+            const double t = fma(N, ns[i], kExpMagic);
+            const double r = fma(N, ns[i], -(t - kExpMagic));
+            const double T = pb_exp_big_load(tab_base, __double2loint(t));
+            double q = fma(r, w2, w1);
+            q = fma(q, r, w0);
+            s[i] = fma(T, q, s[i]);
         }
+        N = __hiloint2double(__double2hiint(N), __double2loint(N) + 4096);   // next chord: integer pipe
     }
     double r = 0.0;
 #pragma unroll
@@ -243,7 +251,7 @@ void launch_probe_dfma(double* out, int blocks, int iters, cudaStream_t st) {
     probe_dfma_kernel<<<blocks, 256, 0, st>>>(out, iters);
 }
 void launch_probe_exp(double* out, int blocks, int iters, const double* exp_tab, cudaStream_t st) {
-    probe_exp_kernel<<<blocks, 256, 0, st>>>(out, iters, exp_tab);
+    probe_exp_kernel<<<blocks, 256, kExpBigEntries * sizeof(double), st>>>(out, iters, exp_tab);
 }
 
 }  // namespace pb200

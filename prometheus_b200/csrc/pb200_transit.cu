@@ -4,15 +4,19 @@
 //
 // restates Transit.sumOverChords (gasProperties.py:1205-1258) together with the atomic branch of
 // Atmosphere.getLOSopticalDepth_Batch (:937-954) without ever materialising tau(chord, lambda):
-//   * a thread owns WPT wavelengths of one orbital phase and keeps -sigma_a(p, w) in registers
-//     (looked up once in the prologue: np.interp + 10**v - offset, i.e. n_interp_log :34-51);
-//   * the chord records {w_in, Ncol_0..Ncol_{S-1}} of the phase stream through shared memory in
-//     256-chord tiles, one 1-D TMA bulk copy per tile (cp.async.bulk + mbarrier, double buffered);
-//     every thread of the CTA reads the same record, so the LDS is a broadcast;
-//   * fp64 exp (table-driven, pb_exp_neg_tab: the kernel is bound by the FP64 pipe, so the exp is
-//     built to need as few FP64 instructions as possible), fp64 accumulators; the chord axis is
-//     split over blockIdx.z to get many more CTAs than resident slots (tail effect), partial sums
-//     reduced in a fixed order by finalize_kernel (deterministic).
+//   * sigma_phase_kernel looks up -sigma_a(p, w) * 4096/ln2 once per (phase, wavelength)
+//     (np.interp + 10**v - offset, i.e. n_interp_log :34-51) -- the chord-axis splits of one
+//     (phase, wavelength) tile would otherwise each repeat the binary search;
+//   * a thread of transit_kernel owns WPT wavelengths of one orbital phase and keeps those values
+//     in registers;
+//   * the chord records {w, w c1, w c2, Ncol_0..Ncol_{S-1}} of the phase stream through shared
+//     memory in 256-chord tiles, one 1-D TMA bulk copy per tile (cp.async.bulk + mbarrier, double
+//     buffered); every thread of the CTA reads the same record, so the LDS is a broadcast;
+//   * fp64 exp (table-driven, see "Big-table form" in pb200_math.cuh: the kernel is bound by the
+//     FP64 pipe and by the instructions issued next to it, so the exp is built to need as few of
+//     both as possible: 6 FP64 + 3 integer + 1 LDS per sample for one absorber), fp64
+//     accumulators; the chord axis is split over blockIdx.z to get many more CTAs than resident
+//     slots (tail effect), partial sums reduced in a fixed order by finalize_kernel (deterministic).
 // The chord-level early-out (w_in == 0: blocked/padding) is CTA-uniform.
 #include <cstdlib>
 
@@ -20,7 +24,7 @@
 
 namespace pb200 {
 
-constexpr int kTransitThreads = 128;
+constexpr int kRecExtra = 3;           // {w, w c1, w c2} in front of the S column densities
 
 // ---- mbarrier / TMA bulk-copy wrappers (PTX ISA 8.x, sm_90+) -----------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -62,51 +66,83 @@ __device__ __forceinline__ void lds_v2f64(uint32_t addr, double& a, double& b) {
     asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(a), "=d"(b) : "r"(addr));
 }
 
+// (b1) for the whole output tile: nsig[a][p][w] = -sigma_a(p, lambda_w) * 4096/ln2
+__global__ void __launch_bounds__(256) sigma_phase_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
+    const DevScene& sc = *scp;
+    const int64_t wi = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (wi >= prm.n_wav_sel) return;
+    const int pi = blockIdx.y, p = prm.phase_lo + pi;
+    const double lam = __ldg(sc.wavelength + prm.wav_lo + wi);
+    int a = 0;
+    for (int k = 0; k < sc.n_cons; ++k) {
+        const DevConstituent& C = sc.cons[k];
+        if (C.kind != 0) continue;
+        const double shift = __ldg(sc.scen[C.scenario].shift + p);
+        const double v = pb_interp_log(C.tab_x, C.tab_y, C.n_tab, shift * lam, C.offset);   // :917, :950-951
+        prm.nsig[((int64_t)a * prm.n_phase + pi) * prm.n_wav_sel + wi] = -v * kExpBigScale;
+        ++a;
+    }
+}
+
 // One 256-chord tile: acc[j] += w_m * exp(-sum_a N_a(m) sigma_a(j)) for the thread's WPT wavelengths.
 // `stage` is the shared-window address of the tile's records (explicit ld.shared: no generic->shared
 // address conversion inside the loop).
 template <int S, int WPT, bool CLAMP>
 __device__ __forceinline__ void transit_tile(uint32_t stage, const double (&nsig)[S][WPT], double (&acc)[WPT],
-                                             uint32_t tab_lane, const ExpConsts& ec) {
-    constexpr uint32_t kRecBytes = (S + 1) * sizeof(double);
+                                             uint32_t tab_base) {
+    constexpr uint32_t kRecBytes = (S + kRecExtra) * sizeof(double);
 #pragma unroll 2
     for (int m = 0; m < kChordTile; ++m) {
         const uint32_t rec = stage + m * kRecBytes;
-        double wv, N[S];
+        double w0, w1, w2, N[S];
         if constexpr (S == 1) {
-            lds_v2f64(rec, wv, N[0]);                                              // broadcast LDS.128
+            lds_v2f64(rec, w0, w1);                                                // broadcast LDS.128 x 2
+            lds_v2f64(rec + 16, w2, N[0]);
         } else {
-            wv = lds_f64(rec);
+            w0 = lds_f64(rec); w1 = lds_f64(rec + 8); w2 = lds_f64(rec + 16);
 #pragma unroll
-            for (int a = 0; a < S; ++a) N[a] = lds_f64(rec + 8 + 8 * a);
+            for (int a = 0; a < S; ++a) N[a] = lds_f64(rec + 24 + 8 * a);
         }
         // blocked chord or padding: F_in = 0 (gasProperties.py:1233); CTA-uniform, integer test
-        if ((__double2hiint(wv) | __double2loint(wv)) == 0) continue;
+        if ((__double2hiint(w0) | __double2loint(w0)) == 0) continue;
 #pragma unroll
         for (int j = 0; j < WPT; ++j) {
-            double u = N[0] * nsig[0][j];                                          // -tau, :954
+            double t, r;
+            if constexpr (S == 1 && !CLAMP) {
+                t = fma(N[0], nsig[0][j], kExpMagic);                              // -tau in scaled units, :954
+                r = fma(N[0], nsig[0][j], -(t - kExpMagic));
+            } else {
+                double v = N[0] * nsig[0][j];
 #pragma unroll
-            for (int a = 1; a < S; ++a) u = fma(N[a], nsig[a][j], u);
-            acc[j] = fma(wv, pb_exp_neg_tab<CLAMP>(u, tab_lane, ec), acc[j]);     // :1241, :1244/:1255
+                for (int a = 1; a < S; ++a) v = fma(N[a], nsig[a][j], v);
+                if (CLAMP) {   // tau <= 693.8 keeps 2^e normal; exp(-693.8) w is < 1e-301
+                    const unsigned hi = min((unsigned)__double2hiint(v), kExpBigClampHi);
+                    v = __hiloint2double((int)hi, __double2loint(v));
+                }
+                t = v + kExpMagic;
+                r = v - (t - kExpMagic);
+            }
+            const double T = pb_exp_big_load(tab_base, __double2loint(t));
+            double q = fma(r, w2, w1);
+            q = fma(q, r, w0);                                                     // w exp(r ln2/4096)
+            acc[j] = fma(T, q, acc[j]);                                            // :1241, :1244/:1255
         }
     }
 }
 
-// S atomic constituents (compile time), WPT wavelengths per thread
-template <int S, int WPT>
-__global__ void __launch_bounds__(kTransitThreads)
+// S atomic constituents (compile time), WPT wavelengths per thread, THREADS threads per CTA
+template <int S, int WPT, int THREADS>
+__global__ void __launch_bounds__(THREADS)
 transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
     const DevScene& sc = *scp;
-    // shared memory: exp table [64][16] | stage 0 records | stage 1 records; a record is
-    // {w_in, Ncol_0 .. Ncol_{S-1}}, a stage holds kChordTile records
+    // shared memory: exp table [4096] | stage 0 records | stage 1 records; a stage holds kChordTile records
     extern __shared__ __align__(128) double smem[];
     __shared__ uint64_t full_bar[2];
-    constexpr int R = S + 1;
-    constexpr int kTabDoubles = kExpTabEntries * kExpTabCopies;
+    constexpr int R = S + kRecExtra;
     constexpr int kStageDoubles = R * kChordTile;
     constexpr uint32_t kStageBytes = kStageDoubles * sizeof(double);
     double* etab = smem;
-    double* stages = smem + kTabDoubles;
+    double* stages = smem + kExpBigEntries;
 
     const int tid = threadIdx.x;
     const int p = prm.phase_lo + blockIdx.y;
@@ -121,9 +157,7 @@ transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
         mbar_init(&full_bar[1], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    for (int i = tid; i < kTabDoubles; i += kTransitThreads) etab[i] = __ldg(sc.exp_tab + (i / kExpTabCopies));
     __syncthreads();
-
     const double* rec_row = sc.rec + ((int64_t)p * sc.Mp + (int64_t)tile0 * kChordTile) * R;
     auto issue = [&](int tile, int stage) {
         mbar_expect_tx(&full_bar[stage], kStageBytes);
@@ -131,32 +165,27 @@ transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
                      &full_bar[stage]);
     };
     if (tid == 0 && n_tiles > 0) issue(0, 0);
+    {   // the exp table: 32 KB from L2, 16-byte loads
+        const double2* src = reinterpret_cast<const double2*>(sc.exp_tab + kExpTabEntries);
+        double2* dst = reinterpret_cast<double2*>(etab);
+        for (int i = tid; i < kExpBigEntries / 2; i += THREADS) dst[i] = __ldg(src + i);
+    }
 
-    // ---- prologue: -sigma_a(p, w) for this thread's wavelengths (kernel (b1) inlined) -----------
-    const int64_t w_base = prm.wav_lo + (int64_t)blockIdx.x * (kTransitThreads * WPT) + tid;
+    // ---- prologue: -sigma_a(p, w) 4096/ln2 for this thread's wavelengths ---------------------------
+    const int64_t w_base = (int64_t)blockIdx.x * (THREADS * WPT) + tid;     // relative to wav_lo
     double nsig[S][WPT];
     double acc[WPT];
     bool bad = false;   // NaN cross-section (NaN wavelength): the reference propagates NaN into R
 #pragma unroll
     for (int j = 0; j < WPT; ++j) {
         acc[j] = 0.0;
-        const int64_t w = w_base + (int64_t)j * kTransitThreads;
-        const bool live = w < prm.wav_lo + prm.n_wav_sel;
-        const double lam = live ? __ldg(sc.wavelength + w) : 0.0;
-        int a = 0;
-        for (int k = 0; k < sc.n_cons && a < S; ++k) {
-            const DevConstituent& C = sc.cons[k];
-            if (C.kind != 0) continue;
-            double v = 0.0;
-            if (live) {
-                const double shift = __ldg(sc.scen[C.scenario].shift + p);
-                v = pb_interp_log(C.tab_x, C.tab_y, C.n_tab, shift * lam, C.offset);   // :917, :950-951
-                bad |= (v != v);
-            }
+        const int64_t w = w_base + (int64_t)j * THREADS;
+        const bool live = w < prm.n_wav_sel;
 #pragma unroll
-            for (int aa = 0; aa < S; ++aa)
-                if (aa == a) nsig[aa][j] = -v;
-            ++a;
+        for (int a = 0; a < S; ++a) {
+            const double v = live ? __ldg(prm.nsig + ((int64_t)a * prm.n_phase + blockIdx.y) * prm.n_wav_sel + w) : 0.0;
+            bad |= (v != v);
+            nsig[a][j] = v;
         }
     }
 
@@ -169,20 +198,21 @@ transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
 #pragma unroll
         for (int a = 0; a < S; ++a)
             tmax = fma(__longlong_as_double((long long)__ldg(sc.nmax + (int64_t)a * sc.n_orb + p)), -nsig[a][j], tmax);
-        clamp |= !(tmax < kExpClampTau);   // NaN -> clamped variant (harmless)
+        clamp |= !(tmax < kExpBigClampDecision);   // NaN -> clamped variant (harmless)
     }
     clamp = __any_sync(0xffffffffu, clamp);
+    __syncthreads();   // exp table complete
 
     // ---- main loop over chord tiles -----------------------------------------------------------
-    const uint32_t tab_lane = smem_u32(etab) + (tid & (kExpTabCopies - 1)) * (uint32_t)sizeof(double);
+    const uint32_t tab_base = smem_u32(etab);
     const uint32_t stages_addr = smem_u32(stages);
     for (int t = 0; t < n_tiles; ++t) {
         const int stage = t & 1;
         if (tid == 0 && t + 1 < n_tiles) issue(t + 1, stage ^ 1);
         mbar_wait(&full_bar[stage], (t >> 1) & 1);
         const uint32_t sw = stages_addr + stage * kStageBytes;
-        if (clamp) transit_tile<S, WPT, true>(sw, nsig, acc, tab_lane, pb_exp_consts());
-        else transit_tile<S, WPT, false>(sw, nsig, acc, tab_lane, pb_exp_consts());
+        if (clamp) transit_tile<S, WPT, true>(sw, nsig, acc, tab_base);
+        else transit_tile<S, WPT, false>(sw, nsig, acc, tab_base);
         __syncthreads();   // stage may be refilled by the producer in the next iteration
     }
 
@@ -190,9 +220,9 @@ transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
     const double fout = (prm.n_split == 1) ? sc.fout[0] : 1.0;
 #pragma unroll
     for (int j = 0; j < WPT; ++j) {
-        const int64_t w = w_base + (int64_t)j * kTransitThreads;
-        if (w >= prm.wav_lo + prm.n_wav_sel) continue;
-        const int64_t o = (int64_t)blockIdx.y * prm.n_wav_sel + (w - prm.wav_lo);
+        const int64_t w = w_base + (int64_t)j * THREADS;
+        if (w >= prm.n_wav_sel) continue;
+        const int64_t o = (int64_t)blockIdx.y * prm.n_wav_sel + w;
         double v = acc[j];
         if (bad) {
 #pragma unroll
@@ -216,47 +246,58 @@ __global__ void finalize_kernel(const DevScene* __restrict__ scp, const TransitP
     }
 }
 
-template <int S, int WPT>
+template <int S, int WPT, int THREADS>
 static cudaError_t launch_one(const DevScene* d_scene, const TransitParams& prm, cudaStream_t st) {
-    const size_t smem = (kExpTabEntries * kExpTabCopies + 2 * (S + 1) * kChordTile) * sizeof(double);
-    auto kern = transit_kernel<S, WPT>;
-    if (smem > 48 * 1024) {
+    const size_t smem = (kExpBigEntries + 2 * (S + kRecExtra) * kChordTile) * sizeof(double);
+    auto kern = transit_kernel<S, WPT, THREADS>;
+    {   // dynamic + static shared memory is always above the 48 KB default limit
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
     }
-    const int64_t per_block = (int64_t)kTransitThreads * WPT;
+    const int64_t per_block = (int64_t)THREADS * WPT;
     dim3 grid((unsigned)((prm.n_wav_sel + per_block - 1) / per_block), (unsigned)prm.n_phase, (unsigned)prm.n_split);
-    kern<<<grid, kTransitThreads, smem, st>>>(d_scene, prm);
+    kern<<<grid, THREADS, smem, st>>>(d_scene, prm);
     return cudaGetLastError();
 }
 
-static int env_wpt() {
-    static const int v = [] { const char* e = getenv("PB200_WPT"); return e ? atoi(e) : 0; }();
-    return v;
+static int env_int(const char* name) {
+    const char* e = getenv(name);
+    return e ? atoi(e) : 0;
 }
 
-int transit_wpt_for(int n_atoms) {
-    const int forced = env_wpt();
-    if (n_atoms <= 4) return (forced == 4 || forced == 8) ? forced : 8;
-    return 2;
+// CTA shape: 256 threads x WPT wavelengths, WPT = 8 for 1-2 absorbers, 4 for 3-4, 2 above (register
+// budget: 2 S WPT + temporaries must leave >= 2 CTAs per SM).  PB200_THREADS=128 selects 128-thread
+// CTAs for 1-2 absorbers (tuning experiments only).
+static int transit_threads() {
+    static const int v = env_int("PB200_THREADS");
+    return v == 128 ? 128 : 256;
+}
+
+int transit_cta_wavelengths(int n_atoms) {
+    return n_atoms <= 2 ? transit_threads() * 8 : n_atoms <= 4 ? 256 * 4 : 256 * 2;
+}
+
+void launch_sigma_phase(const DevScene* d_scene, const TransitParams& prm, cudaStream_t st) {
+    dim3 grid((unsigned)((prm.n_wav_sel + 255) / 256), (unsigned)prm.n_phase);
+    sigma_phase_kernel<<<grid, 256, 0, st>>>(d_scene, prm);
 }
 
 // returns cudaSuccess, or cudaErrorInvalidValue when n_atoms is outside the compiled range
 cudaError_t launch_transit(const DevScene* d_scene, int n_atoms, const TransitParams& prm, cudaStream_t st) {
-    const bool w8 = transit_wpt_for(n_atoms) == 8;
+    const bool t256 = transit_threads() == 256;
     switch (n_atoms) {
-        case 1: return w8 ? launch_one<1, 8>(d_scene, prm, st) : launch_one<1, 4>(d_scene, prm, st);
-        case 2: return w8 ? launch_one<2, 8>(d_scene, prm, st) : launch_one<2, 4>(d_scene, prm, st);
-        case 3: return w8 ? launch_one<3, 8>(d_scene, prm, st) : launch_one<3, 4>(d_scene, prm, st);
-        case 4: return w8 ? launch_one<4, 8>(d_scene, prm, st) : launch_one<4, 4>(d_scene, prm, st);
-        case 5: return launch_one<5, 2>(d_scene, prm, st);
-        case 6: return launch_one<6, 2>(d_scene, prm, st);
-        case 7: return launch_one<7, 2>(d_scene, prm, st);
-        case 8: return launch_one<8, 2>(d_scene, prm, st);
-        case 9: return launch_one<9, 2>(d_scene, prm, st);
-        case 10: return launch_one<10, 2>(d_scene, prm, st);
-        case 11: return launch_one<11, 2>(d_scene, prm, st);
-        case 12: return launch_one<12, 2>(d_scene, prm, st);
+        case 1: return t256 ? launch_one<1, 8, 256>(d_scene, prm, st) : launch_one<1, 8, 128>(d_scene, prm, st);
+        case 2: return t256 ? launch_one<2, 8, 256>(d_scene, prm, st) : launch_one<2, 8, 128>(d_scene, prm, st);
+        case 3: return launch_one<3, 4, 256>(d_scene, prm, st);
+        case 4: return launch_one<4, 4, 256>(d_scene, prm, st);
+        case 5: return launch_one<5, 2, 256>(d_scene, prm, st);
+        case 6: return launch_one<6, 2, 256>(d_scene, prm, st);
+        case 7: return launch_one<7, 2, 256>(d_scene, prm, st);
+        case 8: return launch_one<8, 2, 256>(d_scene, prm, st);
+        case 9: return launch_one<9, 2, 256>(d_scene, prm, st);
+        case 10: return launch_one<10, 2, 256>(d_scene, prm, st);
+        case 11: return launch_one<11, 2, 256>(d_scene, prm, st);
+        case 12: return launch_one<12, 2, 256>(d_scene, prm, st);
         default: return cudaErrorInvalidValue;
     }
 }
