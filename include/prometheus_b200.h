@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define PB200_ABI_VERSION 1
+#define PB200_ABI_VERSION 2
 
 typedef enum {
     PB200_OK = 0,
@@ -120,6 +120,9 @@ typedef struct {
     double download_ms;          /* D2H of R                                                 */
     int64_t launches;            /* kernels launched by the call                             */
     int64_t samples;             /* chord*lambda samples of the call (nominal)               */
+    int64_t executed_samples;    /* samples kernel (c') evaluated: transparent chords (tau <
+                                    2^-54 at every wavelength, exp(-tau) == 1.0) and blocked
+                                    chords are summed without an exp; -1 = not yet known     */
 } pb200_timing;
 
 typedef struct pb200_ctx pb200_ctx;

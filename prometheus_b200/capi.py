@@ -12,7 +12,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libprometheus_b200.so")
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 c_double_p = C.POINTER(C.c_double)
 
@@ -70,7 +70,7 @@ class Scene(C.Structure):
 class Timing(C.Structure):
     _fields_ = [("upload_ms", C.c_double), ("column_ms", C.c_double), ("transit_ms", C.c_double),
                 ("finalize_ms", C.c_double), ("download_ms", C.c_double),
-                ("launches", C.c_int64), ("samples", C.c_int64)]
+                ("launches", C.c_int64), ("samples", C.c_int64), ("executed_samples", C.c_int64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

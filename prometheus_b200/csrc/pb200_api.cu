@@ -28,6 +28,7 @@ cudaError_t launch_transit_general(const DevScene*, const DevScene& host_copy, c
                                    cudaStream_t, int* n_launch);
 int transit_cta_wavelengths(int n_atoms);
 void launch_sigma_phase(const DevScene*, const TransitParams&, cudaStream_t);
+void launch_compact(const DevScene*, int phase_lo, int n_phase, cudaStream_t);
 void launch_finalize(const DevScene*, const TransitParams&, int sm_count, cudaStream_t);
 void launch_sigma_lookup(const double*, const double*, int64_t, double, const double*, int64_t, double*, int,
                          cudaStream_t);
@@ -68,7 +69,8 @@ struct pb200_ctx {
     size_t darena_bytes = 0;     // both arenas are grow-only: repeated pb200_set_scene calls do not cudaMalloc
     double* scratch = nullptr;   // partial sums / R tile / temporary outputs
     size_t scratch_bytes = 0;
-    int* d_oob = nullptr;
+    int* d_oob = nullptr;        // 16 bytes: [0] out-of-grid flag (int), [8..16) active chord records of the last run
+    int64_t last_n_wav_sel = 0;
     double* d_exp_tab = nullptr; // 2^(j/64), j < 64
     cudaEvent_t ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // 6,7: scene upload
     pb200_timing last = {};
@@ -132,8 +134,8 @@ int pb200_create(int device, pb200_ctx** out) {
     if (e == cudaSuccess) { c->own_stream = true; e = cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device); }
     for (int i = 0; i < 8 && e == cudaSuccess; ++i) e = cudaEventCreate(&c->ev[i]);
     if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_scene, sizeof(DevScene));
-    if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_oob, sizeof(int));
-    if (e == cudaSuccess) e = cudaMemset(c->d_oob, 0, sizeof(int));
+    if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_oob, 16);   // [0] out-of-grid flag, [8..16) active records of the run
+    if (e == cudaSuccess) e = cudaMemset(c->d_oob, 0, 16);
     if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_exp_tab, (kExpTabEntries + kExpBigEntries) * sizeof(double));
     if (e == cudaSuccess) {
         double tab[kExpTabEntries];
@@ -372,13 +374,16 @@ extern "C" int pb200_set_scene(pb200_ctx* c, const pb200_scene* s) {
     const bool fstar_per_chord = h.n_fstar > 0 && h.vsini != 0.0;
     struct Want { double** p; size_t n; };
     std::vector<Want> wants;
-    double* nmax_d = nullptr;
+    double *nmax_d = nullptr, *smax_d = nullptr, *nact_d = nullptr;
     wants.push_back({&h.w_out, (size_t)h.Mp});
     wants.push_back({&h.star_shift, (size_t)h.Mp});
     wants.push_back({&h.w_in, (size_t)h.n_orb * h.Mp});
     wants.push_back({&h.ncol, (size_t)n_atoms * h.n_orb * h.Mp});
     wants.push_back({&h.rec, (size_t)(n_atoms + 3) * h.n_orb * h.Mp});
     wants.push_back({&nmax_d, (size_t)(n_atoms ? n_atoms : 1) * h.n_orb});
+    wants.push_back({&smax_d, (size_t)(n_atoms ? n_atoms : 1) * h.n_orb});
+    wants.push_back({&nact_d, (size_t)(h.n_orb + 1) / 2});
+    wants.push_back({&h.w0, (size_t)h.n_orb});
     for (int i = 0; i < s->n_scenarios; ++i)
         if (h.scen[i].density_slot >= 0)
             wants.push_back({&h.density[h.scen[i].density_slot], (size_t)h.n_orb * h.M * h.n_x});
@@ -400,6 +405,9 @@ extern "C" int pb200_set_scene(pb200_ctx* c, const pb200_scene* s) {
     }
     h.exp_tab = c->d_exp_tab;
     h.nmax = reinterpret_cast<unsigned long long*>(nmax_d);
+    h.smax = reinterpret_cast<unsigned long long*>(smax_d);
+    h.n_act = reinterpret_cast<int*>(nact_d);
+    h.stat = reinterpret_cast<unsigned long long*>(c->d_oob);
     PB_CUDA(c, cudaMemsetAsync(nmax_d, 0, (size_t)(n_atoms ? n_atoms : 1) * h.n_orb * sizeof(double), c->stream));
     c->general_path = (n_mols > 0) || fstar_per_chord;
     h.fout_per_wav = fstar_per_chord ? 1 : 0;
@@ -466,8 +474,19 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     prm.nsig = reinterpret_cast<double*>(reinterpret_cast<char*>(c->scratch) + r_bytes + part_bytes);
 
     PB_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
+    if (!c->general_path) {   // sigma(p, w) of the tile and its per-phase maxima, needed by the culling below
+        if (h.n_atoms < 1) return fail(c, PB200_ERR_INVALID, "scene has no absorbing constituent");
+        PB_CUDA(c, cudaMemsetAsync(h.smax, 0, (size_t)h.n_atoms * h.n_orb * sizeof(double), c->stream));
+        PB_CUDA(c, cudaMemsetAsync(reinterpret_cast<char*>(c->d_oob) + 8, 0, 8, c->stream));
+        launch_sigma_phase(c->d_scene, prm, c->stream);
+        c->launches += 1;
+    }
     launch_column(c->d_scene, h.Mp, phase_lo, n_phase, c->d_oob, c->sm_count, c->stream, h.n_mols > 0);
     c->launches += 1;
+    if (!c->general_path) {   // chord records of kernel (c'), transparent chords culled
+        launch_compact(c->d_scene, phase_lo, n_phase, c->stream);
+        c->launches += 1;
+    }
     PB_CUDA(c, cudaGetLastError());
     PB_CUDA(c, cudaEventRecord(c->ev[3], c->stream));
     if (c->general_path) {
@@ -478,13 +497,11 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
         if (e != cudaSuccess) return fail(c, PB200_ERR_CUDA, "transit (general) launch: %s", cudaGetErrorString(e));
         c->launches += n_launch;
     } else {
-        if (h.n_atoms < 1) return fail(c, PB200_ERR_INVALID, "scene has no absorbing constituent");
-        launch_sigma_phase(c->d_scene, prm, c->stream);
         cudaError_t e = launch_transit(c->d_scene, h.n_atoms, prm, c->stream);
         if (e == cudaErrorInvalidValue && h.n_atoms > 12)
             return fail(c, PB200_ERR_UNSUPPORTED, "%d atomic constituents; kernel (c') is compiled for <= 12", h.n_atoms);
         if (e != cudaSuccess) return fail(c, PB200_ERR_CUDA, "transit launch: %s", cudaGetErrorString(e));
-        c->launches += 2;
+        c->launches += 1;
     }
     PB_CUDA(c, cudaEventRecord(c->ev[4], c->stream));
     if (prm.n_split > 1) {
@@ -497,6 +514,8 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     c->last.upload_ms = c->upload_ms;
     c->last.launches = c->launches - launches0;
     c->last.samples = (int64_t)n_phase * h.M * n_wav_sel;
+    c->last.executed_samples = c->general_path ? c->last.samples : -1;   // known after the next synchronisation
+    c->last_n_wav_sel = n_wav_sel;
     return PB200_OK;
 }
 
@@ -516,9 +535,11 @@ int collect_timing(pb200_ctx* c) {
 }
 
 int check_oob(pb200_ctx* c) {
-    int flag = 0;
-    PB_CUDA(c, cudaMemcpyAsync(&flag, c->d_oob, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    unsigned long long st[2] = {0, 0};
+    PB_CUDA(c, cudaMemcpyAsync(st, c->d_oob, sizeof st, cudaMemcpyDeviceToHost, c->stream));
     PB_CUDA(c, cudaStreamSynchronize(c->stream));
+    const int flag = (int)(st[0] & 0xffffffffull);
+    if (c->last.executed_samples < 0) c->last.executed_samples = (int64_t)st[1] * c->last_n_wav_sel;
     if (flag) {
         PB_CUDA(c, cudaMemsetAsync(c->d_oob, 0, sizeof(int), c->stream));
         return fail(c, PB200_ERR_BOUNDS, "tabulated density queried outside its grid (the reference raises ValueError)");

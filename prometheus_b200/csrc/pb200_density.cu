@@ -43,14 +43,6 @@ __device__ __forceinline__ bool pb_blocked(const DevScene& sc, int p, double y, 
     return blocked;
 }
 
-// chord record head for kernel (c'): the weight with the quadratic of the table exp folded in
-// (pb200_math.cuh "Big-table form"): w exp(r c1) ~= w + r (w c1 + r w c2)
-__device__ __forceinline__ void pb_rec_weight(double* rec, double w) {
-    rec[0] = w;
-    rec[1] = w * kExpBigC1;
-    rec[2] = w * kExpBigC2;
-}
-
 // ---- a6 + a7 + a8: density and column density, one warp per chord -----------------------------
 // WRITE_DENSITY: also store n(c, x) of scenarios that carry molecules (needed by kernel (m)).
 __global__ void __launch_bounds__(256)
@@ -67,11 +59,7 @@ column_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, int* 
         if (m >= sc.M) {   // padding of the phase-major rows: zero weight, zero column
             if (lane == 0) {
                 sc.w_in[row] = 0.0;
-                pb_rec_weight(sc.rec + row * (sc.n_atoms + 3), 0.0);
-                for (int a = 0; a < sc.n_atoms; ++a) {
-                    sc.ncol[(int64_t)a * sc.n_orb * sc.Mp + row] = 0.0;
-                    sc.rec[row * (sc.n_atoms + 3) + 3 + a] = 0.0;
-                }
+                for (int a = 0; a < sc.n_atoms; ++a) sc.ncol[(int64_t)a * sc.n_orb * sc.Mp + row] = 0.0;
             }
             continue;
         }
@@ -83,7 +71,6 @@ column_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, int* 
         if (lane == 0) {
             const double wv = blocked ? 0.0 : sc.w_out[m];
             sc.w_in[row] = wv;
-            pb_rec_weight(sc.rec + row * (sc.n_atoms + 3), wv);
         }
         for (int s = 0; s < sc.n_scen; ++s) {
             const DevScenario& S = sc.scen[s];
@@ -122,7 +109,6 @@ column_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, int* 
                     if (C.kind == 0) {   // col = sum_x(n*chi) * delta_x, gasProperties.py:940
                         const double col = (sum * C.chi) * sc.delta_x;
                         sc.ncol[(int64_t)C.atom_index * sc.n_orb * sc.Mp + row] = col;
-                        sc.rec[row * (sc.n_atoms + 3) + 3 + C.atom_index] = col;
                         // densities are >= 0, so the bit patterns order like the values
                         if (col > 0.0) atomicMax(sc.nmax + (int64_t)C.atom_index * sc.n_orb + p, (unsigned long long)__double_as_longlong(col));
                     }
@@ -208,8 +194,6 @@ column_thread_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase
     const int p = phase_lo + (int)(cid / sc.Mp);
     const int m = (int)(cid % sc.Mp);
     const int64_t row = (int64_t)p * sc.Mp + m;
-    const int R = sc.n_atoms + 3;
-    double* rec = sc.rec + row * R;
     bool blocked = true;
     double y = 0.0, z = 0.0, wv = 0.0;
     if (m < sc.M) {
@@ -221,7 +205,6 @@ column_thread_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase
         wv = blocked ? 0.0 : sc.w_out[m];
     }
     sc.w_in[row] = wv;
-    pb_rec_weight(rec, wv);
     for (int s = 0; s < sc.n_scen; ++s) {
         const DevScenario& S = sc.scen[s];
         // the reference evaluates only unblocked chords (gasProperties.py:1235-1240)
@@ -231,9 +214,88 @@ column_thread_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase
             if (C.kind != 0) continue;
             const double col = (sum * C.chi) * sc.delta_x;                      // gasProperties.py:940
             sc.ncol[(int64_t)C.atom_index * sc.n_orb * sc.Mp + row] = col;
-            rec[3 + C.atom_index] = col;
             if (col > 0.0)
                 atomicMax(sc.nmax + (int64_t)C.atom_index * sc.n_orb + p, (unsigned long long)__double_as_longlong(col));
+        }
+    }
+}
+
+// ---- chord records of kernel (c'), transparent chords culled ------------------------------------
+// One CTA per phase walks the phase's chords in order.  A chord is
+//   * dead        if w_in == 0 (blocked by a body, or row padding): it contributes nothing;
+//   * transparent if sum_a Ncol_a * max_w sigma_a(p, w) < 2^-54: at every wavelength of the run
+//                 exp(-tau) rounds to exactly 1.0 (as it does in the reference), so the chord adds exactly
+//                 w_in to F_in -- these weights are summed once into w0[p];
+//   * active      otherwise: it gets a record {w, w c1, w c2, Ncol_0..} (the quadratic of the table exp
+//                 folded into the weight, pb200_math.cuh "Big-table form": w exp(r c1) ~= w + r (w c1 + r w c2)).
+// Active records are packed in chord order at the front of the phase's rec row (block-wide exclusive
+// scan, deterministic), the last tile is padded with all-zero records, n_act[p] = number of tiles.
+constexpr int kCompactThreads = 1024;
+__global__ void __launch_bounds__(kCompactThreads) compact_kernel(const DevScene* __restrict__ scp, int phase_lo) {
+    const DevScene& sc = *scp;
+    const int p = phase_lo + blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int S = sc.n_atoms, R = S + 3;
+    __shared__ double s_smax[16];
+    __shared__ int s_warp[32];
+    __shared__ double s_part[32];
+    __shared__ int s_base;
+    if (tid < S) {
+        const double v = __longlong_as_double((long long)sc.smax[(int64_t)tid * sc.n_orb + p]);
+        s_smax[tid] = (v >= 0.0) ? v : __longlong_as_double(0x7ff0000000000000ll);   // negative or NaN: never cull
+    }
+    if (tid == 0) s_base = 0;
+    __syncthreads();
+    const int64_t row0 = (int64_t)p * sc.Mp;
+    double* rec_row = sc.rec + row0 * R;
+    double w0 = 0.0;
+    for (int m0 = 0; m0 < sc.Mp; m0 += kCompactThreads) {
+        const int m = m0 + tid;
+        double w = 0.0, bound = 0.0;
+        if (m < sc.Mp) {
+            w = sc.w_in[row0 + m];
+            for (int a = 0; a < S; ++a) bound = fma(sc.ncol[(int64_t)a * sc.n_orb * sc.Mp + row0 + m], s_smax[a], bound);
+        }
+        const bool alive = (w != 0.0);
+        const bool active = alive && !(bound < 5.5511151231257827e-17);          // 2^-54; NaN -> active
+        if (alive && !active) w0 += w;
+        const unsigned bal = __ballot_sync(0xffffffffu, active);
+        if (lane == 0) s_warp[wid] = __popc(bal);
+        __syncthreads();
+        if (wid == 0) {   // exclusive scan of the 32 warp counts
+            const int c = s_warp[lane];
+            int x = c;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int y = __shfl_up_sync(0xffffffffu, x, d);
+                if (lane >= d) x += y;
+            }
+            s_warp[lane] = x - c;
+            if (lane == 31) s_part[0] = (double)x;   // chunk total (exact: <= 1024)
+        }
+        __syncthreads();
+        const int base = s_base;
+        if (active) {
+            double* r = rec_row + (int64_t)(base + s_warp[wid] + __popc(bal & ((1u << lane) - 1u))) * R;
+            r[0] = w; r[1] = w * kExpBigC1; r[2] = w * kExpBigC2;
+            for (int a = 0; a < S; ++a) r[3 + a] = sc.ncol[(int64_t)a * sc.n_orb * sc.Mp + row0 + m];
+        }
+        __syncthreads();
+        if (tid == 0) s_base = base + (int)s_part[0];
+        __syncthreads();
+    }
+    const int n_rec = s_base;
+    const int n_tiles = (n_rec + kChordTile - 1) / kChordTile;
+    for (int i = n_rec * R + tid; i < n_tiles * kChordTile * R; i += kCompactThreads) rec_row[i] = 0.0;   // padding
+    // sum of the transparent weights, fixed order
+    w0 = pb_warp_sum(w0);
+    if (lane == 0) s_part[wid] = w0;
+    __syncthreads();
+    if (wid == 0) {
+        const double t = pb_warp_sum(s_part[lane]);
+        if (lane == 0) {
+            sc.w0[p] = t;
+            sc.n_act[p] = n_tiles;
+            atomicAdd(sc.stat + 1, (unsigned long long)n_tiles * kChordTile);
         }
     }
 }
@@ -331,6 +393,9 @@ void launch_column(const DevScene* d_scene, int Mp, int phase_lo, int n_phase, i
         const int64_t n = (int64_t)n_phase * Mp;
         column_thread_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(d_scene, phase_lo, n_phase, oob);
     }
+}
+void launch_compact(const DevScene* d_scene, int phase_lo, int n_phase, cudaStream_t st) {
+    compact_kernel<<<n_phase, kCompactThreads, 0, st>>>(d_scene, phase_lo);
 }
 void launch_number_density_grid(const DevScene* d_scene, int64_t n_chords, int scenario, double* out,
                                 int* oob, int sm_count, cudaStream_t st) {

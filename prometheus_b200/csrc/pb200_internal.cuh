@@ -56,11 +56,18 @@ struct DevScene {
     double* ncol;         // [n_atoms][n_orb][Mp]  column densities
     double* density[kMaxScenarios];  // [n_orb][M][n_x] number density of molecular scenarios
     double* fout;         // [1] or [n_wav]  sum of unattenuated flux
-    // chord records of kernel (c'): [n_orb][Mp][n_atoms+3] = {w_in, w_in c1, w_in c2, Ncol_0 .. Ncol_{S-1}}, one TMA
+    // chord records of kernel (c'): [n_orb][<= Mp][n_atoms+3] = {w_in, w_in c1, w_in c2, Ncol_0 .. Ncol_{S-1}}, one TMA
     // bulk copy per 256-chord tile
     double* rec;
     const double* exp_tab;   // [256] 2^(j/256) then [4096] 2^(j/4096), correctly rounded, high words biased (pb200_math.cuh)
     unsigned long long* nmax;   // [n_atoms][n_orb] bit pattern of max_m Ncol (>= 0), set by kernel (a')
+    // transparent-chord culling (compact_kernel): a chord whose optical depth stays below 2^-54 at every
+    // wavelength of the run contributes exactly w_in (exp(-tau) rounds to 1.0), so only the other
+    // ("active") chords get a record; per phase they are packed at the front of the phase's rec row
+    unsigned long long* smax;   // [n_atoms][n_orb] bit pattern of max_w sigma_a(p, w) over the run's wavelengths
+    int* n_act;                 // [n_orb] 256-chord tiles of active records
+    double* w0;                 // [n_orb] sum of w_in over the transparent chords
+    unsigned long long* stat;   // [2]: [0] low word = tabulated-density out-of-grid flag, [1] active records of the run
 };
 
 // launch parameters of kernel (c') and its variants

@@ -17,7 +17,6 @@
 //     both as possible: 6 FP64 + 3 integer + 1 LDS per sample for one absorber), fp64
 //     accumulators; the chord axis is split over blockIdx.z to get many more CTAs than resident
 //     slots (tail effect), partial sums reduced in a fixed order by finalize_kernel (deterministic).
-// The chord-level early-out (w_in == 0: blocked/padding) is CTA-uniform.
 #include <cstdlib>
 
 #include "pb200_internal.cuh"
@@ -66,32 +65,46 @@ __device__ __forceinline__ void lds_v2f64(uint32_t addr, double& a, double& b) {
     asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(a), "=d"(b) : "r"(addr));
 }
 
-// (b1) for the whole output tile: nsig[a][p][w] = -sigma_a(p, lambda_w) * 4096/ln2
+// (b1) for the whole output tile: nsig[a][p][w] = -sigma_a(p, lambda_w) * 4096/ln2, and the largest
+// sigma_a of the phase over the run's wavelengths (smax, for the transparent-chord test of compact_kernel)
 __global__ void __launch_bounds__(256) sigma_phase_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
     const DevScene& sc = *scp;
     const int64_t wi = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (wi >= prm.n_wav_sel) return;
+    const bool live = wi < prm.n_wav_sel;
     const int pi = blockIdx.y, p = prm.phase_lo + pi;
-    const double lam = __ldg(sc.wavelength + prm.wav_lo + wi);
+    const double lam = live ? __ldg(sc.wavelength + prm.wav_lo + wi) : 0.0;
     int a = 0;
     for (int k = 0; k < sc.n_cons; ++k) {
         const DevConstituent& C = sc.cons[k];
         if (C.kind != 0) continue;
-        const double shift = __ldg(sc.scen[C.scenario].shift + p);
-        const double v = pb_interp_log(C.tab_x, C.tab_y, C.n_tab, shift * lam, C.offset);   // :917, :950-951
-        prm.nsig[((int64_t)a * prm.n_phase + pi) * prm.n_wav_sel + wi] = -v * kExpBigScale;
+        unsigned long long bits = 0ull;
+        if (live) {
+            const double shift = __ldg(sc.scen[C.scenario].shift + p);
+            const double v = pb_interp_log(C.tab_x, C.tab_y, C.n_tab, shift * lam, C.offset);   // :917, :950-951
+            prm.nsig[((int64_t)a * prm.n_phase + pi) * prm.n_wav_sel + wi] = -v * kExpBigScale;
+            bits = (v >= 0.0) ? (unsigned long long)__double_as_longlong(v) : ~0ull;   // negative or NaN: never cull
+        }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            const unsigned long long o = __shfl_xor_sync(0xffffffffu, bits, d);
+            bits = o > bits ? o : bits;
+        }
+        if ((threadIdx.x & 31) == 0 && bits) atomicMax(sc.smax + (int64_t)a * sc.n_orb + p, bits);
         ++a;
     }
 }
 
 // One 256-chord tile: acc[j] += w_m * exp(-sum_a N_a(m) sigma_a(j)) for the thread's WPT wavelengths.
 // `stage` is the shared-window address of the tile's records (explicit ld.shared: no generic->shared
-// address conversion inside the loop).
-template <int S, int WPT, bool CLAMP>
+// address conversion inside the loop).  There is no branch on blocked chords or padding: their record
+// is all zeros (w = w c1 = w c2 = 0, N = 0), so they add T * 0 = +0 exactly (F_in = 0,
+// gasProperties.py:1233) -- a few per cent of wasted samples buy a branch-free loop body that ptxas
+// can software-pipeline across chords.
+template <int S, int WPT, bool CLAMP, int UNROLL = 2, int DROP = 0>
 __device__ __forceinline__ void transit_tile(uint32_t stage, const double (&nsig)[S][WPT], double (&acc)[WPT],
                                              uint32_t tab_base) {
     constexpr uint32_t kRecBytes = (S + kRecExtra) * sizeof(double);
-#pragma unroll 2
+#pragma unroll UNROLL
     for (int m = 0; m < kChordTile; ++m) {
         const uint32_t rec = stage + m * kRecBytes;
         double w0, w1, w2, N[S];
@@ -103,8 +116,6 @@ __device__ __forceinline__ void transit_tile(uint32_t stage, const double (&nsig
 #pragma unroll
             for (int a = 0; a < S; ++a) N[a] = lds_f64(rec + 24 + 8 * a);
         }
-        // blocked chord or padding: F_in = 0 (gasProperties.py:1233); CTA-uniform, integer test
-        if ((__double2hiint(w0) | __double2loint(w0)) == 0) continue;
 #pragma unroll
         for (int j = 0; j < WPT; ++j) {
             double t, r;
@@ -122,7 +133,11 @@ __device__ __forceinline__ void transit_tile(uint32_t stage, const double (&nsig
                 t = v + kExpMagic;
                 r = v - (t - kExpMagic);
             }
-            const double T = pb_exp_big_load(tab_base, __double2loint(t));
+            double T;
+            if constexpr (DROP == 0) T = pb_exp_big_load(tab_base, __double2loint(t));
+            else if constexpr (DROP == 1) T = __hiloint2double(0x3ff00000 + (__double2loint(t) << 8), 0);           // no LOP3/LEA/LDS
+            else if constexpr (DROP == 2) { int lo_, hi_; asm volatile("{.reg .b32 j, a; and.b32 j, %2, 4095; mad.lo.u32 a, j, 8, %3; ld.shared.v2.b32 {%0, %1}, [a];}" : "=r"(lo_), "=r"(hi_) : "r"(__double2loint(t)), "r"(tab_base)); T = __hiloint2double(hi_, lo_); }   // no IMAD
+            else T = __hiloint2double(0x3ff00000, __double2loint(t));                                                  // FP64 only
             double q = fma(r, w2, w1);
             q = fma(q, r, w0);                                                     // w exp(r ln2/4096)
             acc[j] = fma(T, q, acc[j]);                                            // :1241, :1244/:1255
@@ -131,8 +146,8 @@ __device__ __forceinline__ void transit_tile(uint32_t stage, const double (&nsig
 }
 
 // S atomic constituents (compile time), WPT wavelengths per thread, THREADS threads per CTA
-template <int S, int WPT, int THREADS>
-__global__ void __launch_bounds__(THREADS)
+template <int S, int WPT, int THREADS, int VAR = 0>
+__global__ void __launch_bounds__(THREADS, (VAR & 1) ? 4 : (THREADS == 256 ? 3 : 6))
 transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
     const DevScene& sc = *scp;
     // shared memory: exp table [4096] | stage 0 records | stage 1 records; a stage holds kChordTile records
@@ -147,10 +162,34 @@ transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
     const int tid = threadIdx.x;
     const int p = prm.phase_lo + blockIdx.y;
     const int split = blockIdx.z;
-    const int tile0 = split * prm.tiles_per_split;
-    const int n_tiles_total = sc.Mp / kChordTile;
-    int n_tiles = n_tiles_total - tile0;
-    if (n_tiles > prm.tiles_per_split) n_tiles = prm.tiles_per_split;
+    // this CTA's share of the phase's ACTIVE tiles (compact_kernel): even shares, at least 4 tiles per
+    // working CTA so that the table load and the prologue stay amortised; CTAs beyond the need store zeros
+    const int n_act = sc.n_act[p];
+    int tps = (n_act + prm.n_split - 1) / prm.n_split;
+    if (tps < 4) tps = 4;
+    const int tile0 = split * tps;
+    int n_tiles = n_act - tile0;
+    if (n_tiles > tps) n_tiles = tps;
+    const int64_t w_base = (int64_t)blockIdx.x * (THREADS * WPT) + tid;     // relative to wav_lo
+    if (n_tiles <= 0) {   // nothing to do (CTA-uniform): F_in partial = 0, or R = w0 / F_out for the only split
+#pragma unroll
+        for (int j = 0; j < WPT; ++j) {
+            const int64_t w = w_base + (int64_t)j * THREADS;
+            if (w >= prm.n_wav_sel) continue;
+            const int64_t o = (int64_t)blockIdx.y * prm.n_wav_sel + w;
+            if (prm.n_split == 1) {
+                double v = sc.w0[p] / sc.fout[0];
+                for (int a = 0; a < S; ++a) {   // NaN cross-section: the reference propagates NaN into R
+                    const double ns = __ldg(prm.nsig + ((int64_t)a * prm.n_phase + blockIdx.y) * prm.n_wav_sel + w);
+                    if (ns != ns) v = ns;
+                }
+                prm.R[o] = v;
+            } else {
+                prm.partial[(int64_t)split * prm.n_phase * prm.n_wav_sel + o] = 0.0;
+            }
+        }
+        return;
+    }
 
     if (tid == 0) {
         mbar_init(&full_bar[0], 1);
@@ -172,7 +211,6 @@ transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
     }
 
     // ---- prologue: -sigma_a(p, w) 4096/ln2 for this thread's wavelengths ---------------------------
-    const int64_t w_base = (int64_t)blockIdx.x * (THREADS * WPT) + tid;     // relative to wav_lo
     double nsig[S][WPT];
     double acc[WPT];
     bool bad = false;   // NaN cross-section (NaN wavelength): the reference propagates NaN into R
@@ -204,7 +242,10 @@ transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
     __syncthreads();   // exp table complete
 
     // ---- main loop over chord tiles -----------------------------------------------------------
-    const uint32_t tab_base = smem_u32(etab);
+    // laundered through an opaque mov so that the address lives in a register instead of being
+    // re-derived (S2UR CgaCtaId + ULEA) for every chord
+    uint32_t tab_base;
+    asm volatile("mov.u32 %0, %1;" : "=r"(tab_base) : "r"(smem_u32(etab)));
     const uint32_t stages_addr = smem_u32(stages);
     for (int t = 0; t < n_tiles; ++t) {
         const int stage = t & 1;
@@ -212,7 +253,7 @@ transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
         mbar_wait(&full_bar[stage], (t >> 1) & 1);
         const uint32_t sw = stages_addr + stage * kStageBytes;
         if (clamp) transit_tile<S, WPT, true>(sw, nsig, acc, tab_base);
-        else transit_tile<S, WPT, false>(sw, nsig, acc, tab_base);
+        else transit_tile<S, WPT, false, (VAR & 2) ? 4 : 2, (VAR >> 2)>(sw, nsig, acc, tab_base);
         __syncthreads();   // stage may be refilled by the producer in the next iteration
     }
 
@@ -229,7 +270,7 @@ transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
             for (int a = 0; a < S; ++a)
                 if (nsig[a][j] != nsig[a][j]) v = nsig[a][j];
         }
-        if (prm.n_split == 1) prm.R[o] = v / fout;                             // :1258
+        if (prm.n_split == 1) prm.R[o] = (v + sc.w0[p]) / fout;                // :1258
         else prm.partial[(int64_t)split * prm.n_phase * prm.n_wav_sel + o] = v;
     }
 }
@@ -239,17 +280,17 @@ __global__ void finalize_kernel(const DevScene* __restrict__ scp, const TransitP
     const DevScene& sc = *scp;
     const int64_t n = (int64_t)prm.n_phase * prm.n_wav_sel;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-        double s = 0.0;
+        double s = sc.w0[prm.phase_lo + i / prm.n_wav_sel];                     // transparent chords
         for (int k = 0; k < prm.n_split; ++k) s += prm.partial[(int64_t)k * n + i];
         const double fout = sc.fout[sc.fout_per_wav ? prm.wav_lo + i % prm.n_wav_sel : 0];
         prm.R[i] = s / fout;
     }
 }
 
-template <int S, int WPT, int THREADS>
+template <int S, int WPT, int THREADS, int VAR = 0>
 static cudaError_t launch_one(const DevScene* d_scene, const TransitParams& prm, cudaStream_t st) {
     const size_t smem = (kExpBigEntries + 2 * (S + kRecExtra) * kChordTile) * sizeof(double);
-    auto kern = transit_kernel<S, WPT, THREADS>;
+    auto kern = transit_kernel<S, WPT, THREADS, VAR>;
     {   // dynamic + static shared memory is always above the 48 KB default limit
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
@@ -285,6 +326,13 @@ void launch_sigma_phase(const DevScene* d_scene, const TransitParams& prm, cudaS
 // returns cudaSuccess, or cudaErrorInvalidValue when n_atoms is outside the compiled range
 cudaError_t launch_transit(const DevScene* d_scene, int n_atoms, const TransitParams& prm, cudaStream_t st) {
     const bool t256 = transit_threads() == 256;
+    static const int var = env_int("PB200_TV");
+    if (n_atoms == 1 && var == 1) return launch_one<1, 8, 256, 1>(d_scene, prm, st);
+    if (n_atoms == 1 && var == 2) return launch_one<1, 8, 256, 2>(d_scene, prm, st);
+    if (n_atoms == 1 && var == 3) return launch_one<1, 8, 256, 3>(d_scene, prm, st);
+    if (n_atoms == 1 && var == 6) return launch_one<1, 8, 256, 6>(d_scene, prm, st);
+    if (n_atoms == 1 && var == 10) return launch_one<1, 8, 256, 10>(d_scene, prm, st);
+    if (n_atoms == 1 && var == 14) return launch_one<1, 8, 256, 14>(d_scene, prm, st);
     switch (n_atoms) {
         case 1: return t256 ? launch_one<1, 8, 256>(d_scene, prm, st) : launch_one<1, 8, 128>(d_scene, prm, st);
         case 2: return t256 ? launch_one<2, 8, 256>(d_scene, prm, st) : launch_one<2, 8, 128>(d_scene, prm, st);
