@@ -289,7 +289,8 @@ def quick_workload(name, ctx, torch, stream, flush, steps=3, warmup=3):
            "n_atoms": info["n_atoms"], "n_molecules": info["n_mols"], "ms_per_step": float(np.mean(ms)),
            "samples_per_s": samples / (np.mean(ms) * 1e-3), "e2e_ms_one_call": e2e_ms,
            "kernels_ms": {k: float(np.mean([t[k] for t in kern])) for k in ("column_ms", "transit_ms", "finalize_ms")},
-           "setup_seconds": t_setup, "R_min": float(R.min()), "R_max": float(R.max())}
+           "setup_seconds": t_setup, "R_min": float(R.min()), "R_max": float(R.max()),
+           "executed_frac": float(np.mean([t["executed_samples"] for t in kern])) / samples}
     if info["n_mols"]:
         res["molecular_lookups_per_s"] = samples * info["n_x"] * info["n_mols"] / (np.mean(ms) * 1e-3)
     return res
@@ -362,7 +363,38 @@ def run_b200(args):
         kernel_ms = float(np.mean([t["transit_ms"] for t in tile_t]))
         column_ms = float(np.mean([t["column_ms"] for t in tile_t]))
         finalize_ms = float(np.mean([t["finalize_ms"] for t in tile_t]))
+        executed = float(np.mean([t["executed_samples"] for t in tile_t]))
         R_dev = st.to_host(0)
+
+        # ---- the same steps with the transparent-chord culling switched off (every unblocked chord
+        #      goes through the exp, as in the reference's loop): reported next to the headline ----------
+        os.environ["PB200_NO_CULL"] = "1"
+        os.environ["PB200_NO_MIRROR"] = "1"
+        ctx.set_scene(sc, keep)
+        tile_t.clear()
+        for _ in range(2):
+            st.run_device()
+        barrier()
+        tile_t.clear()
+        ev_nc = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(max(3, args.steps // 4))]
+        for a, b in ev_nc:
+            flush.zero_()
+            a.record()
+            st.run_device()
+            b.record()
+        barrier()
+        nc_total = torch.tensor([sum(a.elapsed_time(b) for a, b in ev_nc)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(nc_total, op=dist.ReduceOp.MAX)
+        nc_ms_per_step = float(nc_total.item()) / len(ev_nc)
+        nc_kernel_ms = float(np.mean([t["transit_ms"] for t in tile_t]))
+        nc_executed = float(np.mean([t["executed_samples"] for t in tile_t]))
+        R_nc = st.to_host(0)
+        del os.environ["PB200_NO_CULL"], os.environ["PB200_NO_MIRROR"]
+        ctx.set_scene(sc, keep)
+        tile_t.clear()
+        st.run_device()
+        barrier()
 
         # ---- end to end through the host API (host buffers, H2D + D2H inside) ---------------------
         state = {}
@@ -394,11 +426,16 @@ def run_b200(args):
             dist.destroy_process_group()
         return
     assert R_dev.shape == (n_orb, n_wav) and np.all(np.isfinite(R_dev)) and np.array_equal(R_dev, R_e2e)
+    cull_diff = float(np.max(np.abs(R_dev - R_nc)))
+    assert cull_diff < 1e-12, cull_diff
 
     hbm_peak, peak_src = measured_peaks()
-    tile_samples = float(n_c) * float(st.samples_tile_shape[1])
-    achieved = BYTES_PER_SAMPLE_STAGED * tile_samples / (kernel_ms * 1e-3) / 1e9
-    fl = flops_per_sample(n_atoms) * tile_samples / (kernel_ms * 1e-3) / 1e12
+    tile_samples = float(n_c) * float(st.samples_tile_shape[1])          # nominal samples of this rank's tile
+    if n_mols:
+        executed = nc_executed = tile_samples                               # kernel (m) has no culling
+    # the roofline describes what kernel (c') evaluated: the samples that went through the exp
+    achieved = BYTES_PER_SAMPLE_STAGED * executed / (kernel_ms * 1e-3) / 1e9
+    fl = flops_per_sample(n_atoms) * executed / (kernel_ms * 1e-3) / 1e12
     out = {
         "metric": "chord*lambda samples/s", "value": samples_total / (ms_per_step * 1e-3), "unit": "samples/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
@@ -416,13 +453,24 @@ def run_b200(args):
                      "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "peak_source": peak_src,
                      "convention": "staged-equivalent 16 B per chord*lambda sample (SURVEY 8(d)); the fused kernel's true DRAM traffic is in `traffic`",
                      "traffic": recorded_traffic(args.workload), "kernel_ms": kernel_ms,
+                     "samples_per_launch": executed,
+                     "samples_note": "samples kernel (c') evaluated per launch; transparent chords (tau < 2^-54 at every wavelength, exp(-tau) == 1.0) are summed without an exp, see `culling`",
                      "fp64": {"achieved_tflops": fl, "peak_tflops_dfma_probe": probe["dfma_tflops"],
                               "frac": fl / probe["dfma_tflops"], "flops_per_sample": flops_per_sample(n_atoms),
-                              "pipe_frac": ((6.0 if n_atoms == 1 else 6.0 + n_atoms) * tile_samples / 32.0 * 2.0) /
+                              "pipe_frac": ((6.0 if n_atoms == 1 else 6.0 + n_atoms) * executed / 32.0 * 2.0) /
                                            (148 * 4 * (clk["sm_mhz"] or 1965.0) * 1e6 * kernel_ms * 1e-3) if n_mols == 0 else None,
                               "pipe_frac_note": "issued FP64 warp instructions (6 per sample for one absorber, else 6+S; nominal sample count) x 2 cycles / SMSP cycles: the binding unit",
                               "exp_probe_gops": probe["exp_gops"],
-                              "exp_frac": tile_samples / (kernel_ms * 1e-3) / 1e9 / probe["exp_gops"]}},
+                              "exp_frac": executed / (kernel_ms * 1e-3) / 1e9 / probe["exp_gops"]}},
+        "culling": {"nominal_samples_per_step": tile_samples * world, "executed_samples_per_rank_step": executed,
+                    "executed_frac": executed / tile_samples,
+                    "off": {"value": samples_total / (nc_ms_per_step * 1e-3), "ms_per_step": nc_ms_per_step,
+                            "transit_kernel_ms": nc_kernel_ms, "executed_frac": nc_executed / tile_samples,
+                            "max_abs_diff_R": cull_diff},
+                    "note": "`value` counts the job's chord*lambda samples (BASELINE metric); chords whose optical depth is "
+                            "below 2^-54 at every wavelength of the run contribute exactly w_in and skip the exp, and the chords "
+                            "(phi, rho), (pi - phi, rho) -- equal column densities, the scene is symmetric in z -- share one record. "
+                            "`off` = same steps with PB200_NO_CULL=1 PB200_NO_MIRROR=1: every unblocked chord goes through the exp"},
         "kernels_ms": {"column": column_ms, "transit": kernel_ms, "finalize": finalize_ms},
         "setup": {"seconds": t_setup, "voigt_last_table_ms": voigt["transit_ms"], "voigt_last_table_evals": voigt["samples"]},
     }

@@ -4,6 +4,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -28,7 +29,7 @@ cudaError_t launch_transit_general(const DevScene*, const DevScene& host_copy, c
                                    cudaStream_t, int* n_launch);
 int transit_cta_wavelengths(int n_atoms);
 void launch_sigma_phase(const DevScene*, const TransitParams&, cudaStream_t);
-void launch_compact(const DevScene*, int phase_lo, int n_phase, cudaStream_t);
+void launch_compact(const DevScene*, int phase_lo, int n_phase, bool cull, cudaStream_t);
 void launch_finalize(const DevScene*, const TransitParams&, int sm_count, cudaStream_t);
 void launch_sigma_lookup(const double*, const double*, int64_t, double, const double*, int64_t, double*, int,
                          cudaStream_t);
@@ -410,6 +411,20 @@ extern "C" int pb200_set_scene(pb200_ctx* c, const pb200_scene* s) {
     h.stat = reinterpret_cast<unsigned long long*>(c->d_oob);
     PB_CUDA(c, cudaMemsetAsync(nmax_d, 0, (size_t)(n_atoms ? n_atoms : 1) * h.n_orb * sizeof(double), c->stream));
     c->general_path = (n_mols > 0) || fstar_per_chord;
+    {   // mirror pairing of chords (compact_kernel): all bodies lie in z = 0 and every analytic density depends
+        // on z^2 only; the tabulated (SERPENS) density does not.  The phi axis must be mirror symmetric about
+        // pi/2 and 3 pi/2 on the grid itself: sin(phi_i') = sin(phi_i), cos(phi_i') = -cos(phi_i), i' = n/2-1-i.
+        bool ok = !c->general_path && (s->n_phi % 2 == 0);
+        for (int i = 0; ok && i < s->n_scenarios; ++i) ok = s->scenarios[i].type != PB200_SCN_SERPENS;
+        const int n2 = s->n_phi / 2;
+        for (int hh = 0; ok && hh < 2; ++hh)
+            for (int i = 0; ok && i < n2; ++i) {
+                const int a = hh * n2 + i, b = hh * n2 + n2 - 1 - i;
+                ok = fabs(s->sin_phi[a] - s->sin_phi[b]) <= 1e-14 && fabs(s->cos_phi[a] + s->cos_phi[b]) <= 1e-14;
+            }
+        const char* off = getenv("PB200_NO_MIRROR");   // measurement / debugging only
+        h.mirror = (ok && !(off && off[0] == '1')) ? 1 : 0;
+    }
     h.fout_per_wav = fstar_per_chord ? 1 : 0;
 
     PB_CUDA(c, cudaMemcpyAsync(c->d_scene, &h, sizeof(DevScene), cudaMemcpyHostToDevice, c->stream));
@@ -484,7 +499,9 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     launch_column(c->d_scene, h.Mp, phase_lo, n_phase, c->d_oob, c->sm_count, c->stream, h.n_mols > 0);
     c->launches += 1;
     if (!c->general_path) {   // chord records of kernel (c'), transparent chords culled
-        launch_compact(c->d_scene, phase_lo, n_phase, c->stream);
+        // PB200_NO_CULL=1 (measurement only): every unblocked chord gets a record, as in the reference's loop
+        const char* no_cull = getenv("PB200_NO_CULL");
+        launch_compact(c->d_scene, phase_lo, n_phase, !(no_cull && no_cull[0] == '1'), c->stream);
         c->launches += 1;
     }
     PB_CUDA(c, cudaGetLastError());

@@ -231,7 +231,7 @@ column_thread_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase
 // Active records are packed in chord order at the front of the phase's rec row (block-wide exclusive
 // scan, deterministic), the last tile is padded with all-zero records, n_act[p] = number of tiles.
 constexpr int kCompactThreads = 1024;
-__global__ void __launch_bounds__(kCompactThreads) compact_kernel(const DevScene* __restrict__ scp, int phase_lo) {
+__global__ void __launch_bounds__(kCompactThreads) compact_kernel(const DevScene* __restrict__ scp, int phase_lo, int cull) {
     const DevScene& sc = *scp;
     const int p = phase_lo + blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int S = sc.n_atoms, R = S + 3;
@@ -241,18 +241,42 @@ __global__ void __launch_bounds__(kCompactThreads) compact_kernel(const DevScene
     __shared__ int s_base;
     if (tid < S) {
         const double v = __longlong_as_double((long long)sc.smax[(int64_t)tid * sc.n_orb + p]);
-        s_smax[tid] = (v >= 0.0) ? v : __longlong_as_double(0x7ff0000000000000ll);   // negative or NaN: never cull
+        s_smax[tid] = (cull && v >= 0.0) ? v : __longlong_as_double(0x7ff0000000000000ll);   // negative or NaN: never cull
     }
     if (tid == 0) s_base = 0;
     __syncthreads();
     const int64_t row0 = (int64_t)p * sc.Mp;
     double* rec_row = sc.rec + row0 * R;
     double w0 = 0.0;
-    for (int m0 = 0; m0 < sc.Mp; m0 += kCompactThreads) {
-        const int m = m0 + tid;
+    // mirror pairing (sc.mirror, set by pb200_set_scene when it holds): every body and density centre lies in
+    // the plane z = 0 and every density depends on z through z^2 only, so the chords (phi, rho) and
+    // (pi - phi, rho) have the same column densities; with an even, mirror-symmetric phi axis they are grid
+    // chords i and n_phi/2 - 1 - i of the same half turn.  One record then stands for both: weight =
+    // w_in(i) + w_in(i') (each is zero if that chord is blocked), Ncol from whichever is not blocked.
+    const int n2 = sc.n_phi / 2, P = (n2 + 1) / 2;
+    const int n_items = sc.mirror ? 2 * P * sc.n_rho : sc.Mp;
+    for (int m0 = 0; m0 < n_items; m0 += kCompactThreads) {
+        const int q = m0 + tid;
         double w = 0.0, bound = 0.0;
-        if (m < sc.Mp) {
-            w = sc.w_in[row0 + m];
+        int m = q;
+        if (q < n_items) {
+            if (sc.mirror) {
+                const int h = q / (P * sc.n_rho), rem = q - h * (P * sc.n_rho);
+                const int i = rem / sc.n_rho, irho = rem - i * sc.n_rho;
+                m = (h * n2 + i) * sc.n_rho + irho;
+                const int ip = n2 - 1 - i;
+                const double wa = sc.w_in[row0 + m];
+                if (ip != i) {
+                    const int mb = (h * n2 + ip) * sc.n_rho + irho;
+                    const double wb = sc.w_in[row0 + mb];
+                    if (wa == 0.0) m = mb;               // Ncol of a blocked chord is not evaluated: take the mirror's
+                    w = wa + wb;
+                } else {
+                    w = wa;
+                }
+            } else {
+                w = sc.w_in[row0 + m];
+            }
             for (int a = 0; a < S; ++a) bound = fma(sc.ncol[(int64_t)a * sc.n_orb * sc.Mp + row0 + m], s_smax[a], bound);
         }
         const bool alive = (w != 0.0);
@@ -394,8 +418,8 @@ void launch_column(const DevScene* d_scene, int Mp, int phase_lo, int n_phase, i
         column_thread_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(d_scene, phase_lo, n_phase, oob);
     }
 }
-void launch_compact(const DevScene* d_scene, int phase_lo, int n_phase, cudaStream_t st) {
-    compact_kernel<<<n_phase, kCompactThreads, 0, st>>>(d_scene, phase_lo);
+void launch_compact(const DevScene* d_scene, int phase_lo, int n_phase, bool cull, cudaStream_t st) {
+    compact_kernel<<<n_phase, kCompactThreads, 0, st>>>(d_scene, phase_lo, cull ? 1 : 0);
 }
 void launch_number_density_grid(const DevScene* d_scene, int64_t n_chords, int scenario, double* out,
                                 int* oob, int sm_count, cudaStream_t st) {

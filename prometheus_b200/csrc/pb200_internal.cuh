@@ -65,6 +65,7 @@ struct DevScene {
     // wavelength of the run contributes exactly w_in (exp(-tau) rounds to 1.0), so only the other
     // ("active") chords get a record; per phase they are packed at the front of the phase's rec row
     unsigned long long* smax;   // [n_atoms][n_orb] bit pattern of max_w sigma_a(p, w) over the run's wavelengths
+    int mirror;                 // 1: chords (phi, rho) and (pi - phi, rho) share one record (see compact_kernel)
     int* n_act;                 // [n_orb] 256-chord tiles of active records
     double* w0;                 // [n_orb] sum of w_in over the transparent chords
     unsigned long long* stat;   // [2]: [0] low word = tabulated-density out-of-grid flag, [1] active records of the run
