@@ -18,7 +18,8 @@ namespace pb200 {
 // launchers implemented in the kernel translation units
 void launch_sky_cells(const DevScene*, int Mp, cudaStream_t);
 void launch_fout_scalar(const DevScene*, cudaStream_t);
-void launch_column(const DevScene*, int Mp, int phase_lo, int n_phase, int* oob, int sm_count, cudaStream_t, bool has_molecules);
+void launch_column(const DevScene*, int Mp, int phase_lo, int n_phase, int* oob, int sm_count, cudaStream_t, bool has_molecules,
+                   bool run_mode);
 void launch_number_density_grid(const DevScene*, int64_t n_chords, int scenario, double* out, int* oob, int sm_count,
                                 cudaStream_t);
 void launch_number_density_chords(const DevScene*, int scenario, int64_t n, const double* y, const double* z,
@@ -496,12 +497,15 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
         launch_sigma_phase(c->d_scene, prm, c->stream);
         c->launches += 1;
     }
-    launch_column(c->d_scene, h.Mp, phase_lo, n_phase, c->d_oob, c->sm_count, c->stream, h.n_mols > 0);
+    // PB200_NO_CULL=1 (measurement only): every unblocked chord gets its exact sums and a record, as in the
+    // reference's loop
+    const char* no_cull = getenv("PB200_NO_CULL");
+    const bool cull = !(no_cull && no_cull[0] == '1');
+    launch_column(c->d_scene, h.Mp, phase_lo, n_phase, c->d_oob, c->sm_count, c->stream, h.n_mols > 0,
+                  !c->general_path && cull);
     c->launches += 1;
     if (!c->general_path) {   // chord records of kernel (c'), transparent chords culled
-        // PB200_NO_CULL=1 (measurement only): every unblocked chord gets a record, as in the reference's loop
-        const char* no_cull = getenv("PB200_NO_CULL");
-        launch_compact(c->d_scene, phase_lo, n_phase, !(no_cull && no_cull[0] == '1'), c->stream);
+        launch_compact(c->d_scene, phase_lo, n_phase, cull, c->stream);
         c->launches += 1;
     }
     PB_CUDA(c, cudaGetLastError());
@@ -696,7 +700,7 @@ extern "C" int pb200_column_density(pb200_ctx* c, double* ncol_host) {
     if (rc) return rc;
     const DevScene& h = c->h_scene;
     if (!ncol_host) return fail(c, PB200_ERR_INVALID, "ncol_host == NULL");
-    launch_column(c->d_scene, h.Mp, 0, h.n_orb, c->d_oob, c->sm_count, c->stream, h.n_mols > 0);
+    launch_column(c->d_scene, h.Mp, 0, h.n_orb, c->d_oob, c->sm_count, c->stream, h.n_mols > 0, false);
     c->launches += 1;
     PB_CUDA(c, cudaGetLastError());
     rc = check_oob(c);
@@ -714,7 +718,7 @@ extern "C" int pb200_chord_masks(pb200_ctx* c, uint8_t* blocked_host, double* we
     int rc = check_scene(c);
     if (rc) return rc;
     const DevScene& h = c->h_scene;
-    launch_column(c->d_scene, h.Mp, 0, h.n_orb, c->d_oob, c->sm_count, c->stream, h.n_mols > 0);
+    launch_column(c->d_scene, h.Mp, 0, h.n_orb, c->d_oob, c->sm_count, c->stream, h.n_mols > 0, false);
     c->launches += 1;
     PB_CUDA(c, cudaGetLastError());
     std::vector<double> w_in((size_t)h.n_orb * h.Mp), w_out(h.Mp);
@@ -739,7 +743,7 @@ extern "C" int pb200_optical_depth(pb200_ctx* c, int64_t wav_lo, int64_t wav_hi,
     DevBuf sig, tau;
     PB_CUDA(c, sig.alloc((size_t)(h.n_atoms ? h.n_atoms : 1) * h.n_orb * n_wav_sel * sizeof(double)));
     PB_CUDA(c, tau.alloc((size_t)n_c * n_wav_sel * sizeof(double)));
-    launch_column(c->d_scene, h.Mp, 0, h.n_orb, c->d_oob, c->sm_count, c->stream, h.n_mols > 0);
+    launch_column(c->d_scene, h.Mp, 0, h.n_orb, c->d_oob, c->sm_count, c->stream, h.n_mols > 0, false);
     if (h.n_atoms) launch_sigma_u(c->d_scene, h.n_atoms, h.n_orb, wav_lo, n_wav_sel, sig.as<double>(), c->sm_count, c->stream);
     launch_optical_depth(c->d_scene, sig.as<double>(), n_c, wav_lo, n_wav_sel, tau.as<double>(), c->stream);
     c->launches += 2 + (h.n_atoms ? 1 : 0);

@@ -186,15 +186,43 @@ __device__ __forceinline__ double pb_column_sum(const DevScene& sc, const DevSce
     }
 }
 
+// Upper bound of the x-sum of one scenario on a chord (every term <= its value at dx = 0, the closest
+// approach r_min = sqrt(dy^2 + z^2)); +inf where no cheap bound exists.  Used by the run path only, to skip
+// the sum on chords that compact_kernel will classify as transparent anyway.
+__device__ __forceinline__ double pb_column_bound(const DevScene& sc, const DevScenario& S, int p, double amp, double y,
+                                                  double z) {
+    if (S.type == PB200_SCN_SERPENS) return __longlong_as_double(0x7ff0000000000000ll);
+    const double dy = y - S.centre_y[p];
+    const double n0 = fabs(S.p[0] * amp) * sc.n_x;
+    const double rmin = sqrt(fma(dy, dy, z * z));
+    switch (S.type) {
+        case PB200_SCN_BAROMETRIC: return n0 * ((rmin < S.p[1]) ? 1.0 : exp((S.p[1] - rmin) / S.p[2]));
+        case PB200_SCN_HYDROSTATIC: {
+            const double jc = S.p[2] / S.p[3];
+            return n0 * ((rmin < S.p[1]) ? 1.0 : exp(jc / rmin - jc / S.p[1]));
+        }
+        case PB200_SCN_POWERLAW: return n0 * ((rmin < S.p[1]) ? 1.0 : exp(S.p[2] * (log(S.p[1]) - log(rmin))));
+        case PB200_SCN_TORUS: { const double qz = z / S.p[2]; return n0 * exp(-(qz * qz)); }
+        default: return __longlong_as_double(0x7ff0000000000000ll);
+    }
+}
+
+// run_mode = 0: every unblocked chord gets its exact column densities (inner seams of the API).
+// run_mode = 1 (pb200_run): the sums that compact_kernel does not need are skipped --
+//   * the mirror chord of a pair whose primary chord is not blocked (sc.mirror);
+//   * chords whose upper bound sum_a bound_a * max_w sigma_a(p, w) is already below 2^-54: they are
+//     transparent whatever the exact sum is, and get the bound stored as Ncol (so that compact_kernel's own
+//     test classifies them the same way).
 __global__ void __launch_bounds__(128)
-column_thread_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, int* __restrict__ oob_flag) {
+column_thread_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, int* __restrict__ oob_flag,
+                     int run_mode) {
     const DevScene& sc = *scp;
     const int64_t cid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (cid >= (int64_t)n_phase * sc.Mp) return;
     const int p = phase_lo + (int)(cid / sc.Mp);
     const int m = (int)(cid % sc.Mp);
     const int64_t row = (int64_t)p * sc.Mp + m;
-    bool blocked = true;
+    bool blocked = true, need_sum = false;
     double y = 0.0, z = 0.0, wv = 0.0;
     if (m < sc.M) {
         const int iphi = m / sc.n_rho, irho = m - iphi * sc.n_rho;
@@ -203,12 +231,37 @@ column_thread_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase
         z = __dmul_rn(rho, sc.cos_phi[iphi]);
         blocked = pb_blocked(sc, p, y, z);
         wv = blocked ? 0.0 : sc.w_out[m];
+        need_sum = !blocked;
+        if (run_mode && sc.mirror && need_sum) {
+            const int n2 = sc.n_phi / 2, h = iphi / n2, i = iphi - h * n2, ip = n2 - 1 - i;
+            if (i > ip) {   // mirror chord of the pair: needed only if the primary chord is blocked
+                const int jphi = h * n2 + ip;
+                need_sum = pb_blocked(sc, p, __dmul_rn(rho, sc.sin_phi[jphi]), __dmul_rn(rho, sc.cos_phi[jphi]));
+            }
+        }
     }
     sc.w_in[row] = wv;
+    bool skip = false;
+    if (run_mode && need_sum) {   // transparent whatever the exact sums are?
+        double bound = 0.0;
+        for (int s = 0; s < sc.n_scen; ++s) {
+            const DevScenario& S = sc.scen[s];
+            const double ub = pb_column_bound(sc, S, p, S.amplitude ? S.amplitude[p] : 1.0, y, z);
+            for (int k = S.first_cons; k < S.first_cons + S.n_cons; ++k) {
+                const DevConstituent& C = sc.cons[k];
+                if (C.kind != 0) continue;
+                const double sm = __longlong_as_double((long long)sc.smax[(int64_t)C.atom_index * sc.n_orb + p]);
+                bound += (ub * fabs(C.chi)) * sc.delta_x * ((sm >= 0.0) ? sm : __longlong_as_double(0x7ff0000000000000ll));
+            }
+        }
+        skip = bound < 5.5511151231257827e-17;   // 2^-54; NaN (0 * inf) -> not skipped
+    }
     for (int s = 0; s < sc.n_scen; ++s) {
         const DevScenario& S = sc.scen[s];
+        const double amp = S.amplitude ? S.amplitude[p] : 1.0;
         // the reference evaluates only unblocked chords (gasProperties.py:1235-1240)
-        const double sum = blocked ? 0.0 : pb_column_sum(sc, S, p, S.amplitude ? S.amplitude[p] : 1.0, y, z, oob_flag);
+        double sum = 0.0;
+        if (need_sum) sum = skip ? pb_column_bound(sc, S, p, amp, y, z) : pb_column_sum(sc, S, p, amp, y, z, oob_flag);
         for (int k = S.first_cons; k < S.first_cons + S.n_cons; ++k) {
             const DevConstituent& C = sc.cons[k];
             if (C.kind != 0) continue;
@@ -410,12 +463,12 @@ void launch_fout_scalar(const DevScene* d_scene, cudaStream_t st) {
     fout_scalar_kernel<<<1, 1024, 0, st>>>(d_scene);
 }
 void launch_column(const DevScene* d_scene, int Mp, int phase_lo, int n_phase, int* oob, int sm_count,
-                   cudaStream_t st, bool has_molecules) {
+                   cudaStream_t st, bool has_molecules, bool run_mode) {
     if (has_molecules) {   // density rows n(c, x) are needed by kernel (m): warp per chord, coalesced row stores
         column_kernel<<<grid_for_warps((int64_t)n_phase * Mp, sm_count), 256, 0, st>>>(d_scene, phase_lo, n_phase, oob);
     } else {
         const int64_t n = (int64_t)n_phase * Mp;
-        column_thread_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(d_scene, phase_lo, n_phase, oob);
+        column_thread_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(d_scene, phase_lo, n_phase, oob, run_mode ? 1 : 0);
     }
 }
 void launch_compact(const DevScene* d_scene, int phase_lo, int n_phase, bool cull, cudaStream_t st) {

@@ -280,3 +280,67 @@ def test_trimmed_sigma_tables_are_bit_identical(ctx, transits):
             ctx.set_scene(sc2, keep2)
             part, _ = ctx.run(0, n_orb, lo, hi)
             assert np.array_equal(full, part), (name, lo, hi)
+
+
+# ---- transparent-chord culling and mirror pairing (compact_kernel) --------------------------------
+ATOM_CASES = ["C1", "C3s", "C4s", "C5s", "PLNs", "THMs", "SERs", "HYDs"]
+
+
+def run_with_env(tr, monkeypatch, **env):
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    R = tr.sumOverChords()
+    t = dict(tr.last_timing)
+    for k in env:
+        monkeypatch.delenv(k)
+    return R, t
+
+
+@pytest.mark.parametrize("name", ATOM_CASES)
+def test_culling_and_mirror_leave_R_unchanged(name, transits, monkeypatch):
+    """Transparent chords add exactly w_in (exp(-tau) == 1.0 for tau < 2^-54) and mirrored chords have equal
+    column densities, so switching either off changes R only by summation order / 1e-12-level Ncol noise."""
+    tr = transits(name)
+    if any(con.isMolecule for d in tr.atmosphere.densityDistributionList for con in d.constituents):
+        pytest.skip("kernel (m) has no culling")
+    R, t = run_with_env(tr, monkeypatch)
+    R_full, t_full = run_with_env(tr, monkeypatch, PB200_NO_CULL="1", PB200_NO_MIRROR="1")
+    R_nocull, t_nocull = run_with_env(tr, monkeypatch, PB200_NO_CULL="1")
+    R_nomirror, t_nomirror = run_with_env(tr, monkeypatch, PB200_NO_MIRROR="1")
+    for other in (R_full, R_nocull, R_nomirror):
+        assert np.max(np.abs(R - other)) < 5e-14
+    n_orb, n_wav = R.shape
+    assert t["samples"] == t_full["samples"]
+    # with both switched off every unblocked chord has a record (tiles are padded to 256 chords per phase)
+    M = t["samples"] // (n_wav * n_orb)
+    assert t_full["executed_samples"] <= (M + 255) // 256 * 256 * n_orb * n_wav
+    assert t_full["executed_samples"] >= 0.8 * t["samples"]
+    assert t["executed_samples"] <= t_nocull["executed_samples"] <= t_full["executed_samples"]
+    assert t["executed_samples"] <= t_nomirror["executed_samples"] <= t_full["executed_samples"]
+
+
+def test_mirror_pairing_halves_the_records_when_the_scene_is_symmetric(transits, monkeypatch):
+    tr = transits("C5s")           # power law around the planet, even n_phi
+    _, t_pair = run_with_env(tr, monkeypatch, PB200_NO_CULL="1")
+    _, t_full = run_with_env(tr, monkeypatch, PB200_NO_CULL="1", PB200_NO_MIRROR="1")
+    assert t_pair["executed_samples"] <= 0.6 * t_full["executed_samples"]
+
+
+def test_mirror_pairing_is_off_for_tabulated_densities_and_odd_phi(transits, nist_rows, monkeypatch):
+    tr = transits("SERs")          # SERPENS histogram: no z symmetry
+    _, t_a = run_with_env(tr, monkeypatch, PB200_NO_CULL="1")
+    _, t_b = run_with_env(tr, monkeypatch, PB200_NO_CULL="1", PB200_NO_MIRROR="1")
+    assert t_a["executed_samples"] == t_b["executed_samples"]
+    spec = workloads.get("C4s")
+    spec["grid"] = _with_phi(spec["grid"], 31)
+    odd = builder.build_transit(spec, nist_rows=nist_rows)
+    R_a, t_a = run_with_env(odd, monkeypatch, PB200_NO_CULL="1")
+    R_b, t_b = run_with_env(odd, monkeypatch, PB200_NO_CULL="1", PB200_NO_MIRROR="1")
+    assert t_a["executed_samples"] == t_b["executed_samples"]
+    assert np.array_equal(R_a, R_b)
+
+
+def _with_phi(grid, n_phi):
+    g = list(grid)
+    g[5] = n_phi          # Grid(x_midpoint, x_border, x_steps, rho_border, rho_steps, phi_steps, ...)
+    return g
