@@ -44,6 +44,12 @@ def flops_per_sample(n_atoms: int) -> float:
     return 2.0 * n_atoms + 29.0     # SURVEY 8(d) convention: S FMA + negate + exp(26) + 1 FMA
 
 
+def executed_flops_per_sample(n_atoms: int) -> float:
+    """FP64 flops kernel (c') really issues per sample (pb200_math.cuh "Big-table form"): one absorber
+    2 FMA + 1 ADD + 3 FMA = 11; S absorbers 1 MUL + (S-1) FMA + 3 ADD + 3 FMA = 2S + 8."""
+    return 11.0 if n_atoms == 1 else 2.0 * n_atoms + 8.0
+
+
 # ------------------------------------------------------------------------------------------------
 # workload
 # ------------------------------------------------------------------------------------------------
@@ -435,7 +441,7 @@ def run_b200(args):
         executed = nc_executed = tile_samples                               # kernel (m) has no culling
     # the roofline describes what kernel (c') evaluated: the samples that went through the exp
     achieved = BYTES_PER_SAMPLE_STAGED * executed / (kernel_ms * 1e-3) / 1e9
-    fl = flops_per_sample(n_atoms) * executed / (kernel_ms * 1e-3) / 1e12
+    fl = executed_flops_per_sample(n_atoms) * executed / (kernel_ms * 1e-3) / 1e12
     out = {
         "metric": "chord*lambda samples/s", "value": samples_total / (ms_per_step * 1e-3), "unit": "samples/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
@@ -456,7 +462,8 @@ def run_b200(args):
                      "samples_per_launch": executed,
                      "samples_note": "samples kernel (c') evaluated per launch; transparent chords (tau < 2^-54 at every wavelength, exp(-tau) == 1.0) are summed without an exp, see `culling`",
                      "fp64": {"achieved_tflops": fl, "peak_tflops_dfma_probe": probe["dfma_tflops"],
-                              "frac": fl / probe["dfma_tflops"], "flops_per_sample": flops_per_sample(n_atoms),
+                              "frac": fl / probe["dfma_tflops"], "flops_per_sample": executed_flops_per_sample(n_atoms),
+                              "flops_per_sample_survey_convention": flops_per_sample(n_atoms),
                               "pipe_frac": ((6.0 if n_atoms == 1 else 6.0 + n_atoms) * executed / 32.0 * 2.0) /
                                            (148 * 4 * (clk["sm_mhz"] or 1965.0) * 1e6 * kernel_ms * 1e-3) if n_mols == 0 else None,
                               "pipe_frac_note": "issued FP64 warp instructions (6 per sample for one absorber, else 6+S; nominal sample count) x 2 cycles / SMSP cycles: the binding unit",

@@ -280,8 +280,9 @@ class Context:
 
     def voigt_sigma(self, line_wl, line_gamma, line_f, sigma_v, wl, offset=1e-50, want_log=False):
         lw, lg, lf, wl = as_f64(line_wl), as_f64(line_gamma), as_f64(line_f), as_f64(wl)
-        sig = np.empty(wl.shape, dtype=np.float64)
-        lg10 = np.empty(wl.shape, dtype=np.float64) if want_log else None
+        # page-locked results: a table that goes back into pb200_set_scene is then uploaded without a staging copy
+        sig = pinned_pool.empty(wl.shape)
+        lg10 = pinned_pool.empty(wl.shape) if want_log else None
         self.check(self.lib.pb200_voigt_sigma(self.handle, dptr(lw), dptr(lg), dptr(lf), lw.size, float(sigma_v),
                                               dptr(wl), wl.size, float(offset), dptr(sig),
                                               dptr(lg10) if want_log else None))

@@ -6,6 +6,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <map>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -105,6 +107,19 @@ static int ensure_scratch(pb200_ctx* c, size_t bytes) {
     return PB200_OK;
 }
 
+// page-locked blocks handed out by pb200_host_alloc: arrays inside them are copied to the device
+// straight from where they lie (no staging copy), see pb200_set_scene
+static std::mutex g_pinned_mutex;
+static std::map<uintptr_t, size_t> g_pinned;
+static bool is_pinned(const void* p, size_t bytes) {
+    const uintptr_t a = reinterpret_cast<uintptr_t>(p);
+    std::lock_guard<std::mutex> lock(g_pinned_mutex);
+    auto it = g_pinned.upper_bound(a);
+    if (it == g_pinned.begin()) return false;
+    --it;
+    return a >= it->first && a + bytes <= it->first + it->second;
+}
+
 static void free_scene(pb200_ctx* c) {
     if (c->darena) { cudaFree(c->darena); c->darena = nullptr; c->darena_bytes = 0; }
     if (c->arena) { cudaFree(c->arena); c->arena = nullptr; c->arena_bytes = 0; }
@@ -191,11 +206,19 @@ int pb200_host_alloc(size_t bytes, void** out) {
     *out = nullptr;
     cudaError_t e = cudaMallocHost(out, bytes ? bytes : 1);
     if (e != cudaSuccess) return fail(nullptr, PB200_ERR_CUDA, "cudaMallocHost(%zu): %s", bytes, cudaGetErrorString(e));
+    {
+        std::lock_guard<std::mutex> lock(g_pinned_mutex);
+        g_pinned[reinterpret_cast<uintptr_t>(*out)] = bytes ? bytes : 1;
+    }
     return PB200_OK;
 }
 
 int pb200_host_free(void* p) {
     if (!p) return PB200_OK;
+    {
+        std::lock_guard<std::mutex> lock(g_pinned_mutex);
+        g_pinned.erase(reinterpret_cast<uintptr_t>(p));
+    }
     cudaError_t e = cudaFreeHost(p);
     if (e != cudaSuccess) return fail(nullptr, PB200_ERR_CUDA, "cudaFreeHost: %s", cudaGetErrorString(e));
     return PB200_OK;
@@ -322,14 +345,37 @@ extern "C" int pb200_set_scene(pb200_ctx* c, const pb200_scene* s) {
         PB_CUDA(c, cudaMallocHost(&c->stage, plan.total));
         c->stage_bytes = plan.total;
     }
-    for (const auto& it : plan.items) memcpy(static_cast<char*>(c->stage) + it.offset, it.src, it.bytes);
     if (plan.total > c->arena_bytes) {
         if (c->arena) PB_CUDA(c, cudaFree(c->arena));
         c->arena = nullptr; c->arena_bytes = 0;
         PB_CUDA(c, cudaMalloc(&c->arena, plan.total));
         c->arena_bytes = plan.total;
     }
-    PB_CUDA(c, cudaMemcpyAsync(c->arena, c->stage, plan.total, cudaMemcpyHostToDevice, c->stream));
+    {   // large arrays that already lie in page-locked memory of pb200_host_alloc (the sigma tables built by
+        // pb200_voigt_sigma through the Python mirror) go to the device from where they are; everything
+        // else is gathered in the staging buffer and sent as runs of consecutive items
+        size_t run_lo = 0, run_hi = 0;   // staged byte range not yet sent
+        auto flush_run = [&]() -> cudaError_t {
+            if (run_hi == run_lo) return cudaSuccess;
+            cudaError_t e = cudaMemcpyAsync(static_cast<char*>(c->arena) + run_lo, static_cast<char*>(c->stage) + run_lo,
+                                            run_hi - run_lo, cudaMemcpyHostToDevice, c->stream);
+            run_lo = run_hi;
+            return e;
+        };
+        for (const auto& it : plan.items) {
+            if (it.bytes >= (64u << 10) && is_pinned(it.src, it.bytes)) {
+                PB_CUDA(c, flush_run());
+                PB_CUDA(c, cudaMemcpyAsync(static_cast<char*>(c->arena) + it.offset, it.src, it.bytes,
+                                           cudaMemcpyHostToDevice, c->stream));
+                run_lo = run_hi = it.offset + ((it.bytes + 255) & ~size_t(255));
+            } else {
+                memcpy(static_cast<char*>(c->stage) + it.offset, it.src, it.bytes);
+                run_hi = it.offset + ((it.bytes + 255) & ~size_t(255));
+            }
+        }
+        if (run_hi > plan.total) run_hi = plan.total;
+        PB_CUDA(c, flush_run());
+    }
 
     void* A = c->arena;
     h.x = at<double>(A, o_x); h.rho = at<double>(A, o_rho); h.sin_phi = at<double>(A, o_sin);

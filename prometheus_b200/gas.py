@@ -227,7 +227,9 @@ class AtmosphericConstituent:
         fine.resolutionHigh /= self.wavelengthGridRefinement
         fine.lower_w *= (1.0 - self.wavelengthGridExtension)
         fine.upper_w *= (1.0 + self.wavelengthGridExtension)
-        lam = fine.constructWavelengthGridSingle(self)
+        grid = fine.constructWavelengthGridSingle(self)
+        lam = capi.pinned_pool.empty(grid.shape)     # page-locked like log_sigma: uploaded without a staging copy
+        lam[...] = grid
         lam0, gamma, f = self.getLineParameters(lam)
         _, log_sigma = host.get_context().voigt_sigma(lam0, gamma, f, self.sigma_v, lam, self.lookupOffset, want_log=True)
         return host.TableFunction1D(lam, log_sigma, fill_value=np.log10(self.lookupOffset))
