@@ -525,6 +525,12 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     if (want < 1) want = 1;
     prm.tiles_per_split = (int)((n_tiles + want - 1) / want);
     prm.n_split = (n_tiles + prm.tiles_per_split - 1) / prm.tiles_per_split;
+    {
+        const char* mt = getenv("PB200_MIN_TILES");   // tuning experiments only
+        prm.min_tiles = mt ? atoi(mt) : 1;
+        prm.culled = c->general_path ? 0 : 1;
+        if (prm.min_tiles < 1) prm.min_tiles = 1;
+    }
 
     const size_t r_bytes = R_in_scratch ? (size_t)((n_out * sizeof(double) + 255) & ~255ll) : 0;
     const size_t part_bytes = prm.n_split > 1 ? (size_t)prm.n_split * n_out * sizeof(double) : 0;

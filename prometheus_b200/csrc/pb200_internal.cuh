@@ -71,13 +71,26 @@ struct DevScene {
     unsigned long long* stat;   // [2]: [0] low word = tabulated-density out-of-grid flag, [1] active records of the run
 };
 
+// kernel (c'): tiles per working CTA and number of working splits of a phase with n_act active tiles
+__host__ __device__ inline int pb_tiles_per_split(int n_act, int n_split, int min_tiles) {
+    const int tps = (n_act + n_split - 1) / n_split;
+    return tps < min_tiles ? min_tiles : tps;
+}
+__host__ __device__ inline int pb_splits_used(int n_act, int n_split, int min_tiles) {
+    const int tps = pb_tiles_per_split(n_act, n_split, min_tiles);
+    return (n_act + tps - 1) / tps;
+}
+
 // launch parameters of kernel (c') and its variants
 struct TransitParams {
     int phase_lo, n_phase;
     int64_t wav_lo, n_wav_sel;
     int n_split;          // chord-axis splits (gridDim.z)
-    int tiles_per_split;  // kChordTile-chord tiles per split
-    double* partial;      // [n_split][n_phase][n_wav_sel] sums of w_in*exp(-tau)  (n_split > 1)
+    int tiles_per_split;  // kChordTile-chord tiles per split (kernel (m); kernel (c') shares the ACTIVE tiles, see below)
+    int min_tiles;        // kernel (c'): least number of active tiles a working CTA takes
+    int culled;           // 1: kernel (c') (w0 / n_act valid), 0: kernel (m)
+    double* partial;      // [n_split][n_phase][n_wav_sel] sums of w_in*exp(-tau)  (n_split > 1); kernel (c') only writes
+                          // the slots of splits that have tiles (pb_splits_used)
     double* R;            // [n_phase][n_wav_sel] final ratio
     double* nsig;         // [n_atoms][n_phase][n_wav_sel] -sigma_a(p, w) * 4096/ln2 (sigma_phase_kernel)
 };

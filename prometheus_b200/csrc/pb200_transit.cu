@@ -165,27 +165,25 @@ transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
     // this CTA's share of the phase's ACTIVE tiles (compact_kernel): even shares, at least 4 tiles per
     // working CTA so that the table load and the prologue stay amortised; CTAs beyond the need store zeros
     const int n_act = sc.n_act[p];
-    int tps = (n_act + prm.n_split - 1) / prm.n_split;
-    if (tps < 4) tps = 4;
+    const int tps = pb_tiles_per_split(n_act, prm.n_split, prm.min_tiles);
     const int tile0 = split * tps;
     int n_tiles = n_act - tile0;
     if (n_tiles > tps) n_tiles = tps;
     const int64_t w_base = (int64_t)blockIdx.x * (THREADS * WPT) + tid;     // relative to wav_lo
-    if (n_tiles <= 0) {   // nothing to do (CTA-uniform): F_in partial = 0, or R = w0 / F_out for the only split
+    if (n_tiles <= 0) {   // nothing to do (CTA-uniform): finalize_kernel skips this split; R = w0 / F_out for the only split
+        if (prm.n_split > 1) return;
 #pragma unroll
         for (int j = 0; j < WPT; ++j) {
             const int64_t w = w_base + (int64_t)j * THREADS;
             if (w >= prm.n_wav_sel) continue;
             const int64_t o = (int64_t)blockIdx.y * prm.n_wav_sel + w;
-            if (prm.n_split == 1) {
+            {
                 double v = sc.w0[p] / sc.fout[0];
                 for (int a = 0; a < S; ++a) {   // NaN cross-section: the reference propagates NaN into R
                     const double ns = __ldg(prm.nsig + ((int64_t)a * prm.n_phase + blockIdx.y) * prm.n_wav_sel + w);
                     if (ns != ns) v = ns;
                 }
                 prm.R[o] = v;
-            } else {
-                prm.partial[(int64_t)split * prm.n_phase * prm.n_wav_sel + o] = 0.0;
             }
         }
         return;
@@ -280,8 +278,10 @@ __global__ void finalize_kernel(const DevScene* __restrict__ scp, const TransitP
     const DevScene& sc = *scp;
     const int64_t n = (int64_t)prm.n_phase * prm.n_wav_sel;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-        double s = sc.w0[prm.phase_lo + i / prm.n_wav_sel];                     // transparent chords
-        for (int k = 0; k < prm.n_split; ++k) s += prm.partial[(int64_t)k * n + i];
+        const int p = prm.phase_lo + (int)(i / prm.n_wav_sel);
+        double s = prm.culled ? sc.w0[p] : 0.0;                                 // transparent chords
+        const int used = prm.culled ? pb_splits_used(sc.n_act[p], prm.n_split, prm.min_tiles) : prm.n_split;
+        for (int k = 0; k < used; ++k) s += prm.partial[(int64_t)k * n + i];
         const double fout = sc.fout[sc.fout_per_wav ? prm.wav_lo + i % prm.n_wav_sel : 0];
         prm.R[i] = s / fout;
     }
