@@ -123,6 +123,9 @@ typedef struct {
     int64_t executed_samples;    /* samples kernel (c') evaluated: transparent chords (tau <
                                     2^-54 at every wavelength, exp(-tau) == 1.0) and blocked
                                     chords are summed without an exp; -1 = not yet known     */
+    int64_t exp_samples;         /* of those, samples that went through the table exp (the
+                                    others were optically thin for their warp: tau < 2.1e-5,
+                                    second-order expansion summed per chord); upper bound    */
 } pb200_timing;
 
 typedef struct pb200_ctx pb200_ctx;

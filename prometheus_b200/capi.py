@@ -70,7 +70,8 @@ class Scene(C.Structure):
 class Timing(C.Structure):
     _fields_ = [("upload_ms", C.c_double), ("column_ms", C.c_double), ("transit_ms", C.c_double),
                 ("finalize_ms", C.c_double), ("download_ms", C.c_double),
-                ("launches", C.c_int64), ("samples", C.c_int64), ("executed_samples", C.c_int64)]
+                ("launches", C.c_int64), ("samples", C.c_int64), ("executed_samples", C.c_int64),
+                ("exp_samples", C.c_int64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

@@ -30,9 +30,9 @@ void launch_number_density_chords(const DevScene*, int scenario, int64_t n, cons
 cudaError_t launch_transit(const DevScene*, int n_atoms, const TransitParams&, cudaStream_t);
 cudaError_t launch_transit_general(const DevScene*, const DevScene& host_copy, const TransitParams&, int sm_count,
                                    cudaStream_t, int* n_launch);
-int transit_cta_wavelengths(int n_atoms);
 void launch_sigma_phase(const DevScene*, const TransitParams&, cudaStream_t);
 void launch_compact(const DevScene*, int phase_lo, int n_phase, bool cull, cudaStream_t);
+cudaError_t launch_window_order(const DevScene*, const TransitParams&, int* order, cudaStream_t);
 void launch_finalize(const DevScene*, const TransitParams&, int sm_count, cudaStream_t);
 void launch_sigma_lookup(const double*, const double*, int64_t, double, const double*, int64_t, double*, int,
                          cudaStream_t);
@@ -75,6 +75,7 @@ struct pb200_ctx {
     size_t scratch_bytes = 0;
     int* d_oob = nullptr;        // 16 bytes: [0] out-of-grid flag (int), [8..16) active chord records of the last run
     int64_t last_n_wav_sel = 0;
+    int last_wpt = 8;
     double* d_exp_tab = nullptr; // 2^(j/64), j < 64
     cudaEvent_t ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // 6,7: scene upload
     pb200_timing last = {};
@@ -151,8 +152,8 @@ int pb200_create(int device, pb200_ctx** out) {
     if (e == cudaSuccess) { c->own_stream = true; e = cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device); }
     for (int i = 0; i < 8 && e == cudaSuccess; ++i) e = cudaEventCreate(&c->ev[i]);
     if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_scene, sizeof(DevScene));
-    if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_oob, 16);   // [0] out-of-grid flag, [8..16) active records of the run
-    if (e == cudaSuccess) e = cudaMemset(c->d_oob, 0, 16);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_oob, 32);   // [0] out-of-grid flag, [8..16) active records, [16..24) thick (warp, chord) pairs of the run
+    if (e == cudaSuccess) e = cudaMemset(c->d_oob, 0, 32);
     if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_exp_tab, (kExpTabEntries + kExpBigEntries) * sizeof(double));
     if (e == cudaSuccess) {
         double tab[kExpTabEntries];
@@ -427,11 +428,12 @@ extern "C" int pb200_set_scene(pb200_ctx* c, const pb200_scene* s) {
     wants.push_back({&h.star_shift, (size_t)h.Mp});
     wants.push_back({&h.w_in, (size_t)h.n_orb * h.Mp});
     wants.push_back({&h.ncol, (size_t)n_atoms * h.n_orb * h.Mp});
-    wants.push_back({&h.rec, (size_t)(n_atoms + 3) * h.n_orb * h.Mp});
+    wants.push_back({&h.rec, (size_t)pb_rec_stride(n_atoms) * h.n_orb * h.Mp});
     wants.push_back({&nmax_d, (size_t)(n_atoms ? n_atoms : 1) * h.n_orb});
     wants.push_back({&smax_d, (size_t)(n_atoms ? n_atoms : 1) * h.n_orb});
     wants.push_back({&nact_d, (size_t)(h.n_orb + 1) / 2});
     wants.push_back({&h.w0, (size_t)h.n_orb});
+    wants.push_back({&h.thin_tot, (size_t)h.n_orb * 8});
     for (int i = 0; i < s->n_scenarios; ++i)
         if (h.scen[i].density_slot >= 0)
             wants.push_back({&h.density[h.scen[i].density_slot], (size_t)h.n_orb * h.M * h.n_x});
@@ -516,7 +518,9 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     TransitParams prm;
     prm.phase_lo = phase_lo; prm.n_phase = n_phase; prm.wav_lo = wav_lo; prm.n_wav_sel = n_wav_sel;
     const int n_tiles = h.Mp / kChordTile;
-    const int cta_wav = c->general_path ? 128 : transit_cta_wavelengths(h.n_atoms);
+    // wavelengths per CTA: kernel (m) 128; kernel (c') one window of 32 * WPT (WPT = 8, 4, 2 for <= 2, <= 4, more absorbers)
+    int cta_wav = c->general_path ? 128 : 32 * (h.n_atoms <= 2 ? 8 : h.n_atoms <= 4 ? 4 : 2);
+    if (h.n_atoms == 2 && getenv("PB200_WPT2")) cta_wav = 32 * 4;
     const int64_t ctas = ((n_wav_sel + cta_wav - 1) / cta_wav) * n_phase;
     // many more CTAs than resident slots (~10 per SM) so that the last wave is a small fraction of the
     // run; a CTA keeps at least 4 tiles (1024 chords) to amortise its sigma-lookup prologue
@@ -535,17 +539,23 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     const size_t r_bytes = R_in_scratch ? (size_t)((n_out * sizeof(double) + 255) & ~255ll) : 0;
     const size_t part_bytes = prm.n_split > 1 ? (size_t)prm.n_split * n_out * sizeof(double) : 0;
     const size_t nsig_bytes = c->general_path ? 0 : (size_t)h.n_atoms * n_out * sizeof(double);
-    int rc = ensure_scratch(c, r_bytes + part_bytes + nsig_bytes + 256);
+    prm.win = 32 * (h.n_atoms <= 2 ? 8 : h.n_atoms <= 4 ? 4 : 2);
+    if (h.n_atoms == 2 && getenv("PB200_WPT2")) prm.win = 32 * 4;   // tuning experiment
+    prm.n_win = (int)((n_wav_sel + prm.win - 1) / prm.win);
+    const size_t order_bytes = c->general_path ? 0 : (((size_t)n_phase * prm.n_win * sizeof(int) + 255) & ~size_t(255));
+    int rc = ensure_scratch(c, r_bytes + part_bytes + nsig_bytes + order_bytes + 256);
     if (rc) return rc;
     prm.R = R_in_scratch ? c->scratch : R_dev;
     prm.partial = reinterpret_cast<double*>(reinterpret_cast<char*>(c->scratch) + r_bytes);
     prm.nsig = reinterpret_cast<double*>(reinterpret_cast<char*>(c->scratch) + r_bytes + part_bytes);
+    int* order = reinterpret_cast<int*>(reinterpret_cast<char*>(c->scratch) + r_bytes + part_bytes + nsig_bytes);
+    prm.order = order;
 
     PB_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
     if (!c->general_path) {   // sigma(p, w) of the tile and its per-phase maxima, needed by the culling below
         if (h.n_atoms < 1) return fail(c, PB200_ERR_INVALID, "scene has no absorbing constituent");
         PB_CUDA(c, cudaMemsetAsync(h.smax, 0, (size_t)h.n_atoms * h.n_orb * sizeof(double), c->stream));
-        PB_CUDA(c, cudaMemsetAsync(reinterpret_cast<char*>(c->d_oob) + 8, 0, 8, c->stream));
+        PB_CUDA(c, cudaMemsetAsync(reinterpret_cast<char*>(c->d_oob) + 8, 0, 24, c->stream));
         launch_sigma_phase(c->d_scene, prm, c->stream);
         c->launches += 1;
     }
@@ -558,7 +568,8 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     c->launches += 1;
     if (!c->general_path) {   // chord records of kernel (c'), transparent chords culled
         launch_compact(c->d_scene, phase_lo, n_phase, cull, c->stream);
-        c->launches += 1;
+        PB_CUDA(c, launch_window_order(c->d_scene, prm, order, c->stream));
+        c->launches += 2;
     }
     PB_CUDA(c, cudaGetLastError());
     PB_CUDA(c, cudaEventRecord(c->ev[3], c->stream));
@@ -588,6 +599,8 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     c->last.launches = c->launches - launches0;
     c->last.samples = (int64_t)n_phase * h.M * n_wav_sel;
     c->last.executed_samples = c->general_path ? c->last.samples : -1;   // known after the next synchronisation
+    c->last.exp_samples = c->last.executed_samples;
+    c->last_wpt = prm.win / 32;   // wavelengths per thread of kernel (c')
     c->last_n_wav_sel = n_wav_sel;
     return PB200_OK;
 }
@@ -608,11 +621,14 @@ int collect_timing(pb200_ctx* c) {
 }
 
 int check_oob(pb200_ctx* c) {
-    unsigned long long st[2] = {0, 0};
+    unsigned long long st[4] = {0, 0, 0, 0};
     PB_CUDA(c, cudaMemcpyAsync(st, c->d_oob, sizeof st, cudaMemcpyDeviceToHost, c->stream));
     PB_CUDA(c, cudaStreamSynchronize(c->stream));
     const int flag = (int)(st[0] & 0xffffffffull);
-    if (c->last.executed_samples < 0) c->last.executed_samples = (int64_t)st[1] * c->last_n_wav_sel;
+    if (c->last.executed_samples < 0) {
+        c->last.executed_samples = (int64_t)st[1] * c->last_n_wav_sel;
+        c->last.exp_samples = (int64_t)st[2] * 32 * c->last_wpt;   // a warp owns 32 * WPT wavelengths
+    }
     if (flag) {
         PB_CUDA(c, cudaMemsetAsync(c->d_oob, 0, sizeof(int), c->stream));
         return fail(c, PB200_ERR_BOUNDS, "tabulated density queried outside its grid (the reference raises ValueError)");

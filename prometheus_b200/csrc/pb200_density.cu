@@ -287,7 +287,7 @@ constexpr int kCompactThreads = 1024;
 __global__ void __launch_bounds__(kCompactThreads) compact_kernel(const DevScene* __restrict__ scp, int phase_lo, int cull) {
     const DevScene& sc = *scp;
     const int p = phase_lo + blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const int S = sc.n_atoms, R = S + 3;
+    const int S = sc.n_atoms, R = pb_rec_stride(S);
     __shared__ double s_smax[16];
     __shared__ int s_warp[32];
     __shared__ double s_part[32];
@@ -301,6 +301,7 @@ __global__ void __launch_bounds__(kCompactThreads) compact_kernel(const DevScene
     const int64_t row0 = (int64_t)p * sc.Mp;
     double* rec_row = sc.rec + row0 * R;
     double w0 = 0.0;
+    double tt[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};   // this thread's share of thin_tot
     // mirror pairing (sc.mirror, set by pb200_set_scene when it holds): every body and density centre lies in
     // the plane z = 0 and every density depends on z through z^2 only, so the chords (phi, rho) and
     // (pi - phi, rho) have the same column densities; with an even, mirror-symmetric phi axis they are grid
@@ -353,8 +354,20 @@ __global__ void __launch_bounds__(kCompactThreads) compact_kernel(const DevScene
         const int base = s_base;
         if (active) {
             double* r = rec_row + (int64_t)(base + s_warp[wid] + __popc(bal & ((1u << lane) - 1u))) * R;
-            r[0] = w; r[1] = w * kExpBigC1; r[2] = w * kExpBigC2;
+            const double w1 = w * kExpBigC1, w2 = w * kExpBigC2;
+            r[0] = w; r[1] = w1; r[2] = w2;
             for (int a = 0; a < S; ++a) r[3 + a] = sc.ncol[(int64_t)a * sc.n_orb * sc.Mp + row0 + m];
+            if (3 + S < R) r[3 + S] = 0.0;
+            if (S <= 2) {   // same operations as ThinSums::add of kernel (c')
+                const double N0 = r[3], N1 = (S == 2) ? r[4] : 0.0;
+                tt[0] += w;
+                tt[1] = fma(N0, w1, tt[1]);
+                tt[2] = fma(N1, w1, tt[2]);
+                const double t0 = N0 * w2, t1 = N1 * w2;
+                tt[3] = fma(t0, N0, tt[3]);
+                tt[4] = fma(t0, N1, tt[4]);
+                tt[5] = fma(t1, N1, tt[5]);
+            }
         }
         __syncthreads();
         if (tid == 0) s_base = base + (int)s_part[0];
@@ -363,17 +376,23 @@ __global__ void __launch_bounds__(kCompactThreads) compact_kernel(const DevScene
     const int n_rec = s_base;
     const int n_tiles = (n_rec + kChordTile - 1) / kChordTile;
     for (int i = n_rec * R + tid; i < n_tiles * kChordTile * R; i += kCompactThreads) rec_row[i] = 0.0;   // padding
-    // sum of the transparent weights, fixed order
-    w0 = pb_warp_sum(w0);
-    if (lane == 0) s_part[wid] = w0;
-    __syncthreads();
-    if (wid == 0) {
-        const double t = pb_warp_sum(s_part[lane]);
-        if (lane == 0) {
-            sc.w0[p] = t;
-            sc.n_act[p] = n_tiles;
-            atomicAdd(sc.stat + 1, (unsigned long long)n_tiles * kChordTile);
+    // sum of the transparent weights and the thin totals, fixed order
+#pragma unroll
+    for (int k = 0; k < 7; ++k) {
+        const double v = pb_warp_sum(k == 0 ? w0 : tt[k == 0 ? 0 : k - 1]);
+        __syncthreads();
+        if (lane == 0) s_part[wid] = v;
+        __syncthreads();
+        if (wid == 0) {
+            const double t = pb_warp_sum(s_part[lane]);
+            if (lane == 0) {
+                if (k == 0) sc.w0[p] = t; else sc.thin_tot[(int64_t)p * 8 + k - 1] = t;
+            }
         }
+    }
+    if (tid == 0) {
+        sc.n_act[p] = n_tiles;
+        atomicAdd(sc.stat + 1, (unsigned long long)n_tiles * kChordTile);
     }
 }
 

@@ -56,7 +56,7 @@ struct DevScene {
     double* ncol;         // [n_atoms][n_orb][Mp]  column densities
     double* density[kMaxScenarios];  // [n_orb][M][n_x] number density of molecular scenarios
     double* fout;         // [1] or [n_wav]  sum of unattenuated flux
-    // chord records of kernel (c'): [n_orb][<= Mp][n_atoms+3] = {w_in, w_in c1, w_in c2, Ncol_0 .. Ncol_{S-1}}, one TMA
+    // chord records of kernel (c'): [n_orb][<= Mp][pb_rec_stride(n_atoms)] = {w_in, w_in c1, w_in c2, Ncol_0 .. Ncol_{S-1}[, 0]}, one TMA
     // bulk copy per 256-chord tile
     double* rec;
     const double* exp_tab;   // [256] 2^(j/256) then [4096] 2^(j/4096), correctly rounded, high words biased (pb200_math.cuh)
@@ -68,8 +68,14 @@ struct DevScene {
     int mirror;                 // 1: chords (phi, rho) and (pi - phi, rho) share one record (see compact_kernel)
     int* n_act;                 // [n_orb] 256-chord tiles of active records
     double* w0;                 // [n_orb] sum of w_in over the transparent chords
+    double* thin_tot;           // [n_orb][8] sums over the ACTIVE chords of {w, N0 w c1, N1 w c1, N0^2 w c2, N0 N1 w c2,
+                                //   N1^2 w c2}: what kernel (c') needs for a window in which every chord is thin (S <= 2)
     unsigned long long* stat;   // [2]: [0] low word = tabulated-density out-of-grid flag, [1] active records of the run
 };
+
+// doubles per chord record of kernel (c'): {w, w c1, w c2, Ncol_0..Ncol_{S-1}} padded to an even count, so that a
+// record is a whole number of 16-byte shared-memory loads
+__host__ __device__ constexpr int pb_rec_stride(int n_atoms) { return (n_atoms + 4) & ~1; }
 
 // kernel (c'): tiles per working CTA and number of working splits of a phase with n_act active tiles
 __host__ __device__ inline int pb_tiles_per_split(int n_act, int n_split, int min_tiles) {
@@ -89,6 +95,9 @@ struct TransitParams {
     int tiles_per_split;  // kChordTile-chord tiles per split (kernel (m); kernel (c') shares the ACTIVE tiles, see below)
     int min_tiles;        // kernel (c'): least number of active tiles a working CTA takes
     int culled;           // 1: kernel (c') (w0 / n_act valid), 0: kernel (m)
+    int win;              // kernel (c'): wavelengths per warp window (32 * WPT)
+    int n_win;            // windows per phase = ceil(n_wav_sel / win)
+    const int* order;     // [n_phase][n_win] window indices sorted by decreasing optical thickness (window_order_kernel)
     double* partial;      // [n_split][n_phase][n_wav_sel] sums of w_in*exp(-tau)  (n_split > 1); kernel (c') only writes
                           // the slots of splits that have tiles (pb_splits_used)
     double* R;            // [n_phase][n_wav_sel] final ratio

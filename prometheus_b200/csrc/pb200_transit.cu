@@ -23,7 +23,6 @@
 
 namespace pb200 {
 
-constexpr int kRecExtra = 3;           // {w, w c1, w c2} in front of the S column densities
 
 // ---- mbarrier / TMA bulk-copy wrappers (PTX ISA 8.x, sm_90+) -----------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -96,26 +95,150 @@ __global__ void __launch_bounds__(256) sigma_phase_kernel(const DevScene* __rest
 
 // One 256-chord tile: acc[j] += w_m * exp(-sum_a N_a(m) sigma_a(j)) for the thread's WPT wavelengths.
 // `stage` is the shared-window address of the tile's records (explicit ld.shared: no generic->shared
-// address conversion inside the loop).  There is no branch on blocked chords or padding: their record
-// is all zeros (w = w c1 = w c2 = 0, N = 0), so they add T * 0 = +0 exactly (F_in = 0,
-// gasProperties.py:1233) -- a few per cent of wasted samples buy a branch-free loop body that ptxas
-// can software-pipeline across chords.
-template <int S, int WPT, bool CLAMP, int UNROLL = 2, int DROP = 0>
-__device__ __forceinline__ void transit_tile(uint32_t stage, const double (&nsig)[S][WPT], double (&acc)[WPT],
-                                             uint32_t tab_base) {
-    constexpr uint32_t kRecBytes = (S + kRecExtra) * sizeof(double);
-#pragma unroll UNROLL
-    for (int m = 0; m < kChordTile; ++m) {
-        const uint32_t rec = stage + m * kRecBytes;
-        double w0, w1, w2, N[S];
-        if constexpr (S == 1) {
-            lds_v2f64(rec, w0, w1);                                                // broadcast LDS.128 x 2
-            lds_v2f64(rec + 16, w2, N[0]);
-        } else {
-            w0 = lds_f64(rec); w1 = lds_f64(rec + 8); w2 = lds_f64(rec + 16);
+// address conversion inside the loop).  The padding records of the last tile are all zeros
+// (w = w c1 = w c2 = 0, N = 0): they take the thin path and add +0 exactly.
+// Order of the wavelength windows of a phase.  A warp of kernel (c') owns one window (32 * WPT consecutive
+// wavelengths) and the 8 warps of a CTA walk the chord tiles in lock step, so a CTA is as slow as its
+// thickest window: windows in a line core take the table exp on most chords, windows in the continuum take
+// the thin path on all of them.  CTAs are therefore formed from windows of similar optical thickness:
+// key = sum_a max_m Ncol_a(p, m) * max_{w in window} |nsig_a(p, w)| (the largest scaled tau of the window),
+// sorted in decreasing order by a bitonic network in shared memory (one CTA per phase; ties and the order of
+// equal keys do not matter for the results, only for the load balance).  More than kMaxWindows windows:
+// identity order.
+constexpr int kMaxWindows = 8192;
+__global__ void __launch_bounds__(1024) window_order_kernel(const DevScene* __restrict__ scp, const TransitParams prm,
+                                                            int* __restrict__ order, int n_pow2) {
+    const DevScene& sc = *scp;
+    extern __shared__ __align__(16) unsigned char wsm[];
+    double* key = reinterpret_cast<double*>(wsm);
+    int* idx = reinterpret_cast<int*>(key + n_pow2);
+    const int pi = blockIdx.x, p = prm.phase_lo + pi, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int S = sc.n_atoms;
+    int* out = order + (int64_t)pi * prm.n_win;
+    if (n_pow2 == 0) {   // too many windows to sort in shared memory
+        for (int i = tid; i < prm.n_win; i += blockDim.x) out[i] = i;
+        return;
+    }
+    for (int wdw = wid; wdw < n_pow2; wdw += 32) {   // one warp per window
+        double k = -1.0;                              // padding sorts last
+        if (wdw < prm.n_win) {
+            k = 0.0;
+            for (int a = 0; a < S; ++a) {
+                double mx = 0.0;
+                bool nan = false;
+                for (int64_t w = (int64_t)wdw * prm.win + lane; w < (int64_t)(wdw + 1) * prm.win && w < prm.n_wav_sel; w += 32) {
+                    const double v = fabs(__ldg(prm.nsig + ((int64_t)a * prm.n_phase + pi) * prm.n_wav_sel + w));
+                    nan |= (v != v);
+                    mx = fmax(mx, v);
+                }
 #pragma unroll
-            for (int a = 0; a < S; ++a) N[a] = lds_f64(rec + 24 + 8 * a);
+                for (int d = 16; d > 0; d >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, d));
+                if (__any_sync(0xffffffffu, nan)) mx = __longlong_as_double(0x7ff0000000000000ll);
+                const double nm = __longlong_as_double((long long)__ldg(sc.nmax + (int64_t)a * sc.n_orb + p));
+                k += (nm > 0.0) ? nm * mx : 0.0;
+            }
         }
+        if (lane == 0) { key[wdw] = k; idx[wdw] = wdw; }
+    }
+    __syncthreads();
+    for (int size = 2; size <= n_pow2; size <<= 1)
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            for (int i = tid; i < n_pow2; i += blockDim.x) {
+                const int j = i ^ stride;
+                if (j > i) {
+                    const bool desc = (i & size) == 0;
+                    const double ki = key[i], kj = key[j];
+                    const int ii = idx[i], ij = idx[j];
+                    // total order (key, then index) so that the result does not depend on the network
+                    const bool i_first = (ki > kj) || (ki == kj && ii < ij);
+                    if (i_first != desc) { key[i] = kj; key[j] = ki; idx[i] = ij; idx[j] = ii; }
+                }
+            }
+            __syncthreads();
+        }
+    for (int i = tid; i < prm.n_win; i += blockDim.x) out[i] = idx[i];
+}
+
+// Optically thin chords.  If sum_a N_a max|nsig_a| over the warp's wavelengths is below kThinV (tau < 2.1e-5),
+// then k = 0 and T = 1 for all of them and w exp(-tau) = w + v (w c1 + v w c2), v = sum_a N_a nsig_a, with a
+// truncation error tau^3/6 < 1.6e-15.  For one or two absorbers that polynomial separates into chord sums that
+// do not depend on the wavelength,
+//     sum_m w_m exp(-tau_mj) = SW + nsig_j (SA + nsig_j SB),   SW = sum w, SA = sum N w c1, SB = sum N^2 w c2,
+// so a thin chord costs 4 FP64 instructions per THREAD (8 for two absorbers) instead of 6 FP64 + 4 integer
+// per SAMPLE; the sums are applied to the accumulators once, after the last tile (ThinSums::finish).  The
+// test is warp-uniform (N is a broadcast, the maxima are warp-wide), so the loop never diverges.
+constexpr double kThinV = 0.125;
+template <int S>
+struct ThinSums {
+    double sw = 0.0, sa[S <= 2 ? S : 1] = {}, sb[S == 1 ? 1 : 3] = {};
+    int thick = 0;   // chords of this warp that took the full path (statistics)
+    __device__ __forceinline__ void add(double w0, double w1, double w2, const double (&N)[S]) {
+        sw += w0;
+        if constexpr (S == 1) {
+            sa[0] = fma(N[0], w1, sa[0]);
+            sb[0] = fma(N[0] * N[0], w2, sb[0]);
+        } else if constexpr (S == 2) {
+            sa[0] = fma(N[0], w1, sa[0]);
+            sa[1] = fma(N[1], w1, sa[1]);
+            const double t0 = N[0] * w2, t1 = N[1] * w2;
+            sb[0] = fma(t0, N[0], sb[0]);
+            sb[1] = fma(t0, N[1], sb[1]);
+            sb[2] = fma(t1, N[1], sb[2]);
+        }
+    }
+    template <int WPT>
+    __device__ __forceinline__ void finish(const double (&nsig)[S][WPT], double (&acc)[WPT]) const {
+        if constexpr (S == 1) {
+#pragma unroll
+            for (int j = 0; j < WPT; ++j) acc[j] += fma(nsig[0][j], fma(nsig[0][j], sb[0], sa[0]), sw);
+        } else if constexpr (S == 2) {
+#pragma unroll
+            for (int j = 0; j < WPT; ++j) {
+                const double a = nsig[0][j], b = nsig[1][j];
+                double q = fma(a, sa[0], sw);
+                q = fma(b, sa[1], q);
+                q = fma(a * a, sb[0], q);
+                q = fma(2.0 * a * b, sb[1], q);
+                acc[j] += fma(b * b, sb[2], q);
+            }
+        }
+    }
+};
+
+template <int S, int WPT, bool CLAMP, int NWARPS, int UNROLL = 2, int DROP = 0>
+__device__ __forceinline__ void transit_tile(uint32_t stage, const double (&nsig)[S][WPT], double (&acc)[WPT],
+                                             uint32_t tab_base, const double (&smw)[S], ThinSums<S>& thin, int wid) {
+    constexpr int R = pb_rec_stride(S);
+    constexpr uint32_t kRecBytes = R * sizeof(double);
+    // the warps of the CTA share the window (same wavelengths) and split the chords: warp w takes chords
+    // w, w + NWARPS, ... of the tile
+#pragma unroll UNROLL
+    for (int i = 0; i < kChordTile / NWARPS; ++i) {
+        const uint32_t rec = stage + (uint32_t)(i * NWARPS + wid) * kRecBytes;
+        double d[R], N[S];
+#pragma unroll
+        for (int i = 0; i < R / 2; ++i) lds_v2f64(rec + 16 * i, d[2 * i], d[2 * i + 1]);   // broadcast LDS.128
+        const double w0 = d[0], w1 = d[1], w2 = d[2];
+#pragma unroll
+        for (int a = 0; a < S; ++a) N[a] = d[3 + a];
+        double bound = N[0] * smw[0];
+#pragma unroll
+        for (int a = 1; a < S; ++a) bound = fma(N[a], smw[a], bound);
+        if (bound < kThinV) {   // warp-uniform
+            if constexpr (S <= 2) {
+                thin.add(w0, w1, w2, N);
+            } else {
+#pragma unroll
+                for (int j = 0; j < WPT; ++j) {
+                    double v = N[0] * nsig[0][j];
+#pragma unroll
+                    for (int a = 1; a < S; ++a) v = fma(N[a], nsig[a][j], v);
+                    acc[j] += fma(fma(v, w2, w1), v, w0);
+                }
+            }
+            continue;
+        }
+        ++thin.thick;
 #pragma unroll
         for (int j = 0; j < WPT; ++j) {
             double t, r;
@@ -133,11 +256,7 @@ __device__ __forceinline__ void transit_tile(uint32_t stage, const double (&nsig
                 t = v + kExpMagic;
                 r = v - (t - kExpMagic);
             }
-            double T;
-            if constexpr (DROP == 0) T = pb_exp_big_load(tab_base, __double2loint(t));
-            else if constexpr (DROP == 1) T = __hiloint2double(0x3ff00000 + (__double2loint(t) << 8), 0);           // no LOP3/LEA/LDS
-            else if constexpr (DROP == 2) { int lo_, hi_; asm volatile("{.reg .b32 j, a; and.b32 j, %2, 4095; mad.lo.u32 a, j, 8, %3; ld.shared.v2.b32 {%0, %1}, [a];}" : "=r"(lo_), "=r"(hi_) : "r"(__double2loint(t)), "r"(tab_base)); T = __hiloint2double(hi_, lo_); }   // no IMAD
-            else T = __hiloint2double(0x3ff00000, __double2loint(t));                                                  // FP64 only
+            const double T = pb_exp_big_load(tab_base, __double2loint(t));
             double q = fma(r, w2, w1);
             q = fma(q, r, w0);                                                     // w exp(r ln2/4096)
             acc[j] = fma(T, q, acc[j]);                                            // :1241, :1244/:1255
@@ -145,130 +264,146 @@ __device__ __forceinline__ void transit_tile(uint32_t stage, const double (&nsig
     }
 }
 
-// S atomic constituents (compile time), WPT wavelengths per thread, THREADS threads per CTA
+// S atomic constituents (compile time), WPT wavelengths per thread, THREADS threads per CTA.
+// One CTA = one wavelength window (32 * WPT consecutive wavelengths) x one phase x one chord-axis split.
+// All warps of the CTA hold the SAME wavelengths (lane = fastest index, j = 32-wavelength group) and split
+// the chords of every tile between them, so they see the same mix of thin and thick chords and stay in
+// step; their partial sums are added in a fixed order at the end.  Windows are taken in decreasing order of
+// optical thickness (window_order_kernel: longest CTAs first).  A window that is thin for every chord of
+// the phase (S <= 2) needs no chord loop at all: its sums are the per-phase totals of compact_kernel.
 template <int S, int WPT, int THREADS, int VAR = 0>
-__global__ void __launch_bounds__(THREADS, (VAR & 1) ? 4 : (THREADS == 256 ? 3 : 6))
+__global__ void __launch_bounds__(THREADS, (VAR & 1) ? 4 : (THREADS == 256 ? (S == 1 ? 3 : 2) : 6))
 transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
     const DevScene& sc = *scp;
-    // shared memory: exp table [4096] | stage 0 records | stage 1 records; a stage holds kChordTile records
+    // shared memory: exp table [4096] | stage 0 records | stage 1 records | per-warp sums [NWARPS][WIN]
     extern __shared__ __align__(128) double smem[];
     __shared__ uint64_t full_bar[2];
-    constexpr int R = S + kRecExtra;
+    constexpr int NWARPS = THREADS / 32, WIN = 32 * WPT;
+    constexpr int R = pb_rec_stride(S);
     constexpr int kStageDoubles = R * kChordTile;
     constexpr uint32_t kStageBytes = kStageDoubles * sizeof(double);
     double* etab = smem;
     double* stages = smem + kExpBigEntries;
+    double* red = stages + 2 * kStageDoubles;
 
-    const int tid = threadIdx.x;
-    const int p = prm.phase_lo + blockIdx.y;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int pi = blockIdx.y, p = prm.phase_lo + pi;
     const int split = blockIdx.z;
-    // this CTA's share of the phase's ACTIVE tiles (compact_kernel): even shares, at least 4 tiles per
-    // working CTA so that the table load and the prologue stay amortised; CTAs beyond the need store zeros
+    const int window = __ldg(prm.order + (int64_t)pi * prm.n_win + blockIdx.x);
+    const int64_t win_lo = (int64_t)window * WIN;                         // relative to wav_lo
+    // this CTA's share of the phase's ACTIVE tiles (compact_kernel): even shares over the splits, at least
+    // prm.min_tiles per working CTA; splits beyond the need have nothing to do
     const int n_act = sc.n_act[p];
     const int tps = pb_tiles_per_split(n_act, prm.n_split, prm.min_tiles);
     const int tile0 = split * tps;
     int n_tiles = n_act - tile0;
     if (n_tiles > tps) n_tiles = tps;
-    const int64_t w_base = (int64_t)blockIdx.x * (THREADS * WPT) + tid;     // relative to wav_lo
-    if (n_tiles <= 0) {   // nothing to do (CTA-uniform): finalize_kernel skips this split; R = w0 / F_out for the only split
-        if (prm.n_split > 1) return;
-#pragma unroll
-        for (int j = 0; j < WPT; ++j) {
-            const int64_t w = w_base + (int64_t)j * THREADS;
-            if (w >= prm.n_wav_sel) continue;
-            const int64_t o = (int64_t)blockIdx.y * prm.n_wav_sel + w;
-            {
-                double v = sc.w0[p] / sc.fout[0];
-                for (int a = 0; a < S; ++a) {   // NaN cross-section: the reference propagates NaN into R
-                    const double ns = __ldg(prm.nsig + ((int64_t)a * prm.n_phase + blockIdx.y) * prm.n_wav_sel + w);
-                    if (ns != ns) v = ns;
-                }
-                prm.R[o] = v;
-            }
-        }
-        return;
-    }
+    if (n_tiles <= 0 && prm.n_split > 1) return;   // finalize_kernel skips this split (pb_splits_used)
 
-    if (tid == 0) {
-        mbar_init(&full_bar[0], 1);
-        mbar_init(&full_bar[1], 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    __syncthreads();
-    const double* rec_row = sc.rec + ((int64_t)p * sc.Mp + (int64_t)tile0 * kChordTile) * R;
-    auto issue = [&](int tile, int stage) {
-        mbar_expect_tx(&full_bar[stage], kStageBytes);
-        tma_bulk_g2s(stages + stage * kStageDoubles, rec_row + (int64_t)tile * kStageDoubles, kStageBytes,
-                     &full_bar[stage]);
-    };
-    if (tid == 0 && n_tiles > 0) issue(0, 0);
-    {   // the exp table: 32 KB from L2, 16-byte loads
-        const double2* src = reinterpret_cast<const double2*>(sc.exp_tab + kExpTabEntries);
-        double2* dst = reinterpret_cast<double2*>(etab);
-        for (int i = tid; i < kExpBigEntries / 2; i += THREADS) dst[i] = __ldg(src + i);
-    }
-
-    // ---- prologue: -sigma_a(p, w) 4096/ln2 for this thread's wavelengths ---------------------------
+    // ---- prologue: -sigma_a(p, w) 4096/ln2 of the window (every warp loads the same values) ---------
     double nsig[S][WPT];
     double acc[WPT];
     bool bad = false;   // NaN cross-section (NaN wavelength): the reference propagates NaN into R
 #pragma unroll
     for (int j = 0; j < WPT; ++j) {
         acc[j] = 0.0;
-        const int64_t w = w_base + (int64_t)j * THREADS;
+        const int64_t w = win_lo + j * 32 + lane;
         const bool live = w < prm.n_wav_sel;
 #pragma unroll
         for (int a = 0; a < S; ++a) {
-            const double v = live ? __ldg(prm.nsig + ((int64_t)a * prm.n_phase + blockIdx.y) * prm.n_wav_sel + w) : 0.0;
+            const double v = live ? __ldg(prm.nsig + ((int64_t)a * prm.n_phase + pi) * prm.n_wav_sel + w) : 0.0;
             bad |= (v != v);
             nsig[a][j] = v;
         }
     }
+    // window-wide max |nsig_a| for the thin test (NaN -> +inf: never thin), the largest scaled tau of the
+    // window on the densest chord of the phase, and from it: does any chord need the clamped exp
+    // (tau > 690), does any chord need the exp at all
+    double smw[S];
+    double key = 0.0;
+    const bool any_bad = __any_sync(0xffffffffu, bad);
+#pragma unroll
+    for (int a = 0; a < S; ++a) {
+        double mx = 0.0;
+#pragma unroll
+        for (int j = 0; j < WPT; ++j) mx = fmax(mx, fabs(nsig[a][j]));
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, d));
+        smw[a] = any_bad ? __longlong_as_double(0x7ff0000000000000ll) : mx;
+        key = fma(__longlong_as_double((long long)__ldg(sc.nmax + (int64_t)a * sc.n_orb + p)), smw[a], key);
+    }
+    const bool clamp = !(key < kExpBigClampDecision);   // NaN -> clamped variant (harmless)
+    const bool all_thin = (S <= 2) && (key < kThinV);
+    ThinSums<S> thin;
 
-    // A warp needs the clamped exp only if one of its wavelengths can reach tau > 690 on the densest
-    // chord of this phase (warp-uniform choice, so the two loop variants never diverge).
-    bool clamp = false;
+    if (n_tiles > 0 && !all_thin) {
+        if (tid == 0) {
+            mbar_init(&full_bar[0], 1);
+            mbar_init(&full_bar[1], 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncthreads();
+        const double* rec_row = sc.rec + ((int64_t)p * sc.Mp + (int64_t)tile0 * kChordTile) * R;
+        auto issue = [&](int tile, int stage) {
+            mbar_expect_tx(&full_bar[stage], kStageBytes);
+            tma_bulk_g2s(stages + stage * kStageDoubles, rec_row + (int64_t)tile * kStageDoubles, kStageBytes,
+                         &full_bar[stage]);
+        };
+        if (tid == 0) issue(0, 0);
+        {   // the exp table: 32 KB from L2, 16-byte loads
+            const double2* src = reinterpret_cast<const double2*>(sc.exp_tab + kExpTabEntries);
+            double2* dst = reinterpret_cast<double2*>(etab);
+            for (int i = tid; i < kExpBigEntries / 2; i += THREADS) dst[i] = __ldg(src + i);
+        }
+        __syncthreads();   // exp table complete
+        // laundered through an opaque mov so that the address lives in a register instead of being
+        // re-derived (S2UR CgaCtaId + ULEA) for every chord
+        uint32_t tab_base;
+        asm volatile("mov.u32 %0, %1;" : "=r"(tab_base) : "r"(smem_u32(etab)));
+        const uint32_t stages_addr = smem_u32(stages);
+        for (int t = 0; t < n_tiles; ++t) {
+            const int stage = t & 1;
+            if (tid == 0 && t + 1 < n_tiles) issue(t + 1, stage ^ 1);
+            mbar_wait(&full_bar[stage], (t >> 1) & 1);
+            const uint32_t sw = stages_addr + stage * kStageBytes;
+            if (clamp) transit_tile<S, WPT, true, NWARPS>(sw, nsig, acc, tab_base, smw, thin, wid);
+            else transit_tile<S, WPT, false, NWARPS, (VAR & 2) ? 4 : 2, (VAR >> 2)>(sw, nsig, acc, tab_base, smw, thin, wid);
+            __syncthreads();   // stage may be refilled by the producer in the next iteration
+        }
+        thin.finish(nsig, acc);
+        if (lane == 0 && thin.thick) atomicAdd(sc.stat + 2, (unsigned long long)thin.thick);
+    } else if (n_tiles > 0 && wid == 0 && split == 0) {
+        // every chord of the phase is thin in this window: the chord sums are the phase totals
+        if constexpr (S <= 2) {
+            const double* tt = sc.thin_tot + (int64_t)p * 8;
+            thin.sw = tt[0];
+            thin.sa[0] = tt[1];
+            if constexpr (S == 2) { thin.sa[1] = tt[2]; thin.sb[0] = tt[3]; thin.sb[1] = tt[4]; thin.sb[2] = tt[5]; }
+            else thin.sb[0] = tt[3];
+            thin.finish(nsig, acc);
+        }
+    }
+
+    // ---- epilogue: add the warps' sums in a fixed order, one thread per wavelength --------------------
 #pragma unroll
     for (int j = 0; j < WPT; ++j) {
-        double tmax = 0.0;
-#pragma unroll
-        for (int a = 0; a < S; ++a)
-            tmax = fma(__longlong_as_double((long long)__ldg(sc.nmax + (int64_t)a * sc.n_orb + p)), -nsig[a][j], tmax);
-        clamp |= !(tmax < kExpBigClampDecision);   // NaN -> clamped variant (harmless)
-    }
-    clamp = __any_sync(0xffffffffu, clamp);
-    __syncthreads();   // exp table complete
-
-    // ---- main loop over chord tiles -----------------------------------------------------------
-    // laundered through an opaque mov so that the address lives in a register instead of being
-    // re-derived (S2UR CgaCtaId + ULEA) for every chord
-    uint32_t tab_base;
-    asm volatile("mov.u32 %0, %1;" : "=r"(tab_base) : "r"(smem_u32(etab)));
-    const uint32_t stages_addr = smem_u32(stages);
-    for (int t = 0; t < n_tiles; ++t) {
-        const int stage = t & 1;
-        if (tid == 0 && t + 1 < n_tiles) issue(t + 1, stage ^ 1);
-        mbar_wait(&full_bar[stage], (t >> 1) & 1);
-        const uint32_t sw = stages_addr + stage * kStageBytes;
-        if (clamp) transit_tile<S, WPT, true>(sw, nsig, acc, tab_base);
-        else transit_tile<S, WPT, false, (VAR & 2) ? 4 : 2, (VAR >> 2)>(sw, nsig, acc, tab_base);
-        __syncthreads();   // stage may be refilled by the producer in the next iteration
-    }
-
-    // ---- epilogue -------------------------------------------------------------------------------
-    const double fout = (prm.n_split == 1) ? sc.fout[0] : 1.0;
-#pragma unroll
-    for (int j = 0; j < WPT; ++j) {
-        const int64_t w = w_base + (int64_t)j * THREADS;
-        if (w >= prm.n_wav_sel) continue;
-        const int64_t o = (int64_t)blockIdx.y * prm.n_wav_sel + w;
         double v = acc[j];
-        if (bad) {
+        if (any_bad) {
 #pragma unroll
             for (int a = 0; a < S; ++a)
                 if (nsig[a][j] != nsig[a][j]) v = nsig[a][j];
         }
-        if (prm.n_split == 1) prm.R[o] = (v + sc.w0[p]) / fout;                // :1258
+        red[wid * WIN + j * 32 + lane] = v;
+    }
+    __syncthreads();
+    for (int t = tid; t < WIN; t += THREADS) {
+        const int64_t w = win_lo + t;
+        if (w >= prm.n_wav_sel) continue;
+        double v = red[t];
+#pragma unroll
+        for (int k = 1; k < NWARPS; ++k) v += red[k * WIN + t];
+        const int64_t o = (int64_t)pi * prm.n_wav_sel + w;
+        if (prm.n_split == 1) prm.R[o] = (v + sc.w0[p]) / sc.fout[0];           // :1258
         else prm.partial[(int64_t)split * prm.n_phase * prm.n_wav_sel + o] = v;
     }
 }
@@ -289,14 +424,14 @@ __global__ void finalize_kernel(const DevScene* __restrict__ scp, const TransitP
 
 template <int S, int WPT, int THREADS, int VAR = 0>
 static cudaError_t launch_one(const DevScene* d_scene, const TransitParams& prm, cudaStream_t st) {
-    const size_t smem = (kExpBigEntries + 2 * (S + kRecExtra) * kChordTile) * sizeof(double);
+    const size_t smem = (kExpBigEntries + 2 * pb_rec_stride(S) * kChordTile + (THREADS / 32) * 32 * WPT) * sizeof(double);
     auto kern = transit_kernel<S, WPT, THREADS, VAR>;
     {   // dynamic + static shared memory is always above the 48 KB default limit
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
     }
-    const int64_t per_block = (int64_t)THREADS * WPT;
-    dim3 grid((unsigned)((prm.n_wav_sel + per_block - 1) / per_block), (unsigned)prm.n_phase, (unsigned)prm.n_split);
+    if (prm.win != 32 * WPT) return cudaErrorInvalidValue;
+    dim3 grid((unsigned)prm.n_win, (unsigned)prm.n_phase, (unsigned)prm.n_split);
     kern<<<grid, THREADS, smem, st>>>(d_scene, prm);
     return cudaGetLastError();
 }
@@ -314,8 +449,17 @@ static int transit_threads() {
     return v == 128 ? 128 : 256;
 }
 
-int transit_cta_wavelengths(int n_atoms) {
-    return n_atoms <= 2 ? transit_threads() * 8 : n_atoms <= 4 ? 256 * 4 : 256 * 2;
+cudaError_t launch_window_order(const DevScene* d_scene, const TransitParams& prm, int* order, cudaStream_t st) {
+    int n_pow2 = 1;
+    while (n_pow2 < prm.n_win) n_pow2 <<= 1;
+    if (n_pow2 > kMaxWindows) n_pow2 = 0;
+    const size_t smem = (size_t)n_pow2 * (sizeof(double) + sizeof(int));
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(window_order_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
+    window_order_kernel<<<prm.n_phase, 1024, smem, st>>>(d_scene, prm, order, n_pow2);
+    return cudaGetLastError();
 }
 
 void launch_sigma_phase(const DevScene* d_scene, const TransitParams& prm, cudaStream_t st) {
@@ -335,7 +479,8 @@ cudaError_t launch_transit(const DevScene* d_scene, int n_atoms, const TransitPa
     if (n_atoms == 1 && var == 14) return launch_one<1, 8, 256, 14>(d_scene, prm, st);
     switch (n_atoms) {
         case 1: return t256 ? launch_one<1, 8, 256>(d_scene, prm, st) : launch_one<1, 8, 128>(d_scene, prm, st);
-        case 2: return t256 ? launch_one<2, 8, 256>(d_scene, prm, st) : launch_one<2, 8, 128>(d_scene, prm, st);
+        case 2: if (prm.win == 128) return launch_one<2, 4, 256>(d_scene, prm, st);
+                return t256 ? launch_one<2, 8, 256>(d_scene, prm, st) : launch_one<2, 8, 128>(d_scene, prm, st);
         case 3: return launch_one<3, 4, 256>(d_scene, prm, st);
         case 4: return launch_one<4, 4, 256>(d_scene, prm, st);
         case 5: return launch_one<5, 2, 256>(d_scene, prm, st);

@@ -344,3 +344,17 @@ def _with_phi(grid, n_phi):
     g = list(grid)
     g[5] = n_phi          # Grid(x_midpoint, x_border, x_steps, rho_border, rho_steps, phi_steps, ...)
     return g
+
+
+def test_exp_sample_count_for_an_optically_thick_scene(transits, monkeypatch):
+    """C5s: the power-law envelope is optically thick in every wavelength window (every window holds a line),
+    so every record of every window goes through the table exp: exp_samples counts (warp, chord) pairs x the
+    window width, i.e. the records x the padded wavelength count."""
+    tr = transits("C5s")
+    R, t = run_with_env(tr, monkeypatch)
+    n_orb, n_wav = R.shape
+    records = t["executed_samples"] // n_wav
+    win = 256
+    padded = -(-n_wav // win) * win
+    assert t["exp_samples"] <= records * padded
+    assert t["exp_samples"] >= 0.5 * t["executed_samples"], (t["exp_samples"], t["executed_samples"], records, padded)
