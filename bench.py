@@ -370,12 +370,14 @@ def run_b200(args):
         column_ms = float(np.mean([t["column_ms"] for t in tile_t]))
         finalize_ms = float(np.mean([t["finalize_ms"] for t in tile_t]))
         executed = float(np.mean([t["executed_samples"] for t in tile_t]))
+        exp_samples = float(np.mean([t["exp_samples"] for t in tile_t]))
         R_dev = st.to_host(0)
 
         # ---- the same steps with the transparent-chord culling switched off (every unblocked chord
         #      goes through the exp, as in the reference's loop): reported next to the headline ----------
         os.environ["PB200_NO_CULL"] = "1"
         os.environ["PB200_NO_MIRROR"] = "1"
+        os.environ["PB200_NO_THIN"] = "1"
         ctx.set_scene(sc, keep)
         tile_t.clear()
         for _ in range(2):
@@ -396,7 +398,7 @@ def run_b200(args):
         nc_kernel_ms = float(np.mean([t["transit_ms"] for t in tile_t]))
         nc_executed = float(np.mean([t["executed_samples"] for t in tile_t]))
         R_nc = st.to_host(0)
-        del os.environ["PB200_NO_CULL"], os.environ["PB200_NO_MIRROR"]
+        del os.environ["PB200_NO_CULL"], os.environ["PB200_NO_MIRROR"], os.environ["PB200_NO_THIN"]
         ctx.set_scene(sc, keep)
         tile_t.clear()
         st.run_device()
@@ -438,10 +440,12 @@ def run_b200(args):
     hbm_peak, peak_src = measured_peaks()
     tile_samples = float(n_c) * float(st.samples_tile_shape[1])          # nominal samples of this rank's tile
     if n_mols:
-        executed = nc_executed = tile_samples                               # kernel (m) has no culling
-    # the roofline describes what kernel (c') evaluated: the samples that went through the exp
-    achieved = BYTES_PER_SAMPLE_STAGED * executed / (kernel_ms * 1e-3) / 1e9
-    fl = executed_flops_per_sample(n_atoms) * executed / (kernel_ms * 1e-3) / 1e12
+        executed = nc_executed = exp_samples = tile_samples                 # kernel (m) has no culling
+    # The roofline describes the launch that does the exp on EVERY unblocked sample (the `off` leg below: no
+    # culling, no pairing, no thin path) -- that is the kernel whose per-sample work SURVEY 8(d) counts; the
+    # production launch skips most of those samples and is described under `culling`.
+    achieved = BYTES_PER_SAMPLE_STAGED * nc_executed / (nc_kernel_ms * 1e-3) / 1e9
+    fl = executed_flops_per_sample(n_atoms) * nc_executed / (nc_kernel_ms * 1e-3) / 1e12
     out = {
         "metric": "chord*lambda samples/s", "value": samples_total / (ms_per_step * 1e-3), "unit": "samples/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
@@ -458,26 +462,29 @@ def run_b200(args):
         "roofline": {"kernel": "transit_kernel (c': tau + exp(-tau) + disk sum)", "bound": "hbm", "achieved": achieved,
                      "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "peak_source": peak_src,
                      "convention": "staged-equivalent 16 B per chord*lambda sample (SURVEY 8(d)); the fused kernel's true DRAM traffic is in `traffic`",
-                     "traffic": recorded_traffic(args.workload), "kernel_ms": kernel_ms,
-                     "samples_per_launch": executed,
-                     "samples_note": "samples kernel (c') evaluated per launch; transparent chords (tau < 2^-54 at every wavelength, exp(-tau) == 1.0) are summed without an exp, see `culling`",
+                     "traffic": recorded_traffic(args.workload), "kernel_ms": nc_kernel_ms,
+                     "samples_per_launch": nc_executed,
+                     "samples_note": "measured on the launch with PB200_NO_CULL=1 PB200_NO_MIRROR=1 PB200_NO_THIN=1, where every unblocked chord*lambda sample goes through the table exp; the production launch (kernels_ms.transit) evaluates `culling.exp_samples_per_rank_step` of them that way",
                      "fp64": {"achieved_tflops": fl, "peak_tflops_dfma_probe": probe["dfma_tflops"],
                               "frac": fl / probe["dfma_tflops"], "flops_per_sample": executed_flops_per_sample(n_atoms),
                               "flops_per_sample_survey_convention": flops_per_sample(n_atoms),
-                              "pipe_frac": ((6.0 if n_atoms == 1 else 6.0 + n_atoms) * executed / 32.0 * 2.0) /
-                                           (148 * 4 * (clk["sm_mhz"] or 1965.0) * 1e6 * kernel_ms * 1e-3) if n_mols == 0 else None,
+                              "pipe_frac": ((6.0 if n_atoms == 1 else 6.0 + n_atoms) * nc_executed / 32.0 * 2.0) /
+                                           (148 * 4 * (clk["sm_mhz"] or 1965.0) * 1e6 * nc_kernel_ms * 1e-3) if n_mols == 0 else None,
                               "pipe_frac_note": "issued FP64 warp instructions (6 per sample for one absorber, else 6+S; nominal sample count) x 2 cycles / SMSP cycles: the binding unit",
                               "exp_probe_gops": probe["exp_gops"],
-                              "exp_frac": executed / (kernel_ms * 1e-3) / 1e9 / probe["exp_gops"]}},
+                              "exp_frac": nc_executed / (nc_kernel_ms * 1e-3) / 1e9 / probe["exp_gops"]}},
         "culling": {"nominal_samples_per_step": tile_samples * world, "executed_samples_per_rank_step": executed,
                     "executed_frac": executed / tile_samples,
+                    "exp_samples_per_rank_step": exp_samples, "exp_frac": exp_samples / tile_samples,
                     "off": {"value": samples_total / (nc_ms_per_step * 1e-3), "ms_per_step": nc_ms_per_step,
                             "transit_kernel_ms": nc_kernel_ms, "executed_frac": nc_executed / tile_samples,
                             "max_abs_diff_R": cull_diff},
                     "note": "`value` counts the job's chord*lambda samples (BASELINE metric); chords whose optical depth is "
                             "below 2^-54 at every wavelength of the run contribute exactly w_in and skip the exp, and the chords "
                             "(phi, rho), (pi - phi, rho) -- equal column densities, the scene is symmetric in z -- share one record. "
-                            "`off` = same steps with PB200_NO_CULL=1 PB200_NO_MIRROR=1: every unblocked chord goes through the exp"},
+                            "Of the remaining (`executed`) samples, those whose chord is optically thin over the warp's 256 wavelengths "
+                            "(tau < 2.1e-5) are summed as a second-order expansion per chord; only `exp_samples` take the table exp. "
+                            "`off` = same steps with PB200_NO_CULL=1 PB200_NO_MIRROR=1 PB200_NO_THIN=1: every unblocked sample goes through the exp"},
         "kernels_ms": {"column": column_ms, "transit": kernel_ms, "finalize": finalize_ms},
         "setup": {"seconds": t_setup, "voigt_last_table_ms": voigt["transit_ms"], "voigt_last_table_evals": voigt["samples"]},
     }

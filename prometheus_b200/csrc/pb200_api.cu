@@ -533,6 +533,8 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
         const char* mt = getenv("PB200_MIN_TILES");   // tuning experiments only
         prm.min_tiles = mt ? atoi(mt) : 1;
         prm.culled = c->general_path ? 0 : 1;
+        const char* nt = getenv("PB200_NO_THIN");     // measurement only: every active sample through the table exp
+        prm.thin_v = (nt && nt[0] == '1') ? 0.0 : 0.125;
         if (prm.min_tiles < 1) prm.min_tiles = 1;
     }
 

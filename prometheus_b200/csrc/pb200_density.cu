@@ -267,8 +267,13 @@ column_thread_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase
             if (C.kind != 0) continue;
             const double col = (sum * C.chi) * sc.delta_x;                      // gasProperties.py:940
             sc.ncol[(int64_t)C.atom_index * sc.n_orb * sc.Mp + row] = col;
-            if (col > 0.0)
-                atomicMax(sc.nmax + (int64_t)C.atom_index * sc.n_orb + p, (unsigned long long)__double_as_longlong(col));
+            // max over the warp first (a CTA never straddles two phases: Mp is a multiple of 256): one atomic
+            // per warp instead of 32 on the same address
+            double mx = (col > 0.0) ? col : 0.0;
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, d));
+            if ((threadIdx.x & 31) == 0 && mx > 0.0)
+                atomicMax(sc.nmax + (int64_t)C.atom_index * sc.n_orb + p, (unsigned long long)__double_as_longlong(mx));
         }
     }
 }

@@ -95,6 +95,7 @@ struct TransitParams {
     int tiles_per_split;  // kChordTile-chord tiles per split (kernel (m); kernel (c') shares the ACTIVE tiles, see below)
     int min_tiles;        // kernel (c'): least number of active tiles a working CTA takes
     int culled;           // 1: kernel (c') (w0 / n_act valid), 0: kernel (m)
+    double thin_v;        // kernel (c'): scaled-tau threshold of the thin path (kThinV; 0 switches it off)
     int win;              // kernel (c'): wavelengths per warp window (32 * WPT)
     int n_win;            // windows per phase = ceil(n_wav_sel / win)
     const int* order;     // [n_phase][n_win] window indices sorted by decreasing optical thickness (window_order_kernel)

@@ -207,7 +207,7 @@ struct ThinSums {
 
 template <int S, int WPT, bool CLAMP, int NWARPS, int UNROLL = 2, int DROP = 0>
 __device__ __forceinline__ void transit_tile(uint32_t stage, const double (&nsig)[S][WPT], double (&acc)[WPT],
-                                             uint32_t tab_base, const double (&smw)[S], ThinSums<S>& thin, int wid) {
+                                             uint32_t tab_base, const double (&smw)[S], ThinSums<S>& thin, int wid, double thin_v) {
     constexpr int R = pb_rec_stride(S);
     constexpr uint32_t kRecBytes = R * sizeof(double);
     // the warps of the CTA share the window (same wavelengths) and split the chords: warp w takes chords
@@ -224,7 +224,7 @@ __device__ __forceinline__ void transit_tile(uint32_t stage, const double (&nsig
         double bound = N[0] * smw[0];
 #pragma unroll
         for (int a = 1; a < S; ++a) bound = fma(N[a], smw[a], bound);
-        if (bound < kThinV) {   // warp-uniform
+        if (bound < thin_v) {   // warp-uniform
             if constexpr (S <= 2) {
                 thin.add(w0, w1, w2, N);
             } else {
@@ -333,7 +333,7 @@ transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
         key = fma(__longlong_as_double((long long)__ldg(sc.nmax + (int64_t)a * sc.n_orb + p)), smw[a], key);
     }
     const bool clamp = !(key < kExpBigClampDecision);   // NaN -> clamped variant (harmless)
-    const bool all_thin = (S <= 2) && (key < kThinV);
+    const bool all_thin = (S <= 2) && (key < prm.thin_v);
     ThinSums<S> thin;
 
     if (n_tiles > 0 && !all_thin) {
@@ -366,8 +366,8 @@ transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
             if (tid == 0 && t + 1 < n_tiles) issue(t + 1, stage ^ 1);
             mbar_wait(&full_bar[stage], (t >> 1) & 1);
             const uint32_t sw = stages_addr + stage * kStageBytes;
-            if (clamp) transit_tile<S, WPT, true, NWARPS>(sw, nsig, acc, tab_base, smw, thin, wid);
-            else transit_tile<S, WPT, false, NWARPS, (VAR & 2) ? 4 : 2, (VAR >> 2)>(sw, nsig, acc, tab_base, smw, thin, wid);
+            if (clamp) transit_tile<S, WPT, true, NWARPS>(sw, nsig, acc, tab_base, smw, thin, wid, prm.thin_v);
+            else transit_tile<S, WPT, false, NWARPS, (VAR & 2) ? 4 : 2, (VAR >> 2)>(sw, nsig, acc, tab_base, smw, thin, wid, prm.thin_v);
             __syncthreads();   // stage may be refilled by the producer in the next iteration
         }
         thin.finish(nsig, acc);

@@ -307,8 +307,14 @@ def test_culling_and_mirror_leave_R_unchanged(name, transits, monkeypatch):
     R_full, t_full = run_with_env(tr, monkeypatch, PB200_NO_CULL="1", PB200_NO_MIRROR="1")
     R_nocull, t_nocull = run_with_env(tr, monkeypatch, PB200_NO_CULL="1")
     R_nomirror, t_nomirror = run_with_env(tr, monkeypatch, PB200_NO_MIRROR="1")
-    for other in (R_full, R_nocull, R_nomirror):
+    R_nothin, t_nothin = run_with_env(tr, monkeypatch, PB200_NO_THIN="1")
+    R_brute, t_brute = run_with_env(tr, monkeypatch, PB200_NO_CULL="1", PB200_NO_MIRROR="1", PB200_NO_THIN="1")
+    for other in (R_full, R_nocull, R_nomirror, R_nothin, R_brute):
         assert np.max(np.abs(R - other)) < 5e-14
+    assert t["exp_samples"] <= t_nothin["exp_samples"]
+    # thin path off: every record of every window takes the table exp (windows are padded to whole warps)
+    win = 32 * (8 if t["samples"] and _n_atoms(tr) <= 2 else 4 if _n_atoms(tr) <= 4 else 2)
+    assert t_nothin["exp_samples"] == t_nothin["executed_samples"] // R.shape[1] * (-(-R.shape[1] // win) * win)
     n_orb, n_wav = R.shape
     assert t["samples"] == t_full["samples"]
     # with both switched off every unblocked chord has a record (tiles are padded to 256 chords per phase)
@@ -338,6 +344,10 @@ def test_mirror_pairing_is_off_for_tabulated_densities_and_odd_phi(transits, nis
     R_b, t_b = run_with_env(odd, monkeypatch, PB200_NO_CULL="1", PB200_NO_MIRROR="1")
     assert t_a["executed_samples"] == t_b["executed_samples"]
     assert np.array_equal(R_a, R_b)
+
+
+def _n_atoms(tr):
+    return sum(1 for d in tr.atmosphere.densityDistributionList for con in d.constituents if not con.isMolecule)
 
 
 def _with_phi(grid, n_phi):
