@@ -31,8 +31,7 @@ cudaError_t launch_transit(const DevScene*, int n_atoms, const TransitParams&, c
 cudaError_t launch_transit_general(const DevScene*, const DevScene& host_copy, const TransitParams&, int sm_count,
                                    cudaStream_t, int* n_launch);
 void launch_sigma_phase(const DevScene*, const TransitParams&, cudaStream_t);
-void launch_compact(const DevScene*, int phase_lo, int n_phase, bool cull, cudaStream_t);
-cudaError_t launch_window_order(const DevScene*, const TransitParams&, int* order, cudaStream_t);
+cudaError_t launch_compact(const DevScene*, const TransitParams&, bool cull, cudaStream_t);
 void launch_finalize(const DevScene*, const TransitParams&, int sm_count, cudaStream_t);
 void launch_sigma_lookup(const double*, const double*, int64_t, double, const double*, int64_t, double*, int,
                          cudaStream_t);
@@ -459,6 +458,7 @@ extern "C" int pb200_set_scene(pb200_ctx* c, const pb200_scene* s) {
     h.n_act = reinterpret_cast<int*>(nact_d);
     h.stat = reinterpret_cast<unsigned long long*>(c->d_oob);
     PB_CUDA(c, cudaMemsetAsync(nmax_d, 0, (size_t)(n_atoms ? n_atoms : 1) * h.n_orb * sizeof(double), c->stream));
+    PB_CUDA(c, cudaMemsetAsync(smax_d, 0, (size_t)(n_atoms ? n_atoms : 1) * h.n_orb * sizeof(double), c->stream));
     c->general_path = (n_mols > 0) || fstar_per_chord;
     {   // mirror pairing of chords (compact_kernel): all bodies lie in z = 0 and every analytic density depends
         // on z^2 only; the tabulated (SERPENS) density does not.  The phi axis must be mirror symmetric about
@@ -519,12 +519,13 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     prm.phase_lo = phase_lo; prm.n_phase = n_phase; prm.wav_lo = wav_lo; prm.n_wav_sel = n_wav_sel;
     const int n_tiles = h.Mp / kChordTile;
     // wavelengths per CTA: kernel (m) 128; kernel (c') one window of 32 * WPT (WPT = 8, 4, 2 for <= 2, <= 4, more absorbers)
-    int cta_wav = c->general_path ? 128 : 32 * (h.n_atoms <= 2 ? 8 : h.n_atoms <= 4 ? 4 : 2);
-    if (h.n_atoms == 2 && getenv("PB200_WPT2")) cta_wav = 32 * 4;
+    const int cta_wav = c->general_path ? 128 : 32 * (h.n_atoms <= 2 ? 8 : h.n_atoms <= 4 ? 4 : 2);
     const int64_t ctas = ((n_wav_sel + cta_wav - 1) / cta_wav) * n_phase;
-    // many more CTAs than resident slots (~10 per SM) so that the last wave is a small fraction of the
-    // run; a CTA keeps at least 4 tiles (1024 chords) to amortise its sigma-lookup prologue
-    int64_t want = ((int64_t)c->sm_count * 80 + ctas - 1) / ctas;
+    // Chord-axis splits: enough CTAs that the last wave is a small fraction of the run.  Kernel (m) does the
+    // same work in every CTA and wants ~80 per SM; kernel (c') has one CTA per wavelength window, most of which
+    // finish early (thin or culled), so ~16 per SM is plenty -- and with a single split it writes R itself
+    // and finalize_kernel (and the partial sums' traffic) is not needed at all.
+    int64_t want = ((int64_t)c->sm_count * (c->general_path ? 80 : 16) + ctas - 1) / ctas;
     if (want > n_tiles / 4) want = n_tiles / 4;
     if (want < 1) want = 1;
     prm.tiles_per_split = (int)((n_tiles + want - 1) / want);
@@ -542,22 +543,23 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     const size_t part_bytes = prm.n_split > 1 ? (size_t)prm.n_split * n_out * sizeof(double) : 0;
     const size_t nsig_bytes = c->general_path ? 0 : (size_t)h.n_atoms * n_out * sizeof(double);
     prm.win = 32 * (h.n_atoms <= 2 ? 8 : h.n_atoms <= 4 ? 4 : 2);
-    if (h.n_atoms == 2 && getenv("PB200_WPT2")) prm.win = 32 * 4;   // tuning experiment
     prm.n_win = (int)((n_wav_sel + prm.win - 1) / prm.win);
     const size_t order_bytes = c->general_path ? 0 : (((size_t)n_phase * prm.n_win * sizeof(int) + 255) & ~size_t(255));
-    int rc = ensure_scratch(c, r_bytes + part_bytes + nsig_bytes + order_bytes + 256);
+    const size_t winmax_bytes = c->general_path ? 0 : (size_t)h.n_atoms * n_phase * prm.n_win * sizeof(double);
+    int rc = ensure_scratch(c, r_bytes + part_bytes + nsig_bytes + order_bytes + winmax_bytes + 256);
     if (rc) return rc;
     prm.R = R_in_scratch ? c->scratch : R_dev;
     prm.partial = reinterpret_cast<double*>(reinterpret_cast<char*>(c->scratch) + r_bytes);
     prm.nsig = reinterpret_cast<double*>(reinterpret_cast<char*>(c->scratch) + r_bytes + part_bytes);
     int* order = reinterpret_cast<int*>(reinterpret_cast<char*>(c->scratch) + r_bytes + part_bytes + nsig_bytes);
     prm.order = order;
+    prm.winmax = reinterpret_cast<double*>(reinterpret_cast<char*>(c->scratch) + r_bytes + part_bytes + nsig_bytes + order_bytes);
 
     PB_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
     if (!c->general_path) {   // sigma(p, w) of the tile and its per-phase maxima, needed by the culling below
         if (h.n_atoms < 1) return fail(c, PB200_ERR_INVALID, "scene has no absorbing constituent");
-        PB_CUDA(c, cudaMemsetAsync(h.smax, 0, (size_t)h.n_atoms * h.n_orb * sizeof(double), c->stream));
-        PB_CUDA(c, cudaMemsetAsync(reinterpret_cast<char*>(c->d_oob) + 8, 0, 24, c->stream));
+        // smax is left clean by compact_kernel of the previous run (and by pb200_set_scene), the run
+        // statistics are reset by sigma_phase_kernel: no memset nodes in the run
         launch_sigma_phase(c->d_scene, prm, c->stream);
         c->launches += 1;
     }
@@ -569,9 +571,8 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
                   !c->general_path && cull);
     c->launches += 1;
     if (!c->general_path) {   // chord records of kernel (c'), transparent chords culled
-        launch_compact(c->d_scene, phase_lo, n_phase, cull, c->stream);
-        PB_CUDA(c, launch_window_order(c->d_scene, prm, order, c->stream));
-        c->launches += 2;
+        PB_CUDA(c, launch_compact(c->d_scene, prm, cull, c->stream));
+        c->launches += 1;
     }
     PB_CUDA(c, cudaGetLastError());
     PB_CUDA(c, cudaEventRecord(c->ev[3], c->stream));

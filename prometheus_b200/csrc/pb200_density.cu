@@ -289,8 +289,10 @@ column_thread_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase
 // Active records are packed in chord order at the front of the phase's rec row (block-wide exclusive
 // scan, deterministic), the last tile is padded with all-zero records, n_act[p] = number of tiles.
 constexpr int kCompactThreads = 1024;
-__global__ void __launch_bounds__(kCompactThreads) compact_kernel(const DevScene* __restrict__ scp, int phase_lo, int cull) {
+__global__ void __launch_bounds__(kCompactThreads) compact_kernel(const DevScene* __restrict__ scp, const TransitParams prm, int cull,
+                                                                  int n_pow2) {
     const DevScene& sc = *scp;
+    const int phase_lo = prm.phase_lo;
     const int p = phase_lo + blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int S = sc.n_atoms, R = pb_rec_stride(S);
     __shared__ double s_smax[16];
@@ -399,6 +401,53 @@ __global__ void __launch_bounds__(kCompactThreads) compact_kernel(const DevScene
         sc.n_act[p] = n_tiles;
         atomicAdd(sc.stat + 1, (unsigned long long)n_tiles * kChordTile);
     }
+    if (tid < S) sc.smax[(int64_t)tid * sc.n_orb + p] = 0ull;   // clean for the atomicMax of the next run
+
+    // ---- order of the wavelength windows of this phase for kernel (c') -------------------------------
+    // A CTA of kernel (c') owns one window; windows in a line core take the table exp on most chords, windows
+    // in the continuum none.  They are launched in decreasing order of optical thickness,
+    // key = sum_a max_m Ncol_a(p, m) * max_{w in window} |nsig_a(p, w)| (the largest scaled tau of the window),
+    // so that the long CTAs start first (bitonic network in shared memory; the order only matters for the
+    // load balance, never for the results).  More than kMaxWindows windows: identity order.
+    extern __shared__ __align__(16) unsigned char wsm[];
+    double* key = reinterpret_cast<double*>(wsm);
+    int* idx = reinterpret_cast<int*>(key + n_pow2);
+    int* out = prm.order + (int64_t)blockIdx.x * prm.n_win;
+    if (n_pow2 == 0) {
+        for (int i = tid; i < prm.n_win; i += kCompactThreads) out[i] = i;
+        return;
+    }
+    for (int i = tid; i < n_pow2; i += kCompactThreads) {
+        double k = -1.0;                              // padding sorts last
+        if (i < prm.n_win) {
+            k = 0.0;
+            for (int a = 0; a < S; ++a) {
+                const double nm = __longlong_as_double((long long)sc.nmax[(int64_t)a * sc.n_orb + p]);
+                const double wm = prm.winmax[((int64_t)a * prm.n_phase + blockIdx.x) * prm.n_win + i];
+                k += (nm > 0.0) ? nm * wm : 0.0;
+            }
+            if (!(k == k)) k = __longlong_as_double(0x7ff0000000000000ll);
+        }
+        key[i] = k;
+        idx[i] = i;
+    }
+    __syncthreads();
+    for (int size = 2; size <= n_pow2; size <<= 1)
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            for (int i = tid; i < n_pow2; i += kCompactThreads) {
+                const int j = i ^ stride;
+                if (j > i) {
+                    const bool desc = (i & size) == 0;
+                    const double ki = key[i], kj = key[j];
+                    const int ii = idx[i], ij = idx[j];
+                    // total order (key, then index): the result does not depend on the network
+                    const bool i_first = (ki > kj) || (ki == kj && ii < ij);
+                    if (i_first != desc) { key[i] = kj; key[j] = ki; idx[i] = ij; idx[j] = ii; }
+                }
+            }
+            __syncthreads();
+        }
+    for (int i = tid; i < prm.n_win; i += kCompactThreads) out[i] = idx[i];
 }
 
 // ---- calculateNumberDensity materialised (chord-major, reference chord order) ------------------
@@ -495,8 +544,18 @@ void launch_column(const DevScene* d_scene, int Mp, int phase_lo, int n_phase, i
         column_thread_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(d_scene, phase_lo, n_phase, oob, run_mode ? 1 : 0);
     }
 }
-void launch_compact(const DevScene* d_scene, int phase_lo, int n_phase, bool cull, cudaStream_t st) {
-    compact_kernel<<<n_phase, kCompactThreads, 0, st>>>(d_scene, phase_lo, cull ? 1 : 0);
+constexpr int kMaxWindows = 8192;
+cudaError_t launch_compact(const DevScene* d_scene, const TransitParams& prm, bool cull, cudaStream_t st) {
+    int n_pow2 = 1;
+    while (n_pow2 < prm.n_win) n_pow2 <<= 1;
+    if (n_pow2 > kMaxWindows) n_pow2 = 0;
+    const size_t smem = (size_t)n_pow2 * (sizeof(double) + sizeof(int));
+    if (smem > 40 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(compact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
+    compact_kernel<<<prm.n_phase, kCompactThreads, smem, st>>>(d_scene, prm, cull ? 1 : 0, n_pow2);
+    return cudaGetLastError();
 }
 void launch_number_density_grid(const DevScene* d_scene, int64_t n_chords, int scenario, double* out,
                                 int* oob, int sm_count, cudaStream_t st) {

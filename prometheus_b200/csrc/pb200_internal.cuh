@@ -98,7 +98,8 @@ struct TransitParams {
     double thin_v;        // kernel (c'): scaled-tau threshold of the thin path (kThinV; 0 switches it off)
     int win;              // kernel (c'): wavelengths per warp window (32 * WPT)
     int n_win;            // windows per phase = ceil(n_wav_sel / win)
-    const int* order;     // [n_phase][n_win] window indices sorted by decreasing optical thickness (window_order_kernel)
+    int* order;           // [n_phase][n_win] window indices sorted by decreasing optical thickness (compact_kernel)
+    double* winmax;       // [n_atoms][n_phase][n_win] max |nsig_a| of each window (sigma_phase_kernel)
     double* partial;      // [n_split][n_phase][n_wav_sel] sums of w_in*exp(-tau)  (n_split > 1); kernel (c') only writes
                           // the slots of splits that have tiles (pb_splits_used)
     double* R;            // [n_phase][n_wav_sel] final ratio

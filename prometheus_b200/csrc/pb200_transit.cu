@@ -68,95 +68,49 @@ __device__ __forceinline__ void lds_v2f64(uint32_t addr, double& a, double& b) {
 // sigma_a of the phase over the run's wavelengths (smax, for the transparent-chord test of compact_kernel)
 __global__ void __launch_bounds__(256) sigma_phase_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
     const DevScene& sc = *scp;
+    __shared__ double s_wmax[8];
     const int64_t wi = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const bool live = wi < prm.n_wav_sel;
     const int pi = blockIdx.y, p = prm.phase_lo + pi;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) { sc.stat[1] = 0ull; sc.stat[2] = 0ull; }   // run statistics
     const double lam = live ? __ldg(sc.wavelength + prm.wav_lo + wi) : 0.0;
+    const int wpw = prm.win / 32;   // warps per window: this 256-wavelength CTA covers 8 / wpw whole windows
     int a = 0;
     for (int k = 0; k < sc.n_cons; ++k) {
         const DevConstituent& C = sc.cons[k];
         if (C.kind != 0) continue;
         unsigned long long bits = 0ull;
+        double ns_abs = 0.0;
         if (live) {
             const double shift = __ldg(sc.scen[C.scenario].shift + p);
             const double v = pb_interp_log(C.tab_x, C.tab_y, C.n_tab, shift * lam, C.offset);   // :917, :950-951
-            prm.nsig[((int64_t)a * prm.n_phase + pi) * prm.n_wav_sel + wi] = -v * kExpBigScale;
+            const double ns = -v * kExpBigScale;
+            prm.nsig[((int64_t)a * prm.n_phase + pi) * prm.n_wav_sel + wi] = ns;
             bits = (v >= 0.0) ? (unsigned long long)__double_as_longlong(v) : ~0ull;   // negative or NaN: never cull
+            ns_abs = (ns == ns) ? fabs(ns) : __longlong_as_double(0x7ff0000000000000ll);      // NaN: never thin
         }
 #pragma unroll
         for (int d = 16; d > 0; d >>= 1) {
             const unsigned long long o = __shfl_xor_sync(0xffffffffu, bits, d);
             bits = o > bits ? o : bits;
+            ns_abs = fmax(ns_abs, __shfl_xor_sync(0xffffffffu, ns_abs, d));
         }
-        if ((threadIdx.x & 31) == 0 && bits) atomicMax(sc.smax + (int64_t)a * sc.n_orb + p, bits);
+        if (lane == 0 && bits) atomicMax(sc.smax + (int64_t)a * sc.n_orb + p, bits);
+        // window maxima of |nsig_a| for the thin test / the thickness order of kernel (c')
+        __syncthreads();
+        if (lane == 0) s_wmax[wid] = ns_abs;
+        __syncthreads();
+        if (threadIdx.x < 8 / wpw) {
+            const int window = blockIdx.x * (8 / wpw) + threadIdx.x;
+            if (window < prm.n_win) {
+                double mx = 0.0;
+                for (int i = 0; i < wpw; ++i) mx = fmax(mx, s_wmax[threadIdx.x * wpw + i]);
+                prm.winmax[((int64_t)a * prm.n_phase + pi) * prm.n_win + window] = mx;
+            }
+        }
         ++a;
     }
-}
-
-// One 256-chord tile: acc[j] += w_m * exp(-sum_a N_a(m) sigma_a(j)) for the thread's WPT wavelengths.
-// `stage` is the shared-window address of the tile's records (explicit ld.shared: no generic->shared
-// address conversion inside the loop).  The padding records of the last tile are all zeros
-// (w = w c1 = w c2 = 0, N = 0): they take the thin path and add +0 exactly.
-// Order of the wavelength windows of a phase.  A warp of kernel (c') owns one window (32 * WPT consecutive
-// wavelengths) and the 8 warps of a CTA walk the chord tiles in lock step, so a CTA is as slow as its
-// thickest window: windows in a line core take the table exp on most chords, windows in the continuum take
-// the thin path on all of them.  CTAs are therefore formed from windows of similar optical thickness:
-// key = sum_a max_m Ncol_a(p, m) * max_{w in window} |nsig_a(p, w)| (the largest scaled tau of the window),
-// sorted in decreasing order by a bitonic network in shared memory (one CTA per phase; ties and the order of
-// equal keys do not matter for the results, only for the load balance).  More than kMaxWindows windows:
-// identity order.
-constexpr int kMaxWindows = 8192;
-__global__ void __launch_bounds__(1024) window_order_kernel(const DevScene* __restrict__ scp, const TransitParams prm,
-                                                            int* __restrict__ order, int n_pow2) {
-    const DevScene& sc = *scp;
-    extern __shared__ __align__(16) unsigned char wsm[];
-    double* key = reinterpret_cast<double*>(wsm);
-    int* idx = reinterpret_cast<int*>(key + n_pow2);
-    const int pi = blockIdx.x, p = prm.phase_lo + pi, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const int S = sc.n_atoms;
-    int* out = order + (int64_t)pi * prm.n_win;
-    if (n_pow2 == 0) {   // too many windows to sort in shared memory
-        for (int i = tid; i < prm.n_win; i += blockDim.x) out[i] = i;
-        return;
-    }
-    for (int wdw = wid; wdw < n_pow2; wdw += 32) {   // one warp per window
-        double k = -1.0;                              // padding sorts last
-        if (wdw < prm.n_win) {
-            k = 0.0;
-            for (int a = 0; a < S; ++a) {
-                double mx = 0.0;
-                bool nan = false;
-                for (int64_t w = (int64_t)wdw * prm.win + lane; w < (int64_t)(wdw + 1) * prm.win && w < prm.n_wav_sel; w += 32) {
-                    const double v = fabs(__ldg(prm.nsig + ((int64_t)a * prm.n_phase + pi) * prm.n_wav_sel + w));
-                    nan |= (v != v);
-                    mx = fmax(mx, v);
-                }
-#pragma unroll
-                for (int d = 16; d > 0; d >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, d));
-                if (__any_sync(0xffffffffu, nan)) mx = __longlong_as_double(0x7ff0000000000000ll);
-                const double nm = __longlong_as_double((long long)__ldg(sc.nmax + (int64_t)a * sc.n_orb + p));
-                k += (nm > 0.0) ? nm * mx : 0.0;
-            }
-        }
-        if (lane == 0) { key[wdw] = k; idx[wdw] = wdw; }
-    }
-    __syncthreads();
-    for (int size = 2; size <= n_pow2; size <<= 1)
-        for (int stride = size >> 1; stride > 0; stride >>= 1) {
-            for (int i = tid; i < n_pow2; i += blockDim.x) {
-                const int j = i ^ stride;
-                if (j > i) {
-                    const bool desc = (i & size) == 0;
-                    const double ki = key[i], kj = key[j];
-                    const int ii = idx[i], ij = idx[j];
-                    // total order (key, then index) so that the result does not depend on the network
-                    const bool i_first = (ki > kj) || (ki == kj && ii < ij);
-                    if (i_first != desc) { key[i] = kj; key[j] = ki; idx[i] = ij; idx[j] = ii; }
-                }
-            }
-            __syncthreads();
-        }
-    for (int i = tid; i < prm.n_win; i += blockDim.x) out[i] = idx[i];
 }
 
 // Optically thin chords.  If sum_a N_a max|nsig_a| over the warp's wavelengths is below kThinV (tau < 2.1e-5),
@@ -269,7 +223,7 @@ __device__ __forceinline__ void transit_tile(uint32_t stage, const double (&nsig
 // All warps of the CTA hold the SAME wavelengths (lane = fastest index, j = 32-wavelength group) and split
 // the chords of every tile between them, so they see the same mix of thin and thick chords and stay in
 // step; their partial sums are added in a fixed order at the end.  Windows are taken in decreasing order of
-// optical thickness (window_order_kernel: longest CTAs first).  A window that is thin for every chord of
+// optical thickness (compact_kernel: longest CTAs first).  A window that is thin for every chord of
 // the phase (S <= 2) needs no chord loop at all: its sums are the per-phase totals of compact_kernel.
 template <int S, int WPT, int THREADS, int VAR = 0>
 __global__ void __launch_bounds__(THREADS, (VAR & 1) ? 4 : (THREADS == 256 ? (S == 1 ? 3 : 2) : 6))
@@ -449,19 +403,6 @@ static int transit_threads() {
     return v == 128 ? 128 : 256;
 }
 
-cudaError_t launch_window_order(const DevScene* d_scene, const TransitParams& prm, int* order, cudaStream_t st) {
-    int n_pow2 = 1;
-    while (n_pow2 < prm.n_win) n_pow2 <<= 1;
-    if (n_pow2 > kMaxWindows) n_pow2 = 0;
-    const size_t smem = (size_t)n_pow2 * (sizeof(double) + sizeof(int));
-    if (smem > 48 * 1024) {
-        cudaError_t e = cudaFuncSetAttribute(window_order_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-    }
-    window_order_kernel<<<prm.n_phase, 1024, smem, st>>>(d_scene, prm, order, n_pow2);
-    return cudaGetLastError();
-}
-
 void launch_sigma_phase(const DevScene* d_scene, const TransitParams& prm, cudaStream_t st) {
     dim3 grid((unsigned)((prm.n_wav_sel + 255) / 256), (unsigned)prm.n_phase);
     sigma_phase_kernel<<<grid, 256, 0, st>>>(d_scene, prm);
@@ -479,8 +420,7 @@ cudaError_t launch_transit(const DevScene* d_scene, int n_atoms, const TransitPa
     if (n_atoms == 1 && var == 14) return launch_one<1, 8, 256, 14>(d_scene, prm, st);
     switch (n_atoms) {
         case 1: return t256 ? launch_one<1, 8, 256>(d_scene, prm, st) : launch_one<1, 8, 128>(d_scene, prm, st);
-        case 2: if (prm.win == 128) return launch_one<2, 4, 256>(d_scene, prm, st);
-                return t256 ? launch_one<2, 8, 256>(d_scene, prm, st) : launch_one<2, 8, 128>(d_scene, prm, st);
+        case 2: return t256 ? launch_one<2, 8, 256>(d_scene, prm, st) : launch_one<2, 8, 128>(d_scene, prm, st);
         case 3: return launch_one<3, 4, 256>(d_scene, prm, st);
         case 4: return launch_one<4, 4, 256>(d_scene, prm, st);
         case 5: return launch_one<5, 2, 256>(d_scene, prm, st);
