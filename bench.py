@@ -463,6 +463,7 @@ def run_b200(args):
                      "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "peak_source": peak_src,
                      "convention": "staged-equivalent 16 B per chord*lambda sample (SURVEY 8(d)); the fused kernel's true DRAM traffic is in `traffic`",
                      "traffic": recorded_traffic(args.workload), "kernel_ms": nc_kernel_ms,
+                     "traffic_production_launch": recorded_traffic(args.workload, "transit_kernel_production"),
                      "samples_per_launch": nc_executed,
                      "samples_note": "measured on the launch with PB200_NO_CULL=1 PB200_NO_MIRROR=1 PB200_NO_THIN=1, where every unblocked chord*lambda sample goes through the table exp; the production launch (kernels_ms.transit) evaluates `culling.exp_samples_per_rank_step` of them that way",
                      "fp64": {"achieved_tflops": fl, "peak_tflops_dfma_probe": probe["dfma_tflops"],
