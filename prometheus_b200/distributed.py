@@ -83,11 +83,15 @@ class ShardedTransit:
         p0, p1, w0, w1 = self.tile
         return p1 - p0, w1 - w0
 
-    def run_device(self):
-        """Enqueue this rank's tile and the all-gather; returns the gathered device buffer."""
+    def run_device(self, gather: bool = True):
+        """Enqueue this rank's tile and (gather=True) the all-gather; returns the gathered device buffer, or
+        this rank's tile buffer when the tiles are left where they were computed (the output tiles are
+        independent units: nothing on the data path needs them in one place)."""
         p0, p1, w0, w1 = self.tile
         if p1 > p0 and w1 > w0:
             self.compute_tile(p0, p1, w0, w1, self.local)
+        if not gather:
+            return self.local
         if self.world > 1:
             self.dist.all_gather_into_tensor(self.gathered, self.local, group=self.group)
         return self.gathered
