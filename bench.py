@@ -242,7 +242,7 @@ def workload_config(name, spec, n_c, n_wav, n_gpus):
     g = spec["grid"]
     return {"workload": f"{name}: {spec['title']}", "n_chords": n_c, "n_wav": int(n_wav), "n_x": int(g[2]),
             "n_orb": int(g[7]), "n_phi": int(g[5]), "n_rho": int(g[4]),
-            "sharding": f"wavelength chunks over {n_gpus} rank(s), replicated scene; `value`: the R tiles stay on the GPU that computed them (independent units, no data-path collective); `e2e`: one all-gather + D2H on rank 0",
+            "sharding": f"wavelengths over {n_gpus} rank(s) (blocks of 256 dealt round-robin), replicated scene; `value`: the R tiles stay on the GPU that computed them (independent units, no data-path collective); `e2e`: one all-gather + D2H on rank 0",
             "weak_scaling_rule": "wavelength resolution refined N-fold at N GPUs",
             "cache": "L2 flushed between timed steps (512 MiB write)"}
 
@@ -330,12 +330,12 @@ def run_b200(args):
         sc, keep, info = scene.flatten(tr)
         ctx.set_scene(sc, keep)
         n_orb, n_wav, n_c, n_atoms, n_mols = info["n_orb"], info["n_wav"], info["n_chords"], info["n_atoms"], info["n_mols"]
-        st = pbd.ShardedTransit(n_orb, n_wav, None, "wavelength", dev)
+        # N > 1: block-cyclic wavelength split for atomic scenes (line cores and continuum spread evenly over the
+        # ranks); contiguous chunks for scenes that run kernel (m)
+        axis = "cyclic" if (world > 1 and n_mols == 0 and not (sc.n_fstar > 0 and sc.vsini != 0.0)) else "wavelength"
+        st = pbd.ShardedTransit(n_orb, n_wav, None, axis, dev)
         tile_t = []
-
-        def compute_tile(p0, p1, w0, w1, out):
-            tile_t.append(ctx.run_device(p0, p1, w0, w1, out.data_ptr(), want_timing=True))
-        st.compute_tile = compute_tile
+        st.compute_tile = pbd.tile_function(ctx, axis, world, rank, want_timing=True, sink=tile_t)
         flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
         samples_total = float(n_c) * float(n_wav)
 
@@ -420,7 +420,7 @@ def run_b200(args):
             if world == 1:
                 R_e2e = tr.sumOverChords()                 # the user-facing call: numpy in, numpy out
             else:
-                R_e2e = pbd.sum_over_chords(tr, None, "wavelength", local, 0, state)
+                R_e2e = pbd.sum_over_chords(tr, None, axis, local, 0, state)
             b.record()
             barrier()
             if i >= args.warmup:

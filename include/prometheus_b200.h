@@ -157,6 +157,15 @@ int pb200_run(pb200_ctx* ctx, int phase_lo, int phase_hi, int64_t wav_lo, int64_
               double* R_host, pb200_timing* timing);
 int pb200_run_device(pb200_ctx* ctx, int phase_lo, int phase_hi, int64_t wav_lo, int64_t wav_hi,
                      double* R_dev, pb200_timing* timing);
+/* Multi-GPU tile with balanced work: the wavelength axis is cut into blocks of wav_block (a multiple of
+ * 256) and rank r of n_ranks takes blocks r, r + n_ranks, ... (line cores and continuum are then spread
+ * evenly over the ranks, unlike with contiguous chunks).  R_dev receives [n_phase][n_local] in the order
+ * of the rank's wavelengths, n_local = pb200_cyclic_count(n_wav, wav_block, n_ranks, rank).  Atomic scenes
+ * only (PB200_ERR_UNSUPPORTED with molecules / a per-chord stellar spectrum).  Replaces, together with the
+ * gather in prometheus_b200/distributed.py, memoryHandler.calculate_optimal_chunk_size (memoryHandler.py:55-66). */
+int pb200_run_device_cyclic(pb200_ctx* ctx, int phase_lo, int phase_hi, int64_t wav_block, int n_ranks,
+                            int rank, double* R_dev, pb200_timing* timing);
+int64_t pb200_cyclic_count(int64_t n_wav, int64_t wav_block, int n_ranks, int rank);
 /* timing record of the last pb200_run / pb200_voigt_sigma call of this context */
 int pb200_last_timing(pb200_ctx* ctx, pb200_timing* timing);
 

@@ -19,7 +19,7 @@ c_double_p = C.POINTER(C.c_double)
 # every symbol include/prometheus_b200.h declares (checked by tests/test_abi.py)
 EXPORTS = [
     "pb200_abi_version", "pb200_device_count", "pb200_create", "pb200_destroy", "pb200_last_error",
-    "pb200_set_stream", "pb200_launch_count", "pb200_host_alloc", "pb200_host_free", "pb200_set_scene", "pb200_run", "pb200_run_device",
+    "pb200_set_stream", "pb200_launch_count", "pb200_host_alloc", "pb200_host_free", "pb200_set_scene", "pb200_run", "pb200_run_device", "pb200_run_device_cyclic", "pb200_cyclic_count",
     "pb200_last_timing", "pb200_number_density", "pb200_number_density_chords", "pb200_column_density",
     "pb200_chord_masks", "pb200_optical_depth", "pb200_sigma_lookup", "pb200_voigt_sigma",
     "pb200_voigt_profile", "pb200_molecular_sigma", "pb200_write_output", "pb200_probe_fp64",
@@ -114,6 +114,8 @@ def load():
         "pb200_set_scene": (C.c_int, [vp, C.POINTER(Scene)]),
         "pb200_run": (C.c_int, [vp, i32, i32, i64, i64, c_double_p, C.POINTER(Timing)]),
         "pb200_run_device": (C.c_int, [vp, i32, i32, i64, i64, vp, C.POINTER(Timing)]),
+        "pb200_run_device_cyclic": (C.c_int, [vp, i32, i32, i64, i32, i32, vp, C.POINTER(Timing)]),
+        "pb200_cyclic_count": (C.c_int64, [i64, i64, i32, i32]),
         "pb200_last_timing": (C.c_int, [vp, C.POINTER(Timing)]),
         "pb200_number_density": (C.c_int, [vp, i32, c_double_p]),
         "pb200_number_density_chords": (C.c_int, [vp, i32, i64] + [c_double_p] * 6),
@@ -259,6 +261,12 @@ class Context:
         t = Timing()
         self.check(self.lib.pb200_run_device(self.handle, phase_lo, phase_hi, wav_lo, wav_hi, C.c_void_p(dev_ptr),
                                              C.byref(t) if want_timing else None))
+        return t.as_dict() if want_timing else None
+
+    def run_device_cyclic(self, phase_lo, phase_hi, wav_block, n_ranks, rank, dev_ptr: int, want_timing=False):
+        t = Timing()
+        self.check(self.lib.pb200_run_device_cyclic(self.handle, phase_lo, phase_hi, wav_block, n_ranks, rank,
+                                                    C.c_void_p(dev_ptr), C.byref(t) if want_timing else None))
         return t.as_dict() if want_timing else None
 
     def last_timing(self) -> dict:

@@ -505,7 +505,7 @@ int check_scene(pb200_ctx* c) {
 
 // enqueue kernels (a') and (c') for the tile; R_dev receives [n_phase][n_wav_sel]
 int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_t wav_hi, double* R_dev,
-                bool R_in_scratch) {
+                bool R_in_scratch, int64_t cyc_block = 0, int cyc_n = 1, int cyc_rank = 0) {
     const DevScene& h = c->h_scene;
     if (phase_lo < 0 || phase_hi > h.n_orb || phase_lo >= phase_hi || wav_lo < 0 || wav_hi > h.n_wav || wav_lo >= wav_hi)
         return fail(c, PB200_ERR_INVALID, "tile [%d,%d) x [%lld,%lld) outside the (%d, %lld) grid", phase_lo, phase_hi,
@@ -517,6 +517,9 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
 
     TransitParams prm;
     prm.phase_lo = phase_lo; prm.n_phase = n_phase; prm.wav_lo = wav_lo; prm.n_wav_sel = n_wav_sel;
+    prm.cyc_block = cyc_block; prm.cyc_n = cyc_n; prm.cyc_rank = cyc_rank;
+    if (cyc_block && c->general_path)
+        return fail(c, PB200_ERR_UNSUPPORTED, "block-cyclic wavelength tiles are implemented for atomic scenes (kernel (c')) only");
     const int n_tiles = h.Mp / kChordTile;
     // wavelengths per CTA: kernel (m) 128; kernel (c') one window of 32 * WPT (WPT = 8, 4, 2 for <= 2, <= 4, more absorbers)
     const int cta_wav = c->general_path ? 128 : 32 * (h.n_atoms <= 2 ? 8 : h.n_atoms <= 4 ? 4 : 2);
@@ -673,6 +676,40 @@ extern "C" int pb200_run_device(pb200_ctx* c, int phase_lo, int phase_hi, int64_
     rc = enqueue_run(c, phase_lo, phase_hi, wav_lo, wav_hi, R_dev, false);
     if (rc) return rc;
     if (timing) {   // the caller asked for timings: this needs a synchronisation
+        rc = check_oob(c);
+        if (rc) return rc;
+        rc = collect_timing(c);
+        if (rc) return rc;
+        *timing = c->last;
+    }
+    return PB200_OK;
+}
+
+// number of wavelengths of rank `rank` in a block-cyclic split of n_wav into blocks of `block` over n_ranks
+static int64_t cyclic_count(int64_t n_wav, int64_t block, int n_ranks, int rank) {
+    const int64_t n_blocks = (n_wav + block - 1) / block;
+    int64_t n = 0;
+    for (int64_t b = rank; b < n_blocks; b += n_ranks) n += (b + 1) * block <= n_wav ? block : n_wav - b * block;
+    return n;
+}
+
+extern "C" int64_t pb200_cyclic_count(int64_t n_wav, int64_t wav_block, int n_ranks, int rank) {
+    if (n_wav < 0 || wav_block <= 0 || n_ranks <= 0 || rank < 0 || rank >= n_ranks) return -1;
+    return cyclic_count(n_wav, wav_block, n_ranks, rank);
+}
+
+extern "C" int pb200_run_device_cyclic(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_block, int n_ranks, int rank,
+                                       double* R_dev, pb200_timing* timing) {
+    int rc = check_scene(c);
+    if (rc) return rc;
+    if (!R_dev) return fail(c, PB200_ERR_INVALID, "R_dev == NULL");
+    if (wav_block <= 0 || n_ranks <= 0 || rank < 0 || rank >= n_ranks)
+        return fail(c, PB200_ERR_INVALID, "block-cyclic split: block %lld, rank %d of %d", (long long)wav_block, rank, n_ranks);
+    const int64_t n_local = cyclic_count(c->h_scene.n_wav, wav_block, n_ranks, rank);
+    if (n_local == 0) return PB200_OK;   // more ranks than blocks: nothing to do
+    rc = enqueue_run(c, phase_lo, phase_hi, 0, n_local, R_dev, false, wav_block, n_ranks, rank);
+    if (rc) return rc;
+    if (timing) {
         rc = check_oob(c);
         if (rc) return rc;
         rc = collect_timing(c);

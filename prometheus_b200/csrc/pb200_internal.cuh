@@ -87,10 +87,17 @@ __host__ __device__ inline int pb_splits_used(int n_act, int n_split, int min_ti
     return (n_act + tps - 1) / tps;
 }
 
+// global wavelength index of local index wi of a run
+__host__ __device__ inline int64_t pb_wav_index(const struct TransitParams& prm, int64_t wi);
+
 // launch parameters of kernel (c') and its variants
 struct TransitParams {
     int phase_lo, n_phase;
     int64_t wav_lo, n_wav_sel;
+    // block-cyclic wavelength selection (pb200_run_device_cyclic): local index wi stands for the global index
+    // ((wi / cyc_block) * cyc_n + cyc_rank) * cyc_block + wi % cyc_block; cyc_block = 0: contiguous [wav_lo, wav_lo + n_wav_sel)
+    int64_t cyc_block;
+    int cyc_n, cyc_rank;
     int n_split;          // chord-axis splits (gridDim.z)
     int tiles_per_split;  // kChordTile-chord tiles per split (kernel (m); kernel (c') shares the ACTIVE tiles, see below)
     int min_tiles;        // kernel (c'): least number of active tiles a working CTA takes
@@ -105,6 +112,11 @@ struct TransitParams {
     double* R;            // [n_phase][n_wav_sel] final ratio
     double* nsig;         // [n_atoms][n_phase][n_wav_sel] -sigma_a(p, w) * 4096/ln2 (sigma_phase_kernel)
 };
+__host__ __device__ inline int64_t pb_wav_index(const TransitParams& prm, int64_t wi) {
+    if (prm.cyc_block == 0) return prm.wav_lo + wi;
+    return ((wi / prm.cyc_block) * prm.cyc_n + prm.cyc_rank) * prm.cyc_block + wi % prm.cyc_block;
+}
+
 
 // ---------------------------------------------------------------------------------------------
 // number density of one scenario at offsets (dx, dy, z) from its centre -- SURVEY 8(a) row a7

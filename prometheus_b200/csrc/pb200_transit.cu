@@ -74,7 +74,7 @@ __global__ void __launch_bounds__(256) sigma_phase_kernel(const DevScene* __rest
     const int pi = blockIdx.y, p = prm.phase_lo + pi;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) { sc.stat[1] = 0ull; sc.stat[2] = 0ull; }   // run statistics
-    const double lam = live ? __ldg(sc.wavelength + prm.wav_lo + wi) : 0.0;
+    const double lam = live ? __ldg(sc.wavelength + pb_wav_index(prm, wi)) : 0.0;
     const int wpw = prm.win / 32;   // warps per window: this 256-wavelength CTA covers 8 / wpw whole windows
     int a = 0;
     for (int k = 0; k < sc.n_cons; ++k) {

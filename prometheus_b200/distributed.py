@@ -7,8 +7,10 @@ exchange step on the data path.  This replaces memoryHandler's RAM-bounded chord
 collective is the final all-gather of the fp64 R tiles (NCCL over NVLink; gloo in the CPU tests).
 
 Partition: contiguous wavelength chunks of equal padded width (every rank then does the same
-kernel (c') work; kernel (a') -- n_c*n_x, < 1 % of n_c*n_wav -- is replicated), or contiguous
-phase blocks when asked for (`axis="phase"`: partitions kernel (a') as well; useful for dense
+kernel (c') work; kernel (a') -- n_c*n_x, < 1 % of n_c*n_wav -- is replicated), or -- `axis="cyclic"`,
+atomic scenes -- blocks of 256 wavelengths dealt round-robin to the ranks, which spreads line cores (table
+exp on most chords) and continuum (thin path) evenly where contiguous chunks leave one rank with all the
+lines; or contiguous phase blocks when asked for (`axis="phase"`: partitions kernel (a') as well; useful for dense
 phase sweeps such as C3 where n_orb >> world).
 """
 from __future__ import annotations
@@ -27,11 +29,35 @@ def padded_width(n: int, world: int) -> int:
     return -(-n // world)
 
 
+CYCLIC_BLOCK = 256   # wavelengths per block of the block-cyclic split: one window of kernel (c')
+
+
+def cyclic_indices(n_wav: int, world: int, rank: int, block: int = CYCLIC_BLOCK) -> np.ndarray:
+    """Global wavelength indices of `rank` in the block-cyclic split (blocks rank, rank + world, ...), in the
+    order pb200_run_device_cyclic writes them."""
+    n_blocks = -(-n_wav // block)
+    parts = [np.arange(b * block, min((b + 1) * block, n_wav)) for b in range(rank, n_blocks, world)]
+    return np.concatenate(parts) if parts else np.empty(0, dtype=np.int64)
+
+
+def cyclic_width(n_wav: int, world: int, block: int = CYCLIC_BLOCK) -> int:
+    """Largest per-rank wavelength count of the block-cyclic split (rank 0 has it)."""
+    return int(cyclic_indices(n_wav, world, 0, block).size)
+
+
 def unpack_tiles(flat: np.ndarray, n_orb: int, n_wav: int, world: int, axis: str = "wavelength") -> np.ndarray:
     """[world][n_orb*per] (axis="wavelength") or [world][per*n_wav] (axis="phase") gathered tile
     buffers -> (n_orb, n_wav).  Each rank's tile is C-contiguous [n_phase_sel][n_wav_sel] at the
     start of its slot."""
     R = np.empty((n_orb, n_wav), dtype=np.float64)
+    if axis == "cyclic":
+        per = cyclic_width(n_wav, world)
+        flat = flat.reshape(world, n_orb * per)
+        for r in range(world):
+            idx = cyclic_indices(n_wav, world, r)
+            if idx.size:
+                R[:, idx] = flat[r, : n_orb * idx.size].reshape(n_orb, idx.size)
+        return R
     if axis == "wavelength":
         per = padded_width(n_wav, world)
         flat = flat.reshape(world, n_orb * per)
@@ -66,12 +92,16 @@ class ShardedTransit:
             self.lo, self.hi = partition(self.n_wav, self.world)[self.rank]
             self.tile = (0, self.n_orb, self.lo, self.hi)
             self.slot = self.n_orb * padded_width(self.n_wav, self.world)
+        elif axis == "cyclic":
+            self.lo, self.hi = 0, int(cyclic_indices(self.n_wav, self.world, self.rank).size)   # local wavelength count
+            self.tile = (0, self.n_orb, 0, self.hi)
+            self.slot = self.n_orb * cyclic_width(self.n_wav, self.world)
         elif axis == "phase":
             self.lo, self.hi = partition(self.n_orb, self.world)[self.rank]
             self.tile = (self.lo, self.hi, 0, self.n_wav)
             self.slot = padded_width(self.n_orb, self.world) * self.n_wav
         else:
-            raise ValueError("axis must be 'wavelength' or 'phase'")
+            raise ValueError("axis must be 'wavelength', 'cyclic' or 'phase'")
         self.device = torch.device(device) if device is not None else torch.device("cpu")
         self.local = torch.zeros(self.slot, dtype=torch.float64, device=self.device)
         self.gathered = torch.empty(self.world * self.slot, dtype=torch.float64, device=self.device) if self.world > 1 else self.local
@@ -104,7 +134,14 @@ class ShardedTransit:
         if getattr(self, "full", None) is None:
             self.full = torch.empty((self.n_orb, self.n_wav), dtype=torch.float64, device=self.device)
         slots = self.gathered.view(self.world, self.slot)
-        if self.axis == "wavelength":
+        if self.axis == "cyclic":
+            if getattr(self, "_cyc_idx", None) is None:
+                self._cyc_idx = [torch.from_numpy(cyclic_indices(self.n_wav, self.world, r)).to(self.device)
+                                 for r in range(self.world)]
+            for r, idx in enumerate(self._cyc_idx):
+                if idx.numel():
+                    self.full.index_copy_(1, idx, slots[r, : self.n_orb * idx.numel()].view(self.n_orb, idx.numel()))
+        elif self.axis == "wavelength":
             for r, (lo, hi) in enumerate(partition(self.n_wav, self.world)):
                 if hi > lo:
                     self.full[:, lo:hi] = slots[r, : self.n_orb * (hi - lo)].view(self.n_orb, hi - lo)
@@ -129,6 +166,19 @@ class ShardedTransit:
         return unpack_tiles(self.gathered.numpy(), self.n_orb, self.n_wav, self.world, self.axis)
 
 
+def tile_function(ctx, axis: str, world: int, rank: int, want_timing: bool = False, sink: list | None = None):
+    """compute_tile callable of ShardedTransit for the CUDA library: contiguous tiles through pb200_run_device,
+    axis="cyclic" through pb200_run_device_cyclic (the tile bounds are then the local wavelength count)."""
+    def run(p0, p1, w0, w1, out):
+        if axis == "cyclic":
+            t = ctx.run_device_cyclic(p0, p1, CYCLIC_BLOCK, world, rank, out.data_ptr(), want_timing)
+        else:
+            t = ctx.run_device(p0, p1, w0, w1, out.data_ptr(), want_timing)
+        if sink is not None and t is not None:
+            sink.append(t)
+    return run
+
+
 def sum_over_chords(transit, group=None, axis: str = "wavelength", device: int | None = None, dst: int | None = 0,
                     state: dict | None = None):
     """Sharded replacement of Transit.sumOverChords: every rank uploads the (replicated) scene,
@@ -150,11 +200,11 @@ def sum_over_chords(transit, group=None, axis: str = "wavelength", device: int |
     st = state.get("sharded") if state else None
     if st is None or (st.n_orb, st.n_wav, st.axis) != (info["n_orb"], info["n_wav"], axis):
         st = ShardedTransit(info["n_orb"], info["n_wav"], group, axis, torch.device("cuda", device),
-                            compute_tile=lambda p0, p1, w0, w1, out: ctx.run_device(p0, p1, w0, w1, out.data_ptr()))
+                            compute_tile=tile_function(ctx, axis, world, rank))
         if state is not None:
             state["sharded"] = st
     else:
-        st.compute_tile = lambda p0, p1, w0, w1, out: ctx.run_device(p0, p1, w0, w1, out.data_ptr())
+        st.compute_tile = tile_function(ctx, axis, world, rank)
     st.run_device()
     if state is not None:
         state["info"] = info

@@ -32,8 +32,14 @@ def _worker(rank, world, port, n_orb, n_wav, axis, q):
         calls = []
 
         def compute_tile(p0, p1, w0, w1, out):
-            calls.append((p0, p1, w0, w1))
-            tile = np.ascontiguousarray(R_true[p0:p1, w0:w1]).reshape(-1)
+            if axis == "cyclic":      # what pb200_run_device_cyclic writes: the rank's blocks, in order
+                idx = pbd.cyclic_indices(n_wav, world, rank)
+                assert (w0, w1) == (0, idx.size)
+                calls.append(("cyclic", p0, p1, idx.tolist()))
+                tile = np.ascontiguousarray(R_true[p0:p1][:, idx]).reshape(-1)
+            else:
+                calls.append((p0, p1, w0, w1))
+                tile = np.ascontiguousarray(R_true[p0:p1, w0:w1]).reshape(-1)
             out[: tile.size] = torch.from_numpy(tile)
 
         st = pbd.ShardedTransit(n_orb, n_wav, None, axis, "cpu", compute_tile)
@@ -47,7 +53,8 @@ def _worker(rank, world, port, n_orb, n_wav, axis, q):
 
 
 @pytest.mark.parametrize("world,n_orb,n_wav,axis", [(2, 5, 219, "wavelength"), (2, 5, 219, "phase"),
-                                                    (3, 4, 10, "wavelength"), (3, 2, 7, "phase"), (2, 1, 1, "wavelength")])
+                                                    (3, 4, 10, "wavelength"), (3, 2, 7, "phase"), (2, 1, 1, "wavelength"),
+                                                    (2, 3, 1000, "cyclic"), (3, 2, 300, "cyclic")])
 def test_sharded_gather(world, n_orb, n_wav, axis):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
@@ -62,8 +69,13 @@ def test_sharded_gather(world, n_orb, n_wav, axis):
     covered = np.zeros((n_orb, n_wav), dtype=int)
     for rank, ok, calls in results:
         assert ok, f"rank {rank}"
-        for p0, p1, w0, w1 in calls:
-            covered[p0:p1, w0:w1] += 1
+        for call in calls:
+            if call[0] == "cyclic":
+                _, p0, p1, idx = call
+                covered[p0:p1, idx] += 1
+            else:
+                p0, p1, w0, w1 = call
+                covered[p0:p1, w0:w1] += 1
     assert np.all(covered == 1), "tiles must partition the output exactly once"
 
 
@@ -80,3 +92,14 @@ def test_unpack_single_rank():
     R = _truth(3, 11)
     assert np.array_equal(pbd.unpack_tiles(R.reshape(-1).copy(), 3, 11, 1, "wavelength"), R)
     assert np.array_equal(pbd.unpack_tiles(R.reshape(-1).copy(), 3, 11, 1, "phase"), R)
+
+
+def test_cyclic_indices_match_the_library_count():
+    from prometheus_b200 import capi
+    lib = capi.load()
+    for n in (1, 255, 256, 257, 31969, 300306):
+        for world in (1, 2, 3, 8):
+            seen = np.concatenate([pbd.cyclic_indices(n, world, r) for r in range(world)])
+            assert np.array_equal(np.sort(seen), np.arange(n))
+            for r in range(world):
+                assert lib.pb200_cyclic_count(n, pbd.CYCLIC_BLOCK, world, r) == pbd.cyclic_indices(n, world, r).size

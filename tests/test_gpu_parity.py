@@ -368,3 +368,26 @@ def test_exp_sample_count_for_an_optically_thick_scene(transits, monkeypatch):
     padded = -(-n_wav // win) * win
     assert t["exp_samples"] <= records * padded
     assert t["exp_samples"] >= 0.5 * t["executed_samples"], (t["exp_samples"], t["executed_samples"], records, padded)
+
+
+@pytest.mark.parametrize("name,n_ranks", [("C4s", 2), ("C3s", 3), ("C1", 8)])
+def test_block_cyclic_tiles_reassemble_R(name, n_ranks, transits, ctx):
+    """pb200_run_device_cyclic: the ranks' tiles (computed here one after the other on one GPU) put back in place
+    give the full run, to summation-order noise (the window a wavelength falls in differs)."""
+    import torch
+    from prometheus_b200 import distributed as pbd
+    tr = transits(name)
+    R = tr.sumOverChords()
+    n_orb, n_wav = R.shape
+    out = np.full_like(R, np.nan)
+    for r in range(n_ranks):
+        idx = pbd.cyclic_indices(n_wav, n_ranks, r)
+        assert capi.load().pb200_cyclic_count(n_wav, pbd.CYCLIC_BLOCK, n_ranks, r) == idx.size
+        if idx.size == 0:
+            continue
+        buf = torch.empty(n_orb * idx.size, dtype=torch.float64, device="cuda:0")
+        ctx.set_stream(torch.cuda.current_stream().cuda_stream)
+        ctx.run_device_cyclic(0, n_orb, pbd.CYCLIC_BLOCK, n_ranks, r, buf.data_ptr())
+        torch.cuda.synchronize()
+        out[:, idx] = buf.cpu().numpy().reshape(n_orb, idx.size)
+    assert np.max(np.abs(out - R)) < 5e-14
