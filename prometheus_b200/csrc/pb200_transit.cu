@@ -7,18 +7,20 @@
 //   * sigma_phase_kernel looks up -sigma_a(p, w) * 4096/ln2 once per (phase, wavelength)
 //     (np.interp + 10**v - offset, i.e. n_interp_log :34-51) -- the chord-axis splits of one
 //     (phase, wavelength) tile would otherwise each repeat the binary search;
-//   * a thread of transit_kernel owns WPT wavelengths of one orbital phase and keeps those values
-//     in registers;
-//   * the chord records {w, w c1, w c2, Ncol_0..Ncol_{S-1}} of the phase stream through shared
-//     memory in 256-chord tiles, one 1-D TMA bulk copy per tile (cp.async.bulk + mbarrier, double
-//     buffered); every thread of the CTA reads the same record, so the LDS is a broadcast;
-//   * fp64 exp (table-driven, see "Big-table form" in pb200_math.cuh: the kernel is bound by the
-//     FP64 pipe and by the instructions issued next to it, so the exp is built to need as few of
-//     both as possible: 6 FP64 + 3 integer + 1 LDS per sample for one absorber), fp64
-//     accumulators; the chord axis is split over blockIdx.z to get many more CTAs than resident
-//     slots (tail effect), partial sums reduced in a fixed order by finalize_kernel (deterministic).
-#include <cstdlib>
-
+//   * one CTA of transit_kernel = one window of 32 WPT wavelengths of one orbital phase; a thread keeps
+//     its WPT values of every absorber in registers, the 8 warps hold the same wavelengths and split the
+//     chords;
+//   * the ACTIVE chord records {w, w c1, w c2, Ncol_0..Ncol_{S-1}} of the phase (compact_kernel:
+//     transparent chords removed, mirror chords paired) stream through shared memory in 256-chord tiles,
+//     one 1-D TMA bulk copy per tile (cp.async.bulk + mbarrier, double buffered); every thread of a warp
+//     reads the same record, so the LDS is a broadcast;
+//   * optically thin chords (warp-uniform test) are summed as a second-order expansion per chord
+//     (ThinSums), the rest take the fp64 table exp (see "Big-table form" in pb200_math.cuh: the kernel
+//     is bound by the FP64 pipe and by the instructions issued next to it, so the exp is built to need
+//     as few of both as possible: 6 FP64 + 3 integer + 1 LDS per sample for one absorber); fp64
+//     accumulators; the warps' sums are added in a fixed order (deterministic).  Normally the kernel
+//     writes R itself; only when a run has fewer (window, phase) pairs than CTA slots is the chord axis
+//     split over blockIdx.z and the partial sums reduced by finalize_kernel.
 #include "pb200_internal.cuh"
 
 namespace pb200 {
@@ -159,14 +161,14 @@ struct ThinSums {
     }
 };
 
-template <int S, int WPT, bool CLAMP, int NWARPS, int UNROLL = 2, int DROP = 0>
+template <int S, int WPT, bool CLAMP, int NWARPS>
 __device__ __forceinline__ void transit_tile(uint32_t stage, const double (&nsig)[S][WPT], double (&acc)[WPT],
                                              uint32_t tab_base, const double (&smw)[S], ThinSums<S>& thin, int wid, double thin_v) {
     constexpr int R = pb_rec_stride(S);
     constexpr uint32_t kRecBytes = R * sizeof(double);
     // the warps of the CTA share the window (same wavelengths) and split the chords: warp w takes chords
     // w, w + NWARPS, ... of the tile
-#pragma unroll UNROLL
+#pragma unroll 2
     for (int i = 0; i < kChordTile / NWARPS; ++i) {
         const uint32_t rec = stage + (uint32_t)(i * NWARPS + wid) * kRecBytes;
         double d[R], N[S];
@@ -225,8 +227,8 @@ __device__ __forceinline__ void transit_tile(uint32_t stage, const double (&nsig
 // step; their partial sums are added in a fixed order at the end.  Windows are taken in decreasing order of
 // optical thickness (compact_kernel: longest CTAs first).  A window that is thin for every chord of
 // the phase (S <= 2) needs no chord loop at all: its sums are the per-phase totals of compact_kernel.
-template <int S, int WPT, int THREADS, int VAR = 0>
-__global__ void __launch_bounds__(THREADS, (VAR & 1) ? 4 : (THREADS == 256 ? (S == 1 ? 3 : 2) : 6))
+template <int S, int WPT, int THREADS>
+__global__ void __launch_bounds__(THREADS, S == 1 ? 3 : 2)
 transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
     const DevScene& sc = *scp;
     // shared memory: exp table [4096] | stage 0 records | stage 1 records | per-warp sums [NWARPS][WIN]
@@ -321,7 +323,7 @@ transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
             mbar_wait(&full_bar[stage], (t >> 1) & 1);
             const uint32_t sw = stages_addr + stage * kStageBytes;
             if (clamp) transit_tile<S, WPT, true, NWARPS>(sw, nsig, acc, tab_base, smw, thin, wid, prm.thin_v);
-            else transit_tile<S, WPT, false, NWARPS, (VAR & 2) ? 4 : 2, (VAR >> 2)>(sw, nsig, acc, tab_base, smw, thin, wid, prm.thin_v);
+            else transit_tile<S, WPT, false, NWARPS>(sw, nsig, acc, tab_base, smw, thin, wid, prm.thin_v);
             __syncthreads();   // stage may be refilled by the producer in the next iteration
         }
         thin.finish(nsig, acc);
@@ -376,10 +378,10 @@ __global__ void finalize_kernel(const DevScene* __restrict__ scp, const TransitP
     }
 }
 
-template <int S, int WPT, int THREADS, int VAR = 0>
+template <int S, int WPT, int THREADS = 256>
 static cudaError_t launch_one(const DevScene* d_scene, const TransitParams& prm, cudaStream_t st) {
     const size_t smem = (kExpBigEntries + 2 * pb_rec_stride(S) * kChordTile + (THREADS / 32) * 32 * WPT) * sizeof(double);
-    auto kern = transit_kernel<S, WPT, THREADS, VAR>;
+    auto kern = transit_kernel<S, WPT, THREADS>;
     {   // dynamic + static shared memory is always above the 48 KB default limit
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
@@ -390,47 +392,28 @@ static cudaError_t launch_one(const DevScene* d_scene, const TransitParams& prm,
     return cudaGetLastError();
 }
 
-static int env_int(const char* name) {
-    const char* e = getenv(name);
-    return e ? atoi(e) : 0;
-}
-
-// CTA shape: 256 threads x WPT wavelengths, WPT = 8 for 1-2 absorbers, 4 for 3-4, 2 above (register
-// budget: 2 S WPT + temporaries must leave >= 2 CTAs per SM).  PB200_THREADS=128 selects 128-thread
-// CTAs for 1-2 absorbers (tuning experiments only).
-static int transit_threads() {
-    static const int v = env_int("PB200_THREADS");
-    return v == 128 ? 128 : 256;
-}
-
 void launch_sigma_phase(const DevScene* d_scene, const TransitParams& prm, cudaStream_t st) {
     dim3 grid((unsigned)((prm.n_wav_sel + 255) / 256), (unsigned)prm.n_phase);
     sigma_phase_kernel<<<grid, 256, 0, st>>>(d_scene, prm);
 }
 
+// CTA shape: 256 threads x WPT wavelengths, WPT = 8 for 1-2 absorbers, 4 for 3-4, 2 above (register
+// budget: 2 S WPT + temporaries must leave >= 2 CTAs per SM).
 // returns cudaSuccess, or cudaErrorInvalidValue when n_atoms is outside the compiled range
 cudaError_t launch_transit(const DevScene* d_scene, int n_atoms, const TransitParams& prm, cudaStream_t st) {
-    const bool t256 = transit_threads() == 256;
-    static const int var = env_int("PB200_TV");
-    if (n_atoms == 1 && var == 1) return launch_one<1, 8, 256, 1>(d_scene, prm, st);
-    if (n_atoms == 1 && var == 2) return launch_one<1, 8, 256, 2>(d_scene, prm, st);
-    if (n_atoms == 1 && var == 3) return launch_one<1, 8, 256, 3>(d_scene, prm, st);
-    if (n_atoms == 1 && var == 6) return launch_one<1, 8, 256, 6>(d_scene, prm, st);
-    if (n_atoms == 1 && var == 10) return launch_one<1, 8, 256, 10>(d_scene, prm, st);
-    if (n_atoms == 1 && var == 14) return launch_one<1, 8, 256, 14>(d_scene, prm, st);
     switch (n_atoms) {
-        case 1: return t256 ? launch_one<1, 8, 256>(d_scene, prm, st) : launch_one<1, 8, 128>(d_scene, prm, st);
-        case 2: return t256 ? launch_one<2, 8, 256>(d_scene, prm, st) : launch_one<2, 8, 128>(d_scene, prm, st);
-        case 3: return launch_one<3, 4, 256>(d_scene, prm, st);
-        case 4: return launch_one<4, 4, 256>(d_scene, prm, st);
-        case 5: return launch_one<5, 2, 256>(d_scene, prm, st);
-        case 6: return launch_one<6, 2, 256>(d_scene, prm, st);
-        case 7: return launch_one<7, 2, 256>(d_scene, prm, st);
-        case 8: return launch_one<8, 2, 256>(d_scene, prm, st);
-        case 9: return launch_one<9, 2, 256>(d_scene, prm, st);
-        case 10: return launch_one<10, 2, 256>(d_scene, prm, st);
-        case 11: return launch_one<11, 2, 256>(d_scene, prm, st);
-        case 12: return launch_one<12, 2, 256>(d_scene, prm, st);
+        case 1: return launch_one<1, 8>(d_scene, prm, st);
+        case 2: return launch_one<2, 8>(d_scene, prm, st);
+        case 3: return launch_one<3, 4>(d_scene, prm, st);
+        case 4: return launch_one<4, 4>(d_scene, prm, st);
+        case 5: return launch_one<5, 2>(d_scene, prm, st);
+        case 6: return launch_one<6, 2>(d_scene, prm, st);
+        case 7: return launch_one<7, 2>(d_scene, prm, st);
+        case 8: return launch_one<8, 2>(d_scene, prm, st);
+        case 9: return launch_one<9, 2>(d_scene, prm, st);
+        case 10: return launch_one<10, 2>(d_scene, prm, st);
+        case 11: return launch_one<11, 2>(d_scene, prm, st);
+        case 12: return launch_one<12, 2>(d_scene, prm, st);
         default: return cudaErrorInvalidValue;
     }
 }
