@@ -302,6 +302,55 @@ def quick_workload(name, ctx, torch, stream, flush, steps=3, warmup=3):
     return res
 
 
+def retrieval_workload(n_models=64, steps=5, warmup=3, cpu_models=2):
+    """Retrieval batch: forward models/s of the mainRetrieval.py setup (RET: 60 000 chords x 25
+    phases), n_models parameter vectors per call, end to end through RetrievalBatch.run -- host flattening of every
+    model, H2D of the stacked per-phase arrays, one set of launches, light-curve kernel, D2H of the light curves --
+    next to the oracle's time for the same forward model + light curve on one host core."""
+    import prometheus_b200 as pb
+    from prometheus_b200 import retrieval, workloads
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from helpers import oracle, oracle_inputs
+    spec = workloads.get("RET")
+    template = pb.build_transit(spec, nist_rows=nist_rows())
+    orb = template.spatialGrid.constructOrbphaseAxis()
+    band = retrieval.LightcurveBand.for_planet(template.planet, orb, spec["band"]["line_centres"], spec["band"]["bandwidth"])
+    params = workloads.retrieval_samples(n_models)
+    batch = retrieval.RetrievalBatch(template)
+    info = batch.info
+    wall, timings = [], []
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        variants = retrieval.make_variants(template, params)
+        lc, _, t = batch.run(variants, band)
+        if i >= warmup:
+            wall.append(time.perf_counter() - t0)
+            timings.append(t)
+    batch.reset()
+    # CPU oracle: the same forward model and light curve for the first cpu_models parameter vectors
+    t_cpu, err = [], 0.0
+    for k in range(cpu_models):
+        v = workloads.retrieval_variant(spec, *params[k])
+        inp = oracle_inputs(v, nist_rows())
+        con = template.atmosphere.densityDistributionList[0].constituents[0]
+        inp["tables"] = {(0, con.species.name): (con.lookupFunction.x, con.lookupFunction.y)}
+        m = oracle.build_model(v, inp)
+        t0 = time.perf_counter()
+        R = oracle.sum_over_chords(m, batch_size=oracle.reference_batch_size(info["n_chords"], info["n_wav"], info["n_x"], False))
+        lc_ref = oracle.lightcurve(R, m.wavelength, oracle.band_shift(m), spec["band"]["line_centres"], spec["band"]["bandwidth"])
+        t_cpu.append(time.perf_counter() - t0)
+        err = max(err, float(np.max(np.abs(lc_ref - lc[k]))))
+    sec = float(np.mean(wall))
+    return {"title": spec["title"], "n_models": n_models, "n_chords": info["n_chords"], "n_wav": info["n_wav"],
+            "models_per_s_e2e": n_models / sec, "ms_per_batch_e2e": sec * 1e3,
+            "samples_per_s_e2e": n_models * float(info["n_chords"]) * info["n_wav"] / sec,
+            "kernels_ms": {k: float(np.mean([t[k] for t in timings])) for k in ("upload_ms", "column_ms", "transit_ms", "download_ms")},
+            "launches_per_batch": int(timings[-1]["launches"]) + 3,
+            "h2d_bytes_per_model": int(info["n_orb"] * 8 * (2 + 2 + 4 + 8)), "d2h_bytes_per_model": int(info["n_orb"] * 8),
+            "cpu_oracle_models_per_s_one_core": 1.0 / float(np.mean(t_cpu)),
+            "max_abs_diff_lightcurve_gpu_vs_cpu": err}
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -500,6 +549,8 @@ def run_b200(args):
         for name in [w for w in args.others.split(",") if w and w != args.workload]:
             with torch.cuda.stream(stream):
                 out["other_workloads"][name] = quick_workload(name, ctx, torch, stream, flush)
+    if world == 1 and not args.no_retrieval:
+        out["retrieval"] = retrieval_workload()
 
     # ---- CPU baseline on the host cores of this box (rank 0, N = 1 only) -----------------------------
     if world == 1 and args.cpu_seconds > 0:
@@ -536,6 +587,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="C4")
     ap.add_argument("--others", default="C2,C3,C5", help="other BASELINE configs reported under other_workloads (N=1)")
+    ap.add_argument("--no-retrieval", action="store_true", help="skip the retrieval-batch leg (N=1)")
     ap.add_argument("--cpu-seconds", type=float, default=None,
                     help="CPU budget: cpu_baseline sample (default 15 s) / whole --impl reference run (default 120 s)")
     args = ap.parse_args()

@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define PB200_ABI_VERSION 2
+#define PB200_ABI_VERSION 3
 
 typedef enum {
     PB200_OK = 0,
@@ -128,6 +128,35 @@ typedef struct {
                                     second-order expansion summed per chord); upper bound    */
 } pb200_timing;
 
+/* ---- retrieval batches ------------------------------------------------
+ * The consumer sketched by mainRetrieval.py:18-93: many forward models of ONE setup that differ only in
+ * free parameters (mainRetrieval.py:18-21: moon phase, orbit, radius; equally N, q, T ...).  Axes, the
+ * wavelength grid and every table (sigma, F*, molecules, serpens) of the resident scene stay in HBM; a
+ * model carries what a free parameter can move: the scenario scalars and the per-phase arrays the host
+ * code evaluates with the reference's own expressions.  The models of a batch are stacked along the
+ * orbital-phase axis ("virtual phases", model-major: row m*n_orb + p), so that ONE set of launches does
+ * the whole batch. */
+typedef struct {
+    const pb200_scenario* scenarios; /* [n_scenarios of the resident scene], same types and constituent
+                                        ranges; read: T is ignored, p[8], centre_x, centre_y, shift,
+                                        amplitude ([n_orb] each; amplitude NULL = 1)                 */
+    const double* planet_y;      /* [n_orb]                                                          */
+    const double* moon_R;        /* [n_moons]                                                        */
+    const double* moon_y;        /* [n_moons*n_orb]                                                  */
+} pb200_model;
+
+/* band-averaged light curve (mainRetrieval.py:72-93): for phase p the filter selects the wavelengths with
+   centre_l*shift[p] - bandwidth/2 <= lambda <= centre_l*shift[p] + bandwidth/2 for any line l;
+   lightcurve[p] = mean(R[p, selected]) / max(R[p, :])   (nan if nothing is selected, as np.mean)        */
+typedef struct {
+    int32_t n_lines;             /* <= 16                                                             */
+    int32_t reserved;
+    const double* line_centre;   /* [n_lines] rest wavelengths, cm                                    */
+    const double* shift;         /* [n_orb] Doppler factor of the band centres (planet LOS velocity,
+                                    mainRetrieval.py:77-78); the same for every model of a batch      */
+    double bandwidth;            /* filterBandwidth, cm                                               */
+} pb200_band;
+
 typedef struct pb200_ctx pb200_ctx;
 
 /* ---- life cycle ------------------------------------------------------------------------ */
@@ -166,6 +195,20 @@ int pb200_run_device(pb200_ctx* ctx, int phase_lo, int phase_hi, int64_t wav_lo,
 int pb200_run_device_cyclic(pb200_ctx* ctx, int phase_lo, int phase_hi, int64_t wav_block, int n_ranks,
                             int rank, double* R_dev, pb200_timing* timing);
 int64_t pb200_cyclic_count(int64_t n_wav, int64_t wav_block, int n_ranks, int rank);
+/* ---- retrieval batches -------------------------------------------------------------------
+ * pb200_set_models: stacks n_models models on the resident scene (pb200_set_scene must have been called;
+ * its own per-phase arrays are model-independent inputs such as the grid and are replaced).  Afterwards
+ * the context has n_models*n_orb (virtual) phases: pb200_run*, pb200_column_density ... address row
+ * m*n_orb + p.  pb200_set_models(ctx, 0, NULL) returns to the scene as uploaded.
+ * pb200_lightcurve: light curve of rows [phase_lo, phase_hi) of R (device pointer to
+ * [phase_hi-phase_lo][n_wav], or NULL = the R of the last pb200_run / pb200_run_batch of this context).
+ * pb200_run_batch = pb200_set_models + one run over all rows and wavelengths + pb200_lightcurve;
+ * lightcurve_host[n_models*n_orb]; R_host NULL or [n_models*n_orb*n_wav].                             */
+int pb200_set_models(pb200_ctx* ctx, int n_models, const pb200_model* models);
+int pb200_lightcurve(pb200_ctx* ctx, const pb200_band* band, int phase_lo, int phase_hi,
+                     const double* R_dev, double* lightcurve_host);
+int pb200_run_batch(pb200_ctx* ctx, int n_models, const pb200_model* models, const pb200_band* band,
+                    double* lightcurve_host, double* R_host, pb200_timing* timing);
 /* timing record of the last pb200_run / pb200_voigt_sigma call of this context */
 int pb200_last_timing(pb200_ctx* ctx, pb200_timing* timing);
 

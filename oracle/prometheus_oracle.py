@@ -404,6 +404,27 @@ def sum_over_chords(m: Model, batch_size: int | None = None, wavelength=None, op
     return F_in_sum / F_out_sum
 
 
+# ---------------------------------------------------------------------------------------------------
+# light curve of a retrieval forward model -- mainRetrieval.py:69-93
+# ---------------------------------------------------------------------------------------------------
+def band_shift(m: Model):
+    """mainRetrieval.py:77-78: v_los = planet.getLOSvelocity(orbphase); shift = calculateDopplerShift(v_los)"""
+    return doppler_shift(planet_vlos(m.planet, m.star, m.orb))
+
+
+def lightcurve(R, wavelength, shift, line_centres, bandwidth):
+    """mainRetrieval.py:83-93: per phase, mean of R over the wavelengths within +-bandwidth/2 of any shifted line
+    centre, divided by the maximum of R over all wavelengths."""
+    out = []
+    for idx in range(R.shape[0]):
+        sel = np.zeros(len(wavelength), dtype=bool)
+        for centre in line_centres:
+            sel = sel + ((wavelength >= centre * shift[idx] - bandwidth / 2.) * (wavelength <= centre * shift[idx] + bandwidth / 2.))
+        with np.errstate(invalid="ignore", divide="ignore"):
+            out.append(np.mean(R[idx, sel]) / np.max(R[idx, :]) if sel.any() else np.float64("nan"))
+    return np.array(out)
+
+
 def reference_batch_size(n_chords, n_wav, n_x, has_molecules, max_memory_gb=2.0):
     """memoryHandler.py:34-66 without the psutil clamp"""
     per = (n_x * n_wav * 64 if has_molecules else n_wav * 16) * 2.0

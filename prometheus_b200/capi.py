@@ -12,7 +12,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libprometheus_b200.so")
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 c_double_p = C.POINTER(C.c_double)
 
@@ -23,6 +23,7 @@ EXPORTS = [
     "pb200_last_timing", "pb200_number_density", "pb200_number_density_chords", "pb200_column_density",
     "pb200_chord_masks", "pb200_optical_depth", "pb200_sigma_lookup", "pb200_voigt_sigma",
     "pb200_voigt_profile", "pb200_molecular_sigma", "pb200_write_output", "pb200_probe_fp64",
+    "pb200_set_models", "pb200_lightcurve", "pb200_run_batch",
 ]
 
 SCN_BAROMETRIC, SCN_HYDROSTATIC, SCN_POWERLAW, SCN_TORUS, SCN_SERPENS = range(5)
@@ -65,6 +66,18 @@ class Scene(C.Structure):
         ("planet_y", c_double_p), ("moon_R", c_double_p), ("moon_y", c_double_p),
         ("scenarios", C.POINTER(Scenario)), ("constituents", C.POINTER(Constituent)),
     ]
+
+
+class Model(C.Structure):
+    """pb200_model: what a free parameter of a retrieval can move (mainRetrieval.py:18-21)."""
+    _fields_ = [("scenarios", C.POINTER(Scenario)), ("planet_y", c_double_p), ("moon_R", c_double_p),
+                ("moon_y", c_double_p)]
+
+
+class Band(C.Structure):
+    """pb200_band: the light-curve filter of mainRetrieval.py:72-93."""
+    _fields_ = [("n_lines", C.c_int32), ("reserved", C.c_int32), ("line_centre", c_double_p),
+                ("shift", c_double_p), ("bandwidth", C.c_double)]
 
 
 class Timing(C.Structure):
@@ -131,6 +144,10 @@ def load():
                                             i64, i64, i64, c_double_p]),
         "pb200_write_output": (C.c_int, [C.c_char_p, C.c_char_p, c_double_p, c_double_p, c_double_p, i32, i64, i32]),
         "pb200_probe_fp64": (C.c_int, [vp, c_double_p, c_double_p]),
+        "pb200_set_models": (C.c_int, [vp, i32, C.POINTER(Model)]),
+        "pb200_lightcurve": (C.c_int, [vp, C.POINTER(Band), i32, i32, vp, c_double_p]),
+        "pb200_run_batch": (C.c_int, [vp, i32, C.POINTER(Model), C.POINTER(Band), c_double_p, c_double_p,
+                                      C.POINTER(Timing)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -268,6 +285,28 @@ class Context:
         self.check(self.lib.pb200_run_device_cyclic(self.handle, phase_lo, phase_hi, wav_block, n_ranks, rank,
                                                     C.c_void_p(dev_ptr), C.byref(t) if want_timing else None))
         return t.as_dict() if want_timing else None
+
+    def set_models(self, models, n_models: int, keep=None):
+        """Stack `n_models` pb200_model structs on the resident scene (n_models == 0: back to the scene)."""
+        self._keep_models = keep
+        self.check(self.lib.pb200_set_models(self.handle, n_models, models))
+
+    def lightcurve(self, band: Band, phase_lo: int, phase_hi: int, dev_ptr: int | None = None) -> np.ndarray:
+        out = np.empty(phase_hi - phase_lo, dtype=np.float64)
+        self.check(self.lib.pb200_lightcurve(self.handle, C.byref(band), phase_lo, phase_hi,
+                                             C.c_void_p(dev_ptr) if dev_ptr else None, dptr(out)))
+        return out
+
+    def run_batch(self, models, n_models: int, band: Band | None, n_orb: int, n_wav: int, want_R: bool = False,
+                  keep=None):
+        self._keep_models = keep
+        lc = np.empty((n_models, n_orb), dtype=np.float64) if band is not None else None
+        R = pinned_pool.empty((n_models, n_orb, n_wav)) if want_R else None
+        t = Timing()
+        self.check(self.lib.pb200_run_batch(self.handle, n_models, models, C.byref(band) if band is not None else None,
+                                            dptr(lc) if lc is not None else None, dptr(R) if R is not None else None,
+                                            C.byref(t)))
+        return lc, R, t.as_dict()
 
     def last_timing(self) -> dict:
         t = Timing()

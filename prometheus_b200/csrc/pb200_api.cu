@@ -44,6 +44,8 @@ void launch_molecular_sigma(const MolTable&, double offset, const double* P, dou
                             int64_t n_x, int64_t n_wav, double* out, int sm_count, cudaStream_t);
 void launch_optical_depth(const DevScene*, const double* sigma_u, int64_t n_chords, int64_t wav_lo, int64_t n_wav_sel,
                           double* tau, cudaStream_t);
+cudaError_t launch_lightcurve(const double* R_rows, const double* wavelength, int64_t n_wav, int n_rows, int phase_lo,
+                              int n_orb_model, const pb200_band& band, const double* shift_dev, double* out, cudaStream_t);
 void launch_probe_dfma(double* out, int blocks, int iters, cudaStream_t);
 void launch_probe_exp(double* out, int blocks, int iters, const double* exp_tab, cudaStream_t);
 
@@ -79,6 +81,17 @@ struct pb200_ctx {
     cudaEvent_t ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // 6,7: scene upload
     pb200_timing last = {};
     double upload_ms = 0.0;
+    // retrieval batches (pb200_set_models): the scene as uploaded, the stacked per-phase arrays of the batch
+    DevScene base;               // h_scene at the end of pb200_set_scene
+    void* marena = nullptr;      // device: stacked per-phase arrays + per-phase scenario parameters
+    size_t marena_bytes = 0;
+    void* mstage = nullptr;      // pinned staging of the same
+    size_t mstage_bytes = 0;
+    bool mstage_busy = false;    // a copy out of mstage may still be in flight
+    double* d_band = nullptr;    // device: band shift [n_orb_model] then light curve [rows]
+    size_t band_bytes = 0;
+    int lastR_phase_lo = 0, lastR_n_phase = 0;   // rows of R left in `scratch` by the last pb200_run / pb200_run_batch
+    bool lastR_full = false;                     // ... over the whole wavelength grid
 };
 
 static int fail(pb200_ctx* c, int code, const char* fmt, ...) {
@@ -181,6 +194,9 @@ void pb200_destroy(pb200_ctx* c) {
     free_scene(c);
     if (c->scratch) cudaFree(c->scratch);
     if (c->stage) cudaFreeHost(c->stage);
+    if (c->mstage) cudaFreeHost(c->mstage);
+    if (c->marena) cudaFree(c->marena);
+    if (c->d_band) cudaFree(c->d_band);
     if (c->d_scene) cudaFree(c->d_scene);
     if (c->d_oob) cudaFree(c->d_oob);
     if (c->d_exp_tab) cudaFree(c->d_exp_tab);
@@ -248,6 +264,56 @@ template <typename T>
 const T* at(void* base, size_t off) { return reinterpret_cast<const T*>(static_cast<char*>(base) + off); }
 
 }  // namespace
+
+
+// Lays out the derived device arrays (phase-major rows, see DevScene) for c->h_scene.n_orb phases in the grow-only
+// derived arena and clears the running maxima.  Called by pb200_set_scene and by pb200_set_models (where the
+// number of phases is n_models * n_orb).
+static int plan_derived(pb200_ctx* c) {
+    DevScene& h = c->h_scene;
+    const int n_atoms = h.n_atoms;
+    const bool fstar_per_chord = h.n_fstar > 0 && h.vsini != 0.0;
+    struct Want { double** p; size_t n; };
+    std::vector<Want> wants;
+    double *nmax_d = nullptr, *smax_d = nullptr, *nact_d = nullptr;
+    wants.push_back({&h.w_out, (size_t)h.Mp});
+    wants.push_back({&h.star_shift, (size_t)h.Mp});
+    wants.push_back({&h.w_in, (size_t)h.n_orb * h.Mp});
+    wants.push_back({&h.ncol, (size_t)n_atoms * h.n_orb * h.Mp});
+    wants.push_back({&h.rec, (size_t)pb_rec_stride(n_atoms) * h.n_orb * h.Mp});
+    wants.push_back({&nmax_d, (size_t)(n_atoms ? n_atoms : 1) * h.n_orb});
+    wants.push_back({&smax_d, (size_t)(n_atoms ? n_atoms : 1) * h.n_orb});
+    wants.push_back({&nact_d, (size_t)(h.n_orb + 1) / 2});
+    wants.push_back({&h.w0, (size_t)h.n_orb});
+    wants.push_back({&h.thin_tot, (size_t)h.n_orb * 8});
+    for (int i = 0; i < h.n_scen; ++i)
+        if (h.scen[i].density_slot >= 0)
+            wants.push_back({&h.density[h.scen[i].density_slot], (size_t)h.n_orb * h.M * h.n_x});
+    wants.push_back({&h.fout, fstar_per_chord ? (size_t)h.n_wav : 1});
+    size_t need = 0;
+    for (const auto& w : wants) need += ((w.n ? w.n : 1) * sizeof(double) + 255) & ~size_t(255);
+    if (need > c->darena_bytes) {
+        if (c->darena) PB_CUDA(c, cudaFree(c->darena));
+        c->darena = nullptr; c->darena_bytes = 0;
+        PB_CUDA(c, cudaMalloc(&c->darena, need));
+        c->darena_bytes = need;
+    }
+    {
+        size_t off = 0;
+        for (const auto& w : wants) {
+            *w.p = reinterpret_cast<double*>(static_cast<char*>(c->darena) + off);
+            off += ((w.n ? w.n : 1) * sizeof(double) + 255) & ~size_t(255);
+        }
+    }
+    h.exp_tab = c->d_exp_tab;
+    h.nmax = reinterpret_cast<unsigned long long*>(nmax_d);
+    h.smax = reinterpret_cast<unsigned long long*>(smax_d);
+    h.n_act = reinterpret_cast<int*>(nact_d);
+    h.stat = reinterpret_cast<unsigned long long*>(c->d_oob);
+    PB_CUDA(c, cudaMemsetAsync(nmax_d, 0, (size_t)(n_atoms ? n_atoms : 1) * h.n_orb * sizeof(double), c->stream));
+    PB_CUDA(c, cudaMemsetAsync(smax_d, 0, (size_t)(n_atoms ? n_atoms : 1) * h.n_orb * sizeof(double), c->stream));
+    return PB200_OK;
+}
 
 extern "C" int pb200_set_scene(pb200_ctx* c, const pb200_scene* s) {
     if (!c || !s) return PB200_ERR_INVALID;
@@ -418,48 +484,11 @@ extern "C" int pb200_set_scene(pb200_ctx* c, const pb200_scene* s) {
     }
     h.n_atoms = n_atoms; h.n_mols = n_mols;
 
-    // ---- derived device arrays -------------------------------------------------------------------
-    const bool fstar_per_chord = h.n_fstar > 0 && h.vsini != 0.0;
-    struct Want { double** p; size_t n; };
-    std::vector<Want> wants;
-    double *nmax_d = nullptr, *smax_d = nullptr, *nact_d = nullptr;
-    wants.push_back({&h.w_out, (size_t)h.Mp});
-    wants.push_back({&h.star_shift, (size_t)h.Mp});
-    wants.push_back({&h.w_in, (size_t)h.n_orb * h.Mp});
-    wants.push_back({&h.ncol, (size_t)n_atoms * h.n_orb * h.Mp});
-    wants.push_back({&h.rec, (size_t)pb_rec_stride(n_atoms) * h.n_orb * h.Mp});
-    wants.push_back({&nmax_d, (size_t)(n_atoms ? n_atoms : 1) * h.n_orb});
-    wants.push_back({&smax_d, (size_t)(n_atoms ? n_atoms : 1) * h.n_orb});
-    wants.push_back({&nact_d, (size_t)(h.n_orb + 1) / 2});
-    wants.push_back({&h.w0, (size_t)h.n_orb});
-    wants.push_back({&h.thin_tot, (size_t)h.n_orb * 8});
-    for (int i = 0; i < s->n_scenarios; ++i)
-        if (h.scen[i].density_slot >= 0)
-            wants.push_back({&h.density[h.scen[i].density_slot], (size_t)h.n_orb * h.M * h.n_x});
-    wants.push_back({&h.fout, fstar_per_chord ? (size_t)h.n_wav : 1});
-    size_t need = 0;
-    for (const auto& w : wants) need += ((w.n ? w.n : 1) * sizeof(double) + 255) & ~size_t(255);
-    if (need > c->darena_bytes) {
-        if (c->darena) PB_CUDA(c, cudaFree(c->darena));
-        c->darena = nullptr; c->darena_bytes = 0;
-        PB_CUDA(c, cudaMalloc(&c->darena, need));
-        c->darena_bytes = need;
-    }
+    c->general_path = (n_mols > 0) || (h.n_fstar > 0 && h.vsini != 0.0);
     {
-        size_t off = 0;
-        for (const auto& w : wants) {
-            *w.p = reinterpret_cast<double*>(static_cast<char*>(c->darena) + off);
-            off += ((w.n ? w.n : 1) * sizeof(double) + 255) & ~size_t(255);
-        }
+        int rc = plan_derived(c);
+        if (rc) return rc;
     }
-    h.exp_tab = c->d_exp_tab;
-    h.nmax = reinterpret_cast<unsigned long long*>(nmax_d);
-    h.smax = reinterpret_cast<unsigned long long*>(smax_d);
-    h.n_act = reinterpret_cast<int*>(nact_d);
-    h.stat = reinterpret_cast<unsigned long long*>(c->d_oob);
-    PB_CUDA(c, cudaMemsetAsync(nmax_d, 0, (size_t)(n_atoms ? n_atoms : 1) * h.n_orb * sizeof(double), c->stream));
-    PB_CUDA(c, cudaMemsetAsync(smax_d, 0, (size_t)(n_atoms ? n_atoms : 1) * h.n_orb * sizeof(double), c->stream));
-    c->general_path = (n_mols > 0) || fstar_per_chord;
     {   // mirror pairing of chords (compact_kernel): all bodies lie in z = 0 and every analytic density depends
         // on z^2 only; the tabulated (SERPENS) density does not.  The phi axis must be mirror symmetric about
         // pi/2 and 3 pi/2 on the grid itself: sin(phi_i') = sin(phi_i), cos(phi_i') = -cos(phi_i), i' = n/2-1-i.
@@ -474,7 +503,9 @@ extern "C" int pb200_set_scene(pb200_ctx* c, const pb200_scene* s) {
         const char* off = getenv("PB200_NO_MIRROR");   // measurement / debugging only
         h.mirror = (ok && !(off && off[0] == '1')) ? 1 : 0;
     }
-    h.fout_per_wav = fstar_per_chord ? 1 : 0;
+    h.fout_per_wav = (h.n_fstar > 0 && h.vsini != 0.0) ? 1 : 0;
+    h.n_orb_model = h.n_orb;
+    h.moon_R_per_phase = 0;
 
     PB_CUDA(c, cudaMemcpyAsync(c->d_scene, &h, sizeof(DevScene), cudaMemcpyHostToDevice, c->stream));
     // phase-independent prologue: flux weights and stellar surface shifts
@@ -487,6 +518,8 @@ extern "C" int pb200_set_scene(pb200_ctx* c, const pb200_scene* s) {
     // the next pb200_set_scene, and the upload time is read back lazily (collect_timing)
     c->upload_ms = -1.0;
     c->has_scene = true;
+    c->base = h;
+    c->lastR_full = false;
     return PB200_OK;
 }
 
@@ -514,6 +547,7 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     const int64_t n_wav_sel = wav_hi - wav_lo;
     const int64_t n_out = (int64_t)n_phase * n_wav_sel;
     const int64_t launches0 = c->launches;
+    c->lastR_full = false;
 
     TransitParams prm;
     prm.phase_lo = phase_lo; prm.n_phase = n_phase; prm.wav_lo = wav_lo; prm.n_wav_sel = n_wav_sel;
@@ -608,6 +642,9 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     c->last.exp_samples = c->last.executed_samples;
     c->last_wpt = prm.win / 32;   // wavelengths per thread of kernel (c')
     c->last_n_wav_sel = n_wav_sel;
+    // R left at the start of `scratch` (pb200_lightcurve with R_dev == NULL reads it there)
+    c->lastR_full = R_in_scratch && !cyc_block && wav_lo == 0 && n_wav_sel == h.n_wav;
+    c->lastR_phase_lo = phase_lo; c->lastR_n_phase = n_phase;
     return PB200_OK;
 }
 
@@ -753,6 +790,198 @@ int need_ctx(pb200_ctx* c) {
 }
 
 }  // namespace
+
+// =================================================================================================
+// retrieval batches: models stacked along the phase axis, light-curve epilogue
+// =================================================================================================
+extern "C" int pb200_set_models(pb200_ctx* c, int n_models, const pb200_model* models) {
+    int rc = check_scene(c);
+    if (rc) return rc;
+    if (n_models < 0 || (n_models > 0 && !models)) return fail(c, PB200_ERR_INVALID, "pb200_set_models: n_models=%d", n_models);
+    const DevScene& b = c->base;
+    DevScene& h = c->h_scene;
+    c->lastR_full = false;
+    if (n_models == 0) {   // back to the scene as uploaded
+        h = b;
+    } else {
+        const int nb = b.n_orb;
+        const int64_t n_tot64 = (int64_t)n_models * nb;
+        if (n_tot64 > (1 << 24)) return fail(c, PB200_ERR_INVALID, "batch of %d models x %d phases is too large", n_models, nb);
+        const int n_tot = (int)n_tot64;
+        for (int m = 0; m < n_models; ++m) {
+            const pb200_model& q = models[m];
+            if (!q.scenarios || !q.planet_y || (b.n_moons && (!q.moon_R || !q.moon_y)))
+                return fail(c, PB200_ERR_INVALID, "model %d has NULL array pointers", m);
+            for (int i = 0; i < b.n_scen; ++i) {
+                const pb200_scenario& qs = q.scenarios[i];
+                if (qs.type != b.scen[i].type || qs.n_constituents != b.scen[i].n_cons || qs.first_constituent != b.scen[i].first_cons)
+                    return fail(c, PB200_ERR_INVALID, "model %d scenario %d: type / constituents differ from the resident scene", m, i);
+                if (!qs.shift || (qs.type != PB200_SCN_SERPENS && (!qs.centre_x || !qs.centre_y)))
+                    return fail(c, PB200_ERR_INVALID, "model %d scenario %d: per-phase arrays are NULL", m, i);
+            }
+        }
+        // layout of the model arena, in doubles
+        size_t off = 0;
+        auto take = [&](size_t n) { const size_t o = off; off += (n + 31) & ~size_t(31); return o; };
+        const size_t o_py = take(n_tot);
+        const size_t o_mR = b.n_moons ? take((size_t)b.n_moons * n_tot) : 0;
+        const size_t o_my = b.n_moons ? take((size_t)b.n_moons * n_tot) : 0;
+        struct SO { size_t cx, cy, sh, amp, pp; bool has_centre, has_amp; };
+        SO so[kMaxScenarios];
+        for (int i = 0; i < b.n_scen; ++i) {
+            so[i].has_centre = b.scen[i].type != PB200_SCN_SERPENS;
+            so[i].has_amp = b.scen[i].amplitude != nullptr;
+            for (int m = 0; m < n_models; ++m) so[i].has_amp |= models[m].scenarios[i].amplitude != nullptr;
+            so[i].cx = so[i].has_centre ? take(n_tot) : 0;
+            so[i].cy = so[i].has_centre ? take(n_tot) : 0;
+            so[i].sh = take(n_tot);
+            so[i].amp = so[i].has_amp ? take(n_tot) : 0;
+            so[i].pp = take((size_t)n_tot * 8);
+        }
+        const size_t bytes = off * sizeof(double);
+        PB_CUDA(c, cudaSetDevice(c->device));
+        if (c->mstage_busy) { PB_CUDA(c, cudaStreamSynchronize(c->stream)); c->mstage_busy = false; }
+        if (bytes > c->mstage_bytes) {
+            if (c->mstage) cudaFreeHost(c->mstage);
+            c->mstage = nullptr; c->mstage_bytes = 0;
+            PB_CUDA(c, cudaMallocHost(&c->mstage, bytes));
+            c->mstage_bytes = bytes;
+        }
+        if (bytes > c->marena_bytes) {
+            if (c->marena) PB_CUDA(c, cudaFree(c->marena));
+            c->marena = nullptr; c->marena_bytes = 0;
+            PB_CUDA(c, cudaMalloc(&c->marena, bytes));
+            c->marena_bytes = bytes;
+        }
+        double* st = static_cast<double*>(c->mstage);
+        const size_t row = (size_t)nb * sizeof(double);
+        for (int m = 0; m < n_models; ++m) {
+            const pb200_model& q = models[m];
+            const size_t r0 = (size_t)m * nb;
+            memcpy(st + o_py + r0, q.planet_y, row);
+            for (int k = 0; k < b.n_moons; ++k) {
+                memcpy(st + o_my + (size_t)k * n_tot + r0, q.moon_y + (size_t)k * nb, row);
+                for (int p = 0; p < nb; ++p) st[o_mR + (size_t)k * n_tot + r0 + p] = q.moon_R[k];
+            }
+            for (int i = 0; i < b.n_scen; ++i) {
+                const pb200_scenario& qs = q.scenarios[i];
+                if (so[i].has_centre) { memcpy(st + so[i].cx + r0, qs.centre_x, row); memcpy(st + so[i].cy + r0, qs.centre_y, row); }
+                memcpy(st + so[i].sh + r0, qs.shift, row);
+                if (so[i].has_amp)
+                    for (int p = 0; p < nb; ++p) st[so[i].amp + r0 + p] = qs.amplitude ? qs.amplitude[p] : 1.0;
+                for (int p = 0; p < nb; ++p) memcpy(st + so[i].pp + (r0 + p) * 8, qs.p, 8 * sizeof(double));
+            }
+        }
+        PB_CUDA(c, cudaMemcpyAsync(c->marena, c->mstage, bytes, cudaMemcpyHostToDevice, c->stream));
+        c->mstage_busy = true;
+        const double* A = static_cast<const double*>(c->marena);
+        h = b;
+        h.n_orb = n_tot; h.n_orb_model = nb;
+        h.planet_y = A + o_py;
+        if (b.n_moons) { h.moon_R = A + o_mR; h.moon_y = A + o_my; h.moon_R_per_phase = 1; }
+        for (int i = 0; i < b.n_scen; ++i) {
+            DevScenario& d = h.scen[i];
+            if (so[i].has_centre) { d.centre_x = A + so[i].cx; d.centre_y = A + so[i].cy; }
+            d.shift = A + so[i].sh;
+            d.amplitude = so[i].has_amp ? A + so[i].amp : nullptr;
+            d.p_phase = A + so[i].pp;
+            memcpy(d.p, models[0].scenarios[i].p, sizeof d.p);
+        }
+    }
+    rc = plan_derived(c);
+    if (rc) return rc;
+    PB_CUDA(c, cudaMemcpyAsync(c->d_scene, &h, sizeof(DevScene), cudaMemcpyHostToDevice, c->stream));
+    launch_sky_cells(c->d_scene, h.Mp, c->stream);   // the derived arena was laid out afresh
+    launch_fout_scalar(c->d_scene, c->stream);
+    c->launches += 2;
+    PB_CUDA(c, cudaGetLastError());
+    return PB200_OK;
+}
+
+namespace {
+
+int ensure_band(pb200_ctx* c, size_t doubles) {
+    const size_t bytes = doubles * sizeof(double);
+    if (bytes <= c->band_bytes) return PB200_OK;
+    if (c->d_band) { PB_CUDA(c, cudaFree(c->d_band)); c->d_band = nullptr; c->band_bytes = 0; }
+    PB_CUDA(c, cudaMalloc((void**)&c->d_band, bytes));
+    c->band_bytes = bytes;
+    return PB200_OK;
+}
+
+// light curves of rows [phase_lo, phase_hi) of R_rows (device) into d_band + n_orb_model; not synchronised
+int enqueue_lightcurve(pb200_ctx* c, const pb200_band* band, int phase_lo, int phase_hi, const double* R_rows) {
+    const DevScene& h = c->h_scene;
+    if (!band || band->n_lines < 1 || band->n_lines > 16 || !band->line_centre || !band->shift)
+        return fail(c, PB200_ERR_INVALID, "pb200_band: 1..16 line centres and a shift array are required");
+    if (phase_lo < 0 || phase_hi > h.n_orb || phase_lo >= phase_hi)
+        return fail(c, PB200_ERR_INVALID, "rows [%d,%d) outside [0,%d)", phase_lo, phase_hi, h.n_orb);
+    const int nb = h.n_orb_model, n_rows = phase_hi - phase_lo;
+    int rc = ensure_band(c, (size_t)nb + n_rows);
+    if (rc) return rc;
+    PB_CUDA(c, cudaMemcpyAsync(c->d_band, band->shift, (size_t)nb * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    cudaError_t e = launch_lightcurve(R_rows, h.wavelength, h.n_wav, n_rows, phase_lo, nb, *band, c->d_band, c->d_band + nb, c->stream);
+    if (e != cudaSuccess) return fail(c, PB200_ERR_CUDA, "lightcurve launch: %s", cudaGetErrorString(e));
+    c->launches += 1;
+    return PB200_OK;
+}
+
+}  // namespace
+
+extern "C" int pb200_lightcurve(pb200_ctx* c, const pb200_band* band, int phase_lo, int phase_hi, const double* R_dev,
+                                double* lightcurve_host) {
+    int rc = check_scene(c);
+    if (rc) return rc;
+    if (!lightcurve_host) return fail(c, PB200_ERR_INVALID, "lightcurve_host == NULL");
+    const double* rows = R_dev;
+    if (!rows) {
+        if (!c->lastR_full || phase_lo < c->lastR_phase_lo || phase_hi > c->lastR_phase_lo + c->lastR_n_phase)
+            return fail(c, PB200_ERR_INVALID, "no resident R covers rows [%d,%d): run pb200_run over the whole wavelength grid first", phase_lo, phase_hi);
+        rows = c->scratch + (int64_t)(phase_lo - c->lastR_phase_lo) * c->h_scene.n_wav;
+    }
+    rc = enqueue_lightcurve(c, band, phase_lo, phase_hi, rows);
+    if (rc) return rc;
+    return download(c, lightcurve_host, c->d_band + c->h_scene.n_orb_model, (size_t)(phase_hi - phase_lo) * sizeof(double));
+}
+
+extern "C" int pb200_run_batch(pb200_ctx* c, int n_models, const pb200_model* models, const pb200_band* band,
+                               double* lightcurve_host, double* R_host, pb200_timing* timing) {
+    int rc = check_scene(c);
+    if (rc) return rc;
+    if (n_models < 1) return fail(c, PB200_ERR_INVALID, "pb200_run_batch: n_models=%d", n_models);
+    if (!lightcurve_host && !R_host) return fail(c, PB200_ERR_INVALID, "pb200_run_batch: nothing to return");
+    if (lightcurve_host && !band) return fail(c, PB200_ERR_INVALID, "pb200_run_batch: a band is needed for light curves");
+    PB_CUDA(c, cudaEventRecord(c->ev[6], c->stream));
+    rc = pb200_set_models(c, n_models, models);
+    if (rc) return rc;
+    PB_CUDA(c, cudaEventRecord(c->ev[7], c->stream));
+    c->upload_ms = -1.0;
+    const DevScene& h = c->h_scene;
+    rc = enqueue_run(c, 0, h.n_orb, 0, h.n_wav, nullptr, true);
+    if (rc) return rc;
+    PB_CUDA(c, cudaEventRecord(c->ev[0], c->stream));
+    if (lightcurve_host) {
+        rc = enqueue_lightcurve(c, band, 0, h.n_orb, c->scratch);
+        if (rc) return rc;
+        PB_CUDA(c, cudaMemcpyAsync(lightcurve_host, c->d_band + h.n_orb_model, (size_t)h.n_orb * sizeof(double),
+                                   cudaMemcpyDeviceToHost, c->stream));
+    }
+    if (R_host)
+        PB_CUDA(c, cudaMemcpyAsync(R_host, c->scratch, (size_t)h.n_orb * h.n_wav * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    PB_CUDA(c, cudaEventRecord(c->ev[1], c->stream));
+    rc = check_oob(c);   // synchronises the stream
+    c->mstage_busy = false;
+    if (rc) return rc;
+    PB_CUDA(c, cudaGetLastError());
+    rc = collect_timing(c);
+    if (rc) return rc;
+    float ms = 0;
+    PB_CUDA(c, cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]));
+    c->last.download_ms = ms;   // light-curve kernel + D2H
+    if (timing) *timing = c->last;
+    return PB200_OK;
+}
+
 
 extern "C" int pb200_number_density(pb200_ctx* c, int scenario, double* n_host) {
     int rc = check_scene(c);

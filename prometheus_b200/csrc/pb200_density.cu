@@ -37,7 +37,7 @@ __device__ __forceinline__ bool pb_blocked(const DevScene& sc, int p, double y, 
     bool blocked = __dsqrt_rn(__dadd_rn(__dmul_rn(dyp, dyp), z2)) < sc.planet_R;
     for (int k = 0; k < sc.n_moons; ++k) {
         const double dym = __dsub_rn(y, sc.moon_y[k * sc.n_orb + p]);
-        const double Rm = sc.moon_R[k];
+        const double Rm = sc.moon_R_per_phase ? sc.moon_R[k * sc.n_orb + p] : sc.moon_R[k];
         blocked |= __dadd_rn(__dmul_rn(dym, dym), z2) < __dmul_rn(Rm, Rm);
     }
     return blocked;
@@ -92,8 +92,9 @@ column_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, int* 
                 } else {
                     const double dy = y - S.centre_y[p];
                     const double cx = S.centre_x[p];
+                    const double* sp = pb_params(S, p);
                     for (int ix = lane; ix < sc.n_x; ix += 32) {
-                        const double n = pb_density(S, amp, sc.x[ix] - cx, dy, z);
+                        const double n = pb_density(S, sp, amp, sc.x[ix] - cx, dy, z);
                         if (dens) dens[ix] = n;
                         sum += n;
                     }
@@ -146,10 +147,11 @@ __device__ __forceinline__ double pb_column_sum(const DevScene& sc, const DevSce
     }
     const double cx = S.centre_x[p];
     const double dy = y - S.centre_y[p];
-    const double n0 = S.p[0] * amp;
+    const double* __restrict__ P = pb_params(S, p);
+    const double n0 = P[0] * amp;
     switch (S.type) {
         case PB200_SCN_BAROMETRIC: {   // n0 exp((R - r)/H) H(r - R), gasProperties.py:155-160
-            const double R = S.p[1], invH = 1.0 / S.p[2], c2 = fma(dy, dy, z * z);
+            const double R = P[1], invH = 1.0 / P[2], c2 = fma(dy, dy, z * z);
             return n0 * pb_sum4(n_x, [&](int ix) {
                 const double dx = xs[ix] - cx;
                 const double r = sqrt(fma(dx, dx, c2));
@@ -157,7 +159,7 @@ __device__ __forceinline__ double pb_column_sum(const DevScene& sc, const DevSce
             });
         }
         case PB200_SCN_HYDROSTATIC: {  // n0 exp(J(r) H(r - R) - J(R)), gasProperties.py:197-203
-            const double R = S.p[1], jc = S.p[2] / S.p[3], j0 = jc / R, c2 = fma(dy, dy, z * z);
+            const double R = P[1], jc = P[2] / P[3], j0 = jc / R, c2 = fma(dy, dy, z * z);
             return n0 * pb_sum4(n_x, [&](int ix) {
                 const double dx = xs[ix] - cx;
                 const double r = sqrt(fma(dx, dx, c2));
@@ -165,7 +167,7 @@ __device__ __forceinline__ double pb_column_sum(const DevScene& sc, const DevSce
             });
         }
         case PB200_SCN_POWERLAW: {     // n0 (R/r)^q H(r - R), gasProperties.py:240-243, :326-329, :371-373, :453-460
-            const double R = S.p[1], q = S.p[2], qlogR = q * log(R), hq = -0.5 * q, c2 = fma(dy, dy, z * z);
+            const double R = P[1], q = P[2], qlogR = q * log(R), hq = -0.5 * q, c2 = fma(dy, dy, z * z);
             return n0 * pb_sum4(n_x, [&](int ix) {
                 const double dx = xs[ix] - cx;
                 const double r2 = fma(dx, dx, c2);
@@ -173,7 +175,7 @@ __device__ __forceinline__ double pb_column_sum(const DevScene& sc, const DevSce
             });
         }
         case PB200_SCN_TORUS: {        // n0 exp(-((a - a_t)/4H)^2) exp(-(z/H)^2), gasProperties.py:506-515
-            const double at = S.p[1], inv4H = 1.0 / (4.0 * S.p[2]), qz = z / S.p[2], dy2 = dy * dy;
+            const double at = P[1], inv4H = 1.0 / (4.0 * P[2]), qz = z / P[2], dy2 = dy * dy;
             const double ez = exp(-(qz * qz));
             return (n0 * ez) * pb_sum4(n_x, [&](int ix) {
                 const double dx = xs[ix] - cx;
@@ -193,16 +195,17 @@ __device__ __forceinline__ double pb_column_bound(const DevScene& sc, const DevS
                                                   double z) {
     if (S.type == PB200_SCN_SERPENS) return __longlong_as_double(0x7ff0000000000000ll);
     const double dy = y - S.centre_y[p];
-    const double n0 = fabs(S.p[0] * amp) * sc.n_x;
+    const double* P = pb_params(S, p);
+    const double n0 = fabs(P[0] * amp) * sc.n_x;
     const double rmin = sqrt(fma(dy, dy, z * z));
     switch (S.type) {
-        case PB200_SCN_BAROMETRIC: return n0 * ((rmin < S.p[1]) ? 1.0 : exp((S.p[1] - rmin) / S.p[2]));
+        case PB200_SCN_BAROMETRIC: return n0 * ((rmin < P[1]) ? 1.0 : exp((P[1] - rmin) / P[2]));
         case PB200_SCN_HYDROSTATIC: {
-            const double jc = S.p[2] / S.p[3];
-            return n0 * ((rmin < S.p[1]) ? 1.0 : exp(jc / rmin - jc / S.p[1]));
+            const double jc = P[2] / P[3];
+            return n0 * ((rmin < P[1]) ? 1.0 : exp(jc / rmin - jc / P[1]));
         }
-        case PB200_SCN_POWERLAW: return n0 * ((rmin < S.p[1]) ? 1.0 : exp(S.p[2] * (log(S.p[1]) - log(rmin))));
-        case PB200_SCN_TORUS: { const double qz = z / S.p[2]; return n0 * exp(-(qz * qz)); }
+        case PB200_SCN_POWERLAW: return n0 * ((rmin < P[1]) ? 1.0 : exp(P[2] * (log(P[1]) - log(rmin))));
+        case PB200_SCN_TORUS: { const double qz = z / P[2]; return n0 * exp(-(qz * qz)); }
         default: return __longlong_as_double(0x7ff0000000000000ll);
     }
 }
@@ -475,7 +478,8 @@ number_density_grid_kernel(const DevScene* __restrict__ scp, int scenario, doubl
             if (oob) *oob_flag = 1;
         } else {
             const double dy = y - S.centre_y[p], cx = S.centre_x[p];
-            for (int ix = lane; ix < sc.n_x; ix += 32) row[ix] = pb_density(S, amp, sc.x[ix] - cx, dy, z);
+            const double* sp = pb_params(S, p);
+            for (int ix = lane; ix < sc.n_x; ix += 32) row[ix] = pb_density(S, sp, amp, sc.x[ix] - cx, dy, z);
         }
     }
 }
@@ -501,7 +505,7 @@ number_density_chords_kernel(const DevScene* __restrict__ scp, int scenario, int
             if (oob) *oob_flag = 1;
         } else {
             const double dy = y[c] - cy[c];
-            for (int ix = lane; ix < sc.n_x; ix += 32) row[ix] = pb_density(S, a, sc.x[ix] - cx[c], dy, z[c]);
+            for (int ix = lane; ix < sc.n_x; ix += 32) row[ix] = pb_density(S, S.p, a, sc.x[ix] - cx[c], dy, z[c]);
         }
     }
 }

@@ -17,6 +17,7 @@ struct DevScenario {
     int type, n_cons, first_cons, has_molecule;
     double T;
     double p[8];
+    const double* p_phase;   // NULL or [n_orb][8]: per-(virtual-)phase parameters of a retrieval batch (pb200_set_models)
     const double* centre_x;
     const double* centre_y;
     const double* shift;
@@ -41,6 +42,8 @@ struct DevScene {
     int M;            // chords per phase  = n_phi * n_rho
     int Mp;           // M padded to a multiple of kChordTile
     int fout_per_wav; // 1: fout is [n_wav] (per-chord F* table with stellar rotation), 0: fout is [1]
+    int moon_R_per_phase;   // 1: moon_R is [n_moons][n_orb] (retrieval batch), 0: [n_moons]
+    int n_orb_model;        // phases per model (== n_orb without a batch); row m*n_orb_model + p is model m, phase p
     int64_t n_wav;
     double delta_x, star_R, clv_u1, clv_u2, vsini, planet_R;
     const double* x; const double* rho; const double* sin_phi; const double* cos_phi;
@@ -123,28 +126,33 @@ __host__ __device__ inline int64_t pb_wav_index(const TransitParams& prm, int64_
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ double pb_heaviside1(double u) { return (u < 0.0) ? 0.0 : 1.0; }
 
-__device__ __forceinline__ double pb_density(const DevScenario& s, double amp, double dx, double dy,
-                                             double z) {
+// scalar parameters of a scenario at (virtual) phase p
+__device__ __forceinline__ const double* pb_params(const DevScenario& s, int p) {
+    return s.p_phase ? s.p_phase + (int64_t)p * 8 : s.p;
+}
+
+__device__ __forceinline__ double pb_density(const DevScenario& s, const double* __restrict__ sp, double amp, double dx,
+                                             double dy, double z) {
     switch (s.type) {
         case PB200_SCN_BAROMETRIC: {   // gasProperties.py:155-160
             const double r = sqrt(dx * dx + dy * dy + z * z);
-            return s.p[0] * amp * exp((s.p[1] - r) / s.p[2]) * pb_heaviside1(r - s.p[1]);
+            return sp[0] * amp * exp((sp[1] - r) / sp[2]) * pb_heaviside1(r - sp[1]);
         }
         case PB200_SCN_HYDROSTATIC: {  // gasProperties.py:197-203 (non-zero inside the planet)
             const double r = sqrt(dx * dx + dy * dy + z * z);
-            const double jeans0 = s.p[2] / (s.p[3] * s.p[1]);
-            const double jeans = s.p[2] / (s.p[3] * r) * pb_heaviside1(r - s.p[1]);
-            return s.p[0] * amp * exp(jeans - jeans0);
+            const double jeans0 = sp[2] / (sp[3] * sp[1]);
+            const double jeans = sp[2] / (sp[3] * r) * pb_heaviside1(r - sp[1]);
+            return sp[0] * amp * exp(jeans - jeans0);
         }
         case PB200_SCN_POWERLAW: {     // gasProperties.py:240-243, :326-329, :371-373, :453-460
             const double r = sqrt(dx * dx + dy * dy + z * z);
-            return s.p[0] * amp * pow(s.p[1] / r, s.p[2]) * pb_heaviside1(r - s.p[1]);
+            return sp[0] * amp * pow(sp[1] / r, sp[2]) * pb_heaviside1(r - sp[1]);
         }
         case PB200_SCN_TORUS: {        // gasProperties.py:506-515, celestialBodies.py:438-470
             const double a = sqrt(dx * dx + dy * dy);
-            const double qa = (a - s.p[1]) / (4.0 * s.p[2]);
-            const double qz = z / s.p[2];
-            return s.p[0] * amp * (exp(-(qa * qa)) * exp(-(qz * qz)));
+            const double qa = (a - sp[1]) / (4.0 * sp[2]);
+            const double qz = z / sp[2];
+            return sp[0] * amp * (exp(-(qa * qa)) * exp(-(qz * qz)));
         }
         default:
             return 0.0;

@@ -215,3 +215,50 @@ def flatten(transit, wavelength=None, wav_range=None) -> tuple[capi.Scene, list,
             "n_chords": rho.size * phi.size * n_orb, "n_atoms": n_atoms, "n_mols": n_mols,
             "h2d_bytes": int(h2d)}
     return sc, b.keep, info
+
+
+def flatten_model(transit, phase=None) -> tuple[capi.Model, list]:
+    """The part of a Transit-like object that a free parameter of a retrieval can move (pb200_model):
+    scenario scalars and per-phase arrays, evaluated with the objects' own methods exactly as `flatten`
+    does.  Tables, axes and the wavelength grid are NOT read -- they stay resident from the template's
+    pb200_set_scene (the caller guarantees they are the same; the library checks types and counts)."""
+    b = SceneBuilder()
+    atmos = transit.atmosphere
+    dists = list(atmos.densityDistributionList)
+    planet = getattr(transit, "planet", None) or dists[0].planet
+    if phase is None:
+        phase = np.asarray(transit.spatialGrid.constructOrbphaseAxis(), dtype=np.float64)
+    n_orb = phase.size
+    mdl = capi.Model()
+    mdl.planet_y = b.ptr(planet.a * np.sin(phase))                               # gasProperties.py:1224
+    moons_R, moons_y = [], []
+    for dist in dists:
+        if getattr(dist, "hasMoon", False):                                      # gasProperties.py:1226-1230
+            moons_R.append(float(dist.moon.R))
+            moons_y.append(np.broadcast_to(np.asarray(dist.moon.getPosition(phase)[1], dtype=np.float64), (n_orb,)))
+    if moons_R:
+        mdl.moon_R = b.ptr(np.array(moons_R))
+        mdl.moon_y = b.ptr(np.concatenate(moons_y))
+    scn_arr = (capi.Scenario * len(dists))()
+    first = 0
+    for i, dist in enumerate(dists):
+        q = scn_arr[i]
+        q.type, params = scenario_parameters(dist)
+        for j, v in enumerate(params):
+            q.p[j] = float(v)
+        q.T = float(getattr(dist, "T", 0.0) or 0.0)
+        has_moon = bool(getattr(dist, "hasMoon", False))
+        body = dist.moon if has_moon else dist.planet
+        if q.type != capi.SCN_SERPENS:
+            cx, cy = body.getPosition(phase)                                     # celestialBodies.py:370-383, :518-531
+            q.centre_x, q.centre_y = b.per_phase(cx, n_orb), b.per_phase(cy, n_orb)
+        v_los = body.getLOSvelocity(phase) if atmos.hasOrbitalDopplerShift else np.zeros(n_orb)   # gasProperties.py:908-916
+        q.shift = b.per_phase(const.calculateDopplerShift(-np.asarray(v_los, dtype=np.float64)), n_orb)
+        if _kind(dist) == "TidallyHeatedMoon":                                   # gasProperties.py:425-436
+            q.amplitude = b.per_phase(dist.calculateAbsorberNumber(phase), n_orb)
+        q.first_constituent = first
+        q.n_constituents = len(dist.constituents)
+        first += q.n_constituents
+    mdl.scenarios = C.cast(scn_arr, C.POINTER(capi.Scenario))
+    b.keep.append(scn_arr)
+    return mdl, b.keep

@@ -237,10 +237,50 @@ def _make():
         "wavelength": [5885e-8, 5900e-8, 2e-8, 5e-9, 2e-10],
         "grid": [ap, 5 * Rp, 30, Rs, 20, 24, 0.25, 5],
     }
+    # ---- retrieval forward model: the setup of mainRetrieval.py:18-67 ---------------
+    ret = _w49(u1=0.34, u2=0.28)                                   # mainRetrieval.py:37 CLV of Wyttenbach+2017
+    ret["moon"] = dict(moon)                                        # mainRetrieval.py:18-21, :42-43
+    W["RET"] = {
+        "name": "RET", "title": "retrieval forward model: tidally heated moon Na I, 25 phases (mainRetrieval.py)",
+        "bodies": ret, "doppler": True, "linelist": "nist",
+        "scenarios": [{"type": "tidallyHeated", "q": 3.34, "mdot": {"synthetic": 64},
+                       "tau_photoionization": 241.0,
+                       "species": [{"name": "NaI", "sigma_v": 1e6}]}],
+        "wavelength": [5888e-8, 5900e-8, 2e-8, 5e-9, 2e-10],       # mainRetrieval.py:28
+        "grid": [ap, 5 * Rp, 30, Rs, 40, 60, 0.25, 25],            # mainRetrieval.py:32-33
+        "band": {"line_centres": [5891.583253e-8, 5897.558147e-8], "bandwidth": 0.75e-8},   # mainRetrieval.py:75-81
+    }
+    rets = copy.deepcopy(W["RET"])
+    rets.update(name="RETs", title="RET reduced twin (CI parity case)")
+    rets["grid"] = [ap, 5 * Rp, 30, Rs, 20, 24, 0.25, 9]
+    W["RETs"] = rets
     return W
 
 
 WORKLOADS = _make()
+
+# free parameters of the retrieval sketch (mainRetrieval.py:18-21): moon phase at mid-transit [rad], moon orbit
+# [planetary radii], moon radius [Io radii]
+RETRIEVAL_PARAMS = ("midTransitOrbphase", "a_moon", "R_moon")
+
+
+def retrieval_variant(spec: dict, midTransitOrbphase: float, a_moon: float, R_moon: float) -> dict:
+    """The spec with the three free parameters of mainRetrieval.py:18-21 set."""
+    v = copy.deepcopy(spec)
+    v["bodies"]["moon"] = {"phi0": float(midTransitOrbphase), "R": float(R_moon) * const.R_Io,
+                           "a": float(a_moon) * v["bodies"]["planet"]["R"]}
+    return v
+
+
+def retrieval_samples(n: int, seed: int = 11) -> np.ndarray:
+    """(n, 3) parameter vectors around the values of mainRetrieval.py:18-21 (seeded; row 0 is the script's own)."""
+    rng = np.random.default_rng(seed)
+    out = np.empty((n, 3))
+    out[:, 0] = rng.uniform(0.0, 2.0 * math.pi, n)
+    out[:, 1] = rng.uniform(1.2, 2.5, n)
+    out[:, 2] = rng.uniform(0.05, 0.5, n)
+    out[0] = (0.65 * 2.0 * math.pi, 1.44, 0.1384)
+    return out
 
 # the CI-sized cases with committed golden fixtures (tests/golden/*.npz)
 GOLDEN_CASES = ["C1", "C2s", "C3s", "C4s", "C5s", "PLNs", "THMs", "SERs", "FSTs", "HYDs"]

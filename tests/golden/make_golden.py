@@ -134,14 +134,56 @@ def run_case(ns, name, out_dir=HERE):
           f"R in [{R.min():.6f}, {R.max():.6f}] -> {os.path.getsize(path) / 1e6:.2f} MB", flush=True)
 
 
+def reference_lightcurve_block():
+    """The 'Extract lightcurve' statements of the reference's mainRetrieval.py (from `filterBandwidth = ...` to
+    `lightcurve = np.array(lightcurve)`), as source text: the golden light curves are produced by executing the
+    reference's own lines, not a restatement."""
+    lines = open("/root/reference/mainRetrieval.py").read().split("\n")
+    i0 = next(i for i, l in enumerate(lines) if l.startswith("filterBandwidth ="))
+    i1 = next(i for i, l in enumerate(lines) if l.startswith("lightcurve = np.array(lightcurve)"))
+    return "\n".join(lines[i0:i1 + 1])
+
+
+def run_retrieval_case(ns, name="RETs", n_models=4, out_dir=HERE):
+    """Retrieval forward models: the setup of mainRetrieval.py for n_models parameter vectors
+    (mainRetrieval.py:18-21), R from the reference's sumOverChords, light curves from the reference script's own
+    statements (their band centres are the script's Na D literals)."""
+    from prometheus_b200 import builder, workloads
+    spec = workloads.get(name)
+    params = workloads.retrieval_samples(n_models)
+    block = reference_lightcurve_block()
+    Rs, lcs = [], []
+    t0 = time.time()
+    for pv in params:
+        tr = builder.build_transit(workloads.retrieval_variant(spec, *pv), ns=ns, nist_rows=ns.nist_rows)
+        R = tr.sumOverChords(2.0)
+        env = {"np": np, "const": ns.consts, "W49b": tr.planet, "R": R, "wavelength": tr.wavelength,
+               "orbphase": tr.spatialGrid.constructOrbphaseAxis()}
+        exec(block, env)
+        Rs.append(R)
+        lcs.append(env["lightcurve"])
+        shift = env["shift"]
+    out = {"params": params, "R": np.stack(Rs), "lightcurve": np.stack(lcs), "wavelength": tr.wavelength,
+           "orb": tr.spatialGrid.constructOrbphaseAxis(), "band_shift": np.asarray(shift),
+           "line_centres": np.array([env["NaD2_center"], env["NaD1_center"]]),
+           "bandwidth": np.float64(env["filterBandwidth"])}
+    path = os.path.join(out_dir, f"{name}.npz")
+    np.savez_compressed(path, **out)
+    print(f"{name}: {n_models} models, R {out['R'].shape}, lightcurve in [{out['lightcurve'].min():.6f}, "
+          f"{out['lightcurve'].max():.6f}], {time.time() - t0:.1f}s -> {os.path.getsize(path) / 1e6:.2f} MB", flush=True)
+
+
 def main(argv):
     from prometheus_b200 import workloads
     ns = ReferenceNamespace()
     ll = os.path.join(HERE, "linelist.npz")
     np.savez_compressed(ll, rows=ns.nist_rows)
     print("line list rows:", ns.nist_rows.shape)
-    for name in (argv or workloads.GOLDEN_CASES):
-        run_case(ns, name)
+    for name in (argv or workloads.GOLDEN_CASES + ["RETs"]):
+        if name == "RETs":
+            run_retrieval_case(ns, name)
+        else:
+            run_case(ns, name)
 
 
 if __name__ == "__main__":

@@ -53,6 +53,7 @@ def test_struct_layout_matches_header(tmp_path):
         'printf("%zu %zu %zu %zu\\n", sizeof(pb200_scenario), sizeof(pb200_constituent), sizeof(pb200_scene), sizeof(pb200_timing));\n'
         'printf("%zu %zu %zu\\n", offsetof(pb200_scenario, centre_x), offsetof(pb200_scenario, dims), offsetof(pb200_constituent, fill));\n'
         'printf("%zu %zu %zu\\n", offsetof(pb200_scene, wavelength), offsetof(pb200_scene, planet_y), offsetof(pb200_scene, constituents));\n'
+        'printf("%zu %zu %zu %zu\\n", sizeof(pb200_model), sizeof(pb200_band), offsetof(pb200_model, moon_y), offsetof(pb200_band, bandwidth));\n'
         "return 0;}\n")
     exe = tmp_path / "layout"
     subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
@@ -60,6 +61,7 @@ def test_struct_layout_matches_header(tmp_path):
     assert rows[0] == [C.sizeof(capi.Scenario), C.sizeof(capi.Constituent), C.sizeof(capi.Scene), C.sizeof(capi.Timing)]
     assert rows[1] == [capi.Scenario.centre_x.offset, capi.Scenario.dims.offset, capi.Constituent.fill.offset]
     assert rows[2] == [capi.Scene.wavelength.offset, capi.Scene.planet_y.offset, capi.Scene.constituents.offset]
+    assert rows[3] == [C.sizeof(capi.Model), C.sizeof(capi.Band), capi.Model.moon_y.offset, capi.Band.bandwidth.offset]
 
 
 def test_no_gpu_means_loud_failure():

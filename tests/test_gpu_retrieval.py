@@ -1,0 +1,124 @@
+"""GPU parity of the retrieval batch: pb200_set_models / pb200_run_batch / pb200_lightcurve
+through the C ABI against the reference's outputs (tests/golden/RETs.npz: R from the reference's sumOverChords,
+light curves from the reference script's own statements, mainRetrieval.py:69-93) and the CPU oracle.
+
+Tolerances: the band selection is index work -> the light-curve kernel on a given R agrees with the oracle on the
+same R to 1e-15 (sum order only); end to end the excess-depth criterion on R and 2e-10 absolute on the light curve
+(the kernel-(b2) sigma tables differ from scipy's at 1e-9 relative)."""
+import numpy as np
+import pytest
+
+from helpers import excess_depth_ok, oracle, oracle_inputs
+from prometheus_b200 import builder, capi, host, retrieval, workloads
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def setup(nist_rows):
+    spec = workloads.get("RETs")
+    template = builder.build_transit(spec, nist_rows=nist_rows)
+    orb = template.spatialGrid.constructOrbphaseAxis()
+    band = retrieval.LightcurveBand.for_planet(template.planet, orb, spec["band"]["line_centres"], spec["band"]["bandwidth"])
+    return spec, template, band
+
+
+def test_batch_matches_reference(setup, golden):
+    spec, template, band = setup
+    g = golden("RETs")
+    assert np.array_equal(band.shift, g["band_shift"])
+    variants = retrieval.make_variants(template, g["params"])
+    batch = retrieval.RetrievalBatch(template)
+    lc, R, timing = batch.run(variants, band, want_R=True)
+    n_models, n_orb, n_wav = g["R"].shape
+    assert lc.shape == (n_models, n_orb) and R.shape == (n_models, n_orb, n_wav)
+    for k in range(n_models):
+        ok, worst = excess_depth_ok(R[k], g["R"][k], np.ones_like(R[k]))
+        assert ok, f"model {k}: err/bound {worst}"
+        assert np.max(np.abs(lc[k] - g["lightcurve"][k])) < 2e-10
+        # the epilogue kernel on its own input
+        lc_o = oracle.lightcurve(R[k], g["wavelength"], band.shift, band.line_centres, band.bandwidth)
+        assert np.max(np.abs(lc[k] - lc_o)) < 1e-15
+    # one set of launches for the whole batch: sky cells, F_out, sigma, column, compaction, transit, light curve
+    assert timing["launches"] <= 8
+    batch.reset()
+
+
+def test_batch_rows_equal_single_runs(setup, nist_rows):
+    """Stacking models along the phase axis must not change a bit of any of them."""
+    spec, template, band = setup
+    params = workloads.retrieval_samples(6)
+    variants = retrieval.make_variants(template, params)
+    batch = retrieval.RetrievalBatch(template)
+    lc, R, _ = batch.run(variants, band, want_R=True)
+    batch.reset()
+    for k in (0, 3, 5):
+        single = variants[k].sumOverChords()
+        assert np.array_equal(single, R[k])
+        lc1 = retrieval.extract_lightcurve(host.get_context(), band)
+        assert np.array_equal(lc1, lc[k])
+
+
+def test_batch_against_oracle_variants(setup, nist_rows):
+    spec, template, band = setup
+    params = workloads.retrieval_samples(3, seed=5)
+    variants = retrieval.make_variants(template, params)
+    batch = retrieval.RetrievalBatch(template)
+    lc, R, _ = batch.run(variants, band, want_R=True)
+    batch.reset()
+    for k, pv in enumerate(params):
+        v = workloads.retrieval_variant(spec, *pv)
+        m = oracle.build_model(v, oracle_inputs(v, nist_rows))
+        R_ref = oracle.sum_over_chords(m)
+        R0 = oracle.sum_over_chords(m, opaque_only=True)
+        ok, worst = excess_depth_ok(R[k], R_ref, R0)
+        assert ok, f"model {k}: {worst}"
+        lc_ref = oracle.lightcurve(R_ref, m.wavelength, oracle.band_shift(m), spec["band"]["line_centres"], spec["band"]["bandwidth"])
+        assert np.max(np.abs(lc[k] - lc_ref)) < 2e-10
+
+
+def test_inner_seams_address_stacked_rows(setup):
+    """After pb200_set_models the context has n_models*n_orb phases; pb200_column_density shows them."""
+    spec, template, band = setup
+    params = workloads.retrieval_samples(2, seed=3)
+    variants = retrieval.make_variants(template, params)
+    batch = retrieval.RetrievalBatch(template)
+    ctx = batch.ctx
+    n_orb, M = batch.info["n_orb"], batch.info["n_rho"] * batch.info["n_phi"]
+    batch.set_models(variants)
+    stacked = np.empty((1, M * 2 * n_orb))
+    ctx.check(ctx.lib.pb200_column_density(ctx.handle, capi.dptr(stacked)))
+    stacked = stacked.reshape(M, 2, n_orb)
+    batch.reset()
+    for k in range(2):
+        single = variants[k].getColumnDensityGrid().reshape(M, n_orb)
+        assert np.array_equal(single, stacked[:, k, :])
+
+
+def test_error_conventions(setup):
+    spec, template, band = setup
+    batch = retrieval.RetrievalBatch(template)
+    ctx = batch.ctx
+    variants = retrieval.make_variants(template, workloads.retrieval_samples(1))
+    # no resident R after a fresh scene
+    with pytest.raises(capi.Pb200Error) as ei:
+        ctx.lightcurve(band.struct(), 0, batch.info["n_orb"])
+    assert ei.value.code == -1
+    # a model whose scenario type differs from the resident scene
+    arr, keep = batch._models(variants)
+    arr[0].scenarios[0].type = capi.SCN_TORUS
+    with pytest.raises(capi.Pb200Error) as ei:
+        ctx.set_models(arr, 1, keep)
+    assert ei.value.code == -1
+    # band without lines
+    bad = band.struct()
+    bad.n_lines = 0
+    arr, keep = batch._models(variants)
+    with pytest.raises(capi.Pb200Error) as ei:
+        ctx.run_batch(arr, 1, bad, batch.info["n_orb"], batch.info["n_wav"], False, keep)
+    assert ei.value.code == -1
+    # a band that selects nothing: nan, as np.mean of an empty selection
+    empty = retrieval.LightcurveBand([1.0], 1e-9, band.shift)
+    lc, _, _ = batch.run(variants, empty)
+    assert np.all(np.isnan(lc))
+    batch.reset()
