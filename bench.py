@@ -321,8 +321,8 @@ def retrieval_workload(n_models=64, steps=5, warmup=3, cpu_models=2):
     wall, timings = [], []
     for i in range(warmup + steps):
         t0 = time.perf_counter()
-        variants = retrieval.make_variants(template, params)
-        lc, _, t = batch.run(variants, band)
+        family, K = retrieval.make_family(template, params)
+        lc, _, t = batch.run_family(family, K, band)
         if i >= warmup:
             wall.append(time.perf_counter() - t0)
             timings.append(t)

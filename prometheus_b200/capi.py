@@ -80,6 +80,22 @@ class Band(C.Structure):
                 ("shift", c_double_p), ("bandwidth", C.c_double)]
 
 
+def struct_dtype(struct) -> np.dtype:
+    """numpy structured dtype with the exact layout of a ctypes Structure (pointers as uint64): arrays of
+    pb200_model / pb200_scenario for a whole retrieval batch are then filled with vectorised assignments
+    instead of one ctypes attribute store per field and model."""
+    names, formats, offsets = [], [], []
+    for name, ct in struct._fields_:
+        if isinstance(ct, type) and issubclass(ct, C.Array):
+            fmt = (np.dtype(ct._type_), ct._length_)
+        elif isinstance(ct, type) and issubclass(ct, C._Pointer):
+            fmt = np.dtype(np.uint64)
+        else:
+            fmt = np.dtype(ct)
+        names.append(name); formats.append(fmt); offsets.append(getattr(struct, name).offset)
+    return np.dtype({"names": names, "formats": formats, "offsets": offsets, "itemsize": C.sizeof(struct)})
+
+
 class Timing(C.Structure):
     _fields_ = [("upload_ms", C.c_double), ("column_ms", C.c_double), ("transit_ms", C.c_double),
                 ("finalize_ms", C.c_double), ("download_ms", C.c_double),

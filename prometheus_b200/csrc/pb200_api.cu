@@ -492,7 +492,8 @@ extern "C" int pb200_set_scene(pb200_ctx* c, const pb200_scene* s) {
     {   // mirror pairing of chords (compact_kernel): all bodies lie in z = 0 and every analytic density depends
         // on z^2 only; the tabulated (SERPENS) density does not.  The phi axis must be mirror symmetric about
         // pi/2 and 3 pi/2 on the grid itself: sin(phi_i') = sin(phi_i), cos(phi_i') = -cos(phi_i), i' = n/2-1-i.
-        bool ok = !c->general_path && (s->n_phi % 2 == 0);
+        // kernel (m) pairs too, unless F* is seen through stellar rotation (star_shift differs within a pair)
+        bool ok = !(h.n_fstar > 0 && h.vsini != 0.0) && (s->n_phi % 2 == 0);
         for (int i = 0; ok && i < s->n_scenarios; ++i) ok = s->scenarios[i].type != PB200_SCN_SERPENS;
         const int n2 = s->n_phi / 2;
         for (int hh = 0; ok && hh < 2; ++hh)
@@ -554,7 +555,9 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     prm.cyc_block = cyc_block; prm.cyc_n = cyc_n; prm.cyc_rank = cyc_rank;
     if (cyc_block && c->general_path)
         return fail(c, PB200_ERR_UNSUPPORTED, "block-cyclic wavelength tiles are implemented for atomic scenes (kernel (c')) only");
-    const int n_tiles = h.Mp / kChordTile;
+    // kernel (m) walks mirror pairs when the scene allows it: about half the chords
+    const int n_pairs = 2 * ((h.n_phi / 2 + 1) / 2) * h.n_rho;
+    const int n_tiles = (c->general_path && h.mirror) ? (n_pairs + kChordTile - 1) / kChordTile : h.Mp / kChordTile;
     // wavelengths per CTA: kernel (m) 128; kernel (c') one window of 32 * WPT (WPT = 8, 4, 2 for <= 2, <= 4, more absorbers)
     const int cta_wav = c->general_path ? 128 : 32 * (h.n_atoms <= 2 ? 8 : h.n_atoms <= 4 ? 4 : 2);
     const int64_t ctas = ((n_wav_sel + cta_wav - 1) / cta_wav) * n_phase;

@@ -141,21 +141,39 @@ transit_general_kernel(const DevScene* __restrict__ scp, const TransitParams prm
     }
     __syncthreads();
 
+    // Mirror pairing (sc.mirror, see compact_kernel): the chords (phi, rho) and (pi - phi, rho) have equal densities
+    // along x, so one item with weight w_in(i) + w_in(i') stands for both; the walk is over the pair index q.
+    const int n2 = sc.n_phi / 2, Pm = (n2 + 1) / 2;
+    const int n_items = sc.mirror ? 2 * Pm * sc.n_rho : sc.M;
     const int m_lo = blockIdx.z * prm.tiles_per_split * kChordTile;
     int m_hi = m_lo + prm.tiles_per_split * kChordTile;
-    if (m_hi > sc.M) m_hi = sc.M;
+    if (m_hi > n_items) m_hi = n_items;
     const int64_t atom_stride = (int64_t)sc.n_orb * sc.Mp;
 
     if (producer) {
         // ======================= producer warp ==================================================
         int it = 0;
-        for (int m = m_lo; m <= m_hi; ++m) {
-            const bool end = (m == m_hi);
+        for (int q = m_lo; q <= m_hi; ++q) {
+            const bool end = (q >= m_hi);
             int64_t row = 0;
             double wv = 0.0;
+            int m = q;
             if (!end) {
+                if (sc.mirror) {
+                    const int h = q / (Pm * sc.n_rho), rem = q - h * (Pm * sc.n_rho);
+                    const int i = rem / sc.n_rho, irho = rem - i * sc.n_rho, ip = n2 - 1 - i;
+                    m = (h * n2 + i) * sc.n_rho + irho;
+                    wv = sc.w_in[(int64_t)p * sc.Mp + m];
+                    if (ip != i) {
+                        const int mb = (h * n2 + ip) * sc.n_rho + irho;
+                        const double wb = sc.w_in[(int64_t)p * sc.Mp + mb];
+                        if (wv == 0.0) m = mb;   // the density row of a blocked chord is zero: take the mirror's
+                        wv += wb;
+                    }
+                } else {
+                    wv = sc.w_in[(int64_t)p * sc.Mp + m];
+                }
                 row = (int64_t)p * sc.Mp + m;
-                wv = sc.w_in[row];
                 if (wv == 0.0) continue;   // blocked: F_in = 0 (gasProperties.py:1233)
             }
             const int b = it & 1;

@@ -71,6 +71,16 @@ class RetrievalBatch:
     def reset(self):
         self.ctx.set_models(None, 0)
 
+    def run_family(self, family, n_models: int, band: LightcurveBand | None = None, want_R: bool = False):
+        """As run(), for a broadcast family (make_family): one vectorised flattening for the whole batch."""
+        models, keep = _scene.flatten_models_broadcast(family, self._phase, n_models)
+        keep.append(models)
+        lc, R, timing = self.ctx.run_batch(models.ctypes.data_as(C.POINTER(capi.Model)), n_models,
+                                           band.struct() if band is not None else None,
+                                           self.info["n_orb"], self.info["n_wav"], want_R, keep)
+        self.last_timing = timing
+        return lc, R, timing
+
     def run(self, transits, band: LightcurveBand | None = None, want_R: bool = False):
         """-> (lightcurves (n_models, n_orb) or None, R (n_models, n_orb, n_wav) or None, timing dict)."""
         if band is None and not want_R:
@@ -114,6 +124,25 @@ def make_variants(template, params):
         tr.atmosphere.densityDistributionList = new_dists
         out.append(tr)
     return out
+
+
+def make_family(template, params):
+    """ONE Transit-like object standing for all parameter vectors: its moon carries (n_models, 1) arrays, so the
+    objects' own expressions broadcast over models and phases (scene.flatten_models_broadcast)."""
+    import copy
+    P = np.asarray(params, dtype=np.float64).reshape(-1, 3)
+    dists = list(template.atmosphere.densityDistributionList)
+    planet = getattr(template, "planet", None) or dists[0].planet
+    new_dists = []
+    for d in dists:
+        d2 = copy.copy(d)
+        if getattr(d, "hasMoon", False):
+            d2.moon = type(d.moon)(P[:, 0:1], P[:, 2:3] * const.R_Io, P[:, 1:2] * planet.R, planet)
+        new_dists.append(d2)
+    tr = copy.copy(template)
+    tr.atmosphere = copy.copy(template.atmosphere)
+    tr.atmosphere.densityDistributionList = new_dists
+    return tr, P.shape[0]
 
 
 def model_partition(n_models: int, world: int) -> list[tuple[int, int]]:

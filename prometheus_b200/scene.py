@@ -262,3 +262,64 @@ def flatten_model(transit, phase=None) -> tuple[capi.Model, list]:
     mdl.scenarios = C.cast(scn_arr, C.POINTER(capi.Scenario))
     b.keep.append(scn_arr)
     return mdl, b.keep
+
+
+def flatten_models_broadcast(transit, phase, n_models: int):
+    """pb200_model structs of a whole family at once.  `transit` is ONE Transit-like object whose free
+    attributes (moon.midTransitOrbphase, moon.a, moon.R, dist.N, dist.q ...) are arrays of shape
+    (n_models, 1): the objects' own numpy expressions then broadcast against phase[None, :] to
+    (n_models, n_orb) -- the same expressions as one flatten_model call per model at a tenth of the Python
+    cost.  numpy's SIMD sin/cos are not position independent, so single values can differ from the per-model
+    call in the last bit (as they do inside the reference between batch sizes); integers, types and scalars
+    are identical (tests/test_retrieval_cpu.py::test_broadcast_family_matches_per_model).
+    -> (models as a numpy struct array with the layout of pb200_model, keep-alive list)."""
+    K = int(n_models)
+    atmos = transit.atmosphere
+    dists = list(atmos.densityDistributionList)
+    planet = getattr(transit, "planet", None) or dists[0].planet
+    phase = np.asarray(phase, dtype=np.float64)
+    n_orb = phase.size
+    ph = phase[None, :]
+    keep = []
+
+    def rows(v):
+        a = np.ascontiguousarray(np.broadcast_to(np.asarray(v, dtype=np.float64), (K, n_orb)))
+        keep.append(a)
+        return a.ctypes.data + np.arange(K, dtype=np.uint64) * np.uint64(n_orb * 8)
+
+    models = np.zeros(K, dtype=capi.struct_dtype(capi.Model))
+    scn = np.zeros((K, len(dists)), dtype=capi.struct_dtype(capi.Scenario))
+    keep.append(scn)
+    models["scenarios"] = scn.ctypes.data + np.arange(K, dtype=np.uint64) * np.uint64(scn.strides[0])
+    models["planet_y"] = rows(planet.a * np.sin(ph))                             # gasProperties.py:1224
+    moons_R, moons_y = [], []
+    for dist in dists:
+        if getattr(dist, "hasMoon", False):                                      # gasProperties.py:1226-1230
+            moons_R.append(np.broadcast_to(np.asarray(dist.moon.R, dtype=np.float64), (K, 1)))
+            moons_y.append(np.broadcast_to(np.asarray(dist.moon.getPosition(ph)[1], dtype=np.float64), (K, n_orb)))
+    if moons_R:
+        mR = np.ascontiguousarray(np.concatenate(moons_R, axis=1))               # [K][n_moons]
+        mY = np.ascontiguousarray(np.stack(moons_y, axis=1))                     # [K][n_moons][n_orb]
+        keep += [mR, mY]
+        models["moon_R"] = mR.ctypes.data + np.arange(K, dtype=np.uint64) * np.uint64(mR.strides[0])
+        models["moon_y"] = mY.ctypes.data + np.arange(K, dtype=np.uint64) * np.uint64(mY.strides[0])
+    first = 0
+    for i, dist in enumerate(dists):
+        q = scn[:, i]
+        typ, params = scenario_parameters(dist)
+        q["type"] = typ
+        for j, v in enumerate(params):
+            q["p"][:, j] = np.broadcast_to(np.asarray(v, dtype=np.float64).reshape(-1), (K,))
+        q["T"] = float(getattr(dist, "T", 0.0) or 0.0)
+        body = dist.moon if getattr(dist, "hasMoon", False) else dist.planet
+        if typ != capi.SCN_SERPENS:
+            cx, cy = body.getPosition(ph)                                        # celestialBodies.py:370-383, :518-531
+            q["centre_x"], q["centre_y"] = rows(cx), rows(cy)
+        v_los = body.getLOSvelocity(ph) if atmos.hasOrbitalDopplerShift else np.zeros((1, n_orb))   # gasProperties.py:908-916
+        q["shift"] = rows(const.calculateDopplerShift(-np.asarray(v_los, dtype=np.float64)))
+        if _kind(dist) == "TidallyHeatedMoon":                                   # gasProperties.py:425-436
+            q["amplitude"] = rows(dist.calculateAbsorberNumber(ph))
+        q["first_constituent"] = first
+        q["n_constituents"] = len(dist.constituents)
+        first += len(dist.constituents)
+    return models, keep

@@ -59,6 +59,20 @@ def test_batch_rows_equal_single_runs(setup, nist_rows):
         assert np.array_equal(lc1, lc[k])
 
 
+def test_family_path_agrees_with_object_path(setup):
+    """run_family (one vectorised flattening) against run (one flattening per Transit object): the per-phase arrays
+    agree to the last bit or two (numpy's sin/cos), the light curves to 1e-13."""
+    spec, template, band = setup
+    params = workloads.retrieval_samples(16, seed=2)
+    batch = retrieval.RetrievalBatch(template)
+    lc_obj, R_obj, _ = batch.run(retrieval.make_variants(template, params), band, want_R=True)
+    fam, K = retrieval.make_family(template, params)
+    lc_fam, R_fam, t = batch.run_family(fam, K, band, want_R=True)
+    batch.reset()
+    assert K == 16 and lc_fam.shape == lc_obj.shape
+    assert np.max(np.abs(R_fam - R_obj)) < 1e-13 and np.max(np.abs(lc_fam - lc_obj)) < 1e-13
+
+
 def test_batch_against_oracle_variants(setup, nist_rows):
     spec, template, band = setup
     params = workloads.retrieval_samples(3, seed=5)

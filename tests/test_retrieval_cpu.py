@@ -60,6 +60,32 @@ def test_flatten_model_agrees_with_flatten(nist_rows):
     assert tr.atmosphere.densityDistributionList[0].moon.R == spec["bodies"]["moon"]["R"]
 
 
+def test_broadcast_family_matches_per_model(nist_rows):
+    import ctypes as C
+    from prometheus_b200 import capi
+    spec = workloads.get("RETs")
+    tr = builder.build_transit(spec, nist_rows=nist_rows, build_tables=False)
+    params = workloads.retrieval_samples(7)
+    phase = np.asarray(tr.spatialGrid.constructOrbphaseAxis())
+    n_orb = phase.size
+    fam, K = retrieval.make_family(tr, params)
+    models, keep = scene.flatten_models_broadcast(fam, phase, K)
+    assert models.dtype.itemsize == C.sizeof(capi.Model) and K == 7
+    arr = models.ctypes.data_as(C.POINTER(capi.Model))
+    view = lambda p: np.ctypeslib.as_array(p, (n_orb,))   # noqa: E731
+    for k, var in enumerate(retrieval.make_variants(tr, params)):
+        m, _ = scene.flatten_model(var, phase)
+        b = arr[k]
+        assert m.moon_R[0] == b.moon_R[0]
+        np.testing.assert_allclose(view(b.planet_y), view(m.planet_y), rtol=0, atol=0)
+        np.testing.assert_allclose(view(b.moon_y), view(m.moon_y), rtol=3e-16)
+        sa, sb = m.scenarios[0], b.scenarios[0]
+        assert (sa.type, sa.n_constituents, sa.first_constituent) == (sb.type, sb.n_constituents, sb.first_constituent)
+        assert list(sa.p) == list(sb.p)
+        for name in ("centre_x", "centre_y", "shift", "amplitude"):
+            np.testing.assert_allclose(view(getattr(sb, name)), view(getattr(sa, name)), rtol=3e-16)
+
+
 def test_model_partition():
     for n in (0, 1, 5, 64, 1000):
         for world in (1, 2, 3, 8):
