@@ -242,7 +242,7 @@ def workload_config(name, spec, n_c, n_wav, n_gpus):
     g = spec["grid"]
     return {"workload": f"{name}: {spec['title']}", "n_chords": n_c, "n_wav": int(n_wav), "n_x": int(g[2]),
             "n_orb": int(g[7]), "n_phi": int(g[5]), "n_rho": int(g[4]),
-            "sharding": f"wavelengths over {n_gpus} rank(s) (blocks of 256 dealt round-robin), replicated scene; `value`: the R tiles stay on the GPU that computed them (independent units, no data-path collective); `e2e`: one all-gather + D2H on rank 0",
+            "sharding": f"wavelengths over {n_gpus} rank(s) (blocks of 256 dealt round-robin), replicated scene; `value`: the R tiles stay on the GPU that computed them (independent units, no data-path collective); `e2e`: every rank's kernels store their tiles into one page-locked shared-memory result (pb200_run_scatter), no gather",
             "weak_scaling_rule": "wavelength resolution refined N-fold at N GPUs",
             "cache": "L2 flushed between timed steps (512 MiB write)"}
 
@@ -469,7 +469,10 @@ def run_b200(args):
             if world == 1:
                 R_e2e = tr.sumOverChords()                 # the user-facing call: numpy in, numpy out
             else:
-                R_e2e = pbd.sum_over_chords(tr, None, axis, local, 0, state)
+                if axis == "cyclic" and os.environ.get("PB200_E2E_GATHER") != "1":
+                    R_e2e = pbd.sum_over_chords_shared(tr, None, local, state)    # tiles stored straight into shared pinned memory
+                else:
+                    R_e2e = pbd.sum_over_chords(tr, None, axis, local, 0, state)   # all-gather + D2H on rank 0
             b.record()
             barrier()
             if i >= args.warmup:

@@ -173,6 +173,11 @@ int64_t pb200_launch_count(pb200_ctx* ctx);            /* kernels launched since
    (the reference allocates F_in_sum/F_out_sum afresh per call, gasProperties.py:1202-1203).      */
 int pb200_host_alloc(size_t bytes, void** out);
 int pb200_host_free(void* p);
+/* page-lock and map memory the caller owns (e.g. a POSIX shared-memory segment that several ranks attach to);
+   *dev_ptr receives the address the device uses for it.  Such memory, like that of pb200_host_alloc, can be the
+   target of pb200_run (written without a staging copy) and of pb200_run_scatter.                         */
+int pb200_host_register(void* p, size_t bytes, void** dev_ptr);
+int pb200_host_unregister(void* p);
 
 /* ---- scene ------------------------------------------------------------------------------ */
 /* Uploads everything Transit.sumOverChords reads through `self`.             */
@@ -195,6 +200,13 @@ int pb200_run_device(pb200_ctx* ctx, int phase_lo, int phase_hi, int64_t wav_lo,
 int pb200_run_device_cyclic(pb200_ctx* ctx, int phase_lo, int phase_hi, int64_t wav_block, int n_ranks,
                             int rank, double* R_dev, pb200_timing* timing);
 int64_t pb200_cyclic_count(int64_t n_wav, int64_t wav_block, int n_ranks, int rank);
+/* The same block-cyclic tile written IN PLACE into the full result: R_full is row phase_lo of an array with
+ * row_stride (>= n_wav) doubles per phase that the device can address -- mapped page-locked host memory
+ * (pb200_host_alloc / pb200_host_register; the device-to-host transfer is then the kernel's own stores, each
+ * rank over its own PCIe link, no gather) or a peer GPU's buffer (stores over NVLink).  n_ranks == 1: the whole
+ * wavelength axis (any scene); n_ranks > 1: atomic scenes.  Not synchronised unless timing != NULL.        */
+int pb200_run_scatter(pb200_ctx* ctx, int phase_lo, int phase_hi, int64_t wav_block, int n_ranks, int rank,
+                      double* R_full, int64_t row_stride, pb200_timing* timing);
 /* ---- retrieval batches -------------------------------------------------------------------
  * pb200_set_models: stacks n_models models on the resident scene (pb200_set_scene must have been called;
  * its own per-phase arrays are model-independent inputs such as the grid and are replaced).  Afterwards
@@ -209,6 +221,9 @@ int pb200_lightcurve(pb200_ctx* ctx, const pb200_band* band, int phase_lo, int p
                      const double* R_dev, double* lightcurve_host);
 int pb200_run_batch(pb200_ctx* ctx, int n_models, const pb200_model* models, const pb200_band* band,
                     double* lightcurve_host, double* R_host, pb200_timing* timing);
+/* waits for everything enqueued on the context's stream (pb200_run_device*, pb200_run_scatter do not) and returns
+   PB200_ERR_BOUNDS if a tabulated density was queried outside its grid since the last check            */
+int pb200_sync(pb200_ctx* ctx);
 /* timing record of the last pb200_run / pb200_voigt_sigma call of this context */
 int pb200_last_timing(pb200_ctx* ctx, pb200_timing* timing);
 

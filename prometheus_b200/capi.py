@@ -24,6 +24,7 @@ EXPORTS = [
     "pb200_chord_masks", "pb200_optical_depth", "pb200_sigma_lookup", "pb200_voigt_sigma",
     "pb200_voigt_profile", "pb200_molecular_sigma", "pb200_write_output", "pb200_probe_fp64",
     "pb200_set_models", "pb200_lightcurve", "pb200_run_batch",
+    "pb200_host_register", "pb200_host_unregister", "pb200_run_scatter", "pb200_sync",
 ]
 
 SCN_BAROMETRIC, SCN_HYDROSTATIC, SCN_POWERLAW, SCN_TORUS, SCN_SERPENS = range(5)
@@ -160,6 +161,10 @@ def load():
                                             i64, i64, i64, c_double_p]),
         "pb200_write_output": (C.c_int, [C.c_char_p, C.c_char_p, c_double_p, c_double_p, c_double_p, i32, i64, i32]),
         "pb200_probe_fp64": (C.c_int, [vp, c_double_p, c_double_p]),
+        "pb200_sync": (C.c_int, [vp]),
+        "pb200_host_register": (C.c_int, [vp, C.c_size_t, C.POINTER(vp)]),
+        "pb200_host_unregister": (C.c_int, [vp]),
+        "pb200_run_scatter": (C.c_int, [vp, i32, i32, i64, i32, i32, vp, i64, C.POINTER(Timing)]),
         "pb200_set_models": (C.c_int, [vp, i32, C.POINTER(Model)]),
         "pb200_lightcurve": (C.c_int, [vp, C.POINTER(Band), i32, i32, vp, c_double_p]),
         "pb200_run_batch": (C.c_int, [vp, i32, C.POINTER(Model), C.POINTER(Band), c_double_p, c_double_p,
@@ -323,6 +328,18 @@ class Context:
                                             dptr(lc) if lc is not None else None, dptr(R) if R is not None else None,
                                             C.byref(t)))
         return lc, R, t.as_dict()
+
+    def run_scatter(self, phase_lo, phase_hi, wav_block, n_ranks, rank, full_ptr: int, row_stride: int, want_timing=False):
+        """This rank's block-cyclic tile written in place into the full result at `full_ptr` (mapped host memory
+        or device memory), see pb200_run_scatter."""
+        t = Timing()
+        self.check(self.lib.pb200_run_scatter(self.handle, phase_lo, phase_hi, wav_block, n_ranks, rank,
+                                              C.c_void_p(full_ptr), row_stride, C.byref(t) if want_timing else None))
+        return t.as_dict() if want_timing else None
+
+    def synchronize(self):
+        """Wait for everything enqueued on this context (a pb200_last_timing round trip is not needed for that)."""
+        self.check(self.lib.pb200_sync(self.handle))
 
     def last_timing(self) -> dict:
         t = Timing()

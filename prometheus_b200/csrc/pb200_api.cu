@@ -90,8 +90,9 @@ struct pb200_ctx {
     bool mstage_busy = false;    // a copy out of mstage may still be in flight
     double* d_band = nullptr;    // device: band shift [n_orb_model] then light curve [rows]
     size_t band_bytes = 0;
-    int lastR_phase_lo = 0, lastR_n_phase = 0;   // rows of R left in `scratch` by the last pb200_run / pb200_run_batch
-    bool lastR_full = false;                     // ... over the whole wavelength grid
+    int lastR_phase_lo = 0, lastR_n_phase = 0;   // rows of R left by the last run (in `scratch`, in the caller's device
+    bool lastR_full = false;                     // buffer or in mapped host memory) over the whole wavelength grid
+    const double* lastR_ptr = nullptr;
 };
 
 static int fail(pb200_ctx* c, int code, const char* fmt, ...) {
@@ -123,14 +124,25 @@ static int ensure_scratch(pb200_ctx* c, size_t bytes) {
 // page-locked blocks handed out by pb200_host_alloc: arrays inside them are copied to the device
 // straight from where they lie (no staging copy), see pb200_set_scene
 static std::mutex g_pinned_mutex;
-static std::map<uintptr_t, size_t> g_pinned;
+struct PinnedBlock { size_t bytes; uintptr_t dev; bool registered; };   // dev: the block's address as the device sees it
+static std::map<uintptr_t, PinnedBlock> g_pinned;
 static bool is_pinned(const void* p, size_t bytes) {
     const uintptr_t a = reinterpret_cast<uintptr_t>(p);
     std::lock_guard<std::mutex> lock(g_pinned_mutex);
     auto it = g_pinned.upper_bound(a);
     if (it == g_pinned.begin()) return false;
     --it;
-    return a >= it->first && a + bytes <= it->first + it->second;
+    return a >= it->first && a + bytes <= it->first + it->second.bytes;
+}
+// device-side address of [p, p + bytes) if it lies in a page-locked block of this library, else NULL
+static double* device_view(const void* p, size_t bytes) {
+    const uintptr_t a = reinterpret_cast<uintptr_t>(p);
+    std::lock_guard<std::mutex> lock(g_pinned_mutex);
+    auto it = g_pinned.upper_bound(a);
+    if (it == g_pinned.begin()) return nullptr;
+    --it;
+    if (!(a >= it->first && a + bytes <= it->first + it->second.bytes) || !it->second.dev) return nullptr;
+    return reinterpret_cast<double*>(it->second.dev + (a - it->first));
 }
 
 static void free_scene(pb200_ctx* c) {
@@ -222,10 +234,40 @@ int pb200_host_alloc(size_t bytes, void** out) {
     *out = nullptr;
     cudaError_t e = cudaMallocHost(out, bytes ? bytes : 1);
     if (e != cudaSuccess) return fail(nullptr, PB200_ERR_CUDA, "cudaMallocHost(%zu): %s", bytes, cudaGetErrorString(e));
+    void* dev = nullptr;
+    if (cudaHostGetDevicePointer(&dev, *out, 0) != cudaSuccess) { cudaGetLastError(); dev = nullptr; }
     {
         std::lock_guard<std::mutex> lock(g_pinned_mutex);
-        g_pinned[reinterpret_cast<uintptr_t>(*out)] = bytes ? bytes : 1;
+        g_pinned[reinterpret_cast<uintptr_t>(*out)] = PinnedBlock{bytes ? bytes : 1, reinterpret_cast<uintptr_t>(dev), false};
     }
+    return PB200_OK;
+}
+
+int pb200_host_register(void* p, size_t bytes, void** dev_ptr) {
+    if (!p || !bytes) return PB200_ERR_INVALID;
+    cudaError_t e = cudaHostRegister(p, bytes, cudaHostRegisterPortable | cudaHostRegisterMapped);
+    if (e != cudaSuccess) { cudaGetLastError(); return fail(nullptr, PB200_ERR_CUDA, "cudaHostRegister(%zu): %s", bytes, cudaGetErrorString(e)); }
+    void* dev = nullptr;
+    e = cudaHostGetDevicePointer(&dev, p, 0);
+    if (e != cudaSuccess) { cudaGetLastError(); cudaHostUnregister(p); return fail(nullptr, PB200_ERR_CUDA, "cudaHostGetDevicePointer: %s", cudaGetErrorString(e)); }
+    {
+        std::lock_guard<std::mutex> lock(g_pinned_mutex);
+        g_pinned[reinterpret_cast<uintptr_t>(p)] = PinnedBlock{bytes, reinterpret_cast<uintptr_t>(dev), true};
+    }
+    if (dev_ptr) *dev_ptr = dev;
+    return PB200_OK;
+}
+
+int pb200_host_unregister(void* p) {
+    if (!p) return PB200_OK;
+    {
+        std::lock_guard<std::mutex> lock(g_pinned_mutex);
+        auto it = g_pinned.find(reinterpret_cast<uintptr_t>(p));
+        if (it == g_pinned.end() || !it->second.registered) return fail(nullptr, PB200_ERR_INVALID, "pb200_host_unregister: not a registered block");
+        g_pinned.erase(it);
+    }
+    cudaError_t e = cudaHostUnregister(p);
+    if (e != cudaSuccess) { cudaGetLastError(); return fail(nullptr, PB200_ERR_CUDA, "cudaHostUnregister: %s", cudaGetErrorString(e)); }
     return PB200_OK;
 }
 
@@ -539,7 +581,7 @@ int check_scene(pb200_ctx* c) {
 
 // enqueue kernels (a') and (c') for the tile; R_dev receives [n_phase][n_wav_sel]
 int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_t wav_hi, double* R_dev,
-                bool R_in_scratch, int64_t cyc_block = 0, int cyc_n = 1, int cyc_rank = 0) {
+                bool R_in_scratch, int64_t cyc_block = 0, int cyc_n = 1, int cyc_rank = 0, int64_t R_row_stride = 0) {
     const DevScene& h = c->h_scene;
     if (phase_lo < 0 || phase_hi > h.n_orb || phase_lo >= phase_hi || wav_lo < 0 || wav_hi > h.n_wav || wav_lo >= wav_hi)
         return fail(c, PB200_ERR_INVALID, "tile [%d,%d) x [%lld,%lld) outside the (%d, %lld) grid", phase_lo, phase_hi,
@@ -553,6 +595,7 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     TransitParams prm;
     prm.phase_lo = phase_lo; prm.n_phase = n_phase; prm.wav_lo = wav_lo; prm.n_wav_sel = n_wav_sel;
     prm.cyc_block = cyc_block; prm.cyc_n = cyc_n; prm.cyc_rank = cyc_rank;
+    prm.R_row_stride = R_in_scratch ? 0 : R_row_stride;
     if (cyc_block && c->general_path)
         return fail(c, PB200_ERR_UNSUPPORTED, "block-cyclic wavelength tiles are implemented for atomic scenes (kernel (c')) only");
     // kernel (m) walks mirror pairs when the scene allows it: about half the chords
@@ -645,9 +688,9 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     c->last.exp_samples = c->last.executed_samples;
     c->last_wpt = prm.win / 32;   // wavelengths per thread of kernel (c')
     c->last_n_wav_sel = n_wav_sel;
-    // R left at the start of `scratch` (pb200_lightcurve with R_dev == NULL reads it there)
-    c->lastR_full = R_in_scratch && !cyc_block && wav_lo == 0 && n_wav_sel == h.n_wav;
-    c->lastR_phase_lo = phase_lo; c->lastR_n_phase = n_phase;
+    // where the run leaves R (pb200_lightcurve with R_dev == NULL reads it there; the caller keeps it alive)
+    c->lastR_full = !cyc_block && !prm.R_row_stride && wav_lo == 0 && n_wav_sel == h.n_wav;
+    c->lastR_phase_lo = phase_lo; c->lastR_n_phase = n_phase; c->lastR_ptr = prm.R;
     return PB200_OK;
 }
 
@@ -684,17 +727,30 @@ int check_oob(pb200_ctx* c) {
 
 }  // namespace
 
+static int need_ctx_early(pb200_ctx* c) {
+    if (!c) return PB200_ERR_INVALID;
+    cudaError_t e = cudaSetDevice(c->device);
+    if (e != cudaSuccess) return fail(c, PB200_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e));
+    return PB200_OK;
+}
+
 extern "C" int pb200_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_t wav_hi, double* R_host,
                          pb200_timing* timing) {
     int rc = check_scene(c);
     if (rc) return rc;
     if (!R_host) return fail(c, PB200_ERR_INVALID, "R_host == NULL");
-    rc = enqueue_run(c, phase_lo, phase_hi, wav_lo, wav_hi, nullptr, true);
-    if (rc) return rc;
     const size_t bytes = (size_t)(phase_hi - phase_lo) * (size_t)(wav_hi - wav_lo) * sizeof(double);
+    // A result array in page-locked memory of pb200_host_alloc / pb200_host_register is written by the kernels
+    // themselves (zero-copy stores over PCIe as the windows finish) instead of device scratch + a D2H copy
+    // afterwards; PB200_NO_ZEROCOPY=1 (measurement) keeps the copy.
+    const char* nz = getenv("PB200_NO_ZEROCOPY");
+    double* mapped = (nz && nz[0] == '1') ? nullptr : device_view(R_host, bytes);
+    rc = mapped ? enqueue_run(c, phase_lo, phase_hi, wav_lo, wav_hi, mapped, false)
+                : enqueue_run(c, phase_lo, phase_hi, wav_lo, wav_hi, nullptr, true);
+    if (rc) return rc;
     cudaEvent_t e0 = c->ev[0], e1 = c->ev[1];
     PB_CUDA(c, cudaEventRecord(e0, c->stream));
-    PB_CUDA(c, cudaMemcpyAsync(R_host, c->scratch, bytes, cudaMemcpyDeviceToHost, c->stream));
+    if (!mapped) PB_CUDA(c, cudaMemcpyAsync(R_host, c->scratch, bytes, cudaMemcpyDeviceToHost, c->stream));
     PB_CUDA(c, cudaEventRecord(e1, c->stream));
     rc = check_oob(c);   // synchronises the stream
     if (rc) return rc;
@@ -748,6 +804,48 @@ extern "C" int pb200_run_device_cyclic(pb200_ctx* c, int phase_lo, int phase_hi,
     const int64_t n_local = cyclic_count(c->h_scene.n_wav, wav_block, n_ranks, rank);
     if (n_local == 0) return PB200_OK;   // more ranks than blocks: nothing to do
     rc = enqueue_run(c, phase_lo, phase_hi, 0, n_local, R_dev, false, wav_block, n_ranks, rank);
+    if (rc) return rc;
+    if (timing) {
+        rc = check_oob(c);
+        if (rc) return rc;
+        rc = collect_timing(c);
+        if (rc) return rc;
+        *timing = c->last;
+    }
+    return PB200_OK;
+}
+
+// waits for the context's stream; reports a tabulated-density out-of-grid condition of the runs since the last check
+extern "C" int pb200_sync(pb200_ctx* c) {
+    int rc = need_ctx_early(c);
+    if (rc) return rc;
+    if (!c->has_scene) { PB_CUDA(c, cudaStreamSynchronize(c->stream)); return PB200_OK; }
+    rc = check_oob(c);
+    if (rc) return rc;
+    PB_CUDA(c, cudaGetLastError());
+    return PB200_OK;
+}
+
+// The rank's block-cyclic tile written IN PLACE into the caller's full result: R_full is row phase_lo of an array
+// with row_stride doubles per phase that the device can address -- mapped page-locked host memory
+// (pb200_host_alloc / pb200_host_register: the D2H transfer is then the kernel's own stores, every rank over its
+// own PCIe link) or a peer GPU's buffer (stores over NVLink).  n_ranks == 1: the whole wavelength axis.
+extern "C" int pb200_run_scatter(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_block, int n_ranks, int rank,
+                                 double* R_full, int64_t row_stride, pb200_timing* timing) {
+    int rc = check_scene(c);
+    if (rc) return rc;
+    if (!R_full) return fail(c, PB200_ERR_INVALID, "R_full == NULL");
+    if (n_ranks <= 0 || rank < 0 || rank >= n_ranks || (n_ranks > 1 && wav_block <= 0) || row_stride < c->h_scene.n_wav)
+        return fail(c, PB200_ERR_INVALID, "pb200_run_scatter: block %lld, rank %d of %d, row stride %lld", (long long)wav_block, rank, n_ranks, (long long)row_stride);
+    double* dst = R_full;
+    if (double* m = device_view(R_full, sizeof(double))) dst = m;   // a host address of a page-locked block: use its device view
+    if (n_ranks == 1) {
+        rc = enqueue_run(c, phase_lo, phase_hi, 0, c->h_scene.n_wav, dst, false, 0, 1, 0, row_stride);
+    } else {
+        const int64_t n_local = cyclic_count(c->h_scene.n_wav, wav_block, n_ranks, rank);
+        if (n_local == 0) return PB200_OK;
+        rc = enqueue_run(c, phase_lo, phase_hi, 0, n_local, dst, false, wav_block, n_ranks, rank, row_stride);
+    }
     if (rc) return rc;
     if (timing) {
         rc = check_oob(c);
@@ -940,7 +1038,7 @@ extern "C" int pb200_lightcurve(pb200_ctx* c, const pb200_band* band, int phase_
     if (!rows) {
         if (!c->lastR_full || phase_lo < c->lastR_phase_lo || phase_hi > c->lastR_phase_lo + c->lastR_n_phase)
             return fail(c, PB200_ERR_INVALID, "no resident R covers rows [%d,%d): run pb200_run over the whole wavelength grid first", phase_lo, phase_hi);
-        rows = c->scratch + (int64_t)(phase_lo - c->lastR_phase_lo) * c->h_scene.n_wav;
+        rows = c->lastR_ptr + (int64_t)(phase_lo - c->lastR_phase_lo) * c->h_scene.n_wav;
     }
     rc = enqueue_lightcurve(c, band, phase_lo, phase_hi, rows);
     if (rc) return rc;

@@ -302,7 +302,7 @@ transit_general_kernel(const DevScene* __restrict__ scp, const TransitParams prm
 
     if (!live) return;
     const int64_t o = (int64_t)blockIdx.y * prm.n_wav_sel + (w - prm.wav_lo);
-    if (prm.n_split == 1) prm.R[o] = acc / sc.fout[per_chord_fstar ? w : 0];                  // :1258
+    if (prm.n_split == 1) prm.R[pb_out_index(prm, blockIdx.y, w - prm.wav_lo)] = acc / sc.fout[per_chord_fstar ? w : 0];   // :1258
     else prm.partial[(int64_t)blockIdx.z * prm.n_phase * prm.n_wav_sel + o] = acc;
 }
 

@@ -112,12 +112,19 @@ struct TransitParams {
     double* winmax;       // [n_atoms][n_phase][n_win] max |nsig_a| of each window (sigma_phase_kernel)
     double* partial;      // [n_split][n_phase][n_wav_sel] sums of w_in*exp(-tau)  (n_split > 1); kernel (c') only writes
                           // the slots of splits that have tiles (pb_splits_used)
-    double* R;            // [n_phase][n_wav_sel] final ratio
+    double* R;            // [n_phase][n_wav_sel] final ratio, or (R_row_stride != 0) row 0 of the caller's FULL result:
+                          // element (pi, wi) goes to R[pi * R_row_stride + global wavelength index] -- the tile is
+                          // written in place into memory the device can reach (mapped host memory, a peer GPU)
+    int64_t R_row_stride;
     double* nsig;         // [n_atoms][n_phase][n_wav_sel] -sigma_a(p, w) * 4096/ln2 (sigma_phase_kernel)
 };
 __host__ __device__ inline int64_t pb_wav_index(const TransitParams& prm, int64_t wi) {
     if (prm.cyc_block == 0) return prm.wav_lo + wi;
     return ((wi / prm.cyc_block) * prm.cyc_n + prm.cyc_rank) * prm.cyc_block + wi % prm.cyc_block;
+}
+// where element (pi, wi) of the run's tile goes in prm.R
+__host__ __device__ inline int64_t pb_out_index(const TransitParams& prm, int pi, int64_t wi) {
+    return prm.R_row_stride ? (int64_t)pi * prm.R_row_stride + pb_wav_index(prm, wi) : (int64_t)pi * prm.n_wav_sel + wi;
 }
 
 

@@ -359,7 +359,7 @@ transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
 #pragma unroll
         for (int k = 1; k < NWARPS; ++k) v += red[k * WIN + t];
         const int64_t o = (int64_t)pi * prm.n_wav_sel + w;
-        if (prm.n_split == 1) prm.R[o] = (v + sc.w0[p]) / sc.fout[0];           // :1258
+        if (prm.n_split == 1) prm.R[pb_out_index(prm, pi, w)] = (v + sc.w0[p]) / sc.fout[0];           // :1258
         else prm.partial[(int64_t)split * prm.n_phase * prm.n_wav_sel + o] = v;
     }
 }
@@ -374,7 +374,7 @@ __global__ void finalize_kernel(const DevScene* __restrict__ scp, const TransitP
         const int used = prm.culled ? pb_splits_used(sc.n_act[p], prm.n_split, prm.min_tiles) : prm.n_split;
         for (int k = 0; k < used; ++k) s += prm.partial[(int64_t)k * n + i];
         const double fout = sc.fout[sc.fout_per_wav ? prm.wav_lo + i % prm.n_wav_sel : 0];
-        prm.R[i] = s / fout;
+        prm.R[pb_out_index(prm, (int)(i / prm.n_wav_sel), i % prm.n_wav_sel)] = s / fout;
     }
 }
 

@@ -209,3 +209,208 @@ def sum_over_chords(transit, group=None, axis: str = "wavelength", device: int |
     if state is not None:
         state["info"] = info
     return st.to_host(dst)
+
+
+# ---------------------------------------------------------------------------------------------------
+# node-local result without a gather: every rank's kernels store their tiles straight into ONE page-locked
+# POSIX shared-memory array that all ranks of the node have mapped (pb200_run_scatter) -- the device-to-host
+# transfer runs over every GPU's own PCIe link at once instead of funnelling through rank 0's.
+# ---------------------------------------------------------------------------------------------------
+class SharedResult:
+    """Pool of shared, page-locked (n_orb, n_wav) result arrays plus the few control words the ranks need.
+
+    Control block (int64): [0] sequence number of the current call, [1] segment index chosen by rank 0,
+    [2] its size in bytes, [4 + r] sequence number rank r has completed.  x86 keeps the stores in order; the
+    waits are spins on these words (microseconds: every rank has just synchronised its stream)."""
+
+    CTL_WORDS = 4
+
+    def __init__(self, world: int, rank: int, tag: str, register=None, unregister=None, timeout: float = 120.0):
+        self.world, self.rank, self.tag, self.timeout = int(world), int(rank), str(tag), timeout
+        self._register, self._unregister = register, unregister
+        self.seq = 0
+        self.segments = {}          # index -> (SharedMemory, device pointer)
+        self.free = []              # rank 0: indices not handed out
+        self.sizes = {}
+        self._n_created = 0
+        self.ctl_shm = self._open(f"pb200_{self.tag}_ctl", 8 * (self.CTL_WORDS + self.world), create=(self.rank == 0))
+        self.ctl = np.ndarray((self.CTL_WORDS + self.world,), dtype=np.int64, buffer=self.ctl_shm.buf)
+        if self.rank == 0:
+            self.ctl[:] = 0
+
+    def _open(self, name, size, create):
+        """mmap of /dev/shm/<name> (plain files: no resource tracker involved); the creator sizes it, the others wait
+        until it exists with its full size."""
+        import mmap
+        import os
+        import time
+        path = os.path.join("/dev/shm", name)
+        if create:
+            fd = os.open(path, os.O_CREAT | os.O_EXCL | os.O_RDWR, 0o600)
+            os.ftruncate(fd, size)
+        else:
+            t0 = time.monotonic()
+            while True:
+                try:
+                    fd = os.open(path, os.O_RDWR)
+                    if os.fstat(fd).st_size >= size:
+                        break
+                    os.close(fd)
+                except FileNotFoundError:
+                    pass
+                if time.monotonic() - t0 > self.timeout:
+                    raise TimeoutError(f"SharedResult: {path} did not appear")
+                time.sleep(0.0005)
+        try:
+            mm = mmap.mmap(fd, size)
+        finally:
+            os.close(fd)
+        return _Segment(mm, path, size, create)
+
+    def _spin(self, cond, what):
+        import time
+        t0 = time.monotonic()
+        n = 0
+        while not cond():
+            n += 1
+            if n % 4096 == 0 and time.monotonic() - t0 > self.timeout:
+                raise TimeoutError(f"SharedResult: rank {self.rank} waited {self.timeout}s for {what}")
+
+    def _segment(self, k, size):
+        if k not in self.segments:
+            shm = self._open(f"pb200_{self.tag}_{k}", size, create=(self.rank == 0))
+            addr = C_addressof(shm.buf)
+            dev = self._register(addr, shm.size) if self._register else addr
+            self.segments[k] = (shm, dev, addr)
+            self.sizes[k] = size
+        return self.segments[k]
+
+    def begin(self, n_orb: int, n_wav: int):
+        """-> (segment index, (n_orb, n_wav) float64 view, device pointer) for this call; collective over the ranks."""
+        self.seq += 1
+        nbytes = int(n_orb) * int(n_wav) * 8
+        if self.rank == 0:
+            k = next((i for i in self.free if self.sizes[i] >= nbytes), None)
+            if k is None:
+                k = self._n_created
+                self._n_created += 1
+            else:
+                self.free.remove(k)
+            size = self.sizes.get(k, nbytes)
+            shm, dev, _ = self._segment(k, size)
+            self.ctl[1], self.ctl[2] = k, size
+            self.ctl[0] = self.seq
+        else:
+            self._spin(lambda: self.ctl[0] >= self.seq, f"call {self.seq}")
+            k, size = int(self.ctl[1]), int(self.ctl[2])
+            shm, dev, _ = self._segment(k, size)
+        view = np.ndarray((n_orb, n_wav), dtype=np.float64, buffer=shm.buf)
+        return k, view, dev
+
+    def end(self, k: int, view):
+        """Call after this rank's stream is synchronised.  Rank 0 waits for every rank and gets the array (given
+        back to the pool when it is garbage collected); the others return None."""
+        import weakref
+        self.ctl[self.CTL_WORDS + self.rank] = self.seq
+        if self.rank != 0:
+            return None
+        flags = self.ctl[self.CTL_WORDS:]
+        self._spin(lambda: bool(np.all(flags >= self.seq)), "the other ranks' tiles")
+        out = view.view()
+        weakref.finalize(out, self.free.append, k)
+        return out
+
+    def close(self):
+        for k, (shm, dev, addr) in list(self.segments.items()):
+            try:
+                if self._unregister:
+                    self._unregister(addr)
+            except Exception:
+                pass
+            shm.close()
+        self.segments.clear()
+        if self.ctl_shm is not None:
+            self.ctl = None
+            self.ctl_shm.close()
+            self.ctl_shm = None
+
+
+class _Segment:
+    def __init__(self, mm, path, size, owner):
+        self.buf, self.path, self.size, self.owner = mm, path, size, owner
+
+    def close(self):
+        import os
+        try:
+            self.buf.close()
+        except BufferError:
+            pass              # views handed to the caller are still alive: the mapping goes with the process
+        if self.owner:
+            try:
+                os.unlink(self.path)
+            except FileNotFoundError:
+                pass
+
+
+def C_addressof(buf) -> int:
+    import ctypes
+    return ctypes.addressof(ctypes.c_char.from_buffer(buf))
+
+
+def shared_result_for(group=None, state: dict | None = None) -> SharedResult:
+    """The SharedResult of this process group (created on first use; rank 0's pid and clock name the segments)."""
+    import os
+    import time
+    import torch.distributed as dist
+    if state is not None and state.get("shared") is not None:
+        return state["shared"]
+    from . import capi
+    lib = capi.load()
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    tag = [f"{os.getpid()}_{time.monotonic_ns()}"]
+    if world > 1:
+        dist.broadcast_object_list(tag, src=0, group=group)
+
+    def register(addr, nbytes):
+        import ctypes as C
+        dev = C.c_void_p()
+        rc = lib.pb200_host_register(C.c_void_p(addr), nbytes, C.byref(dev))
+        if rc:
+            raise capi.Pb200Error(rc, (lib.pb200_last_error(None) or b"").decode())
+        return int(dev.value)
+
+    def unregister(addr):
+        import ctypes as C
+        lib.pb200_host_unregister(C.c_void_p(addr))
+
+    sr = SharedResult(world, rank, tag[0], register, unregister)
+    import atexit
+    atexit.register(sr.close)
+    if state is not None:
+        state["shared"] = sr
+    return sr
+
+
+def sum_over_chords_shared(transit, group=None, device: int | None = None, state: dict | None = None):
+    """Sharded Transit.sumOverChords for the ranks of ONE node without a gather: block-cyclic wavelength tiles
+    (atomic scenes), each rank's kernels store into the shared page-locked result (pb200_run_scatter).  Rank 0
+    returns R (n_orb, n_wav) -- a view of pooled shared memory, valid until it is garbage collected -- the others
+    None.  Replaces memoryHandler's chord batching (memoryHandler.py:55-66) on a multi-GPU node."""
+    import torch
+    from . import host, scene
+    if device is None:
+        device = torch.cuda.current_device()
+    ctx = host.get_context(device)
+    ctx.set_stream(torch.cuda.current_stream(device).cuda_stream)
+    world = torch.distributed.get_world_size(group) if torch.distributed.is_initialized() else 1
+    rank = torch.distributed.get_rank(group) if torch.distributed.is_initialized() else 0
+    sr = shared_result_for(group, state)
+    sc, keep, info = scene.flatten(transit)
+    ctx.set_scene(sc, keep)
+    k, view, dev = sr.begin(info["n_orb"], info["n_wav"])
+    ctx.run_scatter(0, info["n_orb"], CYCLIC_BLOCK, world, rank, dev, info["n_wav"])
+    ctx.synchronize()
+    if state is not None:
+        state["info"] = info
+    return sr.end(k, view)

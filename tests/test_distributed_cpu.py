@@ -103,3 +103,48 @@ def test_cyclic_indices_match_the_library_count():
             assert np.array_equal(np.sort(seen), np.arange(n))
             for r in range(world):
                 assert lib.pb200_cyclic_count(n, pbd.CYCLIC_BLOCK, world, r) == pbd.cyclic_indices(n, world, r).size
+
+
+# ---- SharedResult: the gather-free result path (control words + pooled shared segments), no GPU needed ------
+def _shared_worker(rank, world, tag, n_orb, n_wav, n_calls, q):
+    sr = pbd.SharedResult(world, rank, tag, timeout=60.0)
+    try:
+        ok = True
+        held = []
+        for call in range(n_calls):
+            k, view, dev = sr.begin(n_orb, n_wav)
+            idx = pbd.cyclic_indices(n_wav, world, rank)
+            view[:, idx] = _truth(n_orb, n_wav)[:, idx] + call            # what pb200_run_scatter stores
+            R = sr.end(k, view)
+            if rank == 0:
+                ok &= bool(np.array_equal(R, _truth(n_orb, n_wav) + call))
+                if call == 0:
+                    held.append(R)                                         # a result the caller keeps ...
+            else:
+                ok &= R is None
+        if rank == 0:
+            ok &= bool(np.array_equal(held[0], _truth(n_orb, n_wav)))      # ... is not overwritten by later calls
+            ok &= len(sr.segments) <= 3                                    # one held, the others recycled
+        q.put((rank, ok))
+        # leave only after everyone is done with the segments
+        sr.ctl[sr.CTL_WORDS + rank] = 10 ** 9
+        if rank == 0:
+            sr._spin(lambda: bool(np.all(sr.ctl[sr.CTL_WORDS:] >= 10 ** 9)), "exit")
+    finally:
+        held = None
+        sr.close()
+
+
+@pytest.mark.parametrize("world,n_orb,n_wav", [(2, 5, 1000), (3, 2, 300)])
+def test_shared_result_protocol(world, n_orb, n_wav):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    tag = f"test{os.getpid()}_{world}_{n_wav}"
+    procs = [ctx.Process(target=_shared_worker, args=(r, world, tag, n_orb, n_wav, 4, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=120) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert all(ok for _, ok in results), results

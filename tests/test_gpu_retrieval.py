@@ -136,3 +136,48 @@ def test_error_conventions(setup):
     lc, _, _ = batch.run(variants, empty)
     assert np.all(np.isnan(lc))
     batch.reset()
+
+
+# ---- results written in place: zero-copy pb200_run, pb200_run_scatter ------------------------------------------
+def test_scatter_tiles_and_zero_copy_equal_the_plain_run(nist_rows, monkeypatch):
+    import ctypes as C
+    from prometheus_b200 import scene
+    tr = builder.build_transit(workloads.get("C3s"), nist_rows=nist_rows)
+    ctx = host.get_context()
+    sc, keep, info = scene.flatten(tr)
+    ctx.set_scene(sc, keep)
+    n_orb, n_wav = info["n_orb"], info["n_wav"]
+    monkeypatch.setenv("PB200_NO_ZEROCOPY", "1")
+    R_copy, _ = ctx.run(0, n_orb, 0, n_wav)                      # device scratch + D2H
+    monkeypatch.delenv("PB200_NO_ZEROCOPY")
+    R_zero, _ = ctx.run(0, n_orb, 0, n_wav)                      # kernels store into the page-locked result
+    assert np.array_equal(R_copy, R_zero)
+    pageable = np.empty((n_orb, n_wav))
+    R_page, _ = ctx.run(0, n_orb, 0, n_wav, out=pageable)        # not page-locked: falls back to the copy
+    assert np.array_equal(R_copy, R_page)
+    # three "ranks" scatter their block-cyclic tiles into one mapped array with a padded row stride
+    stride = n_wav + 5
+    full = capi.pinned_pool.empty((n_orb, stride))
+    full[...] = -1.0
+    for r in range(3):
+        ctx.run_scatter(0, n_orb, 256, 3, r, full.ctypes.data, stride)
+    ctx.synchronize()
+    assert np.array_equal(full[:, :n_wav], R_copy) and np.all(full[:, n_wav:] == -1.0)
+    # a sub-range of phases, whole wavelength axis, one rank
+    full[...] = -1.0
+    ctx.run_scatter(1, 3, 256, 1, 0, full[1:].ctypes.data, stride)
+    ctx.synchronize()
+    assert np.array_equal(full[1:3, :n_wav], R_copy[1:3]) and np.all(full[0] == -1.0) and np.all(full[3:] == -1.0)
+    # memory the caller owns, registered
+    own = np.zeros(n_orb * n_wav + 512)
+    base = (own.ctypes.data + 4095) // 4096 * 4096
+    lib = capi.load()
+    dev = C.c_void_p()
+    assert lib.pb200_host_register(C.c_void_p(base), n_orb * n_wav * 8, C.byref(dev)) == 0
+    ctx.run_scatter(0, n_orb, 256, 1, 0, base, n_wav)
+    ctx.synchronize()
+    off = (base - own.ctypes.data) // 8
+    assert np.array_equal(own[off:off + n_orb * n_wav].reshape(n_orb, n_wav), R_copy)
+    assert lib.pb200_host_unregister(C.c_void_p(base)) == 0
+    with pytest.raises(capi.Pb200Error):
+        ctx.run_scatter(0, n_orb, 256, 1, 0, full.ctypes.data, n_wav - 1)
