@@ -511,6 +511,7 @@ def run_b200(args):
         "e2e": {"value": samples_total / (e2e_ms_per_step * 1e-3), "unit": "samples/s", "ms_per_step": e2e_ms_per_step,
                 "h2d_bytes_per_step": int(launch_total[1].item()), "d2h_bytes_per_step": int(n_orb * n_wav * 8),
                 "runs_per_s": 1e3 / e2e_ms_per_step},
+        "e2e_host_ms_rank0": (state.get("host_ms") if world > 1 else None),
         "e2e_breakdown_ms": ({k: tr.last_timing[k] for k in ("upload_ms", "column_ms", "transit_ms", "finalize_ms", "download_ms")}
                              if world == 1 and tr.last_timing else None),
         "gpu_launches": int(launch_total[0].item()),

@@ -182,6 +182,13 @@ int pb200_host_unregister(void* p);
 /* ---- scene ------------------------------------------------------------------------------ */
 /* Uploads everything Transit.sumOverChords reads through `self`.             */
 int pb200_set_scene(pb200_ctx* ctx, const pb200_scene* scene);
+/* The same for rank `rank` of n_ranks processes that upload the SAME scene to the GPUs of one node: of every
+   large atomic sigma table only this rank's n_ranks-th crosses PCIe.  Before the first run the ranks complete
+   the tables with one all-gather per region over NVLink: region i is n_ranks*chunk_doubles[i] doubles at device
+   address base[i], rank r owns [r*chunk, (r+1)*chunk) (ncclAllGather in place; prometheus_b200/distributed.py).
+   The reference re-reads its tables from host RAM per chunk (gasProperties.py:948-952).                      */
+int pb200_set_scene_sharded(pb200_ctx* ctx, const pb200_scene* scene, int n_ranks, int rank);
+int pb200_table_regions(pb200_ctx* ctx, int max_regions, void** base, int64_t* chunk_doubles, int* n_regions);
 
 /* ---- Transit.sumOverChords (gasProperties.py:1160-1258) ---------------------------------
  * R[(p-phase_lo)*(wav_hi-wav_lo) + (w-wav_lo)] for p in [phase_lo,phase_hi), w in [wav_lo,wav_hi).

@@ -25,6 +25,7 @@ EXPORTS = [
     "pb200_voigt_profile", "pb200_molecular_sigma", "pb200_write_output", "pb200_probe_fp64",
     "pb200_set_models", "pb200_lightcurve", "pb200_run_batch",
     "pb200_host_register", "pb200_host_unregister", "pb200_run_scatter", "pb200_sync",
+    "pb200_set_scene_sharded", "pb200_table_regions",
 ]
 
 SCN_BAROMETRIC, SCN_HYDROSTATIC, SCN_POWERLAW, SCN_TORUS, SCN_SERPENS = range(5)
@@ -162,6 +163,8 @@ def load():
         "pb200_write_output": (C.c_int, [C.c_char_p, C.c_char_p, c_double_p, c_double_p, c_double_p, i32, i64, i32]),
         "pb200_probe_fp64": (C.c_int, [vp, c_double_p, c_double_p]),
         "pb200_sync": (C.c_int, [vp]),
+        "pb200_set_scene_sharded": (C.c_int, [vp, C.POINTER(Scene), i32, i32]),
+        "pb200_table_regions": (C.c_int, [vp, i32, C.POINTER(vp), C.POINTER(i64), C.POINTER(i32)]),
         "pb200_host_register": (C.c_int, [vp, C.c_size_t, C.POINTER(vp)]),
         "pb200_host_unregister": (C.c_int, [vp]),
         "pb200_run_scatter": (C.c_int, [vp, i32, i32, i64, i32, i32, vp, i64, C.POINTER(Timing)]),
@@ -285,6 +288,17 @@ class Context:
     def set_scene(self, scene: Scene, keep):
         self._keep = keep
         self.check(self.lib.pb200_set_scene(self.handle, C.byref(scene)))
+
+    def set_scene_sharded(self, scene: Scene, keep, n_ranks: int, rank: int):
+        """Upload this rank's share of the large tables; returns [(device pointer, doubles per rank)] -- the regions
+        the ranks must all-gather (in place, rank r owns slice r) before running."""
+        self._keep = keep
+        self.check(self.lib.pb200_set_scene_sharded(self.handle, C.byref(scene), n_ranks, rank))
+        n = C.c_int32(0)
+        base = (C.c_void_p * 64)()
+        chunk = (C.c_int64 * 64)()
+        self.check(self.lib.pb200_table_regions(self.handle, 64, base, chunk, C.byref(n)))
+        return [(int(base[i]), int(chunk[i])) for i in range(min(n.value, 64))]
 
     def run(self, phase_lo, phase_hi, wav_lo, wav_hi, out: np.ndarray | None = None):
         n = (phase_hi - phase_lo, wav_hi - wav_lo)

@@ -93,6 +93,7 @@ struct pb200_ctx {
     int lastR_phase_lo = 0, lastR_n_phase = 0;   // rows of R left by the last run (in `scratch`, in the caller's device
     bool lastR_full = false;                     // buffer or in mapped host memory) over the whole wavelength grid
     const double* lastR_ptr = nullptr;
+    std::vector<std::pair<void*, int64_t>> regions;   // sharded uploads of the current scene: (device base, doubles per rank)
 };
 
 static int fail(pb200_ctx* c, int code, const char* fmt, ...) {
@@ -290,13 +291,22 @@ int pb200_host_free(void* p) {
 namespace {
 
 struct ArenaPlan {
-    struct Item { const void* src; size_t bytes; size_t offset; };
+    struct Item { const void* src; size_t bytes; size_t offset; size_t chunk; };   // chunk != 0: sharded upload, bytes per rank
     std::vector<Item> items;
     size_t total = 0;
+    // a large table of which every rank uploads one n_ranks-th; the ranks complete it with an all-gather
+    // (pb200_set_scene_sharded): room for n_ranks whole chunks
+    size_t add_sharded(const void* src, size_t bytes, int n_ranks) {
+        const size_t per = (((bytes + n_ranks - 1) / n_ranks) + 255) & ~size_t(255);
+        const size_t off = total;
+        items.push_back({src, bytes, off, per});
+        total += per * n_ranks;
+        return off;
+    }
     // returns the offset (in bytes) the array will have inside the arena
     size_t add(const void* src, size_t bytes) {
         const size_t off = total;
-        items.push_back({src, bytes, off});
+        items.push_back({src, bytes, off, 0});
         total += (bytes + 255) & ~size_t(255);   // 256-byte alignment: TMA bulk copies need 16
         return off;
     }
@@ -357,7 +367,29 @@ static int plan_derived(pb200_ctx* c) {
     return PB200_OK;
 }
 
-extern "C" int pb200_set_scene(pb200_ctx* c, const pb200_scene* s) {
+static int set_scene_impl(pb200_ctx* c, const pb200_scene* s, int n_ranks, int rank);
+
+extern "C" int pb200_set_scene(pb200_ctx* c, const pb200_scene* s) { return set_scene_impl(c, s, 1, 0); }
+
+// As pb200_set_scene, for rank `rank` of n_ranks processes that upload the SAME scene to their GPUs: of every large
+// atomic sigma table only this rank's n_ranks-th goes over PCIe; the ranks then complete the tables with one
+// all-gather per region over NVLink (pb200_table_regions; prometheus_b200/distributed.py) before the first run.
+extern "C" int pb200_set_scene_sharded(pb200_ctx* c, const pb200_scene* s, int n_ranks, int rank) {
+    if (n_ranks < 1 || rank < 0 || rank >= n_ranks) return fail(c, PB200_ERR_INVALID, "pb200_set_scene_sharded: rank %d of %d", rank, n_ranks);
+    return set_scene_impl(c, s, n_ranks, rank);
+}
+
+extern "C" int pb200_table_regions(pb200_ctx* c, int max_regions, void** base, int64_t* chunk_doubles, int* n_regions) {
+    if (!c || !n_regions) return PB200_ERR_INVALID;
+    *n_regions = (int)c->regions.size();
+    for (int i = 0; i < (int)c->regions.size() && i < max_regions; ++i) {
+        if (base) base[i] = c->regions[i].first;
+        if (chunk_doubles) chunk_doubles[i] = c->regions[i].second;
+    }
+    return PB200_OK;
+}
+
+static int set_scene_impl(pb200_ctx* c, const pb200_scene* s, int n_ranks, int rank) {
     if (!c || !s) return PB200_ERR_INVALID;
     if (s->abi_version != PB200_ABI_VERSION)
         return fail(c, PB200_ERR_INVALID, "scene abi_version %d != library %d", s->abi_version, PB200_ABI_VERSION);
@@ -434,7 +466,11 @@ extern "C" int pb200_set_scene(pb200_ctx* c, const pb200_scene* s) {
         const pb200_constituent& q = s->constituents[k];
         if (q.kind == 0) {
             if (!q.tab_x || !q.tab_y || q.n_tab < 1) return fail(c, PB200_ERR_INVALID, "constituent %d: sigma table missing", k);
-            co[k].tx = plan.add(q.tab_x, q.n_tab * D); co[k].ty = plan.add(q.tab_y, q.n_tab * D);
+            if (n_ranks > 1 && (size_t)q.n_tab * D >= (size_t(1) << 20)) {
+                co[k].tx = plan.add_sharded(q.tab_x, q.n_tab * D, n_ranks); co[k].ty = plan.add_sharded(q.tab_y, q.n_tab * D, n_ranks);
+            } else {
+                co[k].tx = plan.add(q.tab_x, q.n_tab * D); co[k].ty = plan.add(q.tab_y, q.n_tab * D);
+            }
         } else if (q.kind == 1) {
             if (!q.grid_P || !q.grid_T || !q.grid_w || !q.values || q.dims[0] < 2 || q.dims[1] < 2 || q.dims[2] < 2)
                 return fail(c, PB200_ERR_INVALID, "constituent %d: molecular table missing", k);
@@ -470,8 +506,23 @@ extern "C" int pb200_set_scene(pb200_ctx* c, const pb200_scene* s) {
             run_lo = run_hi;
             return e;
         };
+        c->regions.clear();
         for (const auto& it : plan.items) {
-            if (it.bytes >= (64u << 10) && is_pinned(it.src, it.bytes)) {
+            if (it.chunk) {   // this rank's slice only
+                PB_CUDA(c, flush_run());
+                const size_t lo = it.chunk * rank;
+                const size_t n = lo < it.bytes ? (it.bytes - lo < it.chunk ? it.bytes - lo : it.chunk) : 0;
+                char* dst = static_cast<char*>(c->arena) + it.offset + lo;
+                const char* src = static_cast<const char*>(it.src) + lo;
+                if (n && is_pinned(src, n)) {
+                    PB_CUDA(c, cudaMemcpyAsync(dst, src, n, cudaMemcpyHostToDevice, c->stream));
+                } else if (n) {
+                    memcpy(static_cast<char*>(c->stage) + it.offset + lo, src, n);
+                    PB_CUDA(c, cudaMemcpyAsync(dst, static_cast<char*>(c->stage) + it.offset + lo, n, cudaMemcpyHostToDevice, c->stream));
+                }
+                run_lo = run_hi = it.offset + it.chunk * n_ranks;
+                c->regions.push_back({static_cast<char*>(c->arena) + it.offset, (int64_t)(it.chunk / sizeof(double))});
+            } else if (it.bytes >= (64u << 10) && is_pinned(it.src, it.bytes)) {
                 PB_CUDA(c, flush_run());
                 PB_CUDA(c, cudaMemcpyAsync(static_cast<char*>(c->arena) + it.offset, it.src, it.bytes,
                                            cudaMemcpyHostToDevice, c->stream));

@@ -392,6 +392,21 @@ def shared_result_for(group=None, state: dict | None = None) -> SharedResult:
     return sr
 
 
+class _DevArray:
+    """A device pointer of the library presented through __cuda_array_interface__ (for torch.as_tensor)."""
+
+    def __init__(self, ptr: int, n: int):
+        self.__cuda_array_interface__ = {"shape": (int(n),), "typestr": "<f8", "data": (int(ptr), False), "version": 2}
+
+
+def _device_tensor(torch, ptr: int, n: int, device: int, state: dict | None):
+    cache = state.setdefault("dev_tensors", {}) if state is not None else {}
+    key = (ptr, n, device)
+    if key not in cache:
+        cache[key] = torch.as_tensor(_DevArray(ptr, n), device=torch.device("cuda", device))
+    return cache[key]
+
+
 def sum_over_chords_shared(transit, group=None, device: int | None = None, state: dict | None = None):
     """Sharded Transit.sumOverChords for the ranks of ONE node without a gather: block-cyclic wavelength tiles
     (atomic scenes), each rank's kernels store into the shared page-locked result (pb200_run_scatter).  Rank 0
@@ -405,12 +420,31 @@ def sum_over_chords_shared(transit, group=None, device: int | None = None, state
     ctx.set_stream(torch.cuda.current_stream(device).cuda_stream)
     world = torch.distributed.get_world_size(group) if torch.distributed.is_initialized() else 1
     rank = torch.distributed.get_rank(group) if torch.distributed.is_initialized() else 0
+    import time
     sr = shared_result_for(group, state)
+    t0 = time.perf_counter()
     sc, keep, info = scene.flatten(transit)
-    ctx.set_scene(sc, keep)
+    t1 = time.perf_counter()
+    if world > 1:
+        # every rank sends one world-th of each large sigma table over its PCIe link; the rest arrives from the
+        # peers over NVLink (one in-place all-gather per table)
+        for ptr, chunk in ctx.set_scene_sharded(sc, keep, world, rank):
+            info["h2d_bytes"] -= chunk * 8 * (world - 1)          # the peers' slices do not cross this rank's PCIe link
+            info["nvlink_allgather_bytes"] = info.get("nvlink_allgather_bytes", 0) + chunk * 8 * world
+            full = _device_tensor(torch, ptr, chunk * world, device, state)
+            torch.distributed.all_gather_into_tensor(full, full[rank * chunk:(rank + 1) * chunk], group=group)
+    else:
+        ctx.set_scene(sc, keep)
+    t2 = time.perf_counter()
     k, view, dev = sr.begin(info["n_orb"], info["n_wav"])
+    t3 = time.perf_counter()
     ctx.run_scatter(0, info["n_orb"], CYCLIC_BLOCK, world, rank, dev, info["n_wav"])
     ctx.synchronize()
+    t4 = time.perf_counter()
+    out = sr.end(k, view)
+    t5 = time.perf_counter()
     if state is not None:
         state["info"] = info
-    return sr.end(k, view)
+        state["host_ms"] = {"flatten": (t1 - t0) * 1e3, "set_scene_call": (t2 - t1) * 1e3, "begin": (t3 - t2) * 1e3,
+                            "run_and_sync": (t4 - t3) * 1e3, "end_wait": (t5 - t4) * 1e3}
+    return out
