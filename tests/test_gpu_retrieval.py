@@ -181,3 +181,33 @@ def test_scatter_tiles_and_zero_copy_equal_the_plain_run(nist_rows, monkeypatch)
     assert lib.pb200_host_unregister(C.c_void_p(base)) == 0
     with pytest.raises(capi.Pb200Error):
         ctx.run_scatter(0, n_orb, 256, 1, 0, full.ctypes.data, n_wav - 1)
+
+
+def test_sharded_table_upload_fills_the_whole_table(nist_rows):
+    """pb200_set_scene_sharded: rank r uploads slice r of every large sigma table.  On one GPU the three 'ranks'
+    write into the same (grow-only) arena one after the other, which is what the all-gather does across GPUs."""
+    from prometheus_b200 import scene
+    spec = workloads.get("C4s")
+    spec["wavelength"][4] = 2e-12           # finer grid: the refined sigma table exceeds the 1 MiB sharding threshold
+    tr = builder.build_transit(spec, nist_rows=nist_rows)
+    assert tr.atmosphere.densityDistributionList[0].constituents[0].lookupFunction.x.nbytes > (1 << 20)
+    ctx = host.get_context()
+    sc, keep, info = scene.flatten(tr)
+    ctx.set_scene(sc, keep)
+    R_ref, _ = ctx.run(0, info["n_orb"], 0, info["n_wav"])
+    regions = None
+    for r in (2, 0, 1):
+        regions = ctx.set_scene_sharded(sc, keep, 3, r)
+    assert len(regions) == 2 and all(chunk % 32 == 0 for _, chunk in regions)
+    R, _ = ctx.run(0, info["n_orb"], 0, info["n_wav"])
+    assert np.array_equal(R, R_ref)
+    # a single rank's slice alone is not enough (the test would be vacuous otherwise)
+    big = builder.build_transit(spec, nist_rows=nist_rows)
+    lf = big.atmosphere.densityDistributionList[0].constituents[0].lookupFunction
+    lf.y = lf.y + 1.0                       # a different table: fresh content in every slice
+    sc2, keep2, _ = scene.flatten(big)
+    ctx.set_scene_sharded(sc2, keep2, 3, 0)
+    R_partial, _ = ctx.run(0, info["n_orb"], 0, info["n_wav"])
+    ctx.set_scene(sc2, keep2)
+    R_full, _ = ctx.run(0, info["n_orb"], 0, info["n_wav"])
+    assert not np.array_equal(R_partial, R_full)
