@@ -21,7 +21,7 @@ namespace pb200 {
 void launch_sky_cells(const DevScene*, int Mp, cudaStream_t);
 void launch_fout_scalar(const DevScene*, cudaStream_t);
 void launch_column(const DevScene*, int Mp, int phase_lo, int n_phase, int* oob, int sm_count, cudaStream_t, bool has_molecules,
-                   bool run_mode);
+                   int run_mode);
 void launch_number_density_grid(const DevScene*, int64_t n_chords, int scenario, double* out, int* oob, int sm_count,
                                 cudaStream_t);
 void launch_number_density_chords(const DevScene*, int scenario, int64_t n, const double* y, const double* z,
@@ -179,7 +179,7 @@ int pb200_create(int device, pb200_ctx** out) {
     if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_scene, sizeof(DevScene));
     if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_oob, 32);   // [0] out-of-grid flag, [8..16) active records, [16..24) thick (warp, chord) pairs of the run
     if (e == cudaSuccess) e = cudaMemset(c->d_oob, 0, 32);
-    if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_exp_tab, (kExpTabEntries + kExpBigEntries) * sizeof(double));
+    if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_exp_tab, (kExpTabEntries + kExpBigEntries + 2 * kLogTabEntries) * sizeof(double));
     if (e == cudaSuccess) {
         double tab[kExpTabEntries];
         for (int j = 0; j < kExpTabEntries; ++j) tab[j] = pb_exp_tab_entry((double)exp2l((long double)j / kExpTabEntries), j);
@@ -189,6 +189,15 @@ int pb200_create(int device, pb200_ctx** out) {
         static double big[kExpBigEntries];
         for (int j = 0; j < kExpBigEntries; ++j) big[j] = pb_exp_big_entry((double)exp2l((long double)j / kExpBigEntries), j);
         e = cudaMemcpy(c->d_exp_tab + kExpTabEntries, big, sizeof big, cudaMemcpyHostToDevice);
+    }
+    if (e == cudaSuccess) {   // pb_log2_tab: {inv, -log2(inv)} per 1/256 of the mantissa range
+        static double lt[2 * kLogTabEntries];
+        for (int j = 0; j < kLogTabEntries; ++j) {
+            const double inv = 1.0 / (1.0 + (j + 0.5) / kLogTabEntries);
+            lt[2 * j] = inv;
+            lt[2 * j + 1] = (double)(-log2l((long double)inv));
+        }
+        e = cudaMemcpy(c->d_exp_tab + kExpTabEntries + kExpBigEntries, lt, sizeof lt, cudaMemcpyHostToDevice);
     }
     if (e != cudaSuccess) {
         int rc = fail(nullptr, PB200_ERR_CUDA, "pb200_create: %s", cudaGetErrorString(e));
@@ -576,6 +585,21 @@ static int set_scene_impl(pb200_ctx* c, const pb200_scene* s, int n_ranks, int r
         if (d.has_molecule) d.density_slot = n_density++;
     }
     h.n_atoms = n_atoms; h.n_mols = n_mols;
+    {   // absorbers of the run path (see DevScene::n_abs)
+        const char* ng = getenv("PB200_NO_GROUP");
+        const bool group = !(ng && ng[0] == '1');
+        h.n_abs = 0;
+        for (int i = 0; i < s->n_scenarios; ++i) {
+            const pb200_scenario& q = s->scenarios[i];
+            bool open = false;
+            for (int k = q.first_constituent; k < q.first_constituent + q.n_constituents; ++k) {
+                if (s->constituents[k].kind != 0) { open = false; continue; }
+                if (group && open) { h.abs_count[h.n_abs - 1] = k + 1 - h.abs_first[h.n_abs - 1]; continue; }
+                h.abs_first[h.n_abs] = k; h.abs_count[h.n_abs] = 1; ++h.n_abs;
+                open = true;
+            }
+        }
+    }
 
     c->general_path = (n_mols > 0) || (h.n_fstar > 0 && h.vsini != 0.0);
     {
@@ -653,7 +677,7 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     const int n_pairs = 2 * ((h.n_phi / 2 + 1) / 2) * h.n_rho;
     const int n_tiles = (c->general_path && h.mirror) ? (n_pairs + kChordTile - 1) / kChordTile : h.Mp / kChordTile;
     // wavelengths per CTA: kernel (m) 128; kernel (c') one window of 32 * WPT (WPT = 8, 4, 2 for <= 2, <= 4, more absorbers)
-    const int cta_wav = c->general_path ? 128 : 32 * (h.n_atoms <= 2 ? 8 : h.n_atoms <= 4 ? 4 : 2);
+    const int cta_wav = c->general_path ? 128 : 32 * (h.n_abs <= 2 ? 8 : h.n_abs <= 4 ? 4 : 2);
     const int64_t ctas = ((n_wav_sel + cta_wav - 1) / cta_wav) * n_phase;
     // Chord-axis splits: enough CTAs that the last wave is a small fraction of the run.  Kernel (m) does the
     // same work in every CTA and wants ~80 per SM; kernel (c') has one CTA per wavelength window, most of which
@@ -675,11 +699,11 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
 
     const size_t r_bytes = R_in_scratch ? (size_t)((n_out * sizeof(double) + 255) & ~255ll) : 0;
     const size_t part_bytes = prm.n_split > 1 ? (size_t)prm.n_split * n_out * sizeof(double) : 0;
-    const size_t nsig_bytes = c->general_path ? 0 : (size_t)h.n_atoms * n_out * sizeof(double);
-    prm.win = 32 * (h.n_atoms <= 2 ? 8 : h.n_atoms <= 4 ? 4 : 2);
+    const size_t nsig_bytes = c->general_path ? 0 : (size_t)h.n_abs * n_out * sizeof(double);
+    prm.win = 32 * (h.n_abs <= 2 ? 8 : h.n_abs <= 4 ? 4 : 2);
     prm.n_win = (int)((n_wav_sel + prm.win - 1) / prm.win);
     const size_t order_bytes = c->general_path ? 0 : (((size_t)n_phase * prm.n_win * sizeof(int) + 255) & ~size_t(255));
-    const size_t winmax_bytes = c->general_path ? 0 : (size_t)h.n_atoms * n_phase * prm.n_win * sizeof(double);
+    const size_t winmax_bytes = c->general_path ? 0 : (size_t)h.n_abs * n_phase * prm.n_win * sizeof(double);
     int rc = ensure_scratch(c, r_bytes + part_bytes + nsig_bytes + order_bytes + winmax_bytes + 256);
     if (rc) return rc;
     prm.R = R_in_scratch ? c->scratch : R_dev;
@@ -702,7 +726,7 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     const char* no_cull = getenv("PB200_NO_CULL");
     const bool cull = !(no_cull && no_cull[0] == '1');
     launch_column(c->d_scene, h.Mp, phase_lo, n_phase, c->d_oob, c->sm_count, c->stream, h.n_mols > 0,
-                  !c->general_path && cull);
+                  c->general_path ? 0 : (cull ? 1 : 2));
     c->launches += 1;
     if (!c->general_path) {   // chord records of kernel (c'), transparent chords culled
         PB_CUDA(c, launch_compact(c->d_scene, prm, cull, c->stream));
@@ -718,9 +742,9 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
         if (e != cudaSuccess) return fail(c, PB200_ERR_CUDA, "transit (general) launch: %s", cudaGetErrorString(e));
         c->launches += n_launch;
     } else {
-        cudaError_t e = launch_transit(c->d_scene, h.n_atoms, prm, c->stream);
-        if (e == cudaErrorInvalidValue && h.n_atoms > 12)
-            return fail(c, PB200_ERR_UNSUPPORTED, "%d atomic constituents; kernel (c') is compiled for <= 12", h.n_atoms);
+        cudaError_t e = launch_transit(c->d_scene, h.n_abs, prm, c->stream);
+        if (e == cudaErrorInvalidValue && h.n_abs > 12)
+            return fail(c, PB200_ERR_UNSUPPORTED, "%d absorbers (scenarios with atomic constituents); kernel (c') is compiled for <= 12", h.n_abs);
         if (e != cudaSuccess) return fail(c, PB200_ERR_CUDA, "transit launch: %s", cudaGetErrorString(e));
         c->launches += 1;
     }
@@ -1189,7 +1213,7 @@ extern "C" int pb200_column_density(pb200_ctx* c, double* ncol_host) {
     if (rc) return rc;
     const DevScene& h = c->h_scene;
     if (!ncol_host) return fail(c, PB200_ERR_INVALID, "ncol_host == NULL");
-    launch_column(c->d_scene, h.Mp, 0, h.n_orb, c->d_oob, c->sm_count, c->stream, h.n_mols > 0, false);
+    launch_column(c->d_scene, h.Mp, 0, h.n_orb, c->d_oob, c->sm_count, c->stream, h.n_mols > 0, 0);
     c->launches += 1;
     PB_CUDA(c, cudaGetLastError());
     rc = check_oob(c);
@@ -1207,7 +1231,7 @@ extern "C" int pb200_chord_masks(pb200_ctx* c, uint8_t* blocked_host, double* we
     int rc = check_scene(c);
     if (rc) return rc;
     const DevScene& h = c->h_scene;
-    launch_column(c->d_scene, h.Mp, 0, h.n_orb, c->d_oob, c->sm_count, c->stream, h.n_mols > 0, false);
+    launch_column(c->d_scene, h.Mp, 0, h.n_orb, c->d_oob, c->sm_count, c->stream, h.n_mols > 0, 0);
     c->launches += 1;
     PB_CUDA(c, cudaGetLastError());
     std::vector<double> w_in((size_t)h.n_orb * h.Mp), w_out(h.Mp);
@@ -1232,7 +1256,7 @@ extern "C" int pb200_optical_depth(pb200_ctx* c, int64_t wav_lo, int64_t wav_hi,
     DevBuf sig, tau;
     PB_CUDA(c, sig.alloc((size_t)(h.n_atoms ? h.n_atoms : 1) * h.n_orb * n_wav_sel * sizeof(double)));
     PB_CUDA(c, tau.alloc((size_t)n_c * n_wav_sel * sizeof(double)));
-    launch_column(c->d_scene, h.Mp, 0, h.n_orb, c->d_oob, c->sm_count, c->stream, h.n_mols > 0, false);
+    launch_column(c->d_scene, h.Mp, 0, h.n_orb, c->d_oob, c->sm_count, c->stream, h.n_mols > 0, 0);
     if (h.n_atoms) launch_sigma_u(c->d_scene, h.n_atoms, h.n_orb, wav_lo, n_wav_sel, sig.as<double>(), c->sm_count, c->stream);
     launch_optical_depth(c->d_scene, sig.as<double>(), n_c, wav_lo, n_wav_sel, tau.as<double>(), c->stream);
     c->launches += 2 + (h.n_atoms ? 1 : 0);

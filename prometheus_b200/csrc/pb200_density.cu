@@ -149,6 +149,9 @@ __device__ __forceinline__ double pb_column_sum(const DevScene& sc, const DevSce
     const double dy = y - S.centre_y[p];
     const double* __restrict__ P = pb_params(S, p);
     const double n0 = P[0] * amp;
+    const double* __restrict__ big = sc.exp_tab + kExpTabEntries;
+    const double2* __restrict__ ltab = reinterpret_cast<const double2*>(sc.exp_tab + kExpTabEntries + kExpBigEntries);
+    const double kLog2e = 1.4426950408889634;
     switch (S.type) {
         case PB200_SCN_BAROMETRIC: {   // n0 exp((R - r)/H) H(r - R), gasProperties.py:155-160
             const double R = P[1], invH = 1.0 / P[2], c2 = fma(dy, dy, z * z);
@@ -167,11 +170,13 @@ __device__ __forceinline__ double pb_column_sum(const DevScene& sc, const DevSce
             });
         }
         case PB200_SCN_POWERLAW: {     // n0 (R/r)^q H(r - R), gasProperties.py:240-243, :326-329, :371-373, :453-460
-            const double R = P[1], q = P[2], qlogR = q * log(R), hq = -0.5 * q, c2 = fma(dy, dy, z * z);
+            // (R/r)^q = exp2(q log2 R - (q/2) log2 r^2), table-driven (pb200_math.cuh); r < R <=> r^2 < R^2 up to a
+            // rounding of the boundary sample, which the reference's own sqrt does not define better
+            const double R = P[1], q = P[2], qlog2R = q * log2(R), hq = -0.5 * q, c2 = fma(dy, dy, z * z), R2 = R * R;
             return n0 * pb_sum4(n_x, [&](int ix) {
                 const double dx = xs[ix] - cx;
                 const double r2 = fma(dx, dx, c2);
-                return (sqrt(r2) < R) ? 0.0 : exp(fma(hq, log(r2), qlogR));
+                return (r2 < R2) ? 0.0 : pb_exp2_tab(big, fma(hq, pb_log2_tab(ltab, r2), qlog2R));
             });
         }
         case PB200_SCN_TORUS: {        // n0 exp(-((a - a_t)/4H)^2) exp(-(z/H)^2), gasProperties.py:506-515
@@ -180,7 +185,7 @@ __device__ __forceinline__ double pb_column_sum(const DevScene& sc, const DevSce
             return (n0 * ez) * pb_sum4(n_x, [&](int ix) {
                 const double dx = xs[ix] - cx;
                 const double qa = (sqrt(fma(dx, dx, dy2)) - at) * inv4H;
-                return exp(-(qa * qa));
+                return pb_exp2_tab(big, -(qa * qa) * kLog2e);
             });
         }
         default:
@@ -211,6 +216,7 @@ __device__ __forceinline__ double pb_column_bound(const DevScene& sc, const DevS
 }
 
 // run_mode = 0: every unblocked chord gets its exact column densities (inner seams of the API).
+// run_mode = 2 (pb200_run with PB200_NO_CULL=1): exact sums for every unblocked chord, absorbers as in run_mode 1.
 // run_mode = 1 (pb200_run): the sums that compact_kernel does not need are skipped --
 //   * the mirror chord of a pair whose primary chord is not blocked (sc.mirror);
 //   * chords whose upper bound sum_a bound_a * max_w sigma_a(p, w) is already below 2^-54: they are
@@ -235,7 +241,7 @@ column_thread_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase
         blocked = pb_blocked(sc, p, y, z);
         wv = blocked ? 0.0 : sc.w_out[m];
         need_sum = !blocked;
-        if (run_mode && sc.mirror && need_sum) {
+        if (run_mode == 1 && sc.mirror && need_sum) {
             const int n2 = sc.n_phi / 2, h = iphi / n2, i = iphi - h * n2, ip = n2 - 1 - i;
             if (i > ip) {   // mirror chord of the pair: needed only if the primary chord is blocked
                 const int jphi = h * n2 + ip;
@@ -245,19 +251,39 @@ column_thread_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase
     }
     sc.w_in[row] = wv;
     bool skip = false;
-    if (run_mode && need_sum) {   // transparent whatever the exact sums are?
-        double bound = 0.0;
-        for (int s = 0; s < sc.n_scen; ++s) {
-            const DevScenario& S = sc.scen[s];
-            const double ub = pb_column_bound(sc, S, p, S.amplitude ? S.amplitude[p] : 1.0, y, z);
-            for (int k = S.first_cons; k < S.first_cons + S.n_cons; ++k) {
-                const DevConstituent& C = sc.cons[k];
-                if (C.kind != 0) continue;
-                const double sm = __longlong_as_double((long long)sc.smax[(int64_t)C.atom_index * sc.n_orb + p]);
-                bound += (ub * fabs(C.chi)) * sc.delta_x * ((sm >= 0.0) ? sm : __longlong_as_double(0x7ff0000000000000ll));
+    if (run_mode) {
+        // The run path works with one absorber per group of atomic constituents that share a scenario
+        // (DevScene::n_abs): Ncol_g = sum_x n dx, the mixing ratios are in the group's cross section.
+        if (need_sum && run_mode == 1) {   // transparent whatever the exact sums are?
+            double bound = 0.0;
+            for (int g = 0; g < sc.n_abs; ++g) {
+                const DevScenario& S = sc.scen[sc.cons[sc.abs_first[g]].scenario];
+                const double ub = pb_column_bound(sc, S, p, S.amplitude ? S.amplitude[p] : 1.0, y, z);
+                const double sm = __longlong_as_double((long long)sc.smax[(int64_t)g * sc.n_orb + p]);
+                bound += ub * sc.delta_x * ((sm >= 0.0) ? sm : __longlong_as_double(0x7ff0000000000000ll));
             }
+            skip = bound < 5.5511151231257827e-17;   // 2^-54; NaN (0 * inf) -> not skipped
         }
-        skip = bound < 5.5511151231257827e-17;   // 2^-54; NaN (0 * inf) -> not skipped
+        int prev_scen = -1;
+        double sum = 0.0;
+        for (int g = 0; g < sc.n_abs; ++g) {
+            const int s = sc.cons[sc.abs_first[g]].scenario;
+            const DevScenario& S = sc.scen[s];
+            if (s != prev_scen) {   // (PB200_NO_GROUP: several absorbers of one scenario share the sum)
+                const double amp = S.amplitude ? S.amplitude[p] : 1.0;
+                sum = 0.0;
+                if (need_sum) sum = skip ? pb_column_bound(sc, S, p, amp, y, z) : pb_column_sum(sc, S, p, amp, y, z, oob_flag);
+                prev_scen = s;
+            }
+            const double col = sum * sc.delta_x;
+            sc.ncol[(int64_t)g * sc.n_orb * sc.Mp + row] = col;
+            double mx = (col > 0.0) ? col : 0.0;
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, d));
+            if ((threadIdx.x & 31) == 0 && mx > 0.0)
+                atomicMax(sc.nmax + (int64_t)g * sc.n_orb + p, (unsigned long long)__double_as_longlong(mx));
+        }
+        return;
     }
     for (int s = 0; s < sc.n_scen; ++s) {
         const DevScenario& S = sc.scen[s];
@@ -297,7 +323,7 @@ __global__ void __launch_bounds__(kCompactThreads) compact_kernel(const DevScene
     const DevScene& sc = *scp;
     const int phase_lo = prm.phase_lo;
     const int p = phase_lo + blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const int S = sc.n_atoms, R = pb_rec_stride(S);
+    const int S = sc.n_abs, R = pb_rec_stride(S);
     __shared__ double s_smax[16];
     __shared__ int s_warp[32];
     __shared__ double s_part[32];
@@ -386,18 +412,19 @@ __global__ void __launch_bounds__(kCompactThreads) compact_kernel(const DevScene
     const int n_rec = s_base;
     const int n_tiles = (n_rec + kChordTile - 1) / kChordTile;
     for (int i = n_rec * R + tid; i < n_tiles * kChordTile * R; i += kCompactThreads) rec_row[i] = 0.0;   // padding
-    // sum of the transparent weights and the thin totals, fixed order
+    // sum of the transparent weights and the thin totals, fixed order: warp sums -> s_red[k][warp], then warp k
+    // adds row k (one barrier pair for all seven sums)
+    __shared__ double s_red[7][32];
 #pragma unroll
     for (int k = 0; k < 7; ++k) {
         const double v = pb_warp_sum(k == 0 ? w0 : tt[k == 0 ? 0 : k - 1]);
-        __syncthreads();
-        if (lane == 0) s_part[wid] = v;
-        __syncthreads();
-        if (wid == 0) {
-            const double t = pb_warp_sum(s_part[lane]);
-            if (lane == 0) {
-                if (k == 0) sc.w0[p] = t; else sc.thin_tot[(int64_t)p * 8 + k - 1] = t;
-            }
+        if (lane == 0) s_red[k][wid] = v;
+    }
+    __syncthreads();
+    if (wid < 7) {
+        const double t = pb_warp_sum(s_red[wid][lane]);
+        if (lane == 0) {
+            if (wid == 0) sc.w0[p] = t; else sc.thin_tot[(int64_t)p * 8 + wid - 1] = t;
         }
     }
     if (tid == 0) {
@@ -540,12 +567,12 @@ void launch_fout_scalar(const DevScene* d_scene, cudaStream_t st) {
     fout_scalar_kernel<<<1, 1024, 0, st>>>(d_scene);
 }
 void launch_column(const DevScene* d_scene, int Mp, int phase_lo, int n_phase, int* oob, int sm_count,
-                   cudaStream_t st, bool has_molecules, bool run_mode) {
+                   cudaStream_t st, bool has_molecules, int run_mode) {
     if (has_molecules) {   // density rows n(c, x) are needed by kernel (m): warp per chord, coalesced row stores
         column_kernel<<<grid_for_warps((int64_t)n_phase * Mp, sm_count), 256, 0, st>>>(d_scene, phase_lo, n_phase, oob);
     } else {
         const int64_t n = (int64_t)n_phase * Mp;
-        column_thread_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(d_scene, phase_lo, n_phase, oob, run_mode ? 1 : 0);
+        column_thread_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(d_scene, phase_lo, n_phase, oob, run_mode);
     }
 }
 constexpr int kMaxWindows = 8192;

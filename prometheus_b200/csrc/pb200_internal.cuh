@@ -43,6 +43,12 @@ struct DevScene {
     int Mp;           // M padded to a multiple of kChordTile
     int fout_per_wav; // 1: fout is [n_wav] (per-chord F* table with stellar rotation), 0: fout is [1]
     int moon_R_per_phase;   // 1: moon_R is [n_moons][n_orb] (retrieval batch), 0: [n_moons]
+    // Absorbers of the run path (atomic scenes): the atomic constituents of ONE scenario share its density, so
+    // tau = sum_k Ncol_k sigma_k = (sum_x n dx) * sum_k chi_k sigma_k -- one absorber per scenario with the
+    // effective cross section sum_k chi_k sigma_k(p, lambda) instead of one per constituent (C5: 2 -> 1, C2a: 8 -> 1).
+    // abs_first/abs_count: constituent range of absorber g.  PB200_NO_GROUP=1: one absorber per constituent.
+    int n_abs;
+    int abs_first[kMaxConstituents], abs_count[kMaxConstituents];
     int n_orb_model;        // phases per model (== n_orb without a batch); row m*n_orb_model + p is model m, phase p
     int64_t n_wav;
     double delta_x, star_R, clv_u1, clv_u2, vsini, planet_R;
@@ -62,7 +68,8 @@ struct DevScene {
     // chord records of kernel (c'): [n_orb][<= Mp][pb_rec_stride(n_atoms)] = {w_in, w_in c1, w_in c2, Ncol_0 .. Ncol_{S-1}[, 0]}, one TMA
     // bulk copy per 256-chord tile
     double* rec;
-    const double* exp_tab;   // [256] 2^(j/256) then [4096] 2^(j/4096), correctly rounded, high words biased (pb200_math.cuh)
+    const double* exp_tab;   // [256] 2^(j/256) then [4096] 2^(j/4096), correctly rounded, high words biased (pb200_math.cuh),
+                             // then [256] {1/m_j, -log2(1/m_j)} of pb_log2_tab
     unsigned long long* nmax;   // [n_atoms][n_orb] bit pattern of max_m Ncol (>= 0), set by kernel (a')
     // transparent-chord culling (compact_kernel): a chord whose optical depth stays below 2^-54 at every
     // wavelength of the run contributes exactly w_in (exp(-tau) rounds to 1.0), so only the other

@@ -168,6 +168,50 @@ __device__ __forceinline__ double pb_exp_big_load(uint32_t tab_base, int k) {
     return __hiloint2double(t_hi + (k << kExpBigShift), t_lo);
 }
 
+// ---------------------------------------------------------------------------------------------
+// Table-driven log2 / exp2 from GLOBAL memory (L1-resident: 4 KB + 32 KB), for the x-sums of the column kernel,
+// where (R/r)^q = exp2(q log2 R - (q/2) log2 r^2) per line-of-sight sample is the cost (libdevice: sqrt + log + exp
+// ~ 60 FP64 instructions; this form: 10 + 9).
+//   log2: r2 = 2^e m, m in [1, 2); idx = top 8 mantissa bits; {inv, l2} = table[idx] with inv ~ 1/m_centre and
+//         l2 = -log2(inv) (long double on the host); u = fma(m, inv, -1), |u| <= 2^-9; log2(1+u) by a degree-7
+//         polynomial (truncation u^8/8 < 1e-22).  Absolute error ~ ulp(e + l2)/2 <= 7e-15 for r2 < 2^128 -- the
+//         same as libdevice's log at that magnitude.
+//   exp2: v = 4096 y, k = rint(v), r = v - k; 2^(k/4096) from the big table of kernel (c') (entries pre-biased, see
+//         pb_exp_big_entry) times a CUBIC in r (truncation (ln2/4096)^4/24/16 = 2e-18).  y < -1020: exact exp2()
+//         (denormal tails of a Gaussian stay what they are).
+// ---------------------------------------------------------------------------------------------
+constexpr int kLogTabEntries = 256;
+constexpr double kExpBigC3 = 8.0768402961349e-13;            // (ln 2 / 4096)^3 / 6
+
+__device__ __forceinline__ double pb_log2_tab(const double2* __restrict__ ltab, double x) {
+    const int hi = __double2hiint(x);
+    const int e = (hi >> 20) - 1023;
+    const double2 t = __ldg(ltab + ((hi >> 12) & 255));
+    const double m = __hiloint2double((hi & 0x000FFFFF) | 0x3FF00000, __double2loint(x));
+    const double u = fma(m, t.x, -1.0);
+    double p = 2.0609929155555190e-01;                       //  1/(7 ln2)
+    p = fma(p, u, -2.4044917348149410e-01);                  // -1/(6 ln2)
+    p = fma(p, u, 2.8853900817779268e-01);                   //  1/(5 ln2)
+    p = fma(p, u, -3.6067376022224085e-01);                  // -1/(4 ln2)
+    p = fma(p, u, 4.8089834696298783e-01);                   //  1/(3 ln2)
+    p = fma(p, u, -7.2134752044448170e-01);                  // -1/(2 ln2)
+    p = fma(p, u, 1.4426950408889634e+00);                   //  1/ln2
+    return fma(u, p, (double)e + t.y);
+}
+
+__device__ __forceinline__ double pb_exp2_tab(const double* __restrict__ big, double y) {
+    if (y < -1020.0) return exp2(y);
+    const double t = fma(y, 4096.0, kExpMagic);
+    const int k = __double2loint(t);
+    const double kf = t - kExpMagic;
+    const double r = fma(y, 4096.0, -kf);
+    const double T0 = __ldg(big + (k & (kExpBigEntries - 1)));
+    const double T = __hiloint2double(__double2hiint(T0) + (k << kExpBigShift), __double2loint(T0));
+    double p = fma(r, kExpBigC3, kExpBigC2);
+    p = fma(p, r, kExpBigC1);
+    return fma(T, r * p, T);
+}
+
 // exp(a) for |a| <= 700 (same kernel as pb_exp_neg, two-sided); used for 10**v = exp(v ln10) of the
 // molecular tables, where |v| <= 50 keeps the extra rounding of v*ln10 below 1e-14 relative.
 __device__ __forceinline__ double pb_exp(double a) {

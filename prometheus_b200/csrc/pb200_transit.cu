@@ -78,15 +78,17 @@ __global__ void __launch_bounds__(256) sigma_phase_kernel(const DevScene* __rest
     if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) { sc.stat[1] = 0ull; sc.stat[2] = 0ull; }   // run statistics
     const double lam = live ? __ldg(sc.wavelength + pb_wav_index(prm, wi)) : 0.0;
     const int wpw = prm.win / 32;   // warps per window: this 256-wavelength CTA covers 8 / wpw whole windows
-    int a = 0;
-    for (int k = 0; k < sc.n_cons; ++k) {
-        const DevConstituent& C = sc.cons[k];
-        if (C.kind != 0) continue;
+    for (int a = 0; a < sc.n_abs; ++a) {   // absorber = the atomic constituents of one scenario (DevScene::n_abs)
         unsigned long long bits = 0ull;
         double ns_abs = 0.0;
         if (live) {
-            const double shift = __ldg(sc.scen[C.scenario].shift + p);
-            const double v = pb_interp_log(C.tab_x, C.tab_y, C.n_tab, shift * lam, C.offset);   // :917, :950-951
+            const int k0 = sc.abs_first[a];
+            const double sl = __ldg(sc.scen[sc.cons[k0].scenario].shift + p) * lam;             // :917
+            double v = 0.0;
+            for (int k = k0; k < k0 + sc.abs_count[a]; ++k) {
+                const DevConstituent& C = sc.cons[k];
+                v = fma(C.chi, pb_interp_log(C.tab_x, C.tab_y, C.n_tab, sl, C.offset), v);      // :940 chi, :950-951 sigma
+            }
             const double ns = -v * kExpBigScale;
             prm.nsig[((int64_t)a * prm.n_phase + pi) * prm.n_wav_sel + wi] = ns;
             bits = (v >= 0.0) ? (unsigned long long)__double_as_longlong(v) : ~0ull;   // negative or NaN: never cull
@@ -111,7 +113,6 @@ __global__ void __launch_bounds__(256) sigma_phase_kernel(const DevScene* __rest
                 prm.winmax[((int64_t)a * prm.n_phase + pi) * prm.n_win + window] = mx;
             }
         }
-        ++a;
     }
 }
 

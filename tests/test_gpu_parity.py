@@ -391,3 +391,27 @@ def test_block_cyclic_tiles_reassemble_R(name, n_ranks, transits, ctx):
         torch.cuda.synchronize()
         out[:, idx] = buf.cpu().numpy().reshape(n_orb, idx.size)
     assert np.max(np.abs(out - R)) < 5e-14
+
+
+def test_absorber_grouping_leaves_R_unchanged(nist_rows, golden, monkeypatch):
+    """One absorber per scenario (effective cross section sum_k chi_k sigma_k) against one per constituent
+    (PB200_NO_GROUP=1): the same tau up to the order of two roundings.  C5s: Fe I + Fe II in one power-law
+    atmosphere; HYDs: two scenarios with one constituent each (nothing to merge, identical bits)."""
+    from prometheus_b200 import scene
+    ctx = host.get_context(0)
+    for name, merged in (("C5s", True), ("HYDs", False)):
+        tr = builder.build_transit(workloads.get(name), nist_rows=nist_rows)
+        out = {}
+        for flag in ("0", "1"):
+            monkeypatch.setenv("PB200_NO_GROUP", flag)
+            sc, keep, info = scene.flatten(tr)
+            ctx.set_scene(sc, keep)
+            out[flag], _ = ctx.run(0, info["n_orb"], 0, info["n_wav"])
+        monkeypatch.delenv("PB200_NO_GROUP")
+        if merged:
+            assert np.max(np.abs(out["0"] - out["1"])) < 5e-14
+        else:
+            assert np.array_equal(out["0"], out["1"])
+        g = golden(name)
+        ok, worst = excess_depth_ok(out["0"], g["R"], g["R0"])
+        assert ok, f"{name}: err/bound {worst}"
