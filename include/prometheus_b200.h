@@ -237,6 +237,9 @@ int pb200_last_timing(pb200_ctx* ctx, pb200_timing* timing);
 /* ---- inner seams, same arithmetic as the fused path, materialised ------------------------ */
 /* <Scenario>.calculateNumberDensity on the whole chord grid -> out[n_c*n_x] (chord-major)   */
 int pb200_number_density(pb200_ctx* ctx, int scenario, double* n_host);
+/* the same into device memory (n_dev[n_c*n_x]), not synchronised: kernel (a) on its own, the form the
+   north star calls bandwidth-bound                                                              */
+int pb200_number_density_device(pb200_ctx* ctx, int scenario, double* n_dev);
 /* same for caller-supplied chords: y,z = rho*sin(phi), rho*cos(phi); cx,cy = density centre;
    amp = NULL or per-chord multiplier.  out[n*n_x]                                           */
 int pb200_number_density_chords(pb200_ctx* ctx, int scenario, int64_t n, const double* y,

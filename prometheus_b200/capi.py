@@ -25,7 +25,7 @@ EXPORTS = [
     "pb200_voigt_profile", "pb200_molecular_sigma", "pb200_write_output", "pb200_probe_fp64",
     "pb200_set_models", "pb200_lightcurve", "pb200_run_batch",
     "pb200_host_register", "pb200_host_unregister", "pb200_run_scatter", "pb200_sync",
-    "pb200_set_scene_sharded", "pb200_table_regions",
+    "pb200_set_scene_sharded", "pb200_table_regions", "pb200_number_density_device",
 ]
 
 SCN_BAROMETRIC, SCN_HYDROSTATIC, SCN_POWERLAW, SCN_TORUS, SCN_SERPENS = range(5)
@@ -149,6 +149,7 @@ def load():
         "pb200_cyclic_count": (C.c_int64, [i64, i64, i32, i32]),
         "pb200_last_timing": (C.c_int, [vp, C.POINTER(Timing)]),
         "pb200_number_density": (C.c_int, [vp, i32, c_double_p]),
+        "pb200_number_density_device": (C.c_int, [vp, i32, vp]),
         "pb200_number_density_chords": (C.c_int, [vp, i32, i64] + [c_double_p] * 6),
         "pb200_column_density": (C.c_int, [vp, c_double_p]),
         "pb200_chord_masks": (C.c_int, [vp, C.POINTER(C.c_uint8), c_double_p]),
@@ -354,6 +355,9 @@ class Context:
     def synchronize(self):
         """Wait for everything enqueued on this context (a pb200_last_timing round trip is not needed for that)."""
         self.check(self.lib.pb200_sync(self.handle))
+
+    def number_density_device(self, scenario: int, dev_ptr: int):
+        self.check(self.lib.pb200_number_density_device(self.handle, scenario, C.c_void_p(dev_ptr)))
 
     def last_timing(self) -> dict:
         t = Timing()

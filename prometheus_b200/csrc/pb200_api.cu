@@ -24,6 +24,7 @@ void launch_column(const DevScene*, int Mp, int phase_lo, int n_phase, int* oob,
                    int run_mode);
 void launch_number_density_grid(const DevScene*, int64_t n_chords, int scenario, double* out, int* oob, int sm_count,
                                 cudaStream_t);
+void launch_number_density_thread(const DevScene*, int64_t n_chords, int scenario, double* out, cudaStream_t);
 void launch_number_density_chords(const DevScene*, int scenario, int64_t n, const double* y, const double* z,
                                   const double* cx, const double* cy, const double* amp, double* out, int* oob,
                                   int sm_count, cudaStream_t);
@@ -1173,6 +1174,21 @@ extern "C" int pb200_number_density(pb200_ctx* c, int scenario, double* n_host) 
     rc = check_oob(c);
     if (rc) return rc;
     return download(c, n_host, out.p, (size_t)n_c * h.n_x * sizeof(double));
+}
+
+// the same into device memory, not synchronised: the bandwidth measurement of kernel (a) (bench.py)
+extern "C" int pb200_number_density_device(pb200_ctx* c, int scenario, double* n_dev) {
+    int rc = check_scene(c);
+    if (rc) return rc;
+    const DevScene& h = c->h_scene;
+    if (scenario < 0 || scenario >= h.n_scen || !n_dev) return fail(c, PB200_ERR_INVALID, "bad scenario index %d", scenario);
+    if (h.scen[scenario].type == PB200_SCN_SERPENS)
+        launch_number_density_grid(c->d_scene, (int64_t)h.M * h.n_orb, scenario, n_dev, c->d_oob, c->sm_count, c->stream);
+    else
+        launch_number_density_thread(c->d_scene, (int64_t)h.M * h.n_orb, scenario, n_dev, c->stream);
+    c->launches += 1;
+    PB_CUDA(c, cudaGetLastError());
+    return PB200_OK;
 }
 
 extern "C" int pb200_number_density_chords(pb200_ctx* c, int scenario, int64_t n, const double* y, const double* z,

@@ -135,16 +135,14 @@ __device__ __forceinline__ double pb_sum4(int n, F term) {
     return (a0 + a1) + (a2 + a3);
 }
 
-__device__ __forceinline__ double pb_column_sum(const DevScene& sc, const DevScenario& S, int p, double amp, double y,
-                                                double z, int* oob_flag) {
-    const int n_x = sc.n_x;
+// The analytic scenarios along one chord: use(prefactor, term) is called once with the per-chord prefactor and a
+// functor term(ix) such that n(x_ix) = prefactor * term(ix) -- everything that does not depend on x is hoisted
+// (torus: exp(-(z/H)^2); power law: q log2 R), exp / pow go through the L1-resident tables of pb200_math.cuh.
+// Shared by the fused x-sum (kernel (a'), use = pb_sum4) and the materialising kernel (a) (use = store).
+template <class Use>
+__device__ __forceinline__ double pb_chord_terms(const DevScene& sc, const DevScenario& S, int p, double amp, double y,
+                                                 double z, Use&& use) {
     const double* __restrict__ xs = sc.x;
-    if (S.type == PB200_SCN_SERPENS) {
-        int oob = 0;
-        const double sum = pb_sum4(n_x, [&](int ix) { return pb_trilinear(S, xs[ix], y, z, &oob); });
-        if (oob) *oob_flag = 1;
-        return sum * amp;
-    }
     const double cx = S.centre_x[p];
     const double dy = y - S.centre_y[p];
     const double* __restrict__ P = pb_params(S, p);
@@ -154,26 +152,26 @@ __device__ __forceinline__ double pb_column_sum(const DevScene& sc, const DevSce
     const double kLog2e = 1.4426950408889634;
     switch (S.type) {
         case PB200_SCN_BAROMETRIC: {   // n0 exp((R - r)/H) H(r - R), gasProperties.py:155-160
-            const double R = P[1], invH = 1.0 / P[2], c2 = fma(dy, dy, z * z);
-            return n0 * pb_sum4(n_x, [&](int ix) {
+            const double R = P[1], invH = kLog2e / P[2], c2 = fma(dy, dy, z * z);
+            return use(n0, [&](int ix) {
                 const double dx = xs[ix] - cx;
                 const double r = sqrt(fma(dx, dx, c2));
-                return (r < R) ? 0.0 : exp((R - r) * invH);
+                return (r < R) ? 0.0 : pb_exp2_tab(big, (R - r) * invH);
             });
         }
         case PB200_SCN_HYDROSTATIC: {  // n0 exp(J(r) H(r - R) - J(R)), gasProperties.py:197-203
             const double R = P[1], jc = P[2] / P[3], j0 = jc / R, c2 = fma(dy, dy, z * z);
-            return n0 * pb_sum4(n_x, [&](int ix) {
+            return use(n0, [&](int ix) {
                 const double dx = xs[ix] - cx;
                 const double r = sqrt(fma(dx, dx, c2));
-                return exp(((r < R) ? 0.0 : jc / r) - j0);
+                return pb_exp2_tab(big, (((r < R) ? 0.0 : jc / r) - j0) * kLog2e);
             });
         }
         case PB200_SCN_POWERLAW: {     // n0 (R/r)^q H(r - R), gasProperties.py:240-243, :326-329, :371-373, :453-460
-            // (R/r)^q = exp2(q log2 R - (q/2) log2 r^2), table-driven (pb200_math.cuh); r < R <=> r^2 < R^2 up to a
-            // rounding of the boundary sample, which the reference's own sqrt does not define better
+            // (R/r)^q = exp2(q log2 R - (q/2) log2 r^2); r < R <=> r^2 < R^2 up to a rounding of the boundary sample,
+            // which the reference's own sqrt does not define better
             const double R = P[1], q = P[2], qlog2R = q * log2(R), hq = -0.5 * q, c2 = fma(dy, dy, z * z), R2 = R * R;
-            return n0 * pb_sum4(n_x, [&](int ix) {
+            return use(n0, [&](int ix) {
                 const double dx = xs[ix] - cx;
                 const double r2 = fma(dx, dx, c2);
                 return (r2 < R2) ? 0.0 : pb_exp2_tab(big, fma(hq, pb_log2_tab(ltab, r2), qlog2R));
@@ -182,7 +180,7 @@ __device__ __forceinline__ double pb_column_sum(const DevScene& sc, const DevSce
         case PB200_SCN_TORUS: {        // n0 exp(-((a - a_t)/4H)^2) exp(-(z/H)^2), gasProperties.py:506-515
             const double at = P[1], inv4H = 1.0 / (4.0 * P[2]), qz = z / P[2], dy2 = dy * dy;
             const double ez = exp(-(qz * qz));
-            return (n0 * ez) * pb_sum4(n_x, [&](int ix) {
+            return use(n0 * ez, [&](int ix) {
                 const double dx = xs[ix] - cx;
                 const double qa = (sqrt(fma(dx, dx, dy2)) - at) * inv4H;
                 return pb_exp2_tab(big, -(qa * qa) * kLog2e);
@@ -191,6 +189,19 @@ __device__ __forceinline__ double pb_column_sum(const DevScene& sc, const DevSce
         default:
             return 0.0;
     }
+}
+
+__device__ __forceinline__ double pb_column_sum(const DevScene& sc, const DevScenario& S, int p, double amp, double y,
+                                                double z, int* oob_flag) {
+    const int n_x = sc.n_x;
+    if (S.type == PB200_SCN_SERPENS) {
+        const double* __restrict__ xs = sc.x;
+        int oob = 0;
+        const double sum = pb_sum4(n_x, [&](int ix) { return pb_trilinear(S, xs[ix], y, z, &oob); });
+        if (oob) *oob_flag = 1;
+        return sum * amp;
+    }
+    return pb_chord_terms(sc, S, p, amp, y, z, [&](double pre, auto term) { return pre * pb_sum4(n_x, term); });
 }
 
 // Upper bound of the x-sum of one scenario on a chord (every term <= its value at dx = 0, the closest
@@ -511,6 +522,48 @@ number_density_grid_kernel(const DevScene* __restrict__ scp, int scenario, doubl
     }
 }
 
+// (a) fast form for the analytic scenarios: one THREAD per chord (per-chord factors hoisted once, all lanes busy
+// whatever n_x is), 16 samples at a time staged through shared memory so that the warp writes whole 128-byte
+// segments: a store instruction covers two rows x 16 doubles.  HBM-bound by construction (8 B per sample).
+constexpr int kDensChunk = 16;
+__global__ void __launch_bounds__(128)
+number_density_thread_kernel(const DevScene* __restrict__ scp, int scenario, double* __restrict__ out) {
+    const DevScene& sc = *scp;
+    const DevScenario& S = sc.scen[scenario];
+    __shared__ double tile[4][32][kDensChunk + 1];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int64_t n_chords = (int64_t)sc.M * sc.n_orb;
+    const int64_t c0 = ((int64_t)blockIdx.x * 4 + wid) * 32;
+    if (c0 >= n_chords) return;
+    const int64_t c = c0 + lane;
+    const bool have = c < n_chords;
+    const int64_t cc = have ? c : n_chords - 1;
+    const int m = (int)(cc / sc.n_orb), p = (int)(cc % sc.n_orb);
+    const int iphi = m / sc.n_rho, irho = m - iphi * sc.n_rho;
+    const double rho = sc.rho[irho];
+    const double y = __dmul_rn(rho, sc.sin_phi[iphi]);
+    const double z = __dmul_rn(rho, sc.cos_phi[iphi]);
+    const double amp = S.amplitude ? S.amplitude[p] : 1.0;
+    const int n_x = sc.n_x;
+    double (*my)[kDensChunk + 1] = tile[wid];
+    const int rows = (int)((n_chords - c0 < 32) ? n_chords - c0 : 32);
+    pb_chord_terms(sc, S, p, amp, y, z, [&](double pre, auto term) {
+        for (int x0 = 0; x0 < n_x; x0 += kDensChunk) {
+            const int nk = (n_x - x0 < kDensChunk) ? n_x - x0 : kDensChunk;
+#pragma unroll 4
+            for (int k = 0; k < nk; ++k) my[lane][k] = pre * term(x0 + k);
+            __syncwarp();
+            const int col = lane & 15, half = lane >> 4;
+            if (col < nk) {
+#pragma unroll 4
+                for (int r = half; r < rows; r += 2) out[(c0 + r) * n_x + x0 + col] = my[r][col];
+            }
+            __syncwarp();
+        }
+        return 0.0;
+    });
+}
+
 // same for caller-supplied chords (API parity with <Scenario>.calculateNumberDensity(x, phi, rho, orb))
 __global__ void __launch_bounds__(256)
 number_density_chords_kernel(const DevScene* __restrict__ scp, int scenario, int64_t n,
@@ -591,6 +644,9 @@ cudaError_t launch_compact(const DevScene* d_scene, const TransitParams& prm, bo
 void launch_number_density_grid(const DevScene* d_scene, int64_t n_chords, int scenario, double* out,
                                 int* oob, int sm_count, cudaStream_t st) {
     number_density_grid_kernel<<<grid_for_warps(n_chords, sm_count), 256, 0, st>>>(d_scene, scenario, out, oob);
+}
+void launch_number_density_thread(const DevScene* d_scene, int64_t n_chords, int scenario, double* out, cudaStream_t st) {
+    number_density_thread_kernel<<<(unsigned)((n_chords + 127) / 128), 128, 0, st>>>(d_scene, scenario, out);
 }
 void launch_number_density_chords(const DevScene* d_scene, int scenario, int64_t n, const double* y,
                                   const double* z, const double* cx, const double* cy, const double* amp,
