@@ -547,6 +547,29 @@ def run_b200(args):
         "setup": {"seconds": t_setup, "voigt_last_table_ms": voigt["transit_ms"], "voigt_last_table_evals": voigt["samples"]},
     }
 
+    # ---- kernel (a) on its own: the materialised number density n(chord, x) of the headline scene (N = 1) ------
+    if world == 1:
+        with torch.cuda.stream(stream):
+            ctx.set_scene(sc, keep)
+            n_dens = n_c * info["n_x"]
+            dens = torch.empty(n_dens, dtype=torch.float64, device=dev)
+            d_ms, f_ms = [], []
+            for i in range(8):
+                flush.zero_()
+                a, b, c2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+                a.record(); ctx.number_density_device(0, dens.data_ptr()); b.record()
+                dens.fill_(0.0); c2.record()                       # write-only roofline of the same buffer
+                torch.cuda.synchronize()
+                if i >= 3:
+                    d_ms.append(a.elapsed_time(b)); f_ms.append(b.elapsed_time(c2))
+            d_t, f_t = float(np.mean(d_ms)), float(np.mean(f_ms))
+            out["kernel_a"] = {"kernel": "number_density_thread_kernel (a: n(chord, x) materialised, scenario 0)",
+                               "samples": n_dens, "ms": d_t, "bound": "hbm", "achieved": 8.0 * n_dens / d_t / 1e6,
+                               "unit": "GB/s", "peak": hbm_peak, "frac": 8.0 * n_dens / d_t / 1e6 / hbm_peak,
+                               "write_only_fill_GBs": 8.0 * n_dens / f_t / 1e6,
+                               "convention": "8 B per chord*x sample (one f64 store, SURVEY 8(d) row (a))"}
+            del dens
+
     # ---- the other BASELINE configs, device-resident, few steps (N = 1 only; parity is in tests/) -----------
     if world == 1 and args.others:
         out["other_workloads"] = {}

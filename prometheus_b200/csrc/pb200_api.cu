@@ -24,7 +24,7 @@ void launch_column(const DevScene*, int Mp, int phase_lo, int n_phase, int* oob,
                    int run_mode);
 void launch_number_density_grid(const DevScene*, int64_t n_chords, int scenario, double* out, int* oob, int sm_count,
                                 cudaStream_t);
-void launch_number_density_thread(const DevScene*, int64_t n_chords, int scenario, double* out, cudaStream_t);
+void launch_number_density_thread(const DevScene*, int64_t n_chords, int n_x, int scenario, double* out, int sm_count, cudaStream_t);
 void launch_number_density_chords(const DevScene*, int scenario, int64_t n, const double* y, const double* z,
                                   const double* cx, const double* cy, const double* amp, double* out, int* oob,
                                   int sm_count, cudaStream_t);
@@ -1185,7 +1185,7 @@ extern "C" int pb200_number_density_device(pb200_ctx* c, int scenario, double* n
     if (h.scen[scenario].type == PB200_SCN_SERPENS)
         launch_number_density_grid(c->d_scene, (int64_t)h.M * h.n_orb, scenario, n_dev, c->d_oob, c->sm_count, c->stream);
     else
-        launch_number_density_thread(c->d_scene, (int64_t)h.M * h.n_orb, scenario, n_dev, c->stream);
+        launch_number_density_thread(c->d_scene, (int64_t)h.M * h.n_orb, h.n_x, scenario, n_dev, c->sm_count, c->stream);
     c->launches += 1;
     PB_CUDA(c, cudaGetLastError());
     return PB200_OK;

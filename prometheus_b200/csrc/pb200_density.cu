@@ -201,7 +201,9 @@ __device__ __forceinline__ double pb_column_sum(const DevScene& sc, const DevSce
         if (oob) *oob_flag = 1;
         return sum * amp;
     }
-    return pb_chord_terms(sc, S, p, amp, y, z, [&](double pre, auto term) { return pre * pb_sum4(n_x, term); });
+    return pb_chord_terms(sc, S, p, amp, y, z, [&](double pre, auto term) {
+        return (pre == 0.0) ? 0.0 : pre * pb_sum4(n_x, term);   // terms are finite and <= 1
+    });
 }
 
 // Upper bound of the x-sum of one scenario on a chord (every term <= its value at dx = 0, the closest
@@ -547,11 +549,17 @@ number_density_thread_kernel(const DevScene* __restrict__ scp, int scenario, dou
     const int n_x = sc.n_x;
     double (*my)[kDensChunk + 1] = tile[wid];
     const int rows = (int)((n_chords - c0 < 32) ? n_chords - c0 : 32);
+    // blockIdx.y splits the x axis in whole chunks: enough tasks that the last wave is short
+    const int n_chunks = (n_x + kDensChunk - 1) / kDensChunk;
+    const int x_lo = (int)((int64_t)blockIdx.y * n_chunks / gridDim.y) * kDensChunk;
+    int x_hi = (int)((int64_t)(blockIdx.y + 1) * n_chunks / gridDim.y) * kDensChunk;
+    if (x_hi > n_x) x_hi = n_x;
     pb_chord_terms(sc, S, p, amp, y, z, [&](double pre, auto term) {
-        for (int x0 = 0; x0 < n_x; x0 += kDensChunk) {
-            const int nk = (n_x - x0 < kDensChunk) ? n_x - x0 : kDensChunk;
+        const bool dead = (pre == 0.0);   // every term is finite and <= 1: the whole row is exactly 0 (torus far off the plane)
+        for (int x0 = x_lo; x0 < x_hi; x0 += kDensChunk) {
+            const int nk = (x_hi - x0 < kDensChunk) ? x_hi - x0 : kDensChunk;
 #pragma unroll 4
-            for (int k = 0; k < nk; ++k) my[lane][k] = pre * term(x0 + k);
+            for (int k = 0; k < nk; ++k) my[lane][k] = dead ? 0.0 : pre * term(x0 + k);
             __syncwarp();
             const int col = lane & 15, half = lane >> 4;
             if (col < nk) {
@@ -645,8 +653,14 @@ void launch_number_density_grid(const DevScene* d_scene, int64_t n_chords, int s
                                 int* oob, int sm_count, cudaStream_t st) {
     number_density_grid_kernel<<<grid_for_warps(n_chords, sm_count), 256, 0, st>>>(d_scene, scenario, out, oob);
 }
-void launch_number_density_thread(const DevScene* d_scene, int64_t n_chords, int scenario, double* out, cudaStream_t st) {
-    number_density_thread_kernel<<<(unsigned)((n_chords + 127) / 128), 128, 0, st>>>(d_scene, scenario, out);
+void launch_number_density_thread(const DevScene* d_scene, int64_t n_chords, int n_x, int scenario, double* out, int sm_count,
+                                  cudaStream_t st) {
+    const int64_t blocks = (n_chords + 127) / 128;
+    const int n_chunks = (n_x + kDensChunk - 1) / kDensChunk;
+    int64_t xs = ((int64_t)sm_count * 9 * 8 + blocks - 1) / blocks;   // ~8 tasks per resident block slot
+    if (xs > n_chunks) xs = n_chunks;
+    if (xs < 1) xs = 1;
+    number_density_thread_kernel<<<dim3((unsigned)blocks, (unsigned)xs), 128, 0, st>>>(d_scene, scenario, out);
 }
 void launch_number_density_chords(const DevScene* d_scene, int scenario, int64_t n, const double* y,
                                   const double* z, const double* cx, const double* cy, const double* amp,

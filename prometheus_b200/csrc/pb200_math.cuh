@@ -200,7 +200,7 @@ __device__ __forceinline__ double pb_log2_tab(const double2* __restrict__ ltab, 
 }
 
 __device__ __forceinline__ double pb_exp2_tab(const double* __restrict__ big, double y) {
-    if (y < -1020.0) return exp2(y);
+    if (y < -1020.0) return (y < -1076.0) ? 0.0 : exp2(y);   // below 2^-1075 the result rounds to 0; denormals: exact exp2
     const double t = fma(y, 4096.0, kExpMagic);
     const int k = __double2loint(t);
     const double kf = t - kExpMagic;

@@ -34,3 +34,19 @@ for name, spec in variants():
     zeros_ok = bool(np.array_equal(got == 0.0, ref == 0.0))
     print(f"   vs exact kernel: max rel diff {rel:.2e}, zero pattern equal {zeros_ok}")
     print(f"{name}: {n:.3e} samples, {t:.4f} ms, {8 * n / t / 1e6:.0f} GB/s, sum {float(out.sum()):.6e}")
+# write-only roofline of this box: torch fill of the same 367 MB buffer, and a device copy
+ms = []
+src = torch.empty_like(out)
+for i in range(8):
+    flush.zero_()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record(); out.fill_(1.0); b.record(); torch.cuda.synchronize()
+    if i >= 3: ms.append(a.elapsed_time(b))
+print(f"fill_ of {out.numel() * 8 / 1e6:.0f} MB: {np.mean(ms):.4f} ms, {out.numel() * 8 / np.mean(ms) / 1e6:.0f} GB/s written")
+ms = []
+for i in range(8):
+    flush.zero_()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record(); out.copy_(src); b.record(); torch.cuda.synchronize()
+    if i >= 3: ms.append(a.elapsed_time(b))
+print(f"copy_ of {out.numel() * 8 / 1e6:.0f} MB: {np.mean(ms):.4f} ms, {2 * out.numel() * 8 / np.mean(ms) / 1e6:.0f} GB/s read+written")
