@@ -202,14 +202,7 @@ class AtmosphericConstituent:
     def getLineParameters(self, wavelength):
         """(lambda0 [cm], gamma = A/(4 pi), f) of this species' lines strictly inside the range
         (gasProperties.py:640-670)."""
-        rows = host.LINE_LIST
-        if rows.shape[0] == 0:
-            raise RuntimeError("line list is empty: call prometheus_b200.host.set_line_list(...) first")
-        mine = (rows[:, 0] == self.species.element) & (rows[:, 1] == self.species.ionizationState)
-        mine &= (rows[:, 2] != "") & (rows[:, 3] != "") & (rows[:, 4] != "")
-        lam0 = rows[mine, 2].astype(float) * 1e-8
-        gamma = rows[mine, 3].astype(float) / (4.0 * np.pi)
-        f = rows[mine, 4].astype(float)
+        lam0, gamma, f = host.species_lines(self.species.element, self.species.ionizationState)
         wavelength = np.asarray(wavelength)
         inside = (lam0 > wavelength.min()) & (lam0 < wavelength.max())   # the reference uses builtin min/max (0.13 s each at C5)
         return lam0[inside], gamma[inside], f[inside]

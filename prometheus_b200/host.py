@@ -35,9 +35,32 @@ from . import scene as _scene
 LINE_LIST = np.empty((0, 5), dtype=str)
 
 
+_line_cache: dict = {}
+
+
 def set_line_list(rows) -> None:
     global LINE_LIST
     LINE_LIST = np.asarray(rows, dtype=str).reshape(-1, 5)
+    _line_cache.clear()
+
+
+def species_lines(element: str, ionizationState: str):
+    """(lambda0 [cm], gamma = A/(4 pi), f) of every line of one species, parsed ONCE per line list: the
+    reference converts the whole str array on every getLineParameters call (gasProperties.py:640-670; SURVEY 8(f)
+    rank 3) -- three calls per constituent and set-up."""
+    key = (element, ionizationState)
+    hit = _line_cache.get(key)
+    if hit is None:
+        rows = LINE_LIST
+        if rows.shape[0] == 0:
+            raise RuntimeError("line list is empty: call prometheus_b200.host.set_line_list(...) first")
+        mine = (rows[:, 0] == element) & (rows[:, 1] == ionizationState)
+        mine &= (rows[:, 2] != "") & (rows[:, 3] != "") & (rows[:, 4] != "")
+        hit = (rows[mine, 2].astype(float) * 1e-8, rows[mine, 3].astype(float) / (4.0 * np.pi), rows[mine, 4].astype(float))
+        for a in hit:
+            a.setflags(write=False)
+        _line_cache[key] = hit
+    return hit
 
 
 _contexts: dict[int, capi.Context] = {}
