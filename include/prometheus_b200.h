@@ -277,6 +277,20 @@ int pb200_molecular_sigma(pb200_ctx* ctx, const double* grid_P, const double* gr
                           double fill, double offset, const double* P, double T, const double* wl,
                           int64_t n_c, int64_t n_x, int64_t n_wav, double* out_host);
 
+/* ---- tabulated-density producer ----------------------------------------------------------- */
+/* SerpensExosphere.addInterpolatedDensity (gasProperties.py:548-583), the part after np.loadtxt:
+   out[nx][ny][nz] = histogramdd(pos[n][3]; edges xb, yb, zb) * N / denom   (denom = n * cellVolume, formed by
+   the caller as the reference does), then, if radius > 0, scipy.ndimage.gaussian_filter with the caller's
+   symmetric weights[2*radius+1] (scipy's _gaussian_kernel1d; boundary mode 'reflect') along x, y, z.
+   Binning is bit-exact with numpy (right-open bins, last edge inclusive, outliers dropped).
+   sums_host (or NULL) receives the two sums the reference prints: all cells, and the cells with
+   planet_R^2 < y^2 + z^2 < star_R^2 on the cell midpoints y_points[ny], z_points[nz].              */
+int pb200_serpens_density(pb200_ctx* ctx, const double* pos, int64_t n, const double* xb, int32_t nxb,
+                          const double* yb, int32_t nyb, const double* zb, int32_t nzb, double N,
+                          double denom, const double* weights, int32_t radius, const double* y_points,
+                          const double* z_points, double planet_R, double star_R, double* out_host,
+                          double* sums_host);
+
 /* ---- result file ------------------------------------------------------------------------- */
 /* Byte-identical replacement of the reference's writer (prometheus.py:142-156): first row
    "nan orbphase/(2 pi) ...", then one row per wavelength "lambda R(phase_0, lambda) ...", np.savetxt

@@ -425,6 +425,26 @@ def lightcurve(R, wavelength, shift, line_centres, bandwidth):
     return np.array(out)
 
 
+# ---------------------------------------------------------------------------------------------------
+# tabulated-density producer -- SerpensExosphere.addInterpolatedDensity, gasProperties.py:548-583
+# ---------------------------------------------------------------------------------------------------
+def serpens_density(particle_pos_cm, grid, N, sigma_smoothing):
+    """-> ((xPoints, yPoints, zPoints), n_histogram), the same numpy / scipy calls as the reference."""
+    from scipy.ndimage import gaussian_filter
+    x_mid, x_b, n_x, rho_b, n_rho = grid[0], grid[1], int(grid[2]), grid[3], int(grid[4])
+    xBins = np.linspace(x_mid - x_b, x_mid + x_b, n_x + 1)                                  # geometryHandler.py:112-128
+    yBins = np.linspace(-rho_b, rho_b, 2 * n_rho + 1)
+    zBins = np.linspace(-rho_b, rho_b, 2 * n_rho + 1)
+    cellVolume = (xBins[1] - xBins[0]) * (yBins[1] - yBins[0]) * (zBins[1] - zBins[0])
+    n_histogram = np.histogramdd(particle_pos_cm, bins=[xBins, yBins, zBins])[0] * N / (np.size(particle_pos_cm, axis=0) * cellVolume)
+    if sigma_smoothing > 0.:
+        n_histogram = gaussian_filter(n_histogram, sigma=sigma_smoothing)
+    xPoints = np.linspace(x_mid - x_b, x_mid + x_b, n_x, endpoint=False) + x_b / float(n_x)
+    yPoints = np.linspace(-rho_b, rho_b, 2 * n_rho, endpoint=False) + 2. * rho_b / (4. * n_rho)
+    zPoints = np.linspace(-rho_b, rho_b, 2 * n_rho, endpoint=False) + 2. * rho_b / (4. * n_rho)
+    return (xPoints, yPoints, zPoints), n_histogram
+
+
 def reference_batch_size(n_chords, n_wav, n_x, has_molecules, max_memory_gb=2.0):
     """memoryHandler.py:34-66 without the psutil clamp"""
     per = (n_x * n_wav * 64 if has_molecules else n_wav * 16) * 2.0

@@ -26,6 +26,7 @@ EXPORTS = [
     "pb200_set_models", "pb200_lightcurve", "pb200_run_batch",
     "pb200_host_register", "pb200_host_unregister", "pb200_run_scatter", "pb200_sync",
     "pb200_set_scene_sharded", "pb200_table_regions", "pb200_number_density_device",
+    "pb200_serpens_density",
 ]
 
 SCN_BAROMETRIC, SCN_HYDROSTATIC, SCN_POWERLAW, SCN_TORUS, SCN_SERPENS = range(5)
@@ -164,6 +165,8 @@ def load():
         "pb200_write_output": (C.c_int, [C.c_char_p, C.c_char_p, c_double_p, c_double_p, c_double_p, i32, i64, i32]),
         "pb200_probe_fp64": (C.c_int, [vp, c_double_p, c_double_p]),
         "pb200_sync": (C.c_int, [vp]),
+        "pb200_serpens_density": (C.c_int, [vp, c_double_p, i64, c_double_p, i32, c_double_p, i32, c_double_p, i32, dbl, dbl,
+                                            c_double_p, i32, c_double_p, c_double_p, dbl, dbl, c_double_p, c_double_p]),
         "pb200_set_scene_sharded": (C.c_int, [vp, C.POINTER(Scene), i32, i32]),
         "pb200_table_regions": (C.c_int, [vp, i32, C.POINTER(vp), C.POINTER(i64), C.POINTER(i32)]),
         "pb200_host_register": (C.c_int, [vp, C.c_size_t, C.POINTER(vp)]),
@@ -358,6 +361,20 @@ class Context:
 
     def number_density_device(self, scenario: int, dev_ptr: int):
         self.check(self.lib.pb200_number_density_device(self.handle, scenario, C.c_void_p(dev_ptr)))
+
+    def serpens_density(self, pos, x_edges, y_edges, z_edges, N, denom, weights, y_points, z_points, planet_R, star_R):
+        """histogramdd * N / denom (+ Gaussian smoothing with `weights`) -> ((nx, ny, nz) array, (sum all, sum selected))."""
+        pos = as_f64(pos).reshape(-1, 3)
+        xb, yb, zb = as_f64(x_edges), as_f64(y_edges), as_f64(z_edges)
+        w = as_f64(weights) if weights is not None and len(weights) > 1 else None
+        radius = (w.size - 1) // 2 if w is not None else 0
+        yp, zp = as_f64(y_points), as_f64(z_points)
+        out = np.empty((xb.size - 1, yb.size - 1, zb.size - 1), dtype=np.float64)
+        sums = np.empty(2, dtype=np.float64)
+        self.check(self.lib.pb200_serpens_density(self.handle, dptr(pos), pos.shape[0], dptr(xb), xb.size, dptr(yb), yb.size,
+                                                  dptr(zb), zb.size, float(N), float(denom), dptr(w) if w is not None else None,
+                                                  radius, dptr(yp), dptr(zp), float(planet_R), float(star_R), dptr(out), dptr(sums)))
+        return out, sums
 
     def last_timing(self) -> dict:
         t = Timing()

@@ -47,6 +47,13 @@ void launch_optical_depth(const DevScene*, const double* sigma_u, int64_t n_chor
                           double* tau, cudaStream_t);
 cudaError_t launch_lightcurve(const double* R_rows, const double* wavelength, int64_t n_wav, int n_rows, int phase_lo,
                               int n_orb_model, const pb200_band& band, const double* shift_dev, double* out, cudaStream_t);
+void launch_serpens_histogram(const double* pos, int64_t n, const double* xb, int nxb, const double* yb, int nyb,
+                              const double* zb, int nzb, unsigned int* counts, int sm_count, cudaStream_t);
+void launch_serpens_scale(const unsigned int* counts, int64_t n_cells, double N, double denom, double* out, cudaStream_t);
+void launch_serpens_filter_axis(const double* in, double* out, int64_t n_cells, int len, int64_t stride, const double* w,
+                                int radius, cudaStream_t);
+void launch_serpens_sums(const double* n, int nx, int ny, int nz, const double* yp, const double* zp, double Rp2, double Rs2,
+                         double* sums, cudaStream_t);
 void launch_probe_dfma(double* out, int blocks, int iters, cudaStream_t);
 void launch_probe_exp(double* out, int blocks, int iters, const double* exp_tab, cudaStream_t);
 
@@ -1375,6 +1382,59 @@ extern "C" int pb200_molecular_sigma(pb200_ctx* c, const double* grid_P, const d
     c->launches += 1;
     PB_CUDA(c, cudaGetLastError());
     return download(c, out_host, out.p, (size_t)n_c * n_x * n_wav * D);
+}
+
+// =================================================================================================
+// SerpensExosphere.addInterpolatedDensity (gasProperties.py:548-583): particle histogram + Gaussian smoothing
+// =================================================================================================
+extern "C" int pb200_serpens_density(pb200_ctx* c, const double* pos, int64_t n, const double* xb, int32_t nxb,
+                                     const double* yb, int32_t nyb, const double* zb, int32_t nzb, double N, double denom,
+                                     const double* weights, int32_t radius, const double* y_points, const double* z_points,
+                                     double planet_R, double star_R, double* out_host, double* sums_host) {
+    int rc = need_ctx(c);
+    if (rc) return rc;
+    if (n < 0 || (n && !pos) || !xb || !yb || !zb || nxb < 2 || nyb < 2 || nzb < 2 || !out_host || radius < 0 ||
+        (radius > 0 && !weights) || (sums_host && (!y_points || !z_points)))
+        return fail(c, PB200_ERR_INVALID, "pb200_serpens_density: bad arguments");
+    const int nx = nxb - 1, ny = nyb - 1, nz = nzb - 1;
+    const int64_t cells = (int64_t)nx * ny * nz;
+    DevBuf dpos, dxb, dyb, dzb, dcnt, da, db, dw, dyp, dzp, dsum;
+    const size_t D = sizeof(double);
+    if ((rc = upload(c, dpos, pos, (size_t)n * 3 * D)) || (rc = upload(c, dxb, xb, nxb * D)) || (rc = upload(c, dyb, yb, nyb * D)) ||
+        (rc = upload(c, dzb, zb, nzb * D)))
+        return rc;
+    PB_CUDA(c, dcnt.alloc((size_t)cells * sizeof(unsigned int)));
+    PB_CUDA(c, da.alloc((size_t)cells * D));
+    PB_CUDA(c, cudaMemsetAsync(dcnt.p, 0, (size_t)cells * sizeof(unsigned int), c->stream));
+    if (n) launch_serpens_histogram(dpos.as<double>(), n, dxb.as<double>(), nxb, dyb.as<double>(), nyb, dzb.as<double>(), nzb,
+                                    dcnt.as<unsigned int>(), c->sm_count, c->stream);
+    launch_serpens_scale(dcnt.as<unsigned int>(), cells, N, denom, da.as<double>(), c->stream);
+    c->launches += n ? 2 : 1;
+    double* result = da.as<double>();
+    if (radius > 0) {   // gaussian_filter: one correlate1d pass per axis, x then y then z
+        PB_CUDA(c, db.alloc((size_t)cells * D));
+        if ((rc = upload(c, dw, weights, (size_t)(2 * radius + 1) * D))) return rc;
+        const int len[3] = {nx, ny, nz};
+        const int64_t stride[3] = {(int64_t)ny * nz, nz, 1};
+        double* src = da.as<double>();
+        double* dst = db.as<double>();
+        for (int ax = 0; ax < 3; ++ax) {
+            launch_serpens_filter_axis(src, dst, cells, len[ax], stride[ax], dw.as<double>(), radius, c->stream);
+            double* t = src; src = dst; dst = t;
+        }
+        c->launches += 3;
+        result = src;
+    }
+    if (sums_host) {
+        if ((rc = upload(c, dyp, y_points, ny * D)) || (rc = upload(c, dzp, z_points, nz * D))) return rc;
+        PB_CUDA(c, dsum.alloc(2 * D));
+        launch_serpens_sums(result, nx, ny, nz, dyp.as<double>(), dzp.as<double>(), planet_R * planet_R, star_R * star_R,
+                            dsum.as<double>(), c->stream);
+        c->launches += 1;
+        PB_CUDA(c, cudaMemcpyAsync(sums_host, dsum.p, 2 * D, cudaMemcpyDeviceToHost, c->stream));
+    }
+    PB_CUDA(c, cudaGetLastError());
+    return download(c, out_host, result, (size_t)cells * D);
 }
 
 extern "C" int pb200_last_timing(pb200_ctx* c, pb200_timing* t) {

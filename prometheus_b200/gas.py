@@ -160,9 +160,39 @@ class SerpensExosphere(EvaporativeExosphere):
         self.filename, self.planet, self.sigmaSmoothing = filename, planet, sigmaSmoothing
 
     def addInterpolatedDensity(self, spatialGrid):
-        raise NotImplementedError(
-            "SERPENS particle-file ingestion (histogramdd + Gaussian filter, gasProperties.py:548-583) is outside "
-            "the hot path (SURVEY 8(f) rank 4); attach a table: self.InterpolatedDensity = GridFunction(grid, values)")
+        """Particle file -> 3-D density table (gasProperties.py:548-583).  File reading and the O(axis) bin edges are
+        host code as in the reference; the histogram over the particles, the scaling, the Gaussian smoothing and
+        the two sums the reference prints run on the GPU (pb200_serpens_density)."""
+        serpensOutput = np.loadtxt(self.filename) * 1e2
+        particlePos = np.ascontiguousarray(serpensOutput[:, 0:3])
+        xBins = spatialGrid.constructXaxis(midpoints=False)
+        n_rho = 2 * int(spatialGrid.rho_steps)
+        yBins = np.linspace(-spatialGrid.rho_border, spatialGrid.rho_border, n_rho + 1)
+        zBins = np.linspace(-spatialGrid.rho_border, spatialGrid.rho_border, n_rho + 1)
+        cellVolume = (xBins[1] - xBins[0]) * (yBins[1] - yBins[0]) * (zBins[1] - zBins[0])
+        xPoints = spatialGrid.constructXaxis()
+        yPoints = np.linspace(-spatialGrid.rho_border, spatialGrid.rho_border, n_rho, endpoint=False) \
+            + 2. * spatialGrid.rho_border / (4. * spatialGrid.rho_steps)
+        zPoints = np.linspace(-spatialGrid.rho_border, spatialGrid.rho_border, n_rho, endpoint=False) \
+            + 2. * spatialGrid.rho_border / (4. * spatialGrid.rho_steps)
+        weights = None
+        if self.sigmaSmoothing > 0.:
+            weights = gaussian_weights(self.sigmaSmoothing)
+        n_histogram, sums = host.get_context().serpens_density(
+            particlePos, xBins, yBins, zBins, self.N, np.size(particlePos, axis=0) * cellVolume, weights,
+            yPoints, zPoints, self.planet.R, self.planet.hostStar.R)
+        print('Sum over all particles, potentially smoothed with a Gaussian:', sums[0] * cellVolume)
+        print('Sum over all particles outside of the planetary disk but inside the stellar disk:', sums[1] * cellVolume)
+        self.InterpolatedDensity = host.GridFunction((xPoints, yPoints, zPoints), n_histogram)
+
+
+def gaussian_weights(sigma, truncate=4.0):
+    """The 1-D kernel of scipy.ndimage.gaussian_filter(order=0) -- scipy's _gaussian_kernel1d expression, O(radius)."""
+    sd = float(sigma)
+    radius = int(truncate * sd + 0.5)
+    x = np.arange(-radius, radius + 1)
+    phi_x = np.exp(-0.5 / (sd * sd) * x ** 2)
+    return phi_x / phi_x.sum()
 
 
 def _mini_scene(dist, x):

@@ -89,6 +89,25 @@ def synthetic_serpens_table(grid, planet, seed=7):
     return xP, yP, zP, np.abs(vals)
 
 
+def synthetic_serpens_particles(grid, n=20000, seed=3):
+    """(n, 6) rows in METRES like a SERPENS output file (positions, velocities; the reference reads columns 0-2 and
+    multiplies by 1e2, gasProperties.py:554-555): a Gaussian cloud around the grid's x midpoint, some particles
+    outside the grid, a few exactly on bin edges (first, inner and last edge)."""
+    rng = np.random.default_rng(seed)
+    x_mid, x_b, n_x, rho_b, n_rho = grid[0], grid[1], int(grid[2]), grid[3], int(grid[4])
+    pos = np.empty((n, 3))
+    pos[:, 0] = rng.normal(x_mid, 0.6 * x_b, n)
+    pos[:, 1] = rng.normal(0.0, 0.4 * rho_b, n)
+    pos[:, 2] = rng.normal(0.0, 0.4 * rho_b, n)
+    xe = np.linspace(x_mid - x_b, x_mid + x_b, n_x + 1)
+    ye = np.linspace(-rho_b, rho_b, 2 * n_rho + 1)
+    for k, (i, j) in enumerate([(0, 0), (n_x, 2 * n_rho), (n_x // 2, n_rho), (1, 2 * n_rho), (n_x, 3)]):
+        pos[k] = (xe[i], ye[j], ye[min(j + 1, 2 * n_rho)])
+    out = np.zeros((n, 6))
+    out[:, 0:3] = pos / 1e2
+    return out
+
+
 def synthetic_mdot_table(n=64):
     """Half-orbit mass-loss curve for TidallyHeatedMoon (gasProperties.py:418-423)."""
     ph = np.linspace(0.0, 1.0, n)

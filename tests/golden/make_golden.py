@@ -173,15 +173,45 @@ def run_retrieval_case(ns, name="RETs", n_models=4, out_dir=HERE):
           f"{out['lightcurve'].max():.6f}], {time.time() - t0:.1f}s -> {os.path.getsize(path) / 1e6:.2f} MB", flush=True)
 
 
+def run_serpens_ingest_case(ns, name="SRPs", out_dir=HERE):
+    """SerpensExosphere.addInterpolatedDensity of the reference (gasProperties.py:548-583) on a seeded synthetic
+    particle file, without and with Gaussian smoothing."""
+    import tempfile
+    from prometheus_b200 import builder, workloads
+    spec = workloads.get("SERs")
+    tr = builder.build_transit(spec, ns=ns, nist_rows=ns.nist_rows, build_tables=False)
+    grid, planet = tr.spatialGrid, tr.planet
+    particles = workloads.synthetic_serpens_particles(spec["grid"])
+    fd, path = tempfile.mkstemp(suffix=".txt")
+    os.close(fd)
+    out = {"N": np.float64(1e33), "sigmas": np.array([0.0, 1.3, 0.6])}
+    try:
+        np.savetxt(path, particles)
+        for k, sigma in enumerate(out["sigmas"]):
+            ex = ns.gas.SerpensExosphere(path, float(out["N"]), planet, float(sigma))
+            ex.addInterpolatedDensity(grid)
+            out[f"values_{k}"] = np.asarray(ex.InterpolatedDensity.values)
+            gx, gy, gz = ex.InterpolatedDensity.grid
+            out["gx"], out["gy"], out["gz"] = np.asarray(gx), np.asarray(gy), np.asarray(gz)
+    finally:
+        os.unlink(path)
+    p = os.path.join(out_dir, f"{name}.npz")
+    np.savez_compressed(p, **out)
+    print(f"{name}: table {out['values_0'].shape}, {int(round(out['values_0'].sum() / out['values_0'][out['values_0'] > 0].min()))} particles binned "
+          f"of {len(particles)} -> {os.path.getsize(p) / 1e6:.2f} MB", flush=True)
+
+
 def main(argv):
     from prometheus_b200 import workloads
     ns = ReferenceNamespace()
     ll = os.path.join(HERE, "linelist.npz")
     np.savez_compressed(ll, rows=ns.nist_rows)
     print("line list rows:", ns.nist_rows.shape)
-    for name in (argv or workloads.GOLDEN_CASES + ["RETs"]):
+    for name in (argv or workloads.GOLDEN_CASES + ["RETs", "SRPs"]):
         if name == "RETs":
             run_retrieval_case(ns, name)
+        elif name == "SRPs":
+            run_serpens_ingest_case(ns, name)
         else:
             run_case(ns, name)
 
