@@ -235,7 +235,7 @@ __device__ __forceinline__ double pb_column_bound(const DevScene& sc, const DevS
 //   * chords whose upper bound sum_a bound_a * max_w sigma_a(p, w) is already below 2^-54: they are
 //     transparent whatever the exact sum is, and get the bound stored as Ncol (so that compact_kernel's own
 //     test classifies them the same way).
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, 6)
 column_thread_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, int* __restrict__ oob_flag,
                      int run_mode) {
     const DevScene& sc = *scp;
