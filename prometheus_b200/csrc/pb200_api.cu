@@ -45,6 +45,12 @@ void launch_molecular_sigma(const MolTable&, double offset, const double* P, dou
                             int64_t n_x, int64_t n_wav, double* out, int sm_count, cudaStream_t);
 void launch_optical_depth(const DevScene*, const double* sigma_u, int64_t n_chords, int64_t wav_lo, int64_t n_wav_sel,
                           double* tau, cudaStream_t);
+void launch_mol_dmax(const DevScene*, unsigned long long* stat, int sm_count, cudaStream_t);
+void launch_mol_moments(const DevScene*, int M, int phase_lo, int n_phase, int bins, double* items, int stride_d,
+                        unsigned long long* stat, bool count, cudaStream_t);
+int mol_item_stride(int max_items);
+cudaError_t launch_transit_moments(const DevScene*, const DevScene& host_copy, const TransitParams&, const double* items,
+                                   int stride_d, int max_items, cudaStream_t, int* n_launch);
 cudaError_t launch_lightcurve(const double* R_rows, const double* wavelength, int64_t n_wav, int n_rows, int phase_lo,
                               int n_orb_model, const pb200_band& band, const double* shift_dev, double* out, cudaStream_t);
 void launch_serpens_histogram(const double* pos, int64_t n, const double* xb, int nxb, const double* yb, int nyb,
@@ -101,6 +107,11 @@ struct pb200_ctx {
     int lastR_phase_lo = 0, lastR_n_phase = 0;   // rows of R left by the last run (in `scratch`, in the caller's device
     bool lastR_full = false;                     // buffer or in mapped host memory) over the whole wavelength grid
     const double* lastR_ptr = nullptr;
+    // moment form of kernel (m): per-chord items (grow-only), bins of the current scene (-1: not yet known)
+    double* mol_items = nullptr;
+    size_t mol_items_bytes = 0;
+    unsigned long long* d_mol_stat = nullptr;   // [0] bit pattern of d_max, [1] largest item count of a chord
+    int mol_bins = -1;
     std::vector<std::pair<void*, int64_t>> regions;   // sharded uploads of the current scene: (device base, doubles per rank)
 };
 
@@ -226,6 +237,8 @@ void pb200_destroy(pb200_ctx* c) {
     if (c->stage) cudaFreeHost(c->stage);
     if (c->mstage) cudaFreeHost(c->mstage);
     if (c->marena) cudaFree(c->marena);
+    if (c->mol_items) cudaFree(c->mol_items);
+    if (c->d_mol_stat) cudaFree(c->d_mol_stat);
     if (c->d_band) cudaFree(c->d_band);
     if (c->d_scene) cudaFree(c->d_scene);
     if (c->d_oob) cudaFree(c->d_oob);
@@ -646,6 +659,7 @@ static int set_scene_impl(pb200_ctx* c, const pb200_scene* s, int n_ranks, int r
     c->has_scene = true;
     c->base = h;
     c->lastR_full = false;
+    c->mol_bins = -1;
     return PB200_OK;
 }
 
@@ -742,7 +756,45 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     }
     PB_CUDA(c, cudaGetLastError());
     PB_CUDA(c, cudaEventRecord(c->ev[3], c->stream));
-    if (c->general_path) {
+    const char* rec_env = getenv("PB200_MOL_RECORDS");   // measurement / regression: the per-record form of kernel (m)
+    if (c->general_path && h.n_mols > 0 && !(rec_env && rec_env[0] == '1')) {
+        // moment form of kernel (m): d_max of the tables (once per scene) -> bins; items per chord (count, then fill)
+        if (!c->d_mol_stat) PB_CUDA(c, cudaMalloc((void**)&c->d_mol_stat, 16));
+        unsigned long long st[2] = {0ull, 0ull};
+        if (c->mol_bins < 0) {
+            PB_CUDA(c, cudaMemsetAsync(c->d_mol_stat, 0, 16, c->stream));
+            launch_mol_dmax(c->d_scene, c->d_mol_stat, c->sm_count, c->stream);
+            c->launches += 1;
+            PB_CUDA(c, cudaMemcpyAsync(st, c->d_mol_stat, 8, cudaMemcpyDeviceToHost, c->stream));
+            PB_CUDA(c, cudaStreamSynchronize(c->stream));
+            double dmax;
+            memcpy(&dmax, &st[0], sizeof dmax);
+            if (!(dmax < 64.0 * 0.38)) return fail(c, PB200_ERR_UNSUPPORTED, "molecular table changes by exp(%g) between pressure nodes; set PB200_MOL_RECORDS=1", dmax);
+            c->mol_bins = dmax > 0.0 ? (int)ceil(dmax / 0.38) : 1;
+            if (c->mol_bins < 1) c->mol_bins = 1;
+        }
+        PB_CUDA(c, cudaMemsetAsync(c->d_mol_stat + 1, 0, 8, c->stream));
+        launch_mol_moments(c->d_scene, h.M, phase_lo, n_phase, c->mol_bins, nullptr, 0, c->d_mol_stat, true, c->stream);
+        PB_CUDA(c, cudaMemcpyAsync(st, c->d_mol_stat + 1, 8, cudaMemcpyDeviceToHost, c->stream));
+        PB_CUDA(c, cudaStreamSynchronize(c->stream));
+        const int max_items = st[0] > 0 ? (int)st[0] : 1;
+        const int stride_d = mol_item_stride(max_items);
+        const size_t need = (size_t)n_phase * h.M * stride_d * sizeof(double);
+        if (need > c->mol_items_bytes) {
+            if (c->mol_items) PB_CUDA(c, cudaFree(c->mol_items));
+            c->mol_items = nullptr; c->mol_items_bytes = 0;
+            PB_CUDA(c, cudaMalloc((void**)&c->mol_items, need));
+            c->mol_items_bytes = need;
+        }
+        launch_mol_moments(c->d_scene, h.M, phase_lo, n_phase, c->mol_bins, c->mol_items, stride_d, c->d_mol_stat, false, c->stream);
+        c->launches += 2;
+        int n_launch = 0;
+        cudaError_t e = launch_transit_moments(c->d_scene, h, prm, c->mol_items, stride_d, max_items, c->stream, &n_launch);
+        if (e == cudaErrorInvalidValue)
+            return fail(c, PB200_ERR_UNSUPPORTED, "molecular tables / items need more shared memory than one SM has; set PB200_MOL_RECORDS=1");
+        if (e != cudaSuccess) return fail(c, PB200_ERR_CUDA, "transit (moments) launch: %s", cudaGetErrorString(e));
+        c->launches += n_launch;
+    } else if (c->general_path) {
         int n_launch = 0;
         cudaError_t e = launch_transit_general(c->d_scene, h, prm, c->sm_count, c->stream, &n_launch);
         if (e == cudaErrorInvalidValue)

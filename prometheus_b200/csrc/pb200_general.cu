@@ -53,6 +53,57 @@ fout_table_kernel(const DevScene* __restrict__ scp) {
     sc.fout[w] = s;
 }
 
+// Prologue shared by the two forms of kernel (m): consumers fill sig[a][thread] (atomic sigma at this thread's
+// wavelength) and the molecular columns V[node][thread] = ln sigma(P_node, T, shift*lambda) (T and lambda already
+// interpolated; one extra "fill" node per molecule, one zero pad row at the end); the producer warp copies the
+// pressure grids to pgrid (may be NULL).
+__device__ __forceinline__ void pb_general_prologue(const DevScene& sc, int p, double lam, bool producer, int tid, int lane,
+                                                    double* V, double* sig, double* pgrid, int node_total) {
+    const double kLn10 = 2.302585092994046;
+    if (!producer) {
+        int node0 = 0;
+        for (int k = 0; k < sc.n_cons; ++k) {
+            const DevConstituent& C = sc.cons[k];
+            const DevScenario& S = sc.scen[C.scenario];
+            const double sl = S.shift[p] * lam;                                               // :917
+            if (C.kind == 0) {
+                sig[C.atom_index * kGenThreads + tid] = pb_interp_log(C.tab_x, C.tab_y, C.n_tab, sl, C.offset);
+            } else {
+                const MolTable t = pb_mol_table(C);
+                // outside the table in T or lambda: every sample takes the fill value (:779 bounds_error=False)
+                const bool inside = (S.T >= t.gT[0] && S.T <= t.gT[t.nT - 1] && sl >= t.gW[0] && sl <= t.gW[t.nW - 1]);
+                int iT = 0, iW = 0;
+                double fT = 0.0, fW = 0.0;
+                if (inside) {
+                    iT = pb_interval(t.gT, t.nT, S.T); iW = pb_interval(t.gW, t.nW, sl);
+                    fT = (S.T - t.gT[iT]) / (t.gT[iT + 1] - t.gT[iT]);
+                    fW = (sl - t.gW[iW]) / (t.gW[iW + 1] - t.gW[iW]);
+                }
+                for (int j = 0; j < t.nP; ++j) {
+                    double u = t.fill;
+                    if (inside) {
+                        const double* v = t.values + ((int64_t)j * t.nT + iT) * t.nW + iW;
+                        u = (v[0] * (1.0 - fW) + v[1] * fW) * (1.0 - fT) + (v[t.nW] * (1.0 - fW) + v[t.nW + 1] * fW) * fT;
+                    }
+                    u *= kLn10;
+                    V[(node0 + j) * kGenThreads + tid] = u;
+                }
+                V[(node0 + t.nP) * kGenThreads + tid] = t.fill * kLn10;     // fill node (records point at it with t = 0)
+                node0 += t.nP + 1;
+            }
+        }
+        V[(size_t)node_total * kGenThreads + tid] = 0.0;   // pad row: "V_{j+1}" of the last fill node
+    } else if (pgrid) {
+        int node0 = 0;
+        for (int k = 0; k < sc.n_cons; ++k) {
+            const DevConstituent& C = sc.cons[k];
+            if (C.kind != 1) continue;
+            for (int j = lane; j < C.dims[0]; j += 32) pgrid[node0 + j] = C.grid_P[j];
+            node0 += C.dims[0] + 1;
+        }
+    }
+}
+
 // named barriers (id 0 is __syncthreads): producer warp <-> 4 consumer warps, two chord buffers
 __device__ __forceinline__ void bar_sync(int id, int count) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory"); }
 __device__ __forceinline__ void bar_arrive(int id, int count) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory"); }
@@ -94,51 +145,8 @@ transit_general_kernel(const DevScene* __restrict__ scp, const TransitParams prm
     const bool live = !producer && w < prm.wav_lo + prm.n_wav_sel;
     const double lam = live ? sc.wavelength[w] : sc.wavelength[prm.wav_lo];
     const bool per_chord_fstar = sc.fout_per_wav != 0;
-    const double kLn10 = 2.302585092994046;
 
-    // ---- prologue: atomic sigma and the molecular columns (consumers), pressure grids (producer) ---
-    if (!producer) {
-        int node0 = 0;
-        for (int k = 0; k < sc.n_cons; ++k) {
-            const DevConstituent& C = sc.cons[k];
-            const DevScenario& S = sc.scen[C.scenario];
-            const double sl = S.shift[p] * lam;                                               // :917
-            if (C.kind == 0) {
-                sig[C.atom_index * kGenThreads + tid] = pb_interp_log(C.tab_x, C.tab_y, C.n_tab, sl, C.offset);
-            } else {
-                const MolTable t = pb_mol_table(C);
-                // outside the table in T or lambda: every sample takes the fill value (:779 bounds_error=False)
-                const bool inside = (S.T >= t.gT[0] && S.T <= t.gT[t.nT - 1] && sl >= t.gW[0] && sl <= t.gW[t.nW - 1]);
-                int iT = 0, iW = 0;
-                double fT = 0.0, fW = 0.0;
-                if (inside) {
-                    iT = pb_interval(t.gT, t.nT, S.T); iW = pb_interval(t.gW, t.nW, sl);
-                    fT = (S.T - t.gT[iT]) / (t.gT[iT + 1] - t.gT[iT]);
-                    fW = (sl - t.gW[iW]) / (t.gW[iW + 1] - t.gW[iW]);
-                }
-                for (int j = 0; j < t.nP; ++j) {
-                    double u = t.fill;
-                    if (inside) {
-                        const double* v = t.values + ((int64_t)j * t.nT + iT) * t.nW + iW;
-                        u = (v[0] * (1.0 - fW) + v[1] * fW) * (1.0 - fT) + (v[t.nW] * (1.0 - fW) + v[t.nW + 1] * fW) * fT;
-                    }
-                    u *= kLn10;
-                    V[(node0 + j) * kGenThreads + tid] = u;
-                }
-                V[(node0 + t.nP) * kGenThreads + tid] = t.fill * kLn10;     // fill node (records point at it with t = 0)
-                node0 += t.nP + 1;
-            }
-        }
-        V[(size_t)node_total * kGenThreads + tid] = 0.0;   // pad row: "V_{j+1}" of the last fill node
-    } else {
-        int node0 = 0;
-        for (int k = 0; k < sc.n_cons; ++k) {
-            const DevConstituent& C = sc.cons[k];
-            if (C.kind != 1) continue;
-            for (int j = lane; j < C.dims[0]; j += 32) pgrid[node0 + j] = C.grid_P[j];
-            node0 += C.dims[0] + 1;
-        }
-    }
+    pb_general_prologue(sc, p, lam, producer, tid, lane, V, sig, pgrid, node_total);
     __syncthreads();
 
     // Mirror pairing (sc.mirror, see compact_kernel): the chords (phi, rho) and (pi - phi, rho) have equal densities
@@ -304,6 +312,297 @@ transit_general_kernel(const DevScene* __restrict__ scp, const TransitParams prm
     const int64_t o = (int64_t)blockIdx.y * prm.n_wav_sel + (w - prm.wav_lo);
     if (prm.n_split == 1) prm.R[pb_out_index(prm, blockIdx.y, w - prm.wav_lo)] = acc / sc.fout[per_chord_fstar ? w : 0];   // :1258
     else prm.partial[(int64_t)blockIdx.z * prm.n_phase * prm.n_wav_sel + o] = acc;
+}
+
+// =================================================================================================
+// Moment form of kernel (m).
+// Along a chord, the records of one molecule whose pressure falls into the same interval j (and the same of
+// `bins` equal sub-intervals of t) share V_j(lambda), d_j(lambda) = V_{j+1} - V_j:
+//     sum_rec coef exp(V_j + t d_j) = exp(V_j + tc d_j) * sum_k d_j^k [ sum_rec coef (t - tc)^k / k! ]
+// The bracket -- moments of the records about the bin centre tc -- does not depend on the wavelength.  They are
+// computed ONCE per chord (mol_moment_kernel, one thread per chord walking its density row) instead of once per
+// CTA of 128 wavelengths, and a consumer thread then pays one table exp and kMolK FMAs per ITEM (a handful per
+// chord and molecule: the pressure along a chord crosses a few decades) instead of per x sample.
+// Truncation: |(t - tc) d| <= d_max / (2 bins) <= 0.19  =>  0.19^9 / 9! = 9e-13 relative on a sigma term;
+// bins = ceil(d_max / 0.38) with d_max = max |V_{j+1} - V_j| over the table nodes (mol_dmax_kernel; interpolation in
+// T and lambda is a convex combination of node values, so the node maximum bounds every thread's d_j).
+// =================================================================================================
+constexpr int kMolK = 8;
+constexpr int kMolItemD = 12;   // doubles per item: {V byte offset (int), tc, M_0/0! .. M_8/8!, pad}
+constexpr int kMolHdrD = 2;     // per chord in global memory: {n_items (int), offset * sum coef}
+
+// d_max over the nodes of every molecular table: stat[0] = bit pattern of max |v[iP+1] - v[iP]| * ln 10
+__global__ void __launch_bounds__(256) mol_dmax_kernel(const DevScene* __restrict__ scp, unsigned long long* __restrict__ stat) {
+    const DevScene& sc = *scp;
+    double mx = 0.0;
+    for (int k = 0; k < sc.n_cons; ++k) {
+        const DevConstituent& C = sc.cons[k];
+        if (C.kind != 1) continue;
+        const int64_t plane = (int64_t)C.dims[1] * C.dims[2], n = (int64_t)(C.dims[0] - 1) * plane;
+        for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+            const double d = fabs(__ldg(C.values + i + plane) - __ldg(C.values + i)) * 2.302585092994046;
+            mx = (d == d) ? fmax(mx, d) : __longlong_as_double(0x7ff0000000000000ll);   // NaN in a table: no bound
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if ((threadIdx.x & 31) == 0 && mx > 0.0) atomicMax(stat, (unsigned long long)__double_as_longlong(mx));
+}
+
+// One thread per (phase, chord).  COUNT: only the number of items (atomicMax into stat[1]); else the items.
+template <bool COUNT>
+__global__ void __launch_bounds__(128)
+mol_moment_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, int bins, double* __restrict__ items,
+                  int stride_d, unsigned long long* __restrict__ stat) {
+    const DevScene& sc = *scp;
+    const int64_t cid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int n_items = 0;
+    if (cid < (int64_t)n_phase * sc.M) {
+        const int pi = (int)(cid / sc.M), m = (int)(cid % sc.M), p = phase_lo + pi;
+        double* out = COUNT ? nullptr : items + cid * stride_d;
+        double off_sum = 0.0;
+        if (sc.w_in[(int64_t)p * sc.Mp + m] != 0.0) {   // blocked chords are never read (their density rows are zero)
+            int node0 = 0;
+            for (int k = 0; k < sc.n_cons; ++k) {
+                const DevConstituent& C = sc.cons[k];
+                if (C.kind != 1) continue;
+                const DevScenario& S = sc.scen[C.scenario];
+                const double* __restrict__ dens = sc.density[S.density_slot] + ((int64_t)p * sc.M + m) * sc.n_x;
+                const double* __restrict__ g = C.grid_P;
+                const int nP = C.dims[0];
+                const double kT = kBoltzmann * S.T, g0 = __ldg(g), g1 = __ldg(g + nP - 1);
+                double part = 0.0, M[kMolK + 1], tc = 0.0;
+                int cur = -1, cur_joff = 0;
+                auto flush = [&]() {
+                    if (cur < 0) return;
+                    if (!COUNT) {
+                        double* it = out + kMolHdrD + (int64_t)n_items * kMolItemD;
+                        it[0] = __hiloint2double(0, cur_joff);
+                        it[1] = tc;
+                        double fact = 1.0;
+#pragma unroll
+                        for (int q = 0; q <= kMolK; ++q) { it[2 + q] = M[q] / fact; fact *= (double)(q + 1); }
+                        it[2 + kMolK + 1] = 0.0;
+                    }
+                    ++n_items;
+                };
+                for (int ix = 0; ix < sc.n_x; ++ix) {
+                    const double n = dens[ix];
+                    const double coef = n * C.chi * sc.delta_x;                                   // :932, :936
+                    if (coef == 0.0) continue;
+                    part += coef;
+                    const double P = fmax(n * kT, 1e-4);                                          // :927, :805
+                    int key, joff;
+                    double t = 0.0, centre = 0.0;
+                    if (P >= g0 && P <= g1) {
+                        const int lo = pb_interval(g, nP, P);
+                        const double ga = __ldg(g + lo);
+                        t = (P - ga) / (__ldg(g + lo + 1) - ga);
+                        int b = (int)(t * bins);
+                        b = b < bins ? b : bins - 1;
+                        centre = (b + 0.5) / bins;
+                        key = lo * bins + b;
+                        joff = (node0 + lo) * kGenThreads * 8;
+                    } else {          // outside the pressure grid: the fill node, sigma does not depend on t
+                        key = nP * bins;
+                        joff = (node0 + nP) * kGenThreads * 8;
+                    }
+                    if (key != cur) {
+                        flush();
+                        cur = key; cur_joff = joff; tc = centre;
+#pragma unroll
+                        for (int q = 0; q <= kMolK; ++q) M[q] = 0.0;
+                    }
+                    const double u = t - tc;
+                    double pw = coef;
+#pragma unroll
+                    for (int q = 0; q <= kMolK; ++q) { M[q] += pw; pw *= u; }
+                }
+                flush();
+                off_sum = fma(C.offset, part, off_sum);
+                node0 += nP + 1;
+            }
+        }
+        if (!COUNT) {
+            out[0] = __hiloint2double(0, n_items);
+            out[1] = off_sum;
+        }
+    }
+    if (COUNT) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) n_items = max(n_items, __shfl_xor_sync(0xffffffffu, n_items, o));
+        if ((threadIdx.x & 31) == 0 && n_items > 0) atomicMax(stat + 1, (unsigned long long)n_items);
+    }
+}
+
+// one item of the current chord for this thread's wavelength: exp(V_j + tc d_j) * sum_k d_j^k M_k / k!
+__device__ __forceinline__ double mol_item_term(const double* __restrict__ it, uint32_t vd_lane, uint32_t tab_lane) {
+    const int joff = __double2loint(it[0]);
+    double v, d;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(vd_lane + (uint32_t)joff));
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(d) : "r"(vd_lane + (uint32_t)joff + kGenThreads * 8u));
+    d -= v;
+    const double e = pb_exp_neg_tab<false, kGenTabCopies>(fma(it[1], d, v), tab_lane);
+    double p = it[2 + kMolK];
+#pragma unroll
+    for (int q = kMolK - 1; q >= 0; --q) p = fma(p, d, it[2 + q]);
+    return e * p;
+}
+
+// Same decomposition as transit_general_kernel (one consumer thread per wavelength, one producer warp, two item
+// buffers, named barriers); the producer only copies the chord's items from global memory.
+// Shared memory: exp table | V[node_total + 1][kGenThreads] | sig[n_atoms][kGenThreads] | buf[2][buf_doubles],
+// buf = {w_in, star_shift, valid | n_items, offset sum, Ncol_a ..., items}
+__global__ void __launch_bounds__(kGenBlock)
+transit_moment_kernel(const DevScene* __restrict__ scp, const TransitParams prm, const double* __restrict__ mol_items,
+                      int stride_d, int buf_doubles, int node_total) {
+    const DevScene& sc = *scp;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    double* etab = reinterpret_cast<double*>(smem_raw);
+    double* V = etab + kExpTabEntries * kGenTabCopies;
+    double* sig = V + (size_t)(node_total + 1) * kGenThreads;
+    double* bufs = sig + (size_t)sc.n_atoms * kGenThreads;
+    const int item_off = (4 + sc.n_atoms + 1) & ~1;   // items start 16-byte aligned
+
+    const int tid = threadIdx.x, lane = tid & 31;
+    const bool producer = tid >= kGenThreads;
+    for (int i = tid; i < kExpTabEntries * kGenTabCopies; i += kGenBlock) etab[i] = __ldg(sc.exp_tab + i / kGenTabCopies);
+    const uint32_t tab_lane = (uint32_t)__cvta_generic_to_shared(etab) + (tid & (kGenTabCopies - 1)) * 8u;
+    const int p = prm.phase_lo + blockIdx.y;
+    const int64_t w = prm.wav_lo + (int64_t)blockIdx.x * kGenThreads + tid;
+    const bool live = !producer && w < prm.wav_lo + prm.n_wav_sel;
+    const double lam = live ? sc.wavelength[w] : sc.wavelength[prm.wav_lo];
+    const bool per_chord_fstar = sc.fout_per_wav != 0;
+    pb_general_prologue(sc, p, lam, producer, tid, lane, V, sig, nullptr, node_total);
+    __syncthreads();
+
+    const int n2 = sc.n_phi / 2, Pm = (n2 + 1) / 2;
+    const int n_chord_items = sc.mirror ? 2 * Pm * sc.n_rho : sc.M;
+    const int m_lo = blockIdx.z * prm.tiles_per_split * kChordTile;
+    int m_hi = m_lo + prm.tiles_per_split * kChordTile;
+    if (m_hi > n_chord_items) m_hi = n_chord_items;
+    const int64_t atom_stride = (int64_t)sc.n_orb * sc.Mp;
+
+    if (producer) {
+        int it = 0;
+        for (int q = m_lo; q <= m_hi; ++q) {
+            const bool end = (q >= m_hi);
+            double wv = 0.0;
+            int m = q;
+            if (!end) {
+                if (sc.mirror) {   // pair index -> chord, as in transit_general_kernel
+                    const int h = q / (Pm * sc.n_rho), rem = q - h * (Pm * sc.n_rho);
+                    const int i = rem / sc.n_rho, irho = rem - i * sc.n_rho, ip = n2 - 1 - i;
+                    m = (h * n2 + i) * sc.n_rho + irho;
+                    wv = sc.w_in[(int64_t)p * sc.Mp + m];
+                    if (ip != i) {
+                        const int mb = (h * n2 + ip) * sc.n_rho + irho;
+                        const double wb = sc.w_in[(int64_t)p * sc.Mp + mb];
+                        if (wv == 0.0) m = mb;
+                        wv += wb;
+                    }
+                } else {
+                    wv = sc.w_in[(int64_t)p * sc.Mp + m];
+                }
+                if (wv == 0.0) continue;   // blocked: F_in = 0 (gasProperties.py:1233)
+            }
+            const int b = it & 1;
+            if (it >= 2) bar_sync(kBarEmpty + b, kGenBlock);
+            double* buf = bufs + (size_t)b * buf_doubles;
+            if (end) {
+                if (lane == 0) reinterpret_cast<int*>(buf + 2)[0] = 0;
+            } else {
+                const int64_t row = (int64_t)p * sc.Mp + m;
+                const double* __restrict__ src = mol_items + ((int64_t)blockIdx.y * sc.M + m) * stride_d;
+                const int n_items = __double2loint(__ldg(src));
+                if (lane == 0) {
+                    buf[0] = wv;
+                    buf[1] = per_chord_fstar ? sc.star_shift[m] : 1.0;
+                    reinterpret_cast<int*>(buf + 2)[0] = 1;
+                    reinterpret_cast<int*>(buf + 2)[1] = n_items;
+                    buf[3] = __ldg(src + 1);
+                }
+                for (int a = lane; a < sc.n_atoms; a += 32) buf[4 + a] = sc.ncol[a * atom_stride + row];
+                const double2* __restrict__ s2 = reinterpret_cast<const double2*>(src + kMolHdrD);
+                double2* d2 = reinterpret_cast<double2*>(buf + item_off);
+                for (int i = lane; i < n_items * (kMolItemD / 2); i += 32) d2[i] = __ldg(s2 + i);
+            }
+            __threadfence_block();
+            bar_arrive(kBarFull + b, kGenBlock);
+            ++it;
+        }
+        if (it >= 2) bar_sync(kBarEmpty + ((it - 2) & 1), kGenBlock);
+        return;
+    }
+
+    const uint32_t vd_lane = (uint32_t)__cvta_generic_to_shared(V) + tid * 8u;
+    double acc = 0.0;
+    for (int it = 0;; ++it) {
+        const int b = it & 1;
+        bar_sync(kBarFull + b, kGenBlock);
+        const double* buf = bufs + (size_t)b * buf_doubles;
+        if (reinterpret_cast<const int*>(buf + 2)[0] == 0) break;
+        const double wv = buf[0];
+        double tau = 0.0;
+        for (int a = 0; a < sc.n_atoms; ++a) tau = fma(buf[4 + a], sig[a * kGenThreads + tid], tau);   // :954
+        {
+            const int n_items = reinterpret_cast<const int*>(buf + 2)[1];
+            const double* items = buf + item_off;
+            double s0 = 0.0, s1 = 0.0;
+            int i = 0;
+            for (; i + 2 <= n_items; i += 2) {
+                s0 += mol_item_term(items + (size_t)i * kMolItemD, vd_lane, tab_lane);
+                s1 += mol_item_term(items + (size_t)(i + 1) * kMolItemD, vd_lane, tab_lane);
+            }
+            if (i < n_items) s0 += mol_item_term(items + (size_t)i * kMolItemD, vd_lane, tab_lane);
+            tau += (s0 + s1) - buf[3];   // sum coef (sigma - offset), :814, :936
+        }
+        double f = wv;
+        if (per_chord_fstar) f *= pb_interp_log(sc.fstar_x, sc.fstar_y, sc.n_fstar, lam / buf[1], 0.0);
+        bar_arrive(kBarEmpty + b, kGenBlock);
+        acc = fma(f, pb_exp_neg_tab<true, kGenTabCopies>(-tau, tab_lane), acc);                         // :1241
+    }
+
+    if (!live) return;
+    const int64_t o = (int64_t)blockIdx.y * prm.n_wav_sel + (w - prm.wav_lo);
+    if (prm.n_split == 1) prm.R[pb_out_index(prm, blockIdx.y, w - prm.wav_lo)] = acc / sc.fout[per_chord_fstar ? w : 0];   // :1258
+    else prm.partial[(int64_t)blockIdx.z * prm.n_phase * prm.n_wav_sel + o] = acc;
+}
+
+void launch_mol_dmax(const DevScene* d_scene, unsigned long long* stat, int sm_count, cudaStream_t st) {
+    mol_dmax_kernel<<<sm_count * 4, 256, 0, st>>>(d_scene, stat);
+}
+void launch_mol_moments(const DevScene* d_scene, int M, int phase_lo, int n_phase, int bins, double* items, int stride_d,
+                        unsigned long long* stat, bool count, cudaStream_t st) {
+    const int64_t n = (int64_t)n_phase * M;
+    const unsigned blocks = (unsigned)((n + 127) / 128);
+    if (count) mol_moment_kernel<true><<<blocks, 128, 0, st>>>(d_scene, phase_lo, n_phase, bins, nullptr, 0, stat);
+    else mol_moment_kernel<false><<<blocks, 128, 0, st>>>(d_scene, phase_lo, n_phase, bins, items, stride_d, stat);
+}
+int mol_item_stride(int max_items) { return kMolHdrD + max_items * kMolItemD; }
+
+cudaError_t launch_transit_moments(const DevScene* d_scene, const DevScene& h, const TransitParams& prm, const double* items,
+                                   int stride_d, int max_items, cudaStream_t st, int* n_launch) {
+    *n_launch = 0;
+    int node_total = 0;
+    for (int k = 0; k < h.n_cons; ++k)
+        if (h.cons[k].kind == 1) node_total += h.cons[k].dims[0] + 1;
+    if (node_total > kMaxMolNodes) return cudaErrorInvalidValue;
+    if (h.fout_per_wav) {
+        fout_table_kernel<<<(unsigned)((h.n_wav + kGenThreads - 1) / kGenThreads), kGenThreads, 0, st>>>(d_scene);
+        ++*n_launch;
+    }
+    const int buf_doubles = ((4 + h.n_atoms + 1) & ~1) + max_items * kMolItemD;
+    const size_t smem = (size_t)kExpTabEntries * kGenTabCopies * sizeof(double) +
+                        (size_t)(node_total + 1) * kGenThreads * sizeof(double) + (size_t)h.n_atoms * kGenThreads * sizeof(double) +
+                        2 * (size_t)buf_doubles * sizeof(double);
+    if (smem > 200 * 1024) return cudaErrorInvalidValue;
+    cudaError_t e = cudaFuncSetAttribute(transit_moment_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    dim3 grid((unsigned)((prm.n_wav_sel + kGenThreads - 1) / kGenThreads), (unsigned)prm.n_phase, (unsigned)prm.n_split);
+    transit_moment_kernel<<<grid, kGenBlock, smem, st>>>(d_scene, prm, items, stride_d, buf_doubles, node_total);
+    ++*n_launch;
+    return cudaGetLastError();
 }
 
 cudaError_t launch_transit_general(const DevScene* d_scene, const DevScene& h, const TransitParams& prm, int sm_count,

@@ -415,3 +415,26 @@ def test_absorber_grouping_leaves_R_unchanged(nist_rows, golden, monkeypatch):
         g = golden(name)
         ok, worst = excess_depth_ok(out["0"], g["R"], g["R0"])
         assert ok, f"{name}: err/bound {worst}"
+
+
+def test_moment_form_of_the_molecular_kernel(nist_rows, golden, monkeypatch):
+    """Kernel (m) in moment form (items per pressure interval, computed once per chord) against its per-record form
+    (PB200_MOL_RECORDS=1): same tau up to the 9e-13 truncation of the expansion, and both within the parity
+    criterion of the reference output."""
+    from prometheus_b200 import scene
+    ctx = host.get_context(0)
+    tr = builder.build_transit(workloads.get("C2s"), nist_rows=nist_rows)
+    sc, keep, info = scene.flatten(tr)
+    out = {}
+    for flag in ("1", "0"):
+        monkeypatch.setenv("PB200_MOL_RECORDS", flag)
+        ctx.set_scene(sc, keep)
+        out[flag], _ = ctx.run(0, info["n_orb"], 0, info["n_wav"])
+        # tiles: a sub-range of phases and wavelengths sees the same items
+        tile, _ = ctx.run(1, 3, 100, 700)
+        assert np.max(np.abs(tile - out[flag][1:3, 100:700])) < 1e-14
+    monkeypatch.delenv("PB200_MOL_RECORDS")
+    assert np.max(np.abs(out["0"] - out["1"])) < 2e-13
+    g = golden("C2s")
+    ok, worst = excess_depth_ok(out["0"], g["R"], g["R0"])
+    assert ok, f"err/bound {worst}"
