@@ -46,11 +46,12 @@ void launch_molecular_sigma(const MolTable&, double offset, const double* P, dou
 void launch_optical_depth(const DevScene*, const double* sigma_u, int64_t n_chords, int64_t wav_lo, int64_t n_wav_sel,
                           double* tau, cudaStream_t);
 void launch_mol_dmax(const DevScene*, unsigned long long* stat, int sm_count, cudaStream_t);
-void launch_mol_moments(const DevScene*, int M, int phase_lo, int n_phase, int bins, double* items, int stride_d,
+void launch_mol_moments(const DevScene*, int n_slots, int phase_lo, int n_phase, int bins, double* blocks, int stride_d,
                         unsigned long long* stat, bool count, cudaStream_t);
-int mol_item_stride(int max_items);
-cudaError_t launch_transit_moments(const DevScene*, const DevScene& host_copy, const TransitParams&, const double* items,
-                                   int stride_d, int max_items, cudaStream_t, int* n_launch);
+int mol_block_stride(int n_atoms, int max_items);
+int mol_tile(int stride_d);
+cudaError_t launch_transit_moments(const DevScene*, const DevScene& host_copy, const TransitParams&, const double* blocks,
+                                   int stride_d, int n_slots, cudaStream_t, int* n_launch);
 cudaError_t launch_lightcurve(const double* R_rows, const double* wavelength, int64_t n_wav, int n_rows, int phase_lo,
                               int n_orb_model, const pb200_band& band, const double* shift_dev, double* out, cudaStream_t);
 void launch_serpens_histogram(const double* pos, int64_t n, const double* xb, int nxb, const double* yb, int nyb,
@@ -774,22 +775,25 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
             if (c->mol_bins < 1) c->mol_bins = 1;
         }
         PB_CUDA(c, cudaMemsetAsync(c->d_mol_stat + 1, 0, 8, c->stream));
-        launch_mol_moments(c->d_scene, h.M, phase_lo, n_phase, c->mol_bins, nullptr, 0, c->d_mol_stat, true, c->stream);
+        // pair slots per phase, rounded up to whole chord tiles (the splits of the chord axis are whole tiles too)
+        const int n_chord_items = h.mirror ? n_pairs : h.M;
+        const int n_slots = ((n_chord_items + kChordTile - 1) / kChordTile) * kChordTile;
+        launch_mol_moments(c->d_scene, n_slots, phase_lo, n_phase, c->mol_bins, nullptr, 0, c->d_mol_stat, true, c->stream);
         PB_CUDA(c, cudaMemcpyAsync(st, c->d_mol_stat + 1, 8, cudaMemcpyDeviceToHost, c->stream));
         PB_CUDA(c, cudaStreamSynchronize(c->stream));
         const int max_items = st[0] > 0 ? (int)st[0] : 1;
-        const int stride_d = mol_item_stride(max_items);
-        const size_t need = (size_t)n_phase * h.M * stride_d * sizeof(double);
+        const int stride_d = mol_block_stride(h.n_atoms, max_items);
+        const size_t need = (size_t)n_phase * n_slots * stride_d * sizeof(double);
         if (need > c->mol_items_bytes) {
             if (c->mol_items) PB_CUDA(c, cudaFree(c->mol_items));
             c->mol_items = nullptr; c->mol_items_bytes = 0;
             PB_CUDA(c, cudaMalloc((void**)&c->mol_items, need));
             c->mol_items_bytes = need;
         }
-        launch_mol_moments(c->d_scene, h.M, phase_lo, n_phase, c->mol_bins, c->mol_items, stride_d, c->d_mol_stat, false, c->stream);
+        launch_mol_moments(c->d_scene, n_slots, phase_lo, n_phase, c->mol_bins, c->mol_items, stride_d, c->d_mol_stat, false, c->stream);
         c->launches += 2;
         int n_launch = 0;
-        cudaError_t e = launch_transit_moments(c->d_scene, h, prm, c->mol_items, stride_d, max_items, c->stream, &n_launch);
+        cudaError_t e = launch_transit_moments(c->d_scene, h, prm, c->mol_items, stride_d, n_slots, c->stream, &n_launch);
         if (e == cudaErrorInvalidValue)
             return fail(c, PB200_ERR_UNSUPPORTED, "molecular tables / items need more shared memory than one SM has; set PB200_MOL_RECORDS=1");
         if (e != cudaSuccess) return fail(c, PB200_ERR_CUDA, "transit (moments) launch: %s", cudaGetErrorString(e));

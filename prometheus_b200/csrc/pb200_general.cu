@@ -329,7 +329,13 @@ transit_general_kernel(const DevScene* __restrict__ scp, const TransitParams prm
 // =================================================================================================
 constexpr int kMolK = 8;
 constexpr int kMolItemD = 12;   // doubles per item: {V byte offset (int), tc, M_0/0! .. M_8/8!, pad}
-constexpr int kMolHdrD = 2;     // per chord in global memory: {n_items (int), offset * sum coef}
+// Per (phase, chord pair) one BLOCK in global memory, blocks of consecutive pairs contiguous (stride_d doubles):
+//   [0] weight w_in(i) + w_in(i') (0: blocked or padding -- skipped)   [1] star_shift   [2] n_items (int)
+//   [3] offset * sum coef   [4 ..) Ncol_a   [hdr ..) items
+// so that the producer warp of transit_moment_kernel moves kMolTile whole blocks with ONE sweep of independent
+// coalesced loads: no dependent global load is left on its path (w_in -> chord -> header -> items took ~2400 cycles
+// per chord when it walked the chords one by one).
+__host__ __device__ inline int mol_hdr_doubles(int n_atoms) { return (4 + n_atoms + 1) & ~1; }
 
 // d_max over the nodes of every molecular table: stat[0] = bit pattern of max |v[iP+1] - v[iP]| * ln 10
 __global__ void __launch_bounds__(256) mol_dmax_kernel(const DevScene* __restrict__ scp, unsigned long long* __restrict__ stat) {
@@ -349,19 +355,42 @@ __global__ void __launch_bounds__(256) mol_dmax_kernel(const DevScene* __restric
     if ((threadIdx.x & 31) == 0 && mx > 0.0) atomicMax(stat, (unsigned long long)__double_as_longlong(mx));
 }
 
-// One thread per (phase, chord).  COUNT: only the number of items (atomicMax into stat[1]); else the items.
+// One thread per (phase, pair slot).  COUNT: only the number of items (atomicMax into stat[1]); else the blocks.
+// n_slots = pairs per phase rounded up to the tile; slots beyond the pairs get weight 0.
 template <bool COUNT>
 __global__ void __launch_bounds__(128)
-mol_moment_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, int bins, double* __restrict__ items,
+mol_moment_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, int n_slots, int bins, double* __restrict__ blocks,
                   int stride_d, unsigned long long* __restrict__ stat) {
     const DevScene& sc = *scp;
     const int64_t cid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     int n_items = 0;
-    if (cid < (int64_t)n_phase * sc.M) {
-        const int pi = (int)(cid / sc.M), m = (int)(cid % sc.M), p = phase_lo + pi;
-        double* out = COUNT ? nullptr : items + cid * stride_d;
-        double off_sum = 0.0;
-        if (sc.w_in[(int64_t)p * sc.Mp + m] != 0.0) {   // blocked chords are never read (their density rows are zero)
+    if (cid < (int64_t)n_phase * n_slots) {
+        const int pi = (int)(cid / n_slots), q = (int)(cid % n_slots), p = phase_lo + pi;
+        const int n2 = sc.n_phi / 2, Pm = (n2 + 1) / 2;
+        const int n_pairs = sc.mirror ? 2 * Pm * sc.n_rho : sc.M;
+        double* out = COUNT ? nullptr : blocks + cid * stride_d;
+        const int hdr = mol_hdr_doubles(sc.n_atoms);
+        double off_sum = 0.0, wv = 0.0;
+        int m = q;
+        if (q < n_pairs) {
+            // mirror pairing (sc.mirror, see compact_kernel): chords (phi, rho) and (pi - phi, rho) have equal densities
+            // along x; one block with weight w_in(i) + w_in(i') stands for both
+            if (sc.mirror) {
+                const int h = q / (Pm * sc.n_rho), rem = q - h * (Pm * sc.n_rho);
+                const int i = rem / sc.n_rho, irho = rem - i * sc.n_rho, ip = n2 - 1 - i;
+                m = (h * n2 + i) * sc.n_rho + irho;
+                wv = sc.w_in[(int64_t)p * sc.Mp + m];
+                if (ip != i) {
+                    const int mb = (h * n2 + ip) * sc.n_rho + irho;
+                    const double wb = sc.w_in[(int64_t)p * sc.Mp + mb];
+                    if (wv == 0.0) m = mb;   // the density row of a blocked chord is zero: take the mirror's
+                    wv += wb;
+                }
+            } else {
+                wv = sc.w_in[(int64_t)p * sc.Mp + m];
+            }
+        }
+        if (wv != 0.0) {   // blocked: F_in = 0 (gasProperties.py:1233)
             int node0 = 0;
             for (int k = 0; k < sc.n_cons; ++k) {
                 const DevConstituent& C = sc.cons[k];
@@ -376,12 +405,12 @@ mol_moment_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, i
                 auto flush = [&]() {
                     if (cur < 0) return;
                     if (!COUNT) {
-                        double* it = out + kMolHdrD + (int64_t)n_items * kMolItemD;
+                        double* it = out + hdr + (int64_t)n_items * kMolItemD;
                         it[0] = __hiloint2double(0, cur_joff);
                         it[1] = tc;
                         double fact = 1.0;
 #pragma unroll
-                        for (int q = 0; q <= kMolK; ++q) { it[2 + q] = M[q] / fact; fact *= (double)(q + 1); }
+                        for (int j = 0; j <= kMolK; ++j) { it[2 + j] = M[j] / fact; fact *= (double)(j + 1); }
                         it[2 + kMolK + 1] = 0.0;
                     }
                     ++n_items;
@@ -411,12 +440,12 @@ mol_moment_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, i
                         flush();
                         cur = key; cur_joff = joff; tc = centre;
 #pragma unroll
-                        for (int q = 0; q <= kMolK; ++q) M[q] = 0.0;
+                        for (int j = 0; j <= kMolK; ++j) M[j] = 0.0;
                     }
                     const double u = t - tc;
                     double pw = coef;
 #pragma unroll
-                    for (int q = 0; q <= kMolK; ++q) { M[q] += pw; pw *= u; }
+                    for (int j = 0; j <= kMolK; ++j) { M[j] += pw; pw *= u; }
                 }
                 flush();
                 off_sum = fma(C.offset, part, off_sum);
@@ -424,8 +453,12 @@ mol_moment_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, i
             }
         }
         if (!COUNT) {
-            out[0] = __hiloint2double(0, n_items);
-            out[1] = off_sum;
+            out[0] = wv;
+            out[1] = (wv != 0.0 && sc.fout_per_wav) ? sc.star_shift[m] : 1.0;
+            out[2] = __hiloint2double(0, n_items);
+            out[3] = off_sum;
+            const int64_t row = (int64_t)p * sc.Mp + m, atom_stride = (int64_t)sc.n_orb * sc.Mp;
+            for (int a = 0; a < sc.n_atoms; ++a) out[4 + a] = (wv != 0.0) ? sc.ncol[a * atom_stride + row] : 0.0;
         }
     }
     if (COUNT) {
@@ -449,20 +482,21 @@ __device__ __forceinline__ double mol_item_term(const double* __restrict__ it, u
     return e * p;
 }
 
-// Same decomposition as transit_general_kernel (one consumer thread per wavelength, one producer warp, two item
-// buffers, named barriers); the producer only copies the chord's items from global memory.
-// Shared memory: exp table | V[node_total + 1][kGenThreads] | sig[n_atoms][kGenThreads] | buf[2][buf_doubles],
-// buf = {w_in, star_shift, valid | n_items, offset sum, Ncol_a ..., items}
+// Same decomposition as transit_general_kernel (one consumer thread per wavelength, one producer warp, two
+// buffers, named barriers), but the unit that moves is a TILE of `tile` consecutive pair blocks: the producer warp
+// copies tile * stride_d doubles with one sweep of independent coalesced 16-byte loads.
+// Shared memory: exp table | V[node_total + 1][kGenThreads] | sig[n_atoms][kGenThreads] | buf[2][tile * stride_d]
 __global__ void __launch_bounds__(kGenBlock)
-transit_moment_kernel(const DevScene* __restrict__ scp, const TransitParams prm, const double* __restrict__ mol_items,
-                      int stride_d, int buf_doubles, int node_total) {
+transit_moment_kernel(const DevScene* __restrict__ scp, const TransitParams prm, const double* __restrict__ blocks,
+                      int stride_d, int n_slots, int tile, int node_total) {
     const DevScene& sc = *scp;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     double* etab = reinterpret_cast<double*>(smem_raw);
     double* V = etab + kExpTabEntries * kGenTabCopies;
     double* sig = V + (size_t)(node_total + 1) * kGenThreads;
     double* bufs = sig + (size_t)sc.n_atoms * kGenThreads;
-    const int item_off = (4 + sc.n_atoms + 1) & ~1;   // items start 16-byte aligned
+    const int hdr = mol_hdr_doubles(sc.n_atoms);
+    const int buf_doubles = tile * stride_d;
 
     const int tid = threadIdx.x, lane = tid & 31;
     const bool producer = tid >= kGenThreads;
@@ -476,78 +510,44 @@ transit_moment_kernel(const DevScene* __restrict__ scp, const TransitParams prm,
     pb_general_prologue(sc, p, lam, producer, tid, lane, V, sig, nullptr, node_total);
     __syncthreads();
 
-    const int n2 = sc.n_phi / 2, Pm = (n2 + 1) / 2;
-    const int n_chord_items = sc.mirror ? 2 * Pm * sc.n_rho : sc.M;
-    const int m_lo = blockIdx.z * prm.tiles_per_split * kChordTile;
-    int m_hi = m_lo + prm.tiles_per_split * kChordTile;
-    if (m_hi > n_chord_items) m_hi = n_chord_items;
-    const int64_t atom_stride = (int64_t)sc.n_orb * sc.Mp;
+    // this split's slots [q_lo, q_hi): whole tiles (n_slots and the split size are multiples of the tile)
+    const int q_lo = blockIdx.z * prm.tiles_per_split * kChordTile;
+    int q_hi = q_lo + prm.tiles_per_split * kChordTile;
+    if (q_hi > n_slots) q_hi = n_slots;
+    const int n_tiles = (q_hi > q_lo) ? (q_hi - q_lo) / tile : 0;
+    const double* __restrict__ src0 = blocks + ((int64_t)blockIdx.y * n_slots + q_lo) * stride_d;
 
     if (producer) {
-        int it = 0;
-        for (int q = m_lo; q <= m_hi; ++q) {
-            const bool end = (q >= m_hi);
-            double wv = 0.0;
-            int m = q;
-            if (!end) {
-                if (sc.mirror) {   // pair index -> chord, as in transit_general_kernel
-                    const int h = q / (Pm * sc.n_rho), rem = q - h * (Pm * sc.n_rho);
-                    const int i = rem / sc.n_rho, irho = rem - i * sc.n_rho, ip = n2 - 1 - i;
-                    m = (h * n2 + i) * sc.n_rho + irho;
-                    wv = sc.w_in[(int64_t)p * sc.Mp + m];
-                    if (ip != i) {
-                        const int mb = (h * n2 + ip) * sc.n_rho + irho;
-                        const double wb = sc.w_in[(int64_t)p * sc.Mp + mb];
-                        if (wv == 0.0) m = mb;
-                        wv += wb;
-                    }
-                } else {
-                    wv = sc.w_in[(int64_t)p * sc.Mp + m];
-                }
-                if (wv == 0.0) continue;   // blocked: F_in = 0 (gasProperties.py:1233)
-            }
+        for (int it = 0; it < n_tiles; ++it) {
             const int b = it & 1;
             if (it >= 2) bar_sync(kBarEmpty + b, kGenBlock);
-            double* buf = bufs + (size_t)b * buf_doubles;
-            if (end) {
-                if (lane == 0) reinterpret_cast<int*>(buf + 2)[0] = 0;
-            } else {
-                const int64_t row = (int64_t)p * sc.Mp + m;
-                const double* __restrict__ src = mol_items + ((int64_t)blockIdx.y * sc.M + m) * stride_d;
-                const int n_items = __double2loint(__ldg(src));
-                if (lane == 0) {
-                    buf[0] = wv;
-                    buf[1] = per_chord_fstar ? sc.star_shift[m] : 1.0;
-                    reinterpret_cast<int*>(buf + 2)[0] = 1;
-                    reinterpret_cast<int*>(buf + 2)[1] = n_items;
-                    buf[3] = __ldg(src + 1);
-                }
-                for (int a = lane; a < sc.n_atoms; a += 32) buf[4 + a] = sc.ncol[a * atom_stride + row];
-                const double2* __restrict__ s2 = reinterpret_cast<const double2*>(src + kMolHdrD);
-                double2* d2 = reinterpret_cast<double2*>(buf + item_off);
-                for (int i = lane; i < n_items * (kMolItemD / 2); i += 32) d2[i] = __ldg(s2 + i);
-            }
+            const double2* __restrict__ s2 = reinterpret_cast<const double2*>(src0 + (int64_t)it * buf_doubles);
+            double2* d2 = reinterpret_cast<double2*>(bufs + (size_t)b * buf_doubles);
+#pragma unroll 8
+            for (int i = lane; i < buf_doubles / 2; i += 32) d2[i] = __ldg(s2 + i);
             __threadfence_block();
             bar_arrive(kBarFull + b, kGenBlock);
-            ++it;
         }
-        if (it >= 2) bar_sync(kBarEmpty + ((it - 2) & 1), kGenBlock);
+        // the consumers' last "empty" arrivals have no matching wait yet: drain them so the barriers are idle at exit
+        if (n_tiles >= 2) bar_sync(kBarEmpty + ((n_tiles - 2) & 1), kGenBlock);
+        if (n_tiles >= 1) bar_sync(kBarEmpty + ((n_tiles - 1) & 1), kGenBlock);
         return;
     }
 
     const uint32_t vd_lane = (uint32_t)__cvta_generic_to_shared(V) + tid * 8u;
     double acc = 0.0;
-    for (int it = 0;; ++it) {
+    for (int it = 0; it < n_tiles; ++it) {
         const int b = it & 1;
         bar_sync(kBarFull + b, kGenBlock);
         const double* buf = bufs + (size_t)b * buf_doubles;
-        if (reinterpret_cast<const int*>(buf + 2)[0] == 0) break;
-        const double wv = buf[0];
-        double tau = 0.0;
-        for (int a = 0; a < sc.n_atoms; ++a) tau = fma(buf[4 + a], sig[a * kGenThreads + tid], tau);   // :954
-        {
-            const int n_items = reinterpret_cast<const int*>(buf + 2)[1];
-            const double* items = buf + item_off;
+        for (int c = 0; c < tile; ++c) {
+            const double* blk = buf + (size_t)c * stride_d;
+            const double wv = blk[0];
+            if (wv == 0.0) continue;   // blocked or padding (block-uniform branch)
+            double tau = 0.0;
+            for (int a = 0; a < sc.n_atoms; ++a) tau = fma(blk[4 + a], sig[a * kGenThreads + tid], tau);   // :954
+            const int n_items = __double2loint(blk[2]);
+            const double* items = blk + hdr;
             double s0 = 0.0, s1 = 0.0;
             int i = 0;
             for (; i + 2 <= n_items; i += 2) {
@@ -555,12 +555,12 @@ transit_moment_kernel(const DevScene* __restrict__ scp, const TransitParams prm,
                 s1 += mol_item_term(items + (size_t)(i + 1) * kMolItemD, vd_lane, tab_lane);
             }
             if (i < n_items) s0 += mol_item_term(items + (size_t)i * kMolItemD, vd_lane, tab_lane);
-            tau += (s0 + s1) - buf[3];   // sum coef (sigma - offset), :814, :936
+            tau += (s0 + s1) - blk[3];   // sum coef (sigma - offset), :814, :936
+            double f = wv;
+            if (per_chord_fstar) f *= pb_interp_log(sc.fstar_x, sc.fstar_y, sc.n_fstar, lam / blk[1], 0.0);
+            acc = fma(f, pb_exp_neg_tab<true, kGenTabCopies>(-tau, tab_lane), acc);                         // :1241
         }
-        double f = wv;
-        if (per_chord_fstar) f *= pb_interp_log(sc.fstar_x, sc.fstar_y, sc.n_fstar, lam / buf[1], 0.0);
-        bar_arrive(kBarEmpty + b, kGenBlock);
-        acc = fma(f, pb_exp_neg_tab<true, kGenTabCopies>(-tau, tab_lane), acc);                         // :1241
+        bar_arrive(kBarEmpty + b, kGenBlock);   // every read of the buffer is done
     }
 
     if (!live) return;
@@ -572,17 +572,23 @@ transit_moment_kernel(const DevScene* __restrict__ scp, const TransitParams prm,
 void launch_mol_dmax(const DevScene* d_scene, unsigned long long* stat, int sm_count, cudaStream_t st) {
     mol_dmax_kernel<<<sm_count * 4, 256, 0, st>>>(d_scene, stat);
 }
-void launch_mol_moments(const DevScene* d_scene, int M, int phase_lo, int n_phase, int bins, double* items, int stride_d,
+void launch_mol_moments(const DevScene* d_scene, int n_slots, int phase_lo, int n_phase, int bins, double* blocks, int stride_d,
                         unsigned long long* stat, bool count, cudaStream_t st) {
-    const int64_t n = (int64_t)n_phase * M;
-    const unsigned blocks = (unsigned)((n + 127) / 128);
-    if (count) mol_moment_kernel<true><<<blocks, 128, 0, st>>>(d_scene, phase_lo, n_phase, bins, nullptr, 0, stat);
-    else mol_moment_kernel<false><<<blocks, 128, 0, st>>>(d_scene, phase_lo, n_phase, bins, items, stride_d, stat);
+    const int64_t n = (int64_t)n_phase * n_slots;
+    const unsigned nb = (unsigned)((n + 127) / 128);
+    if (count) mol_moment_kernel<true><<<nb, 128, 0, st>>>(d_scene, phase_lo, n_phase, n_slots, bins, nullptr, 0, stat);
+    else mol_moment_kernel<false><<<nb, 128, 0, st>>>(d_scene, phase_lo, n_phase, n_slots, bins, blocks, stride_d, stat);
 }
-int mol_item_stride(int max_items) { return kMolHdrD + max_items * kMolItemD; }
+int mol_block_stride(int n_atoms, int max_items) { return mol_hdr_doubles(n_atoms) + max_items * kMolItemD; }
+// blocks per tile: as many as fit 2 x 24 KB of shared memory, a power of two <= 8 (divides kChordTile)
+int mol_tile(int stride_d) {
+    int t = 8;
+    while (t > 1 && (size_t)2 * t * stride_d * sizeof(double) > 48 * 1024) t >>= 1;
+    return t;
+}
 
-cudaError_t launch_transit_moments(const DevScene* d_scene, const DevScene& h, const TransitParams& prm, const double* items,
-                                   int stride_d, int max_items, cudaStream_t st, int* n_launch) {
+cudaError_t launch_transit_moments(const DevScene* d_scene, const DevScene& h, const TransitParams& prm, const double* blocks,
+                                   int stride_d, int n_slots, cudaStream_t st, int* n_launch) {
     *n_launch = 0;
     int node_total = 0;
     for (int k = 0; k < h.n_cons; ++k)
@@ -592,15 +598,15 @@ cudaError_t launch_transit_moments(const DevScene* d_scene, const DevScene& h, c
         fout_table_kernel<<<(unsigned)((h.n_wav + kGenThreads - 1) / kGenThreads), kGenThreads, 0, st>>>(d_scene);
         ++*n_launch;
     }
-    const int buf_doubles = ((4 + h.n_atoms + 1) & ~1) + max_items * kMolItemD;
+    const int tile = mol_tile(stride_d);
     const size_t smem = (size_t)kExpTabEntries * kGenTabCopies * sizeof(double) +
                         (size_t)(node_total + 1) * kGenThreads * sizeof(double) + (size_t)h.n_atoms * kGenThreads * sizeof(double) +
-                        2 * (size_t)buf_doubles * sizeof(double);
+                        2 * (size_t)tile * stride_d * sizeof(double);
     if (smem > 200 * 1024) return cudaErrorInvalidValue;
     cudaError_t e = cudaFuncSetAttribute(transit_moment_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     dim3 grid((unsigned)((prm.n_wav_sel + kGenThreads - 1) / kGenThreads), (unsigned)prm.n_phase, (unsigned)prm.n_split);
-    transit_moment_kernel<<<grid, kGenBlock, smem, st>>>(d_scene, prm, items, stride_d, buf_doubles, node_total);
+    transit_moment_kernel<<<grid, kGenBlock, smem, st>>>(d_scene, prm, blocks, stride_d, n_slots, tile, node_total);
     ++*n_launch;
     return cudaGetLastError();
 }
