@@ -49,7 +49,6 @@ void launch_mol_dmax(const DevScene*, unsigned long long* stat, int sm_count, cu
 void launch_mol_moments(const DevScene*, int n_slots, int phase_lo, int n_phase, int bins, double* blocks, int stride_d,
                         unsigned long long* stat, bool count, cudaStream_t);
 int mol_block_stride(int n_atoms, int max_items);
-int mol_tile(int stride_d);
 cudaError_t launch_transit_moments(const DevScene*, const DevScene& host_copy, const TransitParams&, const double* blocks,
                                    int stride_d, int n_slots, cudaStream_t, int* n_launch);
 cudaError_t launch_lightcurve(const double* R_rows, const double* wavelength, int64_t n_wav, int n_rows, int phase_lo,

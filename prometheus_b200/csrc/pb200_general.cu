@@ -469,16 +469,25 @@ mol_moment_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, i
 }
 
 // one item of the current chord for this thread's wavelength: exp(V_j + tc d_j) * sum_k d_j^k M_k / k!
+// (the item is read with six broadcast 16-byte loads)
 __device__ __forceinline__ double mol_item_term(const double* __restrict__ it, uint32_t vd_lane, uint32_t tab_lane) {
-    const int joff = __double2loint(it[0]);
+    const uint32_t ia = (uint32_t)__cvta_generic_to_shared(it);
+    double f0, tc, m0, m1, m2, m3, m4, m5, m6, m7, m8, pad;
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(f0), "=d"(tc) : "r"(ia));
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(m0), "=d"(m1) : "r"(ia + 16u));
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(m2), "=d"(m3) : "r"(ia + 32u));
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(m4), "=d"(m5) : "r"(ia + 48u));
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(m6), "=d"(m7) : "r"(ia + 64u));
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(m8), "=d"(pad) : "r"(ia + 80u));
+    const int joff = __double2loint(f0);
     double v, d;
     asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(vd_lane + (uint32_t)joff));
     asm volatile("ld.shared.f64 %0, [%1];" : "=d"(d) : "r"(vd_lane + (uint32_t)joff + kGenThreads * 8u));
     d -= v;
-    const double e = pb_exp_neg_tab<false, kGenTabCopies>(fma(it[1], d, v), tab_lane);
-    double p = it[2 + kMolK];
-#pragma unroll
-    for (int q = kMolK - 1; q >= 0; --q) p = fma(p, d, it[2 + q]);
+    const double e = pb_exp_neg_tab<false, kGenTabCopies>(fma(tc, d, v), tab_lane);
+    double p = fma(m8, d, m7);
+    p = fma(p, d, m6); p = fma(p, d, m5); p = fma(p, d, m4); p = fma(p, d, m3);
+    p = fma(p, d, m2); p = fma(p, d, m1); p = fma(p, d, m0);
     return e * p;
 }
 
@@ -548,7 +557,7 @@ transit_moment_kernel(const DevScene* __restrict__ scp, const TransitParams prm,
             for (int a = 0; a < sc.n_atoms; ++a) tau = fma(blk[4 + a], sig[a * kGenThreads + tid], tau);   // :954
             const int n_items = __double2loint(blk[2]);
             const double* items = blk + hdr;
-            double s0 = 0.0, s1 = 0.0;
+            double s0 = 0.0, s1 = 0.0;   // (four interleaved items: 72 registers, 20.4 against 18.7 ms at C2)
             int i = 0;
             for (; i + 2 <= n_items; i += 2) {
                 s0 += mol_item_term(items + (size_t)i * kMolItemD, vd_lane, tab_lane);
@@ -580,10 +589,11 @@ void launch_mol_moments(const DevScene* d_scene, int n_slots, int phase_lo, int 
     else mol_moment_kernel<false><<<nb, 128, 0, st>>>(d_scene, phase_lo, n_phase, n_slots, bins, blocks, stride_d, stat);
 }
 int mol_block_stride(int n_atoms, int max_items) { return mol_hdr_doubles(n_atoms) + max_items * kMolItemD; }
-// blocks per tile: as many as fit 2 x 24 KB of shared memory, a power of two <= 8 (divides kChordTile)
-int mol_tile(int stride_d) {
+// blocks per tile: a power of two <= 8 (divides kChordTile) within `budget` bytes for the two buffers, at least one
+// block.  (Tiles of 2 blocks to fit four CTAs per SM instead of three were slower: 22.8 against 18.7 ms at C2.)
+int mol_tile(int stride_d, size_t fixed_bytes, size_t budget) {
     int t = 8;
-    while (t > 1 && (size_t)2 * t * stride_d * sizeof(double) > 48 * 1024) t >>= 1;
+    while (t > 1 && fixed_bytes + (size_t)2 * t * stride_d * sizeof(double) > budget) t >>= 1;
     return t;
 }
 
@@ -598,10 +608,10 @@ cudaError_t launch_transit_moments(const DevScene* d_scene, const DevScene& h, c
         fout_table_kernel<<<(unsigned)((h.n_wav + kGenThreads - 1) / kGenThreads), kGenThreads, 0, st>>>(d_scene);
         ++*n_launch;
     }
-    const int tile = mol_tile(stride_d);
-    const size_t smem = (size_t)kExpTabEntries * kGenTabCopies * sizeof(double) +
-                        (size_t)(node_total + 1) * kGenThreads * sizeof(double) + (size_t)h.n_atoms * kGenThreads * sizeof(double) +
-                        2 * (size_t)tile * stride_d * sizeof(double);
+    const size_t fixed = (size_t)kExpTabEntries * kGenTabCopies * sizeof(double) +
+                         (size_t)(node_total + 1) * kGenThreads * sizeof(double) + (size_t)h.n_atoms * kGenThreads * sizeof(double);
+    const int tile = mol_tile(stride_d, 0, 48 * 1024);
+    const size_t smem = fixed + 2 * (size_t)tile * stride_d * sizeof(double);
     if (smem > 200 * 1024) return cudaErrorInvalidValue;
     cudaError_t e = cudaFuncSetAttribute(transit_moment_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
