@@ -699,7 +699,7 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     const int n_pairs = 2 * ((h.n_phi / 2 + 1) / 2) * h.n_rho;
     const int n_tiles = (c->general_path && h.mirror) ? (n_pairs + kChordTile - 1) / kChordTile : h.Mp / kChordTile;
     // wavelengths per CTA: kernel (m) 128; kernel (c') one window of 32 * WPT (WPT = 8, 4, 2 for <= 2, <= 4, more absorbers)
-    const int cta_wav = c->general_path ? 128 : 32 * (h.n_abs <= 2 ? 8 : h.n_abs <= 4 ? 4 : 2);
+    const int cta_wav = c->general_path ? 256 : 32 * (h.n_abs <= 2 ? 8 : h.n_abs <= 4 ? 4 : 2);
     const int64_t ctas = ((n_wav_sel + cta_wav - 1) / cta_wav) * n_phase;
     // Chord-axis splits: enough CTAs that the last wave is a small fraction of the run.  Kernel (m) does the
     // same work in every CTA and wants ~80 per SM; kernel (c') has one CTA per wavelength window, most of which
@@ -756,12 +756,15 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     }
     PB_CUDA(c, cudaGetLastError());
     PB_CUDA(c, cudaEventRecord(c->ev[3], c->stream));
-    const char* rec_env = getenv("PB200_MOL_RECORDS");   // measurement / regression: the per-record form of kernel (m)
+    // Kernel (m) runs in moment form unless the tables are too steep for it (more than 64 sub-intervals per pressure
+    // interval would be needed), its blocks do not fit shared memory, or PB200_MOL_RECORDS=1 asks for the per-record
+    // form (measurement / regression).
+    const char* rec_env = getenv("PB200_MOL_RECORDS");
+    bool moments_done = false;
     if (c->general_path && h.n_mols > 0 && !(rec_env && rec_env[0] == '1')) {
-        // moment form of kernel (m): d_max of the tables (once per scene) -> bins; items per chord (count, then fill)
         if (!c->d_mol_stat) PB_CUDA(c, cudaMalloc((void**)&c->d_mol_stat, 16));
         unsigned long long st[2] = {0ull, 0ull};
-        if (c->mol_bins < 0) {
+        if (c->mol_bins < 0) {   // d_max of the tables, once per scene
             PB_CUDA(c, cudaMemsetAsync(c->d_mol_stat, 0, 16, c->stream));
             launch_mol_dmax(c->d_scene, c->d_mol_stat, c->sm_count, c->stream);
             c->launches += 1;
@@ -769,34 +772,37 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
             PB_CUDA(c, cudaStreamSynchronize(c->stream));
             double dmax;
             memcpy(&dmax, &st[0], sizeof dmax);
-            if (!(dmax < 64.0 * 0.38)) return fail(c, PB200_ERR_UNSUPPORTED, "molecular table changes by exp(%g) between pressure nodes; set PB200_MOL_RECORDS=1", dmax);
-            c->mol_bins = dmax > 0.0 ? (int)ceil(dmax / 0.38) : 1;
-            if (c->mol_bins < 1) c->mol_bins = 1;
+            c->mol_bins = (dmax < 64.0 * 0.38) ? (dmax > 0.38 ? (int)ceil(dmax / 0.38) : 1) : 0;   // 0: too steep (or NaN)
         }
-        PB_CUDA(c, cudaMemsetAsync(c->d_mol_stat + 1, 0, 8, c->stream));
-        // pair slots per phase, rounded up to whole chord tiles (the splits of the chord axis are whole tiles too)
-        const int n_chord_items = h.mirror ? n_pairs : h.M;
-        const int n_slots = ((n_chord_items + kChordTile - 1) / kChordTile) * kChordTile;
-        launch_mol_moments(c->d_scene, n_slots, phase_lo, n_phase, c->mol_bins, nullptr, 0, c->d_mol_stat, true, c->stream);
-        PB_CUDA(c, cudaMemcpyAsync(st, c->d_mol_stat + 1, 8, cudaMemcpyDeviceToHost, c->stream));
-        PB_CUDA(c, cudaStreamSynchronize(c->stream));
-        const int max_items = st[0] > 0 ? (int)st[0] : 1;
-        const int stride_d = mol_block_stride(h.n_atoms, max_items);
-        const size_t need = (size_t)n_phase * n_slots * stride_d * sizeof(double);
-        if (need > c->mol_items_bytes) {
-            if (c->mol_items) PB_CUDA(c, cudaFree(c->mol_items));
-            c->mol_items = nullptr; c->mol_items_bytes = 0;
-            PB_CUDA(c, cudaMalloc((void**)&c->mol_items, need));
-            c->mol_items_bytes = need;
+        if (c->mol_bins > 0) {
+            // pair slots per phase, rounded up to whole chord tiles (the splits of the chord axis are whole tiles too)
+            const int n_chord_items = h.mirror ? n_pairs : h.M;
+            const int n_slots = ((n_chord_items + kChordTile - 1) / kChordTile) * kChordTile;
+            PB_CUDA(c, cudaMemsetAsync(c->d_mol_stat + 1, 0, 8, c->stream));
+            launch_mol_moments(c->d_scene, n_slots, phase_lo, n_phase, c->mol_bins, nullptr, 0, c->d_mol_stat, true, c->stream);
+            PB_CUDA(c, cudaMemcpyAsync(st, c->d_mol_stat + 1, 8, cudaMemcpyDeviceToHost, c->stream));
+            PB_CUDA(c, cudaStreamSynchronize(c->stream));
+            c->launches += 1;
+            const int max_items = st[0] > 0 ? (int)st[0] : 1;
+            const int stride_d = mol_block_stride(h.n_atoms, max_items);
+            const size_t need = (size_t)n_phase * n_slots * stride_d * sizeof(double);
+            if (need > c->mol_items_bytes) {
+                if (c->mol_items) PB_CUDA(c, cudaFree(c->mol_items));
+                c->mol_items = nullptr; c->mol_items_bytes = 0;
+                PB_CUDA(c, cudaMalloc((void**)&c->mol_items, need));
+                c->mol_items_bytes = need;
+            }
+            launch_mol_moments(c->d_scene, n_slots, phase_lo, n_phase, c->mol_bins, c->mol_items, stride_d, c->d_mol_stat, false, c->stream);
+            c->launches += 1;
+            int n_launch = 0;
+            cudaError_t e = launch_transit_moments(c->d_scene, h, prm, c->mol_items, stride_d, n_slots, c->stream, &n_launch);
+            if (e == cudaSuccess) { c->launches += n_launch; moments_done = true; }
+            else if (e != cudaErrorInvalidValue) return fail(c, PB200_ERR_CUDA, "transit (moments) launch: %s", cudaGetErrorString(e));
+            else cudaGetLastError();   // does not fit shared memory: the per-record form below
         }
-        launch_mol_moments(c->d_scene, n_slots, phase_lo, n_phase, c->mol_bins, c->mol_items, stride_d, c->d_mol_stat, false, c->stream);
-        c->launches += 2;
-        int n_launch = 0;
-        cudaError_t e = launch_transit_moments(c->d_scene, h, prm, c->mol_items, stride_d, n_slots, c->stream, &n_launch);
-        if (e == cudaErrorInvalidValue)
-            return fail(c, PB200_ERR_UNSUPPORTED, "molecular tables / items need more shared memory than one SM has; set PB200_MOL_RECORDS=1");
-        if (e != cudaSuccess) return fail(c, PB200_ERR_CUDA, "transit (moments) launch: %s", cudaGetErrorString(e));
-        c->launches += n_launch;
+    }
+    if (moments_done) {
+        // kernel (m) has run in moment form
     } else if (c->general_path) {
         int n_launch = 0;
         cudaError_t e = launch_transit_general(c->d_scene, h, prm, c->sm_count, c->stream, &n_launch);

@@ -12,10 +12,11 @@
 // over the records (broadcast LDS) with its own U column.  sigma(chord, x, lambda) is never stored.
 #include "pb200_internal.cuh"
 #include "pb200_molecule.cuh"
+#include <cstdlib>
 
 namespace pb200 {
 
-constexpr int kGenThreads = 128;
+constexpr int kGenThreads = 256;
 constexpr int kGenTabCopies = 4;   // exp table [256][4]: 8 KB, so that four CTAs fit one SM
 constexpr int kGenWarps = kGenThreads / 32;
 constexpr int kMaxMolNodes = 64;   // sum over molecules of (pressure nodes + 1) held in shared memory
@@ -592,7 +593,7 @@ int mol_block_stride(int n_atoms, int max_items) { return mol_hdr_doubles(n_atom
 // blocks per tile: a power of two <= 8 (divides kChordTile) within `budget` bytes for the two buffers, at least one
 // block.  (Tiles of 2 blocks to fit four CTAs per SM instead of three were slower: 22.8 against 18.7 ms at C2.)
 int mol_tile(int stride_d, size_t fixed_bytes, size_t budget) {
-    int t = 8;
+    int t = 8;   // (16: 25.7 ms, 32: 43.9 ms, 8: 18.7 ms at C2 -- occupancy matters more than barrier rounds)
     while (t > 1 && fixed_bytes + (size_t)2 * t * stride_d * sizeof(double) > budget) t >>= 1;
     return t;
 }
