@@ -211,3 +211,34 @@ def test_sharded_table_upload_fills_the_whole_table(nist_rows):
     ctx.set_scene(sc2, keep2)
     R_full, _ = ctx.run(0, info["n_orb"], 0, info["n_wav"])
     assert not np.array_equal(R_partial, R_full)
+
+
+def test_lightcurve_and_batch_edge_cases(setup):
+    """One model; a band that covers everything; a light curve of a sub-range of rows; more scatter ranks than
+    wavelength blocks."""
+    spec, template, band = setup
+    batch = retrieval.RetrievalBatch(template)
+    n_orb, n_wav = batch.info["n_orb"], batch.info["n_wav"]
+    variants = retrieval.make_variants(template, workloads.retrieval_samples(1, seed=9))
+    wide = retrieval.LightcurveBand([5.9e-5], 1.0, band.shift)            # selects every wavelength
+    lc, R, _ = batch.run(variants, wide, want_R=True)
+    assert lc.shape == (1, n_orb)
+    ref = oracle.lightcurve(R[0], np.asarray(template.wavelength), wide.shift, wide.line_centres, wide.bandwidth)
+    assert np.max(np.abs(lc[0] - ref)) < 1e-15
+    # rows [2, 5) of the resident R
+    part = batch.ctx.lightcurve(band.struct(), 2, 5)
+    full = oracle.lightcurve(R[0], np.asarray(template.wavelength), band.shift, band.line_centres, band.bandwidth)
+    assert np.max(np.abs(part - full[2:5])) < 1e-15
+    batch.reset()
+    # scatter with more ranks than 256-wavelength blocks: the extra ranks have nothing to do
+    from prometheus_b200 import scene
+    sc, keep, info = scene.flatten(template)
+    batch.ctx.set_scene(sc, keep)
+    R_ref, _ = batch.ctx.run(0, n_orb, 0, n_wav)
+    full = capi.pinned_pool.empty((n_orb, n_wav))
+    full[...] = -1.0
+    n_blocks = -(-n_wav // 256)
+    for r in range(n_blocks + 2):
+        batch.ctx.run_scatter(0, n_orb, 256, n_blocks + 2, r, full.ctypes.data, n_wav)
+    batch.ctx.synchronize()
+    assert np.array_equal(full, R_ref)

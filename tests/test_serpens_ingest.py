@@ -81,3 +81,33 @@ def test_gpu_ingested_table_runs_through_the_transit(nist_rows):
     (gx, gy, gz), vals = oracle.serpens_density(particles[:, 0:3] * 1e2, spec["grid"], dist.N, 1.3)
     assert np.all(np.isfinite(R)) and R.min() < 1.0
     assert np.max(np.abs(np.asarray(dist.InterpolatedDensity.values) - vals)) <= 1e-13 * vals.max()
+
+
+@pytest.mark.gpu
+def test_gpu_ingest_edge_cases(nist_rows):
+    """No particles at all, particles only outside the grid, particles exactly on edges, a filter wider than an axis."""
+    from prometheus_b200 import host
+    ctx = host.get_context()
+    xb = np.linspace(0.0, 4.0, 5)
+    yb = np.linspace(-1.0, 1.0, 4)
+    zb = np.linspace(-1.0, 1.0, 3)
+    yp, zp = 0.5 * (yb[1:] + yb[:-1]), 0.5 * (zb[1:] + zb[:-1])
+
+    def run(pos, sigma):
+        w = gas.gaussian_weights(sigma) if sigma > 0 else None
+        vals, sums = ctx.serpens_density(pos, xb, yb, zb, 7.0, 3.0, w, yp, zp, 0.1, 10.0)
+        from scipy.ndimage import gaussian_filter
+        ref = np.histogramdd(np.asarray(pos, dtype=float).reshape(-1, 3), bins=[xb, yb, zb])[0] * 7.0 / 3.0
+        if sigma > 0:
+            ref = gaussian_filter(ref, sigma=sigma)
+        return vals, ref, sums
+
+    vals, ref, sums = run(np.empty((0, 3)), 0.0)
+    assert np.array_equal(vals, ref) and vals.sum() == 0.0 and sums[0] == 0.0
+    vals, ref, _ = run(np.array([[9.0, 0.0, 0.0], [-1.0, 0.0, 0.0], [1.0, 5.0, 0.0], [np.nan, 0.0, 0.0]]), 0.0)
+    assert np.array_equal(vals, ref) and vals.sum() == 0.0
+    edges = np.array([[0.0, -1.0, -1.0], [4.0, 1.0, 1.0], [1.0, yb[1], 0.0], [2.0, yb[2], zb[1]], [4.0, 0.0, 0.0]])
+    vals, ref, _ = run(edges, 0.0)
+    assert np.array_equal(vals, ref) and np.count_nonzero(vals) == np.count_nonzero(ref) and vals.sum() == ref.sum()
+    vals, ref, _ = run(edges, 2.5)          # radius 10 > every axis length: repeated reflection
+    assert np.max(np.abs(vals - ref)) <= 1e-14 * ref.max()
