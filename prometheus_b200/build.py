@@ -15,7 +15,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libprometheus_b200.so")
-SOURCES = ["pb200_api.cu", "pb200_density.cu", "pb200_sigma.cu", "pb200_transit.cu", "pb200_general.cu", "pb200_io.cu", "pb200_retrieval.cu", "pb200_serpens.cu"]
+SOURCES = ["pb200_api.cu", "pb200_density.cu", "pb200_sigma.cu", "pb200_transit.cu", "pb200_general.cu", "pb200_io.cu", "pb200_retrieval.cu", "pb200_serpens.cu", "pb200_sort.cu"]
 HEADERS = ["pb200_internal.cuh", "pb200_math.cuh", "pb200_molecule.cuh", "../../include/prometheus_b200.h"]
 # per-translation-unit extra flags (none at present; -Xptxas -O1 on pb200_transit.cu was tried to keep a
 # software-interleaved instruction order and made no difference)

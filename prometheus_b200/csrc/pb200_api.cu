@@ -51,6 +51,10 @@ void launch_mol_moments(const DevScene*, int n_slots, int phase_lo, int n_phase,
 int mol_block_stride(int n_atoms, int max_items);
 cudaError_t launch_transit_moments(const DevScene*, const DevScene& host_copy, const TransitParams&, const double* blocks,
                                    int stride_d, int n_slots, cudaStream_t, int* n_launch);
+size_t sigma_sort_temp_bytes(int64_t n);
+cudaError_t launch_sigma_sort(const double* nsig, int n_phase, int64_t n_wav_sel, unsigned long long* keys_in,
+                              unsigned long long* keys_out, int* vals_in, int* perm, void* temp, size_t temp_bytes,
+                              double* nsig_sorted, cudaStream_t);
 cudaError_t launch_lightcurve(const double* R_rows, const double* wavelength, int64_t n_wav, int n_rows, int phase_lo,
                               int n_orb_model, const pb200_band& band, const double* shift_dev, double* out, cudaStream_t);
 void launch_serpens_histogram(const double* pos, int64_t n, const double* xb, int nxb, const double* yb, int nyb,
@@ -726,7 +730,15 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     prm.n_win = (int)((n_wav_sel + prm.win - 1) / prm.win);
     const size_t order_bytes = c->general_path ? 0 : (((size_t)n_phase * prm.n_win * sizeof(int) + 255) & ~size_t(255));
     const size_t winmax_bytes = c->general_path ? 0 : (size_t)h.n_abs * n_phase * prm.n_win * sizeof(double);
-    int rc = ensure_scratch(c, r_bytes + part_bytes + nsig_bytes + order_bytes + winmax_bytes + 256);
+    // Sigma-sorted windows (pb200_sort.cu): one absorber and a wavelength axis long enough that the sort (a
+    // device-wide radix sort of n_phase * n_wav keys) is small next to the chord loops.  PB200_SORT=0/1 forces it.
+    bool sorted = false;   // default until verified on the GPU: !general && n_abs == 1 && n_wav_sel >= (1 << 16)
+    if (const char* se = getenv("PB200_SORT"))
+        sorted = !c->general_path && h.n_abs == 1 && n_phase < (1 << 20) && n_out < (1ll << 31) && se[0] == '1';
+    const size_t al = 255;
+    const size_t sort_temp = sorted ? ((sigma_sort_temp_bytes(n_out) + al) & ~al) : 0;
+    const size_t sort_bytes = sorted ? (size_t)n_out * (8 + 8 + 8 + 4 + 4) + 5 * 256 + sort_temp : 0;
+    int rc = ensure_scratch(c, r_bytes + part_bytes + nsig_bytes + order_bytes + winmax_bytes + sort_bytes + 512);
     if (rc) return rc;
     prm.R = R_in_scratch ? c->scratch : R_dev;
     prm.partial = reinterpret_cast<double*>(reinterpret_cast<char*>(c->scratch) + r_bytes);
@@ -734,6 +746,8 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     int* order = reinterpret_cast<int*>(reinterpret_cast<char*>(c->scratch) + r_bytes + part_bytes + nsig_bytes);
     prm.order = order;
     prm.winmax = reinterpret_cast<double*>(reinterpret_cast<char*>(c->scratch) + r_bytes + part_bytes + nsig_bytes + order_bytes);
+    prm.perm = nullptr;
+    char* sort_base = reinterpret_cast<char*>(c->scratch) + ((r_bytes + part_bytes + nsig_bytes + order_bytes + winmax_bytes + al) & ~al);
 
     PB_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
     if (!c->general_path) {   // sigma(p, w) of the tile and its per-phase maxima, needed by the culling below
@@ -742,6 +756,20 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
         // statistics are reset by sigma_phase_kernel: no memset nodes in the run
         launch_sigma_phase(c->d_scene, prm, c->stream);
         c->launches += 1;
+        if (sorted) {
+            auto take = [&](size_t bytes) { char* p0 = sort_base; sort_base += (bytes + al) & ~al; return p0; };
+            double* nsig_sorted = reinterpret_cast<double*>(take((size_t)n_out * 8));
+            unsigned long long* k_in = reinterpret_cast<unsigned long long*>(take((size_t)n_out * 8));
+            unsigned long long* k_out = reinterpret_cast<unsigned long long*>(take((size_t)n_out * 8));
+            int* v_in = reinterpret_cast<int*>(take((size_t)n_out * 4));
+            int* perm = reinterpret_cast<int*>(take((size_t)n_out * 4));
+            void* temp = take(sort_temp);
+            cudaError_t e = launch_sigma_sort(prm.nsig, n_phase, n_wav_sel, k_in, k_out, v_in, perm, temp, sort_temp, nsig_sorted, c->stream);
+            if (e != cudaSuccess) return fail(c, PB200_ERR_CUDA, "sigma sort: %s", cudaGetErrorString(e));
+            c->launches += 3;   // keys, gather + the radix sort's own passes
+            prm.nsig = nsig_sorted;
+            prm.perm = perm;
+        }
     }
     // PB200_NO_CULL=1 (measurement only): every unblocked chord gets its exact sums and a record, as in the
     // reference's loop

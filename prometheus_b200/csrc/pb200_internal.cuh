@@ -123,7 +123,9 @@ struct TransitParams {
                           // element (pi, wi) goes to R[pi * R_row_stride + global wavelength index] -- the tile is
                           // written in place into memory the device can reach (mapped host memory, a peer GPU)
     int64_t R_row_stride;
-    double* nsig;         // [n_atoms][n_phase][n_wav_sel] -sigma_a(p, w) * 4096/ln2 (sigma_phase_kernel)
+    double* nsig;         // [n_atoms][n_phase][n_wav_sel] -sigma_a(p, w) * 4096/ln2 (sigma_phase_kernel); with perm != NULL
+                          // in the sorted order of each phase
+    const int* perm;      // NULL, or [n_phase][n_wav_sel]: local wavelength index of sorted position i (pb200_sort.cu)
 };
 __host__ __device__ inline int64_t pb_wav_index(const TransitParams& prm, int64_t wi) {
     if (prm.cyc_block == 0) return prm.wav_lo + wi;

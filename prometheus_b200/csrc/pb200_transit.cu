@@ -162,9 +162,45 @@ struct ThinSums {
     }
 };
 
-template <int S, int WPT, bool CLAMP, int NWARPS>
+// Sigma-sorted windows (one absorber, pb200_sort.cu): a window's wavelengths have nearly the same sigma, so two more
+// warp-uniform decisions pay.  (1) tau < 0.1 on the whole window: w exp(-tau) = w sum_k (v c1)^k / k!, v = N nsig_j,
+// to order 8 (truncation 0.1^9/9! = 2.8e-15): per chord and THREAD the nine sums A_k = sum w (N c1)^k / k!
+// (25 FP64 instructions) instead of 8 samples through the table exp; applied by Horner at the end.  (2) tau > 50 on
+// the whole window: w exp(-tau) < 2e-22 w, the chord is skipped (the reference's own term is below 1e-21 of the sum).
+constexpr double kThinHiV = 0.1 * kExpBigScale;
+constexpr double kOpaqueV = 50.0 * kExpBigScale;
+struct ThinHi {
+    double a[9] = {};
+    __device__ __forceinline__ void add(double w0, double N) {
+        const double t = N * kExpBigC1;
+        double term = w0;
+        a[0] += term;
+        term *= t;                   a[1] += term;
+        term *= t * 0.5;             a[2] += term;
+        term *= t * (1.0 / 3.0);     a[3] += term;
+        term *= t * 0.25;            a[4] += term;
+        term *= t * 0.2;             a[5] += term;
+        term *= t * (1.0 / 6.0);     a[6] += term;
+        term *= t * (1.0 / 7.0);     a[7] += term;
+        term *= t * 0.125;           a[8] += term;
+    }
+    template <int WPT>
+    __device__ __forceinline__ void finish(const double (&nsig)[WPT], double (&acc)[WPT]) const {
+#pragma unroll
+        for (int j = 0; j < WPT; ++j) {
+            const double n = nsig[j];
+            double q = fma(a[8], n, a[7]);
+            q = fma(q, n, a[6]); q = fma(q, n, a[5]); q = fma(q, n, a[4]); q = fma(q, n, a[3]);
+            q = fma(q, n, a[2]); q = fma(q, n, a[1]); q = fma(q, n, a[0]);
+            acc[j] += q;
+        }
+    }
+};
+
+template <int S, int WPT, bool CLAMP, int NWARPS, bool HI>
 __device__ __forceinline__ void transit_tile(uint32_t stage, const double (&nsig)[S][WPT], double (&acc)[WPT],
-                                             uint32_t tab_base, const double (&smw)[S], ThinSums<S>& thin, int wid, double thin_v) {
+                                             uint32_t tab_base, const double (&smw)[S], ThinSums<S>& thin, int wid, double thin_v,
+                                             double hi_v, double smin0, ThinHi& hi) {
     constexpr int R = pb_rec_stride(S);
     constexpr uint32_t kRecBytes = R * sizeof(double);
     // the warps of the CTA share the window (same wavelengths) and split the chords: warp w takes chords
@@ -194,6 +230,10 @@ __device__ __forceinline__ void transit_tile(uint32_t stage, const double (&nsig
                 }
             }
             continue;
+        }
+        if constexpr (HI) {
+            if (bound < hi_v) { hi.add(w0, N[0]); continue; }   // warp-uniform
+            if (N[0] * smin0 > kOpaqueV) continue;              // opaque over the whole window
         }
         ++thin.thick;
 #pragma unroll
@@ -228,9 +268,10 @@ __device__ __forceinline__ void transit_tile(uint32_t stage, const double (&nsig
 // step; their partial sums are added in a fixed order at the end.  Windows are taken in decreasing order of
 // optical thickness (compact_kernel: longest CTAs first).  A window that is thin for every chord of
 // the phase (S <= 2) needs no chord loop at all: its sums are the per-phase totals of compact_kernel.
-template <int S, int WPT, int THREADS>
+template <int S, int WPT, int THREADS, bool HI>
 __global__ void __launch_bounds__(THREADS, S == 1 ? 3 : 2)
 transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
+    static_assert(!HI || S == 1, "sigma-sorted windows are for one absorber");
     const DevScene& sc = *scp;
     // shared memory: exp table [4096] | stage 0 records | stage 1 records | per-warp sums [NWARPS][WIN]
     extern __shared__ __align__(128) double smem[];
@@ -246,7 +287,8 @@ transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int pi = blockIdx.y, p = prm.phase_lo + pi;
     const int split = blockIdx.z;
-    const int window = __ldg(prm.order + (int64_t)pi * prm.n_win + blockIdx.x);
+    // sorted wavelengths: window 0 holds the largest cross sections, the launch order is the thickness order already
+    const int window = HI ? (int)blockIdx.x : __ldg(prm.order + (int64_t)pi * prm.n_win + blockIdx.x);
     const int64_t win_lo = (int64_t)window * WIN;                         // relative to wav_lo
     // this CTA's share of the phase's ACTIVE tiles (compact_kernel): even shares over the splits, at least
     // prm.min_tiles per working CTA; splits beyond the need have nothing to do
@@ -292,6 +334,18 @@ transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
     const bool clamp = !(key < kExpBigClampDecision);   // NaN -> clamped variant (harmless)
     const bool all_thin = (S <= 2) && (key < prm.thin_v);
     ThinSums<S> thin;
+    ThinHi hi;
+    double smin0 = 0.0;   // smallest |nsig| of the window's live wavelengths (0 with a NaN: never opaque)
+    if constexpr (HI) {
+        double mn = __longlong_as_double(0x7ff0000000000000ll);
+#pragma unroll
+        for (int j = 0; j < WPT; ++j)
+            if (win_lo + j * 32 + lane < prm.n_wav_sel) mn = fmin(mn, fabs(nsig[0][j]));
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) mn = fmin(mn, __shfl_xor_sync(0xffffffffu, mn, d));
+        smin0 = any_bad ? 0.0 : mn;
+    }
+    const double hi_v = (prm.thin_v > 0.0) ? kThinHiV : 0.0;
 
     if (n_tiles > 0 && !all_thin) {
         if (tid == 0) {
@@ -323,11 +377,12 @@ transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
             if (tid == 0 && t + 1 < n_tiles) issue(t + 1, stage ^ 1);
             mbar_wait(&full_bar[stage], (t >> 1) & 1);
             const uint32_t sw = stages_addr + stage * kStageBytes;
-            if (clamp) transit_tile<S, WPT, true, NWARPS>(sw, nsig, acc, tab_base, smw, thin, wid, prm.thin_v);
-            else transit_tile<S, WPT, false, NWARPS>(sw, nsig, acc, tab_base, smw, thin, wid, prm.thin_v);
+            if (clamp) transit_tile<S, WPT, true, NWARPS, HI>(sw, nsig, acc, tab_base, smw, thin, wid, prm.thin_v, hi_v, smin0, hi);
+            else transit_tile<S, WPT, false, NWARPS, HI>(sw, nsig, acc, tab_base, smw, thin, wid, prm.thin_v, hi_v, smin0, hi);
             __syncthreads();   // stage may be refilled by the producer in the next iteration
         }
         thin.finish(nsig, acc);
+        if constexpr (HI) hi.finish(nsig[0], acc);
         if (lane == 0 && thin.thick) atomicAdd(sc.stat + 2, (unsigned long long)thin.thick);
     } else if (n_tiles > 0 && wid == 0 && split == 0) {
         // every chord of the phase is thin in this window: the chord sums are the phase totals
@@ -360,7 +415,8 @@ transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
 #pragma unroll
         for (int k = 1; k < NWARPS; ++k) v += red[k * WIN + t];
         const int64_t o = (int64_t)pi * prm.n_wav_sel + w;
-        if (prm.n_split == 1) prm.R[pb_out_index(prm, pi, w)] = (v + sc.w0[p]) / sc.fout[0];           // :1258
+        const int64_t wl = HI ? (int64_t)__ldg(prm.perm + o) : w;   // sorted position -> local wavelength index
+        if (prm.n_split == 1) prm.R[pb_out_index(prm, pi, wl)] = (v + sc.w0[p]) / sc.fout[0];           // :1258
         else prm.partial[(int64_t)split * prm.n_phase * prm.n_wav_sel + o] = v;
     }
 }
@@ -375,14 +431,15 @@ __global__ void finalize_kernel(const DevScene* __restrict__ scp, const TransitP
         const int used = prm.culled ? pb_splits_used(sc.n_act[p], prm.n_split, prm.min_tiles) : prm.n_split;
         for (int k = 0; k < used; ++k) s += prm.partial[(int64_t)k * n + i];
         const double fout = sc.fout[sc.fout_per_wav ? prm.wav_lo + i % prm.n_wav_sel : 0];
-        prm.R[pb_out_index(prm, (int)(i / prm.n_wav_sel), i % prm.n_wav_sel)] = s / fout;
+        const int64_t wl = prm.perm ? (int64_t)__ldg(prm.perm + i) : i % prm.n_wav_sel;   // partial sums are in sorted order
+        prm.R[pb_out_index(prm, (int)(i / prm.n_wav_sel), wl)] = s / fout;
     }
 }
 
-template <int S, int WPT, int THREADS = 256>
+template <int S, int WPT, int THREADS = 256, bool HI = false>
 static cudaError_t launch_one(const DevScene* d_scene, const TransitParams& prm, cudaStream_t st) {
     const size_t smem = (kExpBigEntries + 2 * pb_rec_stride(S) * kChordTile + (THREADS / 32) * 32 * WPT) * sizeof(double);
-    auto kern = transit_kernel<S, WPT, THREADS>;
+    auto kern = transit_kernel<S, WPT, THREADS, HI>;
     {   // dynamic + static shared memory is always above the 48 KB default limit
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
@@ -403,7 +460,7 @@ void launch_sigma_phase(const DevScene* d_scene, const TransitParams& prm, cudaS
 // returns cudaSuccess, or cudaErrorInvalidValue when n_atoms is outside the compiled range
 cudaError_t launch_transit(const DevScene* d_scene, int n_atoms, const TransitParams& prm, cudaStream_t st) {
     switch (n_atoms) {
-        case 1: return launch_one<1, 8>(d_scene, prm, st);
+        case 1: return prm.perm ? launch_one<1, 8, 256, true>(d_scene, prm, st) : launch_one<1, 8>(d_scene, prm, st);
         case 2: return launch_one<2, 8>(d_scene, prm, st);
         case 3: return launch_one<3, 4>(d_scene, prm, st);
         case 4: return launch_one<4, 4>(d_scene, prm, st);

@@ -438,3 +438,29 @@ def test_moment_form_of_the_molecular_kernel(nist_rows, golden, monkeypatch):
     g = golden("C2s")
     ok, worst = excess_depth_ok(out["0"], g["R"], g["R0"])
     assert ok, f"err/bound {worst}"
+
+
+@pytest.mark.parametrize("name", ["C1", "C4s", "PLNs", "THMs", "FSTs"])
+def test_sigma_sorted_windows_leave_R_unchanged(name, nist_rows, golden, monkeypatch):
+    """One absorber: wavelengths of a phase processed in the order of their cross section (PB200_SORT=1 forces it on
+    these small grids), with the order-8 thin expansion (tau < 0.1 on a whole window) and the opaque skip (tau > 50).
+    FSTs runs kernel (m) (per-chord stellar spectrum): the switch must be ignored there."""
+    from prometheus_b200 import scene
+    ctx = host.get_context(0)
+    tr = builder.build_transit(workloads.get(name), nist_rows=nist_rows)
+    sc, keep, info = scene.flatten(tr)
+    ctx.set_scene(sc, keep)
+    out = {}
+    for flag in ("0", "1"):
+        monkeypatch.setenv("PB200_SORT", flag)
+        out[flag], t = ctx.run(0, info["n_orb"], 0, info["n_wav"])
+        tile, _ = ctx.run(1, 3, 5, info["n_wav"] - 7)                      # ragged tile: same values
+        assert np.max(np.abs(tile - out[flag][1:3, 5:info["n_wav"] - 7])) < 5e-14
+    monkeypatch.setenv("PB200_NO_THIN", "1")                                   # every active sample through the exp, sorted
+    R_exp, _ = ctx.run(0, info["n_orb"], 0, info["n_wav"])
+    monkeypatch.delenv("PB200_NO_THIN")
+    monkeypatch.delenv("PB200_SORT")
+    assert np.max(np.abs(out["0"] - out["1"])) < 5e-14 and np.max(np.abs(R_exp - out["0"])) < 5e-14
+    g = golden(name)
+    ok, worst = excess_depth_ok(out["1"], g["R"], g["R0"])
+    assert ok, f"{name}: err/bound {worst}"
