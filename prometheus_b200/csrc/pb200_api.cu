@@ -732,7 +732,7 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     const size_t winmax_bytes = c->general_path ? 0 : (size_t)h.n_abs * n_phase * prm.n_win * sizeof(double);
     // Sigma-sorted windows (pb200_sort.cu): one absorber and a wavelength axis long enough that the sort (a
     // device-wide radix sort of n_phase * n_wav keys) is small next to the chord loops.  PB200_SORT=0/1 forces it.
-    bool sorted = false;   // default until verified on the GPU: !general && n_abs == 1 && n_wav_sel >= (1 << 16)
+    bool sorted = !c->general_path && h.n_abs == 1 && n_wav_sel >= (1 << 16) && n_phase < (1 << 20) && n_out < (1ll << 31);
     if (const char* se = getenv("PB200_SORT"))
         sorted = !c->general_path && h.n_abs == 1 && n_phase < (1 << 20) && n_out < (1ll << 31) && se[0] == '1';
     const size_t al = 255;

@@ -28,7 +28,9 @@ def test_full_size_columns_against_oracle(name, n_cols, nist_rows):
     tr = builder.build_transit(spec, nist_rows=nist_rows)
     R = tr.sumOverChords()
     n_orb, n_wav = R.shape
-    assert np.all(np.isfinite(R)) and R.max() <= 1.0 + 1e-15 and R.min() > 0.0
+    # (>= 0: in the cores of C5's strongest lines every chord has tau > 745 and exp(-tau) is exactly 0 in float64, in
+    # the reference too; the sigma-sorted kernel also drops chords with tau > 50 on a whole window, < 2e-22 of the sum)
+    assert np.all(np.isfinite(R)) and R.max() <= 1.0 + 1e-15 and R.min() >= 0.0
     # columns: the deepest one (a line core), its neighbours, and a strided set
     core = int(np.argmin(R.min(axis=0)))
     sel = np.unique(np.clip(np.concatenate([[core - 1, core, core + 1], np.linspace(0, n_wav - 1, n_cols).astype(int)]), 0, n_wav - 1))
