@@ -464,3 +464,26 @@ def test_sigma_sorted_windows_leave_R_unchanged(name, nist_rows, golden, monkeyp
     g = golden(name)
     ok, worst = excess_depth_ok(out["1"], g["R"], g["R0"])
     assert ok, f"{name}: err/bound {worst}"
+
+
+def test_sigma_sorted_windows_with_block_cyclic_tiles(nist_rows, monkeypatch):
+    """The multi-GPU tiles (blocks of 256 wavelengths dealt round-robin, written in place) through the sorted kernel:
+    the permutation maps a sorted position to the rank's LOCAL wavelength index, the scatter to the global one."""
+    from prometheus_b200 import scene
+    ctx = host.get_context(0)
+    spec = workloads.get("C4s")
+    spec["wavelength"][4] = 2e-11                      # ~2000 wavelengths: several blocks per rank
+    tr = builder.build_transit(spec, nist_rows=nist_rows)
+    sc, keep, info = scene.flatten(tr)
+    ctx.set_scene(sc, keep)
+    n_orb, n_wav = info["n_orb"], info["n_wav"]
+    monkeypatch.setenv("PB200_SORT", "0")
+    R_ref, _ = ctx.run(0, n_orb, 0, n_wav)
+    monkeypatch.setenv("PB200_SORT", "1")
+    full = capi.pinned_pool.empty((n_orb, n_wav))
+    full[...] = -1.0
+    for r in range(3):
+        ctx.run_scatter(0, n_orb, 256, 3, r, full.ctypes.data, n_wav)
+    ctx.synchronize()
+    monkeypatch.delenv("PB200_SORT")
+    assert n_wav > 3 * 256 and np.max(np.abs(full - R_ref)) < 5e-14
