@@ -266,7 +266,7 @@ __device__ __forceinline__ void transit_tile(uint32_t stage, const double (&nsig
 // adds it to its own copies of the chord sums (ThinSums order 2 below 2.1e-5, ThinHi order 8 below 0.1; the lanes'
 // copies are added once, after the last tile) -- 1/32 of the work of letting every thread repeat it.  Only the
 // chords that need the table exp (ballot) are then walked by the whole warp, their records re-read as broadcasts.
-template <int WPT, bool CLAMP, int NWARPS>
+template <int WPT, bool CLAMP, int NWARPS, bool HI>
 __device__ __forceinline__ void transit_tile_sorted(uint32_t stage, const double (&nsig)[1][WPT], double (&acc)[WPT],
                                                     uint32_t tab_base, double smw0, ThinSums<1>& thin, int wid, int lane,
                                                     double thin_v, double hi_v, double smin0, ThinHi& hi) {
@@ -283,9 +283,9 @@ __device__ __forceinline__ void transit_tile_sorted(uint32_t stage, const double
     if (bound < thin_v) {
         const double Nl[1] = {N0};
         thin.add(w0, w1, w2, Nl);
-    } else if (bound < hi_v) {
+    } else if (HI && bound < hi_v) {
         hi.add(w0, N0);
-    } else if (!(N0 * smin0 > kOpaqueV)) {
+    } else if (!(HI && N0 * smin0 > kOpaqueV)) {
         need_exp = true;
     }
     unsigned mask = __ballot_sync(0xffffffffu, need_exp);
@@ -434,20 +434,21 @@ transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
             if (tid == 0 && t + 1 < n_tiles) issue(t + 1, stage ^ 1);
             mbar_wait(&full_bar[stage], (t >> 1) & 1);
             const uint32_t sw = stages_addr + stage * kStageBytes;
-            if constexpr (HI) {
-                if (clamp) transit_tile_sorted<WPT, true, NWARPS>(sw, nsig, acc, tab_base, smw[0], thin, wid, lane, prm.thin_v, hi_v, smin0, hi);
-                else transit_tile_sorted<WPT, false, NWARPS>(sw, nsig, acc, tab_base, smw[0], thin, wid, lane, prm.thin_v, hi_v, smin0, hi);
+            if constexpr (S == 1) {   // one absorber: lane-parallel per-chord decisions (sorted or not)
+                if (clamp) transit_tile_sorted<WPT, true, NWARPS, HI>(sw, nsig, acc, tab_base, smw[0], thin, wid, lane, prm.thin_v, hi_v, smin0, hi);
+                else transit_tile_sorted<WPT, false, NWARPS, HI>(sw, nsig, acc, tab_base, smw[0], thin, wid, lane, prm.thin_v, hi_v, smin0, hi);
             } else {
                 if (clamp) transit_tile<S, WPT, true, NWARPS, HI>(sw, nsig, acc, tab_base, smw, thin, wid, prm.thin_v, hi_v, smin0, hi);
                 else transit_tile<S, WPT, false, NWARPS, HI>(sw, nsig, acc, tab_base, smw, thin, wid, prm.thin_v, hi_v, smin0, hi);
             }
             __syncthreads();   // stage may be refilled by the producer in the next iteration
         }
-        if constexpr (HI) {   // the lanes' copies of the chord sums -> warp totals (fixed order)
+        if constexpr (S == 1) {   // the lanes' copies of the chord sums -> warp totals (fixed order)
             thin.sw = pb_warp_sum(thin.sw); thin.sa[0] = pb_warp_sum(thin.sa[0]); thin.sb[0] = pb_warp_sum(thin.sb[0]);
+            if constexpr (HI) {
 #pragma unroll
-            for (int k = 0; k < 9; ++k) hi.a[k] = pb_warp_sum(hi.a[k]);
-            thin.thick = __shfl_sync(0xffffffffu, thin.thick, 0);
+                for (int k = 0; k < 9; ++k) hi.a[k] = pb_warp_sum(hi.a[k]);
+            }
         }
         thin.finish(nsig, acc);
         if constexpr (HI) hi.finish(nsig[0], acc);
