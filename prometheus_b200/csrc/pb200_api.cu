@@ -32,6 +32,7 @@ cudaError_t launch_transit(const DevScene*, int n_atoms, const TransitParams&, c
 cudaError_t launch_transit_general(const DevScene*, const DevScene& host_copy, const TransitParams&, int sm_count,
                                    cudaStream_t, int* n_launch);
 void launch_sigma_phase(const DevScene*, const TransitParams&, cudaStream_t);
+void launch_bucket_build(const DevScene*, int sm_count, cudaStream_t);
 cudaError_t launch_compact(const DevScene*, const TransitParams&, bool cull, cudaStream_t);
 void launch_finalize(const DevScene*, const TransitParams&, int sm_count, cudaStream_t);
 void launch_sigma_lookup(const double*, const double*, int64_t, double, const double*, int64_t, double*, int,
@@ -116,6 +117,7 @@ struct pb200_ctx {
     size_t mol_items_bytes = 0;
     unsigned long long* d_mol_stat = nullptr;   // [0] bit pattern of d_max, [1] largest item count of a chord
     int mol_bins = -1;
+    bool buckets_ready = false;   // bucket indices of the sigma tables (built on the device before the first run of a scene)
     std::vector<std::pair<void*, int64_t>> regions;   // sharded uploads of the current scene: (device base, doubles per rank)
 };
 
@@ -376,6 +378,9 @@ static int plan_derived(pb200_ctx* c) {
         if (h.scen[i].density_slot >= 0)
             wants.push_back({&h.density[h.scen[i].density_slot], (size_t)h.n_orb * h.M * h.n_x});
     wants.push_back({&h.fout, fstar_per_chord ? (size_t)h.n_wav : 1});
+    double* bucket_d[kMaxConstituents] = {};
+    for (int k = 0; k < h.n_cons; ++k)
+        if (h.cons[k].kind == 0 && h.cons[k].n_bucket > 0) wants.push_back({&bucket_d[k], (size_t)(h.cons[k].n_bucket + 2) / 2 + 1});
     size_t need = 0;
     for (const auto& w : wants) need += ((w.n ? w.n : 1) * sizeof(double) + 255) & ~size_t(255);
     if (need > c->darena_bytes) {
@@ -391,6 +396,9 @@ static int plan_derived(pb200_ctx* c) {
             off += ((w.n ? w.n : 1) * sizeof(double) + 255) & ~size_t(255);
         }
     }
+    for (int k = 0; k < h.n_cons; ++k)
+        h.cons[k].bucket = (h.cons[k].kind == 0 && h.cons[k].n_bucket > 0) ? reinterpret_cast<const int*>(bucket_d[k]) : nullptr;
+    c->buckets_ready = false;
     h.exp_tab = c->d_exp_tab;
     h.nmax = reinterpret_cast<unsigned long long*>(nmax_d);
     h.smax = reinterpret_cast<unsigned long long*>(smax_d);
@@ -599,6 +607,13 @@ static int set_scene_impl(pb200_ctx* c, const pb200_scene* s, int n_ranks, int r
             if (qc.kind == 0) {
                 dc.atom_index = n_atoms++;
                 dc.tab_x = at<double>(A, co[k].tx); dc.tab_y = at<double>(A, co[k].ty); dc.n_tab = qc.n_tab;
+                dc.bucket = nullptr; dc.n_bucket = 0;
+                const double span = qc.tab_x[qc.n_tab - 1] - qc.tab_x[0];
+                if (qc.n_tab >= 1024 && span > 0.0 && span < 1e300) {   // worth an index (and a finite, ascending table)
+                    dc.n_bucket = (int)(qc.n_tab < (1 << 22) ? qc.n_tab : (1 << 22));
+                    dc.bucket_x0 = qc.tab_x[0];
+                    dc.bucket_inv = (double)dc.n_bucket / span;
+                }
             } else {
                 dc.mol_index = n_mols++;
                 d.has_molecule = 1;
@@ -754,6 +769,11 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
         if (h.n_atoms < 1) return fail(c, PB200_ERR_INVALID, "scene has no absorbing constituent");
         // smax is left clean by compact_kernel of the previous run (and by pb200_set_scene), the run
         // statistics are reset by sigma_phase_kernel: no memset nodes in the run
+        if (!c->buckets_ready) {   // after the (possibly sharded + all-gathered) tables are complete on the device
+            launch_bucket_build(c->d_scene, c->sm_count, c->stream);
+            c->launches += 1;
+            c->buckets_ready = true;
+        }
         launch_sigma_phase(c->d_scene, prm, c->stream);
         c->launches += 1;
         if (sorted) {

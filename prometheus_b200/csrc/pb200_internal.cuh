@@ -31,6 +31,10 @@ struct DevConstituent {
     int kind, scenario, atom_index, mol_index;
     double chi, offset, fill;
     const double* tab_x; const double* tab_y; int64_t n_tab;
+    // bucket index of tab_x (atoms, built on the device before the first run of a scene): bucket[b] = smallest j with
+    // pb_bucket_of(tab_x[j]) >= b (n_tab if none), b = 0 .. n_bucket; brackets the binary search of sigma_phase_kernel
+    const int* bucket; int n_bucket; int pad2;
+    double bucket_x0, bucket_inv;
     const double* grid_P; const double* grid_T; const double* grid_w; const double* values;
     int dims[3];
     int pad;

@@ -265,6 +265,33 @@ __device__ __forceinline__ double pb_interp(const double* __restrict__ xs,
     return slope * (x - x0) + y0;
 }
 
+// bucket of x in the bucket index of a table (DevConstituent::bucket); the index is built with this same expression
+__device__ __forceinline__ int pb_bucket_of(double x, double x0, double inv, int n_bucket) {
+    const double fb = (x - x0) * inv;
+    return (fb > 0.0) ? ((fb < (double)n_bucket) ? (int)fb : n_bucket - 1) : 0;   // NaN -> 0
+}
+
+// The same value as pb_interp, with the binary search started from a bracket [lo, hi] that is known to contain the
+// answer (bucket index of the table, DevConstituent::bucket): 3-4 dependent loads instead of ~19 on a 3e5-entry table.
+__device__ __forceinline__ double pb_interp_bracket(const double* __restrict__ xs, const double* __restrict__ ys, int64_t n,
+                                                    double x, int64_t lo, int64_t hi) {
+    if (!(x == x)) return x;
+    if (n == 1) return __ldg(ys);
+    if (x <= __ldg(xs)) return __ldg(ys);
+    if (x >= __ldg(xs + n - 1)) return __ldg(ys + n - 1);
+    // invariant of pb_search_le: xs[lo] <= x < xs[hi]
+    if (hi > n - 1) hi = n - 1;
+    if (lo < 0) lo = 0;
+    while (hi - lo > 1) {
+        const int64_t mid = (lo + hi) >> 1;
+        if (__ldg(xs + mid) <= x) lo = mid; else hi = mid;
+    }
+    const double x0 = __ldg(xs + lo), x1 = __ldg(xs + lo + 1);
+    const double y0 = __ldg(ys + lo), y1 = __ldg(ys + lo + 1);
+    const double slope = (y1 - y0) / (x1 - x0);
+    return slope * (x - x0) + y0;
+}
+
 __device__ __forceinline__ double pb_interp_log(const double* __restrict__ xs,
                                                 const double* __restrict__ ys, int64_t n, double x,
                                                 double offset) {

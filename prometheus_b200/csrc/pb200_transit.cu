@@ -87,7 +87,14 @@ __global__ void __launch_bounds__(256) sigma_phase_kernel(const DevScene* __rest
             double v = 0.0;
             for (int k = k0; k < k0 + sc.abs_count[a]; ++k) {
                 const DevConstituent& C = sc.cons[k];
-                v = fma(C.chi, pb_interp_log(C.tab_x, C.tab_y, C.n_tab, sl, C.offset), v);      // :940 chi, :950-951 sigma
+                double lg;
+                if (C.bucket) {   // the answer j (largest with tab_x[j] <= sl) lies in [bucket[b] - 1, bucket[b + 1])
+                    const int b = pb_bucket_of(sl, C.bucket_x0, C.bucket_inv, C.n_bucket);
+                    lg = pb_interp_bracket(C.tab_x, C.tab_y, C.n_tab, sl, (int64_t)__ldg(C.bucket + b) - 1, __ldg(C.bucket + b + 1));
+                } else {
+                    lg = pb_interp(C.tab_x, C.tab_y, C.n_tab, sl);
+                }
+                v = fma(C.chi, exp10(lg) - C.offset, v);                                      // :940 chi, :950-951 sigma
             }
             const double ns = -v * kExpBigScale;
             prm.nsig[((int64_t)a * prm.n_phase + pi) * prm.n_wav_sel + wi] = ns;
@@ -517,6 +524,43 @@ static cudaError_t launch_one(const DevScene* d_scene, const TransitParams& prm,
     dim3 grid((unsigned)prm.n_win, (unsigned)prm.n_phase, (unsigned)prm.n_split);
     kern<<<grid, THREADS, smem, st>>>(d_scene, prm);
     return cudaGetLastError();
+}
+
+// bucket index of every atomic table: with bfun(x) = clamp(int((x - x0) * inv), 0, n_bucket - 1) -- the SAME expression the
+// lookup evaluates -- bucket[b] = smallest j with bfun(tab_x[j]) >= b (n_tab if none), b = 0 .. n_bucket.  One thread per
+// table entry fills the buckets between its predecessor's and its own: no search, no dependent loads.
+__global__ void __launch_bounds__(256) bucket_build_kernel(const DevScene* __restrict__ scp) {
+    const DevScene& sc = *scp;
+    const int lane = threadIdx.x & 31;
+    for (int k = 0; k < sc.n_cons; ++k) {
+        const DevConstituent& C = sc.cons[k];
+        if (C.kind != 0 || !C.bucket) continue;
+        int* out = const_cast<int*>(C.bucket);
+        const int64_t n = C.n_tab, n_round = (n + 31) & ~int64_t(31);
+        for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += (int64_t)gridDim.x * blockDim.x) {
+            int b0 = 1, b1 = 0;   // buckets (b0 .. b1) get the value i: those above the predecessor's bucket up to this entry's
+            if (i < n) {
+                b1 = pb_bucket_of(__ldg(C.tab_x + i), C.bucket_x0, C.bucket_inv, C.n_bucket);
+                b0 = (i > 0 ? pb_bucket_of(__ldg(C.tab_x + i - 1), C.bucket_x0, C.bucket_inv, C.n_bucket) : -1) + 1;
+            }
+            const bool big = (b1 - b0) >= 4;   // a gap of the coarse part of the grid: filled by the whole warp
+            if (!big)
+                for (int b = b0; b <= b1; ++b) out[b] = (int)i;
+            unsigned mask = __ballot_sync(0xffffffffu, big);
+            while (mask) {
+                const int l = __ffs(mask) - 1;
+                mask &= mask - 1;
+                const int g0 = __shfl_sync(0xffffffffu, b0, l), g1 = __shfl_sync(0xffffffffu, b1, l);
+                const int gi = (int)__shfl_sync(0xffffffffu, (int)i, l);
+                for (int b = g0 + lane; b <= g1; b += 32) out[b] = gi;
+            }
+            if (i == n - 1)   // beyond the last entry's bucket
+                for (int b = b1 + 1; b <= C.n_bucket; ++b) out[b] = (int)n;
+        }
+    }
+}
+void launch_bucket_build(const DevScene* d_scene, int sm_count, cudaStream_t st) {
+    bucket_build_kernel<<<sm_count * 8, 256, 0, st>>>(d_scene);
 }
 
 void launch_sigma_phase(const DevScene* d_scene, const TransitParams& prm, cudaStream_t st) {
