@@ -96,6 +96,36 @@ def _trim_table(tx, ty, q_lo, q_hi):
     return tx[i0:i1], ty[i0:i1]
 
 
+_AXES_CACHE: dict = {}
+_GRID_FIELDS = ("x_midpoint", "x_border", "x_steps", "rho_border", "rho_steps", "phi_steps", "orbphase_border", "orbphase_steps")
+
+
+def _axes(grid, phi_rot):
+    """(x, rho, phase, sin phi, cos phi, cos(phi - phi_rot), delta_x) of a Grid, evaluated by the grid's own methods.
+    The axes depend only on the grid's eight constructor arguments (geometryHandler.py:64-71) and phiStarrot, so they
+    are kept per (class, arguments): a retrieval or a multi-GPU loop calls sumOverChords thousands of times on one
+    grid, and the ~10 small numpy calls were a quarter of the host time of a call.  Objects without those attributes
+    are evaluated every time."""
+    try:
+        key = (type(grid),) + tuple(float(getattr(grid, f)) for f in _GRID_FIELDS) + (float(phi_rot),)
+    except (AttributeError, TypeError, ValueError):
+        key = None
+    hit = _AXES_CACHE.get(key) if key is not None else None
+    if hit is None:
+        x = np.asarray(grid.constructXaxis(), dtype=np.float64)
+        rho = np.asarray(grid.constructRhoAxis(), dtype=np.float64)
+        phi = np.asarray(grid.constructPhiAxis(), dtype=np.float64)
+        phase = np.asarray(grid.constructOrbphaseAxis(), dtype=np.float64)
+        hit = (x, rho, phase, np.sin(phi), np.cos(phi), np.cos(phi - phi_rot), float(grid.getDeltaX()))
+        for a in hit[:6]:
+            a.setflags(write=False)
+        if key is not None:
+            if len(_AXES_CACHE) > 64:
+                _AXES_CACHE.clear()
+            _AXES_CACHE[key] = hit
+    return hit
+
+
 def flatten(transit, wavelength=None, wav_range=None) -> tuple[capi.Scene, list, dict]:
     """Transit-like object -> (pb200_scene, keep-alive list, info).
 
@@ -113,20 +143,17 @@ def flatten(transit, wavelength=None, wav_range=None) -> tuple[capi.Scene, list,
         wavelength = transit.wavelength
     wavelength = np.asarray(wavelength, dtype=np.float64)
 
-    x = np.asarray(grid.constructXaxis(), dtype=np.float64)
-    rho = np.asarray(grid.constructRhoAxis(), dtype=np.float64)
-    phi = np.asarray(grid.constructPhiAxis(), dtype=np.float64)
-    phase = np.asarray(grid.constructOrbphaseAxis(), dtype=np.float64)
+    x, rho, phase, sin_phi, cos_phi, cos_phi_rot, delta_x = _axes(grid, star.phiStarrot)
     n_orb = phase.size
 
     sc = capi.Scene()
     sc.abi_version = capi.ABI_VERSION
-    sc.n_x, sc.n_rho, sc.n_phi, sc.n_orb, sc.n_wav = x.size, rho.size, phi.size, n_orb, wavelength.size
+    sc.n_x, sc.n_rho, sc.n_phi, sc.n_orb, sc.n_wav = x.size, rho.size, sin_phi.size, n_orb, wavelength.size
     sc.x, sc.rho = b.ptr(x), b.ptr(rho)
-    sc.sin_phi, sc.cos_phi = b.ptr(np.sin(phi)), b.ptr(np.cos(phi))            # geometryHandler.py:84-85
-    sc.cos_phi_rot = b.ptr(np.cos(phi - star.phiStarrot))                        # gasProperties.py:1182
+    sc.sin_phi, sc.cos_phi = b.ptr(sin_phi), b.ptr(cos_phi)                      # geometryHandler.py:84-85
+    sc.cos_phi_rot = b.ptr(cos_phi_rot)                                          # gasProperties.py:1182
     sc.wavelength = b.ptr(wavelength)
-    sc.delta_x = float(grid.getDeltaX())
+    sc.delta_x = delta_x
     sc.star_R, sc.clv_u1, sc.clv_u2 = float(star.R), float(star.CLV_u1), float(star.CLV_u2)
     sc.vsini = float(star.vsiniStarrot)
     fstar = getattr(star, "Fstar_function", None)
@@ -211,8 +238,8 @@ def flatten(transit, wavelength=None, wav_range=None) -> tuple[capi.Scene, list,
     b.keep += [scn_arr, cons_arr]
 
     h2d = sum(a.nbytes for a in b.keep if isinstance(a, np.ndarray))
-    info = {"n_x": x.size, "n_rho": rho.size, "n_phi": phi.size, "n_orb": n_orb, "n_wav": wavelength.size,
-            "n_chords": rho.size * phi.size * n_orb, "n_atoms": n_atoms, "n_mols": n_mols,
+    info = {"n_x": x.size, "n_rho": rho.size, "n_phi": sin_phi.size, "n_orb": n_orb, "n_wav": wavelength.size,
+            "n_chords": rho.size * sin_phi.size * n_orb, "n_atoms": n_atoms, "n_mols": n_mols,
             "h2d_bytes": int(h2d)}
     return sc, b.keep, info
 
