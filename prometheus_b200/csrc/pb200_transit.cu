@@ -273,26 +273,31 @@ __device__ __forceinline__ void transit_tile(uint32_t stage, const double (&nsig
 // adds it to its own copies of the chord sums (ThinSums order 2 below 2.1e-5, ThinHi order 8 below 0.1; the lanes'
 // copies are added once, after the last tile) -- 1/32 of the work of letting every thread repeat it.  Only the
 // chords that need the table exp (ballot) are then walked by the whole warp, their records re-read as broadcasts.
-template <int WPT, bool CLAMP, int NWARPS, bool HI>
-__device__ __forceinline__ void transit_tile_sorted(uint32_t stage, const double (&nsig)[1][WPT], double (&acc)[WPT],
-                                                    uint32_t tab_base, double smw0, ThinSums<1>& thin, int wid, int lane,
+template <int S, int WPT, bool CLAMP, int NWARPS, bool HI>
+__device__ __forceinline__ void transit_tile_sorted(uint32_t stage, const double (&nsig)[S][WPT], double (&acc)[WPT],
+                                                    uint32_t tab_base, const double (&smw)[S], ThinSums<S>& thin, int wid, int lane,
                                                     double thin_v, double hi_v, double smin0, ThinHi& hi) {
     static_assert(kChordTile / NWARPS == 32, "one chord per lane");
-    constexpr uint32_t kRecBytes = pb_rec_stride(1) * sizeof(double);   // {w, w c1, w c2, N}
-    double w0, w1, w2, N0;
+    static_assert(S <= 2 && (!HI || S == 1), "chord sums separate for one or two absorbers");
+    constexpr int R = pb_rec_stride(S);
+    constexpr uint32_t kRecBytes = R * sizeof(double);   // {w, w c1, w c2, N_0[, N_1, 0]}
+    double d[R], N[S];
     {
         const uint32_t rec = stage + (uint32_t)(lane * NWARPS + wid) * kRecBytes;
-        lds_v2f64(rec, w0, w1);
-        lds_v2f64(rec + 16, w2, N0);
+#pragma unroll
+        for (int i = 0; i < R / 2; ++i) lds_v2f64(rec + 16 * i, d[2 * i], d[2 * i + 1]);
     }
-    const double bound = N0 * smw0;
+#pragma unroll
+    for (int a = 0; a < S; ++a) N[a] = d[3 + a];
+    double bound = N[0] * smw[0];
+#pragma unroll
+    for (int a = 1; a < S; ++a) bound = fma(N[a], smw[a], bound);
     bool need_exp = false;
     if (bound < thin_v) {
-        const double Nl[1] = {N0};
-        thin.add(w0, w1, w2, Nl);
+        thin.add(d[0], d[1], d[2], N);
     } else if (HI && bound < hi_v) {
-        hi.add(w0, N0);
-    } else if (!(HI && N0 * smin0 > kOpaqueV)) {
+        hi.add(d[0], N[0]);
+    } else if (!(HI && N[0] * smin0 > kOpaqueV)) {
         need_exp = true;
     }
     unsigned mask = __ballot_sync(0xffffffffu, need_exp);
@@ -301,25 +306,29 @@ __device__ __forceinline__ void transit_tile_sorted(uint32_t stage, const double
         const int l = __ffs(mask) - 1;
         mask &= mask - 1;
         const uint32_t rec = stage + (uint32_t)(l * NWARPS + wid) * kRecBytes;
-        double a0, a1, a2, Nb;
-        lds_v2f64(rec, a0, a1);            // broadcast
-        lds_v2f64(rec + 16, a2, Nb);
+        double b[R];
+#pragma unroll
+        for (int i = 0; i < R / 2; ++i) lds_v2f64(rec + 16 * i, b[2 * i], b[2 * i + 1]);   // broadcast
 #pragma unroll
         for (int j = 0; j < WPT; ++j) {
             double t, r;
-            if constexpr (!CLAMP) {
-                t = fma(Nb, nsig[0][j], kExpMagic);                                // -tau in scaled units, :954
-                r = fma(Nb, nsig[0][j], -(t - kExpMagic));
+            if constexpr (S == 1 && !CLAMP) {
+                t = fma(b[3], nsig[0][j], kExpMagic);                              // -tau in scaled units, :954
+                r = fma(b[3], nsig[0][j], -(t - kExpMagic));
             } else {
-                double v = Nb * nsig[0][j];
-                const unsigned hi32 = min((unsigned)__double2hiint(v), kExpBigClampHi);   // tau <= 693.8
-                v = __hiloint2double((int)hi32, __double2loint(v));
+                double v = b[3] * nsig[0][j];
+#pragma unroll
+                for (int a = 1; a < S; ++a) v = fma(b[3 + a], nsig[a][j], v);
+                if (CLAMP) {   // tau <= 693.8 keeps 2^e normal
+                    const unsigned hi32 = min((unsigned)__double2hiint(v), kExpBigClampHi);
+                    v = __hiloint2double((int)hi32, __double2loint(v));
+                }
                 t = v + kExpMagic;
                 r = v - (t - kExpMagic);
             }
             const double T = pb_exp_big_load(tab_base, __double2loint(t));
-            double q = fma(r, a2, a1);
-            q = fma(q, r, a0);                                                     // w exp(r ln2/4096)
+            double q = fma(r, b[2], b[1]);
+            q = fma(q, r, b[0]);                                                   // w exp(r ln2/4096)
             acc[j] = fma(T, q, acc[j]);                                            // :1241, :1244/:1255
         }
     }
@@ -441,17 +450,21 @@ transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
             if (tid == 0 && t + 1 < n_tiles) issue(t + 1, stage ^ 1);
             mbar_wait(&full_bar[stage], (t >> 1) & 1);
             const uint32_t sw = stages_addr + stage * kStageBytes;
-            if constexpr (S == 1) {   // one absorber: lane-parallel per-chord decisions (sorted or not)
-                if (clamp) transit_tile_sorted<WPT, true, NWARPS, HI>(sw, nsig, acc, tab_base, smw[0], thin, wid, lane, prm.thin_v, hi_v, smin0, hi);
-                else transit_tile_sorted<WPT, false, NWARPS, HI>(sw, nsig, acc, tab_base, smw[0], thin, wid, lane, prm.thin_v, hi_v, smin0, hi);
+            if constexpr (S <= 2) {   // one or two absorbers: lane-parallel per-chord decisions (sorted or not)
+                if (clamp) transit_tile_sorted<S, WPT, true, NWARPS, HI>(sw, nsig, acc, tab_base, smw, thin, wid, lane, prm.thin_v, hi_v, smin0, hi);
+                else transit_tile_sorted<S, WPT, false, NWARPS, HI>(sw, nsig, acc, tab_base, smw, thin, wid, lane, prm.thin_v, hi_v, smin0, hi);
             } else {
                 if (clamp) transit_tile<S, WPT, true, NWARPS, HI>(sw, nsig, acc, tab_base, smw, thin, wid, prm.thin_v, hi_v, smin0, hi);
                 else transit_tile<S, WPT, false, NWARPS, HI>(sw, nsig, acc, tab_base, smw, thin, wid, prm.thin_v, hi_v, smin0, hi);
             }
             __syncthreads();   // stage may be refilled by the producer in the next iteration
         }
-        if constexpr (S == 1) {   // the lanes' copies of the chord sums -> warp totals (fixed order)
-            thin.sw = pb_warp_sum(thin.sw); thin.sa[0] = pb_warp_sum(thin.sa[0]); thin.sb[0] = pb_warp_sum(thin.sb[0]);
+        if constexpr (S <= 2) {   // the lanes' copies of the chord sums -> warp totals (fixed order)
+            thin.sw = pb_warp_sum(thin.sw);
+#pragma unroll
+            for (int a = 0; a < S; ++a) thin.sa[a] = pb_warp_sum(thin.sa[a]);
+#pragma unroll
+            for (int a = 0; a < (S == 1 ? 1 : 3); ++a) thin.sb[a] = pb_warp_sum(thin.sb[a]);
             if constexpr (HI) {
 #pragma unroll
                 for (int k = 0; k < 9; ++k) hi.a[k] = pb_warp_sum(hi.a[k]);
