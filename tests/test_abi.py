@@ -107,3 +107,25 @@ def test_full_size_workload_shapes(nist_rows):
         tr = builder.build_transit(workloads.get(name), nist_rows=nist_rows, build_tables=False)
         assert workloads.shape(workloads.get(name))["n_chords"] == n_c
         assert tr.wavelength.size == n_wav
+
+
+def test_flatten_axes_cache_follows_the_grid(nist_rows):
+    """scene.flatten keeps the grid axes per (class, constructor arguments, phiStarrot): a changed grid or rotation
+    angle must give new axes, an unchanged one the very same arrays, all equal to what the grid's methods return."""
+    from prometheus_b200 import scene
+    tr = builder.build_transit(workloads.get("C1"), nist_rows=nist_rows, build_tables=False)
+    for d in tr.atmosphere.densityDistributionList:
+        for con in d.constituents:
+            con.lookupFunction = pb.host.TableFunction1D(np.linspace(5.88e-5, 5.91e-5, 64), np.zeros(64))
+    g = tr.spatialGrid
+    a = scene._axes(g, 0.0)
+    assert scene._axes(g, 0.0)[0] is a[0]
+    assert np.array_equal(a[0], g.constructXaxis()) and np.array_equal(a[1], g.constructRhoAxis())
+    assert np.array_equal(a[2], g.constructOrbphaseAxis()) and np.array_equal(a[3], np.sin(g.constructPhiAxis()))
+    g.x_steps = int(g.x_steps) + 3
+    b = scene._axes(g, 0.0)
+    assert b[0].size == a[0].size + 3 and np.array_equal(b[0], g.constructXaxis()) and b[6] == g.getDeltaX()
+    c = scene._axes(g, 0.25)
+    assert np.array_equal(c[5], np.cos(g.constructPhiAxis() - 0.25)) and not np.array_equal(c[5], b[5])
+    sc, keep, info = scene.flatten(tr)
+    assert info["n_x"] == b[0].size and sc.n_x == b[0].size
