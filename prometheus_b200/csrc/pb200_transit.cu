@@ -342,7 +342,7 @@ __device__ __forceinline__ void transit_tile_sorted(uint32_t stage, const double
 // optical thickness (compact_kernel: longest CTAs first).  A window that is thin for every chord of
 // the phase (S <= 2) needs no chord loop at all: its sums are the per-phase totals of compact_kernel.
 template <int S, int WPT, int THREADS, bool HI>
-__global__ void __launch_bounds__(THREADS, S == 1 ? 3 : 2)
+__global__ void __launch_bounds__(THREADS, (S == 1 && !HI) ? 3 : 2)
 transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
     static_assert(!HI || S == 1, "sigma-sorted windows are for one absorber");
     const DevScene& sc = *scp;
