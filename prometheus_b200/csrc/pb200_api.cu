@@ -687,6 +687,17 @@ static int set_scene_impl(pb200_ctx* c, const pb200_scene* s, int n_ranks, int r
 // =================================================================================================
 namespace {
 
+// Sigma-sorted windows (pb200_sort.cu): one absorber, a wavelength axis and a sky grid large enough that the sort (a
+// device-wide radix sort of n_phase * n_wav keys) is small next to the chord loops it shortens: C5 (36 000 chords per
+// phase x 300 306 wavelengths) 72 -> 24 ms; C2 without its molecules (3 000 x 95 897) would lose 0.2 ms to the sort.
+// PB200_SORT=0/1 forces it.
+bool want_sorted(const pb200_ctx* c, int n_phase, int64_t n_wav_sel) {
+    const DevScene& h = c->h_scene;
+    const bool possible = !c->general_path && h.n_abs == 1 && n_phase < (1 << 20) && (int64_t)n_phase * n_wav_sel < (1ll << 31);
+    if (const char* se = getenv("PB200_SORT")) return possible && se[0] == '1';
+    return possible && n_wav_sel >= (1 << 16) && h.M >= (1 << 14);
+}
+
 int check_scene(pb200_ctx* c) {
     if (!c) return PB200_ERR_INVALID;
     if (!c->has_scene) return fail(c, PB200_ERR_NO_SCENE, "no scene: call pb200_set_scene first");
@@ -745,11 +756,7 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     prm.n_win = (int)((n_wav_sel + prm.win - 1) / prm.win);
     const size_t order_bytes = c->general_path ? 0 : (((size_t)n_phase * prm.n_win * sizeof(int) + 255) & ~size_t(255));
     const size_t winmax_bytes = c->general_path ? 0 : (size_t)h.n_abs * n_phase * prm.n_win * sizeof(double);
-    // Sigma-sorted windows (pb200_sort.cu): one absorber and a wavelength axis long enough that the sort (a
-    // device-wide radix sort of n_phase * n_wav keys) is small next to the chord loops.  PB200_SORT=0/1 forces it.
-    bool sorted = !c->general_path && h.n_abs == 1 && n_wav_sel >= (1 << 16) && n_phase < (1 << 20) && n_out < (1ll << 31);
-    if (const char* se = getenv("PB200_SORT"))
-        sorted = !c->general_path && h.n_abs == 1 && n_phase < (1 << 20) && n_out < (1ll << 31) && se[0] == '1';
+    const bool sorted = want_sorted(c, n_phase, n_wav_sel);
     const size_t al = 255;
     const size_t sort_temp = sorted ? ((sigma_sort_temp_bytes(n_out) + al) & ~al) : 0;
     const size_t sort_bytes = sorted ? (size_t)n_out * (8 + 8 + 8 + 4 + 4) + 5 * 256 + sort_temp : 0;
@@ -937,6 +944,9 @@ extern "C" int pb200_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_l
     // afterwards; PB200_NO_ZEROCOPY=1 (measurement) keeps the copy.
     const char* nz = getenv("PB200_NO_ZEROCOPY");
     double* mapped = (nz && nz[0] == '1') ? nullptr : device_view(R_host, bytes);
+    // the sorted kernel scatters R through a permutation: 8-byte stores over PCIe would be slow, so it writes to
+    // device scratch and R crosses PCIe as one copy
+    if (mapped && wav_lo >= 0 && wav_hi > wav_lo && phase_hi > phase_lo && want_sorted(c, phase_hi - phase_lo, wav_hi - wav_lo)) mapped = nullptr;
     rc = mapped ? enqueue_run(c, phase_lo, phase_hi, wav_lo, wav_hi, mapped, false)
                 : enqueue_run(c, phase_lo, phase_hi, wav_lo, wav_hi, nullptr, true);
     if (rc) return rc;
