@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define PB200_ABI_VERSION 3
+#define PB200_ABI_VERSION 4
 
 typedef enum {
     PB200_OK = 0,
@@ -130,7 +130,7 @@ typedef struct {
 
 /* ---- retrieval batches ------------------------------------------------
  * The consumer sketched by mainRetrieval.py:18-93: many forward models of ONE setup that differ only in
- * free parameters (mainRetrieval.py:18-21: moon phase, orbit, radius; equally N, q, T ...).  Axes, the
+ * free parameters (mainRetrieval.py:18-21: moon phase, orbit, radius; equally N, q, T, R ...).  Axes, the
  * wavelength grid and every table (sigma, F*, molecules, serpens) of the resident scene stay in HBM; a
  * model carries what a free parameter can move: the scenario scalars and the per-phase arrays the host
  * code evaluates with the reference's own expressions.  The models of a batch are stacked along the
@@ -138,11 +138,14 @@ typedef struct {
  * the whole batch. */
 typedef struct {
     const pb200_scenario* scenarios; /* [n_scenarios of the resident scene], same types and constituent
-                                        ranges; read: T is ignored, p[8], centre_x, centre_y, shift,
-                                        amplitude ([n_orb] each; amplitude NULL = 1)                 */
+                                        ranges; read: T (P = n kB T and the temperature axis of molecular
+                                        tables), p[8], centre_x, centre_y, shift, amplitude ([n_orb] each;
+                                        amplitude NULL = 1)                                          */
     const double* planet_y;      /* [n_orb]                                                          */
     const double* moon_R;        /* [n_moons]                                                        */
     const double* moon_y;        /* [n_moons*n_orb]                                                  */
+    double planet_R;             /* radius of the opaque planet disk of this model (blocking mask,
+                                    gasProperties.py:1224); <= 0: the resident scene's               */
 } pb200_model;
 
 /* band-averaged light curve (mainRetrieval.py:72-93): for phase p the filter selects the wavelengths with
@@ -158,6 +161,32 @@ typedef struct {
 } pb200_band;
 
 typedef struct pb200_ctx pb200_ctx;
+
+/* ---- run-time options ---------------------------------------------------------------------
+ * Every default is the production path.  The switches exist for measurement (the brute-force launch the
+ * roofline is quoted on) and for regression tests (each reduction of the work must leave R unchanged); they are
+ * per context and the library never reads the process environment.  MIRROR and GROUP are read by
+ * pb200_set_scene (they shape the resident scene); the others by the next run.                          */
+typedef enum {
+    PB200_OPT_CULL = 0,          /* 1: chords with tau < 2^-54 at every wavelength are summed without a record   */
+    PB200_OPT_MIRROR = 1,        /* 1: chords (phi, rho) and (pi - phi, rho) share one record (set_scene)         */
+    PB200_OPT_THIN = 2,          /* 1: optically thin (chord, window) pairs as a per-chord expansion              */
+    PB200_OPT_GROUP = 3,         /* 1: one absorber per scenario, 0: one per atomic constituent (set_scene)       */
+    PB200_OPT_SORT = 4,          /* -1: automatic, 0 / 1: sigma-sorted windows of kernel (c') forced off / on     */
+    PB200_OPT_MOL_RECORDS = 5,   /* 1: per-record form of kernel (m) instead of the moment form                   */
+    PB200_OPT_ZEROCOPY = 6,      /* 1: pb200_run stores R straight into a page-locked result                      */
+    PB200_OPT_MIN_TILES = 7,     /* least number of active chord tiles per working CTA of kernel (c') (>= 1)      */
+    PB200_OPT_GRAPH = 8,         /* 1: the launches of a run are replayed from a CUDA graph keyed on the tile     */
+    PB200_OPT_COUNT = 9
+} pb200_option;
+int pb200_set_option(pb200_ctx* ctx, int option, int64_t value);
+int pb200_get_option(pb200_ctx* ctx, int option, int64_t* value);
+/* compiled limits: PB200_ERR_INVALID / PB200_ERR_UNSUPPORTED beyond them */
+#define PB200_MAX_SCENARIOS 8
+#define PB200_MAX_CONSTITUENTS 32
+#define PB200_MAX_MOONS 8
+#define PB200_MAX_ABSORBERS 12   /* absorbers of the atomic run path = scenarios with atomic constituents (every
+                                    atomic constituent with PB200_OPT_GROUP = 0); kernel (c') is compiled for 1..12 */
 
 /* ---- life cycle ------------------------------------------------------------------------ */
 int pb200_abi_version(void);

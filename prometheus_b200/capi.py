@@ -12,7 +12,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libprometheus_b200.so")
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 c_double_p = C.POINTER(C.c_double)
 
@@ -26,8 +26,13 @@ EXPORTS = [
     "pb200_set_models", "pb200_lightcurve", "pb200_run_batch",
     "pb200_host_register", "pb200_host_unregister", "pb200_run_scatter", "pb200_sync",
     "pb200_set_scene_sharded", "pb200_table_regions", "pb200_number_density_device",
-    "pb200_serpens_density",
+    "pb200_serpens_density", "pb200_set_option", "pb200_get_option",
 ]
+
+# pb200_option (include/prometheus_b200.h)
+OPT = {"cull": 0, "mirror": 1, "thin": 2, "group": 3, "sort": 4, "mol_records": 5, "zerocopy": 6, "min_tiles": 7, "graph": 8}
+OPT_DEFAULTS = {"cull": 1, "mirror": 1, "thin": 1, "group": 1, "sort": -1, "mol_records": 0, "zerocopy": 1, "min_tiles": 1,
+                "graph": 0}
 
 SCN_BAROMETRIC, SCN_HYDROSTATIC, SCN_POWERLAW, SCN_TORUS, SCN_SERPENS = range(5)
 
@@ -74,7 +79,7 @@ class Scene(C.Structure):
 class Model(C.Structure):
     """pb200_model: what a free parameter of a retrieval can move (mainRetrieval.py:18-21)."""
     _fields_ = [("scenarios", C.POINTER(Scenario)), ("planet_y", c_double_p), ("moon_R", c_double_p),
-                ("moon_y", c_double_p)]
+                ("moon_y", c_double_p), ("planet_R", C.c_double)]
 
 
 class Band(C.Structure):
@@ -141,6 +146,8 @@ def load():
         "pb200_last_error": (C.c_char_p, [vp]),
         "pb200_set_stream": (C.c_int, [vp, vp]),
         "pb200_launch_count": (i64, [vp]),
+        "pb200_set_option": (C.c_int, [vp, i32, i64]),
+        "pb200_get_option": (C.c_int, [vp, i32, C.POINTER(i64)]),
         "pb200_host_alloc": (C.c_int, [C.c_size_t, C.POINTER(vp)]),
         "pb200_host_free": (C.c_int, [vp]),
         "pb200_set_scene": (C.c_int, [vp, C.POINTER(Scene)]),
@@ -288,6 +295,32 @@ class Context:
 
     def launch_count(self) -> int:
         return int(self.lib.pb200_launch_count(self.handle))
+
+    def set_option(self, name: str, value: int):
+        """pb200_set_option by name (capi.OPT).  MIRROR and GROUP take effect at the next set_scene."""
+        self.check(self.lib.pb200_set_option(self.handle, OPT[name], int(value)))
+
+    def get_option(self, name: str) -> int:
+        v = C.c_int64()
+        self.check(self.lib.pb200_get_option(self.handle, OPT[name], C.byref(v)))
+        return int(v.value)
+
+    def options(self, **kw):
+        """Context manager: the given options for the duration of the block, the previous values afterwards."""
+        ctx = self
+
+        class _Scope:
+            def __enter__(self):
+                self.saved = {k: ctx.get_option(k) for k in kw}
+                for k, v in kw.items():
+                    ctx.set_option(k, v)
+                return ctx
+
+            def __exit__(self, *exc):
+                for k, v in self.saved.items():
+                    ctx.set_option(k, v)
+
+        return _Scope()
 
     def set_scene(self, scene: Scene, keep):
         self._keep = keep

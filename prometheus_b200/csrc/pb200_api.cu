@@ -119,6 +119,8 @@ struct pb200_ctx {
     int mol_bins = -1;
     bool buckets_ready = false;   // bucket indices of the sigma tables (built on the device before the first run of a scene)
     std::vector<std::pair<void*, int64_t>> regions;   // sharded uploads of the current scene: (device base, doubles per rank)
+    // run-time options (pb200_set_option); the library never reads the environment
+    int64_t opt[PB200_OPT_COUNT] = {1, 1, 1, 1, -1, 0, 1, 1, 0};
 };
 
 static int fail(pb200_ctx* c, int code, const char* fmt, ...) {
@@ -265,6 +267,24 @@ int pb200_set_stream(pb200_ctx* c, void* cuda_stream) {
 }
 
 int64_t pb200_launch_count(pb200_ctx* c) { return c ? c->launches : 0; }
+
+int pb200_set_option(pb200_ctx* c, int option, int64_t value) {
+    if (!c) return PB200_ERR_INVALID;
+    if (option < 0 || option >= PB200_OPT_COUNT) return fail(c, PB200_ERR_INVALID, "pb200_set_option: unknown option %d", option);
+    const bool ok = option == PB200_OPT_SORT ? (value >= -1 && value <= 1)
+                  : option == PB200_OPT_MIN_TILES ? (value >= 1 && value <= (1 << 20))
+                  : (value == 0 || value == 1);
+    if (!ok) return fail(c, PB200_ERR_INVALID, "pb200_set_option: value %lld out of range for option %d", (long long)value, option);
+    c->opt[option] = value;
+    return PB200_OK;
+}
+
+int pb200_get_option(pb200_ctx* c, int option, int64_t* value) {
+    if (!c || !value) return PB200_ERR_INVALID;
+    if (option < 0 || option >= PB200_OPT_COUNT) return fail(c, PB200_ERR_INVALID, "pb200_get_option: unknown option %d", option);
+    *value = c->opt[option];
+    return PB200_OK;
+}
 
 int pb200_host_alloc(size_t bytes, void** out) {
     if (!out) return PB200_ERR_INVALID;
@@ -626,8 +646,7 @@ static int set_scene_impl(pb200_ctx* c, const pb200_scene* s, int n_ranks, int r
     }
     h.n_atoms = n_atoms; h.n_mols = n_mols;
     {   // absorbers of the run path (see DevScene::n_abs)
-        const char* ng = getenv("PB200_NO_GROUP");
-        const bool group = !(ng && ng[0] == '1');
+        const bool group = c->opt[PB200_OPT_GROUP] != 0;
         h.n_abs = 0;
         for (int i = 0; i < s->n_scenarios; ++i) {
             const pb200_scenario& q = s->scenarios[i];
@@ -658,8 +677,7 @@ static int set_scene_impl(pb200_ctx* c, const pb200_scene* s, int n_ranks, int r
                 const int a = hh * n2 + i, b = hh * n2 + n2 - 1 - i;
                 ok = fabs(s->sin_phi[a] - s->sin_phi[b]) <= 1e-14 && fabs(s->cos_phi[a] + s->cos_phi[b]) <= 1e-14;
             }
-        const char* off = getenv("PB200_NO_MIRROR");   // measurement / debugging only
-        h.mirror = (ok && !(off && off[0] == '1')) ? 1 : 0;
+        h.mirror = (ok && c->opt[PB200_OPT_MIRROR] != 0) ? 1 : 0;
     }
     h.fout_per_wav = (h.n_fstar > 0 && h.vsini != 0.0) ? 1 : 0;
     h.n_orb_model = h.n_orb;
@@ -690,11 +708,11 @@ namespace {
 // Sigma-sorted windows (pb200_sort.cu): one absorber, a wavelength axis and a sky grid large enough that the sort (a
 // device-wide radix sort of n_phase * n_wav keys) is small next to the chord loops it shortens: C5 (36 000 chords per
 // phase x 300 306 wavelengths) 72 -> 24 ms; C2 without its molecules (3 000 x 95 897) would lose 0.2 ms to the sort.
-// PB200_SORT=0/1 forces it.
+// PB200_OPT_SORT = 0 / 1 forces it.
 bool want_sorted(const pb200_ctx* c, int n_phase, int64_t n_wav_sel) {
     const DevScene& h = c->h_scene;
     const bool possible = !c->general_path && h.n_abs == 1 && n_phase < (1 << 20) && (int64_t)n_phase * n_wav_sel < (1ll << 31);
-    if (const char* se = getenv("PB200_SORT")) return possible && se[0] == '1';
+    if (c->opt[PB200_OPT_SORT] >= 0) return possible && c->opt[PB200_OPT_SORT] == 1;
     return possible && n_wav_sel >= (1 << 16) && h.M >= (1 << 14);
 }
 
@@ -741,11 +759,9 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     prm.tiles_per_split = (int)((n_tiles + want - 1) / want);
     prm.n_split = (n_tiles + prm.tiles_per_split - 1) / prm.tiles_per_split;
     {
-        const char* mt = getenv("PB200_MIN_TILES");   // tuning experiments only
-        prm.min_tiles = mt ? atoi(mt) : 1;
+        prm.min_tiles = (int)c->opt[PB200_OPT_MIN_TILES];   // tuning experiments only
         prm.culled = c->general_path ? 0 : 1;
-        const char* nt = getenv("PB200_NO_THIN");     // measurement only: every active sample through the table exp
-        prm.thin_v = (nt && nt[0] == '1') ? 0.0 : 0.125;
+        prm.thin_v = c->opt[PB200_OPT_THIN] ? 0.125 : 0.0;   // 0 (measurement only): every active sample through the table exp
         if (prm.min_tiles < 1) prm.min_tiles = 1;
     }
 
@@ -774,6 +790,8 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     PB_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
     if (!c->general_path) {   // sigma(p, w) of the tile and its per-phase maxima, needed by the culling below
         if (h.n_atoms < 1) return fail(c, PB200_ERR_INVALID, "scene has no absorbing constituent");
+        if (h.n_abs > PB200_MAX_ABSORBERS)   // before any kernel that sizes shared memory by the absorber count
+            return fail(c, PB200_ERR_UNSUPPORTED, "%d absorbers (scenarios with atomic constituents); kernel (c') is compiled for <= %d", h.n_abs, PB200_MAX_ABSORBERS);
         // smax is left clean by compact_kernel of the previous run (and by pb200_set_scene), the run
         // statistics are reset by sigma_phase_kernel: no memset nodes in the run
         if (!c->buckets_ready) {   // after the (possibly sharded + all-gathered) tables are complete on the device
@@ -798,10 +816,9 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
             prm.perm = perm;
         }
     }
-    // PB200_NO_CULL=1 (measurement only): every unblocked chord gets its exact sums and a record, as in the
+    // PB200_OPT_CULL = 0 (measurement only): every unblocked chord gets its exact sums and a record, as in the
     // reference's loop
-    const char* no_cull = getenv("PB200_NO_CULL");
-    const bool cull = !(no_cull && no_cull[0] == '1');
+    const bool cull = c->opt[PB200_OPT_CULL] != 0;
     launch_column(c->d_scene, h.Mp, phase_lo, n_phase, c->d_oob, c->sm_count, c->stream, h.n_mols > 0,
                   c->general_path ? 0 : (cull ? 1 : 2));
     c->launches += 1;
@@ -812,11 +829,10 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     PB_CUDA(c, cudaGetLastError());
     PB_CUDA(c, cudaEventRecord(c->ev[3], c->stream));
     // Kernel (m) runs in moment form unless the tables are too steep for it (more than 64 sub-intervals per pressure
-    // interval would be needed), its blocks do not fit shared memory, or PB200_MOL_RECORDS=1 asks for the per-record
+    // interval would be needed), its blocks do not fit shared memory, or PB200_OPT_MOL_RECORDS asks for the per-record
     // form (measurement / regression).
-    const char* rec_env = getenv("PB200_MOL_RECORDS");
     bool moments_done = false;
-    if (c->general_path && h.n_mols > 0 && !(rec_env && rec_env[0] == '1')) {
+    if (c->general_path && h.n_mols > 0 && !c->opt[PB200_OPT_MOL_RECORDS]) {
         if (!c->d_mol_stat) PB_CUDA(c, cudaMalloc((void**)&c->d_mol_stat, 16));
         unsigned long long st[2] = {0ull, 0ull};
         if (c->mol_bins < 0) {   // d_max of the tables, once per scene
@@ -867,8 +883,6 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
         c->launches += n_launch;
     } else {
         cudaError_t e = launch_transit(c->d_scene, h.n_abs, prm, c->stream);
-        if (e == cudaErrorInvalidValue && h.n_abs > 12)
-            return fail(c, PB200_ERR_UNSUPPORTED, "%d absorbers (scenarios with atomic constituents); kernel (c') is compiled for <= 12", h.n_abs);
         if (e != cudaSuccess) return fail(c, PB200_ERR_CUDA, "transit launch: %s", cudaGetErrorString(e));
         c->launches += 1;
     }
@@ -941,9 +955,8 @@ extern "C" int pb200_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_l
     const size_t bytes = (size_t)(phase_hi - phase_lo) * (size_t)(wav_hi - wav_lo) * sizeof(double);
     // A result array in page-locked memory of pb200_host_alloc / pb200_host_register is written by the kernels
     // themselves (zero-copy stores over PCIe as the windows finish) instead of device scratch + a D2H copy
-    // afterwards; PB200_NO_ZEROCOPY=1 (measurement) keeps the copy.
-    const char* nz = getenv("PB200_NO_ZEROCOPY");
-    double* mapped = (nz && nz[0] == '1') ? nullptr : device_view(R_host, bytes);
+    // afterwards; PB200_OPT_ZEROCOPY = 0 (measurement) keeps the copy.
+    double* mapped = c->opt[PB200_OPT_ZEROCOPY] ? device_view(R_host, bytes) : nullptr;
     // the sorted kernel scatters R through a permutation: 8-byte stores over PCIe would be slow, so it writes to
     // device scratch and R crosses PCIe as one copy
     if (mapped && wav_lo >= 0 && wav_hi > wav_lo && phase_hi > phase_lo && want_sorted(c, phase_hi - phase_lo, wav_hi - wav_lo)) mapped = nullptr;
@@ -1126,7 +1139,7 @@ extern "C" int pb200_set_models(pb200_ctx* c, int n_models, const pb200_model* m
         // layout of the model arena, in doubles
         size_t off = 0;
         auto take = [&](size_t n) { const size_t o = off; off += (n + 31) & ~size_t(31); return o; };
-        const size_t o_py = take(n_tot);
+        const size_t o_py = take(n_tot), o_pR = take(n_tot);
         const size_t o_mR = b.n_moons ? take((size_t)b.n_moons * n_tot) : 0;
         const size_t o_my = b.n_moons ? take((size_t)b.n_moons * n_tot) : 0;
         struct SO { size_t cx, cy, sh, amp, pp; bool has_centre, has_amp; };
@@ -1162,6 +1175,7 @@ extern "C" int pb200_set_models(pb200_ctx* c, int n_models, const pb200_model* m
             const pb200_model& q = models[m];
             const size_t r0 = (size_t)m * nb;
             memcpy(st + o_py + r0, q.planet_y, row);
+            for (int p = 0; p < nb; ++p) st[o_pR + r0 + p] = q.planet_R > 0.0 ? q.planet_R : b.planet_R;
             for (int k = 0; k < b.n_moons; ++k) {
                 memcpy(st + o_my + (size_t)k * n_tot + r0, q.moon_y + (size_t)k * nb, row);
                 for (int p = 0; p < nb; ++p) st[o_mR + (size_t)k * n_tot + r0 + p] = q.moon_R[k];
@@ -1172,7 +1186,10 @@ extern "C" int pb200_set_models(pb200_ctx* c, int n_models, const pb200_model* m
                 memcpy(st + so[i].sh + r0, qs.shift, row);
                 if (so[i].has_amp)
                     for (int p = 0; p < nb; ++p) st[so[i].amp + r0 + p] = qs.amplitude ? qs.amplitude[p] : 1.0;
-                for (int p = 0; p < nb; ++p) memcpy(st + so[i].pp + (r0 + p) * 8, qs.p, 8 * sizeof(double));
+                for (int p = 0; p < nb; ++p) {
+                    memcpy(st + so[i].pp + (r0 + p) * 8, qs.p, 7 * sizeof(double));
+                    st[so[i].pp + (r0 + p) * 8 + 7] = qs.T;   // pb_scn_T
+                }
             }
         }
         PB_CUDA(c, cudaMemcpyAsync(c->marena, c->mstage, bytes, cudaMemcpyHostToDevice, c->stream));
@@ -1181,6 +1198,7 @@ extern "C" int pb200_set_models(pb200_ctx* c, int n_models, const pb200_model* m
         h = b;
         h.n_orb = n_tot; h.n_orb_model = nb;
         h.planet_y = A + o_py;
+        h.planet_R_phase = A + o_pR;
         if (b.n_moons) { h.moon_R = A + o_mR; h.moon_y = A + o_my; h.moon_R_per_phase = 1; }
         for (int i = 0; i < b.n_scen; ++i) {
             DevScenario& d = h.scen[i];

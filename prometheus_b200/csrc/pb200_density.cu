@@ -34,7 +34,7 @@ __global__ void sky_cell_kernel(const DevScene* __restrict__ scp) {
 __device__ __forceinline__ bool pb_blocked(const DevScene& sc, int p, double y, double z) {
     const double z2 = __dmul_rn(z, z);
     const double dyp = __dsub_rn(y, sc.planet_y[p]);
-    bool blocked = __dsqrt_rn(__dadd_rn(__dmul_rn(dyp, dyp), z2)) < sc.planet_R;
+    bool blocked = __dsqrt_rn(__dadd_rn(__dmul_rn(dyp, dyp), z2)) < (sc.planet_R_phase ? sc.planet_R_phase[p] : sc.planet_R);
     for (int k = 0; k < sc.n_moons; ++k) {
         const double dym = __dsub_rn(y, sc.moon_y[k * sc.n_orb + p]);
         const double Rm = sc.moon_R_per_phase ? sc.moon_R[k * sc.n_orb + p] : sc.moon_R[k];
@@ -222,7 +222,11 @@ __device__ __forceinline__ double pb_column_bound(const DevScene& sc, const DevS
             const double jc = P[2] / P[3];
             return n0 * ((rmin < P[1]) ? 1.0 : exp(jc / rmin - jc / P[1]));
         }
-        case PB200_SCN_POWERLAW: return n0 * ((rmin < P[1]) ? 1.0 : exp(P[2] * (log(P[1]) - log(rmin))));
+        case PB200_SCN_POWERLAW:
+            // (R/r)^q falls with r only for q > 0; for q <= 0 (the reference accepts any q) the closest approach is not
+            // the maximum: no cheap bound
+            if (!(P[2] > 0.0)) return __longlong_as_double(0x7ff0000000000000ll);
+            return n0 * ((rmin < P[1]) ? 1.0 : exp(P[2] * (log(P[1]) - log(rmin))));
         case PB200_SCN_TORUS: { const double qz = z / P[2]; return n0 * exp(-(qz * qz)); }
         default: return __longlong_as_double(0x7ff0000000000000ll);
     }
@@ -337,7 +341,7 @@ __global__ void __launch_bounds__(kCompactThreads) compact_kernel(const DevScene
     const int phase_lo = prm.phase_lo;
     const int p = phase_lo + blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int S = sc.n_abs, R = pb_rec_stride(S);
-    __shared__ double s_smax[16];
+    __shared__ double s_smax[kMaxConstituents];
     __shared__ int s_warp[32];
     __shared__ double s_part[32];
     __shared__ int s_base;

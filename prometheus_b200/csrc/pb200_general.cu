@@ -71,13 +71,14 @@ __device__ __forceinline__ void pb_general_prologue(const DevScene& sc, int p, d
                 sig[C.atom_index * kGenThreads + tid] = pb_interp_log(C.tab_x, C.tab_y, C.n_tab, sl, C.offset);
             } else {
                 const MolTable t = pb_mol_table(C);
+                const double Tk = pb_scn_T(S, p);
                 // outside the table in T or lambda: every sample takes the fill value (:779 bounds_error=False)
-                const bool inside = (S.T >= t.gT[0] && S.T <= t.gT[t.nT - 1] && sl >= t.gW[0] && sl <= t.gW[t.nW - 1]);
+                const bool inside = (Tk >= t.gT[0] && Tk <= t.gT[t.nT - 1] && sl >= t.gW[0] && sl <= t.gW[t.nW - 1]);
                 int iT = 0, iW = 0;
                 double fT = 0.0, fW = 0.0;
                 if (inside) {
-                    iT = pb_interval(t.gT, t.nT, S.T); iW = pb_interval(t.gW, t.nW, sl);
-                    fT = (S.T - t.gT[iT]) / (t.gT[iT + 1] - t.gT[iT]);
+                    iT = pb_interval(t.gT, t.nT, Tk); iW = pb_interval(t.gW, t.nW, sl);
+                    fT = (Tk - t.gT[iT]) / (t.gT[iT + 1] - t.gT[iT]);
                     fW = (sl - t.gW[iW]) / (t.gW[iW + 1] - t.gW[iW]);
                 }
                 for (int j = 0; j < t.nP; ++j) {
@@ -206,7 +207,7 @@ transit_general_kernel(const DevScene* __restrict__ scp, const TransitParams prm
                     const double* dens = sc.density[S.density_slot] + ((int64_t)p * sc.M + m) * sc.n_x;
                     const int nP = C.dims[0];
                     const double* g = pgrid + node0;
-                    const double kT = kBoltzmann * S.T, g0 = g[0], g1 = g[nP - 1];
+                    const double kT = kBoltzmann * pb_scn_T(S, p), g0 = g[0], g1 = g[nP - 1];
                     double part = 0.0;
                     for (int ix0 = 0; ix0 < sc.n_x; ix0 += 32) {
                         const int ix = ix0 + lane;
@@ -400,7 +401,7 @@ mol_moment_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, i
                 const double* __restrict__ dens = sc.density[S.density_slot] + ((int64_t)p * sc.M + m) * sc.n_x;
                 const double* __restrict__ g = C.grid_P;
                 const int nP = C.dims[0];
-                const double kT = kBoltzmann * S.T, g0 = __ldg(g), g1 = __ldg(g + nP - 1);
+                const double kT = kBoltzmann * pb_scn_T(S, p), g0 = __ldg(g), g1 = __ldg(g + nP - 1);
                 double part = 0.0, M[kMolK + 1], tc = 0.0;
                 int cur = -1, cur_joff = 0;
                 auto flush = [&]() {

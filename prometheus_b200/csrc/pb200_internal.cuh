@@ -8,16 +8,17 @@
 
 namespace pb200 {
 
-constexpr int kMaxScenarios = 8;
-constexpr int kMaxConstituents = 32;
-constexpr int kMaxMoons = 8;
+constexpr int kMaxScenarios = PB200_MAX_SCENARIOS;
+constexpr int kMaxConstituents = PB200_MAX_CONSTITUENTS;
+constexpr int kMaxMoons = PB200_MAX_MOONS;
 constexpr int kChordTile = 256;   // chords per shared-memory tile of kernel (c'); rows are padded to it
 
 struct DevScenario {
     int type, n_cons, first_cons, has_molecule;
     double T;
     double p[8];
-    const double* p_phase;   // NULL or [n_orb][8]: per-(virtual-)phase parameters of a retrieval batch (pb200_set_models)
+    const double* p_phase;   // NULL or [n_orb][8]: per-(virtual-)phase parameters of a retrieval batch (pb200_set_models);
+                             // slot 7 carries the model's temperature T (no scenario uses more than p[0..3])
     const double* centre_x;
     const double* centre_y;
     const double* shift;
@@ -60,6 +61,7 @@ struct DevScene {
     const double* cos_phi_rot; const double* wavelength;
     const double* fstar_x; const double* fstar_y; int64_t n_fstar;
     const double* planet_y; const double* moon_R; const double* moon_y;
+    const double* planet_R_phase;   // NULL, or [n_orb]: planet radius of the model a (virtual) phase belongs to
     DevScenario scen[kMaxScenarios];
     DevConstituent cons[kMaxConstituents];
     // derived, device-resident, phase-major ("m" = i_phi*n_rho + i_rho):
@@ -149,6 +151,11 @@ __device__ __forceinline__ double pb_heaviside1(double u) { return (u < 0.0) ? 0
 // scalar parameters of a scenario at (virtual) phase p
 __device__ __forceinline__ const double* pb_params(const DevScenario& s, int p) {
     return s.p_phase ? s.p_phase + (int64_t)p * 8 : s.p;
+}
+
+// temperature of a scenario at (virtual) phase p: P = n kB T, the T axis of molecular tables (gasProperties.py:927)
+__device__ __forceinline__ double pb_scn_T(const DevScenario& s, int p) {
+    return s.p_phase ? s.p_phase[(int64_t)p * 8 + 7] : s.T;
 }
 
 __device__ __forceinline__ double pb_density(const DevScenario& s, const double* __restrict__ sp, double amp, double dx,

@@ -152,10 +152,11 @@ optical_depth_kernel(const DevScene* __restrict__ scp, const double* __restrict_
                 const double lam = S.shift[p] * sc.wavelength[wav_lo + w];
                 const double* dens = sc.density[S.density_slot] + ((int64_t)p * sc.M + m) * sc.n_x;
                 double s = 0.0;
+                const double Tk = pb_scn_T(S, p);
                 for (int ix = 0; ix < sc.n_x; ++ix) {
                     const double n = dens[ix];
-                    const double Pc = fmax(n * kBoltzmann * S.T, 1e-4);                       // :927, :805
-                    const double sg = exp10(pb_mol_log_sigma(tab, Pc, S.T, lam)) - C.offset;
+                    const double Pc = fmax(n * kBoltzmann * Tk, 1e-4);                        // :927, :805
+                    const double sg = exp10(pb_mol_log_sigma(tab, Pc, Tk, lam)) - C.offset;
                     s = fma(n * C.chi, sg, s);                                                // :932-936
                 }
                 t += s * sc.delta_x;

@@ -308,17 +308,17 @@ class SharedResult:
         return k, view, dev
 
     def end(self, k: int, view):
-        """Call after this rank's stream is synchronised.  Rank 0 waits for every rank and gets the array (given
-        back to the pool when it is garbage collected); the others return None."""
-        import weakref
+        """Call after this rank's stream is synchronised.  Rank 0 waits for every rank and gets the array; the others
+        return None.  The segment goes back to the pool when the LAST array that looks into it dies: the returned
+        array and every slice or view taken from it have one `_ResultToken` as their ultimate base (numpy collapses
+        `.base` chains onto it), and the give-back hangs on that token, not on the outermost array object."""
         self.ctl[self.CTL_WORDS + self.rank] = self.seq
         if self.rank != 0:
             return None
         flags = self.ctl[self.CTL_WORDS:]
         self._spin(lambda: bool(np.all(flags >= self.seq)), "the other ranks' tiles")
-        out = view.view()
-        weakref.finalize(out, self.free.append, k)
-        return out
+        token = _ResultToken(self.segments[k][2], view.nbytes, self.free, k, view)
+        return np.asarray(token).view(np.float64).reshape(view.shape)
 
     def close(self):
         for k, (shm, dev, addr) in list(self.segments.items()):
@@ -333,6 +333,22 @@ class SharedResult:
             self.ctl = None
             self.ctl_shm.close()
             self.ctl_shm = None
+
+
+class _ResultToken:
+    """Lifetime token of one handed-out result: exposes the segment's memory through __array_interface__, so every
+    numpy array derived from the result keeps it alive; returns the segment index to the pool's free list when the
+    last of them is gone (capi._PinnedBlock does the same for page-locked blocks)."""
+
+    def __init__(self, addr: int, nbytes: int, free_list: list, k: int, keep):
+        self._free, self._k, self._keep = free_list, k, keep      # keep: the mmap-backed view (the mapping stays valid)
+        self.__array_interface__ = {"shape": (int(nbytes),), "typestr": "|u1", "data": (int(addr), False), "version": 3}
+
+    def __del__(self):
+        try:
+            self._free.append(self._k)
+        except Exception:
+            pass
 
 
 class _Segment:

@@ -258,6 +258,7 @@ def flatten_model(transit, phase=None) -> tuple[capi.Model, list]:
     n_orb = phase.size
     mdl = capi.Model()
     mdl.planet_y = b.ptr(planet.a * np.sin(phase))                               # gasProperties.py:1224
+    mdl.planet_R = float(planet.R)
     moons_R, moons_y = [], []
     for dist in dists:
         if getattr(dist, "hasMoon", False):                                      # gasProperties.py:1226-1230
@@ -319,6 +320,7 @@ def flatten_models_broadcast(transit, phase, n_models: int):
     keep.append(scn)
     models["scenarios"] = scn.ctypes.data + np.arange(K, dtype=np.uint64) * np.uint64(scn.strides[0])
     models["planet_y"] = rows(planet.a * np.sin(ph))                             # gasProperties.py:1224
+    models["planet_R"] = np.broadcast_to(np.asarray(planet.R, dtype=np.float64).reshape(-1), (K,))
     moons_R, moons_y = [], []
     for dist in dists:
         if getattr(dist, "hasMoon", False):                                      # gasProperties.py:1226-1230

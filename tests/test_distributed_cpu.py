@@ -148,3 +148,36 @@ def test_shared_result_protocol(world, n_orb, n_wav):
         p.join(timeout=60)
         assert p.exitcode == 0
     assert all(ok for _, ok in results), results
+
+
+def test_shared_result_segment_lives_as_long_as_any_slice_of_it():
+    """A caller that keeps only a slice of the returned array (R[0], R[:, lo:hi]) still owns the segment: it must not
+    go back to the pool -- and be overwritten by the next call's kernels -- while that slice is alive."""
+    import gc
+    sr = pbd.SharedResult(1, 0, f"slice{os.getpid()}", timeout=10.0)
+    try:
+        k0, view, _ = sr.begin(4, 100)
+        view[...] = 7.0
+        R = sr.end(k0, view)
+        row = R[1]                      # numpy collapses .base: the slice does not reference R itself
+        part = R[:, 10:20]
+        del R, view
+        gc.collect()
+        assert sr.free == [], "segment given back while slices of the result are alive"
+        k1, view1, _ = sr.begin(4, 100)
+        view1[...] = -1.0               # what the next call's kernels would store
+        assert k1 != k0 and np.all(row == 7.0) and np.all(part == 7.0)
+        R1 = sr.end(k1, view1)
+        del row
+        gc.collect()
+        assert sr.free == []            # `part` still holds segment k0
+        del part
+        gc.collect()
+        assert sr.free == [k0]
+        k2, view2, _ = sr.begin(4, 100)
+        assert k2 == k0                 # recycled only now
+        sr.end(k2, view2)
+        del R1, view1, view2
+    finally:
+        gc.collect()
+        sr.close()

@@ -286,13 +286,11 @@ def test_trimmed_sigma_tables_are_bit_identical(ctx, transits):
 ATOM_CASES = ["C1", "C3s", "C4s", "C5s", "PLNs", "THMs", "SERs", "HYDs"]
 
 
-def run_with_env(tr, monkeypatch, **env):
-    for k, v in env.items():
-        monkeypatch.setenv(k, v)
-    R = tr.sumOverChords()
-    t = dict(tr.last_timing)
-    for k in env:
-        monkeypatch.delenv(k)
+def run_with_env(tr, monkeypatch=None, **opts):
+    """One Transit.sumOverChords with the given pb200_set_option values (capi.OPT names), defaults restored after."""
+    with host.get_context(0).options(**opts):
+        R = tr.sumOverChords()
+        t = dict(tr.last_timing)
     return R, t
 
 
@@ -304,11 +302,11 @@ def test_culling_and_mirror_leave_R_unchanged(name, transits, monkeypatch):
     if any(con.isMolecule for d in tr.atmosphere.densityDistributionList for con in d.constituents):
         pytest.skip("kernel (m) has no culling")
     R, t = run_with_env(tr, monkeypatch)
-    R_full, t_full = run_with_env(tr, monkeypatch, PB200_NO_CULL="1", PB200_NO_MIRROR="1")
-    R_nocull, t_nocull = run_with_env(tr, monkeypatch, PB200_NO_CULL="1")
-    R_nomirror, t_nomirror = run_with_env(tr, monkeypatch, PB200_NO_MIRROR="1")
-    R_nothin, t_nothin = run_with_env(tr, monkeypatch, PB200_NO_THIN="1")
-    R_brute, t_brute = run_with_env(tr, monkeypatch, PB200_NO_CULL="1", PB200_NO_MIRROR="1", PB200_NO_THIN="1")
+    R_full, t_full = run_with_env(tr, monkeypatch, cull=0, mirror=0)
+    R_nocull, t_nocull = run_with_env(tr, monkeypatch, cull=0)
+    R_nomirror, t_nomirror = run_with_env(tr, monkeypatch, mirror=0)
+    R_nothin, t_nothin = run_with_env(tr, monkeypatch, thin=0)
+    R_brute, t_brute = run_with_env(tr, monkeypatch, cull=0, mirror=0, thin=0)
     for other in (R_full, R_nocull, R_nomirror, R_nothin, R_brute):
         assert np.max(np.abs(R - other)) < 5e-14
     assert t["exp_samples"] <= t_nothin["exp_samples"]
@@ -327,21 +325,21 @@ def test_culling_and_mirror_leave_R_unchanged(name, transits, monkeypatch):
 
 def test_mirror_pairing_halves_the_records_when_the_scene_is_symmetric(transits, monkeypatch):
     tr = transits("C5s")           # power law around the planet, even n_phi
-    _, t_pair = run_with_env(tr, monkeypatch, PB200_NO_CULL="1")
-    _, t_full = run_with_env(tr, monkeypatch, PB200_NO_CULL="1", PB200_NO_MIRROR="1")
+    _, t_pair = run_with_env(tr, monkeypatch, cull=0)
+    _, t_full = run_with_env(tr, monkeypatch, cull=0, mirror=0)
     assert t_pair["executed_samples"] <= 0.6 * t_full["executed_samples"]
 
 
 def test_mirror_pairing_is_off_for_tabulated_densities_and_odd_phi(transits, nist_rows, monkeypatch):
     tr = transits("SERs")          # SERPENS histogram: no z symmetry
-    _, t_a = run_with_env(tr, monkeypatch, PB200_NO_CULL="1")
-    _, t_b = run_with_env(tr, monkeypatch, PB200_NO_CULL="1", PB200_NO_MIRROR="1")
+    _, t_a = run_with_env(tr, monkeypatch, cull=0)
+    _, t_b = run_with_env(tr, monkeypatch, cull=0, mirror=0)
     assert t_a["executed_samples"] == t_b["executed_samples"]
     spec = workloads.get("C4s")
     spec["grid"] = _with_phi(spec["grid"], 31)
     odd = builder.build_transit(spec, nist_rows=nist_rows)
-    R_a, t_a = run_with_env(odd, monkeypatch, PB200_NO_CULL="1")
-    R_b, t_b = run_with_env(odd, monkeypatch, PB200_NO_CULL="1", PB200_NO_MIRROR="1")
+    R_a, t_a = run_with_env(odd, monkeypatch, cull=0)
+    R_b, t_b = run_with_env(odd, monkeypatch, cull=0, mirror=0)
     assert t_a["executed_samples"] == t_b["executed_samples"]
     assert np.array_equal(R_a, R_b)
 
@@ -395,7 +393,7 @@ def test_block_cyclic_tiles_reassemble_R(name, n_ranks, transits, ctx):
 
 def test_absorber_grouping_leaves_R_unchanged(nist_rows, golden, monkeypatch):
     """One absorber per scenario (effective cross section sum_k chi_k sigma_k) against one per constituent
-    (PB200_NO_GROUP=1): the same tau up to the order of two roundings.  C5s: Fe I + Fe II in one power-law
+    (PB200_OPT_GROUP = 0): the same tau up to the order of two roundings.  C5s: Fe I + Fe II in one power-law
     atmosphere; HYDs: two scenarios with one constituent each (nothing to merge, identical bits)."""
     from prometheus_b200 import scene
     ctx = host.get_context(0)
@@ -403,11 +401,10 @@ def test_absorber_grouping_leaves_R_unchanged(nist_rows, golden, monkeypatch):
         tr = builder.build_transit(workloads.get(name), nist_rows=nist_rows)
         out = {}
         for flag in ("0", "1"):
-            monkeypatch.setenv("PB200_NO_GROUP", flag)
-            sc, keep, info = scene.flatten(tr)
-            ctx.set_scene(sc, keep)
-            out[flag], _ = ctx.run(0, info["n_orb"], 0, info["n_wav"])
-        monkeypatch.delenv("PB200_NO_GROUP")
+            with ctx.options(group=0 if flag == "1" else 1):
+                sc, keep, info = scene.flatten(tr)
+                ctx.set_scene(sc, keep)
+                out[flag], _ = ctx.run(0, info["n_orb"], 0, info["n_wav"])
         if merged:
             assert np.max(np.abs(out["0"] - out["1"])) < 5e-14
         else:
@@ -419,7 +416,7 @@ def test_absorber_grouping_leaves_R_unchanged(nist_rows, golden, monkeypatch):
 
 def test_moment_form_of_the_molecular_kernel(nist_rows, golden, monkeypatch):
     """Kernel (m) in moment form (items per pressure interval, computed once per chord) against its per-record form
-    (PB200_MOL_RECORDS=1): same tau up to the 9e-13 truncation of the expansion, and both within the parity
+    (PB200_OPT_MOL_RECORDS = 1): same tau up to the 9e-13 truncation of the expansion, and both within the parity
     criterion of the reference output."""
     from prometheus_b200 import scene
     ctx = host.get_context(0)
@@ -427,13 +424,12 @@ def test_moment_form_of_the_molecular_kernel(nist_rows, golden, monkeypatch):
     sc, keep, info = scene.flatten(tr)
     out = {}
     for flag in ("1", "0"):
-        monkeypatch.setenv("PB200_MOL_RECORDS", flag)
-        ctx.set_scene(sc, keep)
-        out[flag], _ = ctx.run(0, info["n_orb"], 0, info["n_wav"])
-        # tiles: a sub-range of phases and wavelengths sees the same items
-        tile, _ = ctx.run(1, 3, 100, 700)
-        assert np.max(np.abs(tile - out[flag][1:3, 100:700])) < 1e-14
-    monkeypatch.delenv("PB200_MOL_RECORDS")
+        with ctx.options(mol_records=int(flag)):
+            ctx.set_scene(sc, keep)
+            out[flag], _ = ctx.run(0, info["n_orb"], 0, info["n_wav"])
+            # tiles: a sub-range of phases and wavelengths sees the same items
+            tile, _ = ctx.run(1, 3, 100, 700)
+            assert np.max(np.abs(tile - out[flag][1:3, 100:700])) < 1e-14
     assert np.max(np.abs(out["0"] - out["1"])) < 2e-13
     g = golden("C2s")
     ok, worst = excess_depth_ok(out["0"], g["R"], g["R0"])
@@ -442,7 +438,7 @@ def test_moment_form_of_the_molecular_kernel(nist_rows, golden, monkeypatch):
 
 @pytest.mark.parametrize("name", ["C1", "C4s", "PLNs", "THMs", "FSTs"])
 def test_sigma_sorted_windows_leave_R_unchanged(name, nist_rows, golden, monkeypatch):
-    """One absorber: wavelengths of a phase processed in the order of their cross section (PB200_SORT=1 forces it on
+    """One absorber: wavelengths of a phase processed in the order of their cross section (PB200_OPT_SORT = 1 forces it on
     these small grids), with the order-8 thin expansion (tau < 0.1 on a whole window) and the opaque skip (tau > 50).
     FSTs runs kernel (m) (per-chord stellar spectrum): the switch must be ignored there."""
     from prometheus_b200 import scene
@@ -452,14 +448,12 @@ def test_sigma_sorted_windows_leave_R_unchanged(name, nist_rows, golden, monkeyp
     ctx.set_scene(sc, keep)
     out = {}
     for flag in ("0", "1"):
-        monkeypatch.setenv("PB200_SORT", flag)
-        out[flag], t = ctx.run(0, info["n_orb"], 0, info["n_wav"])
-        tile, _ = ctx.run(1, 3, 5, info["n_wav"] - 7)                      # ragged tile: same values
-        assert np.max(np.abs(tile - out[flag][1:3, 5:info["n_wav"] - 7])) < 5e-14
-    monkeypatch.setenv("PB200_NO_THIN", "1")                                   # every active sample through the exp, sorted
-    R_exp, _ = ctx.run(0, info["n_orb"], 0, info["n_wav"])
-    monkeypatch.delenv("PB200_NO_THIN")
-    monkeypatch.delenv("PB200_SORT")
+        with ctx.options(sort=int(flag)):
+            out[flag], t = ctx.run(0, info["n_orb"], 0, info["n_wav"])
+            tile, _ = ctx.run(1, 3, 5, info["n_wav"] - 7)                      # ragged tile: same values
+            assert np.max(np.abs(tile - out[flag][1:3, 5:info["n_wav"] - 7])) < 5e-14
+    with ctx.options(sort=1, thin=0):                                          # every active sample through the exp, sorted
+        R_exp, _ = ctx.run(0, info["n_orb"], 0, info["n_wav"])
     assert np.max(np.abs(out["0"] - out["1"])) < 5e-14 and np.max(np.abs(R_exp - out["0"])) < 5e-14
     g = golden(name)
     ok, worst = excess_depth_ok(out["1"], g["R"], g["R0"])
@@ -477,13 +471,50 @@ def test_sigma_sorted_windows_with_block_cyclic_tiles(nist_rows, monkeypatch):
     sc, keep, info = scene.flatten(tr)
     ctx.set_scene(sc, keep)
     n_orb, n_wav = info["n_orb"], info["n_wav"]
-    monkeypatch.setenv("PB200_SORT", "0")
-    R_ref, _ = ctx.run(0, n_orb, 0, n_wav)
-    monkeypatch.setenv("PB200_SORT", "1")
+    with ctx.options(sort=0):
+        R_ref, _ = ctx.run(0, n_orb, 0, n_wav)
     full = capi.pinned_pool.empty((n_orb, n_wav))
     full[...] = -1.0
-    for r in range(3):
-        ctx.run_scatter(0, n_orb, 256, 3, r, full.ctypes.data, n_wav)
-    ctx.synchronize()
-    monkeypatch.delenv("PB200_SORT")
+    with ctx.options(sort=1):
+        for r in range(3):
+            ctx.run_scatter(0, n_orb, 256, 3, r, full.ctypes.data, n_wav)
+        ctx.synchronize()
     assert n_wav > 3 * 256 and np.max(np.abs(full - R_ref)) < 5e-14
+
+
+def test_power_law_with_non_positive_exponent_is_not_culled(nist_rows):
+    """PowerLawAtmosphere accepts any q (gasProperties.py:228-244).  For q <= 0 the density grows along the chord, so
+    the closest approach is no upper bound of the x-sum: the transparent-chord shortcut must not fire."""
+    from helpers import oracle_inputs
+    spec = workloads.get("HYDs")
+    spec["scenarios"] = [{"type": "powerLaw", "T": 3000.0, "P_0": 3e-7, "q_esc": -0.5,
+                          "species": [{"name": "NaI", "chi": 1e-5}]}]
+    tr = builder.build_transit(spec, nist_rows=nist_rows)
+    R = tr.sumOverChords()
+    inputs = oracle_inputs(spec, nist_rows)
+    con = tr.atmosphere.densityDistributionList[0].constituents[0]
+    inputs["tables"] = {(0, "NaI"): (con.lookupFunction.x, con.lookupFunction.y)}
+    m = oracle.build_model(spec, inputs)
+    R_ref = oracle.sum_over_chords(m)
+    R0 = oracle.sum_over_chords(m, opaque_only=True)
+    ok, worst = excess_depth_ok(R, R_ref, R0)
+    assert ok, worst
+    assert np.max(np.abs(R - R_ref)) < 5e-13 and float((R0 - R).max()) > 1e-6
+    R_nocull, _ = run_with_env(tr, cull=0, mirror=0, thin=0)
+    assert np.max(np.abs(R - R_nocull)) < 5e-14
+
+
+def test_options_are_per_context_and_validated(ctx):
+    assert {k: ctx.get_option(k) for k in capi.OPT} == capi.OPT_DEFAULTS
+    with ctx.options(cull=0, sort=1):
+        assert ctx.get_option("cull") == 0 and ctx.get_option("sort") == 1
+        other = capi.Context(0)
+        assert other.get_option("cull") == 1
+        other.close()
+    assert ctx.get_option("cull") == 1 and ctx.get_option("sort") == -1
+    for name, bad in (("cull", 2), ("sort", 5), ("min_tiles", 0)):
+        with pytest.raises(capi.Pb200Error) as ei:
+            ctx.set_option(name, bad)
+        assert ei.value.code == -1
+    with pytest.raises(capi.Pb200Error):
+        ctx.check(ctx.lib.pb200_set_option(ctx.handle, 99, 0))

@@ -147,9 +147,8 @@ def test_scatter_tiles_and_zero_copy_equal_the_plain_run(nist_rows, monkeypatch)
     sc, keep, info = scene.flatten(tr)
     ctx.set_scene(sc, keep)
     n_orb, n_wav = info["n_orb"], info["n_wav"]
-    monkeypatch.setenv("PB200_NO_ZEROCOPY", "1")
-    R_copy, _ = ctx.run(0, n_orb, 0, n_wav)                      # device scratch + D2H
-    monkeypatch.delenv("PB200_NO_ZEROCOPY")
+    with ctx.options(zerocopy=0):
+        R_copy, _ = ctx.run(0, n_orb, 0, n_wav)                  # device scratch + D2H
     R_zero, _ = ctx.run(0, n_orb, 0, n_wav)                      # kernels store into the page-locked result
     assert np.array_equal(R_copy, R_zero)
     pageable = np.empty((n_orb, n_wav))
