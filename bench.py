@@ -428,9 +428,8 @@ def run_b200(args):
 
         # ---- the same steps with the transparent-chord culling switched off (every unblocked chord
         #      goes through the exp, as in the reference's loop): reported next to the headline ----------
-        os.environ["PB200_NO_CULL"] = "1"
-        os.environ["PB200_NO_MIRROR"] = "1"
-        os.environ["PB200_NO_THIN"] = "1"
+        for opt in ("cull", "mirror", "thin"):
+            ctx.set_option(opt, 0)
         ctx.set_scene(sc, keep)
         tile_t.clear()
         for _ in range(2):
@@ -453,7 +452,8 @@ def run_b200(args):
         st.run_device()
         barrier()
         R_nc = st.to_host(0)
-        del os.environ["PB200_NO_CULL"], os.environ["PB200_NO_MIRROR"], os.environ["PB200_NO_THIN"]
+        for opt in ("cull", "mirror", "thin"):
+            ctx.set_option(opt, 1)
         ctx.set_scene(sc, keep)
         tile_t.clear()
         st.run_device()
@@ -471,7 +471,7 @@ def run_b200(args):
             if world == 1:
                 R_e2e = tr.sumOverChords()                 # the user-facing call: numpy in, numpy out
             else:
-                if axis == "cyclic" and os.environ.get("PB200_E2E_GATHER") != "1":
+                if axis == "cyclic" and not args.e2e_gather:
                     R_e2e = pbd.sum_over_chords_shared(tr, None, local, state)    # tiles stored straight into shared pinned memory
                 else:
                     R_e2e = pbd.sum_over_chords(tr, None, axis, local, 0, state)   # all-gather + D2H on rank 0
@@ -524,7 +524,7 @@ def run_b200(args):
                      "traffic": recorded_traffic(args.workload), "kernel_ms": nc_kernel_ms,
                      "traffic_production_launch": recorded_traffic(args.workload, "transit_kernel_production"),
                      "samples_per_launch": nc_executed,
-                     "samples_note": "measured on the launch with PB200_NO_CULL=1 PB200_NO_MIRROR=1 PB200_NO_THIN=1, where every unblocked chord*lambda sample goes through the table exp; the production launch (kernels_ms.transit) evaluates `culling.exp_samples_per_rank_step` of them that way",
+                     "samples_note": "measured on the launch with pb200_set_option CULL = MIRROR = THIN = 0, where every unblocked chord*lambda sample goes through the table exp; the production launch (kernels_ms.transit) evaluates `culling.exp_samples_per_rank_step` of them that way",
                      "fp64": {"achieved_tflops": fl, "peak_tflops_dfma_probe": probe["dfma_tflops"],
                               "frac": fl / probe["dfma_tflops"], "flops_per_sample": executed_flops_per_sample(n_atoms),
                               "flops_per_sample_survey_convention": flops_per_sample(n_atoms),
@@ -544,7 +544,7 @@ def run_b200(args):
                             "(phi, rho), (pi - phi, rho) -- equal column densities, the scene is symmetric in z -- share one record. "
                             "Of the remaining (`executed`) samples, those whose chord is optically thin over the warp's 256 wavelengths "
                             "(tau < 2.1e-5) are summed as a second-order expansion per chord; only `exp_samples` take the table exp. "
-                            "`off` = same steps with PB200_NO_CULL=1 PB200_NO_MIRROR=1 PB200_NO_THIN=1: every unblocked sample goes through the exp"},
+                            "`off` = same steps with pb200_set_option CULL = MIRROR = THIN = 0: every unblocked sample goes through the exp"},
         "kernels_ms": {"column": column_ms, "transit": kernel_ms, "finalize": finalize_ms},
         "setup": {"seconds": t_setup, "voigt_last_table_ms": voigt["transit_ms"], "voigt_last_table_evals": voigt["samples"]},
     }
@@ -617,6 +617,7 @@ def main():
     ap.add_argument("--workload", default="C4")
     ap.add_argument("--others", default="C2,C3,C5", help="other BASELINE configs reported under other_workloads (N=1)")
     ap.add_argument("--no-retrieval", action="store_true", help="skip the retrieval-batch leg (N=1)")
+    ap.add_argument("--e2e-gather", action="store_true", help="N>1 e2e through all-gather + rank-0 D2H instead of the shared result")
     ap.add_argument("--cpu-seconds", type=float, default=None,
                     help="CPU budget: cpu_baseline sample (default 15 s) / whole --impl reference run (default 120 s)")
     args = ap.parse_args()
