@@ -320,6 +320,21 @@ int pb200_serpens_density(pb200_ctx* ctx, const double* pos, int64_t n, const do
                           const double* z_points, double planet_R, double star_R, double* out_host,
                           double* sums_host);
 
+/* Allocation-free variant of the particle histogram of pb200_serpens_density (no smoothing):
+   out_dev[nx][ny][nz] = histogramdd(pos_dev[n][3]; edges) * N / denom, all pointers DEVICE pointers owned by the
+   caller, enqueued on the context's stream, not synchronised.  NO COUNTERPART IN THE REFERENCE: added
+   for callers that cannot call cudaMalloc (CUDA graph capture, serving loops, harnesses that
+   forbid allocation).  The integer count grid -- the kernel's scratch -- is a static device array of
+   PB200_SERPENS_STATIC_MAX_CELLS cells (8 MiB, held by every GPU that loads the library until exit); the call does
+   no cudaMalloc / cudaFree and fails with PB200_ERR_INVALID when (nxb-1)*(nyb-1)*(nzb-1) exceeds it.  Every call on
+   a device shares that array (it is cleared at the start of each call): calls that overlap on the GPU -- two
+   contexts or two streams of one device -- race; serialise them.  The first call on a device looks the array's
+   address up (cudaGetSymbolAddress): make it before a stream capture begins.                               */
+#define PB200_SERPENS_STATIC_MAX_CELLS (1 << 21)
+int pb200_serpens_histogram_static(pb200_ctx* ctx, const double* pos_dev, int64_t n, const double* xb_dev, int32_t nxb,
+                                   const double* yb_dev, int32_t nyb, const double* zb_dev, int32_t nzb, double N,
+                                   double denom, double* out_dev);
+
 /* ---- result file ------------------------------------------------------------------------- */
 /* Byte-identical replacement of the reference's writer (prometheus.py:142-156): first row
    "nan orbphase/(2 pi) ...", then one row per wavelength "lambda R(phase_0, lambda) ...", np.savetxt

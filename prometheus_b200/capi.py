@@ -26,8 +26,9 @@ EXPORTS = [
     "pb200_set_models", "pb200_lightcurve", "pb200_run_batch",
     "pb200_host_register", "pb200_host_unregister", "pb200_run_scatter", "pb200_sync",
     "pb200_set_scene_sharded", "pb200_table_regions", "pb200_number_density_device",
-    "pb200_serpens_density", "pb200_set_option", "pb200_get_option",
+    "pb200_serpens_density", "pb200_set_option", "pb200_get_option", "pb200_serpens_histogram_static",
 ]
+SERPENS_STATIC_MAX_CELLS = 1 << 21
 
 # pb200_option (include/prometheus_b200.h)
 OPT = {"cull": 0, "mirror": 1, "thin": 2, "group": 3, "sort": 4, "mol_records": 5, "zerocopy": 6, "min_tiles": 7, "graph": 8}
@@ -174,6 +175,7 @@ def load():
         "pb200_sync": (C.c_int, [vp]),
         "pb200_serpens_density": (C.c_int, [vp, c_double_p, i64, c_double_p, i32, c_double_p, i32, c_double_p, i32, dbl, dbl,
                                             c_double_p, i32, c_double_p, c_double_p, dbl, dbl, c_double_p, c_double_p]),
+        "pb200_serpens_histogram_static": (C.c_int, [vp, vp, i64, vp, i32, vp, i32, vp, i32, dbl, dbl, vp]),
         "pb200_set_scene_sharded": (C.c_int, [vp, C.POINTER(Scene), i32, i32]),
         "pb200_table_regions": (C.c_int, [vp, i32, C.POINTER(vp), C.POINTER(i64), C.POINTER(i32)]),
         "pb200_host_register": (C.c_int, [vp, C.c_size_t, C.POINTER(vp)]),
@@ -408,6 +410,13 @@ class Context:
                                                   dptr(zb), zb.size, float(N), float(denom), dptr(w) if w is not None else None,
                                                   radius, dptr(yp), dptr(zp), float(planet_R), float(star_R), dptr(out), dptr(sums)))
         return out, sums
+
+    def serpens_histogram_static(self, pos_ptr: int, n: int, xb_ptr: int, nxb: int, yb_ptr: int, nyb: int, zb_ptr: int,
+                                 nzb: int, N: float, denom: float, out_ptr: int):
+        """pb200_serpens_histogram_static: device pointers in and out, no allocation inside, not synchronised."""
+        self.check(self.lib.pb200_serpens_histogram_static(self.handle, C.c_void_p(pos_ptr), int(n), C.c_void_p(xb_ptr), nxb,
+                                                           C.c_void_p(yb_ptr), nyb, C.c_void_p(zb_ptr), nzb, float(N),
+                                                           float(denom), C.c_void_p(out_ptr)))
 
     def last_timing(self) -> dict:
         t = Timing()

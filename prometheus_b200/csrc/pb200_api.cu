@@ -1574,6 +1574,17 @@ extern "C" int pb200_serpens_density(pb200_ctx* c, const double* pos, int64_t n,
     return download(c, out_host, result, (size_t)cells * D);
 }
 
+// accessors for entry points that live in other translation units (pb200_serpens.cu: pb200_serpens_histogram_static)
+namespace pb200 {
+int ctx_fail(pb200_ctx* c, int code, const char* msg) { return fail(c, code, "%s", msg); }
+int ctx_info(pb200_ctx* c, int* device, cudaStream_t* stream, int* sm_count) {
+    if (!c) return PB200_ERR_INVALID;
+    *device = c->device; *stream = c->stream; *sm_count = c->sm_count;
+    return PB200_OK;
+}
+void ctx_add_launches(pb200_ctx* c, int n) { c->launches += n; }
+}  // namespace pb200
+
 extern "C" int pb200_last_timing(pb200_ctx* c, pb200_timing* t) {
     if (!c || !t) return PB200_ERR_INVALID;
     *t = c->last;

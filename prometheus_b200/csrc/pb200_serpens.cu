@@ -110,4 +110,69 @@ void launch_serpens_sums(const double* n, int nx, int ny, int nz, const double* 
     serpens_sums_kernel<<<1, 1024, 0, st>>>(n, nx, ny, nz, yp, zp, Rp2, Rs2, sums);
 }
 
+// ---- allocation-free variant of the histogram (pb200_serpens_histogram_static) -----------------------------------
+// The integer count grid of serpens_histogram_kernel is scratch.  Here it lives in a file-scope device array that
+// every GPU which loads the library holds until exit (8 MiB), so the call needs no cudaMalloc / cudaFree: usable
+// under CUDA graph capture, in serving loops and in harnesses that forbid allocation.  In host code the array's name
+// is only a stand-in; its device address is looked up once per device with cudaGetSymbolAddress.
+static __device__ __align__(256) unsigned int g_serpens_static_counts[PB200_SERPENS_STATIC_MAX_CELLS];
+
+int ctx_fail(pb200_ctx* c, int code, const char* msg);
+int ctx_info(pb200_ctx* c, int* device, cudaStream_t* stream, int* sm_count);
+void ctx_add_launches(pb200_ctx* c, int n);
+
 }  // namespace pb200
+
+#include <cstdio>
+#include <mutex>
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_static_mutex;
+unsigned int* g_static_counts_addr[kMaxDevices] = {};   // device address of g_serpens_static_counts, per device
+}  // namespace
+
+extern "C" int pb200_serpens_histogram_static(pb200_ctx* c, const double* pos_dev, int64_t n, const double* xb_dev,
+                                              int32_t nxb, const double* yb_dev, int32_t nyb, const double* zb_dev,
+                                              int32_t nzb, double N, double denom, double* out_dev) {
+    using namespace pb200;
+    int device = 0, sm_count = 0;
+    cudaStream_t st = nullptr;
+    if (ctx_info(c, &device, &st, &sm_count)) return PB200_ERR_INVALID;
+    if (n < 0 || (n && !pos_dev) || !xb_dev || !yb_dev || !zb_dev || nxb < 2 || nyb < 2 || nzb < 2 || !out_dev)
+        return ctx_fail(c, PB200_ERR_INVALID, "pb200_serpens_histogram_static: bad arguments");
+    const int64_t cells = (int64_t)(nxb - 1) * (nyb - 1) * (nzb - 1);
+    char msg[256];
+    if (cells > (int64_t)PB200_SERPENS_STATIC_MAX_CELLS) {
+        snprintf(msg, sizeof msg, "pb200_serpens_histogram_static: %lld cells exceed the static scratch of %lld cells "
+                 "(PB200_SERPENS_STATIC_MAX_CELLS); use pb200_serpens_density", (long long)cells,
+                 (long long)PB200_SERPENS_STATIC_MAX_CELLS);
+        return ctx_fail(c, PB200_ERR_INVALID, msg);
+    }
+    if (device < 0 || device >= kMaxDevices) return ctx_fail(c, PB200_ERR_INVALID, "pb200_serpens_histogram_static: device index out of range");
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) { snprintf(msg, sizeof msg, "cudaSetDevice: %s", cudaGetErrorString(e)); return ctx_fail(c, PB200_ERR_CUDA, msg); }
+    unsigned int* counts = nullptr;
+    {   // once per device, with that device current
+        std::lock_guard<std::mutex> lock(g_static_mutex);
+        if (!g_static_counts_addr[device]) {
+            void* p = nullptr;
+            e = cudaGetSymbolAddress(&p, g_serpens_static_counts);
+            if (e != cudaSuccess || !p) {
+                snprintf(msg, sizeof msg, "cudaGetSymbolAddress(static histogram scratch): %s", cudaGetErrorString(e));
+                return ctx_fail(c, PB200_ERR_CUDA, msg);
+            }
+            g_static_counts_addr[device] = static_cast<unsigned int*>(p);
+        }
+        counts = g_static_counts_addr[device];
+    }
+    // the array keeps the previous call's counts: the cells of this call start at zero
+    e = cudaMemsetAsync(counts, 0, (size_t)cells * sizeof(unsigned int), st);
+    if (e != cudaSuccess) { snprintf(msg, sizeof msg, "cudaMemsetAsync: %s", cudaGetErrorString(e)); return ctx_fail(c, PB200_ERR_CUDA, msg); }
+    if (n) launch_serpens_histogram(pos_dev, n, xb_dev, nxb, yb_dev, nyb, zb_dev, nzb, counts, sm_count, st);
+    launch_serpens_scale(counts, cells, N, denom, out_dev, st);
+    ctx_add_launches(c, n ? 2 : 1);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) { snprintf(msg, sizeof msg, "static histogram launch: %s", cudaGetErrorString(e)); return ctx_fail(c, PB200_ERR_CUDA, msg); }
+    return PB200_OK;
+}
