@@ -313,3 +313,101 @@ def shape(spec: dict) -> dict:
     g = spec["grid"]
     return {"n_x": int(g[2]), "n_rho": int(g[4]), "n_phi": int(g[5]), "n_orb": int(g[7]),
             "n_chords": int(g[4]) * int(g[5]) * int(g[7])}
+
+
+# ---------------------------------------------------------------------------------------------------
+# the reference's setup-file schema (written by pythonScripts/setup.py:207-211, :258-304, :368-391, :424-479,
+# :521-544 as JSON into <parent>/setupFiles/<name>.txt; read by prometheus.py:56-134)
+# ---------------------------------------------------------------------------------------------------
+_CLI_SCENARIOS = ("barometric", "hydrostatic", "powerLaw", "exomoon", "torus", "serpens")
+
+
+def to_setup_file(spec: dict) -> dict:
+    """The setup-file twin of a workload spec, for `python prometheus.py <name>`.  Raises ValueError for what the
+    reference's CLI cannot express: CLV / stellar rotation / an F* table (prometheus.py never applies them), two
+    scenarios of one type (the file is keyed by type), species outside the reference's registry, synthetic molecular
+    tables, tidally heated moons, and the number-normalised power law (prometheus.py:85 indexes dict.keys())."""
+    st = spec["bodies"]["star"]
+    if st.get("u1") or st.get("u2") or st.get("vsini") or st.get("fstar"):
+        raise ValueError("the reference CLI applies neither CLV nor stellar rotation nor an F* table")
+    if spec.get("linelist", "nist") != "nist":
+        raise ValueError("the reference CLI reads Resources/LineList.txt only")
+    fundamentals = {"ExomoonSource": False, "DopplerPlanetRotation": False, "CLV_variations": False, "RM_effect": False,
+                    "DopplerOrbitalMotion": bool(spec["doppler"])}
+    scenarios, species = {}, {}
+    arch = {"planetName": spec["bodies"]["planetName"]}
+    for s in spec["scenarios"]:
+        kind = s["type"]
+        if kind not in _CLI_SCENARIOS or kind in scenarios:
+            raise ValueError(f"scenario {kind!r}: not expressible in a setup file (unknown to the CLI, or given twice)")
+        if s.get("molecules"):
+            raise ValueError("synthetic molecular tables cannot be named in a setup file")
+        collisional = kind in ("barometric", "hydrostatic") or (kind == "powerLaw" and "P_0" in s)
+        if kind in ("barometric", "hydrostatic"):
+            scenarios[kind] = {"T": s["T"], "P_0": s["P_0"], "mu": s["mu"]}
+        elif kind == "powerLaw":
+            if not collisional:
+                raise ValueError("number-normalised power law: prometheus.py:85 fails on dict.keys()[0]")
+            scenarios[kind] = {"q_esc": s["q_esc"], "P_0": s["P_0"], "T": s["T"]}
+        elif kind == "exomoon":
+            mo = spec["bodies"]["moon"]
+            fundamentals["ExomoonSource"] = True
+            scenarios[kind] = {"q_moon": s["q"]}
+            arch.update(R_moon=mo["R"], a_moon=mo["a"], starting_orbphase_moon=mo["phi0"])
+        elif kind == "torus":
+            scenarios[kind] = {"a_torus": s["a_torus"], "v_ej": s["v_ej"]}
+        else:
+            scenarios[kind] = {"serpensPath": s["serpensPath"]}
+        species[kind] = {}
+        for sp in s.get("species", []):
+            if sp["name"] not in const.SPECIES_TABLE:
+                raise ValueError(f"species {sp['name']} is not in the reference's registry")
+            species[kind][sp["name"]] = {"chi": sp["chi"]} if collisional else {"sigma_v": sp["sigma_v"], "Nparticles": s["N"]}
+    w, g = spec["wavelength"], spec["grid"]
+    grids = {"lower_w": w[0], "upper_w": w[1], "widthHighRes": w[2], "resolutionLow": w[3], "resolutionHigh": w[4],
+             "x_midpoint": g[0], "x_border": g[1], "x_steps": int(g[2]), "upper_rho": g[3], "rho_steps": int(g[4]),
+             "phi_steps": int(g[5]), "orbphase_border": g[6], "orbphase_steps": int(g[7])}
+    return {"Fundamentals": fundamentals, "Scenarios": scenarios, "Architecture": arch, "Species": species, "Grids": grids}
+
+
+def from_setup_file(param: dict, name: str = "setup", bodies: dict | None = None) -> dict:
+    """A setup file (parsed JSON) -> workload spec.  The planet's scalars come from `bodies` (default: BODIES, the
+    values the reference derives from its catalogue for the planets used here)."""
+    arch, grids = param["Architecture"], param["Grids"]
+    b = copy.deepcopy((bodies or BODIES)[arch["planetName"]])
+    b["planetName"] = arch["planetName"]
+    b["star"].update({"u1": 0.0, "u2": 0.0, "vsini": 0.0, "phi_rot": 0.0, "fstar": None})
+    if "starting_orbphase_moon" in arch:
+        b["moon"] = {"phi0": arch["starting_orbphase_moon"], "R": arch["R_moon"], "a": arch["a_moon"]}
+    scenarios = []
+    for kind, prm in param["Scenarios"].items():
+        sp = param["Species"].get(kind, {})
+        s = {"type": kind}
+        if "T" in prm:                       # collisional (prometheus.py:112)
+            s.update({k: prm[k] for k in ("T", "P_0", "mu", "q_esc") if k in prm})
+            s["species"] = [{"name": n, "chi": d["chi"]} for n, d in sp.items()]
+        else:
+            first = next(iter(sp.values()))
+            s["N"] = first["Nparticles"]
+            if kind == "exomoon":
+                s["q"] = prm["q_moon"]
+            elif kind == "torus":
+                s.update(a_torus=prm["a_torus"], v_ej=prm["v_ej"])
+            elif kind == "powerLaw":
+                s["q_esc"] = prm["q_esc"]
+            elif kind == "serpens":
+                s["serpensPath"] = prm["serpensPath"]
+            s["species"] = [{"name": n, "sigma_v": d["sigma_v"]} for n, d in sp.items()]
+        scenarios.append(s)
+    return {"name": name, "title": f"setup file {name}", "bodies": b, "doppler": bool(param["Fundamentals"]["DopplerOrbitalMotion"]),
+            "linelist": "nist", "scenarios": scenarios,
+            "wavelength": [grids[k] for k in ("lower_w", "upper_w", "widthHighRes", "resolutionLow", "resolutionHigh")],
+            "grid": [grids["x_midpoint"], grids["x_border"], int(grids["x_steps"]), grids["upper_rho"], int(grids["rho_steps"]),
+                     int(grids["phi_steps"]), grids["orbphase_border"], int(grids["orbphase_steps"])]}
+
+
+def cli_twin(name: str) -> dict:
+    """Workload `name` in the form the reference's CLI can run: C3 / C3s without the CLV of the direct-API variant."""
+    spec = get(name)
+    spec["bodies"]["star"].update(u1=0.0, u2=0.0)
+    return spec
