@@ -260,6 +260,12 @@ int pb200_run_batch(pb200_ctx* ctx, int n_models, const pb200_model* models, con
 /* waits for everything enqueued on the context's stream (pb200_run_device*, pb200_run_scatter do not) and returns
    PB200_ERR_BOUNDS if a tabulated density was queried outside its grid since the last check            */
 int pb200_sync(pb200_ctx* ctx);
+/* Diagnostics (tests pick their oracle columns with it): the order in which the last run walked its wavelengths when
+   it used sigma-sorted windows -- perm[pi*n_wav_sel + i] = local wavelength index at sorted position i of phase pi
+   (a window of kernel (c') is 256 consecutive positions), nsig_sorted = -sigma(p, lambda) * 4096/ln2 in that order.
+   In: *n = capacity of the arrays (either may be NULL); out: *n = n_phase*n_wav_sel of the run, 0 if not sorted.
+   Valid until the next run of the context.  No counterpart in the reference.                                  */
+int pb200_last_sort_order(pb200_ctx* ctx, int64_t* n, int32_t* perm_host, double* nsig_sorted_host);
 /* timing record of the last pb200_run / pb200_voigt_sigma call of this context */
 int pb200_last_timing(pb200_ctx* ctx, pb200_timing* timing);
 

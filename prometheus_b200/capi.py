@@ -27,6 +27,7 @@ EXPORTS = [
     "pb200_host_register", "pb200_host_unregister", "pb200_run_scatter", "pb200_sync",
     "pb200_set_scene_sharded", "pb200_table_regions", "pb200_number_density_device",
     "pb200_serpens_density", "pb200_set_option", "pb200_get_option", "pb200_serpens_histogram_static",
+    "pb200_last_sort_order",
 ]
 SERPENS_STATIC_MAX_CELLS = 1 << 21
 
@@ -176,6 +177,7 @@ def load():
         "pb200_serpens_density": (C.c_int, [vp, c_double_p, i64, c_double_p, i32, c_double_p, i32, c_double_p, i32, dbl, dbl,
                                             c_double_p, i32, c_double_p, c_double_p, dbl, dbl, c_double_p, c_double_p]),
         "pb200_serpens_histogram_static": (C.c_int, [vp, vp, i64, vp, i32, vp, i32, vp, i32, dbl, dbl, vp]),
+        "pb200_last_sort_order": (C.c_int, [vp, C.POINTER(i64), C.POINTER(C.c_int32), c_double_p]),
         "pb200_set_scene_sharded": (C.c_int, [vp, C.POINTER(Scene), i32, i32]),
         "pb200_table_regions": (C.c_int, [vp, i32, C.POINTER(vp), C.POINTER(i64), C.POINTER(i32)]),
         "pb200_host_register": (C.c_int, [vp, C.c_size_t, C.POINTER(vp)]),
@@ -417,6 +419,18 @@ class Context:
         self.check(self.lib.pb200_serpens_histogram_static(self.handle, C.c_void_p(pos_ptr), int(n), C.c_void_p(xb_ptr), nxb,
                                                            C.c_void_p(yb_ptr), nyb, C.c_void_p(zb_ptr), nzb, float(N),
                                                            float(denom), C.c_void_p(out_ptr)))
+
+    def last_sort_order(self, n_phase: int):
+        """(perm [n_phase][n_wav_sel] int32, nsig_sorted [n_phase][n_wav_sel]) of the last run, or None if it did not
+        use sigma-sorted windows (pb200_last_sort_order)."""
+        n = C.c_int64(0)
+        self.check(self.lib.pb200_last_sort_order(self.handle, C.byref(n), None, None))
+        if n.value == 0:
+            return None
+        perm = np.empty(n.value, dtype=np.int32)
+        nsig = np.empty(n.value, dtype=np.float64)
+        self.check(self.lib.pb200_last_sort_order(self.handle, C.byref(n), perm.ctypes.data_as(C.POINTER(C.c_int32)), dptr(nsig)))
+        return perm.reshape(n_phase, -1), nsig.reshape(n_phase, -1)
 
     def last_timing(self) -> dict:
         t = Timing()

@@ -119,6 +119,10 @@ struct pb200_ctx {
     int mol_bins = -1;
     bool buckets_ready = false;   // bucket indices of the sigma tables (built on the device before the first run of a scene)
     std::vector<std::pair<void*, int64_t>> regions;   // sharded uploads of the current scene: (device base, doubles per rank)
+    // sigma-sorted order of the last run (pb200_last_sort_order; lives in `scratch` until the next run)
+    const int* last_perm = nullptr;
+    const double* last_nsig_sorted = nullptr;
+    int64_t last_sort_n = 0;
     // run-time options (pb200_set_option); the library never reads the environment
     int64_t opt[PB200_OPT_COUNT] = {1, 1, 1, 1, -1, 0, 1, 1, 0};
 };
@@ -736,6 +740,7 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     const int64_t n_out = (int64_t)n_phase * n_wav_sel;
     const int64_t launches0 = c->launches;
     c->lastR_full = false;
+    c->last_perm = nullptr; c->last_nsig_sorted = nullptr; c->last_sort_n = 0;
 
     TransitParams prm;
     prm.phase_lo = phase_lo; prm.n_phase = n_phase; prm.wav_lo = wav_lo; prm.n_wav_sel = n_wav_sel;
@@ -814,6 +819,7 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
             c->launches += 3;   // keys, gather + the radix sort's own passes
             prm.nsig = nsig_sorted;
             prm.perm = perm;
+            c->last_perm = perm; c->last_nsig_sorted = nsig_sorted; c->last_sort_n = n_out;
         }
     }
     // PB200_OPT_CULL = 0 (measurement only): every unblocked chord gets its exact sums and a record, as in the
@@ -1572,6 +1578,24 @@ extern "C" int pb200_serpens_density(pb200_ctx* c, const double* pos, int64_t n,
     }
     PB_CUDA(c, cudaGetLastError());
     return download(c, out_host, result, (size_t)cells * D);
+}
+
+// Diagnostics: the order in which the last run of this context walked its wavelengths (sigma-sorted windows of kernel
+// (c'), pb200_sort.cu).  perm[pi * n_wav_sel + i] = local wavelength index at sorted position i of phase pi,
+// nsig_sorted the matching -sigma * 4096/ln2.  *n receives n_phase * n_wav_sel of that run, 0 if it was not sorted;
+// the arrays (may be NULL) must hold that many entries.  Valid until the next run of the context.
+extern "C" int pb200_last_sort_order(pb200_ctx* c, int64_t* n, int32_t* perm_host, double* nsig_sorted_host) {
+    int rc = check_scene(c);
+    if (rc) return rc;
+    if (!n) return fail(c, PB200_ERR_INVALID, "pb200_last_sort_order: n == NULL");
+    const int64_t cap = *n;
+    *n = c->last_sort_n;
+    if (c->last_sort_n == 0 || (!perm_host && !nsig_sorted_host)) return PB200_OK;
+    if (cap < c->last_sort_n) return fail(c, PB200_ERR_INVALID, "pb200_last_sort_order: room for %lld entries, the run had %lld", (long long)cap, (long long)c->last_sort_n);
+    if (perm_host) PB_CUDA(c, cudaMemcpyAsync(perm_host, c->last_perm, (size_t)c->last_sort_n * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    if (nsig_sorted_host) PB_CUDA(c, cudaMemcpyAsync(nsig_sorted_host, c->last_nsig_sorted, (size_t)c->last_sort_n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    PB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return PB200_OK;
 }
 
 // accessors for entry points that live in other translation units (pb200_serpens.cu: pb200_serpens_histogram_static)

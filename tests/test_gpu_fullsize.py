@@ -72,3 +72,134 @@ def test_c4_properties(nist_rows):
     spec2["scenarios"][0]["N"] *= 2.0
     R2 = builder.build_transit(spec2, nist_rows=nist_rows).sumOverChords()
     assert np.all(R2 <= R + 1e-15)
+
+
+# ---- C2 at full size: kernel (m), both forms (gasProperties.py:925-936, :789-818) -----------------
+def _c2_columns(R, wavelength, n_strided=6):
+    """Oracle columns for C2: the maximum of the synthetic molecular band, the deepest atomic line core with its
+    neighbours, and a strided set."""
+    lam_A = wavelength * 1e8
+    band = (1.0 + np.sin(lam_A / 3.0 + 1) ** 2) + (1.0 + np.sin(lam_A / 3.0 + 2) ** 2)      # workloads.synthetic_molecule_table
+    core = int(np.argmin(R.min(axis=0)))
+    n_wav = wavelength.size
+    cols = np.concatenate([[int(np.argmax(band)), int(np.argmin(band)), core - 1, core, core + 1],
+                           np.linspace(0, n_wav - 1, n_strided).astype(int)])
+    return np.unique(np.clip(cols, 0, n_wav - 1))
+
+
+def test_c2_full_size_columns_against_oracle(nist_rows):
+    """configs[1]: 33 000 chords x 50 x-samples x 95 897 wavelengths, 8 atoms + 2 molecules.  All chords, >= 8 columns,
+    the moment form (default) and the per-record form of kernel (m) against the oracle's scipy RGI path."""
+    ctx = host.get_context(0)
+    spec = workloads.get("C2")
+    tr = builder.build_transit(spec, nist_rows=nist_rows)
+    R = tr.sumOverChords()
+    with ctx.options(mol_records=1):
+        R_rec = tr.sumOverChords()
+    assert np.all(np.isfinite(R)) and R.max() <= 1.0 and R.min() > 0.0
+    sel = _c2_columns(R, tr.wavelength)
+    assert sel.size >= 8
+    inputs = oracle_inputs(spec, nist_rows)
+    inputs["tables"] = gpu_tables(tr)
+    m = oracle.build_model(spec, inputs)
+    assert np.array_equal(m.wavelength, tr.wavelength)
+    n_c = len(m.rho) * len(m.phi) * len(m.orb)
+    bs = oracle.reference_batch_size(n_c, len(sel), len(m.x), True, 2.0)                    # memoryHandler.py:42-47, 64 B per point
+    kw = dict(batch_size=None if bs >= n_c else bs, wavelength=m.wavelength[sel])
+    R_ref = oracle.sum_over_chords(m, **kw)
+    R0 = oracle.sum_over_chords(m, opaque_only=True, **kw)
+    for label, got in (("moments", R[:, sel]), ("records", R_rec[:, sel])):
+        ok, worst = excess_depth_ok(got, R_ref, R0)
+        assert ok, f"C2 {label}: worst err/bound {worst:.3g}"
+        assert np.max(np.abs(got - R_ref)) < 5e-13, (label, float(np.max(np.abs(got - R_ref))))
+    assert np.max(np.abs(R - R_rec)) < 5e-13
+    assert float((R0 - R_ref).max()) > 1e-3
+
+
+def test_steep_molecular_table_takes_the_per_record_form(nist_rows):
+    """A table whose log sigma jumps by 12 dex between two pressure nodes needs more than 64 sub-intervals for the
+    9e-13 truncation bound of the moment expansion: kernel (m) must fall back to the per-record form by itself
+    (mol_bins == 0) and still match scipy's RGI."""
+    spec = workloads.get("C2s")
+    P = np.array([1e-4, 1e8])
+    T = np.linspace(100.0, 3400.0, 12)
+    lam = np.linspace(5700e-8, 6100e-8, 2001)
+    logsig = np.empty((2, 12, lam.size))
+    logsig[0] = -34.0 + 0.3 * np.sin(lam * 1e8 / 5.0)[None, :]
+    logsig[1] = logsig[0] + 12.0
+    tr = builder.build_transit(spec, nist_rows=nist_rows)
+    tr_steep = builder.build_transit(spec, nist_rows=nist_rows)
+    for con in tr_steep.atmosphere.densityDistributionList[0].constituents:
+        if con.isMolecule:
+            con.lookupFunction = host.GridFunction((P, T, lam), logsig, np.log10(1e-50))
+    tr.sumOverChords()
+    tr.sumOverChords()
+    launches_moment = tr.last_timing["launches"]
+    tr_steep.sumOverChords()
+    R = tr_steep.sumOverChords()
+    assert tr_steep.last_timing["launches"] < launches_moment, "the steep table must not run the moment kernels"
+    inputs = oracle_inputs(spec, nist_rows)
+    inputs["tables"] = gpu_tables(tr_steep)
+    for key in inputs["molecules"]:
+        inputs["molecules"][key] = (P, T, lam, logsig)
+    m = oracle.build_model(spec, inputs)
+    sel = np.unique(np.concatenate([[int(np.argmin(R.min(axis=0)))], np.linspace(0, R.shape[1] - 1, 24).astype(int)]))
+    R_ref = oracle.sum_over_chords(m, wavelength=m.wavelength[sel])
+    R0 = oracle.sum_over_chords(m, wavelength=m.wavelength[sel], opaque_only=True)
+    ok, worst = excess_depth_ok(R[:, sel], R_ref, R0)
+    assert ok, worst
+    assert np.max(np.abs(R[:, sel] - R_ref)) < 5e-13 and float((R0 - R_ref).max()) > 1e-4
+
+
+# ---- C5: columns chosen by the sigma-sorted kernel's own per-window decisions -------------------------------------
+def test_c5_regime_boundary_columns_against_oracle(nist_rows):
+    """The sorted variant of kernel (c') decides per (chord, window of 256 sorted wavelengths): order-2 expansion below
+    tau = 2.1e-5, order-8 below 0.1, skipped above 50, table exp between (pb200_transit.cu:172-205, :296-302).  The
+    boundaries sit at intermediate sigma, where a "deepest + strided" pick does not look: take, for two phases, the
+    first and the last window in which each regime occurs, read back from the device's own sort order."""
+    ctx = host.get_context(0)
+    spec = workloads.get("C5")
+    tr = builder.build_transit(spec, nist_rows=nist_rows)
+    R = tr.sumOverChords()
+    n_orb, n_wav = R.shape
+    order = ctx.last_sort_order(n_orb)
+    assert order is not None, "C5 runs the sigma-sorted windows by default"
+    perm, nsig = order
+    ncol = tr.getColumnDensityGrid()                               # [constituent][chord], chord = m*n_orb + p
+    chi = [con.chi for con in tr.atmosphere.densityDistributionList[0].constituents]
+    scale = 4096.0 / np.log(2.0)
+    thin_v, hi_v, opaque_v = 0.125, 0.1 * scale, 50.0 * scale
+    sel = []
+    for p in (0, n_orb // 2):
+        N = ncol[0].reshape(-1, n_orb)[:, p] / chi[0]              # the absorber's column sum_x n dx; mixing ratios live in sigma
+        N = N[N > 0.0]
+        N_lo, N_hi = N.min(), N.max()
+        a = np.abs(nsig[p])
+        n_win = -(-n_wav // 256)
+        w = np.concatenate([a, np.full(n_win * 256 - n_wav, np.nan)]).reshape(n_win, 256)
+        smw, smin = np.nanmax(w, axis=1), np.nanmin(w, axis=1)
+        regimes = {
+            "thin2": N_lo * smw < thin_v,
+            "thin8": (N_lo * smw < hi_v) & (N_hi * smw >= thin_v),
+            "opaque": N_hi * smin > opaque_v,
+            "exp": (N_hi * smw >= hi_v) & (N_lo * smin <= opaque_v),
+        }
+        for name, mask in regimes.items():
+            idx = np.flatnonzero(mask)
+            assert idx.size, f"phase {p}: no window in regime {name}"
+            for win in (idx[0], idx[-1]):
+                for pos in (win * 256, min(win * 256 + 255, n_wav - 1)):      # both ends of the window
+                    sel.append(int(perm[p, pos]))
+    sel = np.unique(np.array(sel))
+    assert sel.size >= 16
+    inputs = oracle_inputs(spec, nist_rows)
+    inputs["tables"] = gpu_tables(tr)
+    m = oracle.build_model(spec, inputs)
+    n_c = len(m.rho) * len(m.phi) * len(m.orb)
+    bs = oracle.reference_batch_size(n_c, len(sel), len(m.x), False, 2.0)
+    kw = dict(batch_size=None if bs >= n_c else bs, wavelength=m.wavelength[sel])
+    R_ref = oracle.sum_over_chords(m, **kw)
+    R0 = oracle.sum_over_chords(m, opaque_only=True, **kw)
+    ok, worst = excess_depth_ok(R[:, sel], R_ref, R0)
+    assert ok, f"C5 regime columns: worst err/bound {worst:.3g}"
+    assert np.max(np.abs(R[:, sel] - R_ref)) < 5e-13, float(np.max(np.abs(R[:, sel] - R_ref)))
