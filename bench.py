@@ -321,6 +321,64 @@ def workload_config(name, spec, n_c, n_wav, n_gpus):
 
 
 # ------------------------------------------------------------------------------------------------
+# parity of the benchmarked result itself: the oracle (CPU, rank 0, as the checker) on a few columns over ALL chords
+# ------------------------------------------------------------------------------------------------
+def sigma_tables_of(tr):
+    out = {}
+    for i, d in enumerate(tr.atmosphere.densityDistributionList):
+        for con in d.constituents:
+            if not con.isMolecule:
+                out[(i, con.species.name)] = (np.asarray(con.lookupFunction.x), np.asarray(con.lookupFunction.y))
+    return out
+
+
+def parity_check(spec, tr, R, n_cols=8):
+    """R (n_orb, n_wav) of the timed workload against the oracle on the deepest line core, its neighbours and a
+    strided set of columns (>= n_cols), every chord, the GPU's own sigma tables.  North-star criterion:
+    |E - E_ref| <= 1e-10 + 1e-6 |E_ref| with E = R0 - R."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from helpers import oracle, oracle_inputs
+    t0 = time.perf_counter()
+    inputs = oracle_inputs(spec, nist_rows() if spec.get("linelist", "nist") == "nist" else None)
+    inputs["tables"] = sigma_tables_of(tr)
+    m = oracle.build_model(spec, inputs)
+    n_orb, n_wav = R.shape
+    assert np.array_equal(m.wavelength, np.asarray(tr.wavelength))
+    core = int(np.argmin(R.min(axis=0)))
+    sel = np.unique(np.clip(np.concatenate([[core - 1, core, core + 1], np.linspace(0, n_wav - 1, n_cols).astype(int)]), 0, n_wav - 1))
+    has_mol = any(c.kind == "molecule" for sc_ in m.scenarios for c in sc_.constituents)
+    n_c = len(m.rho) * len(m.phi) * len(m.orb)
+    bs = oracle.reference_batch_size(n_c, len(sel), len(m.x), has_mol, 2.0)
+    kw = dict(batch_size=None if bs >= n_c else bs, wavelength=m.wavelength[sel])
+    R_ref = oracle.sum_over_chords(m, **kw)
+    R0 = oracle.sum_over_chords(m, opaque_only=True, **kw)
+    E, E_ref = R0 - R[:, sel], R0 - R_ref
+    worst = float(np.max(np.abs(E - E_ref) / (1e-10 + 1e-6 * np.abs(E_ref))))
+    return {"n_cols": int(sel.size), "n_chords": int(n_c), "columns": [int(i) for i in sel],
+            "max_abs_diff": float(np.max(np.abs(R[:, sel] - R_ref))), "worst_err_over_bound": worst,
+            "max_excess_depth": float(E_ref.max()), "checker": "oracle/prometheus_oracle.py on rank 0's host cores",
+            "seconds": time.perf_counter() - t0}
+
+
+# ------------------------------------------------------------------------------------------------
+# FP64 work per unit, counted from the instruction streams (profiles/r02_sass_*.txt), add/mul = 1, FMA = 2
+# ------------------------------------------------------------------------------------------------
+FLOPS_MOMENT_ITEM = 33.0      # kernel (m), per (item, wavelength): d = V1 - V0 (1), fma(tc, d, V0) (2), table exp (12),
+                              # Horner of 8 moments (16), e * p (1), accumulate (1)
+FLOPS_MOMENT_BLOCK = 15.0     # kernel (m), per (chord pair, wavelength) besides its items and atoms: table exp (12) + clamp,
+                              # subtract the offset sum (1), weight * exp accumulate (2)
+
+
+def fp64_roofline(kernel, flops, kernel_ms, peak_tflops, clocks_mhz=None, **extra):
+    ach = flops / (kernel_ms * 1e-3) / 1e12
+    out = {"kernel": kernel, "bound": "fp64", "achieved": ach, "peak": peak_tflops, "unit": "TFLOP/s", "frac": ach / peak_tflops,
+           "peak_source": "DFMA-chain probe on this GPU in this run (pb200_probe_fp64; MEASURED_PEAKS.json holds no FP64 figure)",
+           "kernel_ms": kernel_ms, "flops_per_launch": flops}
+    out.update(extra)
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
 # B200 arm
 # ------------------------------------------------------------------------------------------------
 def measured_peaks():
@@ -424,6 +482,92 @@ def retrieval_workload(n_models=64, steps=5, warmup=3, cpu_models=2):
             "h2d_bytes_per_model": int(info["n_orb"] * 8 * (2 + 2 + 4 + 8)), "d2h_bytes_per_model": int(info["n_orb"] * 8),
             "cpu_oracle_models_per_s_one_core": 1.0 / float(np.mean(t_cpu)),
             "max_abs_diff_lightcurve_gpu_vs_cpu": err}
+
+
+def strong_scaling(name, torch, dist, ctx, flush, dev, rank, world, local, steps=5, warmup=3):
+    """Fixed-size (strong) scaling of one BASELINE config: the UNCHANGED workload split over the `world` ranks --
+    block-cyclic wavelength tiles for atomic scenes (C5), contiguous wavelength chunks with trimmed sigma tables for
+    scenes that run kernel (m) (C2).  `ms_per_step`: device-resident, CUDA events, max over ranks, INCLUDING the NCCL
+    all-gather of the R tiles over NVLink and their placement into one (n_orb, n_wav) device array on every rank;
+    `ms_no_gather` without; `ms_one_gpu`: the whole job on one GPU in the same run (max over ranks);
+    efficiency = ms_one_gpu / (N * ms_per_step).  Parity: rank 0 checks the gathered result against the oracle."""
+    import prometheus_b200 as pb
+    from prometheus_b200 import distributed as pbd, scene
+    spec = scaled_spec(name, 1)
+    t0 = time.perf_counter()
+    tr = pb.build_transit(spec, nist_rows=nist_rows())
+    t_setup = time.perf_counter() - t0
+    sc, keep, info = scene.flatten(tr)
+    n_orb, n_wav, n_c = info["n_orb"], info["n_wav"], info["n_chords"]
+    atomic = info["n_mols"] == 0 and not (sc.n_fstar > 0 and sc.vsini != 0.0)
+    axis = "cyclic" if atomic else "wavelength"
+
+    def timed(fn, n):
+        ms = []
+        for i in range(warmup + n):
+            flush.zero_()
+            if world > 1:
+                dist.barrier()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            torch.cuda.synchronize(dev)
+            if i >= warmup:
+                ms.append(a.elapsed_time(b))
+        t = torch.tensor([float(np.mean(ms))], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # the whole job on one GPU (every rank does it; max over ranks)
+    ctx.set_scene(sc, keep)
+    whole = torch.empty(n_orb * n_wav, dtype=torch.float64, device=dev)
+    kern1 = []
+    ms_one = timed(lambda: kern1.append(ctx.run_device(0, n_orb, 0, n_wav, whole.data_ptr(), want_timing=True)), steps)
+    res = {"title": spec["title"], "n_chords": n_c, "n_wav": n_wav, "axis": axis, "ms_one_gpu": ms_one,
+           "kernels_ms_one_gpu": {k: float(np.mean([t[k] for t in kern1[warmup:]])) for k in ("column_ms", "transit_ms", "finalize_ms")},
+           "setup_seconds": t_setup}
+    if world == 1:
+        res.update(ms_per_step=ms_one, ms_no_gather=ms_one, efficiency=1.0)
+        R = whole.view(n_orb, n_wav).cpu().numpy()
+    else:
+        if axis == "wavelength":     # this rank's chunk only needs the part of each sigma table its wavelengths reach
+            sc_r, keep_r, _ = scene.flatten(tr, wav_range=pbd.partition(n_wav, world)[rank])
+            ctx.set_scene(sc_r, keep_r)
+        st = pbd.ShardedTransit(n_orb, n_wav, None, axis, dev)
+        kern = []
+        st.compute_tile = pbd.tile_function(ctx, axis, world, rank, want_timing=True, sink=kern)
+        ms_ng = timed(lambda: st.run_device(gather=False), steps)
+        mine = {k: float(np.mean([t[k] for t in kern[warmup:]])) for k in ("column_ms", "transit_ms", "finalize_ms")}
+        st.compute_tile = pbd.tile_function(ctx, axis, world, rank)
+
+        def step():
+            st.run_device(gather=True)
+            st.unpack_device()
+        ms_n = timed(step, steps)
+        per_rank = [None] * world
+        dist.all_gather_object(per_rank, mine)
+        state = {}
+        wall = []
+        for i in range(2 + 3):
+            dist.barrier()
+            torch.cuda.synchronize(dev)
+            t0 = time.perf_counter()
+            R = pbd.sum_over_chords(tr, None, axis, local, 0, state)     # host buffers in, numpy out on rank 0
+            wall.append((time.perf_counter() - t0) * 1e3)
+        e2e = torch.tensor([float(np.mean(wall[2:]))], dtype=torch.float64, device=dev)
+        dist.all_reduce(e2e, op=dist.ReduceOp.MAX)
+        res.update(ms_per_step=ms_n, ms_no_gather=ms_ng, efficiency=ms_one / (world * ms_n),
+                   efficiency_no_gather=ms_one / (world * ms_ng), kernels_ms_per_rank=per_rank,
+                   e2e_ms_per_call=float(e2e.item()), gather_bytes=int(n_orb * n_wav * 8))
+        st.run_device(gather=True)
+        R = st.to_host(0)
+    if rank == 0:
+        res["samples_per_s"] = float(n_c) * n_wav / (res["ms_per_step"] * 1e-3)
+        res["parity_check"] = parity_check(spec, tr, R, 8)
+        assert res["parity_check"]["worst_err_over_bound"] <= 1.0, res["parity_check"]
+    return res
 
 
 def run_b200(args):
@@ -556,6 +700,19 @@ def run_b200(args):
         if world > 1:
             dist.all_reduce(e2e_total, op=dist.ReduceOp.MAX)
         e2e_ms_per_step = float(e2e_total.item()) / args.steps
+        # ---- per-rank host timeline of the last e2e call, fixed-size scaling block (all ranks take part) --------
+        breakdown = None
+        if world > 1:
+            mine = dict(state.get("host_ms") or {})
+            mine["rank"] = rank
+            breakdown = [None] * world
+            dist.all_gather_object(breakdown, mine)
+        strong = {}
+        for name in [w for w in args.strong.split(",") if w]:
+            strong[name] = strong_scaling(name, torch, dist, ctx, flush, dev, rank, world, local)
+        ctx.set_scene(sc, keep)
+    # ---- parity of the benchmarked result (rank 0; the others wait in the collective below) -------------------
+    pcheck = parity_check(spec, tr, R_e2e, 8) if rank == 0 else None
     h2d_local = state["info"]["h2d_bytes"] if (world > 1 and "info" in state) else info["h2d_bytes"]
     launch_total = torch.tensor([launches, h2d_local], dtype=torch.int64, device=dev)
     if world > 1:
@@ -567,16 +724,43 @@ def run_b200(args):
     assert R_dev.shape == (n_orb, n_wav) and np.all(np.isfinite(R_dev)) and np.array_equal(R_dev, R_e2e)
     cull_diff = float(np.max(np.abs(R_dev - R_nc)))
     assert cull_diff < 1e-12, cull_diff
+    assert pcheck["worst_err_over_bound"] <= 1.0, pcheck
 
     hbm_peak, peak_src = measured_peaks()
     tile_samples = float(n_c) * float(st.samples_tile_shape[1])          # nominal samples of this rank's tile
     if n_mols:
         executed = nc_executed = exp_samples = tile_samples                 # kernel (m) has no culling
-    # The roofline describes the launch that does the exp on EVERY unblocked sample (the `off` leg below: no
-    # culling, no pairing, no thin path) -- that is the kernel whose per-sample work SURVEY 8(d) counts; the
-    # production launch skips most of those samples and is described under `culling`.
-    achieved = BYTES_PER_SAMPLE_STAGED * nc_executed / (nc_kernel_ms * 1e-3) / 1e9
-    fl = executed_flops_per_sample(n_atoms) * nc_executed / (nc_kernel_ms * 1e-3) / 1e12
+    n_abs = sum(1 for d in tr.atmosphere.densityDistributionList if any(not c.isMolecule for c in d.constituents))
+    fps = executed_flops_per_sample(n_abs)
+    # The bound of kernel (c') is the FP64 pipe (31 flops against 0.1 B per sample).  The headline figure is taken on the
+    # launch that does the exp on EVERY unblocked sample (pb200_set_option CULL = MIRROR = THIN = 0: the kernel whose
+    # per-sample work SURVEY 8(d) counts); the production launch of this workload -- most samples culled or summed as
+    # thin-chord expansions -- is described beside it, and for the configs where a kernel dominates the production
+    # launch itself carries the roofline (other_workloads.C5 / .C2).
+    staged = BYTES_PER_SAMPLE_STAGED * nc_executed / (nc_kernel_ms * 1e-3) / 1e9
+    roof = fp64_roofline("transit_kernel (c': tau + exp(-tau) + disk sum), every unblocked sample through the table exp",
+                         fps * nc_executed, nc_kernel_ms, probe["dfma_tflops"],
+                         flops_per_sample=fps, samples_per_launch=nc_executed,
+                         flops_per_sample_survey_convention=flops_per_sample(n_abs),
+                         launch="pb200_set_option CULL = MIRROR = THIN = 0 (measurement launch; same kernel, same tiles)",
+                         traffic=recorded_traffic(args.workload),
+                         traffic_note="dram bytes per launch from the committed ncu capture (profiles/traffic.json); below the algorithmic bytes: R stays in L2",
+                         pipe_frac=((6.0 if n_abs == 1 else 6.0 + n_abs) * nc_executed / 32.0 * 2.0) /
+                                   (148 * 4 * (clk["sm_mhz"] or 1965.0) * 1e6 * nc_kernel_ms * 1e-3) if n_mols == 0 else None,
+                         pipe_frac_note="issued FP64 warp instructions (6 per sample for one absorber, else 6+S) x 2 issue cycles / SMSP cycles",
+                         exp_probe_gops=probe["exp_gops"], exp_frac=nc_executed / (nc_kernel_ms * 1e-3) / 1e9 / probe["exp_gops"],
+                         staged_hbm_equivalent={"achieved": staged, "peak": hbm_peak, "unit": "GB/s", "frac": staged / hbm_peak,
+                                                "peak_source": peak_src,
+                                                "convention": "the north star's staged-equivalent 16 B per chord*lambda sample (one f64 tau store + "
+                                                              "one load, SURVEY 8(d)); tau is never staged, so this exceeds 1 by construction and "
+                                                              "is not a physical roofline"},
+                         production_launch={"kernel_ms": kernel_ms, "exp_samples": exp_samples, "flops": fps * exp_samples,
+                                            "achieved": fps * exp_samples / (kernel_ms * 1e-3) / 1e12,
+                                            "frac": fps * exp_samples / (kernel_ms * 1e-3) / 1e12 / probe["dfma_tflops"],
+                                            "traffic": recorded_traffic(args.workload, "transit_kernel_production"),
+                                            "note": "flops of the samples that take the table exp only; the thin-chord expansions "
+                                                    "(4 FP64 instructions per chord and thread) are not counted; this launch is short "
+                                                    "and latency-bound, see kernels_ms and DESIGN.md"})
     out = {
         "metric": "chord*lambda samples/s", "value": samples_total / (ms_per_step * 1e-3), "unit": "samples/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
@@ -586,26 +770,14 @@ def run_b200(args):
         "e2e": {"value": samples_total / (e2e_ms_per_step * 1e-3), "unit": "samples/s", "ms_per_step": e2e_ms_per_step,
                 "h2d_bytes_per_step": int(launch_total[1].item()), "d2h_bytes_per_step": int(n_orb * n_wav * 8),
                 "runs_per_s": 1e3 / e2e_ms_per_step},
-        "e2e_host_ms_rank0": (state.get("host_ms") if world > 1 else None),
-        "e2e_breakdown_ms": ({k: tr.last_timing[k] for k in ("upload_ms", "column_ms", "transit_ms", "finalize_ms", "download_ms")}
-                             if world == 1 and tr.last_timing else None),
+        "parity_check": pcheck,
+        "e2e_breakdown_ms": (breakdown if world > 1 else
+                             ({k: tr.last_timing[k] for k in ("upload_ms", "column_ms", "transit_ms", "finalize_ms", "download_ms")}
+                              if tr.last_timing else None)),
+        "strong": strong or None,
         "gpu_launches": int(launch_total[0].item()),
         "clocks": clk,
-        "roofline": {"kernel": "transit_kernel (c': tau + exp(-tau) + disk sum)", "bound": "hbm", "achieved": achieved,
-                     "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "peak_source": peak_src,
-                     "convention": "staged-equivalent 16 B per chord*lambda sample (SURVEY 8(d)); the fused kernel's true DRAM traffic is in `traffic`",
-                     "traffic": recorded_traffic(args.workload), "kernel_ms": nc_kernel_ms,
-                     "traffic_production_launch": recorded_traffic(args.workload, "transit_kernel_production"),
-                     "samples_per_launch": nc_executed,
-                     "samples_note": "measured on the launch with pb200_set_option CULL = MIRROR = THIN = 0, where every unblocked chord*lambda sample goes through the table exp; the production launch (kernels_ms.transit) evaluates `culling.exp_samples_per_rank_step` of them that way",
-                     "fp64": {"achieved_tflops": fl, "peak_tflops_dfma_probe": probe["dfma_tflops"],
-                              "frac": fl / probe["dfma_tflops"], "flops_per_sample": executed_flops_per_sample(n_atoms),
-                              "flops_per_sample_survey_convention": flops_per_sample(n_atoms),
-                              "pipe_frac": ((6.0 if n_atoms == 1 else 6.0 + n_atoms) * nc_executed / 32.0 * 2.0) /
-                                           (148 * 4 * (clk["sm_mhz"] or 1965.0) * 1e6 * nc_kernel_ms * 1e-3) if n_mols == 0 else None,
-                              "pipe_frac_note": "issued FP64 warp instructions (6 per sample for one absorber, else 6+S; nominal sample count) x 2 cycles / SMSP cycles: the binding unit",
-                              "exp_probe_gops": probe["exp_gops"],
-                              "exp_frac": nc_executed / (nc_kernel_ms * 1e-3) / 1e9 / probe["exp_gops"]}},
+        "roofline": roof,
         "culling": {"nominal_samples_per_step": tile_samples * world, "executed_samples_per_rank_step": executed,
                     "executed_frac": executed / tile_samples,
                     "exp_samples_per_rank_step": exp_samples, "exp_frac": exp_samples / tile_samples,
@@ -700,6 +872,7 @@ def main():
     ap.add_argument("--workload", default="C4")
     ap.add_argument("--others", default="C2,C3,C5", help="other BASELINE configs reported under other_workloads (N=1)")
     ap.add_argument("--no-retrieval", action="store_true", help="skip the retrieval-batch leg (N=1)")
+    ap.add_argument("--strong", default="C5,C2", help="configs of the fixed-size (strong) scaling block, split over the N ranks")
     ap.add_argument("--e2e-gather", action="store_true", help="N>1 e2e through all-gather + rank-0 D2H instead of the shared result")
     ap.add_argument("--cpu-seconds", type=float, default=None,
                     help="CPU budget: cpu_baseline sample (default 15 s) / whole --impl reference run (default 120 s)")

@@ -125,7 +125,10 @@ typedef struct {
                                     chords are summed without an exp; -1 = not yet known     */
     int64_t exp_samples;         /* of those, samples that went through the table exp (the
                                     others were optically thin for their warp: tau < 2.1e-5,
-                                    second-order expansion summed per chord); upper bound    */
+                                    second-order expansion summed per chord); upper bound.
+                                    Scenes with molecules (kernel (m), moment form): executed_samples =
+                                    unblocked chord-pair blocks x wavelengths, exp_samples = moment
+                                    items x wavelengths (one table exp + 8 FMAs each)         */
 } pb200_timing;
 
 /* ---- retrieval batches ------------------------------------------------

@@ -115,8 +115,11 @@ struct pb200_ctx {
     // moment form of kernel (m): per-chord items (grow-only), bins of the current scene (-1: not yet known)
     double* mol_items = nullptr;
     size_t mol_items_bytes = 0;
-    unsigned long long* d_mol_stat = nullptr;   // [0] bit pattern of d_max, [1] largest item count of a chord
+    unsigned long long* d_mol_stat = nullptr;   // [0] bit pattern of d_max, [1] largest item count of a chord, [2] items and
+                                                // [3] live (phase, chord pair) blocks of the last fill pass
     int mol_bins = -1;
+    int mol_max_items = -1;      // largest item count of a chord over ALL phases of the resident scene (-1: not yet counted)
+    bool mol_stats_pending = false;   // the last run was kernel (m) in moment form: check_oob reads [2], [3]
     bool buckets_ready = false;   // bucket indices of the sigma tables (built on the device before the first run of a scene)
     std::vector<std::pair<void*, int64_t>> regions;   // sharded uploads of the current scene: (device base, doubles per rank)
     // sigma-sorted order of the last run (pb200_last_sort_order; lives in `scratch` until the next run)
@@ -701,6 +704,7 @@ static int set_scene_impl(pb200_ctx* c, const pb200_scene* s, int n_ranks, int r
     c->base = h;
     c->lastR_full = false;
     c->mol_bins = -1;
+    c->mol_max_items = -1;
     return PB200_OK;
 }
 
@@ -741,6 +745,7 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     const int64_t launches0 = c->launches;
     c->lastR_full = false;
     c->last_perm = nullptr; c->last_nsig_sorted = nullptr; c->last_sort_n = 0;
+    c->mol_stats_pending = false;
 
     TransitParams prm;
     prm.phase_lo = phase_lo; prm.n_phase = n_phase; prm.wav_lo = wav_lo; prm.n_wav_sel = n_wav_sel;
@@ -839,10 +844,10 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     // form (measurement / regression).
     bool moments_done = false;
     if (c->general_path && h.n_mols > 0 && !c->opt[PB200_OPT_MOL_RECORDS]) {
-        if (!c->d_mol_stat) PB_CUDA(c, cudaMalloc((void**)&c->d_mol_stat, 16));
+        if (!c->d_mol_stat) PB_CUDA(c, cudaMalloc((void**)&c->d_mol_stat, 32));
         unsigned long long st[2] = {0ull, 0ull};
         if (c->mol_bins < 0) {   // d_max of the tables, once per scene
-            PB_CUDA(c, cudaMemsetAsync(c->d_mol_stat, 0, 16, c->stream));
+            PB_CUDA(c, cudaMemsetAsync(c->d_mol_stat, 0, 32, c->stream));
             launch_mol_dmax(c->d_scene, c->d_mol_stat, c->sm_count, c->stream);
             c->launches += 1;
             PB_CUDA(c, cudaMemcpyAsync(st, c->d_mol_stat, 8, cudaMemcpyDeviceToHost, c->stream));
@@ -855,12 +860,21 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
             // pair slots per phase, rounded up to whole chord tiles (the splits of the chord axis are whole tiles too)
             const int n_chord_items = h.mirror ? n_pairs : h.M;
             const int n_slots = ((n_chord_items + kChordTile - 1) / kChordTile) * kChordTile;
-            PB_CUDA(c, cudaMemsetAsync(c->d_mol_stat + 1, 0, 8, c->stream));
-            launch_mol_moments(c->d_scene, n_slots, phase_lo, n_phase, c->mol_bins, nullptr, 0, c->d_mol_stat, true, c->stream);
-            PB_CUDA(c, cudaMemcpyAsync(st, c->d_mol_stat + 1, 8, cudaMemcpyDeviceToHost, c->stream));
-            PB_CUDA(c, cudaStreamSynchronize(c->stream));
-            c->launches += 1;
-            const int max_items = st[0] > 0 ? (int)st[0] : 1;
+            // The item count of a chord depends on the scene (density rows, pressure grids, bins), not on the wavelength
+            // tile: counted once per scene over ALL its phases, so later runs of the scene have no host round trip.
+            if (c->mol_max_items < 0) {
+                PB_CUDA(c, cudaMemsetAsync(c->d_mol_stat + 1, 0, 8, c->stream));
+                if (!(phase_lo == 0 && n_phase == h.n_orb)) {   // the count needs every phase's density rows
+                    launch_column(c->d_scene, h.Mp, 0, h.n_orb, c->d_oob, c->sm_count, c->stream, true, 0);
+                    c->launches += 1;
+                }
+                launch_mol_moments(c->d_scene, n_slots, 0, h.n_orb, c->mol_bins, nullptr, 0, c->d_mol_stat, true, c->stream);
+                PB_CUDA(c, cudaMemcpyAsync(st, c->d_mol_stat + 1, 8, cudaMemcpyDeviceToHost, c->stream));
+                PB_CUDA(c, cudaStreamSynchronize(c->stream));
+                c->launches += 1;
+                c->mol_max_items = st[0] > 0 ? (int)st[0] : 1;
+            }
+            const int max_items = c->mol_max_items;
             const int stride_d = mol_block_stride(h.n_atoms, max_items);
             const size_t need = (size_t)n_phase * n_slots * stride_d * sizeof(double);
             if (need > c->mol_items_bytes) {
@@ -869,11 +883,12 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
                 PB_CUDA(c, cudaMalloc((void**)&c->mol_items, need));
                 c->mol_items_bytes = need;
             }
+            PB_CUDA(c, cudaMemsetAsync(c->d_mol_stat + 2, 0, 16, c->stream));
             launch_mol_moments(c->d_scene, n_slots, phase_lo, n_phase, c->mol_bins, c->mol_items, stride_d, c->d_mol_stat, false, c->stream);
             c->launches += 1;
             int n_launch = 0;
             cudaError_t e = launch_transit_moments(c->d_scene, h, prm, c->mol_items, stride_d, n_slots, c->stream, &n_launch);
-            if (e == cudaSuccess) { c->launches += n_launch; moments_done = true; }
+            if (e == cudaSuccess) { c->launches += n_launch; moments_done = true; c->mol_stats_pending = true; }
             else if (e != cudaErrorInvalidValue) return fail(c, PB200_ERR_CUDA, "transit (moments) launch: %s", cudaGetErrorString(e));
             else cudaGetLastError();   // does not fit shared memory: the per-record form below
         }
@@ -936,6 +951,13 @@ int check_oob(pb200_ctx* c) {
     if (c->last.executed_samples < 0) {
         c->last.executed_samples = (int64_t)st[1] * c->last_n_wav_sel;
         c->last.exp_samples = (int64_t)st[2] * 32 * c->last_wpt;   // a warp owns 32 * WPT wavelengths
+    }
+    if (c->mol_stats_pending) {   // kernel (m), moment form: (live chord-pair blocks, items) x wavelengths
+        unsigned long long ms[2] = {0, 0};
+        PB_CUDA(c, cudaMemcpy(ms, c->d_mol_stat + 2, sizeof ms, cudaMemcpyDeviceToHost));
+        c->last.executed_samples = (int64_t)ms[1] * c->last_n_wav_sel;
+        c->last.exp_samples = (int64_t)ms[0] * c->last_n_wav_sel;
+        c->mol_stats_pending = false;
     }
     if (flag) {
         PB_CUDA(c, cudaMemsetAsync(c->d_oob, 0, sizeof(int), c->stream));
@@ -1217,6 +1239,7 @@ extern "C" int pb200_set_models(pb200_ctx* c, int n_models, const pb200_model* m
     }
     rc = plan_derived(c);
     if (rc) return rc;
+    c->mol_max_items = -1;   // other densities: other item counts
     PB_CUDA(c, cudaMemcpyAsync(c->d_scene, &h, sizeof(DevScene), cudaMemcpyHostToDevice, c->stream));
     launch_sky_cells(c->d_scene, h.Mp, c->stream);   // the derived arena was laid out afresh
     launch_fout_scalar(c->d_scene, c->stream);

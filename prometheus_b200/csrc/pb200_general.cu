@@ -366,6 +366,7 @@ mol_moment_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, i
     const DevScene& sc = *scp;
     const int64_t cid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     int n_items = 0;
+    bool live_block = false;
     if (cid < (int64_t)n_phase * n_slots) {
         const int pi = (int)(cid / n_slots), q = (int)(cid % n_slots), p = phase_lo + pi;
         const int n2 = sc.n_phi / 2, Pm = (n2 + 1) / 2;
@@ -394,6 +395,7 @@ mol_moment_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, i
         }
         if (wv != 0.0) {   // blocked: F_in = 0 (gasProperties.py:1233)
             int node0 = 0;
+            live_block = true;
             for (int k = 0; k < sc.n_cons; ++k) {
                 const DevConstituent& C = sc.cons[k];
                 if (C.kind != 1) continue;
@@ -467,6 +469,11 @@ mol_moment_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, i
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) n_items = max(n_items, __shfl_xor_sync(0xffffffffu, n_items, o));
         if ((threadIdx.x & 31) == 0 && n_items > 0) atomicMax(stat + 1, (unsigned long long)n_items);
+    } else {   // run statistics: items and live blocks of the run (the work kernel (m) does per wavelength)
+        int live = n_items > 0 || live_block ? 1 : 0, tot = n_items;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { tot += __shfl_xor_sync(0xffffffffu, tot, o); live += __shfl_xor_sync(0xffffffffu, live, o); }
+        if ((threadIdx.x & 31) == 0 && live > 0) { atomicAdd(stat + 2, (unsigned long long)tot); atomicAdd(stat + 3, (unsigned long long)live); }
     }
 }
 
