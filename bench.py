@@ -396,7 +396,7 @@ def recorded_traffic(workload, kernel="transit_kernel"):
     return None
 
 
-def quick_workload(name, ctx, torch, stream, flush, steps=3, warmup=3):
+def quick_workload(name, ctx, torch, stream, flush, peak_tflops, steps=3, warmup=3):
     """Device-resident samples/s of another workload on this rank's GPU (3 warm-up + 3 timed steps)."""
     import prometheus_b200 as pb
     from prometheus_b200 import scene
@@ -430,6 +430,7 @@ def quick_workload(name, ctx, torch, stream, flush, steps=3, warmup=3):
            "kernels_ms": {k: float(np.mean([t[k] for t in kern])) for k in ("column_ms", "transit_ms", "finalize_ms")},
            "setup_seconds": t_setup, "R_min": float(R.min()), "R_max": float(R.max()),
            "executed_frac": float(np.mean([t["executed_samples"] for t in kern])) / samples}
+    res["roofline"] = workload_roofline(name, tr, info, kern, peak_tflops)
     if info["n_mols"]:
         res["molecular_lookups_per_s"] = samples * info["n_x"] * info["n_mols"] / (np.mean(ms) * 1e-3)
     return res
@@ -484,7 +485,28 @@ def retrieval_workload(n_models=64, steps=5, warmup=3, cpu_models=2):
             "max_abs_diff_lightcurve_gpu_vs_cpu": err}
 
 
-def strong_scaling(name, torch, dist, ctx, flush, dev, rank, world, local, steps=5, warmup=3):
+def workload_roofline(name, tr, info, timings, peak_tflops):
+    """FP64-pipe roofline of the PRODUCTION launch of a workload's dominant kernel, from the library's own counters:
+    atomic scenes -- kernel (c'): samples that took the table exp x flops per sample; scenes with molecules -- kernel (m)
+    in moment form: items x wavelengths x 33 + blocks x wavelengths x (15 + 2 per atomic constituent)."""
+    ms = float(np.mean([t["transit_ms"] for t in timings]))
+    exp_s = float(np.mean([t["exp_samples"] for t in timings]))
+    exe_s = float(np.mean([t["executed_samples"] for t in timings]))
+    if info["n_mols"]:
+        flops = FLOPS_MOMENT_ITEM * exp_s + (FLOPS_MOMENT_BLOCK + 2.0 * info["n_atoms"]) * exe_s
+        return fp64_roofline("transit_moment_kernel (m: molecular tau in moment form + atoms + exp + disk sum)", flops, ms, peak_tflops,
+                             item_wavelengths=exp_s, block_wavelengths=exe_s, flops_per_item=FLOPS_MOMENT_ITEM,
+                             flops_per_block=FLOPS_MOMENT_BLOCK + 2.0 * info["n_atoms"],
+                             traffic=recorded_traffic(name, "transit_moment_kernel"))
+    n_abs = sum(1 for d in tr.atmosphere.densityDistributionList if any(not c.isMolecule for c in d.constituents))
+    fps = executed_flops_per_sample(n_abs)
+    return fp64_roofline("transit_kernel (c'), production launch", fps * exp_s, ms, peak_tflops, exp_samples=exp_s,
+                         flops_per_sample=fps, executed_samples=exe_s,
+                         note="flops of the samples that take the table exp; thin-chord expansions and skipped (opaque) chords not counted",
+                         traffic=recorded_traffic(name, "transit_kernel_production"))
+
+
+def strong_scaling(name, torch, dist, ctx, flush, dev, rank, world, local, peak_tflops, steps=5, warmup=3):
     """Fixed-size (strong) scaling of one BASELINE config: the UNCHANGED workload split over the `world` ranks --
     block-cyclic wavelength tiles for atomic scenes (C5), contiguous wavelength chunks with trimmed sigma tables for
     scenes that run kernel (m) (C2).  `ms_per_step`: device-resident, CUDA events, max over ranks, INCLUDING the NCCL
@@ -527,7 +549,7 @@ def strong_scaling(name, torch, dist, ctx, flush, dev, rank, world, local, steps
     ms_one = timed(lambda: kern1.append(ctx.run_device(0, n_orb, 0, n_wav, whole.data_ptr(), want_timing=True)), steps)
     res = {"title": spec["title"], "n_chords": n_c, "n_wav": n_wav, "axis": axis, "ms_one_gpu": ms_one,
            "kernels_ms_one_gpu": {k: float(np.mean([t[k] for t in kern1[warmup:]])) for k in ("column_ms", "transit_ms", "finalize_ms")},
-           "setup_seconds": t_setup}
+           "setup_seconds": t_setup, "roofline_one_gpu": workload_roofline(name, tr, info, kern1[warmup:], peak_tflops)}
     if world == 1:
         res.update(ms_per_step=ms_one, ms_no_gather=ms_one, efficiency=1.0)
         R = whole.view(n_orb, n_wav).cpu().numpy()
@@ -590,7 +612,8 @@ def run_b200(args):
     spec = scaled_spec(args.workload, world)
     with torch.cuda.stream(stream):
         ctx.set_stream(stream.cuda_stream)
-        probe = ctx.probe_fp64() if rank == 0 else None
+        probe = ctx.probe_fp64()
+        peak_dfma = probe["dfma_tflops"]
         t0 = time.perf_counter()
         tr = pb.build_transit(spec, nist_rows=nist_rows())            # sigma tables: kernel (b2), set-up time
         t_setup = time.perf_counter() - t0
@@ -709,7 +732,7 @@ def run_b200(args):
             dist.all_gather_object(breakdown, mine)
         strong = {}
         for name in [w for w in args.strong.split(",") if w]:
-            strong[name] = strong_scaling(name, torch, dist, ctx, flush, dev, rank, world, local)
+            strong[name] = strong_scaling(name, torch, dist, ctx, flush, dev, rank, world, local, peak_dfma)
         ctx.set_scene(sc, keep)
     # ---- parity of the benchmarked result (rank 0; the others wait in the collective below) -------------------
     pcheck = parity_check(spec, tr, R_e2e, 8) if rank == 0 else None
@@ -822,7 +845,7 @@ def run_b200(args):
         out["other_workloads"] = {}
         for name in [w for w in args.others.split(",") if w and w != args.workload]:
             with torch.cuda.stream(stream):
-                out["other_workloads"][name] = quick_workload(name, ctx, torch, stream, flush)
+                out["other_workloads"][name] = quick_workload(name, ctx, torch, stream, flush, peak_dfma)
     if world == 1 and not args.no_retrieval:
         out["retrieval"] = retrieval_workload()
 

@@ -1,0 +1,44 @@
+"""One workload, a few runs, for ncu (profiles/ holds the summaries):
+
+    ncu --set full --clock-control none --import-source on -k regex:<kernel> -c <n> -o gpurun_out/<name> \
+        python profiles/run_once.py <workload> [runs] [kernel_a] [opt=value ...]
+
+`kernel_a`: also launch the materialised number density (pb200_number_density_device) of scenario 0."""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch  # noqa: E402
+
+import prometheus_b200 as pb  # noqa: E402
+from prometheus_b200 import host, scene, workloads  # noqa: E402
+
+
+def main(argv):
+    name = argv[0]
+    runs = int(argv[1]) if len(argv) > 1 and argv[1].isdigit() else 3
+    opts = dict(a.split("=") for a in argv[1:] if "=" in a)
+    rows = np.load(os.path.join(ROOT, "tests", "golden", "linelist.npz"))["rows"]
+    ctx = host.get_context(0)
+    for k, v in opts.items():
+        ctx.set_option(k, int(v))
+    tr = pb.build_transit(workloads.get(name), nist_rows=rows)
+    sc, keep, info = scene.flatten(tr)
+    ctx.set_scene(sc, keep)
+    out = torch.empty(info["n_orb"] * info["n_wav"], dtype=torch.float64, device="cuda:0")
+    for _ in range(runs):
+        t = ctx.run_device(0, info["n_orb"], 0, info["n_wav"], out.data_ptr(), want_timing=True)
+    print(name, {k: round(v, 4) if isinstance(v, float) else v for k, v in t.items()})
+    if "kernel_a" in argv:
+        dens = torch.empty(info["n_chords"] * info["n_x"], dtype=torch.float64, device="cuda:0")
+        for _ in range(runs):
+            ctx.number_density_device(0, dens.data_ptr())
+        ctx.synchronize()
+        torch.cuda.synchronize()
+
+
+if __name__ == "__main__":
+    main(sys.argv[1:])

@@ -33,7 +33,7 @@ cudaError_t launch_transit_general(const DevScene*, const DevScene& host_copy, c
                                    cudaStream_t, int* n_launch);
 void launch_sigma_phase(const DevScene*, const TransitParams&, cudaStream_t);
 void launch_bucket_build(const DevScene*, int sm_count, cudaStream_t);
-cudaError_t launch_compact(const DevScene*, const TransitParams&, bool cull, cudaStream_t);
+cudaError_t launch_compact(const DevScene*, const TransitParams&, bool cull, bool small, cudaStream_t);
 void launch_finalize(const DevScene*, const TransitParams&, int sm_count, cudaStream_t);
 void launch_sigma_lookup(const double*, const double*, int64_t, double, const double*, int64_t, double*, int,
                          cudaStream_t);
@@ -98,6 +98,8 @@ struct pb200_ctx {
     int last_wpt = 8;
     double* d_exp_tab = nullptr; // 2^(j/64), j < 64
     cudaEvent_t ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // 6,7: scene upload
+    cudaStream_t aux = nullptr;          // sigma_phase (+ sort) of a run goes here, beside the column kernel on `stream`
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     pb200_timing last = {};
     double upload_ms = 0.0;
     // retrieval batches (pb200_set_models): the scene as uploaded, the stacked per-phase arrays of the batch
@@ -210,6 +212,9 @@ int pb200_create(int device, pb200_ctx** out) {
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) { c->own_stream = true; e = cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device); }
     for (int i = 0; i < 8 && e == cudaSuccess; ++i) e = cudaEventCreate(&c->ev[i]);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->aux, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_scene, sizeof(DevScene));
     if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_oob, 32);   // [0] out-of-grid flag, [8..16) active records, [16..24) thick (warp, chord) pairs of the run
     if (e == cudaSuccess) e = cudaMemset(c->d_oob, 0, 32);
@@ -259,6 +264,9 @@ void pb200_destroy(pb200_ctx* c) {
     if (c->d_oob) cudaFree(c->d_oob);
     if (c->d_exp_tab) cudaFree(c->d_exp_tab);
     for (auto& e : c->ev) if (e) cudaEventDestroy(e);
+    if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+    if (c->ev_join) cudaEventDestroy(c->ev_join);
+    if (c->aux) { cudaStreamSynchronize(c->aux); cudaStreamDestroy(c->aux); }
     if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -390,7 +398,7 @@ static int plan_derived(pb200_ctx* c) {
     const bool fstar_per_chord = h.n_fstar > 0 && h.vsini != 0.0;
     struct Want { double** p; size_t n; };
     std::vector<Want> wants;
-    double *nmax_d = nullptr, *smax_d = nullptr, *nact_d = nullptr;
+    double *nmax_d = nullptr, *smax_d = nullptr, *nact_d = nullptr, *ymax_d = nullptr;
     wants.push_back({&h.w_out, (size_t)h.Mp});
     wants.push_back({&h.star_shift, (size_t)h.Mp});
     wants.push_back({&h.w_in, (size_t)h.n_orb * h.Mp});
@@ -399,6 +407,7 @@ static int plan_derived(pb200_ctx* c) {
     wants.push_back({&nmax_d, (size_t)(n_atoms ? n_atoms : 1) * h.n_orb});
     wants.push_back({&smax_d, (size_t)(n_atoms ? n_atoms : 1) * h.n_orb});
     wants.push_back({&nact_d, (size_t)(h.n_orb + 1) / 2});
+    wants.push_back({&ymax_d, (size_t)kMaxConstituents});
     wants.push_back({&h.w0, (size_t)h.n_orb});
     wants.push_back({&h.thin_tot, (size_t)h.n_orb * 8});
     for (int i = 0; i < h.n_scen; ++i)
@@ -430,6 +439,8 @@ static int plan_derived(pb200_ctx* c) {
     h.nmax = reinterpret_cast<unsigned long long*>(nmax_d);
     h.smax = reinterpret_cast<unsigned long long*>(smax_d);
     h.n_act = reinterpret_cast<int*>(nact_d);
+    h.tab_ymax = reinterpret_cast<unsigned long long*>(ymax_d);
+    PB_CUDA(c, cudaMemsetAsync(ymax_d, 0, kMaxConstituents * sizeof(double), c->stream));
     h.stat = reinterpret_cast<unsigned long long*>(c->d_oob);
     PB_CUDA(c, cudaMemsetAsync(nmax_d, 0, (size_t)(n_atoms ? n_atoms : 1) * h.n_orb * sizeof(double), c->stream));
     PB_CUDA(c, cudaMemsetAsync(smax_d, 0, (size_t)(n_atoms ? n_atoms : 1) * h.n_orb * sizeof(double), c->stream));
@@ -798,6 +809,7 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     char* sort_base = reinterpret_cast<char*>(c->scratch) + ((r_bytes + part_bytes + nsig_bytes + order_bytes + winmax_bytes + al) & ~al);
 
     PB_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
+    cudaStream_t sig_stream = c->stream;
     if (!c->general_path) {   // sigma(p, w) of the tile and its per-phase maxima, needed by the culling below
         if (h.n_atoms < 1) return fail(c, PB200_ERR_INVALID, "scene has no absorbing constituent");
         if (h.n_abs > PB200_MAX_ABSORBERS)   // before any kernel that sizes shared memory by the absorber count
@@ -809,7 +821,12 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
             c->launches += 1;
             c->buckets_ready = true;
         }
-        launch_sigma_phase(c->d_scene, prm, c->stream);
+        // sigma_phase (+ the sort) and the column kernel do not depend on each other (the column kernel bounds sigma by
+        // the tables' maxima): fork -- sigma on the auxiliary stream, column on the main one -- and join before compaction
+        PB_CUDA(c, cudaEventRecord(c->ev_fork, c->stream));
+        PB_CUDA(c, cudaStreamWaitEvent(c->aux, c->ev_fork, 0));
+        sig_stream = c->aux;
+        launch_sigma_phase(c->d_scene, prm, sig_stream);
         c->launches += 1;
         if (sorted) {
             auto take = [&](size_t bytes) { char* p0 = sort_base; sort_base += (bytes + al) & ~al; return p0; };
@@ -819,7 +836,7 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
             int* v_in = reinterpret_cast<int*>(take((size_t)n_out * 4));
             int* perm = reinterpret_cast<int*>(take((size_t)n_out * 4));
             void* temp = take(sort_temp);
-            cudaError_t e = launch_sigma_sort(prm.nsig, n_phase, n_wav_sel, k_in, k_out, v_in, perm, temp, sort_temp, nsig_sorted, c->stream);
+            cudaError_t e = launch_sigma_sort(prm.nsig, n_phase, n_wav_sel, k_in, k_out, v_in, perm, temp, sort_temp, nsig_sorted, sig_stream);
             if (e != cudaSuccess) return fail(c, PB200_ERR_CUDA, "sigma sort: %s", cudaGetErrorString(e));
             c->launches += 3;   // keys, gather + the radix sort's own passes
             prm.nsig = nsig_sorted;
@@ -834,7 +851,9 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
                   c->general_path ? 0 : (cull ? 1 : 2));
     c->launches += 1;
     if (!c->general_path) {   // chord records of kernel (c'), transparent chords culled
-        PB_CUDA(c, launch_compact(c->d_scene, prm, cull, c->stream));
+        PB_CUDA(c, cudaEventRecord(c->ev_join, c->aux));
+        PB_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_join, 0));
+        PB_CUDA(c, launch_compact(c->d_scene, prm, cull, h.M <= 4096, c->stream));
         c->launches += 1;
     }
     PB_CUDA(c, cudaGetLastError());

@@ -1,9 +1,10 @@
 // pb200_density.cu -- kernels (a)/(a'): chord weights, blocking mask, number density and
 // column density on the chord grid.  SURVEY 8(a) rows a2, a4, a6, a7, a8 (column part).
 //
-// Work decomposition: one warp per chord (phase p, sky cell m = i_phi*n_rho + i_rho); the 32 lanes
-// stride over the line-of-sight axis x and are reduced with warp shuffles in fp64.  Chord axes are a
-// few hundred doubles and live in L1; the only HBM traffic is the coalesced store of the result.
+// Work decomposition: atoms-only scenes (the run path) -- column_cta_kernel, one CTA per 256 chords of a phase, 8 lanes
+// per chord in the x-sum; scenes with molecules -- column_kernel, one warp per chord, which also stores the density
+// rows kernel (m) needs.  Chord axes are a few hundred doubles and live in L1 / shared memory; the only HBM traffic is
+// the coalesced store of the result.
 #include "pb200_internal.cuh"
 
 namespace pb200 {
@@ -119,135 +120,235 @@ column_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, int* 
     }
 }
 
-// ---- (a') fast form for scenes without molecules: one THREAD per chord -------------------------
-// All 32 lanes stay busy whatever n_x is, there are no shuffles, x[ix] is a warp-uniform load, and the
-// per-chord pieces of the formulas are hoisted out of the x loop (torus: exp(-(z/H)^2); power law:
-// (R/r)^q = exp(q (ln R - ln(r^2)/2)) instead of pow: <= 3e-14 relative, Ncol is tested to 1e-12).
-// Four partial sums per thread give ILP and halve the rounding growth of the long sum.
-template <class F>
-__device__ __forceinline__ double pb_sum4(int n, F term) {
-    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-    int ix = 0;
-    for (; ix + 4 <= n; ix += 4) {
-        a0 += term(ix); a1 += term(ix + 1); a2 += term(ix + 2); a3 += term(ix + 3);
-    }
-    for (; ix < n; ++ix) a0 += term(ix);
-    return (a0 + a1) + (a2 + a3);
-}
+// ---- (a') fast form for scenes without molecules ------------------------------------------------
+// The analytic scenarios along one chord.  What does not depend on x is hoisted twice:
+//   * per (scenario, phase) -- ScnConst: radii, scale heights, exponents, q log2 R, the density centre; uniform over
+//     a CTA whose chords share the phase;
+//   * per chord -- (pre, cc): n(x) = pre * term(dx^2, cc) with cc = dy^2 + z^2 (spherical scenarios) or dy^2 (torus,
+//     whose exp(-(z/H)^2) goes into pre).
+// term() is branch-free (pb_rsqrt_nb, pb_exp2_tab_nb, pb_log2_tab: no sqrt / division / libm slow paths), so the
+// independent samples of a lane interleave; the rare denormal band of the exp is redone exactly by pb_term_exact.
+// Accuracy against the libm forms of pb_density: <= 3e-14 relative (Ncol is tested to 1e-12).
+struct ScnConst {
+    int type;
+    double n0;        // P[0] * amplitude(p)
+    double a, b, c;   // barometric {R, log2e/H, -}; hydrostatic {R, G mu M/(kB T), jc/R}; power law {R^2, -q/2, q log2 R};
+                      // torus {a_t, 1/(4 H), 1/H}
+    double cx, cy;    // density centre at this phase
+};
 
-// The analytic scenarios along one chord: use(prefactor, term) is called once with the per-chord prefactor and a
-// functor term(ix) such that n(x_ix) = prefactor * term(ix) -- everything that does not depend on x is hoisted
-// (torus: exp(-(z/H)^2); power law: q log2 R), exp / pow go through the L1-resident tables of pb200_math.cuh.
-// Shared by the fused x-sum (kernel (a'), use = pb_sum4) and the materialising kernel (a) (use = store).
-template <class Use>
-__device__ __forceinline__ double pb_chord_terms(const DevScene& sc, const DevScenario& S, int p, double amp, double y,
-                                                 double z, Use&& use) {
-    const double* __restrict__ xs = sc.x;
-    const double cx = S.centre_x[p];
-    const double dy = y - S.centre_y[p];
+__device__ __forceinline__ ScnConst pb_scn_const(const DevScenario& S, int p) {
+    ScnConst k;
     const double* __restrict__ P = pb_params(S, p);
-    const double n0 = P[0] * amp;
-    const double* __restrict__ big = sc.exp_tab + kExpTabEntries;
-    const double2* __restrict__ ltab = reinterpret_cast<const double2*>(sc.exp_tab + kExpTabEntries + kExpBigEntries);
+    k.type = S.type;
+    k.n0 = P[0] * (S.amplitude ? S.amplitude[p] : 1.0);
+    k.cx = S.centre_x ? S.centre_x[p] : 0.0;
+    k.cy = S.centre_y ? S.centre_y[p] : 0.0;
+    k.a = k.b = k.c = 0.0;
     const double kLog2e = 1.4426950408889634;
     switch (S.type) {
-        case PB200_SCN_BAROMETRIC: {   // n0 exp((R - r)/H) H(r - R), gasProperties.py:155-160
-            const double R = P[1], invH = kLog2e / P[2], c2 = fma(dy, dy, z * z);
-            return use(n0, [&](int ix) {
-                const double dx = xs[ix] - cx;
-                const double r = sqrt(fma(dx, dx, c2));
-                return (r < R) ? 0.0 : pb_exp2_tab(big, (R - r) * invH);
-            });
-        }
-        case PB200_SCN_HYDROSTATIC: {  // n0 exp(J(r) H(r - R) - J(R)), gasProperties.py:197-203
-            const double R = P[1], jc = P[2] / P[3], j0 = jc / R, c2 = fma(dy, dy, z * z);
-            return use(n0, [&](int ix) {
-                const double dx = xs[ix] - cx;
-                const double r = sqrt(fma(dx, dx, c2));
-                return pb_exp2_tab(big, (((r < R) ? 0.0 : jc / r) - j0) * kLog2e);
-            });
-        }
-        case PB200_SCN_POWERLAW: {     // n0 (R/r)^q H(r - R), gasProperties.py:240-243, :326-329, :371-373, :453-460
-            // (R/r)^q = exp2(q log2 R - (q/2) log2 r^2); r < R <=> r^2 < R^2 up to a rounding of the boundary sample,
-            // which the reference's own sqrt does not define better
-            const double R = P[1], q = P[2], qlog2R = q * log2(R), hq = -0.5 * q, c2 = fma(dy, dy, z * z), R2 = R * R;
-            return use(n0, [&](int ix) {
-                const double dx = xs[ix] - cx;
-                const double r2 = fma(dx, dx, c2);
-                return (r2 < R2) ? 0.0 : pb_exp2_tab(big, fma(hq, pb_log2_tab(ltab, r2), qlog2R));
-            });
-        }
-        case PB200_SCN_TORUS: {        // n0 exp(-((a - a_t)/4H)^2) exp(-(z/H)^2), gasProperties.py:506-515
-            const double at = P[1], inv4H = 1.0 / (4.0 * P[2]), qz = z / P[2], dy2 = dy * dy;
-            const double ez = exp(-(qz * qz));
-            return use(n0 * ez, [&](int ix) {
-                const double dx = xs[ix] - cx;
-                const double qa = (sqrt(fma(dx, dx, dy2)) - at) * inv4H;
-                return pb_exp2_tab(big, -(qa * qa) * kLog2e);
-            });
-        }
-        default:
-            return 0.0;
+        case PB200_SCN_BAROMETRIC: k.a = P[1]; k.b = kLog2e / P[2]; break;                                  // gasProperties.py:155-160
+        case PB200_SCN_HYDROSTATIC: k.a = P[1]; k.b = P[2] / P[3]; k.c = k.b / P[1]; break;                   // :197-203
+        case PB200_SCN_POWERLAW: k.a = P[1] * P[1]; k.b = -0.5 * P[2]; k.c = P[2] * log2(P[1]); break;       // :240-243, :326-329, :371-373, :453-460
+        case PB200_SCN_TORUS: k.a = P[1]; k.b = 1.0 / (4.0 * P[2]); k.c = 1.0 / P[2]; break;                 // :506-515
+        default: break;
+    }
+    return k;
+}
+
+// per chord: n(x) = pre * term(dx^2, cc)
+// exp2(y) for any y <= 0: the table path, 0 below 2^-1076, libm in the denormal band (per-chord use only)
+__device__ __forceinline__ double pb_exp2_any(const double* __restrict__ big, double y) {
+    bool rare = false;
+    const bool tiny = pb_exp2_class(y, rare);
+    if (rare) return exp2(y);
+    return tiny ? 0.0 : pb_exp2_core(big, y);
+}
+
+__device__ __forceinline__ void pb_chord_pre(const ScnConst& k, const double* __restrict__ big, double y, double z, double& pre, double& cc) {
+    const double dy = y - k.cy;
+    if (k.type == PB200_SCN_TORUS) {
+        const double qz = z * k.c;
+        pre = k.n0 * pb_exp2_any(big, -(qz * qz) * pb_kc[6]);
+        cc = dy * dy;
+    } else {
+        pre = k.n0;
+        cc = fma(dy, dy, z * z);
     }
 }
 
-__device__ __forceinline__ double pb_column_sum(const DevScene& sc, const DevScenario& S, int p, double amp, double y,
-                                                double z, int* oob_flag) {
-    const int n_x = sc.n_x;
-    if (S.type == PB200_SCN_SERPENS) {
-        const double* __restrict__ xs = sc.x;
-        int oob = 0;
-        const double sum = pb_sum4(n_x, [&](int ix) { return pb_trilinear(S, xs[ix], y, z, &oob); });
-        if (oob) *oob_flag = 1;
-        return sum * amp;
+// n(x)/pre at one sample.  `rare`: see pb_exp2_class.  No branch, no call; the only selects are the final one and the
+// Jeans term of the hydrostatic law.  The heaviside of the reference (H(r - R), = 1 at r = R) shares the predicate
+// of the exp's underflow.
+template <int TYPE>
+__device__ __forceinline__ double pb_term(const ScnConst& k, const double* __restrict__ big, const double2* __restrict__ ltab,
+                                          double dx2, double cc, bool& rare) {
+    const double kLog2e = pb_kc[6];
+    const double s = dx2 + cc;                                  // r^2 (torus: a^2); > 0 on a midpoint grid
+    double yv;
+    bool dead = false;
+    if constexpr (TYPE == PB200_SCN_POWERLAW) {
+        // (R/r)^q = exp2(q log2 R - (q/2) log2 r^2); r < R <=> r^2 < R^2 up to a rounding of the boundary sample
+        dead = s < k.a;
+        yv = fma(k.b, pb_log2_tab(ltab, s), k.c);
+    } else {
+        const double ri = pb_rsqrt_nb(s), r = s * ri;
+        if constexpr (TYPE == PB200_SCN_BAROMETRIC) {
+            dead = r < k.a;
+            yv = (k.a - r) * k.b;
+        } else if constexpr (TYPE == PB200_SCN_HYDROSTATIC) {
+            const double J = (r < k.a) ? 0.0 : k.b * ri;        // non-zero inside the planet, as the reference
+            yv = (J - k.c) * kLog2e;
+        } else {                                                // torus
+            const double qa = (r - k.a) * k.b;
+            yv = -(qa * qa) * kLog2e;
+        }
     }
-    return pb_chord_terms(sc, S, p, amp, y, z, [&](double pre, auto term) {
-        return (pre == 0.0) ? 0.0 : pre * pb_sum4(n_x, term);   // terms are finite and <= 1
-    });
+    const double v = pb_exp2_core(big, yv);
+    const bool zero = pb_exp2_class(yv, rare) | dead;   // one predicate, one select
+    return zero ? 0.0 : v;
 }
 
-// Upper bound of the x-sum of one scenario on a chord (every term <= its value at dx = 0, the closest
-// approach r_min = sqrt(dy^2 + z^2)); +inf where no cheap bound exists.  Used by the run path only, to skip
-// the sum on chords that compact_kernel will classify as transparent anyway.
-__device__ __forceinline__ double pb_column_bound(const DevScene& sc, const DevScenario& S, int p, double amp, double y,
-                                                  double z) {
-    if (S.type == PB200_SCN_SERPENS) return __longlong_as_double(0x7ff0000000000000ll);
-    const double dy = y - S.centre_y[p];
-    const double* P = pb_params(S, p);
-    const double n0 = fabs(P[0] * amp) * sc.n_x;
-    const double rmin = sqrt(fma(dy, dy, z * z));
-    switch (S.type) {
-        case PB200_SCN_BAROMETRIC: return n0 * ((rmin < P[1]) ? 1.0 : exp((P[1] - rmin) / P[2]));
-        case PB200_SCN_HYDROSTATIC: {
-            const double jc = P[2] / P[3];
-            return n0 * ((rmin < P[1]) ? 1.0 : exp(jc / rmin - jc / P[1]));
-        }
+// the same value through libm (exp2 keeps the denormal band exact): for the chords flagged `rare`
+template <int TYPE>
+__device__ __forceinline__ double pb_term_exact(const ScnConst& k, const double2* __restrict__ ltab, double dx2, double cc) {
+    const double kLog2e = 1.4426950408889634;
+    const double s = dx2 + cc;
+    if (TYPE == PB200_SCN_POWERLAW) return (s < k.a) ? 0.0 : exp2(fma(k.b, pb_log2_tab(ltab, s), k.c));
+    const double ri = pb_rsqrt_nb(s), r = s * ri;
+    if (TYPE == PB200_SCN_BAROMETRIC) return (r < k.a) ? 0.0 : exp2((k.a - r) * k.b);
+    if (TYPE == PB200_SCN_HYDROSTATIC) return exp2((((r < k.a) ? 0.0 : k.b * ri) - k.c) * kLog2e);
+    const double qa = (r - k.a) * k.b;
+    return exp2(-(qa * qa) * kLog2e);
+}
+
+// x-sum of one chord over the samples ix = l8, l8 + 8, ... of one of the 8 lanes that share the chord: two samples per
+// iteration, two accumulators.  XS: (x - cx)^2 comes from shared memory (s_dx2), else it is formed from the x axis.
+// *rare_out is raised when a sample fell into the denormal band of the exp: the caller then takes pb_lane_sum_exact.
+constexpr int kColLanes = 8;
+template <int TYPE, bool XS>
+__device__ __forceinline__ double pb_lane_sum(const ScnConst& k, const double* __restrict__ big, const double2* __restrict__ ltab,
+                                              const double* __restrict__ s_dx2, const double* __restrict__ xs, int n_x, int l8,
+                                              double cc, bool& rare) {
+    double a0 = 0.0, a1 = 0.0;
+    int ix = l8;
+    for (; ix + kColLanes < n_x; ix += 2 * kColLanes) {
+        double d0, d1;
+        if constexpr (XS) { d0 = s_dx2[ix]; d1 = s_dx2[ix + kColLanes]; }
+        else { const double u = xs[ix] - k.cx, w = xs[ix + kColLanes] - k.cx; d0 = u * u; d1 = w * w; }
+        a0 += pb_term<TYPE>(k, big, ltab, d0, cc, rare);
+        a1 += pb_term<TYPE>(k, big, ltab, d1, cc, rare);
+    }
+    if (ix < n_x) {
+        double d0;
+        if constexpr (XS) d0 = s_dx2[ix]; else { const double u = xs[ix] - k.cx; d0 = u * u; }
+        a0 += pb_term<TYPE>(k, big, ltab, d0, cc, rare);
+    }
+    return a0 + a1;
+}
+
+template <int TYPE>
+static __device__ __noinline__ double pb_lane_sum_exact(const ScnConst k, const double2* __restrict__ ltab,
+                                                        const double* __restrict__ xs, int n_x, int l8, double cc) {
+    double a0 = 0.0, a1 = 0.0;   // same samples, same order of additions as pb_lane_sum
+    int ix = l8;
+    for (; ix + kColLanes < n_x; ix += 2 * kColLanes) {
+        const double u = xs[ix] - k.cx, w = xs[ix + kColLanes] - k.cx;
+        a0 += pb_term_exact<TYPE>(k, ltab, u * u, cc);
+        a1 += pb_term_exact<TYPE>(k, ltab, w * w, cc);
+    }
+    if (ix < n_x) { const double u = xs[ix] - k.cx; a0 += pb_term_exact<TYPE>(k, ltab, u * u, cc); }
+    return a0 + a1;
+}
+
+template <int TYPE, bool XS>
+__device__ __forceinline__ double pb_lane_sum_checked(const ScnConst& k, const double* __restrict__ big, const double2* __restrict__ ltab,
+                                                      const double* __restrict__ s_dx2, const double* __restrict__ xs, int n_x,
+                                                      int l8, double cc) {
+    bool rare = false;
+    const double sum = pb_lane_sum<TYPE, XS>(k, big, ltab, s_dx2, xs, n_x, l8, cc, rare);
+    // a dropped term is < 2^-1020: it changes the sum (relative 2^-53) only if the sum itself is below 2^-960
+    return (rare && sum < 1.0261342003245941e-289) ? pb_lane_sum_exact<TYPE>(k, ltab, xs, n_x, l8, cc) : sum;
+}
+
+template <bool XS>
+__device__ __forceinline__ double pb_lane_sum_any(const ScnConst& k, const double* __restrict__ big, const double2* __restrict__ ltab,
+                                                  const double* __restrict__ s_dx2, const double* __restrict__ xs, int n_x, int l8,
+                                                  double cc) {
+    switch (k.type) {   // uniform over the CTA
+        case PB200_SCN_BAROMETRIC: return pb_lane_sum_checked<PB200_SCN_BAROMETRIC, XS>(k, big, ltab, s_dx2, xs, n_x, l8, cc);
+        case PB200_SCN_HYDROSTATIC: return pb_lane_sum_checked<PB200_SCN_HYDROSTATIC, XS>(k, big, ltab, s_dx2, xs, n_x, l8, cc);
+        case PB200_SCN_POWERLAW: return pb_lane_sum_checked<PB200_SCN_POWERLAW, XS>(k, big, ltab, s_dx2, xs, n_x, l8, cc);
+        case PB200_SCN_TORUS: return pb_lane_sum_checked<PB200_SCN_TORUS, XS>(k, big, ltab, s_dx2, xs, n_x, l8, cc);
+        default: return 0.0;
+    }
+}
+
+// Upper bound of the x-sum of one scenario on a chord (every term <= its value at dx = 0, the closest approach
+// r_min^2 = dy^2 + z^2), from the per-phase constants with the table math of the sample loop (a 1e-9 margin covers its
+// rounding); +inf where no cheap bound exists.  Used by the run path only, to skip the sum on chords that
+// compact_kernel will classify as transparent anyway; the bound is what such a chord gets stored as its Ncol.
+__device__ __forceinline__ double pb_column_bound(const ScnConst& k, const double* __restrict__ big, const double2* __restrict__ ltab,
+                                                  int n_x, double y, double z) {
+    const double kInf = __longlong_as_double(0x7ff0000000000000ll);
+    const double n0 = fabs(k.n0) * (double)n_x * (1.0 + 1e-9);
+    const double dy = y - k.cy;
+    const double s = fma(dy, dy, z * z);
+    double yv;
+    switch (k.type) {
+        case PB200_SCN_BAROMETRIC: { const double r = s * pb_rsqrt_nb(s); if (r < k.a) return n0; yv = (k.a - r) * k.b; break; }
+        case PB200_SCN_HYDROSTATIC: { const double ri = pb_rsqrt_nb(s); if (s * ri < k.a) return n0; yv = (k.b * ri - k.c) * pb_kc[6]; break; }
         case PB200_SCN_POWERLAW:
             // (R/r)^q falls with r only for q > 0; for q <= 0 (the reference accepts any q) the closest approach is not
             // the maximum: no cheap bound
-            if (!(P[2] > 0.0)) return __longlong_as_double(0x7ff0000000000000ll);
-            return n0 * ((rmin < P[1]) ? 1.0 : exp(P[2] * (log(P[1]) - log(rmin))));
-        case PB200_SCN_TORUS: { const double qz = z / P[2]; return n0 * exp(-(qz * qz)); }
-        default: return __longlong_as_double(0x7ff0000000000000ll);
+            if (!(k.b < 0.0)) return kInf;
+            if (s < k.a) return n0;
+            yv = fma(k.b, pb_log2_tab(ltab, s), k.c);
+            break;
+        case PB200_SCN_TORUS: { const double qz = z * k.c; yv = -(qz * qz) * pb_kc[6]; break; }
+        default: return kInf;   // tabulated density
     }
+    if (!(yv == yv)) return kInf;
+    bool rare = false;
+    const bool tiny = pb_exp2_class(yv, rare);
+    return n0 * (tiny ? 1.1125369292536007e-307 : pb_exp2_core(big, yv));   // 2^-1020 bounds everything below
 }
 
-// run_mode = 0: every unblocked chord gets its exact column densities (inner seams of the API).
-// run_mode = 2 (pb200_run with PB200_NO_CULL=1): exact sums for every unblocked chord, absorbers as in run_mode 1.
+// One CTA = 256 consecutive chords of ONE phase (rows are padded to 256 chords).
+//   Phase A, one thread per chord: y, z, blocking mask and weight (bit-exact operation order), then -- run path -- the
+//     decisions which sums compact_kernel will not need (see run_mode below); the chords that need an exact sum are
+//     compacted into a work list, so that no lane idles in phase B for a blocked, mirrored or culled neighbour.
+//   Phase B, per scenario: (x - cx(p))^2 of the phase goes to shared memory once; 8 lanes share a listed chord and
+//     stride x (pb_lane_sum), their partial sums are added in a fixed order (xor tree) -- deterministic.
+//   Then one thread per chord again writes Ncol (coalesced) and feeds the running maxima (one atomicMax per warp).
+// run_mode = 0: every unblocked chord gets its exact column densities, one per atomic constituent (inner seams).
+// run_mode = 2 (pb200_run with PB200_OPT_CULL = 0): exact sums for every unblocked chord, absorbers as in run_mode 1.
 // run_mode = 1 (pb200_run): the sums that compact_kernel does not need are skipped --
 //   * the mirror chord of a pair whose primary chord is not blocked (sc.mirror);
 //   * chords whose upper bound sum_a bound_a * max_w sigma_a(p, w) is already below 2^-54: they are
 //     transparent whatever the exact sum is, and get the bound stored as Ncol (so that compact_kernel's own
 //     test classifies them the same way).
-__global__ void __launch_bounds__(128, 6)
-column_thread_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, int* __restrict__ oob_flag,
-                     int run_mode) {
+constexpr int kColCta = 256;
+constexpr int kColMaxXs = 2048;   // x samples whose (x - cx)^2 are kept in shared memory (16 KB); beyond: formed per sample
+__global__ void __launch_bounds__(kColCta, 4)
+column_cta_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, int* __restrict__ oob_flag, int run_mode) {
     const DevScene& sc = *scp;
-    const int64_t cid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (cid >= (int64_t)n_phase * sc.Mp) return;
-    const int p = phase_lo + (int)(cid / sc.Mp);
-    const int m = (int)(cid % sc.Mp);
+    __shared__ double s_y[kColCta], s_z[kColCta], s_val[kColCta], s_pre[kColCta], s_cc[kColCta], s_dx2[kColMaxXs];
+    __shared__ unsigned char s_list[kColCta];
+    __shared__ int s_cnt[kColCta / 32];
+    __shared__ ScnConst s_k[kMaxScenarios];
+    __shared__ double s_sigmax[PB200_MAX_ABSORBERS];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int64_t cid0 = (int64_t)blockIdx.x * kColCta;
+    const int p = phase_lo + (int)(cid0 / sc.Mp);
+    const int m = (int)(cid0 % sc.Mp) + tid;
     const int64_t row = (int64_t)p * sc.Mp + m;
+    const int n_x = sc.n_x;
+    const double* __restrict__ xs = sc.x;
+    const double* __restrict__ big = sc.exp_tab + kExpTabEntries;
+    const double2* __restrict__ ltab = reinterpret_cast<const double2*>(sc.exp_tab + kExpTabEntries + kExpBigEntries);
+
+    // ---- phase A -------------------------------------------------------------------------------------
     bool blocked = true, need_sum = false;
     double y = 0.0, z = 0.0, wv = 0.0;
     if (m < sc.M) {
@@ -257,7 +358,7 @@ column_thread_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase
         z = __dmul_rn(rho, sc.cos_phi[iphi]);
         blocked = pb_blocked(sc, p, y, z);
         wv = blocked ? 0.0 : sc.w_out[m];
-        need_sum = !blocked;
+        need_sum = !blocked;      // the reference evaluates only unblocked chords (gasProperties.py:1235-1240)
         if (run_mode == 1 && sc.mirror && need_sum) {
             const int n2 = sc.n_phi / 2, h = iphi / n2, i = iphi - h * n2, ip = n2 - 1 - i;
             if (i > ip) {   // mirror chord of the pair: needed only if the primary chord is blocked
@@ -267,59 +368,118 @@ column_thread_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase
         }
     }
     sc.w_in[row] = wv;
-    bool skip = false;
-    if (run_mode) {
-        // The run path works with one absorber per group of atomic constituents that share a scenario
-        // (DevScene::n_abs): Ncol_g = sum_x n dx, the mixing ratios are in the group's cross section.
-        if (need_sum && run_mode == 1) {   // transparent whatever the exact sums are?
-            double bound = 0.0;
-            for (int g = 0; g < sc.n_abs; ++g) {
-                const DevScenario& S = sc.scen[sc.cons[sc.abs_first[g]].scenario];
-                const double ub = pb_column_bound(sc, S, p, S.amplitude ? S.amplitude[p] : 1.0, y, z);
-                const double sm = __longlong_as_double((long long)sc.smax[(int64_t)g * sc.n_orb + p]);
-                bound += ub * sc.delta_x * ((sm >= 0.0) ? sm : __longlong_as_double(0x7ff0000000000000ll));
-            }
-            skip = bound < 5.5511151231257827e-17;   // 2^-54; NaN (0 * inf) -> not skipped
+    if (tid < sc.n_scen) s_k[tid] = pb_scn_const(sc.scen[tid], p);   // log2(R), 1/H, ...: once per CTA, not once per thread
+    if (run_mode == 1 && tid >= 32 && tid < 32 + sc.n_abs) {
+        // upper bound of the absorber's cross section at ANY wavelength: sum_k chi_k (10^max(tab_y_k) - offset_k) (the
+        // table lookup is a convex combination of table values).  Independent of sigma_phase_kernel, which therefore
+        // runs beside this kernel; compact_kernel's own test uses the run's exact maxima, which are not larger.
+        const int g = tid - 32;
+        double sm = 0.0;
+        for (int c = sc.abs_first[g]; c < sc.abs_first[g] + sc.abs_count[g]; ++c) {
+            const unsigned long long b = sc.tab_ymax[c];
+            const double ymax = (b == 0ull || b == ~0ull) ? __longlong_as_double(0x7ff0000000000000ll) : pb_from_ordered_bits(b);
+            sm += sc.cons[c].chi * (exp10(ymax) - sc.cons[c].offset);
         }
-        int prev_scen = -1;
-        double sum = 0.0;
-        for (int g = 0; g < sc.n_abs; ++g) {
-            const int s = sc.cons[sc.abs_first[g]].scenario;
-            const DevScenario& S = sc.scen[s];
-            if (s != prev_scen) {   // (PB200_NO_GROUP: several absorbers of one scenario share the sum)
-                const double amp = S.amplitude ? S.amplitude[p] : 1.0;
-                sum = 0.0;
-                if (need_sum) sum = skip ? pb_column_bound(sc, S, p, amp, y, z) : pb_column_sum(sc, S, p, amp, y, z, oob_flag);
-                prev_scen = s;
-            }
-            const double col = sum * sc.delta_x;
-            sc.ncol[(int64_t)g * sc.n_orb * sc.Mp + row] = col;
-            double mx = (col > 0.0) ? col : 0.0;
-#pragma unroll
-            for (int d = 16; d > 0; d >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, d));
-            if ((threadIdx.x & 31) == 0 && mx > 0.0)
-                atomicMax(sc.nmax + (int64_t)g * sc.n_orb + p, (unsigned long long)__double_as_longlong(mx));
-        }
-        return;
+        s_sigmax[g] = (sm >= 0.0) ? sm * (1.0 + 1e-12) : __longlong_as_double(0x7ff0000000000000ll);   // negative or NaN: never cull
     }
+    __syncthreads();
+    bool skip = false;
+    if (need_sum && run_mode == 1) {   // transparent whatever the exact sums are?
+        double bound = 0.0;
+        for (int g = 0; g < sc.n_abs; ++g) {
+            const double ub = pb_column_bound(s_k[sc.cons[sc.abs_first[g]].scenario], big, ltab, n_x, y, z);
+            bound += ub * sc.delta_x * s_sigmax[g];
+        }
+        skip = bound < 5.5511151231257827e-17;   // 2^-54; NaN (0 * inf) -> not skipped
+    }
+    s_y[tid] = y;
+    s_z[tid] = z;
+    const bool listed = need_sum && !skip;
+    const unsigned bal = __ballot_sync(0xffffffffu, listed);
+    if (lane == 0) s_cnt[wid] = __popc(bal);
+    __syncthreads();
+    int base = 0, n_list = 0;
+#pragma unroll
+    for (int w = 0; w < kColCta / 32; ++w) { base += (w < wid) ? s_cnt[w] : 0; n_list += s_cnt[w]; }
+    if (listed) s_list[base + __popc(bal & ((1u << lane) - 1u))] = (unsigned char)tid;
+
+    // ---- per scenario: phase B + the writes ---------------------------------------------------------------
+    const int grp = tid / kColLanes, l8 = tid % kColLanes;
     for (int s = 0; s < sc.n_scen; ++s) {
         const DevScenario& S = sc.scen[s];
+        int g_lo = 0, g_hi = -1;     // run path: the absorbers that share this scenario's sum (consecutive)
+        if (run_mode) {
+            g_lo = sc.n_abs;
+            for (int g = 0; g < sc.n_abs; ++g)
+                if (sc.cons[sc.abs_first[g]].scenario == s) { g_lo = g < g_lo ? g : g_lo; g_hi = g; }
+            if (g_hi < 0) continue;   // uniform
+        }
+        const bool serp = S.type == PB200_SCN_SERPENS;
         const double amp = S.amplitude ? S.amplitude[p] : 1.0;
-        // the reference evaluates only unblocked chords (gasProperties.py:1235-1240)
-        double sum = 0.0;
-        if (need_sum) sum = skip ? pb_column_bound(sc, S, p, amp, y, z) : pb_column_sum(sc, S, p, amp, y, z, oob_flag);
-        for (int k = S.first_cons; k < S.first_cons + S.n_cons; ++k) {
-            const DevConstituent& C = sc.cons[k];
-            if (C.kind != 0) continue;
-            const double col = (sum * C.chi) * sc.delta_x;                      // gasProperties.py:940
-            sc.ncol[(int64_t)C.atom_index * sc.n_orb * sc.Mp + row] = col;
-            // max over the warp first (a CTA never straddles two phases: Mp is a multiple of 256): one atomic
-            // per warp instead of 32 on the same address
-            double mx = (col > 0.0) ? col : 0.0;
+        const bool xs_smem = !serp && n_x <= kColMaxXs;
+        __syncthreads();   // work list complete; the previous scenario's s_val / s_dx2 are no longer read
+        const ScnConst k = s_k[s];
+        if (xs_smem)
+            for (int ix = tid; ix < n_x; ix += kColCta) { const double dx = xs[ix] - k.cx; s_dx2[ix] = dx * dx; }
+        s_val[tid] = (need_sum && skip) ? pb_column_bound(k, big, ltab, n_x, y, z) : 0.0;
+        if (listed && !serp) {
+            double pre, cc;
+            pb_chord_pre(k, big, y, z, pre, cc);
+            // the sample loop decides underflow on bit patterns: a NaN (NaN scene parameters) would read as "tiny".
+            // It is caught here, once per chord: pre = NaN makes the sum NaN, as the reference's arithmetic would
+            if (!(cc == cc) || !((k.a + k.b) + (k.c + k.cx) == (k.a + k.b) + (k.c + k.cx))) pre = __longlong_as_double(0x7ff8000000000000ll);
+            s_pre[tid] = pre;
+            s_cc[tid] = cc;
+        }
+        __syncthreads();
+        for (int i0 = 0; i0 < n_list; i0 += kColCta / kColLanes) {   // every lane of a warp makes the same number of rounds
+            const int i = i0 + grp;
+            const bool act = i < n_list;
+            const int t = act ? s_list[i] : 0;
+            double sum = 0.0;
+            if (act) {
+                if (serp) {
+                    int oob = 0;
+                    for (int ix = l8; ix < n_x; ix += kColLanes) sum += pb_trilinear(S, xs[ix], s_y[t], s_z[t], &oob);
+                    if (oob) *oob_flag = 1;
+                    sum *= amp;
+                } else {
+                    const double pre = s_pre[t];   // every term is finite and <= 1: pre == 0 gives an exact 0 (torus far off the plane)
+                    if (pre != 0.0)
+                        sum = pre * (xs_smem ? pb_lane_sum_any<true>(k, big, ltab, s_dx2, xs, n_x, l8, s_cc[t])
+                                             : pb_lane_sum_any<false>(k, big, ltab, s_dx2, xs, n_x, l8, s_cc[t]));
+                }
+            }
+            sum += __shfl_xor_sync(0xffffffffu, sum, 4);
+            sum += __shfl_xor_sync(0xffffffffu, sum, 2);
+            sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+            if (act && l8 == 0) s_val[t] = sum;
+        }
+        __syncthreads();
+        const double val = s_val[tid];
+        if (run_mode) {
+            // one absorber per group of atomic constituents that share a scenario (DevScene::n_abs):
+            // Ncol_g = sum_x n dx, the mixing ratios are in the group's cross section
+            for (int g = g_lo; g <= g_hi; ++g) {
+                if (sc.cons[sc.abs_first[g]].scenario != s) continue;
+                const double col = val * sc.delta_x;
+                sc.ncol[(int64_t)g * sc.n_orb * sc.Mp + row] = col;
+                double mx = (col > 0.0) ? col : 0.0;   // densities are >= 0: the bit patterns order like the values
 #pragma unroll
-            for (int d = 16; d > 0; d >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, d));
-            if ((threadIdx.x & 31) == 0 && mx > 0.0)
-                atomicMax(sc.nmax + (int64_t)C.atom_index * sc.n_orb + p, (unsigned long long)__double_as_longlong(mx));
+                for (int d = 16; d > 0; d >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, d));
+                if (lane == 0 && mx > 0.0) atomicMax(sc.nmax + (int64_t)g * sc.n_orb + p, (unsigned long long)__double_as_longlong(mx));
+            }
+        } else {
+            for (int c = S.first_cons; c < S.first_cons + S.n_cons; ++c) {
+                const DevConstituent& C = sc.cons[c];
+                if (C.kind != 0) continue;
+                const double col = (val * C.chi) * sc.delta_x;                      // gasProperties.py:940
+                sc.ncol[(int64_t)C.atom_index * sc.n_orb * sc.Mp + row] = col;
+                double mx = (col > 0.0) ? col : 0.0;
+#pragma unroll
+                for (int d = 16; d > 0; d >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, d));
+                if (lane == 0 && mx > 0.0) atomicMax(sc.nmax + (int64_t)C.atom_index * sc.n_orb + p, (unsigned long long)__double_as_longlong(mx));
+            }
         }
     }
 }
@@ -334,7 +494,9 @@ column_thread_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase
 //                 folded into the weight, pb200_math.cuh "Big-table form": w exp(r c1) ~= w + r (w c1 + r w c2)).
 // Active records are packed in chord order at the front of the phase's rec row (block-wide exclusive
 // scan, deterministic), the last tile is padded with all-zero records, n_act[p] = number of tiles.
-constexpr int kCompactThreads = 1024;
+// CTA size: 1024 threads for large sky grids; 256 for small ones (a dense phase sweep like C3 has 401 phases of 1 200
+// chord pairs: four small CTAs per SM run concurrently where one large one spent its time in barriers).
+template <int kCompactThreads>
 __global__ void __launch_bounds__(kCompactThreads) compact_kernel(const DevScene* __restrict__ scp, const TransitParams prm, int cull,
                                                                   int n_pow2) {
     const DevScene& sc = *scp;
@@ -393,7 +555,7 @@ __global__ void __launch_bounds__(kCompactThreads) compact_kernel(const DevScene
         if (lane == 0) s_warp[wid] = __popc(bal);
         __syncthreads();
         if (wid == 0) {   // exclusive scan of the 32 warp counts
-            const int c = s_warp[lane];
+            const int c = (lane < kCompactThreads / 32) ? s_warp[lane] : 0;
             int x = c;
 #pragma unroll
             for (int d = 1; d < 32; d <<= 1) {
@@ -439,7 +601,7 @@ __global__ void __launch_bounds__(kCompactThreads) compact_kernel(const DevScene
     }
     __syncthreads();
     if (wid < 7) {
-        const double t = pb_warp_sum(s_red[wid][lane]);
+        const double t = pb_warp_sum((lane < kCompactThreads / 32) ? s_red[wid][lane] : 0.0);
         if (lane == 0) {
             if (wid == 0) sc.w0[p] = t; else sc.thin_tot[(int64_t)p * 8 + wid - 1] = t;
         }
@@ -528,52 +690,86 @@ number_density_grid_kernel(const DevScene* __restrict__ scp, int scenario, doubl
     }
 }
 
-// (a) fast form for the analytic scenarios: one THREAD per chord (per-chord factors hoisted once, all lanes busy
-// whatever n_x is), 16 samples at a time staged through shared memory so that the warp writes whole 128-byte
-// segments: a store instruction covers two rows x 16 doubles.  HBM-bound by construction (8 B per sample).
-constexpr int kDensChunk = 16;
-__global__ void __launch_bounds__(128)
-number_density_thread_kernel(const DevScene* __restrict__ scp, int scenario, double* __restrict__ out) {
+// (a) fast form for the analytic scenarios, materialised n(chord, x) in the reference's chord order c = m*n_orb + p.
+// A tile is 256 consecutive chords: one thread per chord hoists its constants (ScnConst of its phase, pre, cc) into
+// shared memory, then 8 lanes share a chord row and stride x two samples at a time -- each lane stores 16 bytes, the 8
+// lanes of a chord one 128-byte line, a warp four of them: no staging through shared memory, no partial sectors.
+// CTAs are persistent over the tiles.  8 B of HBM traffic per sample against ~23-27 FP64
+// instructions: which of the two binds depends on the scenario, see DESIGN.md.
+constexpr int kRowsCta = 256;
+template <int TYPE>
+__device__ __forceinline__ void pb_lane_rows(const ScnConst& k, const double* __restrict__ big, const double2* __restrict__ ltab,
+                                             const double* __restrict__ xs, int n_x, int l8, double pre, double cc,
+                                             double* __restrict__ row, bool vec) {
+    // the values themselves are the output here, so a sample in the denormal band of the exp is redone through exp2()
+    // on the spot (a rarely taken branch after the pair, not a call inside the arithmetic)
+    bool rare = false;
+    if (vec) {
+        for (int ix = 2 * l8; ix < n_x; ix += 2 * kColLanes) {     // n_x is even here
+            const double u = xs[ix] - k.cx, w = xs[ix + 1] - k.cx;
+            const double d0 = u * u, d1 = w * w;
+            double t0 = pb_term<TYPE>(k, big, ltab, d0, cc, rare);
+            double t1 = pb_term<TYPE>(k, big, ltab, d1, cc, rare);
+            if (rare) { t0 = pb_term_exact<TYPE>(k, ltab, d0, cc); t1 = pb_term_exact<TYPE>(k, ltab, d1, cc); rare = false; }
+            *reinterpret_cast<double2*>(row + ix) = make_double2(pre * t0, pre * t1);
+        }
+    } else {
+        for (int ix = l8; ix < n_x; ix += kColLanes) {
+            const double u = xs[ix] - k.cx, d0 = u * u;
+            double t0 = pb_term<TYPE>(k, big, ltab, d0, cc, rare);
+            if (rare) { t0 = pb_term_exact<TYPE>(k, ltab, d0, cc); rare = false; }
+            row[ix] = pre * t0;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kRowsCta, 3)
+number_density_rows_kernel(const DevScene* __restrict__ scp, int scenario, double* __restrict__ out, int64_t n_tiles) {
     const DevScene& sc = *scp;
     const DevScenario& S = sc.scen[scenario];
-    __shared__ double tile[4][32][kDensChunk + 1];
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    __shared__ ScnConst s_k[kRowsCta];
+    __shared__ double s_pre[kRowsCta], s_cc[kRowsCta];
+    const int tid = threadIdx.x, grp = tid / kColLanes, l8 = tid % kColLanes;
     const int64_t n_chords = (int64_t)sc.M * sc.n_orb;
-    const int64_t c0 = ((int64_t)blockIdx.x * 4 + wid) * 32;
-    if (c0 >= n_chords) return;
-    const int64_t c = c0 + lane;
-    const bool have = c < n_chords;
-    const int64_t cc = have ? c : n_chords - 1;
-    const int m = (int)(cc / sc.n_orb), p = (int)(cc % sc.n_orb);
-    const int iphi = m / sc.n_rho, irho = m - iphi * sc.n_rho;
-    const double rho = sc.rho[irho];
-    const double y = __dmul_rn(rho, sc.sin_phi[iphi]);
-    const double z = __dmul_rn(rho, sc.cos_phi[iphi]);
-    const double amp = S.amplitude ? S.amplitude[p] : 1.0;
     const int n_x = sc.n_x;
-    double (*my)[kDensChunk + 1] = tile[wid];
-    const int rows = (int)((n_chords - c0 < 32) ? n_chords - c0 : 32);
-    // blockIdx.y splits the x axis in whole chunks: enough tasks that the last wave is short
-    const int n_chunks = (n_x + kDensChunk - 1) / kDensChunk;
-    const int x_lo = (int)((int64_t)blockIdx.y * n_chunks / gridDim.y) * kDensChunk;
-    int x_hi = (int)((int64_t)(blockIdx.y + 1) * n_chunks / gridDim.y) * kDensChunk;
-    if (x_hi > n_x) x_hi = n_x;
-    pb_chord_terms(sc, S, p, amp, y, z, [&](double pre, auto term) {
-        const bool dead = (pre == 0.0);   // every term is finite and <= 1: the whole row is exactly 0 (torus far off the plane)
-        for (int x0 = x_lo; x0 < x_hi; x0 += kDensChunk) {
-            const int nk = (x_hi - x0 < kDensChunk) ? x_hi - x0 : kDensChunk;
-#pragma unroll 4
-            for (int k = 0; k < nk; ++k) my[lane][k] = dead ? 0.0 : pre * term(x0 + k);
-            __syncwarp();
-            const int col = lane & 15, half = lane >> 4;
-            if (col < nk) {
-#pragma unroll 4
-                for (int r = half; r < rows; r += 2) out[(c0 + r) * n_x + x0 + col] = my[r][col];
-            }
-            __syncwarp();
+    const double* __restrict__ xs = sc.x;
+    const double* __restrict__ big = sc.exp_tab + kExpTabEntries;
+    const double2* __restrict__ ltab = reinterpret_cast<const double2*>(sc.exp_tab + kExpTabEntries + kExpBigEntries);
+    const bool vec = (n_x % 2 == 0) && ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const int64_t c0 = tile * kRowsCta, c = c0 + tid;
+        __syncthreads();   // the previous tile's constants are no longer read
+        if (c < n_chords) {
+            const int m = (int)(c / sc.n_orb), p = (int)(c % sc.n_orb);
+            const int iphi = m / sc.n_rho, irho = m - iphi * sc.n_rho;
+            const double rho = sc.rho[irho];
+            const ScnConst k = pb_scn_const(S, p);
+            double pre, cc;
+            pb_chord_pre(k, big, __dmul_rn(rho, sc.sin_phi[iphi]), __dmul_rn(rho, sc.cos_phi[iphi]), pre, cc);
+            s_k[tid] = k;
+            s_pre[tid] = pre;
+            s_cc[tid] = cc;
         }
-        return 0.0;
-    });
+        __syncthreads();
+        const int rows = (int)((n_chords - c0 < kRowsCta) ? n_chords - c0 : kRowsCta);
+        for (int i = grp; i < rows; i += kRowsCta / kColLanes) {
+            const ScnConst k = s_k[i];
+            const double pre = s_pre[i], cc = s_cc[i];
+            double* __restrict__ row = out + (c0 + i) * n_x;
+            if (pre == 0.0) {   // every term is finite and <= 1: the whole row is exactly 0 (torus far off the plane)
+                if (vec) for (int ix = 2 * l8; ix < n_x; ix += 2 * kColLanes) *reinterpret_cast<double2*>(row + ix) = make_double2(0.0, 0.0);
+                else for (int ix = l8; ix < n_x; ix += kColLanes) row[ix] = 0.0;
+                continue;
+            }
+            switch (k.type) {
+                case PB200_SCN_BAROMETRIC: pb_lane_rows<PB200_SCN_BAROMETRIC>(k, big, ltab, xs, n_x, l8, pre, cc, row, vec); break;
+                case PB200_SCN_HYDROSTATIC: pb_lane_rows<PB200_SCN_HYDROSTATIC>(k, big, ltab, xs, n_x, l8, pre, cc, row, vec); break;
+                case PB200_SCN_POWERLAW: pb_lane_rows<PB200_SCN_POWERLAW>(k, big, ltab, xs, n_x, l8, pre, cc, row, vec); break;
+                case PB200_SCN_TORUS: pb_lane_rows<PB200_SCN_TORUS>(k, big, ltab, xs, n_x, l8, pre, cc, row, vec); break;
+                default: break;
+            }
+        }
+    }
 }
 
 // same for caller-supplied chords (API parity with <Scenario>.calculateNumberDensity(x, phi, rho, orb))
@@ -636,21 +832,23 @@ void launch_column(const DevScene* d_scene, int Mp, int phase_lo, int n_phase, i
     if (has_molecules) {   // density rows n(c, x) are needed by kernel (m): warp per chord, coalesced row stores
         column_kernel<<<grid_for_warps((int64_t)n_phase * Mp, sm_count), 256, 0, st>>>(d_scene, phase_lo, n_phase, oob);
     } else {
-        const int64_t n = (int64_t)n_phase * Mp;
-        column_thread_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(d_scene, phase_lo, n_phase, oob, run_mode);
+        const int64_t n = (int64_t)n_phase * Mp;   // Mp is a multiple of kColCta: a CTA never straddles two phases
+        column_cta_kernel<<<(unsigned)(n / kColCta), kColCta, 0, st>>>(d_scene, phase_lo, n_phase, oob, run_mode);
     }
 }
 constexpr int kMaxWindows = 8192;
-cudaError_t launch_compact(const DevScene* d_scene, const TransitParams& prm, bool cull, cudaStream_t st) {
+cudaError_t launch_compact(const DevScene* d_scene, const TransitParams& prm, bool cull, bool small, cudaStream_t st) {
     int n_pow2 = 1;
     while (n_pow2 < prm.n_win) n_pow2 <<= 1;
     if (n_pow2 > kMaxWindows) n_pow2 = 0;
     const size_t smem = (size_t)n_pow2 * (sizeof(double) + sizeof(int));
     if (smem > 40 * 1024) {
-        cudaError_t e = cudaFuncSetAttribute(compact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(compact_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(compact_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
     }
-    compact_kernel<<<prm.n_phase, kCompactThreads, smem, st>>>(d_scene, prm, cull ? 1 : 0, n_pow2);
+    if (small) compact_kernel<256><<<prm.n_phase, 256, smem, st>>>(d_scene, prm, cull ? 1 : 0, n_pow2);
+    else compact_kernel<1024><<<prm.n_phase, 1024, smem, st>>>(d_scene, prm, cull ? 1 : 0, n_pow2);
     return cudaGetLastError();
 }
 void launch_number_density_grid(const DevScene* d_scene, int64_t n_chords, int scenario, double* out,
@@ -659,12 +857,13 @@ void launch_number_density_grid(const DevScene* d_scene, int64_t n_chords, int s
 }
 void launch_number_density_thread(const DevScene* d_scene, int64_t n_chords, int n_x, int scenario, double* out, int sm_count,
                                   cudaStream_t st) {
-    const int64_t blocks = (n_chords + 127) / 128;
-    const int n_chunks = (n_x + kDensChunk - 1) / kDensChunk;
-    int64_t xs = ((int64_t)sm_count * 9 * 8 + blocks - 1) / blocks;   // ~8 tasks per resident block slot
-    if (xs > n_chunks) xs = n_chunks;
-    if (xs < 1) xs = 1;
-    number_density_thread_kernel<<<dim3((unsigned)blocks, (unsigned)xs), 128, 0, st>>>(d_scene, scenario, out);
+    (void)n_x;
+    const int64_t n_tiles = (n_chords + kRowsCta - 1) / kRowsCta;
+    // persistent CTAs with equal shares: ceil(tiles / slots) tiles each
+    const int64_t slots = (int64_t)sm_count * 3;
+    const int64_t per = (n_tiles + slots - 1) / slots;
+    const int64_t ctas = (n_tiles + per - 1) / (per > 0 ? per : 1);
+    number_density_rows_kernel<<<(unsigned)(ctas > 0 ? ctas : 1), kRowsCta, 0, st>>>(d_scene, scenario, out, n_tiles);
 }
 void launch_number_density_chords(const DevScene* d_scene, int scenario, int64_t n, const double* y,
                                   const double* z, const double* cx, const double* cy, const double* amp,

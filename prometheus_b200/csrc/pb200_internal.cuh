@@ -87,7 +87,21 @@ struct DevScene {
     double* thin_tot;           // [n_orb][8] sums over the ACTIVE chords of {w, N0 w c1, N1 w c1, N0^2 w c2, N0 N1 w c2,
                                 //   N1^2 w c2}: what kernel (c') needs for a window in which every chord is thin (S <= 2)
     unsigned long long* stat;   // [2]: [0] low word = tabulated-density out-of-grid flag, [1] active records of the run
+    // [n_cons] order-preserving bit pattern of max(tab_y) of every atomic table (bucket_build_kernel, once per scene; 0:
+    // not known): the column kernel bounds sigma with it and so does not wait for sigma_phase_kernel
+    unsigned long long* tab_ymax;
 };
+
+// order-preserving map double -> uint64 (larger double, larger integer; 0 is below every double) and back
+__host__ __device__ inline unsigned long long pb_ordered_bits(double v) {
+    union { double d; unsigned long long u; } x; x.d = v;
+    return (x.u >> 63) ? ~x.u : (x.u | 0x8000000000000000ull);
+}
+__host__ __device__ inline double pb_from_ordered_bits(unsigned long long b) {
+    union { double d; unsigned long long u; } x;
+    x.u = (b >> 63) ? (b & 0x7fffffffffffffffull) : ~b;
+    return x.d;
+}
 
 // doubles per chord record of kernel (c'): {w, w c1, w c2, Ncol_0..Ncol_{S-1}} padded to an even count, so that a
 // record is a whole number of 16-byte shared-memory loads

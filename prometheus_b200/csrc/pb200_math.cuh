@@ -183,19 +183,34 @@ __device__ __forceinline__ double pb_exp_big_load(uint32_t tab_base, int k) {
 constexpr int kLogTabEntries = 256;
 constexpr double kExpBigC3 = 8.0768402961349e-13;            // (ln 2 / 4096)^3 / 6
 
+// Coefficients whose low word is not zero cannot be FP64 immediates; as literals the compiler re-materialises each
+// with two moves INSIDE the x loops (23 of 120 instructions of the power-law loop).  From __constant__ memory they are
+// constant-bank operands of the DFMAs themselves.
+static __constant__ double pb_kc[12] = {
+    2.0609929155555190e-01,    // [0]  1/(7 ln2)
+    -2.4044917348149410e-01,   // [1] -1/(6 ln2)
+    2.8853900817779268e-01,    // [2]  1/(5 ln2)
+    -3.6067376022224085e-01,   // [3] -1/(4 ln2)
+    4.8089834696298783e-01,    // [4]  1/(3 ln2)
+    -7.2134752044448170e-01,   // [5] -1/(2 ln2)
+    1.4426950408889634e+00,    // [6]  1/ln2 = log2(e)
+    8.0768402961349e-13,       // [7]  kExpBigC3
+    1.43186156129301e-08,      // [8]  kExpBigC2
+    1.6922538587889289e-04,    // [9]  kExpBigC1
+    0.0, 0.0};
+
 __device__ __forceinline__ double pb_log2_tab(const double2* __restrict__ ltab, double x) {
     const int hi = __double2hiint(x);
     const int e = (hi >> 20) - 1023;
     const double2 t = __ldg(ltab + ((hi >> 12) & 255));
     const double m = __hiloint2double((hi & 0x000FFFFF) | 0x3FF00000, __double2loint(x));
     const double u = fma(m, t.x, -1.0);
-    double p = 2.0609929155555190e-01;                       //  1/(7 ln2)
-    p = fma(p, u, -2.4044917348149410e-01);                  // -1/(6 ln2)
-    p = fma(p, u, 2.8853900817779268e-01);                   //  1/(5 ln2)
-    p = fma(p, u, -3.6067376022224085e-01);                  // -1/(4 ln2)
-    p = fma(p, u, 4.8089834696298783e-01);                   //  1/(3 ln2)
-    p = fma(p, u, -7.2134752044448170e-01);                  // -1/(2 ln2)
-    p = fma(p, u, 1.4426950408889634e+00);                   //  1/ln2
+    double p = fma(pb_kc[0], u, pb_kc[1]);
+    p = fma(p, u, pb_kc[2]);
+    p = fma(p, u, pb_kc[3]);
+    p = fma(p, u, pb_kc[4]);
+    p = fma(p, u, pb_kc[5]);
+    p = fma(p, u, pb_kc[6]);
     return fma(u, p, (double)e + t.y);
 }
 
@@ -210,6 +225,42 @@ __device__ __forceinline__ double pb_exp2_tab(const double* __restrict__ big, do
     double p = fma(r, kExpBigC3, kExpBigC2);
     p = fma(p, r, kExpBigC1);
     return fma(T, r * p, T);
+}
+
+// Branch-free forms for the x-sums of kernels (a) / (a'): a loop body without branches, calls or select chains lets
+// the compiler interleave the independent sample chains and keeps the instructions issued next to the FP64 pipe few.
+//   pb_rsqrt_nb(s):   1/sqrt(s) for normal s > 0 from the MUFU seed (rel. error < 2^-20) and ONE third-order step
+//                     y (1 + e/2 + 3 e^2/8), e = 1 - s y^2: error (5/16) e^3 < 2^-62 before rounding, <= 1.5 ulp after.
+//   pb_exp2_core(y):  the table path of pb_exp2_tab without its range checks: exact for y >= -1020.0005; below, the
+//                     result is garbage (the table index stays in range) and must be discarded by the caller.
+//   pb_exp2_class(y): the range checks as INTEGER compares on the high word (for negative y the unsigned high word
+//                     grows with |y|): `tiny` -- y < -1020: the caller returns 0; `rare` is raised when y lies in the band
+//                     [-1076, -1020) whose true results are denormal: the caller redoes that chord with exp2().
+constexpr unsigned kHiM1020 = 0xC08FE000u;   // high word of -1020.0
+constexpr unsigned kHiM1076 = 0xC090D000u;   // high word of -1076.0
+__device__ __forceinline__ double pb_rsqrt_nb(double s) {
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(s));
+    const double e = fma(-(s * y), y, 1.0);
+    return fma(y * e, fma(e, 0.375, 0.5), y);
+}
+
+__device__ __forceinline__ double pb_exp2_core(const double* __restrict__ big, double y) {
+    const double t = fma(y, 4096.0, kExpMagic);
+    const int k = __double2loint(t);
+    const double kf = t - kExpMagic;
+    const double r = fma(y, 4096.0, -kf);
+    const double T0 = __ldg(big + (k & (kExpBigEntries - 1)));
+    const double T = __hiloint2double(__double2hiint(T0) + (k << kExpBigShift), __double2loint(T0));
+    double p = fma(r, pb_kc[7], pb_kc[8]);
+    p = fma(p, r, pb_kc[9]);
+    return fma(T, r * p, T);
+}
+
+__device__ __forceinline__ bool pb_exp2_class(double y, bool& rare) {
+    const unsigned hy = (unsigned)__double2hiint(y);
+    rare |= (hy - (kHiM1020 + 1u)) <= (kHiM1076 - kHiM1020);   // one subtract + one compare for the band
+    return hy > kHiM1020;
 }
 
 // exp(a) for |a| <= 700 (same kernel as pb_exp_neg, two-sided); used for 10**v = exp(v ln10) of the

@@ -545,6 +545,19 @@ static cudaError_t launch_one(const DevScene* d_scene, const TransitParams& prm,
 __global__ void __launch_bounds__(256) bucket_build_kernel(const DevScene* __restrict__ scp) {
     const DevScene& sc = *scp;
     const int lane = threadIdx.x & 31;
+    for (int k = 0; k < sc.n_cons; ++k) {   // largest log10(sigma + offset) of every atomic table (DevScene::tab_ymax)
+        const DevConstituent& C = sc.cons[k];
+        if (C.kind != 0) continue;
+        unsigned long long mx = 0ull;
+        for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < C.n_tab; i += (int64_t)gridDim.x * blockDim.x) {
+            const double y = __ldg(C.tab_y + i);
+            const unsigned long long b = (y == y) ? pb_ordered_bits(y) : ~0ull;   // NaN in a table: no bound
+            mx = b > mx ? b : mx;
+        }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) { const unsigned long long o = __shfl_xor_sync(0xffffffffu, mx, d); mx = o > mx ? o : mx; }
+        if (lane == 0 && mx) atomicMax(sc.tab_ymax + k, mx);
+    }
     for (int k = 0; k < sc.n_cons; ++k) {
         const DevConstituent& C = sc.cons[k];
         if (C.kind != 0 || !C.bucket) continue;
