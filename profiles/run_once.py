@@ -24,8 +24,21 @@ def main(argv):
     rows = np.load(os.path.join(ROOT, "tests", "golden", "linelist.npz"))["rows"]
     ctx = host.get_context(0)
     for k, v in opts.items():
-        ctx.set_option(k, int(v))
+        if k != "batch":
+            ctx.set_option(k, int(v))
     tr = pb.build_transit(workloads.get(name), nist_rows=rows)
+    if "batch" in opts:       # retrieval batch: `batch` parameter vectors stacked along the phase axis (pb200_run_batch)
+        from prometheus_b200 import retrieval
+        spec = workloads.get(name)
+        n = int(opts.pop("batch"))
+        band = retrieval.LightcurveBand.for_planet(tr.planet, tr.spatialGrid.constructOrbphaseAxis(), spec["band"]["line_centres"],
+                                                   spec["band"]["bandwidth"])
+        batch = retrieval.RetrievalBatch(tr)
+        for _ in range(runs):
+            family, K = retrieval.make_family(tr, workloads.retrieval_samples(n))
+            lc, _, t = batch.run_family(family, K, band)
+        print(name, "batch", n, {k: round(v, 4) if isinstance(v, float) else v for k, v in t.items()})
+        return
     sc, keep, info = scene.flatten(tr)
     ctx.set_scene(sc, keep)
     out = torch.empty(info["n_orb"] * info["n_wav"], dtype=torch.float64, device="cuda:0")

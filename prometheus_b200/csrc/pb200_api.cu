@@ -48,10 +48,11 @@ void launch_optical_depth(const DevScene*, const double* sigma_u, int64_t n_chor
                           double* tau, cudaStream_t);
 void launch_mol_dmax(const DevScene*, unsigned long long* stat, int sm_count, cudaStream_t);
 void launch_mol_moments(const DevScene*, int n_slots, int phase_lo, int n_phase, int bins, double* blocks, int stride_d,
-                        unsigned long long* stat, bool count, cudaStream_t);
-int mol_block_stride(int n_atoms, int max_items);
+                        unsigned long long* stat, bool count, const MolLayout& lay, cudaStream_t);
+int mol_block_stride(int n_groups, int max_items);
+MolLayout mol_layout(const DevScene& host_copy, const unsigned long long* ranges, int grouped);
 cudaError_t launch_transit_moments(const DevScene*, const DevScene& host_copy, const TransitParams&, const double* blocks,
-                                   int stride_d, int n_slots, cudaStream_t, int* n_launch);
+                                   int stride_d, int n_slots, const MolLayout& lay, cudaStream_t, int* n_launch);
 size_t sigma_sort_temp_bytes(int64_t n);
 cudaError_t launch_sigma_sort(const double* nsig, int n_phase, int64_t n_wav_sel, unsigned long long* keys_in,
                               unsigned long long* keys_out, int* vals_in, int* perm, void* temp, size_t temp_bytes,
@@ -121,6 +122,7 @@ struct pb200_ctx {
                                                 // [3] live (phase, chord pair) blocks of the last fill pass
     int mol_bins = -1;
     int mol_max_items = -1;      // largest item count of a chord over ALL phases of the resident scene (-1: not yet counted)
+    MolLayout mol_lay = {};      // rows of the V columns the scene's chords reach (same count pass)
     bool mol_stats_pending = false;   // the last run was kernel (m) in moment form: check_oob reads [2], [3]
     bool buckets_ready = false;   // bucket indices of the sigma tables (built on the device before the first run of a scene)
     std::vector<std::pair<void*, int64_t>> regions;   // sharded uploads of the current scene: (device base, doubles per rank)
@@ -863,7 +865,7 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     // form (measurement / regression).
     bool moments_done = false;
     if (c->general_path && h.n_mols > 0 && !c->opt[PB200_OPT_MOL_RECORDS]) {
-        if (!c->d_mol_stat) PB_CUDA(c, cudaMalloc((void**)&c->d_mol_stat, 32));
+        if (!c->d_mol_stat) PB_CUDA(c, cudaMalloc((void**)&c->d_mol_stat, 256));   // [0..3] see above, [4 + 2 i], [5 + 2 i] node range of molecule i
         unsigned long long st[2] = {0ull, 0ull};
         if (c->mol_bins < 0) {   // d_max of the tables, once per scene
             PB_CUDA(c, cudaMemsetAsync(c->d_mol_stat, 0, 32, c->stream));
@@ -882,19 +884,26 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
             // The item count of a chord depends on the scene (density rows, pressure grids, bins), not on the wavelength
             // tile: counted once per scene over ALL its phases, so later runs of the scene have no host round trip.
             if (c->mol_max_items < 0) {
+                unsigned long long init[2 + 2 * kMaxMols];
+                for (int i = 0; i < kMaxMols; ++i) { init[2 + 2 * i] = ~0ull; init[3 + 2 * i] = 0ull; }   // atomicMin / atomicMax targets
+                PB_CUDA(c, cudaMemcpyAsync(c->d_mol_stat + 4, init + 2, 2 * kMaxMols * sizeof(unsigned long long), cudaMemcpyHostToDevice, c->stream));
                 PB_CUDA(c, cudaMemsetAsync(c->d_mol_stat + 1, 0, 8, c->stream));
                 if (!(phase_lo == 0 && n_phase == h.n_orb)) {   // the count needs every phase's density rows
                     launch_column(c->d_scene, h.Mp, 0, h.n_orb, c->d_oob, c->sm_count, c->stream, true, 0);
                     c->launches += 1;
                 }
-                launch_mol_moments(c->d_scene, n_slots, 0, h.n_orb, c->mol_bins, nullptr, 0, c->d_mol_stat, true, c->stream);
-                PB_CUDA(c, cudaMemcpyAsync(st, c->d_mol_stat + 1, 8, cudaMemcpyDeviceToHost, c->stream));
+                launch_mol_moments(c->d_scene, n_slots, 0, h.n_orb, c->mol_bins, nullptr, 0, c->d_mol_stat, true, MolLayout{}, c->stream);
+                unsigned long long back[4 + 2 * kMaxMols];
+                PB_CUDA(c, cudaMemcpyAsync(back, c->d_mol_stat, sizeof back, cudaMemcpyDeviceToHost, c->stream));
                 PB_CUDA(c, cudaStreamSynchronize(c->stream));
                 c->launches += 1;
-                c->mol_max_items = st[0] > 0 ? (int)st[0] : 1;
+                c->mol_max_items = back[1] > 0 ? (int)back[1] : 1;
+                for (int i = 0; i < kMaxMols; ++i)
+                    if (back[5 + 2 * i] == 0ull) back[4 + 2 * i] = 0ull;   // no in-grid sample of this molecule anywhere
+                c->mol_lay = mol_layout(h, back + 4, 1);
             }
             const int max_items = c->mol_max_items;
-            const int stride_d = mol_block_stride(h.n_atoms, max_items);
+            const int stride_d = mol_block_stride(h.n_abs, max_items);
             const size_t need = (size_t)n_phase * n_slots * stride_d * sizeof(double);
             if (need > c->mol_items_bytes) {
                 if (c->mol_items) PB_CUDA(c, cudaFree(c->mol_items));
@@ -903,10 +912,10 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
                 c->mol_items_bytes = need;
             }
             PB_CUDA(c, cudaMemsetAsync(c->d_mol_stat + 2, 0, 16, c->stream));
-            launch_mol_moments(c->d_scene, n_slots, phase_lo, n_phase, c->mol_bins, c->mol_items, stride_d, c->d_mol_stat, false, c->stream);
+            launch_mol_moments(c->d_scene, n_slots, phase_lo, n_phase, c->mol_bins, c->mol_items, stride_d, c->d_mol_stat, false, c->mol_lay, c->stream);
             c->launches += 1;
             int n_launch = 0;
-            cudaError_t e = launch_transit_moments(c->d_scene, h, prm, c->mol_items, stride_d, n_slots, c->stream, &n_launch);
+            cudaError_t e = launch_transit_moments(c->d_scene, h, prm, c->mol_items, stride_d, n_slots, c->mol_lay, c->stream, &n_launch);
             if (e == cudaSuccess) { c->launches += n_launch; moments_done = true; c->mol_stats_pending = true; }
             else if (e != cudaErrorInvalidValue) return fail(c, PB200_ERR_CUDA, "transit (moments) launch: %s", cudaGetErrorString(e));
             else cudaGetLastError();   // does not fit shared memory: the per-record form below

@@ -328,6 +328,16 @@ __device__ __forceinline__ double pb_column_bound(const ScnConst& k, const doubl
 //   * chords whose upper bound sum_a bound_a * max_w sigma_a(p, w) is already below 2^-54: they are
 //     transparent whatever the exact sum is, and get the bound stored as Ncol (so that compact_kernel's own
 //     test classifies them the same way).
+// Running maximum of the column densities of a phase (DevScene::nmax: clamp decision, thin test and window order of
+// kernel (c') -- an UPPER bound is what they need).  Columns are >= 0, so their bit patterns order like the values: one
+// warp-wide integer max of the high words (redux.sync), rounded up by one unit of the high word (2^-20 relative), one
+// atomic per warp.
+__device__ __forceinline__ void pb_feed_max(unsigned long long* __restrict__ dst, double col, int lane) {
+    const unsigned hi = (col > 0.0) ? (unsigned)__double2hiint(col) + 1u : 0u;   // NaN compares false: not fed (as before)
+    const unsigned wmax = __reduce_max_sync(0xffffffffu, hi);
+    if (lane == 0 && wmax) atomicMax(dst, (unsigned long long)wmax << 32);
+}
+
 constexpr int kColCta = 256;
 constexpr int kColMaxXs = 2048;   // x samples whose (x - cx)^2 are kept in shared memory (16 KB); beyond: formed per sample
 __global__ void __launch_bounds__(kColCta, 4)
@@ -338,10 +348,10 @@ column_cta_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, i
     __shared__ int s_cnt[kColCta / 32];
     __shared__ ScnConst s_k[kMaxScenarios];
     __shared__ double s_sigmax[PB200_MAX_ABSORBERS];
+    __shared__ int s_abs_scn[PB200_MAX_ABSORBERS];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const int64_t cid0 = (int64_t)blockIdx.x * kColCta;
-    const int p = phase_lo + (int)(cid0 / sc.Mp);
-    const int m = (int)(cid0 % sc.Mp) + tid;
+    const int p = phase_lo + blockIdx.y;            // grid: (Mp / 256 tiles of a phase, phases)
+    const int m = blockIdx.x * kColCta + tid;
     const int64_t row = (int64_t)p * sc.Mp + m;
     const int n_x = sc.n_x;
     const double* __restrict__ xs = sc.x;
@@ -369,6 +379,7 @@ column_cta_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, i
     }
     sc.w_in[row] = wv;
     if (tid < sc.n_scen) s_k[tid] = pb_scn_const(sc.scen[tid], p);   // log2(R), 1/H, ...: once per CTA, not once per thread
+    if (run_mode && tid >= 64 && tid < 64 + sc.n_abs) s_abs_scn[tid - 64] = sc.cons[sc.abs_first[tid - 64]].scenario;
     if (run_mode == 1 && tid >= 32 && tid < 32 + sc.n_abs) {
         // upper bound of the absorber's cross section at ANY wavelength: sum_k chi_k (10^max(tab_y_k) - offset_k) (the
         // table lookup is a convex combination of table values).  Independent of sigma_phase_kernel, which therefore
@@ -387,7 +398,7 @@ column_cta_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, i
     if (need_sum && run_mode == 1) {   // transparent whatever the exact sums are?
         double bound = 0.0;
         for (int g = 0; g < sc.n_abs; ++g) {
-            const double ub = pb_column_bound(s_k[sc.cons[sc.abs_first[g]].scenario], big, ltab, n_x, y, z);
+            const double ub = pb_column_bound(s_k[s_abs_scn[g]], big, ltab, n_x, y, z);
             bound += ub * sc.delta_x * s_sigmax[g];
         }
         skip = bound < 5.5511151231257827e-17;   // 2^-54; NaN (0 * inf) -> not skipped
@@ -411,7 +422,7 @@ column_cta_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, i
         if (run_mode) {
             g_lo = sc.n_abs;
             for (int g = 0; g < sc.n_abs; ++g)
-                if (sc.cons[sc.abs_first[g]].scenario == s) { g_lo = g < g_lo ? g : g_lo; g_hi = g; }
+                if (s_abs_scn[g] == s) { g_lo = g < g_lo ? g : g_lo; g_hi = g; }
             if (g_hi < 0) continue;   // uniform
         }
         const bool serp = S.type == PB200_SCN_SERPENS;
@@ -461,13 +472,10 @@ column_cta_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, i
             // one absorber per group of atomic constituents that share a scenario (DevScene::n_abs):
             // Ncol_g = sum_x n dx, the mixing ratios are in the group's cross section
             for (int g = g_lo; g <= g_hi; ++g) {
-                if (sc.cons[sc.abs_first[g]].scenario != s) continue;
+                if (s_abs_scn[g] != s) continue;
                 const double col = val * sc.delta_x;
                 sc.ncol[(int64_t)g * sc.n_orb * sc.Mp + row] = col;
-                double mx = (col > 0.0) ? col : 0.0;   // densities are >= 0: the bit patterns order like the values
-#pragma unroll
-                for (int d = 16; d > 0; d >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, d));
-                if (lane == 0 && mx > 0.0) atomicMax(sc.nmax + (int64_t)g * sc.n_orb + p, (unsigned long long)__double_as_longlong(mx));
+                pb_feed_max(sc.nmax + (int64_t)g * sc.n_orb + p, col, lane);
             }
         } else {
             for (int c = S.first_cons; c < S.first_cons + S.n_cons; ++c) {
@@ -475,10 +483,7 @@ column_cta_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, i
                 if (C.kind != 0) continue;
                 const double col = (val * C.chi) * sc.delta_x;                      // gasProperties.py:940
                 sc.ncol[(int64_t)C.atom_index * sc.n_orb * sc.Mp + row] = col;
-                double mx = (col > 0.0) ? col : 0.0;
-#pragma unroll
-                for (int d = 16; d > 0; d >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, d));
-                if (lane == 0 && mx > 0.0) atomicMax(sc.nmax + (int64_t)C.atom_index * sc.n_orb + p, (unsigned long long)__double_as_longlong(mx));
+                pb_feed_max(sc.nmax + (int64_t)C.atom_index * sc.n_orb + p, col, lane);
             }
         }
     }
@@ -833,7 +838,11 @@ void launch_column(const DevScene* d_scene, int Mp, int phase_lo, int n_phase, i
         column_kernel<<<grid_for_warps((int64_t)n_phase * Mp, sm_count), 256, 0, st>>>(d_scene, phase_lo, n_phase, oob);
     } else {
         const int64_t n = (int64_t)n_phase * Mp;   // Mp is a multiple of kColCta: a CTA never straddles two phases
-        column_cta_kernel<<<(unsigned)(n / kColCta), kColCta, 0, st>>>(d_scene, phase_lo, n_phase, oob, run_mode);
+        (void)n;
+        for (int p0 = 0; p0 < n_phase; p0 += 65535) {   // gridDim.y limit; a retrieval batch can stack more phases than that
+            const int np = n_phase - p0 < 65535 ? n_phase - p0 : 65535;
+            column_cta_kernel<<<dim3((unsigned)(Mp / kColCta), (unsigned)np), kColCta, 0, st>>>(d_scene, phase_lo + p0, np, oob, run_mode);
+        }
     }
 }
 constexpr int kMaxWindows = 8192;

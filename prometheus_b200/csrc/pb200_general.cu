@@ -59,16 +59,27 @@ fout_table_kernel(const DevScene* __restrict__ scp) {
 // interpolated; one extra "fill" node per molecule, one zero pad row at the end); the producer warp copies the
 // pressure grids to pgrid (may be NULL).
 __device__ __forceinline__ void pb_general_prologue(const DevScene& sc, int p, double lam, bool producer, int tid, int lane,
-                                                    double* V, double* sig, double* pgrid, int node_total) {
+                                                    double* V, double* sig, double* pgrid, const MolLayout& lay) {
     const double kLn10 = 2.302585092994046;
     if (!producer) {
-        int node0 = 0;
+        int imol = 0;
+        if (lay.grouped) {   // one effective cross section per absorber group: tau_atoms = (sum_x n dx) * sum_k chi_k sigma_k
+            for (int g = 0; g < sc.n_abs; ++g) {
+                double v = 0.0;
+                for (int k = sc.abs_first[g]; k < sc.abs_first[g] + sc.abs_count[g]; ++k) {
+                    const DevConstituent& C = sc.cons[k];
+                    const double sl = sc.scen[C.scenario].shift[p] * lam;                     // :917
+                    v = fma(C.chi, pb_interp_log(C.tab_x, C.tab_y, C.n_tab, sl, C.offset), v);
+                }
+                sig[g * kGenThreads + tid] = v;
+            }
+        }
         for (int k = 0; k < sc.n_cons; ++k) {
             const DevConstituent& C = sc.cons[k];
             const DevScenario& S = sc.scen[C.scenario];
             const double sl = S.shift[p] * lam;                                               // :917
             if (C.kind == 0) {
-                sig[C.atom_index * kGenThreads + tid] = pb_interp_log(C.tab_x, C.tab_y, C.n_tab, sl, C.offset);
+                if (!lay.grouped) sig[C.atom_index * kGenThreads + tid] = pb_interp_log(C.tab_x, C.tab_y, C.n_tab, sl, C.offset);
             } else {
                 const MolTable t = pb_mol_table(C);
                 const double Tk = pb_scn_T(S, p);
@@ -81,20 +92,22 @@ __device__ __forceinline__ void pb_general_prologue(const DevScene& sc, int p, d
                     fT = (Tk - t.gT[iT]) / (t.gT[iT + 1] - t.gT[iT]);
                     fW = (sl - t.gW[iW]) / (t.gW[iW + 1] - t.gW[iW]);
                 }
-                for (int j = 0; j < t.nP; ++j) {
+                const int row0 = lay.row0[imol], jmin = lay.jmin[imol], cnt = lay.cnt[imol];
+                for (int r = 0; r < cnt; ++r) {
+                    const int j = jmin + r;
                     double u = t.fill;
                     if (inside) {
                         const double* v = t.values + ((int64_t)j * t.nT + iT) * t.nW + iW;
                         u = (v[0] * (1.0 - fW) + v[1] * fW) * (1.0 - fT) + (v[t.nW] * (1.0 - fW) + v[t.nW + 1] * fW) * fT;
                     }
                     u *= kLn10;
-                    V[(node0 + j) * kGenThreads + tid] = u;
+                    V[(row0 + r) * kGenThreads + tid] = u;
                 }
-                V[(node0 + t.nP) * kGenThreads + tid] = t.fill * kLn10;     // fill node (records point at it with t = 0)
-                node0 += t.nP + 1;
+                V[(row0 + cnt) * kGenThreads + tid] = t.fill * kLn10;       // fill node (records point at it with t = 0)
+                ++imol;
             }
         }
-        V[(size_t)node_total * kGenThreads + tid] = 0.0;   // pad row: "V_{j+1}" of the last fill node
+        V[(size_t)lay.rows * kGenThreads + tid] = 0.0;     // pad row: "V_{j+1}" of the last fill node
     } else if (pgrid) {
         int node0 = 0;
         for (int k = 0; k < sc.n_cons; ++k) {
@@ -123,7 +136,8 @@ constexpr int kGenBlock = kGenThreads + 32;   // + one producer warp
 // "fill" node ln(fill sigma); one zero pad row at the end) | sig[n_atoms][kGenThreads] |
 // pgrid[node_total] | item[2]
 __global__ void __launch_bounds__(kGenBlock)
-transit_general_kernel(const DevScene* __restrict__ scp, const TransitParams prm, int item_doubles, int node_total, int n_mol) {
+transit_general_kernel(const DevScene* __restrict__ scp, const TransitParams prm, int item_doubles, int node_total, int n_mol,
+                       const MolLayout lay) {
     const DevScene& sc = *scp;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     double* etab = reinterpret_cast<double*>(smem_raw);
@@ -148,7 +162,7 @@ transit_general_kernel(const DevScene* __restrict__ scp, const TransitParams prm
     const double lam = live ? sc.wavelength[w] : sc.wavelength[prm.wav_lo];
     const bool per_chord_fstar = sc.fout_per_wav != 0;
 
-    pb_general_prologue(sc, p, lam, producer, tid, lane, V, sig, pgrid, node_total);
+    pb_general_prologue(sc, p, lam, producer, tid, lane, V, sig, pgrid, lay);
     __syncthreads();
 
     // Mirror pairing (sc.mirror, see compact_kernel): the chords (phi, rho) and (pi - phi, rho) have equal densities
@@ -362,7 +376,7 @@ __global__ void __launch_bounds__(256) mol_dmax_kernel(const DevScene* __restric
 template <bool COUNT>
 __global__ void __launch_bounds__(128)
 mol_moment_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, int n_slots, int bins, double* __restrict__ blocks,
-                  int stride_d, unsigned long long* __restrict__ stat) {
+                  int stride_d, unsigned long long* __restrict__ stat, const MolLayout lay) {
     const DevScene& sc = *scp;
     const int64_t cid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     int n_items = 0;
@@ -372,7 +386,7 @@ mol_moment_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, i
         const int n2 = sc.n_phi / 2, Pm = (n2 + 1) / 2;
         const int n_pairs = sc.mirror ? 2 * Pm * sc.n_rho : sc.M;
         double* out = COUNT ? nullptr : blocks + cid * stride_d;
-        const int hdr = mol_hdr_doubles(sc.n_atoms);
+        const int hdr = mol_hdr_doubles(sc.n_abs);
         double off_sum = 0.0, wv = 0.0;
         int m = q;
         if (q < n_pairs) {
@@ -394,7 +408,7 @@ mol_moment_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, i
             }
         }
         if (wv != 0.0) {   // blocked: F_in = 0 (gasProperties.py:1233)
-            int node0 = 0;
+            int imol = -1;
             live_block = true;
             for (int k = 0; k < sc.n_cons; ++k) {
                 const DevConstituent& C = sc.cons[k];
@@ -406,6 +420,9 @@ mol_moment_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, i
                 const double kT = kBoltzmann * pb_scn_T(S, p), g0 = __ldg(g), g1 = __ldg(g + nP - 1);
                 double part = 0.0, M[kMolK + 1], tc = 0.0;
                 int cur = -1, cur_joff = 0;
+                ++imol;
+                int lo_min = 1 << 30, lo_max = -1;               // COUNT: pressure intervals this chord reaches
+                const int row0 = lay.row0[imol], jmin = lay.jmin[imol], fill_row = lay.row0[imol] + lay.cnt[imol];
                 auto flush = [&]() {
                     if (cur < 0) return;
                     if (!COUNT) {
@@ -435,10 +452,12 @@ mol_moment_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, i
                         b = b < bins ? b : bins - 1;
                         centre = (b + 0.5) / bins;
                         key = lo * bins + b;
-                        joff = (node0 + lo) * kGenThreads * 8;
+                        joff = (row0 + lo - jmin) * kGenThreads * 8;
+                        lo_min = lo < lo_min ? lo : lo_min;
+                        lo_max = lo > lo_max ? lo : lo_max;
                     } else {          // outside the pressure grid: the fill node, sigma does not depend on t
                         key = nP * bins;
-                        joff = (node0 + nP) * kGenThreads * 8;
+                        joff = fill_row * kGenThreads * 8;
                     }
                     if (key != cur) {
                         flush();
@@ -453,7 +472,10 @@ mol_moment_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, i
                 }
                 flush();
                 off_sum = fma(C.offset, part, off_sum);
-                node0 += nP + 1;
+                if (COUNT && lo_max >= 0 && imol < kMaxMols) {   // (one atomic pair per chord and molecule, count pass only)
+                    atomicMin(stat + 4 + 2 * imol, (unsigned long long)lo_min);
+                    atomicMax(stat + 5 + 2 * imol, (unsigned long long)lo_max + 1ull);
+                }
             }
         }
         if (!COUNT) {
@@ -462,7 +484,14 @@ mol_moment_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, i
             out[2] = __hiloint2double(0, n_items);
             out[3] = off_sum;
             const int64_t row = (int64_t)p * sc.Mp + m, atom_stride = (int64_t)sc.n_orb * sc.Mp;
-            for (int a = 0; a < sc.n_atoms; ++a) out[4 + a] = (wv != 0.0) ? sc.ncol[a * atom_stride + row] : 0.0;
+            // one column per absorber group: sum_x n dx = Ncol_k / chi_k of a constituent with chi_k != 0
+            for (int g = 0; g < sc.n_abs; ++g) {
+                double N = 0.0;
+                if (wv != 0.0)
+                    for (int k = sc.abs_first[g]; k < sc.abs_first[g] + sc.abs_count[g]; ++k)
+                        if (sc.cons[k].chi != 0.0) { N = sc.ncol[sc.cons[k].atom_index * atom_stride + row] / sc.cons[k].chi; break; }
+                out[4 + g] = N;
+            }
         }
     }
     if (COUNT) {
@@ -506,14 +535,15 @@ __device__ __forceinline__ double mol_item_term(const double* __restrict__ it, u
 // Shared memory: exp table | V[node_total + 1][kGenThreads] | sig[n_atoms][kGenThreads] | buf[2][tile * stride_d]
 __global__ void __launch_bounds__(kGenBlock)
 transit_moment_kernel(const DevScene* __restrict__ scp, const TransitParams prm, const double* __restrict__ blocks,
-                      int stride_d, int n_slots, int tile, int node_total) {
+                      int stride_d, int n_slots, int tile, const MolLayout lay) {
     const DevScene& sc = *scp;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     double* etab = reinterpret_cast<double*>(smem_raw);
     double* V = etab + kExpTabEntries * kGenTabCopies;
-    double* sig = V + (size_t)(node_total + 1) * kGenThreads;
-    double* bufs = sig + (size_t)sc.n_atoms * kGenThreads;
-    const int hdr = mol_hdr_doubles(sc.n_atoms);
+    double* sig = V + (size_t)(lay.rows + 1) * kGenThreads;
+    double* bufs = sig + (size_t)sc.n_abs * kGenThreads;
+    const int hdr = mol_hdr_doubles(sc.n_abs);
+    const int n_grp = sc.n_abs;
     const int buf_doubles = tile * stride_d;
 
     const int tid = threadIdx.x, lane = tid & 31;
@@ -525,7 +555,7 @@ transit_moment_kernel(const DevScene* __restrict__ scp, const TransitParams prm,
     const bool live = !producer && w < prm.wav_lo + prm.n_wav_sel;
     const double lam = live ? sc.wavelength[w] : sc.wavelength[prm.wav_lo];
     const bool per_chord_fstar = sc.fout_per_wav != 0;
-    pb_general_prologue(sc, p, lam, producer, tid, lane, V, sig, nullptr, node_total);
+    pb_general_prologue(sc, p, lam, producer, tid, lane, V, sig, nullptr, lay);
     __syncthreads();
 
     // this split's slots [q_lo, q_hi): whole tiles (n_slots and the split size are multiples of the tile)
@@ -563,7 +593,7 @@ transit_moment_kernel(const DevScene* __restrict__ scp, const TransitParams prm,
             const double wv = blk[0];
             if (wv == 0.0) continue;   // blocked or padding (block-uniform branch)
             double tau = 0.0;
-            for (int a = 0; a < sc.n_atoms; ++a) tau = fma(blk[4 + a], sig[a * kGenThreads + tid], tau);   // :954
+            for (int g = 0; g < n_grp; ++g) tau = fma(blk[4 + g], sig[g * kGenThreads + tid], tau);   // :954, atoms of a scenario as one absorber
             const int n_items = __double2loint(blk[2]);
             const double* items = blk + hdr;
             double s0 = 0.0, s1 = 0.0;   // (four interleaved items: 72 registers, 20.4 against 18.7 ms at C2)
@@ -591,13 +621,38 @@ void launch_mol_dmax(const DevScene* d_scene, unsigned long long* stat, int sm_c
     mol_dmax_kernel<<<sm_count * 4, 256, 0, st>>>(d_scene, stat);
 }
 void launch_mol_moments(const DevScene* d_scene, int n_slots, int phase_lo, int n_phase, int bins, double* blocks, int stride_d,
-                        unsigned long long* stat, bool count, cudaStream_t st) {
+                        unsigned long long* stat, bool count, const MolLayout& lay, cudaStream_t st) {
     const int64_t n = (int64_t)n_phase * n_slots;
     const unsigned nb = (unsigned)((n + 127) / 128);
-    if (count) mol_moment_kernel<true><<<nb, 128, 0, st>>>(d_scene, phase_lo, n_phase, n_slots, bins, nullptr, 0, stat);
-    else mol_moment_kernel<false><<<nb, 128, 0, st>>>(d_scene, phase_lo, n_phase, n_slots, bins, blocks, stride_d, stat);
+    if (count) mol_moment_kernel<true><<<nb, 128, 0, st>>>(d_scene, phase_lo, n_phase, n_slots, bins, nullptr, 0, stat, lay);
+    else mol_moment_kernel<false><<<nb, 128, 0, st>>>(d_scene, phase_lo, n_phase, n_slots, bins, blocks, stride_d, stat, lay);
 }
-int mol_block_stride(int n_atoms, int max_items) { return mol_hdr_doubles(n_atoms) + max_items * kMolItemD; }
+
+// Row layout of the V columns.  ranges == NULL: every pressure node of every molecule (per-record form); else
+// ranges[2 i], ranges[2 i + 1] = first interval and last interval + 1 the chords of the scene reach in molecule i
+// (0, 0: none) -- interval lo needs the nodes lo and lo + 1.
+MolLayout mol_layout(const DevScene& h, const unsigned long long* ranges, int grouped) {
+    MolLayout lay{};
+    int row = 0, i = 0;
+    for (int k = 0; k < h.n_cons && i < kMaxMols; ++k) {
+        if (h.cons[k].kind != 1) continue;
+        const int nP = h.cons[k].dims[0];
+        int jmin = 0, cnt = nP;
+        if (ranges) {
+            const long long lo = (long long)ranges[2 * i], hi1 = (long long)ranges[2 * i + 1];
+            if (hi1 <= 0 || lo >= nP) { jmin = 0; cnt = 0; }
+            else { jmin = (int)lo; cnt = (int)(hi1 - lo) + 1; if (jmin + cnt > nP) cnt = nP - jmin; }
+        }
+        lay.row0[i] = row; lay.jmin[i] = jmin; lay.cnt[i] = cnt;
+        row += cnt + 1;
+        ++i;
+    }
+    lay.n_mol = i;
+    lay.rows = row;
+    lay.grouped = grouped;
+    return lay;
+}
+int mol_block_stride(int n_groups, int max_items) { return mol_hdr_doubles(n_groups) + max_items * kMolItemD; }
 // blocks per tile: a power of two <= 8 (divides kChordTile) within `budget` bytes for the two buffers, at least one
 // block.  (Tiles of 2 blocks to fit four CTAs per SM instead of three were slower: 22.8 against 18.7 ms at C2.)
 int mol_tile(int stride_d, size_t fixed_bytes, size_t budget) {
@@ -607,25 +662,22 @@ int mol_tile(int stride_d, size_t fixed_bytes, size_t budget) {
 }
 
 cudaError_t launch_transit_moments(const DevScene* d_scene, const DevScene& h, const TransitParams& prm, const double* blocks,
-                                   int stride_d, int n_slots, cudaStream_t st, int* n_launch) {
+                                   int stride_d, int n_slots, const MolLayout& lay, cudaStream_t st, int* n_launch) {
     *n_launch = 0;
-    int node_total = 0;
-    for (int k = 0; k < h.n_cons; ++k)
-        if (h.cons[k].kind == 1) node_total += h.cons[k].dims[0] + 1;
-    if (node_total > kMaxMolNodes) return cudaErrorInvalidValue;
+    if (lay.rows > kMaxMolNodes || h.n_mols > kMaxMols) return cudaErrorInvalidValue;
     if (h.fout_per_wav) {
         fout_table_kernel<<<(unsigned)((h.n_wav + kGenThreads - 1) / kGenThreads), kGenThreads, 0, st>>>(d_scene);
         ++*n_launch;
     }
     const size_t fixed = (size_t)kExpTabEntries * kGenTabCopies * sizeof(double) +
-                         (size_t)(node_total + 1) * kGenThreads * sizeof(double) + (size_t)h.n_atoms * kGenThreads * sizeof(double);
+                         (size_t)(lay.rows + 1) * kGenThreads * sizeof(double) + (size_t)h.n_abs * kGenThreads * sizeof(double);
     const int tile = mol_tile(stride_d, 0, 48 * 1024);
     const size_t smem = fixed + 2 * (size_t)tile * stride_d * sizeof(double);
     if (smem > 200 * 1024) return cudaErrorInvalidValue;
     cudaError_t e = cudaFuncSetAttribute(transit_moment_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     dim3 grid((unsigned)((prm.n_wav_sel + kGenThreads - 1) / kGenThreads), (unsigned)prm.n_phase, (unsigned)prm.n_split);
-    transit_moment_kernel<<<grid, kGenBlock, smem, st>>>(d_scene, prm, blocks, stride_d, n_slots, tile, node_total);
+    transit_moment_kernel<<<grid, kGenBlock, smem, st>>>(d_scene, prm, blocks, stride_d, n_slots, tile, lay);
     ++*n_launch;
     return cudaGetLastError();
 }
@@ -637,11 +689,12 @@ cudaError_t launch_transit_general(const DevScene* d_scene, const DevScene& h, c
     int node_total = 0, n_mol = 0;
     for (int k = 0; k < h.n_cons; ++k)
         if (h.cons[k].kind == 1) { node_total += h.cons[k].dims[0] + 1; ++n_mol; }
-    if (node_total > kMaxMolNodes) return cudaErrorInvalidValue;
+    if (node_total > kMaxMolNodes || n_mol > kMaxMols) return cudaErrorInvalidValue;
     if (h.fout_per_wav) {
         fout_table_kernel<<<(unsigned)((h.n_wav + kGenThreads - 1) / kGenThreads), kGenThreads, 0, st>>>(d_scene);
         ++*n_launch;
     }
+    const MolLayout lay = mol_layout(h, nullptr, 0);   // every node; one sigma column per atomic constituent
     const int n_rec_all = n_mol * h.n_x;
     const int run_off = ((4 + h.n_atoms + 1) + 1) & ~1;
     const int item_doubles = run_off + ((n_rec_all + 1 + 1) & ~1) + n_rec_all * (int)(sizeof(MolRecord) / sizeof(double));
@@ -652,7 +705,7 @@ cudaError_t launch_transit_general(const DevScene* d_scene, const DevScene& h, c
     cudaError_t e = cudaFuncSetAttribute(transit_general_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     dim3 grid((unsigned)((prm.n_wav_sel + kGenThreads - 1) / kGenThreads), (unsigned)prm.n_phase, (unsigned)prm.n_split);
-    transit_general_kernel<<<grid, kGenBlock, smem, st>>>(d_scene, prm, item_doubles, node_total, n_mol);
+    transit_general_kernel<<<grid, kGenBlock, smem, st>>>(d_scene, prm, item_doubles, node_total, n_mol, lay);
     ++*n_launch;
     return cudaGetLastError();
 }

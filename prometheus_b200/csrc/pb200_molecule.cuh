@@ -24,6 +24,21 @@ __device__ __host__ __forceinline__ MolTable pb_mol_table(const DevConstituent& 
     return t;
 }
 
+// Rows of the per-thread columns V[row][thread] = ln sigma(P_node, T, shift * lambda) that kernel (m) keeps in shared
+// memory.  The per-record form holds every pressure node; the moment form only the nodes the scene's chords reach
+// (found once per scene by the count pass of mol_moment_kernel): C2's pressures span 9 of the 13 decades of its tables,
+// and with the atoms of a scenario folded into one effective cross section that is the difference between two and three
+// CTAs per SM.
+constexpr int kMaxMols = 8;
+struct MolLayout {
+    int n_mol;
+    int row0[kMaxMols];   // first row of molecule i
+    int jmin[kMaxMols];   // pressure node held in row0[i]
+    int cnt[kMaxMols];    // node rows held: nodes jmin .. jmin + cnt - 1; the molecule's fill row follows at row0 + cnt
+    int rows;             // all rows; one zero pad row follows ("V_{j+1}" of the last fill row)
+    int grouped;          // 1: sig[g] = sum_k chi_k sigma_k per absorber group (DevScene::n_abs); 0: sig[a] per atomic constituent
+};
+
 // interval index with g[i] <= v < g[i+1], clipped to [0, n-2]
 __device__ __forceinline__ int pb_interval(const double* __restrict__ g, int n, double v) {
     int lo = 0, hi = n - 1;
