@@ -75,7 +75,7 @@ class ClockSampler:
                0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
                0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting"}
 
-    def __init__(self, index: int, period: float = 0.05):
+    def __init__(self, index: int, period: float = 0.005):
         self.samples, self.mask, self.max_mhz, self.power = [], 0, None, []
         self._stop = threading.Event()
         self._thr = None
@@ -407,17 +407,20 @@ def quick_workload(name, ctx, torch, stream, flush, peak_tflops, steps=3, warmup
     sc, keep, info = scene.flatten(tr)
     ctx.set_scene(sc, keep)
     out = torch.empty(info["n_orb"] * info["n_wav"], dtype=torch.float64, device=flush.device)
-    ms, kern = [], []
-    for i in range(warmup + steps):
+    ms, kern, evs = [], [], []
+    for i in range(warmup + steps):      # timed steps queue without a host synchronisation (see run_b200)
         flush.zero_()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
-        t = ctx.run_device(0, info["n_orb"], 0, info["n_wav"], out.data_ptr(), want_timing=True)
+        ctx.run_device(0, info["n_orb"], 0, info["n_wav"], out.data_ptr())
         b.record()
-        torch.cuda.synchronize()
         if i >= warmup:
-            ms.append(a.elapsed_time(b))
-            kern.append(t)
+            evs.append((a, b))
+    torch.cuda.synchronize()
+    ms = [a.elapsed_time(b) for a, b in evs]
+    for i in range(3):                   # instrumented steps: the library's per-kernel record
+        flush.zero_()
+        kern.append(ctx.run_device(0, info["n_orb"], 0, info["n_wav"], out.data_ptr(), want_timing=True))
     R = tr.sumOverChords()                       # warm-up: page-locked result block, scratch growth
     R = None                                     # give the block back to the pool: the timed call reuses it
     t0 = time.perf_counter()
@@ -636,10 +639,14 @@ def run_b200(args):
             torch.cuda.synchronize(dev)
 
         # ---- device-resident timing --------------------------------------------------------------
+        # The timed steps are enqueued WITHOUT asking for the library's timing record (that costs a host synchronisation
+        # per step and would put every step's launch latency into the measurement); they are bracketed by CUDA events on
+        # the launching stream, the L2 flush between them.  The per-kernel breakdown comes from instrumented steps after.
+        tile_inst = st.compute_tile
+        st.compute_tile = pbd.tile_function(ctx, axis, world, rank)
         for _ in range(args.warmup):
             st.run_device(gather=False)
         barrier()
-        tile_t.clear()
         launches0 = ctx.launch_count()
         ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
         clocks = ClockSampler(local)
@@ -650,8 +657,13 @@ def run_b200(args):
             st.run_device(gather=False)       # the R tiles stay on the GPUs that computed them (independent units)
             b.record()
         barrier()
-        clk = clocks.stop()
         launches = ctx.launch_count() - launches0
+        st.compute_tile = tile_inst
+        tile_t.clear()
+        for _ in range(5):
+            flush.zero_()
+            st.run_device(gather=False)
+        barrier()
         step_ms = [a.elapsed_time(b) for a, b in ev]
         total_ms = torch.tensor([sum(step_ms)], dtype=torch.float64, device=dev)
         if world > 1:
@@ -683,6 +695,7 @@ def run_b200(args):
             st.run_device(gather=False)
             b.record()
         barrier()
+        clk = clocks.stop()                   # sampled over both timed loops (production steps and the brute-force launches)
         nc_total = torch.tensor([sum(a.elapsed_time(b) for a, b in ev_nc)], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(nc_total, op=dist.ReduceOp.MAX)
@@ -700,7 +713,7 @@ def run_b200(args):
         barrier()
 
         # ---- end to end through the host API (host buffers, H2D + D2H inside) ---------------------
-        state = {}
+        state = {"timeline": True}
         e2e_ms = []
         R_e2e = None
         for i in range(args.warmup + args.steps):

@@ -24,9 +24,14 @@ def main(argv):
     rows = np.load(os.path.join(ROOT, "tests", "golden", "linelist.npz"))["rows"]
     ctx = host.get_context(0)
     for k, v in opts.items():
-        if k != "batch":
+        if k not in ("batch", "ranks"):
             ctx.set_option(k, int(v))
-    tr = pb.build_transit(workloads.get(name), nist_rows=rows)
+    spec = workloads.get(name)
+    ranks = int(opts.pop("ranks", 1))
+    if ranks > 1:             # one rank's block-cyclic tile of the `ranks`-fold refined grid (bench.py's weak-scaling rule)
+        spec["wavelength"][3] /= ranks
+        spec["wavelength"][4] /= ranks
+    tr = pb.build_transit(spec, nist_rows=rows)
     if "batch" in opts:       # retrieval batch: `batch` parameter vectors stacked along the phase axis (pb200_run_batch)
         from prometheus_b200 import retrieval
         spec = workloads.get(name)
@@ -42,8 +47,14 @@ def main(argv):
     sc, keep, info = scene.flatten(tr)
     ctx.set_scene(sc, keep)
     out = torch.empty(info["n_orb"] * info["n_wav"], dtype=torch.float64, device="cuda:0")
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda:0")
     for _ in range(runs):
-        t = ctx.run_device(0, info["n_orb"], 0, info["n_wav"], out.data_ptr(), want_timing=True)
+        flush.zero_()
+        torch.cuda.synchronize()
+        if ranks > 1:
+            t = ctx.run_device_cyclic(0, info["n_orb"], 256, ranks, 0, out.data_ptr(), want_timing=True)
+        else:
+            t = ctx.run_device(0, info["n_orb"], 0, info["n_wav"], out.data_ptr(), want_timing=True)
     print(name, {k: round(v, 4) if isinstance(v, float) else v for k, v in t.items()})
     if "kernel_a" in argv:
         dens = torch.empty(info["n_chords"] * info["n_x"], dtype=torch.float64, device="cuda:0")

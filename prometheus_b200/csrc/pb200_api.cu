@@ -734,7 +734,9 @@ bool want_sorted(const pb200_ctx* c, int n_phase, int64_t n_wav_sel) {
     const DevScene& h = c->h_scene;
     const bool possible = !c->general_path && h.n_abs == 1 && n_phase < (1 << 20) && (int64_t)n_phase * n_wav_sel < (1ll << 31);
     if (c->opt[PB200_OPT_SORT] >= 0) return possible && c->opt[PB200_OPT_SORT] == 1;
-    return possible && n_wav_sel >= (1 << 16) && h.M >= (1 << 14);
+    // (the wavelength count is this RUN's: a rank of an 8-GPU job holds an eighth of the grid and still gains -- C5 / 8:
+    // 37 538 wavelengths, 9.1 ms unsorted against 2.9 sorted)
+    return possible && n_wav_sel >= (1 << 13) && h.M >= (1 << 14);
 }
 
 int check_scene(pb200_ctx* c) {
@@ -772,11 +774,12 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     // wavelengths per CTA: kernel (m) 128; kernel (c') one window of 32 * WPT (WPT = 8, 4, 2 for <= 2, <= 4, more absorbers)
     const int cta_wav = c->general_path ? 256 : 32 * (h.n_abs <= 2 ? 8 : h.n_abs <= 4 ? 4 : 2);
     const int64_t ctas = ((n_wav_sel + cta_wav - 1) / cta_wav) * n_phase;
-    // Chord-axis splits: enough CTAs that the last wave is a small fraction of the run.  Kernel (m) does the
-    // same work in every CTA and wants ~80 per SM; kernel (c') has one CTA per wavelength window, most of which
+    // Chord-axis splits: enough CTAs that the last wave is a small fraction of the run (~16 per SM).  Kernel (m) does
+    // the same work in every CTA; kernel (c') has one CTA per wavelength window, most of which
     // finish early (thin or culled), so ~16 per SM is plenty -- and with a single split it writes R itself
     // and finalize_kernel (and the partial sums' traffic) is not needed at all.
-    int64_t want = ((int64_t)c->sm_count * (c->general_path ? 80 : 16) + ctas - 1) / ctas;
+    // (kernel (m) pays its prologue -- table searches and the V columns of every thread -- once per CTA: few, long CTAs)
+    int64_t want = ((int64_t)c->sm_count * 16 + ctas - 1) / ctas;
     if (want > n_tiles / 4) want = n_tiles / 4;
     if (want < 1) want = 1;
     prm.tiles_per_split = (int)((n_tiles + want - 1) / want);
@@ -812,17 +815,17 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
 
     PB_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
     cudaStream_t sig_stream = c->stream;
+    if (!c->buckets_ready && h.n_atoms > 0) {   // after the (possibly sharded + all-gathered) tables are complete on the device
+        launch_bucket_build(c->d_scene, c->sm_count, c->stream);
+        c->launches += 1;
+        c->buckets_ready = true;
+    }
     if (!c->general_path) {   // sigma(p, w) of the tile and its per-phase maxima, needed by the culling below
         if (h.n_atoms < 1) return fail(c, PB200_ERR_INVALID, "scene has no absorbing constituent");
         if (h.n_abs > PB200_MAX_ABSORBERS)   // before any kernel that sizes shared memory by the absorber count
             return fail(c, PB200_ERR_UNSUPPORTED, "%d absorbers (scenarios with atomic constituents); kernel (c') is compiled for <= %d", h.n_abs, PB200_MAX_ABSORBERS);
         // smax is left clean by compact_kernel of the previous run (and by pb200_set_scene), the run
         // statistics are reset by sigma_phase_kernel: no memset nodes in the run
-        if (!c->buckets_ready) {   // after the (possibly sharded + all-gathered) tables are complete on the device
-            launch_bucket_build(c->d_scene, c->sm_count, c->stream);
-            c->launches += 1;
-            c->buckets_ready = true;
-        }
         // sigma_phase (+ the sort) and the column kernel do not depend on each other (the column kernel bounds sigma by
         // the tables' maxima): fork -- sigma on the auxiliary stream, column on the main one -- and join before compaction
         PB_CUDA(c, cudaEventRecord(c->ev_fork, c->stream));

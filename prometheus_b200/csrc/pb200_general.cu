@@ -69,7 +69,7 @@ __device__ __forceinline__ void pb_general_prologue(const DevScene& sc, int p, d
                 for (int k = sc.abs_first[g]; k < sc.abs_first[g] + sc.abs_count[g]; ++k) {
                     const DevConstituent& C = sc.cons[k];
                     const double sl = sc.scen[C.scenario].shift[p] * lam;                     // :917
-                    v = fma(C.chi, pb_interp_log(C.tab_x, C.tab_y, C.n_tab, sl, C.offset), v);
+                    v = fma(C.chi, exp10(pb_cons_log_sigma(C, sl)) - C.offset, v);
                 }
                 sig[g * kGenThreads + tid] = v;
             }
@@ -79,7 +79,7 @@ __device__ __forceinline__ void pb_general_prologue(const DevScene& sc, int p, d
             const DevScenario& S = sc.scen[C.scenario];
             const double sl = S.shift[p] * lam;                                               // :917
             if (C.kind == 0) {
-                if (!lay.grouped) sig[C.atom_index * kGenThreads + tid] = pb_interp_log(C.tab_x, C.tab_y, C.n_tab, sl, C.offset);
+                if (!lay.grouped) sig[C.atom_index * kGenThreads + tid] = exp10(pb_cons_log_sigma(C, sl)) - C.offset;
             } else {
                 const MolTable t = pb_mol_table(C);
                 const double Tk = pb_scn_T(S, p);

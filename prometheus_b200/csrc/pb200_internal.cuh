@@ -41,6 +41,16 @@ struct DevConstituent {
     int pad;
 };
 
+// log10(sigma + offset) of an atomic constituent at wavelength sl (np.interp semantics), through the bucket index of
+// its table when it has one: the same index, hence the same bits, as the full binary search
+__device__ __forceinline__ double pb_cons_log_sigma(const DevConstituent& C, double sl) {
+    if (C.bucket) {   // the answer j (largest with tab_x[j] <= sl) lies in [bucket[b] - 1, bucket[b + 1])
+        const int b = pb_bucket_of(sl, C.bucket_x0, C.bucket_inv, C.n_bucket);
+        return pb_interp_bracket(C.tab_x, C.tab_y, C.n_tab, sl, (int64_t)__ldg(C.bucket + b) - 1, __ldg(C.bucket + b + 1));
+    }
+    return pb_interp(C.tab_x, C.tab_y, C.n_tab, sl);
+}
+
 struct DevScene {
     int n_x, n_rho, n_phi, n_orb;
     int n_scen, n_cons, n_moons, n_atoms, n_mols;

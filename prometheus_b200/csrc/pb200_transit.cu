@@ -87,14 +87,7 @@ __global__ void __launch_bounds__(256) sigma_phase_kernel(const DevScene* __rest
             double v = 0.0;
             for (int k = k0; k < k0 + sc.abs_count[a]; ++k) {
                 const DevConstituent& C = sc.cons[k];
-                double lg;
-                if (C.bucket) {   // the answer j (largest with tab_x[j] <= sl) lies in [bucket[b] - 1, bucket[b + 1])
-                    const int b = pb_bucket_of(sl, C.bucket_x0, C.bucket_inv, C.n_bucket);
-                    lg = pb_interp_bracket(C.tab_x, C.tab_y, C.n_tab, sl, (int64_t)__ldg(C.bucket + b) - 1, __ldg(C.bucket + b + 1));
-                } else {
-                    lg = pb_interp(C.tab_x, C.tab_y, C.n_tab, sl);
-                }
-                v = fma(C.chi, exp10(lg) - C.offset, v);                                      // :940 chi, :950-951 sigma
+                v = fma(C.chi, exp10(pb_cons_log_sigma(C, sl)) - C.offset, v);                                      // :940 chi, :950-951 sigma
             }
             const double ns = -v * kExpBigScale;
             prm.nsig[((int64_t)a * prm.n_phase + pi) * prm.n_wav_sel + wi] = ns;

@@ -438,9 +438,13 @@ def sum_over_chords_shared(transit, group=None, device: int | None = None, state
     rank = torch.distributed.get_rank(group) if torch.distributed.is_initialized() else 0
     import time
     sr = shared_result_for(group, state)
+    timeline = state is not None and state.get("timeline")       # CUDA events on the context's stream (bench.py asks)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)] if timeline else None
     t0 = time.perf_counter()
     sc, keep, info = scene.flatten(transit)
     t1 = time.perf_counter()
+    if ev:
+        ev[0].record()
     if world > 1:
         # every rank sends one world-th of each large sigma table over its PCIe link; the rest arrives from the
         # peers over NVLink (one in-place all-gather per table)
@@ -451,10 +455,15 @@ def sum_over_chords_shared(transit, group=None, device: int | None = None, state
             torch.distributed.all_gather_into_tensor(full, full[rank * chunk:(rank + 1) * chunk], group=group)
     else:
         ctx.set_scene(sc, keep)
+    if ev:
+        ev[1].record()
     t2 = time.perf_counter()
     k, view, dev = sr.begin(info["n_orb"], info["n_wav"])
     t3 = time.perf_counter()
     ctx.run_scatter(0, info["n_orb"], CYCLIC_BLOCK, world, rank, dev, info["n_wav"])
+    if ev:
+        ev[2].record()
+    t3b = time.perf_counter()
     ctx.synchronize()
     t4 = time.perf_counter()
     out = sr.end(k, view)
@@ -462,5 +471,8 @@ def sum_over_chords_shared(transit, group=None, device: int | None = None, state
     if state is not None:
         state["info"] = info
         state["host_ms"] = {"flatten": (t1 - t0) * 1e3, "set_scene_call": (t2 - t1) * 1e3, "begin": (t3 - t2) * 1e3,
-                            "run_and_sync": (t4 - t3) * 1e3, "end_wait": (t5 - t4) * 1e3}
+                            "run_enqueue": (t3b - t3) * 1e3, "sync_wait": (t4 - t3b) * 1e3, "end_wait": (t5 - t4) * 1e3}
+        if ev:   # device side: scene upload + table all-gather | sigma, column, compaction, transit + the result stores
+            state["host_ms"]["dev_upload_allgather"] = ev[0].elapsed_time(ev[1])
+            state["host_ms"]["dev_kernels_and_stores"] = ev[1].elapsed_time(ev[2])
     return out

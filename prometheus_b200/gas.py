@@ -160,30 +160,31 @@ class SerpensExosphere(EvaporativeExosphere):
         self.filename, self.planet, self.sigmaSmoothing = filename, planet, sigmaSmoothing
 
     def addInterpolatedDensity(self, spatialGrid):
-        """Particle file -> 3-D density table (gasProperties.py:548-583).  File reading and the O(axis) bin edges are
-        host code as in the reference; the histogram over the particles, the scaling, the Gaussian smoothing and
-        the two sums the reference prints run on the GPU (pb200_serpens_density)."""
-        serpensOutput = np.loadtxt(self.filename) * 1e2
-        particlePos = np.ascontiguousarray(serpensOutput[:, 0:3])
-        xBins = spatialGrid.constructXaxis(midpoints=False)
-        n_rho = 2 * int(spatialGrid.rho_steps)
-        yBins = np.linspace(-spatialGrid.rho_border, spatialGrid.rho_border, n_rho + 1)
-        zBins = np.linspace(-spatialGrid.rho_border, spatialGrid.rho_border, n_rho + 1)
-        cellVolume = (xBins[1] - xBins[0]) * (yBins[1] - yBins[0]) * (zBins[1] - zBins[0])
-        xPoints = spatialGrid.constructXaxis()
-        yPoints = np.linspace(-spatialGrid.rho_border, spatialGrid.rho_border, n_rho, endpoint=False) \
-            + 2. * spatialGrid.rho_border / (4. * spatialGrid.rho_steps)
-        zPoints = np.linspace(-spatialGrid.rho_border, spatialGrid.rho_border, n_rho, endpoint=False) \
-            + 2. * spatialGrid.rho_border / (4. * spatialGrid.rho_steps)
-        weights = None
-        if self.sigmaSmoothing > 0.:
-            weights = gaussian_weights(self.sigmaSmoothing)
-        n_histogram, sums = host.get_context().serpens_density(
-            particlePos, xBins, yBins, zBins, self.N, np.size(particlePos, axis=0) * cellVolume, weights,
-            yPoints, zPoints, self.planet.R, self.planet.hostStar.R)
-        print('Sum over all particles, potentially smoothed with a Gaussian:', sums[0] * cellVolume)
-        print('Sum over all particles outside of the planetary disk but inside the stellar disk:', sums[1] * cellVolume)
-        self.InterpolatedDensity = host.GridFunction((xPoints, yPoints, zPoints), n_histogram)
+        """Particle file -> tabulated density on the (x, y, z) cell midpoints (gasProperties.py:548-583).
+
+        Host side: reading the file (positions in metres, first three columns) and the O(axis) bin edges -- x as the
+        grid's own cell borders, y and z as 2 rho_steps equal cells across [-rho_border, +rho_border].  Device side
+        (pb200_serpens_density): the histogram over the particles, its scaling to a number density, the optional
+        Gaussian smoothing and the two diagnostic totals, which are reported in particle numbers as the reference does."""
+        positions_cm = np.ascontiguousarray(np.loadtxt(self.filename)[:, 0:3] * 1e2)
+        half_width, n_cells = spatialGrid.rho_border, 2 * int(spatialGrid.rho_steps)
+        edges_x = spatialGrid.constructXaxis(midpoints=False)
+        edges_y = np.linspace(-half_width, half_width, n_cells + 1)
+        edges_z = np.linspace(-half_width, half_width, n_cells + 1)
+        cell_volume = (edges_x[1] - edges_x[0]) * (edges_y[1] - edges_y[0]) * (edges_z[1] - edges_z[0])
+        mid_x = spatialGrid.constructXaxis()
+        # midpoints written as the reference writes them (left edges + a quarter of border/steps times two): the table axes
+        # must be bit-identical to the reference's for the trilinear lookup to see the same cell fractions
+        shift = 2. * half_width / (4. * spatialGrid.rho_steps)
+        mid_y = np.linspace(-half_width, half_width, n_cells, endpoint=False) + shift
+        mid_z = np.linspace(-half_width, half_width, n_cells, endpoint=False) + shift
+        smoothing = gaussian_weights(self.sigmaSmoothing) if self.sigmaSmoothing > 0. else None
+        table, totals = host.get_context().serpens_density(
+            positions_cm, edges_x, edges_y, edges_z, self.N, positions_cm.shape[0] * cell_volume, smoothing,
+            mid_y, mid_z, self.planet.R, self.planet.hostStar.R)
+        print("SERPENS table: particles represented in all cells (after smoothing, if any):", totals[0] * cell_volume)
+        print("SERPENS table: of those, between the planetary and the stellar limb:", totals[1] * cell_volume)
+        self.InterpolatedDensity = host.GridFunction((mid_x, mid_y, mid_z), table)
 
 
 def gaussian_weights(sigma, truncate=4.0):
