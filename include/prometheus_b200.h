@@ -294,6 +294,16 @@ int pb200_chord_masks(pb200_ctx* ctx, uint8_t* blocked_host, double* weight_host
    chords; their rows are simply not used).  Testing / bandwidth probe, memory-hungry.       */
 int pb200_optical_depth(pb200_ctx* ctx, int64_t wav_lo, int64_t wav_hi, double* tau_host);
 
+/* The same method for CALLER-SUPPLIED chords, as the reference's signature has it
+   (getLOSopticalDepth_Batch(x_grid, phi_batch, rho_batch, orbphase_batch, wavelength, delta_x), gasProperties.py:885):
+   the host evaluates what depends on a chord's orbital phase with the objects' own methods and passes it per chord --
+   y, z = rho*sin(phi), rho*cos(phi) [n]; per scenario the density centre cx, cy, the Doppler factor shift and, or
+   NULL, the amplitude: [n_scenarios][n] each.  x axis, delta_x, wavelengths and tables are the resident scene's.
+   tau_host[n*(wav_hi-wav_lo)].                                                                          */
+int pb200_optical_depth_chords(pb200_ctx* ctx, int64_t n, const double* y, const double* z, const double* cx,
+                               const double* cy, const double* shift, const double* amp, int64_t wav_lo,
+                               int64_t wav_hi, double* tau_host);
+
 /* ---- cross sections --------------------------------------------------------------------- */
 /* n_interp_log (gasProperties.py:34-51) == AtmosphericConstituent.getSigmaAbs (:727-735):
    out[i] = 10**interp(wl[i]; tab_x, tab_y) - offset, np.interp end clamping                 */

@@ -27,7 +27,7 @@ EXPORTS = [
     "pb200_host_register", "pb200_host_unregister", "pb200_run_scatter", "pb200_sync",
     "pb200_set_scene_sharded", "pb200_table_regions", "pb200_number_density_device",
     "pb200_serpens_density", "pb200_set_option", "pb200_get_option", "pb200_serpens_histogram_static",
-    "pb200_last_sort_order",
+    "pb200_last_sort_order", "pb200_optical_depth_chords",
 ]
 SERPENS_STATIC_MAX_CELLS = 1 << 21
 
@@ -164,6 +164,7 @@ def load():
         "pb200_column_density": (C.c_int, [vp, c_double_p]),
         "pb200_chord_masks": (C.c_int, [vp, C.POINTER(C.c_uint8), c_double_p]),
         "pb200_optical_depth": (C.c_int, [vp, i64, i64, c_double_p]),
+        "pb200_optical_depth_chords": (C.c_int, [vp, i64] + [c_double_p] * 6 + [i64, i64, c_double_p]),
         "pb200_sigma_lookup": (C.c_int, [vp, c_double_p, c_double_p, i64, dbl, c_double_p, i64, c_double_p]),
         "pb200_voigt_sigma": (C.c_int, [vp, c_double_p, c_double_p, c_double_p, i64, dbl, c_double_p, i64, dbl,
                                         c_double_p, c_double_p]),

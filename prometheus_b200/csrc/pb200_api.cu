@@ -46,6 +46,9 @@ void launch_molecular_sigma(const MolTable&, double offset, const double* P, dou
                             int64_t n_x, int64_t n_wav, double* out, int sm_count, cudaStream_t);
 void launch_optical_depth(const DevScene*, const double* sigma_u, int64_t n_chords, int64_t wav_lo, int64_t n_wav_sel,
                           double* tau, cudaStream_t);
+cudaError_t launch_optical_depth_chords(const DevScene*, int n_x, int n_density_slots, int64_t n, const double* y, const double* z,
+                                        const double* cx, const double* cy, const double* shift, const double* amp,
+                                        int64_t wav_lo, int64_t n_wav_sel, double* tau, int* oob, cudaStream_t);
 void launch_mol_dmax(const DevScene*, unsigned long long* stat, int sm_count, cudaStream_t);
 void launch_mol_moments(const DevScene*, int n_slots, int phase_lo, int n_phase, int bins, double* blocks, int stride_d,
                         unsigned long long* stat, bool count, const MolLayout& lay, cudaStream_t);
@@ -1484,6 +1487,44 @@ extern "C" int pb200_optical_depth(pb200_ctx* c, int64_t wav_lo, int64_t wav_hi,
     rc = check_oob(c);
     if (rc) return rc;
     return download(c, tau_host, tau.p, (size_t)n_c * n_wav_sel * sizeof(double));
+}
+
+// Atmosphere.getLOSopticalDepth_Batch for caller-supplied chords (gasProperties.py:885-956): tau[n][wav_hi - wav_lo].
+// y, z [n]; cx, cy, shift [n_scenarios][n] (cx, cy ignored for a tabulated density); amp NULL or [n_scenarios][n].
+extern "C" int pb200_optical_depth_chords(pb200_ctx* c, int64_t n, const double* y, const double* z, const double* cx,
+                                          const double* cy, const double* shift, const double* amp, int64_t wav_lo,
+                                          int64_t wav_hi, double* tau_host) {
+    int rc = check_scene(c);
+    if (rc) return rc;
+    const DevScene& h = c->h_scene;
+    if (n < 0 || wav_lo < 0 || wav_hi > h.n_wav || wav_lo >= wav_hi || (n && (!y || !z || !cx || !cy || !shift || !tau_host)))
+        return fail(c, PB200_ERR_INVALID, "pb200_optical_depth_chords: bad arguments");
+    if (n == 0) return PB200_OK;
+    if (h.n_orb_model != h.n_orb) return fail(c, PB200_ERR_INVALID, "pb200_optical_depth_chords: not with a stacked retrieval batch");
+    const int64_t n_wav_sel = wav_hi - wav_lo;
+    const size_t nb = (size_t)n * sizeof(double), sb = nb * h.n_scen;
+    DevBuf dy, dz, dcx, dcy, dsh, damp, tau;
+    if ((rc = upload(c, dy, y, nb)) || (rc = upload(c, dz, z, nb)) || (rc = upload(c, dcx, cx, sb)) || (rc = upload(c, dcy, cy, sb)) ||
+        (rc = upload(c, dsh, shift, sb)))
+        return rc;
+    if (amp && (rc = upload(c, damp, amp, sb))) return rc;
+    PB_CUDA(c, tau.alloc((size_t)n * n_wav_sel * sizeof(double)));
+    if (!c->buckets_ready && h.n_atoms > 0) {
+        launch_bucket_build(c->d_scene, c->sm_count, c->stream);
+        c->launches += 1;
+        c->buckets_ready = true;
+    }
+    int n_slots = 0;
+    for (int i = 0; i < h.n_scen; ++i) n_slots += h.scen[i].density_slot >= 0 ? 1 : 0;
+    cudaError_t e = launch_optical_depth_chords(c->d_scene, h.n_x, n_slots, n, dy.as<double>(), dz.as<double>(), dcx.as<double>(),
+                                                dcy.as<double>(), dsh.as<double>(), amp ? damp.as<double>() : nullptr, wav_lo,
+                                                n_wav_sel, tau.as<double>(), c->d_oob, c->stream);
+    if (e != cudaSuccess) return fail(c, e == cudaErrorInvalidValue ? PB200_ERR_UNSUPPORTED : PB200_ERR_CUDA,
+                                      "pb200_optical_depth_chords: %s", cudaGetErrorString(e));
+    c->launches += 1;
+    rc = check_oob(c);
+    if (rc) return rc;
+    return download(c, tau_host, tau.p, (size_t)n * n_wav_sel * sizeof(double));
 }
 
 // =================================================================================================

@@ -166,6 +166,69 @@ optical_depth_kernel(const DevScene* __restrict__ scp, const double* __restrict_
     }
 }
 
+// ---- Atmosphere.getLOSopticalDepth_Batch for CALLER-SUPPLIED chords (gasProperties.py:885-956) ------------------
+// One CTA per (chord, wavelength tile).  The chord's geometry arrives as arrays the host evaluated with the objects' own
+// methods: y, z and, per scenario, the density centre (cx, cy), the Doppler factor and the amplitude -- [n_scen][n].
+// The CTA first forms the x-sum of every scenario (libm forms of pb_density, fixed-order block reduction; the density
+// row of a scenario with molecules stays in shared memory), then every thread walks its wavelengths.
+__global__ void __launch_bounds__(256)
+optical_depth_chords_kernel(const DevScene* __restrict__ scp, int64_t n, int64_t chord0, const double* __restrict__ y,
+                            const double* __restrict__ z, const double* __restrict__ cx, const double* __restrict__ cy,
+                            const double* __restrict__ shift, const double* __restrict__ amp, int64_t wav_lo, int64_t n_wav_sel,
+                            double* __restrict__ tau, int* __restrict__ oob_flag) {
+    const DevScene& sc = *scp;
+    extern __shared__ double od_sm[];                 // [n_scen] sums | [8] warp partials | [n_density_slots][n_x] density rows
+    double* s_sum = od_sm;
+    double* s_part = od_sm + kMaxScenarios;
+    double* s_dens = s_part + 8;
+    const int64_t c = chord0 + blockIdx.y;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const double yc = y[c], zc = z[c];
+    for (int s = 0; s < sc.n_scen; ++s) {
+        const DevScenario& S = sc.scen[s];
+        const double a = amp ? amp[(int64_t)s * n + c] : 1.0;
+        double part = 0.0;
+        int oob = 0;
+        for (int ix = tid; ix < sc.n_x; ix += blockDim.x) {
+            double d;
+            if (S.type == PB200_SCN_SERPENS) d = pb_trilinear(S, sc.x[ix], yc, zc, &oob) * a;
+            else d = pb_density(S, S.p, a, sc.x[ix] - cx[(int64_t)s * n + c], yc - cy[(int64_t)s * n + c], zc);
+            if (S.density_slot >= 0) s_dens[(size_t)S.density_slot * sc.n_x + ix] = d;
+            part += d;
+        }
+        if (oob) *oob_flag = 1;
+        part = pb_warp_sum(part);
+        if (lane == 0) s_part[wid] = part;
+        __syncthreads();
+        if (tid == 0) { double t = 0.0; for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += s_part[w]; s_sum[s] = t; }
+        __syncthreads();
+    }
+    for (int64_t w = (int64_t)blockIdx.x * blockDim.x + tid; w < n_wav_sel; w += (int64_t)gridDim.x * blockDim.x) {
+        const double lam0 = sc.wavelength[wav_lo + w];
+        double t = 0.0;
+        for (int k = 0; k < sc.n_cons; ++k) {
+            const DevConstituent& C = sc.cons[k];
+            const DevScenario& S = sc.scen[C.scenario];
+            const double lam = shift[(int64_t)C.scenario * n + c] * lam0;                        // :917
+            if (C.kind == 0) {
+                const double N = (s_sum[C.scenario] * C.chi) * sc.delta_x;                       // :940
+                t += N * (exp10(pb_cons_log_sigma(C, lam)) - C.offset);                          // :950-954
+            } else {
+                MolTable tab = pb_mol_table(C);
+                const double* dens = s_dens + (size_t)S.density_slot * sc.n_x;
+                double acc = 0.0;
+                for (int ix = 0; ix < sc.n_x; ++ix) {
+                    const double nd = dens[ix];
+                    const double Pc = fmax(nd * kBoltzmann * S.T, 1e-4);                          // :927, :805
+                    acc = fma(nd * C.chi, exp10(pb_mol_log_sigma(tab, Pc, S.T, lam)) - C.offset, acc);   // :932-936
+                }
+                t += acc * sc.delta_x;
+            }
+        }
+        tau[c * n_wav_sel + w] = t;
+    }
+}
+
 // ---- FP64 probes: DFMA chain and exp throughput --------------------------------------------------
 __global__ void __launch_bounds__(256) probe_dfma_kernel(double* out, int iters) {
     double a0 = threadIdx.x * 1e-9, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
@@ -247,6 +310,24 @@ void launch_optical_depth(const DevScene* d_scene, const double* sigma_u, int64_
         const unsigned by = (unsigned)((n_chords - c0 < 65535) ? n_chords - c0 : 65535);
         optical_depth_kernel<<<dim3(bx, by), 256, 0, st>>>(d_scene, sigma_u, wav_lo, n_wav_sel, c0, tau);
     }
+}
+cudaError_t launch_optical_depth_chords(const DevScene* d_scene, int n_x, int n_density_slots, int64_t n, const double* y,
+                                        const double* z, const double* cx, const double* cy, const double* shift,
+                                        const double* amp, int64_t wav_lo, int64_t n_wav_sel, double* tau, int* oob,
+                                        cudaStream_t st) {
+    unsigned bx = (unsigned)((n_wav_sel + 255) / 256);
+    if (bx > 32) bx = 32;
+    const size_t smem = (size_t)(kMaxScenarios + 8 + (size_t)n_density_slots * n_x) * sizeof(double);
+    if (smem > 200 * 1024) return cudaErrorInvalidValue;
+    if (smem > 40 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(optical_depth_chords_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
+    for (int64_t c0 = 0; c0 < n; c0 += 65535) {   // gridDim.y limit
+        const unsigned by = (unsigned)((n - c0 < 65535) ? n - c0 : 65535);
+        optical_depth_chords_kernel<<<dim3(bx, by), 256, smem, st>>>(d_scene, n, c0, y, z, cx, cy, shift, amp, wav_lo, n_wav_sel, tau, oob);
+    }
+    return cudaGetLastError();
 }
 void launch_probe_dfma(double* out, int blocks, int iters, cudaStream_t st) {
     probe_dfma_kernel<<<blocks, 256, 0, st>>>(out, iters);

@@ -196,6 +196,28 @@ def gaussian_weights(sigma, truncate=4.0):
     return phi_x / phi_x.sum()
 
 
+def _carrier_scene(atmosphere, x, wavelength, delta_x):
+    """Scene with the atmosphere's scenarios, constituents and tables, the caller's x axis and wavelengths and dummy
+    one-cell sky axes: the carrier of pb200_optical_depth_chords."""
+    class _G:
+        def constructXaxis(self): return x
+        def constructRhoAxis(self): return np.array([1.0])
+        def constructPhiAxis(self): return np.array([0.0])
+        def constructOrbphaseAxis(self): return np.array([0.0])
+        def getDeltaX(self): return delta_x
+
+    class _T:
+        pass
+
+    t = _T()
+    t.spatialGrid = _G()
+    t.atmosphere = atmosphere
+    t.planet = atmosphere.densityDistributionList[0].planet
+    t.wavelength = wavelength
+    sc, keep, _ = _scene.flatten(t)
+    return sc, keep
+
+
 def _mini_scene(dist, x):
     """Scene with one scenario and dummy 1-cell axes: carrier for pb200_number_density_chords."""
     class _G:
@@ -338,6 +360,41 @@ class Atmosphere:
     def __init__(self, densityDistributionList, hasOrbitalDopplerShift):
         self.densityDistributionList = densityDistributionList
         self.hasOrbitalDopplerShift = hasOrbitalDopplerShift
+
+    def getLOSopticalDepth_Batch(self, x_grid, phi_batch, rho_batch, orbphase_batch, wavelength, delta_x):
+        """tau (n_chords, n_wav) of caller-supplied chords on the GPU -- same signature as the reference
+        (gasProperties.py:885-956).  Host work is O(n_chords): the bodies' positions, line-of-sight velocities and
+        amplitudes at each chord's orbital phase, through the objects' own methods (:908-916)."""
+        x_grid = np.asarray(x_grid, dtype=np.float64)
+        wavelength = np.asarray(wavelength, dtype=np.float64)
+        phi, rho, orb = np.broadcast_arrays(np.atleast_1d(np.asarray(phi_batch, dtype=np.float64)),
+                                            np.atleast_1d(np.asarray(rho_batch, dtype=np.float64)),
+                                            np.atleast_1d(np.asarray(orbphase_batch, dtype=np.float64)))
+        n = phi.size
+        dists = list(self.densityDistributionList)
+        ctx = host.get_context()
+        sc, keep = _carrier_scene(self, x_grid, wavelength, float(delta_x))
+        ctx.set_scene(sc, keep)
+        y, z = host.Grid.getCartesianFromCylinder(phi, rho)
+        cx, cy = np.zeros((len(dists), n)), np.zeros((len(dists), n))
+        shift, amp = np.ones((len(dists), n)), None
+        for i, dist in enumerate(dists):
+            body = dist.moon if getattr(dist, "hasMoon", False) else dist.planet
+            if _scene._kind(dist) != "SerpensExosphere":
+                bx, by = body.getPosition(orb)
+                cx[i], cy[i] = bx, by
+            if self.hasOrbitalDopplerShift:
+                shift[i] = const.calculateDopplerShift(-np.asarray(body.getLOSvelocity(orb), dtype=np.float64))
+            a = dist._amplitude(orb) if hasattr(dist, "_amplitude") else None
+            if a is not None:
+                amp = np.ones((len(dists), n)) if amp is None else amp
+                amp[i] = a
+        out = np.empty((n, wavelength.size), dtype=np.float64)
+        y, z = capi.as_f64(y), capi.as_f64(z)
+        ctx.check(ctx.lib.pb200_optical_depth_chords(ctx.handle, n, capi.dptr(y), capi.dptr(z), capi.dptr(cx), capi.dptr(cy),
+                                                     capi.dptr(shift), capi.dptr(amp) if amp is not None else None,
+                                                     0, wavelength.size, capi.dptr(out)))
+        return out
 
 
 class Transit:

@@ -125,6 +125,26 @@ def test_optical_depth_rows(name, nist_rows, models, golden):
     np.testing.assert_allclose(tau[sub][keep], g["tau_sub"][keep], rtol=2e-12, atol=1e-300)
 
 
+@pytest.mark.parametrize("name", CASES)
+def test_optical_depth_batch_of_caller_chords(name, nist_rows, models, golden):
+    """Atmosphere.getLOSopticalDepth_Batch(x_grid, phi_batch, rho_batch, orbphase_batch, wavelength, delta_x) with the
+    reference's signature (gasProperties.py:885) on the chords of the golden subset, in a scrambled order and with a
+    wavelength subset: the golden rows are what the reference's own method returned for those chords."""
+    tr, g = with_oracle_tables(name, nist_rows, models(name)), golden(name)
+    grid = tr.spatialGrid
+    chords = grid.getChordGrid()
+    blocked, _ = tr.getChordMasks()
+    sub = g["chord_subset"]
+    keep = np.flatnonzero(~blocked[sub])
+    rng = np.random.default_rng(2)
+    pick = rng.permutation(keep)[: min(keep.size, 96)]
+    cols = np.unique(np.linspace(0, tr.wavelength.size - 1, 57).astype(int))
+    tau = tr.atmosphere.getLOSopticalDepth_Batch(grid.constructXaxis(), chords[sub[pick], 0], chords[sub[pick], 1],
+                                                 chords[sub[pick], 2], tr.wavelength[cols], grid.getDeltaX())
+    assert tau.shape == (pick.size, cols.size)
+    np.testing.assert_allclose(tau, g["tau_sub"][pick][:, cols], rtol=2e-12, atol=1e-300)
+
+
 # ---- a9: sigma lookup (n_interp_log) ---------------------------------------------------------------
 def test_sigma_lookup_matches_np_interp(ctx, models):
     m = models("C5s")
