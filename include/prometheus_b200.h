@@ -179,8 +179,7 @@ typedef enum {
     PB200_OPT_MOL_RECORDS = 5,   /* 1: per-record form of kernel (m) instead of the moment form                   */
     PB200_OPT_ZEROCOPY = 6,      /* 1: pb200_run stores R straight into a page-locked result                      */
     PB200_OPT_MIN_TILES = 7,     /* least number of active chord tiles per working CTA of kernel (c') (>= 1)      */
-    PB200_OPT_GRAPH = 8,         /* 1: the launches of a run are replayed from a CUDA graph keyed on the tile     */
-    PB200_OPT_COUNT = 9
+    PB200_OPT_COUNT = 8
 } pb200_option;
 int pb200_set_option(pb200_ctx* ctx, int option, int64_t value);
 int pb200_get_option(pb200_ctx* ctx, int option, int64_t* value);

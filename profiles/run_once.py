@@ -24,9 +24,10 @@ def main(argv):
     rows = np.load(os.path.join(ROOT, "tests", "golden", "linelist.npz"))["rows"]
     ctx = host.get_context(0)
     for k, v in opts.items():
-        if k not in ("batch", "ranks"):
+        if k not in ("batch", "ranks", "strong"):
             ctx.set_option(k, int(v))
     spec = workloads.get(name)
+    strong = int(opts.pop("strong", 1))   # rank 0's share of the UNCHANGED grid split over `strong` ranks
     ranks = int(opts.pop("ranks", 1))
     if ranks > 1:             # one rank's block-cyclic tile of the `ranks`-fold refined grid (bench.py's weak-scaling rule)
         spec["wavelength"][3] /= ranks
@@ -51,7 +52,11 @@ def main(argv):
     for _ in range(runs):
         flush.zero_()
         torch.cuda.synchronize()
-        if ranks > 1:
+        if strong > 1 and info["n_mols"] == 0:
+            t = ctx.run_device_cyclic(0, info["n_orb"], 256, strong, 0, out.data_ptr(), want_timing=True)
+        elif strong > 1:
+            t = ctx.run_device(0, info["n_orb"], 0, -(-info["n_wav"] // strong), out.data_ptr(), want_timing=True)
+        elif ranks > 1:
             t = ctx.run_device_cyclic(0, info["n_orb"], 256, ranks, 0, out.data_ptr(), want_timing=True)
         else:
             t = ctx.run_device(0, info["n_orb"], 0, info["n_wav"], out.data_ptr(), want_timing=True)

@@ -134,7 +134,7 @@ struct pb200_ctx {
     const double* last_nsig_sorted = nullptr;
     int64_t last_sort_n = 0;
     // run-time options (pb200_set_option); the library never reads the environment
-    int64_t opt[PB200_OPT_COUNT] = {1, 1, 1, 1, -1, 0, 1, 1, 0};
+    int64_t opt[PB200_OPT_COUNT] = {1, 1, 1, 1, -1, 0, 1, 1};
 };
 
 static int fail(pb200_ctx* c, int code, const char* fmt, ...) {
@@ -782,8 +782,14 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     // finish early (thin or culled), so ~16 per SM is plenty -- and with a single split it writes R itself
     // and finalize_kernel (and the partial sums' traffic) is not needed at all.
     // (kernel (m) pays its prologue -- table searches and the V columns of every thread -- once per CTA: few, long CTAs)
-    int64_t want = ((int64_t)c->sm_count * 16 + ctas - 1) / ctas;
-    if (want > n_tiles / 4) want = n_tiles / 4;
+    // (the sigma-sorted windows differ in cost by orders of magnitude -- a window in the tau ~ 1 band walks every chord
+    // through the exp, most others are decided per chord without one: more, shorter CTAs keep the tail short)
+    const int per_sm = (!c->general_path && want_sorted(c, n_phase, n_wav_sel)) ? 64 : 16;
+    int64_t want = ((int64_t)c->sm_count * per_sm + ctas - 1) / ctas;
+    // at least 4 tiles per CTA of kernel (c'), 2 of kernel (m) (whose tiles are ~30 us of work each: with mirror pairing
+    // C2 has only 6 tiles per phase, and an eighth of its wavelengths is 517 CTAs -- 1.16 waves -- unless the chords split)
+    const int min_tiles_per_cta = c->general_path ? 2 : 4;
+    if (want > n_tiles / min_tiles_per_cta) want = n_tiles / min_tiles_per_cta;
     if (want < 1) want = 1;
     prm.tiles_per_split = (int)((n_tiles + want - 1) / want);
     prm.n_split = (n_tiles + prm.tiles_per_split - 1) / prm.tiles_per_split;
