@@ -439,6 +439,55 @@ def quick_workload(name, ctx, torch, stream, flush, peak_tflops, steps=3, warmup
     return res
 
 
+def setup_comparison(name="C2"):
+    """Set-up time of a workload: the mirror's build_transit -- line-list cache, refined wavelength
+    grids (host numpy), Voigt tables (kernel (b2)) -- profiled by function, next to the reference's own classes building
+    the same scene (AtmosphericConstituent.addLookupFunctionToConstituent: single-threaded scipy.special.voigt_profile,
+    gasProperties.py:672-715), when the reference copy is on the box."""
+    import cProfile
+    import pstats
+    import prometheus_b200 as pb
+    from prometheus_b200 import workloads
+    spec = workloads.get(name)
+    pb.build_transit(spec, nist_rows=nist_rows())                   # warm: context, pinned pool
+    prof = cProfile.Profile()
+    t0 = time.perf_counter()
+    prof.enable()
+    tr = pb.build_transit(spec, nist_rows=nist_rows())
+    prof.disable()
+    total = time.perf_counter() - t0
+    stats = pstats.Stats(prof).stats
+    want = {"arangeWavelengthGrid": "refined / merged wavelength grids (host numpy)", "voigt_sigma": "Voigt tables incl. H2D/D2H (kernel b2)",
+            "getLineParameters": "line selection", "species_lines": "line-list parsing (cached per list)",
+            "resolve_line_list": "line list rows", "empty": "page-locked table buffers"}
+    parts = {}
+    for (fn, _, func), (_, _, _, cum, _) in stats.items():
+        if func in want:
+            parts[func] = parts.get(func, 0.0) + cum
+    out = {"workload": name, "mirror_seconds": total, "mirror_by_function_seconds": {f"{k} ({want[k]})": v for k, v in parts.items()},
+           "n_tables": sum(1 for d in tr.atmosphere.densityDistributionList for c in d.constituents if not c.isMolecule)}
+    if reference_available():
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import make_ref
+        from prometheus_b200 import builder
+        ns = make_ref.ReferenceNamespace()
+        t0 = time.perf_counter()
+        ref = builder.build_transit(spec, ns=ns, nist_rows=ns.nist_rows)
+        out["reference_seconds"] = time.perf_counter() - t0
+        out["speedup"] = out["reference_seconds"] / total
+        worst = 0.0
+        for d_m, d_r in zip(tr.atmosphere.densityDistributionList, ref.atmosphere.densityDistributionList):
+            for c_m, c_r in zip(d_m.constituents, d_r.constituents):
+                if not c_m.isMolecule:
+                    assert np.array_equal(np.asarray(c_m.lookupFunction.x), c_r.lookupFunction.x)
+                    s_m, s_r = 10 ** np.asarray(c_m.lookupFunction.y), 10 ** c_r.lookupFunction.y
+                    big = s_r > 1e-40
+                    if big.any():
+                        worst = max(worst, float(np.max(np.abs(s_m[big] - s_r[big]) / s_r[big])))
+        out["max_rel_diff_sigma_tables"] = worst
+    return out
+
+
 def retrieval_workload(n_models=64, steps=5, warmup=3, cpu_models=2):
     """Retrieval batch: forward models/s of the mainRetrieval.py setup (RET: 60 000 chords x 25
     phases), n_models parameter vectors per call, end to end through RetrievalBatch.run -- host flattening of every
@@ -862,6 +911,8 @@ def run_b200(args):
     if world == 1 and not args.no_retrieval:
         out["retrieval"] = retrieval_workload()
 
+    if world == 1 and args.cpu_seconds > 0:
+        out["setup_comparison"] = setup_comparison("C2")
     # ---- CPU baseline on the host cores of this box (rank 0, N = 1 only) -----------------------------
     if world == 1 and args.cpu_seconds > 0:
         tables = {}

@@ -324,6 +324,13 @@ int pb200_molecular_sigma(pb200_ctx* ctx, const double* grid_P, const double* gr
                           double fill, double offset, const double* P, double T, const double* wl,
                           int64_t n_c, int64_t n_x, int64_t n_wav, double* out_host);
 
+/* Elementwise part of the table producers: out[r][c] = log10(values[r][reverse_cols ? n_cols-1-c : c] + offset).
+   MolecularConstituent.constructLookupFunction (gasProperties.py:773-781: sigma_abs = xsecarr[:, :, ::-1],
+   log10(sigma_abs + lookupOffset); n_rows = n_P*n_T, n_cols = n_lambda) and Star.addFstarFunction
+   (celestialBodies.py:263: log10(F_0); n_rows = 1, offset 0).  Reading the HDF5 / FITS files stays host code. */
+int pb200_log_table(pb200_ctx* ctx, const double* values, int64_t n_rows, int64_t n_cols, int reverse_cols,
+                    double offset, double* out_host);
+
 /* ---- tabulated-density producer ----------------------------------------------------------- */
 /* SerpensExosphere.addInterpolatedDensity (gasProperties.py:548-583), the part after np.loadtxt:
    out[nx][ny][nz] = histogramdd(pos[n][3]; edges xb, yb, zb) * N / denom   (denom = n * cellVolume, formed by

@@ -70,12 +70,16 @@ def make(force: bool = False) -> str | None:
 def pythonpath() -> list[str]:
     """sys.path entries a process needs to run the copy: the reference directory (prometheus.py imports
     `pythonScripts.*` top-level, prometheus.py:14-18) and the stubs -- the latter only for packages really missing."""
+    import importlib.util
     out = [REF_DIR]
-    try:
-        import h5py  # noqa: F401
-        import astropy.io.fits  # noqa: F401
-    except Exception:
-        out.append(STUBS)
+    for name in ("h5py", "astropy"):
+        try:
+            spec = importlib.util.find_spec(name)
+        except (ImportError, ValueError):
+            spec = None
+        if spec is None or (spec.origin or "").startswith(STUBS):
+            out.append(STUBS)
+            break
     return out
 
 

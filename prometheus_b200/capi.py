@@ -27,7 +27,7 @@ EXPORTS = [
     "pb200_host_register", "pb200_host_unregister", "pb200_run_scatter", "pb200_sync",
     "pb200_set_scene_sharded", "pb200_table_regions", "pb200_number_density_device",
     "pb200_serpens_density", "pb200_set_option", "pb200_get_option", "pb200_serpens_histogram_static",
-    "pb200_last_sort_order", "pb200_optical_depth_chords",
+    "pb200_last_sort_order", "pb200_optical_depth_chords", "pb200_log_table",
 ]
 SERPENS_STATIC_MAX_CELLS = 1 << 21
 
@@ -164,6 +164,7 @@ def load():
         "pb200_chord_masks": (C.c_int, [vp, C.POINTER(C.c_uint8), c_double_p]),
         "pb200_optical_depth": (C.c_int, [vp, i64, i64, c_double_p]),
         "pb200_optical_depth_chords": (C.c_int, [vp, i64] + [c_double_p] * 6 + [i64, i64, c_double_p]),
+        "pb200_log_table": (C.c_int, [vp, c_double_p, i64, i64, i32, dbl, c_double_p]),
         "pb200_sigma_lookup": (C.c_int, [vp, c_double_p, c_double_p, i64, dbl, c_double_p, i64, c_double_p]),
         "pb200_voigt_sigma": (C.c_int, [vp, c_double_p, c_double_p, c_double_p, i64, dbl, c_double_p, i64, dbl,
                                         c_double_p, c_double_p]),
@@ -431,6 +432,15 @@ class Context:
         nsig = np.empty(n.value, dtype=np.float64)
         self.check(self.lib.pb200_last_sort_order(self.handle, C.byref(n), perm.ctypes.data_as(C.POINTER(C.c_int32)), dptr(nsig)))
         return perm.reshape(n_phase, -1), nsig.reshape(n_phase, -1)
+
+    def log_table(self, values, offset: float = 0.0, reverse_last_axis: bool = False) -> np.ndarray:
+        """log10(values + offset), optionally with the last axis reversed (pb200_log_table); page-locked result."""
+        values = as_f64(values)
+        n_cols = values.shape[-1] if values.ndim else 1
+        out = pinned_pool.empty(values.shape)
+        self.check(self.lib.pb200_log_table(self.handle, dptr(values), values.size // max(n_cols, 1), n_cols,
+                                            1 if reverse_last_axis else 0, float(offset), dptr(out)))
+        return out
 
     def last_timing(self) -> dict:
         t = Timing()

@@ -24,7 +24,8 @@ void launch_column(const DevScene*, int Mp, int phase_lo, int n_phase, int* oob,
                    int run_mode);
 void launch_number_density_grid(const DevScene*, int64_t n_chords, int scenario, double* out, int* oob, int sm_count,
                                 cudaStream_t);
-void launch_number_density_thread(const DevScene*, int64_t n_chords, int n_x, int scenario, double* out, int sm_count, cudaStream_t);
+void launch_number_density_thread(const DevScene*, int64_t n_chords, int n_x, int scenario, double* out, int sm_count,
+                                  unsigned long long* next_tile, cudaStream_t);
 void launch_number_density_chords(const DevScene*, int scenario, int64_t n, const double* y, const double* z,
                                   const double* cx, const double* cy, const double* amp, double* out, int* oob,
                                   int sm_count, cudaStream_t);
@@ -49,6 +50,8 @@ void launch_optical_depth(const DevScene*, const double* sigma_u, int64_t n_chor
 cudaError_t launch_optical_depth_chords(const DevScene*, int n_x, int n_density_slots, int64_t n, const double* y, const double* z,
                                         const double* cx, const double* cy, const double* shift, const double* amp,
                                         int64_t wav_lo, int64_t n_wav_sel, double* tau, int* oob, cudaStream_t);
+void launch_log_table(const double* in, int64_t n_rows, int64_t n_cols, int reverse, double offset, double* out, int sm_count,
+                      cudaStream_t);
 void launch_mol_dmax(const DevScene*, unsigned long long* stat, int sm_count, cudaStream_t);
 void launch_mol_moments(const DevScene*, int n_slots, int phase_lo, int n_phase, int bins, double* blocks, int stride_d,
                         unsigned long long* stat, bool count, const MolLayout& lay, cudaStream_t);
@@ -1398,7 +1401,8 @@ extern "C" int pb200_number_density_device(pb200_ctx* c, int scenario, double* n
     if (h.scen[scenario].type == PB200_SCN_SERPENS)
         launch_number_density_grid(c->d_scene, (int64_t)h.M * h.n_orb, scenario, n_dev, c->d_oob, c->sm_count, c->stream);
     else
-        launch_number_density_thread(c->d_scene, (int64_t)h.M * h.n_orb, h.n_x, scenario, n_dev, c->sm_count, c->stream);
+        launch_number_density_thread(c->d_scene, (int64_t)h.M * h.n_orb, h.n_x, scenario, n_dev, c->sm_count,
+                                     reinterpret_cast<unsigned long long*>(c->d_oob) + 3, c->stream);
     c->launches += 1;
     PB_CUDA(c, cudaGetLastError());
     return PB200_OK;
@@ -1584,6 +1588,23 @@ extern "C" int pb200_voigt_sigma(pb200_ctx* c, const double* line_wl, const doub
     c->last.launches = 1;
     c->last.samples = n * n_lines;
     return PB200_OK;
+}
+
+// out[r][c] = log10(values[r][reverse ? n_cols-1-c : c] + offset): the elementwise part of the table producers
+extern "C" int pb200_log_table(pb200_ctx* c, const double* values, int64_t n_rows, int64_t n_cols, int reverse_cols,
+                               double offset, double* out_host) {
+    int rc = need_ctx(c);
+    if (rc) return rc;
+    if (n_rows < 0 || n_cols < 0 || (n_rows * n_cols && (!values || !out_host))) return fail(c, PB200_ERR_INVALID, "pb200_log_table: bad arguments");
+    if (n_rows * n_cols == 0) return PB200_OK;
+    DevBuf in, out;
+    const size_t nb = (size_t)n_rows * n_cols * sizeof(double);
+    if ((rc = upload(c, in, values, nb))) return rc;
+    PB_CUDA(c, out.alloc(nb));
+    launch_log_table(in.as<double>(), n_rows, n_cols, reverse_cols ? 1 : 0, offset, out.as<double>(), c->sm_count, c->stream);
+    c->launches += 1;
+    PB_CUDA(c, cudaGetLastError());
+    return download(c, out_host, out.p, nb);
 }
 
 extern "C" int pb200_voigt_profile(pb200_ctx* c, const double* x, const double* sigma, const double* gamma, int64_t n,

@@ -728,12 +728,14 @@ __device__ __forceinline__ void pb_lane_rows(const ScnConst& k, const double* __
     }
 }
 
-__global__ void __launch_bounds__(kRowsCta, 3)
-number_density_rows_kernel(const DevScene* __restrict__ scp, int scenario, double* __restrict__ out, int64_t n_tiles) {
+__global__ void __launch_bounds__(kRowsCta, 4)
+number_density_rows_kernel(const DevScene* __restrict__ scp, int scenario, double* __restrict__ out, int64_t n_tiles,
+                           unsigned long long* __restrict__ next_tile) {
     const DevScene& sc = *scp;
     const DevScenario& S = sc.scen[scenario];
     __shared__ ScnConst s_k[kRowsCta];
     __shared__ double s_pre[kRowsCta], s_cc[kRowsCta];
+    __shared__ long long s_tile;
     const int tid = threadIdx.x, grp = tid / kColLanes, l8 = tid % kColLanes;
     const int64_t n_chords = (int64_t)sc.M * sc.n_orb;
     const int n_x = sc.n_x;
@@ -741,9 +743,12 @@ number_density_rows_kernel(const DevScene* __restrict__ scp, int scenario, doubl
     const double* __restrict__ big = sc.exp_tab + kExpTabEntries;
     const double2* __restrict__ ltab = reinterpret_cast<const double2*>(sc.exp_tab + kExpTabEntries + kExpBigEntries);
     const bool vec = (n_x % 2 == 0) && ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
-    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    // persistent CTAs; the first tile is the CTA's own, further ones come from a counter (rows differ in cost: a torus row
+    // off the plane is all zeros), so the CTAs finish together
+    for (int64_t tile = blockIdx.x; tile < n_tiles;) {
         const int64_t c0 = tile * kRowsCta, c = c0 + tid;
         __syncthreads();   // the previous tile's constants are no longer read
+        if (tid == 0) s_tile = (long long)gridDim.x + (long long)atomicAdd(next_tile, 1ull);
         if (c < n_chords) {
             const int m = (int)(c / sc.n_orb), p = (int)(c % sc.n_orb);
             const int iphi = m / sc.n_rho, irho = m - iphi * sc.n_rho;
@@ -774,6 +779,7 @@ number_density_rows_kernel(const DevScene* __restrict__ scp, int scenario, doubl
                 default: break;
             }
         }
+        tile = s_tile;   // written before the barrier in the middle of this iteration, read after the row loop
     }
 }
 
@@ -865,14 +871,13 @@ void launch_number_density_grid(const DevScene* d_scene, int64_t n_chords, int s
     number_density_grid_kernel<<<grid_for_warps(n_chords, sm_count), 256, 0, st>>>(d_scene, scenario, out, oob);
 }
 void launch_number_density_thread(const DevScene* d_scene, int64_t n_chords, int n_x, int scenario, double* out, int sm_count,
-                                  cudaStream_t st) {
+                                  unsigned long long* next_tile, cudaStream_t st) {
     (void)n_x;
     const int64_t n_tiles = (n_chords + kRowsCta - 1) / kRowsCta;
-    // persistent CTAs with equal shares: ceil(tiles / slots) tiles each
-    const int64_t slots = (int64_t)sm_count * 3;
-    const int64_t per = (n_tiles + slots - 1) / slots;
-    const int64_t ctas = (n_tiles + per - 1) / (per > 0 ? per : 1);
-    number_density_rows_kernel<<<(unsigned)(ctas > 0 ? ctas : 1), kRowsCta, 0, st>>>(d_scene, scenario, out, n_tiles);
+    const int64_t slots = (int64_t)sm_count * 4;     // resident CTAs (64 registers x 256 threads)
+    const int64_t ctas = n_tiles < slots ? n_tiles : slots;
+    cudaMemsetAsync(next_tile, 0, sizeof(unsigned long long), st);
+    number_density_rows_kernel<<<(unsigned)(ctas > 0 ? ctas : 1), kRowsCta, 0, st>>>(d_scene, scenario, out, n_tiles, next_tile);
 }
 void launch_number_density_chords(const DevScene* d_scene, int scenario, int64_t n, const double* y,
                                   const double* z, const double* cx, const double* cy, const double* amp,

@@ -229,6 +229,25 @@ optical_depth_chords_kernel(const DevScene* __restrict__ scp, int64_t n, int64_t
     }
 }
 
+// ---- table producers: log10(values + offset), optionally with the last axis reversed ---------------------------
+// MolecularConstituent.constructLookupFunction (gasProperties.py:773-781: xsecarr[:, :, ::-1], log10(sigma + offset)) and
+// Star.addFstarFunction (celestialBodies.py:263: log10(F)).  HBM-bound: 16 B per element.
+__global__ void __launch_bounds__(256)
+log_table_kernel(const double* __restrict__ in, int64_t n_rows, int64_t n_cols, int reverse, double offset, double* __restrict__ out) {
+    const int64_t n = n_rows * n_cols;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / n_cols, col = i - r * n_cols;
+        const double v = in[reverse ? r * n_cols + (n_cols - 1 - col) : i];
+        out[i] = log10(__dadd_rn(v, offset));
+    }
+}
+void launch_log_table(const double* in, int64_t n_rows, int64_t n_cols, int reverse, double offset, double* out, int sm_count,
+                      cudaStream_t st) {
+    int64_t blocks = (n_rows * n_cols + 255) / 256;
+    if (blocks > (int64_t)sm_count * 16) blocks = (int64_t)sm_count * 16;
+    log_table_kernel<<<(unsigned)(blocks > 0 ? blocks : 1), 256, 0, st>>>(in, n_rows, n_cols, reverse, offset, out);
+}
+
 // ---- FP64 probes: DFMA chain and exp throughput --------------------------------------------------
 __global__ void __launch_bounds__(256) probe_dfma_kernel(double* out, int iters) {
     double a0 = threadIdx.x * 1e-9, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;

@@ -295,10 +295,27 @@ class MolecularConstituent:
         self.lookupOffset = const.LOOKUP_OFFSET
         self.moleculeName, self.chi = moleculeName, chi
 
+    def setOpacityArrays(self, p_bar, t, bin_edges, xsecarr):
+        """The four datasets of an ExoMol-style opacity file as arrays ('p' [bar], 't' [K], 'bin_edges' [1/cm, ascending],
+        'xsecarr' [n_p][n_t][n_bins], cm^2): the file-format-free door of constructLookupFunction."""
+        self.opacityArrays = tuple(np.asarray(a, dtype=np.float64) for a in (p_bar, t, bin_edges, xsecarr))
+
     def constructLookupFunction(self):
-        raise NotImplementedError(
-            "ExoMol HDF5 ingestion (gasProperties.py:765-781) is outside the hot path (h5py is not in this image); "
-            "attach a table: self.lookupFunction = GridFunction((P, T, lambda), log10(sigma + 1e-50), fill_value)")
+        """(P [dyn/cm^2], T, lambda [cm], ascending) grid and log10(sigma + offset) with fill value log10(offset)
+        (gasProperties.py:765-781).  The arrays come from setOpacityArrays or, where h5py exists, from
+        <molecularResources>/<moleculeName>.h5; the reversal of the wavenumber axis and the log10 run on the GPU."""
+        arrays = getattr(self, "opacityArrays", None)
+        if arrays is None:
+            try:
+                import h5py
+            except ImportError:
+                raise NotImplementedError("h5py is not installed: attach the datasets with setOpacityArrays(p, t, bin_edges, "
+                                          "xsecarr) (gasProperties.py:774-778 reads exactly these four)") from None
+            with h5py.File(getattr(self, "opacityPath", self.moleculeName + ".h5"), "r") as f:
+                arrays = (f["p"][:], f["t"][:], f["bin_edges"][:], f["xsecarr"][:])
+        p_bar, t, bin_edges, xsec = arrays
+        log_sigma = host.get_context().log_table(xsec, self.lookupOffset, reverse_last_axis=True)
+        return host.GridFunction((p_bar * 10., t, 1. / bin_edges[::-1]), log_sigma, np.log10(self.lookupOffset))
 
     def addLookupFunctionToConstituent(self):
         self.lookupFunction = self.constructLookupFunction()

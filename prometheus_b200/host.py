@@ -164,6 +164,27 @@ class Star:
     def addRMparameters(self, vsiniStarrot, phiStarrot):
         self.vsiniStarrot, self.phiStarrot = vsiniStarrot, phiStarrot
 
+    def setSpectrum(self, wavelength_cm, flux):
+        """Attach a stellar spectrum as arrays: what getSpectrum returns (wavelength [cm], flux / pi) -- the
+        file-format-free door; the reference fetches a PHOENIX FITS pair over the network (celestialBodies.py:128-210)."""
+        self.spectrum = (np.asarray(wavelength_cm, dtype=np.float64), np.asarray(flux, dtype=np.float64))
+
+    def getSpectrum(self):
+        if getattr(self, "spectrum", None) is None:
+            raise NotImplementedError("no stellar spectrum attached: the PHOENIX download (celestialBodies.py:128-210) needs "
+                                      "the network and astropy; use star.setSpectrum(wavelength_cm, flux)")
+        return self.spectrum
+
+    def addFstarFunction(self, wavelength):
+        """log10 F*(lambda) table over the simulation's wavelength range widened by the rotational Doppler factors, one
+        table point of margin below and two above (celestialBodies.py:242-265); the log10 runs on the GPU."""
+        w_star, flux = self.getSpectrum()
+        w_hi = np.max(wavelength) * const.calculateDopplerShift(-self.vsiniStarrot)
+        w_lo = np.min(wavelength) * const.calculateDopplerShift(self.vsiniStarrot)
+        inside = np.flatnonzero((w_star >= w_lo) & (w_star <= w_hi))
+        first, last = max(int(inside[0]) - 1, 0), int(inside[-1]) + 2
+        self.Fstar_function = TableFunction1D(w_star[first:last], get_context().log_table(flux[first:last]))
+
 
 class Planet:
     def __init__(self, name, R, M, a, hostStar, transitDuration=0.0, orbitalPeriod=0.0, b=0.0):
