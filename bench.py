@@ -361,7 +361,7 @@ def parity_check(spec, tr, R, n_cols=8):
 
 
 # ------------------------------------------------------------------------------------------------
-# FP64 work per unit, counted from the instruction streams (profiles/r02_sass_*.txt), add/mul = 1, FMA = 2
+# FP64 work per unit, counted from the instruction streams (profiles/sass_transit_inner_loop.txt, profiles/sass_moment_item_loop.txt), add/mul = 1, FMA = 2
 # ------------------------------------------------------------------------------------------------
 FLOPS_MOMENT_ITEM = 33.0      # kernel (m), per (item, wavelength): d = V1 - V0 (1), fma(tc, d, V0) (2), table exp (12),
                               # Horner of 8 moments (16), e * p (1), accumulate (1)
@@ -544,13 +544,13 @@ def workload_roofline(name, tr, info, timings, peak_tflops):
     ms = float(np.mean([t["transit_ms"] for t in timings]))
     exp_s = float(np.mean([t["exp_samples"] for t in timings]))
     exe_s = float(np.mean([t["executed_samples"] for t in timings]))
-    if info["n_mols"]:
-        flops = FLOPS_MOMENT_ITEM * exp_s + (FLOPS_MOMENT_BLOCK + 2.0 * info["n_atoms"]) * exe_s
+    n_abs = sum(1 for d in tr.atmosphere.densityDistributionList if any(not c.isMolecule for c in d.constituents))
+    if info["n_mols"]:      # the atoms of a scenario are ONE absorber in kernel (m) too (MolLayout::grouped): one FMA per group
+        flops = FLOPS_MOMENT_ITEM * exp_s + (FLOPS_MOMENT_BLOCK + 2.0 * n_abs) * exe_s
         return fp64_roofline("transit_moment_kernel (m: molecular tau in moment form + atoms + exp + disk sum)", flops, ms, peak_tflops,
                              item_wavelengths=exp_s, block_wavelengths=exe_s, flops_per_item=FLOPS_MOMENT_ITEM,
-                             flops_per_block=FLOPS_MOMENT_BLOCK + 2.0 * info["n_atoms"],
+                             flops_per_block=FLOPS_MOMENT_BLOCK + 2.0 * n_abs,
                              traffic=recorded_traffic(name, "transit_moment_kernel"))
-    n_abs = sum(1 for d in tr.atmosphere.densityDistributionList if any(not c.isMolecule for c in d.constituents))
     fps = executed_flops_per_sample(n_abs)
     return fp64_roofline("transit_kernel (c'), production launch", fps * exp_s, ms, peak_tflops, exp_samples=exp_s,
                          flops_per_sample=fps, executed_samples=exe_s,
@@ -815,7 +815,6 @@ def run_b200(args):
     tile_samples = float(n_c) * float(st.samples_tile_shape[1])          # nominal samples of this rank's tile
     if n_mols:
         executed = nc_executed = exp_samples = tile_samples                 # kernel (m) has no culling
-    n_abs = sum(1 for d in tr.atmosphere.densityDistributionList if any(not c.isMolecule for c in d.constituents))
     fps = executed_flops_per_sample(n_abs)
     # The bound of kernel (c') is the FP64 pipe (31 flops against 0.1 B per sample).  The headline figure is taken on the
     # launch that does the exp on EVERY unblocked sample (pb200_set_option CULL = MIRROR = THIN = 0: the kernel whose
@@ -895,11 +894,28 @@ def run_b200(args):
                 if i >= 3:
                     d_ms.append(a.elapsed_time(b)); f_ms.append(b.elapsed_time(c2))
             d_t, f_t = float(np.mean(d_ms)), float(np.mean(f_ms))
-            out["kernel_a"] = {"kernel": "number_density_thread_kernel (a: n(chord, x) materialised, scenario 0)",
-                               "samples": n_dens, "ms": d_t, "bound": "hbm", "achieved": 8.0 * n_dens / d_t / 1e6,
-                               "unit": "GB/s", "peak": hbm_peak, "frac": 8.0 * n_dens / d_t / 1e6 / hbm_peak,
-                               "write_only_fill_GBs": 8.0 * n_dens / f_t / 1e6,
-                               "convention": "8 B per chord*x sample (one f64 store, SURVEY 8(d) row (a))"}
+            ka = (json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("C4", {}).get("kernel_a", {})
+                  if args.workload == "C4" else {})
+            mhz = float((out.get("clocks") or {}).get("sm_mhz") or 1965.0)
+            smsp = 4 * torch.cuda.get_device_properties(dev).multi_processor_count
+            ach = 8.0 * n_dens / d_t / 1e6
+            out["kernel_a"] = {"kernel": "number_density_rows_kernel (a: n(chord, x) materialised, scenario 0)",
+                               "samples": n_dens, "ms": d_t, "bound": "issue", "achieved": ach, "unit": "GB/s",
+                               "convention": "8 B per chord*x sample (one f64 store, SURVEY 8(d) row (a))",
+                               "hbm": {"peak": hbm_peak, "frac": ach / hbm_peak, "write_only_fill_GBs": 8.0 * n_dens / f_t / 1e6,
+                                       "traffic": ka.get("dram_bytes")}}
+            if ka.get("warp_inst_per_32_samples"):     # ceilings from the committed ncu capture of this kernel (profiles/traffic.json)
+                per_s = smsp * mhz * 1e6               # warp instructions per second the SMSPs can issue (1 per cycle)
+                issue = 256.0 * per_s / ka["warp_inst_per_32_samples"] / 1e9
+                fp64 = 256.0 * per_s / (2.0 * ka["fp64_inst_per_32_samples"]) / 1e9
+                out["kernel_a"].update(peak=issue, frac=ach / issue, fp64_pipe_ceiling_GBs=fp64,
+                                       warp_inst_per_32_samples=ka["warp_inst_per_32_samples"],
+                                       fp64_inst_per_32_samples=ka["fp64_inst_per_32_samples"],
+                                       peak_source="issue slots: SMSPs x clock / executed warp instructions per 32 samples (ncu, "
+                                                   + ka.get("capture", "profiles/") + "); the FP64 pipe allows fp64_pipe_ceiling_GBs, "
+                                                   "HBM hbm.peak: the kernel is instruction-bound, not bandwidth-bound (DESIGN.md 4(a'))")
+            else:
+                out["kernel_a"].update(peak=hbm_peak, frac=ach / hbm_peak, bound="hbm")
             del dens
 
     # ---- the other BASELINE configs, device-resident, few steps (N = 1 only; parity is in tests/) -----------

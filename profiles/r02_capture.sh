@@ -1,0 +1,28 @@
+#!/bin/bash
+# Round-2 ncu captures (one GPU).  Run on the GPU box from the repo root:  bash profiles/r02_capture.sh
+# Every program is run once WITHOUT ncu first (a number printed under ncu is never a bench value); reports go to
+# gpurun_out/ and are summarised in the build container with profiles/summarize.py.
+set -u
+O=gpurun_out
+mkdir -p $O
+NCU="ncu --set full --clock-control none --import-source on"
+run() { # name, kernel regex, count, run_once arguments...
+    local name=$1 re=$2 cnt=$3; shift 3
+    timeout 600 python profiles/run_once.py "$@" > $O/once_$name.log 2>&1 || { echo "run_once $name failed"; tail -3 $O/once_$name.log; return; }
+    timeout 900 $NCU -k regex:"$re" -c $cnt -f -o $O/r02_$name python profiles/run_once.py "$@" > $O/ncu_$name.log 2>&1
+    echo "$name: rc=$? $(tail -1 $O/once_$name.log | cut -c1-200)"
+}
+# launch list of the bench command itself
+timeout 900 python bench.py --steps 2 --warmup 3 --cpu-seconds 0 > $O/bench_short.json 2> $O/bench_short.err
+echo "bench short rc=$?"
+timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $O/r02_launches_bench_C4.csv \
+    python bench.py --steps 2 --warmup 3 --cpu-seconds 0 > $O/ncu_bench.log 2>&1
+echo "bench launch list rc=$?"
+run C4_production  "transit_kernel|column_cta|compact|sigma_phase|finalize|bucket" 12 C4 1
+run C4_bruteforce  "transit_kernel" 1 C4 1 cull=0 mirror=0 thin=0
+run C4_kernel_a    "number_density_rows" 1 C4 1 kernel_a
+run C5_production  "transit_kernel|column_cta|compact" 6 C5 1
+run C2_production  "moment|column_cta|fout" 8 C2 1
+run C3_production  "transit_kernel|column_cta|compact" 6 C3 1
+run RET_batch64    "transit_kernel|column_cta|compact|lightcurve" 8 RET 1 batch=64
+ls -la $O/*.ncu-rep
