@@ -815,6 +815,7 @@ def run_b200(args):
     tile_samples = float(n_c) * float(st.samples_tile_shape[1])          # nominal samples of this rank's tile
     if n_mols:
         executed = nc_executed = exp_samples = tile_samples                 # kernel (m) has no culling
+    n_abs = sum(1 for d in tr.atmosphere.densityDistributionList if any(not c.isMolecule for c in d.constituents))
     fps = executed_flops_per_sample(n_abs)
     # The bound of kernel (c') is the FP64 pipe (31 flops against 0.1 B per sample).  The headline figure is taken on the
     # launch that does the exp on EVERY unblocked sample (pb200_set_option CULL = MIRROR = THIN = 0: the kernel whose

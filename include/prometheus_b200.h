@@ -126,6 +126,10 @@ typedef struct {
     int64_t exp_samples;         /* of those, samples that went through the table exp (the
                                     others were optically thin for their warp: tau < 2.1e-5,
                                     second-order expansion summed per chord); upper bound.
+                                    Narrow sigma-sorted windows (relative half spread of sigma
+                                    <= 1/40) count ONE per (chord, window) -- or per (chord,
+                                    32-wavelength group): one table exp feeds the nine Taylor
+                                    sums about the centre.
                                     Scenes with molecules (kernel (m), moment form): executed_samples =
                                     unblocked chord-pair blocks x wavelengths, exp_samples = moment
                                     items x wavelengths (one table exp + 8 FMAs each)         */
@@ -179,7 +183,9 @@ typedef enum {
     PB200_OPT_MOL_RECORDS = 5,   /* 1: per-record form of kernel (m) instead of the moment form                   */
     PB200_OPT_ZEROCOPY = 6,      /* 1: pb200_run stores R straight into a page-locked result                      */
     PB200_OPT_MIN_TILES = 7,     /* least number of active chord tiles per working CTA of kernel (c') (>= 1)      */
-    PB200_OPT_COUNT = 8
+    PB200_OPT_CENTRE = 8,        /* sigma-sorted windows with a narrow sigma range as Taylor sums about their centre:
+                                    0 off, 1 whole windows (256 wavelengths), 2 also per 32-wavelength group      */
+    PB200_OPT_COUNT = 9
 } pb200_option;
 int pb200_set_option(pb200_ctx* ctx, int option, int64_t value);
 int pb200_get_option(pb200_ctx* ctx, int option, int64_t* value);

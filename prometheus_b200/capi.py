@@ -32,8 +32,8 @@ EXPORTS = [
 SERPENS_STATIC_MAX_CELLS = 1 << 21
 
 # pb200_option (include/prometheus_b200.h)
-OPT = {"cull": 0, "mirror": 1, "thin": 2, "group": 3, "sort": 4, "mol_records": 5, "zerocopy": 6, "min_tiles": 7}
-OPT_DEFAULTS = {"cull": 1, "mirror": 1, "thin": 1, "group": 1, "sort": -1, "mol_records": 0, "zerocopy": 1, "min_tiles": 1}
+OPT = {"cull": 0, "mirror": 1, "thin": 2, "group": 3, "sort": 4, "mol_records": 5, "zerocopy": 6, "min_tiles": 7, "centre": 8}
+OPT_DEFAULTS = {"cull": 1, "mirror": 1, "thin": 1, "group": 1, "sort": -1, "mol_records": 0, "zerocopy": 1, "min_tiles": 1, "centre": 2}
 
 SCN_BAROMETRIC, SCN_HYDROSTATIC, SCN_POWERLAW, SCN_TORUS, SCN_SERPENS = range(5)
 

@@ -137,7 +137,7 @@ struct pb200_ctx {
     const double* last_nsig_sorted = nullptr;
     int64_t last_sort_n = 0;
     // run-time options (pb200_set_option); the library never reads the environment
-    int64_t opt[PB200_OPT_COUNT] = {1, 1, 1, 1, -1, 0, 1, 1};
+    int64_t opt[PB200_OPT_COUNT] = {1, 1, 1, 1, -1, 0, 1, 1, 2};
 };
 
 static int fail(pb200_ctx* c, int code, const char* fmt, ...) {
@@ -224,8 +224,9 @@ int pb200_create(int device, pb200_ctx** out) {
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_scene, sizeof(DevScene));
-    if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_oob, 32);   // [0] out-of-grid flag, [8..16) active records, [16..24) thick (warp, chord) pairs of the run
-    if (e == cudaSuccess) e = cudaMemset(c->d_oob, 0, 32);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_oob, 64);   // [0] out-of-grid flag, [8..16) active records, [16..24) thick (warp, chord) pairs of the run,
+                                                                 // [24..32) tile counter of kernel (a), [32..40) (chord, narrow window) pairs of the run
+    if (e == cudaSuccess) e = cudaMemset(c->d_oob, 0, 64);
     if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_exp_tab, (kExpTabEntries + kExpBigEntries + 2 * kLogTabEntries) * sizeof(double));
     if (e == cudaSuccess) {
         double tab[kExpTabEntries];
@@ -296,6 +297,7 @@ int pb200_set_option(pb200_ctx* c, int option, int64_t value) {
     if (option < 0 || option >= PB200_OPT_COUNT) return fail(c, PB200_ERR_INVALID, "pb200_set_option: unknown option %d", option);
     const bool ok = option == PB200_OPT_SORT ? (value >= -1 && value <= 1)
                   : option == PB200_OPT_MIN_TILES ? (value >= 1 && value <= (1 << 20))
+                  : option == PB200_OPT_CENTRE ? (value >= 0 && value <= 2)
                   : (value == 0 || value == 1);
     if (!ok) return fail(c, PB200_ERR_INVALID, "pb200_set_option: value %lld out of range for option %d", (long long)value, option);
     c->opt[option] = value;
@@ -800,6 +802,7 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
         prm.min_tiles = (int)c->opt[PB200_OPT_MIN_TILES];   // tuning experiments only
         prm.culled = c->general_path ? 0 : 1;
         prm.thin_v = c->opt[PB200_OPT_THIN] ? 0.125 : 0.0;   // 0 (measurement only): every active sample through the table exp
+        prm.centre = c->opt[PB200_OPT_THIN] ? (int)c->opt[PB200_OPT_CENTRE] : 0;
         if (prm.min_tiles < 1) prm.min_tiles = 1;
     }
 
@@ -987,13 +990,14 @@ int collect_timing(pb200_ctx* c) {
 }
 
 int check_oob(pb200_ctx* c) {
-    unsigned long long st[4] = {0, 0, 0, 0};
+    unsigned long long st[5] = {0, 0, 0, 0, 0};
     PB_CUDA(c, cudaMemcpyAsync(st, c->d_oob, sizeof st, cudaMemcpyDeviceToHost, c->stream));
     PB_CUDA(c, cudaStreamSynchronize(c->stream));
     const int flag = (int)(st[0] & 0xffffffffull);
     if (c->last.executed_samples < 0) {
         c->last.executed_samples = (int64_t)st[1] * c->last_n_wav_sel;
-        c->last.exp_samples = (int64_t)st[2] * 32 * c->last_wpt;   // a warp owns 32 * WPT wavelengths
+        c->last.exp_samples = (int64_t)st[2] * 32 * c->last_wpt   // a warp owns 32 * WPT wavelengths
+                              + (int64_t)st[4];                    // narrow sorted windows: one exp per (chord, window)
     }
     if (c->mol_stats_pending) {   // kernel (m), moment form: (live chord-pair blocks, items) x wavelengths
         unsigned long long ms[2] = {0, 0};

@@ -180,7 +180,7 @@ __device__ __forceinline__ void pb_chord_pre(const ScnConst& k, const double* __
 // n(x)/pre at one sample.  `rare`: see pb_exp2_class.  No branch, no call; the only selects are the final one and the
 // Jeans term of the hydrostatic law.  The heaviside of the reference (H(r - R), = 1 at r = R) shares the predicate
 // of the exp's underflow.
-template <int TYPE>
+template <int TYPE, bool SH = false>
 __device__ __forceinline__ double pb_term(const ScnConst& k, const double* __restrict__ big, const double2* __restrict__ ltab,
                                           double dx2, double cc, bool& rare) {
     const double kLog2e = pb_kc[6];
@@ -204,7 +204,7 @@ __device__ __forceinline__ double pb_term(const ScnConst& k, const double* __res
             yv = -(qa * qa) * kLog2e;
         }
     }
-    const double v = pb_exp2_core(big, yv);
+    const double v = pb_exp2_core<SH>(big, yv);
     const bool zero = pb_exp2_class(yv, rare) | dead;   // one predicate, one select
     return zero ? 0.0 : v;
 }
@@ -699,10 +699,13 @@ number_density_grid_kernel(const DevScene* __restrict__ scp, int scenario, doubl
 // A tile is 256 consecutive chords: one thread per chord hoists its constants (ScnConst of its phase, pre, cc) into
 // shared memory, then 8 lanes share a chord row and stride x two samples at a time -- each lane stores 16 bytes, the 8
 // lanes of a chord one 128-byte line, a warp four of them: no staging through shared memory, no partial sectors.
-// CTAs are persistent over the tiles.  8 B of HBM traffic per sample against ~23-27 FP64
-// instructions: which of the two binds depends on the scenario, see DESIGN.md.
+// CTAs are persistent over the tiles and keep the 4096-entry exp table (32 KB) and the x axis (up to kRowsMaxXs samples)
+// in shared memory: with the table in global memory the kernel waited on those loads (ncu: long_scoreboard the top
+// stall, issue slots 54 % busy).  8 B of HBM traffic per sample against ~24 FP64 and ~51 warp
+// instructions per 32 samples: the bound is instruction issue, see DESIGN.md.
 constexpr int kRowsCta = 256;
-template <int TYPE>
+constexpr int kRowsMaxXs = 512;
+template <int TYPE, bool XSH>
 __device__ __forceinline__ void pb_lane_rows(const ScnConst& k, const double* __restrict__ big, const double2* __restrict__ ltab,
                                              const double* __restrict__ xs, int n_x, int l8, double pre, double cc,
                                              double* __restrict__ row, bool vec) {
@@ -711,20 +714,36 @@ __device__ __forceinline__ void pb_lane_rows(const ScnConst& k, const double* __
     bool rare = false;
     if (vec) {
         for (int ix = 2 * l8; ix < n_x; ix += 2 * kColLanes) {     // n_x is even here
-            const double u = xs[ix] - k.cx, w = xs[ix + 1] - k.cx;
+            double x0, x1;
+            if constexpr (XSH) { const double2 xx = *reinterpret_cast<const double2*>(xs + ix); x0 = xx.x; x1 = xx.y; }
+            else { x0 = xs[ix]; x1 = xs[ix + 1]; }
+            const double u = x0 - k.cx, w = x1 - k.cx;
             const double d0 = u * u, d1 = w * w;
-            double t0 = pb_term<TYPE>(k, big, ltab, d0, cc, rare);
-            double t1 = pb_term<TYPE>(k, big, ltab, d1, cc, rare);
+            double t0 = pb_term<TYPE, true>(k, big, ltab, d0, cc, rare);
+            double t1 = pb_term<TYPE, true>(k, big, ltab, d1, cc, rare);
             if (rare) { t0 = pb_term_exact<TYPE>(k, ltab, d0, cc); t1 = pb_term_exact<TYPE>(k, ltab, d1, cc); rare = false; }
             *reinterpret_cast<double2*>(row + ix) = make_double2(pre * t0, pre * t1);
         }
     } else {
         for (int ix = l8; ix < n_x; ix += kColLanes) {
             const double u = xs[ix] - k.cx, d0 = u * u;
-            double t0 = pb_term<TYPE>(k, big, ltab, d0, cc, rare);
+            double t0 = pb_term<TYPE, true>(k, big, ltab, d0, cc, rare);
             if (rare) { t0 = pb_term_exact<TYPE>(k, ltab, d0, cc); rare = false; }
             row[ix] = pre * t0;
         }
+    }
+}
+
+template <bool XSH>
+__device__ __forceinline__ void pb_lane_rows_any(const ScnConst& k, const double* __restrict__ big, const double2* __restrict__ ltab,
+                                                 const double* __restrict__ xs, int n_x, int l8, double pre, double cc,
+                                                 double* __restrict__ row, bool vec) {
+    switch (k.type) {
+        case PB200_SCN_BAROMETRIC: pb_lane_rows<PB200_SCN_BAROMETRIC, XSH>(k, big, ltab, xs, n_x, l8, pre, cc, row, vec); break;
+        case PB200_SCN_HYDROSTATIC: pb_lane_rows<PB200_SCN_HYDROSTATIC, XSH>(k, big, ltab, xs, n_x, l8, pre, cc, row, vec); break;
+        case PB200_SCN_POWERLAW: pb_lane_rows<PB200_SCN_POWERLAW, XSH>(k, big, ltab, xs, n_x, l8, pre, cc, row, vec); break;
+        case PB200_SCN_TORUS: pb_lane_rows<PB200_SCN_TORUS, XSH>(k, big, ltab, xs, n_x, l8, pre, cc, row, vec); break;
+        default: break;
     }
 }
 
@@ -733,21 +752,30 @@ number_density_rows_kernel(const DevScene* __restrict__ scp, int scenario, doubl
                            unsigned long long* __restrict__ next_tile) {
     const DevScene& sc = *scp;
     const DevScenario& S = sc.scen[scenario];
+    extern __shared__ __align__(16) double s_dyn[];   // exp table [kExpBigEntries] | x axis [n_x] (n_x <= kRowsMaxXs)
     __shared__ ScnConst s_k[kRowsCta];
     __shared__ double s_pre[kRowsCta], s_cc[kRowsCta];
     __shared__ long long s_tile;
     const int tid = threadIdx.x, grp = tid / kColLanes, l8 = tid % kColLanes;
     const int64_t n_chords = (int64_t)sc.M * sc.n_orb;
     const int n_x = sc.n_x;
-    const double* __restrict__ xs = sc.x;
-    const double* __restrict__ big = sc.exp_tab + kExpTabEntries;
+    const double* __restrict__ gbig = sc.exp_tab + kExpTabEntries;
     const double2* __restrict__ ltab = reinterpret_cast<const double2*>(sc.exp_tab + kExpTabEntries + kExpBigEntries);
     const bool vec = (n_x % 2 == 0) && ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
+    const bool xsh = n_x <= kRowsMaxXs;
+    double* s_big = s_dyn;
+    double* s_xs = s_dyn + kExpBigEntries;
+    {
+        const double2* src = reinterpret_cast<const double2*>(gbig);
+        double2* dst = reinterpret_cast<double2*>(s_big);
+        for (int i = tid; i < kExpBigEntries / 2; i += kRowsCta) dst[i] = __ldg(src + i);
+        if (xsh) for (int i = tid; i < n_x; i += kRowsCta) s_xs[i] = sc.x[i];
+    }
     // persistent CTAs; the first tile is the CTA's own, further ones come from a counter (rows differ in cost: a torus row
     // off the plane is all zeros), so the CTAs finish together
     for (int64_t tile = blockIdx.x; tile < n_tiles;) {
         const int64_t c0 = tile * kRowsCta, c = c0 + tid;
-        __syncthreads();   // the previous tile's constants are no longer read
+        __syncthreads();   // the previous tile's constants are no longer read (first pass: the tables are complete)
         if (tid == 0) s_tile = (long long)gridDim.x + (long long)atomicAdd(next_tile, 1ull);
         if (c < n_chords) {
             const int m = (int)(c / sc.n_orb), p = (int)(c % sc.n_orb);
@@ -755,7 +783,7 @@ number_density_rows_kernel(const DevScene* __restrict__ scp, int scenario, doubl
             const double rho = sc.rho[irho];
             const ScnConst k = pb_scn_const(S, p);
             double pre, cc;
-            pb_chord_pre(k, big, __dmul_rn(rho, sc.sin_phi[iphi]), __dmul_rn(rho, sc.cos_phi[iphi]), pre, cc);
+            pb_chord_pre(k, gbig, __dmul_rn(rho, sc.sin_phi[iphi]), __dmul_rn(rho, sc.cos_phi[iphi]), pre, cc);
             s_k[tid] = k;
             s_pre[tid] = pre;
             s_cc[tid] = cc;
@@ -771,13 +799,8 @@ number_density_rows_kernel(const DevScene* __restrict__ scp, int scenario, doubl
                 else for (int ix = l8; ix < n_x; ix += kColLanes) row[ix] = 0.0;
                 continue;
             }
-            switch (k.type) {
-                case PB200_SCN_BAROMETRIC: pb_lane_rows<PB200_SCN_BAROMETRIC>(k, big, ltab, xs, n_x, l8, pre, cc, row, vec); break;
-                case PB200_SCN_HYDROSTATIC: pb_lane_rows<PB200_SCN_HYDROSTATIC>(k, big, ltab, xs, n_x, l8, pre, cc, row, vec); break;
-                case PB200_SCN_POWERLAW: pb_lane_rows<PB200_SCN_POWERLAW>(k, big, ltab, xs, n_x, l8, pre, cc, row, vec); break;
-                case PB200_SCN_TORUS: pb_lane_rows<PB200_SCN_TORUS>(k, big, ltab, xs, n_x, l8, pre, cc, row, vec); break;
-                default: break;
-            }
+            if (xsh) pb_lane_rows_any<true>(k, s_big, ltab, s_xs, n_x, l8, pre, cc, row, vec);
+            else pb_lane_rows_any<false>(k, s_big, ltab, sc.x, n_x, l8, pre, cc, row, vec);
         }
         tile = s_tile;   // written before the barrier in the middle of this iteration, read after the row loop
     }
@@ -872,12 +895,18 @@ void launch_number_density_grid(const DevScene* d_scene, int64_t n_chords, int s
 }
 void launch_number_density_thread(const DevScene* d_scene, int64_t n_chords, int n_x, int scenario, double* out, int sm_count,
                                   unsigned long long* next_tile, cudaStream_t st) {
-    (void)n_x;
     const int64_t n_tiles = (n_chords + kRowsCta - 1) / kRowsCta;
     const int64_t slots = (int64_t)sm_count * 4;     // resident CTAs (64 registers x 256 threads)
     const int64_t ctas = n_tiles < slots ? n_tiles : slots;
     cudaMemsetAsync(next_tile, 0, sizeof(unsigned long long), st);
-    number_density_rows_kernel<<<(unsigned)(ctas > 0 ? ctas : 1), kRowsCta, 0, st>>>(d_scene, scenario, out, n_tiles, next_tile);
+    const size_t smem = (kExpBigEntries + (n_x <= kRowsMaxXs ? ((n_x + 1) & ~1) : 0)) * sizeof(double);
+    static bool attr_set = false;      // 32 KB of table + the static arrays exceed the 48 KB default
+    if (!attr_set) {
+        cudaFuncSetAttribute(number_density_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)((kExpBigEntries + kRowsMaxXs) * sizeof(double)));
+        attr_set = true;
+    }
+    number_density_rows_kernel<<<(unsigned)(ctas > 0 ? ctas : 1), kRowsCta, smem, st>>>(d_scene, scenario, out, n_tiles, next_tile);
 }
 void launch_number_density_chords(const DevScene* d_scene, int scenario, int64_t n, const double* y,
                                   const double* z, const double* cx, const double* cy, const double* amp,

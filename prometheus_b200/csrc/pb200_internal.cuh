@@ -143,6 +143,7 @@ struct TransitParams {
     int min_tiles;        // kernel (c'): least number of active tiles a working CTA takes
     int culled;           // 1: kernel (c') (w0 / n_act valid), 0: kernel (m)
     double thin_v;        // kernel (c'): scaled-tau threshold of the thin path (kThinV; 0 switches it off)
+    int centre;           // kernel (c'), sorted windows: 0 no Taylor sums about the centre, 1 whole windows, 2 also per 32-wavelength group
     int win;              // kernel (c'): wavelengths per warp window (32 * WPT)
     int n_win;            // windows per phase = ceil(n_wav_sel / win)
     int* order;           // [n_phase][n_win] window indices sorted by decreasing optical thickness (compact_kernel)

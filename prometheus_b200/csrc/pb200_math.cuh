@@ -245,12 +245,14 @@ __device__ __forceinline__ double pb_rsqrt_nb(double s) {
     return fma(y * e, fma(e, 0.375, 0.5), y);
 }
 
+// SH: `big` is a copy of the table in shared memory (a persistent CTA loads it once) instead of the one in global memory
+template <bool SH = false>
 __device__ __forceinline__ double pb_exp2_core(const double* __restrict__ big, double y) {
     const double t = fma(y, 4096.0, kExpMagic);
     const int k = __double2loint(t);
     const double kf = t - kExpMagic;
     const double r = fma(y, 4096.0, -kf);
-    const double T0 = __ldg(big + (k & (kExpBigEntries - 1)));
+    const double T0 = SH ? big[k & (kExpBigEntries - 1)] : __ldg(big + (k & (kExpBigEntries - 1)));
     const double T = __hiloint2double(__double2hiint(T0) + (k << kExpBigShift), __double2loint(T0));
     double p = fma(r, pb_kc[7], pb_kc[8]);
     p = fma(p, r, pb_kc[9]);

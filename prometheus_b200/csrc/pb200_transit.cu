@@ -75,7 +75,7 @@ __global__ void __launch_bounds__(256) sigma_phase_kernel(const DevScene* __rest
     const bool live = wi < prm.n_wav_sel;
     const int pi = blockIdx.y, p = prm.phase_lo + pi;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) { sc.stat[1] = 0ull; sc.stat[2] = 0ull; }   // run statistics
+    if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) { sc.stat[1] = 0ull; sc.stat[2] = 0ull; sc.stat[4] = 0ull; }   // run statistics
     const double lam = live ? __ldg(sc.wavelength + pb_wav_index(prm, wi)) : 0.0;
     const int wpw = prm.win / 32;   // warps per window: this 256-wavelength CTA covers 8 / wpw whole windows
     for (int a = 0; a < sc.n_abs; ++a) {   // absorber = the atomic constituents of one scenario (DevScene::n_abs)
@@ -171,8 +171,9 @@ constexpr double kThinHiV = 0.1 * kExpBigScale;
 constexpr double kOpaqueV = 50.0 * kExpBigScale;
 struct ThinHi {
     double a[9] = {};
-    __device__ __forceinline__ void add(double w0, double N) {
-        const double t = N * kExpBigC1;
+    __device__ __forceinline__ void add(double w0, double N) { add_scaled(w0, N * kExpBigC1); }
+    // a[k] += w0 t^k / k!
+    __device__ __forceinline__ void add_scaled(double w0, double t) {
         double term = w0;
         a[0] += term;
         term *= t;                   a[1] += term;
@@ -184,16 +185,16 @@ struct ThinHi {
         term *= t * (1.0 / 7.0);     a[7] += term;
         term *= t * 0.125;           a[8] += term;
     }
+    __device__ __forceinline__ double value(double n) const {
+        double q = fma(a[8], n, a[7]);
+        q = fma(q, n, a[6]); q = fma(q, n, a[5]); q = fma(q, n, a[4]); q = fma(q, n, a[3]);
+        q = fma(q, n, a[2]); q = fma(q, n, a[1]); q = fma(q, n, a[0]);
+        return q;
+    }
     template <int WPT>
     __device__ __forceinline__ void finish(const double (&nsig)[WPT], double (&acc)[WPT]) const {
 #pragma unroll
-        for (int j = 0; j < WPT; ++j) {
-            const double n = nsig[j];
-            double q = fma(a[8], n, a[7]);
-            q = fma(q, n, a[6]); q = fma(q, n, a[5]); q = fma(q, n, a[4]); q = fma(q, n, a[3]);
-            q = fma(q, n, a[2]); q = fma(q, n, a[1]); q = fma(q, n, a[0]);
-            acc[j] += q;
-        }
+        for (int j = 0; j < WPT; ++j) acc[j] += value(nsig[j]);
     }
 };
 
@@ -327,6 +328,50 @@ __device__ __forceinline__ void transit_tile_sorted(uint32_t stage, const double
     }
 }
 
+// NARROW sigma-sorted windows.  For one absorber R(p, w) depends on the wavelength only through sigma(p, w):
+//     sum_m w_m exp(-N_m sigma) =: f_p(sigma),   a smooth function of ONE variable.
+// In a sorted window the cross sections lie in [s_lo, s_hi]; with the centre s_c, the half width h and
+// sigma_j = s_c + h x_j, |x_j| <= 1:
+//     w exp(-N sigma_j) = [w exp(-N s_c)] * sum_k (-N h x_j)^k / k!  =  sum_k x_j^k * [E u^k / k!],  E = w exp(-N s_c), u = -N h,
+// so the window needs per chord ONE table exp and the nine running sums A_k = sum_m E_m u_m^k / k! (lane-parallel, 26 FP64
+// instructions per chord and window) instead of 256 samples through the exp (1536), and per wavelength a Horner
+// evaluation at the end.  Truncation after k = 8 with tau_c = N s_c and eps = h / s_c:  the remainder of a chord is below
+// w e^{-tau_c (1 - eps)} (tau_c eps)^9 / 9!  <=  w (9 eps / (e (1 - eps)))^9 / 9!   (maximum over tau_c, at tau_c = 9 / (1 - eps));
+// eps <= 1/40 (kCentreEps) gives 6.3e-16 w if EVERY chord sat at that optical depth -- a few units in the last place of
+// R for any distribution of column densities, so the test needs nothing but the window's own sigma range.  Opaque chords (tau > 50 on the whole window) are skipped as in
+// the other sorted windows, which also keeps the table exp inside its unclamped range (tau_c <= 50 (1 + 2 eps)).
+// The sums live in the registers of ThinHi (the two expansions never occur in the same window).
+constexpr double kCentreEps = 1.0 / 40.0;
+// GROUPS = false: the window as a whole is narrow; the warps split the chords of the tile (one chord per lane).
+// GROUPS = true: the window is not, but each of its 32-wavelength groups is (line wings: sigma changes by a few per cent
+// across 256 sorted wavelengths, by a few per mille across 32): warp g owns group g -- centre, half width and opaque
+// limit of ITS wavelengths -- and walks all 256 chords of the tile, 8 per lane: 8 x 26 FP64 instructions per chord
+// and window, still 7 times fewer than the table exp per sample.
+template <int NWARPS, bool GROUPS>
+__device__ __forceinline__ void transit_tile_centre(uint32_t stage, uint32_t tab_base, int wid, int lane, double nc, double hu,
+                                                    double smin0, ThinHi& hi, int& n_centre) {
+    static_assert(kChordTile / NWARPS == 32, "one chord per lane");
+    constexpr uint32_t kRecBytes = pb_rec_stride(1) * sizeof(double);   // {w, w c1, w c2, N}
+#pragma unroll 2
+    for (int i = 0; i < (GROUPS ? NWARPS : 1); ++i) {
+        const uint32_t rec = stage + (uint32_t)(lane * NWARPS + (GROUPS ? i : wid)) * kRecBytes;
+        double w0, w1, w2, N;
+        lds_v2f64(rec, w0, w1);
+        lds_v2f64(rec + 16, w2, N);
+        const bool live = !(N * smin0 > kOpaqueV);     // padding records have w = 0 and N = 0: they add exact zeros
+        if (live) {
+            const double t = fma(N, nc, kExpMagic);                                    // -tau_c in scaled units
+            const double r = fma(N, nc, -(t - kExpMagic));
+            const double T = pb_exp_big_load(tab_base, __double2loint(t));
+            double q = fma(r, w2, w1);
+            q = fma(q, r, w0);
+            hi.add_scaled(T * q, N * hu);                                              // E = w exp(-tau_c), u = N h ln2/4096
+        }
+        const unsigned took = __ballot_sync(0xffffffffu, live);   // every lane votes (not inside the conditional below)
+        n_centre += (lane == 0) ? __popc(took) : 0;
+    }
+}
+
 // S atomic constituents (compile time), WPT wavelengths per thread, THREADS threads per CTA.
 // One CTA = one wavelength window (32 * WPT consecutive wavelengths) x one phase x one chord-axis split.
 // All warps of the CTA hold the SAME wavelengths (lane = fastest index, j = 32-wavelength group) and split
@@ -412,6 +457,36 @@ transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
         smin0 = any_bad ? 0.0 : mn;
     }
     const double hi_v = (prm.thin_v > 0.0) ? kThinHiV : 0.0;
+    // narrow window (transit_tile_centre): centre and half width of the window's nsig (all <= 0 up to rounding of sigma = 0)
+    bool narrow = false;
+    double nc = 0.0, hw = 0.0;
+    int n_centre = 0;
+    bool groups = false;   // every 32-wavelength group is narrow about its own centre: warp g takes group g
+    double smin_c = smin0;
+    if constexpr (HI) {
+        const double span = smw[0] - smin0, mid2 = smw[0] + smin0;
+        narrow = prm.centre >= 1 && !any_bad && span <= kCentreEps * mid2 && !all_thin;   // inf / NaN compare false
+        nc = -0.5 * mid2;
+        hw = 0.5 * span;
+        if (!narrow && prm.centre >= 2 && !any_bad && !all_thin) {
+            static_assert(WPT == NWARPS, "one 32-wavelength group per warp");
+            bool ok = true;
+#pragma unroll
+            for (int j = 0; j < WPT; ++j) {
+                const double a = fabs(nsig[0][j]);
+                double mx = a, mn = (win_lo + j * 32 + lane < prm.n_wav_sel) ? a : __longlong_as_double(0x7ff0000000000000ll);
+#pragma unroll
+                for (int d = 16; d > 0; d >>= 1) {
+                    mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, d));
+                    mn = fmin(mn, __shfl_xor_sync(0xffffffffu, mn, d));
+                }
+                ok = ok && (mx - mn <= kCentreEps * (mx + mn));   // a group without live wavelengths: inf, not narrow
+                if (j == wid) { nc = -0.5 * (mx + mn); hw = 0.5 * (mx - mn); smin_c = mn; }
+            }
+            groups = narrow = ok;    // the same for every warp of the CTA (all of them looked at all eight groups)
+            if (!ok) { nc = -0.5 * mid2; hw = 0.5 * span; smin_c = smin0; }
+        }
+    }
 
     if (n_tiles > 0 && !all_thin) {
         if (tid == 0) {
@@ -443,7 +518,12 @@ transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
             if (tid == 0 && t + 1 < n_tiles) issue(t + 1, stage ^ 1);
             mbar_wait(&full_bar[stage], (t >> 1) & 1);
             const uint32_t sw = stages_addr + stage * kStageBytes;
-            if constexpr (S <= 2) {   // one or two absorbers: lane-parallel per-chord decisions (sorted or not)
+            if (HI && narrow) {
+                if constexpr (HI) {
+                    if (groups) transit_tile_centre<NWARPS, true>(sw, tab_base, wid, lane, nc, hw * kExpBigC1, smin_c, hi, n_centre);
+                    else transit_tile_centre<NWARPS, false>(sw, tab_base, wid, lane, nc, hw * kExpBigC1, smin_c, hi, n_centre);
+                }
+            } else if constexpr (S <= 2) {   // one or two absorbers: lane-parallel per-chord decisions (sorted or not)
                 if (clamp) transit_tile_sorted<S, WPT, true, NWARPS, HI>(sw, nsig, acc, tab_base, smw, thin, wid, lane, prm.thin_v, hi_v, smin0, hi);
                 else transit_tile_sorted<S, WPT, false, NWARPS, HI>(sw, nsig, acc, tab_base, smw, thin, wid, lane, prm.thin_v, hi_v, smin0, hi);
             } else {
@@ -464,7 +544,29 @@ transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
             }
         }
         thin.finish(nsig, acc);
-        if constexpr (HI) hi.finish(nsig[0], acc);
+        if constexpr (HI) {
+            if (narrow) {   // Horner in x_j = (nsig_j - centre) / half width
+                const double inv_h = hw > 0.0 ? 1.0 / hw : 0.0;
+                double xs[WPT];
+#pragma unroll
+                for (int j = 0; j < WPT; ++j) xs[j] = (nsig[0][j] - nc) * inv_h;
+                if (groups) {   // this warp's sums belong to its own group of wavelengths only
+                    double x = 0.0;
+#pragma unroll
+                    for (int j = 0; j < WPT; ++j)
+                        if (j == wid) x = xs[j];
+                    const double q = hi.value(x);
+#pragma unroll
+                    for (int j = 0; j < WPT; ++j)
+                        if (j == wid) acc[j] += q;
+                } else {
+                    hi.finish(xs, acc);
+                }
+                if (lane == 0 && n_centre) atomicAdd(sc.stat + 4, (unsigned long long)n_centre);
+            } else {
+                hi.finish(nsig[0], acc);
+            }
+        }
         if (lane == 0 && thin.thick) atomicAdd(sc.stat + 2, (unsigned long long)thin.thick);
     } else if (n_tiles > 0 && wid == 0 && split == 0) {
         // every chord of the phase is thin in this window: the chord sums are the phase totals

@@ -154,7 +154,9 @@ def test_steep_molecular_table_takes_the_per_record_form(nist_rows):
 # ---- C5: columns chosen by the sigma-sorted kernel's own per-window decisions -------------------------------------
 def test_c5_regime_boundary_columns_against_oracle(nist_rows):
     """The sorted variant of kernel (c') decides per (chord, window of 256 sorted wavelengths): order-2 expansion below
-    tau = 2.1e-5, order-8 below 0.1, skipped above 50, table exp between (pb200_transit.cu:172-205, :296-302).  The
+    tau = 2.1e-5, order-8 below 0.1, skipped above 50, table exp between (pb200_transit.cu: ThinSums, ThinHi,
+    transit_tile_sorted) -- and, where a window's (or each 32-wavelength group's) sigma spread is below 1/40, one exp per chord feeding Taylor sums about the
+    window's centre (transit_tile_centre).  The
     boundaries sit at intermediate sigma, where a "deepest + strided" pick does not look: take, for two phases, the
     first and the last window in which each regime occurs, read back from the device's own sort order."""
     ctx = host.get_context(0)
@@ -178,18 +180,28 @@ def test_c5_regime_boundary_columns_against_oracle(nist_rows):
         n_win = -(-n_wav // 256)
         w = np.concatenate([a, np.full(n_win * 256 - n_wav, np.nan)]).reshape(n_win, 256)
         smw, smin = np.nanmax(w, axis=1), np.nanmin(w, axis=1)
+        narrow = (smw - smin) <= (smw + smin) / 40.0      # kCentreEps: Taylor sums about the window's centre (transit_tile_centre)
+        with np.errstate(invalid="ignore"):
+            g = w.reshape(n_win, 8, 32)                    # warp g of the CTA owns the window's g-th group of 32 sorted wavelengths
+            gmx, gmn = np.nanmax(g, axis=2), np.nanmin(g, axis=2)
+            by_group = np.all((gmx - gmn) <= (gmx + gmn) / 40.0, axis=1) & ~np.isnan(g).any(axis=(1, 2))
+        needs_exp = (N_hi * smw >= hi_v) & (N_lo * smin <= opaque_v)
         regimes = {
             "thin2": N_lo * smw < thin_v,
             "thin8": (N_lo * smw < hi_v) & (N_hi * smw >= thin_v),
             "opaque": N_hi * smin > opaque_v,
-            "exp": (N_hi * smw >= hi_v) & (N_lo * smin <= opaque_v),
+            "exp": needs_exp & ~narrow & ~by_group,        # line cores: per-sample table exp
+            "centre": needs_exp & narrow,                  # narrow windows: one exp per (chord, window)
+            "groups": needs_exp & ~narrow & by_group,      # narrow 32-wavelength groups: one exp per (chord, group)
         }
         for name, mask in regimes.items():
             idx = np.flatnonzero(mask)
+            if name == "exp" and not idx.size:
+                continue                                   # every line core of the phase resolved by its groups
             assert idx.size, f"phase {p}: no window in regime {name}"
-            for win in (idx[0], idx[-1]):
-                for pos in (win * 256, min(win * 256 + 255, n_wav - 1)):      # both ends of the window
-                    sel.append(int(perm[p, pos]))
+            for win in (idx[0], idx[len(idx) // 2], idx[-1]):
+                for pos in (win * 256, win * 256 + 128, win * 256 + 255):     # both ends (|x| = 1) and the middle of the window
+                    sel.append(int(perm[p, min(pos, n_wav - 1)]))
     sel = np.unique(np.array(sel))
     assert sel.size >= 16
     inputs = oracle_inputs(spec, nist_rows)

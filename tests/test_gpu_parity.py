@@ -475,6 +475,10 @@ def test_sigma_sorted_windows_leave_R_unchanged(name, nist_rows, golden, monkeyp
     with ctx.options(sort=1, thin=0):                                          # every active sample through the exp, sorted
         R_exp, _ = ctx.run(0, info["n_orb"], 0, info["n_wav"])
     assert np.max(np.abs(out["0"] - out["1"])) < 5e-14 and np.max(np.abs(R_exp - out["0"])) < 5e-14
+    for centre in (0, 1):     # Taylor sums about the centre of narrow windows / groups: off, whole windows only (default: 2)
+        with ctx.options(sort=1, centre=centre):
+            R_c, _ = ctx.run(0, info["n_orb"], 0, info["n_wav"])
+        assert np.max(np.abs(R_c - out["0"])) < 5e-14, centre
     g = golden(name)
     ok, worst = excess_depth_ok(out["1"], g["R"], g["R0"])
     assert ok, f"{name}: err/bound {worst}"
@@ -500,6 +504,33 @@ def test_sigma_sorted_windows_with_block_cyclic_tiles(nist_rows, monkeypatch):
             ctx.run_scatter(0, n_orb, 256, 3, r, full.ctypes.data, n_wav)
         ctx.synchronize()
     assert n_wav > 3 * 256 and np.max(np.abs(full - R_ref)) < 5e-14
+
+
+def test_narrow_sorted_windows_as_taylor_sums(nist_rows):
+    """On a fine wavelength grid most sorted windows (256 wavelengths) or their 32-wavelength groups span less than 1/40 in
+    sigma: kernel (c') then needs one exp per (chord, window / group) and nine Taylor sums about the centre
+    (transit_tile_centre).  Same R as the per-sample exp and as the unsorted run; far fewer exp evaluations."""
+    from prometheus_b200 import scene
+    ctx = host.get_context(0)
+    spec = workloads.get("C4s")
+    spec["wavelength"] = list(workloads.get("C4")["wavelength"])      # the high-resolution grid of C4: 31 969 wavelengths
+    tr = builder.build_transit(spec, nist_rows=nist_rows)
+    sc, keep, info = scene.flatten(tr)
+    ctx.set_scene(sc, keep)
+    n_orb, n_wav = info["n_orb"], info["n_wav"]
+    assert n_wav > 8192
+    with ctx.options(sort=0):
+        R_ref, _ = ctx.run(0, n_orb, 0, n_wav)
+    R, exps = {}, {}
+    for centre in (0, 1, 2):
+        with ctx.options(sort=1, centre=centre):
+            R[centre], t = ctx.run(0, n_orb, 0, n_wav)
+            exps[centre] = t["exp_samples"]
+        assert np.max(np.abs(R[centre] - R_ref)) < 5e-14, centre
+    assert exps[2] <= exps[1] <= exps[0] and exps[2] < 0.5 * exps[0], exps
+    with ctx.options(sort=1):                          # a ragged tile and a phase subset through the same path
+        tile, _ = ctx.run(1, 2, 3, n_wav - 11)
+    assert np.max(np.abs(tile - R[2][1:2, 3:n_wav - 11])) < 5e-14
 
 
 def test_power_law_with_non_positive_exponent_is_not_culled(nist_rows):
