@@ -365,6 +365,7 @@ def parity_check(spec, tr, R, n_cols=8):
 # ------------------------------------------------------------------------------------------------
 FLOPS_MOMENT_ITEM = 33.0      # kernel (m), per (item, wavelength): d = V1 - V0 (1), fma(tc, d, V0) (2), table exp (12),
                               # Horner of 8 moments (16), e * p (1), accumulate (1)
+FLOPS_CENTRE_PAIR = 37.0      # kernel (c'), sigma cells, per (chord, cell): table exp (11), E = T q (1), u (1), nine sums (1 + 2 + 7 x 3)
 FLOPS_MOMENT_BLOCK = 15.0     # kernel (m), per (chord pair, wavelength) besides its items and atoms: table exp (12) + clamp,
                               # subtract the offset sum (1), weight * exp accumulate (2)
 
@@ -552,6 +553,15 @@ def workload_roofline(name, tr, info, timings, peak_tflops):
                              flops_per_block=FLOPS_MOMENT_BLOCK + 2.0 * n_abs,
                              traffic=recorded_traffic(name, "transit_moment_kernel"))
     fps = executed_flops_per_sample(n_abs)
+    pairs = float(np.mean([t.get("centre_pairs", 0) for t in timings]))
+    if pairs > 0.0:     # sigma cells (or narrow sorted windows): one table exp + the nine Taylor sums per (chord, cell)
+        flops = fps * (exp_s - pairs) + FLOPS_CENTRE_PAIR * pairs
+        return fp64_roofline("cell_moment_kernel + cell_eval_kernel (c': R tabulated per phase on sigma cells), production launch",
+                             flops, ms, peak_tflops, centre_pairs=pairs, flops_per_pair=FLOPS_CENTRE_PAIR,
+                             exp_samples=exp_s - pairs, flops_per_sample=fps, executed_samples=exe_s,
+                             note="the work no longer scales with the wavelength count: `executed_samples` (records x wavelengths) is what "
+                                  "the per-sample kernel would have walked; the launch is short and partly latency-bound, see DESIGN.md 6b",
+                             traffic=recorded_traffic(name, "cell_moment_kernel"))
     return fp64_roofline("transit_kernel (c'), production launch", fps * exp_s, ms, peak_tflops, exp_samples=exp_s,
                          flops_per_sample=fps, executed_samples=exe_s,
                          note="flops of the samples that take the table exp; thin-chord expansions and skipped (opaque) chords not counted",
@@ -606,22 +616,38 @@ def strong_scaling(name, torch, dist, ctx, flush, dev, rank, world, local, peak_
         res.update(ms_per_step=ms_one, ms_no_gather=ms_one, efficiency=1.0)
         R = whole.view(n_orb, n_wav).cpu().numpy()
     else:
-        if axis == "wavelength":     # this rank's chunk only needs the part of each sigma table its wavelengths reach
-            sc_r, keep_r, _ = scene.flatten(tr, wav_range=pbd.partition(n_wav, world)[rank])
-            ctx.set_scene(sc_r, keep_r)
-        st = pbd.ShardedTransit(n_orb, n_wav, None, axis, dev)
-        kern = []
-        st.compute_tile = pbd.tile_function(ctx, axis, world, rank, want_timing=True, sink=kern)
-        ms_ng = timed(lambda: st.run_device(gather=False), steps)
-        mine = {k: float(np.mean([t[k] for t in kern[warmup:]])) for k in ("column_ms", "transit_ms", "finalize_ms")}
-        st.compute_tile = pbd.tile_function(ctx, axis, world, rank)
+        def measure(axis):
+            if axis == "wavelength":     # this rank's chunk only needs the part of each sigma table its wavelengths reach
+                sc_r, keep_r, _ = scene.flatten(tr, wav_range=pbd.partition(n_wav, world)[rank])
+                ctx.set_scene(sc_r, keep_r)
+            else:
+                ctx.set_scene(sc, keep)
+            st = pbd.ShardedTransit(n_orb, n_wav, None, axis, dev)
+            kern = []
+            st.compute_tile = pbd.tile_function(ctx, axis, world, rank, want_timing=True, sink=kern)
+            ms_ng = timed(lambda: st.run_device(gather=False), steps)
+            mine = {k: float(np.mean([t[k] for t in kern[warmup:]])) for k in ("column_ms", "transit_ms", "finalize_ms")}
+            st.compute_tile = pbd.tile_function(ctx, axis, world, rank)
 
-        def step():
-            st.run_device(gather=True)
-            st.unpack_device()
-        ms_n = timed(step, steps)
-        per_rank = [None] * world
-        dist.all_gather_object(per_rank, mine)
+            def step():
+                st.run_device(gather=True)
+                st.unpack_device()
+            ms_n = timed(step, steps)
+            per_rank = [None] * world
+            dist.all_gather_object(per_rank, mine)
+            return st, {"axis": axis, "ms_per_step": ms_n, "ms_no_gather": ms_ng, "efficiency": ms_one / (world * ms_n),
+                        "efficiency_no_gather": ms_one / (world * ms_ng), "kernels_ms_per_rank": per_rank}
+        # atomic scenes: wavelength tiles dealt round-robin (every rank still walks every chord of every phase) or whole
+        # phases per rank (partitions ALL the work, but n_orb / N phases per rank may be uneven): measured both, the
+        # faster one is reported on top, the other under `other_axis`
+        axes = ["cyclic", "phase"] if (atomic and n_orb >= world) else [axis]
+        tried = [measure(ax) for ax in axes]
+        tried.sort(key=lambda t: t[1]["ms_per_step"])
+        st, best = tried[0]
+        axis = best["axis"]
+        if len(tried) > 1:
+            best["other_axis"] = {k: v for k, v in tried[1][1].items() if k != "kernels_ms_per_rank"}
+            st, _ = measure(axis)        # leaves the context and the buffers in the state of the reported axis
         state = {}
         wall = []
         for i in range(2 + 3):
@@ -632,9 +658,8 @@ def strong_scaling(name, torch, dist, ctx, flush, dev, rank, world, local, peak_
             wall.append((time.perf_counter() - t0) * 1e3)
         e2e = torch.tensor([float(np.mean(wall[2:]))], dtype=torch.float64, device=dev)
         dist.all_reduce(e2e, op=dist.ReduceOp.MAX)
-        res.update(ms_per_step=ms_n, ms_no_gather=ms_ng, efficiency=ms_one / (world * ms_n),
-                   efficiency_no_gather=ms_one / (world * ms_ng), kernels_ms_per_rank=per_rank,
-                   e2e_ms_per_call=float(e2e.item()), gather_bytes=int(n_orb * n_wav * 8))
+        res.update(best)
+        res.update(e2e_ms_per_call=float(e2e.item()), gather_bytes=int(n_orb * n_wav * 8))
         st.run_device(gather=True)
         R = st.to_host(0)
     if rank == 0:

@@ -133,6 +133,9 @@ typedef struct {
                                     Scenes with molecules (kernel (m), moment form): executed_samples =
                                     unblocked chord-pair blocks x wavelengths, exp_samples = moment
                                     items x wavelengths (one table exp + 8 FMAs each)         */
+    int64_t centre_pairs;        /* (chord, sigma cell) or (chord, narrow window / group) pairs that
+                                    fed Taylor sums about a centre (one table exp + 18 FP64
+                                    instructions each); they are also counted in exp_samples   */
 } pb200_timing;
 
 /* ---- retrieval batches ------------------------------------------------
@@ -183,8 +186,10 @@ typedef enum {
     PB200_OPT_MOL_RECORDS = 5,   /* 1: per-record form of kernel (m) instead of the moment form                   */
     PB200_OPT_ZEROCOPY = 6,      /* 1: pb200_run stores R straight into a page-locked result                      */
     PB200_OPT_MIN_TILES = 7,     /* least number of active chord tiles per working CTA of kernel (c') (>= 1)      */
-    PB200_OPT_CENTRE = 8,        /* sigma-sorted windows with a narrow sigma range as Taylor sums about their centre:
-                                    0 off, 1 whole windows (256 wavelengths), 2 also per 32-wavelength group      */
+    PB200_OPT_CENTRE = 8,        /* one absorber, where the sigma-sorted windows apply: 3 (default) no sort at all -- R(p, .)
+                                    tabulated per phase on a geometric grid of sigma cells (Taylor sums about each cell's
+                                    centre), one polynomial per wavelength; 0..2 sorted windows: 0 without, 1 with Taylor
+                                    sums about the centre of narrow windows (256 wavelengths), 2 also per 32-wavelength group */
     PB200_OPT_COUNT = 9
 } pb200_option;
 int pb200_set_option(pb200_ctx* ctx, int option, int64_t value);

@@ -18,10 +18,12 @@ echo "bench short rc=$?"
 timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $O/r02_launches_bench_C4.csv \
     python bench.py --steps 2 --warmup 3 --cpu-seconds 0 > $O/ncu_bench.log 2>&1
 echo "bench launch list rc=$?"
-run C4_production  "transit_kernel|column_cta|compact|sigma_phase|finalize|bucket" 12 C4 1
+run C4_production  "cell_|transit_kernel|column_cta|compact|sigma_phase|finalize|bucket" 12 C4 1
 run C4_bruteforce  "transit_kernel" 1 C4 1 cull=0 mirror=0 thin=0
 run C4_kernel_a    "number_density_rows" 1 C4 1 kernel_a
-run C5_production  "transit_kernel|column_cta|compact" 6 C5 1
+run C5_production  "cell_|transit_kernel|column_cta|compact|sigma_phase" 8 C5 1
+run C5_sorted      "transit_kernel" 1 C5 1 centre=2
+run C4_windows     "transit_kernel" 1 C4 1 sort=0
 run C2_production  "moment|column_cta|fout" 8 C2 1
 run C3_production  "transit_kernel|column_cta|compact" 6 C3 1
 run RET_batch64    "transit_kernel|column_cta|compact|lightcurve" 8 RET 1 batch=64

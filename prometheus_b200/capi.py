@@ -33,7 +33,7 @@ SERPENS_STATIC_MAX_CELLS = 1 << 21
 
 # pb200_option (include/prometheus_b200.h)
 OPT = {"cull": 0, "mirror": 1, "thin": 2, "group": 3, "sort": 4, "mol_records": 5, "zerocopy": 6, "min_tiles": 7, "centre": 8}
-OPT_DEFAULTS = {"cull": 1, "mirror": 1, "thin": 1, "group": 1, "sort": -1, "mol_records": 0, "zerocopy": 1, "min_tiles": 1, "centre": 2}
+OPT_DEFAULTS = {"cull": 1, "mirror": 1, "thin": 1, "group": 1, "sort": -1, "mol_records": 0, "zerocopy": 1, "min_tiles": 1, "centre": 3}
 
 SCN_BAROMETRIC, SCN_HYDROSTATIC, SCN_POWERLAW, SCN_TORUS, SCN_SERPENS = range(5)
 
@@ -109,7 +109,7 @@ class Timing(C.Structure):
     _fields_ = [("upload_ms", C.c_double), ("column_ms", C.c_double), ("transit_ms", C.c_double),
                 ("finalize_ms", C.c_double), ("download_ms", C.c_double),
                 ("launches", C.c_int64), ("samples", C.c_int64), ("executed_samples", C.c_int64),
-                ("exp_samples", C.c_int64)]
+                ("exp_samples", C.c_int64), ("centre_pairs", C.c_int64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

@@ -36,6 +36,9 @@ void launch_sigma_phase(const DevScene*, const TransitParams&, cudaStream_t);
 void launch_bucket_build(const DevScene*, int sm_count, cudaStream_t);
 cudaError_t launch_compact(const DevScene*, const TransitParams&, bool cull, bool small, cudaStream_t);
 void launch_finalize(const DevScene*, const TransitParams&, int sm_count, cudaStream_t);
+int cell_chord_splits(int sm_count, int n_phase, int n_tiles);
+size_t cell_scratch_bytes(int n_phase, int n_cs);
+cudaError_t launch_cells(const DevScene* d_scene, const TransitParams& prm, int n_cs, void* scratch, cudaStream_t st, int* n_launch);
 void launch_sigma_lookup(const double*, const double*, int64_t, double, const double*, int64_t, double*, int,
                          cudaStream_t);
 void launch_sigma_u(const DevScene*, int n_atoms, int n_orb, int64_t wav_lo, int64_t n_wav_sel, double* out, int,
@@ -137,7 +140,7 @@ struct pb200_ctx {
     const double* last_nsig_sorted = nullptr;
     int64_t last_sort_n = 0;
     // run-time options (pb200_set_option); the library never reads the environment
-    int64_t opt[PB200_OPT_COUNT] = {1, 1, 1, 1, -1, 0, 1, 1, 2};
+    int64_t opt[PB200_OPT_COUNT] = {1, 1, 1, 1, -1, 0, 1, 1, 3};
 };
 
 static int fail(pb200_ctx* c, int code, const char* fmt, ...) {
@@ -297,7 +300,7 @@ int pb200_set_option(pb200_ctx* c, int option, int64_t value) {
     if (option < 0 || option >= PB200_OPT_COUNT) return fail(c, PB200_ERR_INVALID, "pb200_set_option: unknown option %d", option);
     const bool ok = option == PB200_OPT_SORT ? (value >= -1 && value <= 1)
                   : option == PB200_OPT_MIN_TILES ? (value >= 1 && value <= (1 << 20))
-                  : option == PB200_OPT_CENTRE ? (value >= 0 && value <= 2)
+                  : option == PB200_OPT_CENTRE ? (value >= 0 && value <= 3)
                   : (value == 0 || value == 1);
     if (!ok) return fail(c, PB200_ERR_INVALID, "pb200_set_option: value %lld out of range for option %d", (long long)value, option);
     c->opt[option] = value;
@@ -747,6 +750,17 @@ bool want_sorted(const pb200_ctx* c, int n_phase, int64_t n_wav_sel) {
     return possible && n_wav_sel >= (1 << 13) && h.M >= (1 << 14);
 }
 
+// Sigma cells (pb200_transit.cu, cell_*_kernel): where the sorted windows would run and the expansions are allowed, R is
+// tabulated per phase on a grid of sigma cells instead -- no sort, work independent of the wavelength count.
+// There is no sort to pay for, so the sky grid may be small: the cells cost ~650 x 25 FP64 instructions per active chord
+// record whatever the wavelength count (C4, 9 000 chords per phase x 31 969 wavelengths: transit stage 0.100 -> 0.070 ms).
+bool want_cells(const pb200_ctx* c, int n_phase, int64_t n_wav_sel) {
+    const DevScene& h = c->h_scene;
+    if (c->opt[PB200_OPT_CENTRE] < 3 || c->opt[PB200_OPT_THIN] == 0 || c->general_path || h.n_abs != 1) return false;
+    if (c->opt[PB200_OPT_SORT] >= 0) return c->opt[PB200_OPT_SORT] == 1;
+    return n_wav_sel >= (1 << 13);
+}
+
 int check_scene(pb200_ctx* c) {
     if (!c) return PB200_ERR_INVALID;
     if (!c->has_scene) return fail(c, PB200_ERR_NO_SCENE, "no scene: call pb200_set_scene first");
@@ -789,6 +803,7 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     // (kernel (m) pays its prologue -- table searches and the V columns of every thread -- once per CTA: few, long CTAs)
     // (the sigma-sorted windows differ in cost by orders of magnitude -- a window in the tau ~ 1 band walks every chord
     // through the exp, most others are decided per chord without one: more, shorter CTAs keep the tail short)
+    const bool cells = want_cells(c, n_phase, n_wav_sel);
     const int per_sm = (!c->general_path && want_sorted(c, n_phase, n_wav_sel)) ? 64 : 16;
     int64_t want = ((int64_t)c->sm_count * per_sm + ctas - 1) / ctas;
     // at least 4 tiles per CTA of kernel (c'), 2 of kernel (m) (whose tiles are ~30 us of work each: with mirror pairing
@@ -796,8 +811,10 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     const int min_tiles_per_cta = c->general_path ? 2 : 4;
     if (want > n_tiles / min_tiles_per_cta) want = n_tiles / min_tiles_per_cta;
     if (want < 1) want = 1;
+    if (cells) want = 1;    // cell_eval_kernel writes R itself: no partial sums, no finalize_kernel
     prm.tiles_per_split = (int)((n_tiles + want - 1) / want);
     prm.n_split = (n_tiles + prm.tiles_per_split - 1) / prm.tiles_per_split;
+    const int n_cs = cells ? cell_chord_splits(c->sm_count, n_phase, n_tiles) : 0;
     {
         prm.min_tiles = (int)c->opt[PB200_OPT_MIN_TILES];   // tuning experiments only
         prm.culled = c->general_path ? 0 : 1;
@@ -813,17 +830,18 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     prm.n_win = (int)((n_wav_sel + prm.win - 1) / prm.win);
     const size_t order_bytes = c->general_path ? 0 : (((size_t)n_phase * prm.n_win * sizeof(int) + 255) & ~size_t(255));
     const size_t winmax_bytes = c->general_path ? 0 : (size_t)h.n_abs * n_phase * prm.n_win * sizeof(double);
-    const bool sorted = want_sorted(c, n_phase, n_wav_sel);
+    const bool sorted = !cells && want_sorted(c, n_phase, n_wav_sel);
+    const size_t cell_bytes = cells ? ((cell_scratch_bytes(n_phase, n_cs) + 255) & ~size_t(255)) : 0;
     const size_t al = 255;
     const size_t sort_temp = sorted ? ((sigma_sort_temp_bytes(n_out) + al) & ~al) : 0;
     const size_t sort_bytes = sorted ? (size_t)n_out * (8 + 8 + 8 + 4 + 4) + 5 * 256 + sort_temp : 0;
-    int rc = ensure_scratch(c, r_bytes + part_bytes + nsig_bytes + order_bytes + winmax_bytes + sort_bytes + 512);
+    int rc = ensure_scratch(c, r_bytes + part_bytes + nsig_bytes + order_bytes + winmax_bytes + sort_bytes + cell_bytes + 1024);
     if (rc) return rc;
     prm.R = R_in_scratch ? c->scratch : R_dev;
     prm.partial = reinterpret_cast<double*>(reinterpret_cast<char*>(c->scratch) + r_bytes);
     prm.nsig = reinterpret_cast<double*>(reinterpret_cast<char*>(c->scratch) + r_bytes + part_bytes);
     int* order = reinterpret_cast<int*>(reinterpret_cast<char*>(c->scratch) + r_bytes + part_bytes + nsig_bytes);
-    prm.order = order;
+    prm.order = (cells || sorted) ? nullptr : order;   // compact_kernel sorts the window keys only for the kernel that reads them
     prm.winmax = reinterpret_cast<double*>(reinterpret_cast<char*>(c->scratch) + r_bytes + part_bytes + nsig_bytes + order_bytes);
     prm.perm = nullptr;
     char* sort_base = reinterpret_cast<char*>(c->scratch) + ((r_bytes + part_bytes + nsig_bytes + order_bytes + winmax_bytes + al) & ~al);
@@ -948,6 +966,11 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
             return fail(c, PB200_ERR_UNSUPPORTED, "molecular tables need more shared memory than one SM has (pressure nodes x molecules > 64)");
         if (e != cudaSuccess) return fail(c, PB200_ERR_CUDA, "transit (general) launch: %s", cudaGetErrorString(e));
         c->launches += n_launch;
+    } else if (cells) {
+        int n_launch = 0;
+        cudaError_t e = launch_cells(c->d_scene, prm, n_cs, sort_base, c->stream, &n_launch);
+        if (e != cudaSuccess) return fail(c, PB200_ERR_CUDA, "sigma cells launch: %s", cudaGetErrorString(e));
+        c->launches += n_launch;
     } else {
         cudaError_t e = launch_transit(c->d_scene, h.n_abs, prm, c->stream);
         if (e != cudaSuccess) return fail(c, PB200_ERR_CUDA, "transit launch: %s", cudaGetErrorString(e));
@@ -997,7 +1020,8 @@ int check_oob(pb200_ctx* c) {
     if (c->last.executed_samples < 0) {
         c->last.executed_samples = (int64_t)st[1] * c->last_n_wav_sel;
         c->last.exp_samples = (int64_t)st[2] * 32 * c->last_wpt   // a warp owns 32 * WPT wavelengths
-                              + (int64_t)st[4];                    // narrow sorted windows: one exp per (chord, window)
+                              + (int64_t)st[4];                    // sigma cells / narrow sorted windows: one exp per (chord, cell)
+        c->last.centre_pairs = (int64_t)st[4];
     }
     if (c->mol_stats_pending) {   // kernel (m), moment form: (live chord-pair blocks, items) x wavelengths
         unsigned long long ms[2] = {0, 0};
@@ -1034,7 +1058,8 @@ extern "C" int pb200_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_l
     double* mapped = c->opt[PB200_OPT_ZEROCOPY] ? device_view(R_host, bytes) : nullptr;
     // the sorted kernel scatters R through a permutation: 8-byte stores over PCIe would be slow, so it writes to
     // device scratch and R crosses PCIe as one copy
-    if (mapped && wav_lo >= 0 && wav_hi > wav_lo && phase_hi > phase_lo && want_sorted(c, phase_hi - phase_lo, wav_hi - wav_lo)) mapped = nullptr;
+    if (mapped && wav_lo >= 0 && wav_hi > wav_lo && phase_hi > phase_lo && want_sorted(c, phase_hi - phase_lo, wav_hi - wav_lo) &&
+        !want_cells(c, phase_hi - phase_lo, wav_hi - wav_lo)) mapped = nullptr;   // (the cell path stores R in wavelength order)
     rc = mapped ? enqueue_run(c, phase_lo, phase_hi, wav_lo, wav_hi, mapped, false)
                 : enqueue_run(c, phase_lo, phase_hi, wav_lo, wav_hi, nullptr, true);
     if (rc) return rc;

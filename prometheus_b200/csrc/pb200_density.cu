@@ -623,6 +623,7 @@ __global__ void __launch_bounds__(kCompactThreads) compact_kernel(const DevScene
     // key = sum_a max_m Ncol_a(p, m) * max_{w in window} |nsig_a(p, w)| (the largest scaled tau of the window),
     // so that the long CTAs start first (bitonic network in shared memory; the order only matters for the
     // load balance, never for the results).  More than kMaxWindows windows: identity order.
+    if (prm.order == nullptr) return;   // sigma cells / sigma-sorted windows: the launch order is not taken from here
     extern __shared__ __align__(16) unsigned char wsm[];
     double* key = reinterpret_cast<double*>(wsm);
     int* idx = reinterpret_cast<int*>(key + n_pow2);

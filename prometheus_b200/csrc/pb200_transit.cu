@@ -172,18 +172,18 @@ constexpr double kOpaqueV = 50.0 * kExpBigScale;
 struct ThinHi {
     double a[9] = {};
     __device__ __forceinline__ void add(double w0, double N) { add_scaled(w0, N * kExpBigC1); }
-    // a[k] += w0 t^k / k!
+    // a[k] += w0 t^k / k!   (two FP64 instructions per order: the running power and one FMA with 1/k!)
     __device__ __forceinline__ void add_scaled(double w0, double t) {
-        double term = w0;
-        a[0] += term;
-        term *= t;                   a[1] += term;
-        term *= t * 0.5;             a[2] += term;
-        term *= t * (1.0 / 3.0);     a[3] += term;
-        term *= t * 0.25;            a[4] += term;
-        term *= t * 0.2;             a[5] += term;
-        term *= t * (1.0 / 6.0);     a[6] += term;
-        term *= t * (1.0 / 7.0);     a[7] += term;
-        term *= t * 0.125;           a[8] += term;
+        double p = w0;
+        a[0] += p;
+        p *= t;  a[1] += p;
+        p *= t;  a[2] = fma(p, 0.5, a[2]);
+        p *= t;  a[3] = fma(p, 1.0 / 6.0, a[3]);
+        p *= t;  a[4] = fma(p, 1.0 / 24.0, a[4]);
+        p *= t;  a[5] = fma(p, 1.0 / 120.0, a[5]);
+        p *= t;  a[6] = fma(p, 1.0 / 720.0, a[6]);
+        p *= t;  a[7] = fma(p, 1.0 / 5040.0, a[7]);
+        p *= t;  a[8] = fma(p, 1.0 / 40320.0, a[8]);
     }
     __device__ __forceinline__ double value(double n) const {
         double q = fma(a[8], n, a[7]);
@@ -480,7 +480,8 @@ transit_kernel(const DevScene* __restrict__ scp, const TransitParams prm) {
                     mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, d));
                     mn = fmin(mn, __shfl_xor_sync(0xffffffffu, mn, d));
                 }
-                ok = ok && (mx - mn <= kCentreEps * (mx + mn));   // a group without live wavelengths: inf, not narrow
+                if (mn > mx) mn = mx;   // a group of the last window without live wavelengths (mx = 0): results never stored
+                ok = ok && (mx - mn <= kCentreEps * (mx + mn));
                 if (j == wid) { nc = -0.5 * (mx + mn); hw = 0.5 * (mx - mn); smin_c = mn; }
             }
             groups = narrow = ok;    // the same for every warp of the CTA (all of them looked at all eight groups)
@@ -618,6 +619,212 @@ __global__ void finalize_kernel(const DevScene* __restrict__ scp, const TransitP
         const int64_t wl = prm.perm ? (int64_t)__ldg(prm.perm + i) : i % prm.n_wav_sel;   // partial sums are in sorted order
         prm.R[pb_out_index(prm, (int)(i / prm.n_wav_sel), wl)] = s / fout;
     }
+}
+
+// =====================================================================================================================
+// Sigma cells (one absorber): R(p, w) = f_p(sigma(p, w)) with f_p(s) = sum_m w_m exp(-N_m s), a smooth function of the
+// cross section ALONE -- so it is tabulated once per phase on a geometric grid of sigma cells and every wavelength only
+// evaluates a polynomial.  Cell k holds the scaled cross sections a = |nsig| in [g^k, g^(k+1)), g = (1 + eps)/(1 - eps),
+// eps = 1/40: about its centre a_c = (g^k + g^(k+1))/2 with half width h = eps a_c,
+//     w exp(-N a) = sum_k x^k [E u^k / k!],   E = w exp(-N a_c), u = -N h, x = (a - a_c)/h in [-1, 1],
+// truncated after k = 8: per chord below w (9 eps/(e (1 - eps)))^9 / 9! = 6.3e-16 w whatever its optical depth (see
+// transit_tile_centre).  cell_moment_kernel forms the nine sums A_k = sum_m E_m u_m^k / k! of every cell (ONE table exp and
+// 26 FP64 instructions per chord and cell, lane = cell, the warps of a CTA and the chord-axis splits share the chords),
+// cell_reduce_kernel adds the splits in a fixed order, cell_eval_kernel applies Horner per wavelength.  The work no longer
+// depends on the number of wavelengths: C5 has 300 306 per phase but only ~650 cells between "every chord thin"
+// (N_max a < 2.1e-5 scaled: the order-2 totals of compact_kernel) and its largest cross section.  No sort, no permutation.
+// =====================================================================================================================
+constexpr int kCellCap = 1024;                              // cells per phase the arrays hold (g^1024 = 1.6e22 in sigma)
+constexpr double kCellPerOctave = 13.860055016436705;       // 1 / log2((1 + 1/40) / (1 - 1/40))
+__device__ __forceinline__ int pb_cell_index(double a) { return (int)floor(log2(a) * kCellPerOctave); }
+__device__ __forceinline__ double pb_cell_edge(int k) { return exp2((double)k * (1.0 / kCellPerOctave)); }
+
+// per phase: {absolute index of the first cell, number of cells}: from "thin for every chord" up to the largest |nsig|
+__global__ void __launch_bounds__(256) cell_range_kernel(const DevScene* __restrict__ scp, const TransitParams prm, int2* __restrict__ range) {
+    const DevScene& sc = *scp;
+    __shared__ double s_mx[8];
+    const int pi = blockIdx.x, p = prm.phase_lo + pi;
+    double mx = 0.0;
+    for (int i = threadIdx.x; i < prm.n_win; i += blockDim.x) mx = fmax(mx, prm.winmax[(int64_t)pi * prm.n_win + i]);   // NaN / inf windows: see below
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, d));
+    if ((threadIdx.x & 31) == 0) s_mx[threadIdx.x >> 5] = mx;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int i = 1; i < 8; ++i) mx = fmax(mx, s_mx[i]);
+        const double nmax = __longlong_as_double((long long)sc.nmax[p]);
+        int2 r = make_int2(0, 0);
+        const double a_thin = prm.thin_v / nmax;                       // below: thin for every chord of the phase
+        if (nmax > 0.0 && sc.n_act[p] > 0 && mx >= a_thin && a_thin > 0.0) {
+            r.x = pb_cell_index(a_thin);
+            // (a window with a NaN cross section reports inf: every cell then; wavelengths beyond the cap: exact sum in cell_eval_kernel)
+            int n = (mx < __longlong_as_double(0x7ff0000000000000ll)) ? pb_cell_index(mx) - r.x + 1 : kCellCap;
+            r.y = n < 1 ? 1 : (n > kCellCap ? kCellCap : n);
+        }
+        range[pi] = r;
+    }
+}
+
+// partial[((pi * n_cs + split) * 9 + k) * kCellCap + cell]
+__global__ void __launch_bounds__(256, 3)
+cell_moment_kernel(const DevScene* __restrict__ scp, const TransitParams prm, const int2* __restrict__ range, double* __restrict__ partial, int n_cs) {
+    const DevScene& sc = *scp;
+    extern __shared__ __align__(128) double smem[];
+    __shared__ uint64_t full_bar[2];
+    constexpr int NWARPS = 8;
+    constexpr int R = pb_rec_stride(1);
+    constexpr int kStageDoubles = R * kChordTile;
+    constexpr uint32_t kStageBytes = kStageDoubles * sizeof(double);
+    constexpr uint32_t kRecBytes = R * sizeof(double);
+    double* etab = smem;
+    double* stages = smem + kExpBigEntries;
+    double* red = stages + 2 * kStageDoubles;      // [NWARPS][9][32]
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int pi = blockIdx.y, p = prm.phase_lo + pi, split = blockIdx.z;
+    const int2 rg = range[pi];
+    if ((int)blockIdx.x * 32 >= rg.y) return;      // no such cells in this phase (the same for the whole CTA)
+    const int cell = blockIdx.x * 32 + lane;
+    const int n_act = sc.n_act[p];
+    const int tps = pb_tiles_per_split(n_act, n_cs, 1);
+    const int tile0 = split * tps;
+    int n_tiles = n_act - tile0;
+    if (n_tiles > tps) n_tiles = tps;
+
+    ThinHi hi;
+    int n_live = 0;
+    if (n_tiles > 0) {
+        const double e_lo = pb_cell_edge(rg.x + cell), e_hi = pb_cell_edge(rg.x + cell + 1);
+        const double nc = -0.5 * (e_lo + e_hi);                       // centre of the cell's nsig (<= 0)
+        const double hu = 0.5 * (e_hi - e_lo) * kExpBigC1;            // half width as an exponent
+        if (tid == 0) {
+            mbar_init(&full_bar[0], 1);
+            mbar_init(&full_bar[1], 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncthreads();
+        const double* rec_row = sc.rec + ((int64_t)p * sc.Mp + (int64_t)tile0 * kChordTile) * R;
+        auto issue = [&](int tile, int stage) {
+            mbar_expect_tx(&full_bar[stage], kStageBytes);
+            tma_bulk_g2s(stages + stage * kStageDoubles, rec_row + (int64_t)tile * kStageDoubles, kStageBytes, &full_bar[stage]);
+        };
+        if (tid == 0) issue(0, 0);
+        {
+            const double2* src = reinterpret_cast<const double2*>(sc.exp_tab + kExpTabEntries);
+            double2* dst = reinterpret_cast<double2*>(etab);
+            for (int i = tid; i < kExpBigEntries / 2; i += 256) dst[i] = __ldg(src + i);
+        }
+        __syncthreads();
+        uint32_t tab_base;
+        asm volatile("mov.u32 %0, %1;" : "=r"(tab_base) : "r"(smem_u32(etab)));
+        const uint32_t stages_addr = smem_u32(stages);
+        for (int t = 0; t < n_tiles; ++t) {
+            const int stage = t & 1;
+            if (tid == 0 && t + 1 < n_tiles) issue(t + 1, stage ^ 1);
+            mbar_wait(&full_bar[stage], (t >> 1) & 1);
+            const uint32_t sw = stages_addr + stage * kStageBytes;
+#pragma unroll 2
+            for (int i = 0; i < kChordTile / NWARPS; ++i) {            // warp w takes records w, w + 8, ...: every lane the same record
+                const uint32_t rec = sw + (uint32_t)(i * NWARPS + wid) * kRecBytes;
+                double w0, w1, w2, N;
+                lds_v2f64(rec, w0, w1);                                 // broadcast
+                lds_v2f64(rec + 16, w2, N);
+                const bool live = !(N * e_lo > kOpaqueV) && w0 != 0.0; // opaque over the whole cell / padding record
+                if (live) {
+                    const double tt = fma(N, nc, kExpMagic);            // -tau at the centre, scaled
+                    const double r = fma(N, nc, -(tt - kExpMagic));
+                    const double T = pb_exp_big_load(tab_base, __double2loint(tt));
+                    double q = fma(r, w2, w1);
+                    q = fma(q, r, w0);
+                    hi.add_scaled(T * q, N * hu);
+                    ++n_live;
+                }
+            }
+            __syncthreads();   // stage may be refilled by the producer in the next iteration
+        }
+    }
+    // the warps' sums in a fixed order; a split without tiles writes zeros (cell_reduce_kernel adds every split)
+#pragma unroll
+    for (int k = 0; k < 9; ++k) red[(wid * 9 + k) * 32 + lane] = hi.a[k];
+    __syncthreads();
+    for (int i = tid; i < 9 * 32; i += 256) {
+        double v = red[i];
+#pragma unroll
+        for (int w = 1; w < NWARPS; ++w) v += red[w * 9 * 32 + i];
+        const int k = i >> 5, l = i & 31;
+        partial[(((int64_t)pi * n_cs + split) * 9 + k) * kCellCap + blockIdx.x * 32 + l] = v;
+    }
+    n_live = (int)pb_warp_sum((double)n_live);
+    if (lane == 0 && n_live) atomicAdd(sc.stat + 4, (unsigned long long)n_live);
+}
+
+// sums[(pi * 9 + k) * kCellCap + cell] = sum over the chord-axis splits, fixed order
+__global__ void __launch_bounds__(256) cell_reduce_kernel(const TransitParams prm, const int2* __restrict__ range, const double* __restrict__ partial,
+                                                           double* __restrict__ sums, int n_cs) {
+    const int pi = blockIdx.y;
+    const int n_cells = range[pi].y;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 9 * kCellCap; i += gridDim.x * blockDim.x) {
+        if ((i & (kCellCap - 1)) >= ((n_cells + 31) & ~31)) continue;
+        double v = 0.0;
+        for (int s = 0; s < n_cs; ++s) v += partial[((int64_t)pi * n_cs + s) * 9 * kCellCap + i];
+        sums[(int64_t)pi * 9 * kCellCap + i] = v;
+    }
+}
+
+__global__ void __launch_bounds__(256) cell_eval_kernel(const DevScene* __restrict__ scp, const TransitParams prm, const int2* __restrict__ range,
+                                                         const double* __restrict__ sums) {
+    const DevScene& sc = *scp;
+    const int64_t wi = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (wi >= prm.n_wav_sel) return;
+    const int pi = blockIdx.y, p = prm.phase_lo + pi;
+    const double ns = __ldg(prm.nsig + (int64_t)pi * prm.n_wav_sel + wi);
+    const double a = fabs(ns);
+    const int2 rg = range[pi];
+    double v;
+    int k = 0;
+    if (!(a < __longlong_as_double(0x7ff0000000000000ll))) {
+        v = ns * 0.0;                                                   // NaN (or infinite) cross section: NaN in R, as the reference
+    } else if (rg.y == 0 || (k = pb_cell_index(a) - rg.x) < 0 || !(a * __longlong_as_double((long long)sc.nmax[p]) >= prm.thin_v)) {
+        const double* tt = sc.thin_tot + (int64_t)p * 8;                // thin for every chord of the phase: order-2 totals
+        v = fma(ns, fma(ns, tt[3], tt[1]), tt[0]);
+    } else if (k < kCellCap) {
+        const double e_lo = pb_cell_edge(rg.x + k), e_hi = pb_cell_edge(rg.x + k + 1);
+        const double x = (ns + 0.5 * (e_lo + e_hi)) / (0.5 * (e_hi - e_lo));
+        const double* A = sums + (int64_t)pi * 9 * kCellCap + k;
+        double q = fma(A[8 * kCellCap], x, A[7 * kCellCap]);
+#pragma unroll
+        for (int j = 6; j >= 0; --j) q = fma(q, x, A[j * kCellCap]);
+        v = q;
+    } else {                                                            // beyond the cell arrays (tau spans > 22 decades): exact sum
+        v = 0.0;
+        const double* rec = sc.rec + (int64_t)p * sc.Mp * pb_rec_stride(1);
+        const int64_t n_rec = (int64_t)sc.n_act[p] * kChordTile;
+        for (int64_t m = 0; m < n_rec; ++m) v = fma(rec[m * 4], exp(rec[m * 4 + 3] * ns * kExpBigC1), v);
+    }
+    prm.R[pb_out_index(prm, pi, wi)] = (v + sc.w0[p]) / sc.fout[0];    // :1258
+}
+
+int cell_chord_splits(int sm_count, int n_phase, int n_tiles) {
+    int n_cs = (sm_count * 16 + 20 * n_phase - 1) / (20 * n_phase);     // ~20 cell blocks per phase are in use (650 cells)
+    if (n_cs > n_tiles / 2) n_cs = n_tiles / 2;
+    return n_cs < 1 ? 1 : n_cs;
+}
+size_t cell_scratch_bytes(int n_phase, int n_cs) {
+    return ((size_t)n_phase * sizeof(int2) + 255 & ~size_t(255)) + (size_t)n_phase * (n_cs + 1) * 9 * kCellCap * sizeof(double);
+}
+// nsig, winmax (sigma_phase_kernel) and the records, thin totals, w0 (compact_kernel) of the run -> R
+cudaError_t launch_cells(const DevScene* d_scene, const TransitParams& prm, int n_cs, void* scratch, cudaStream_t st, int* n_launch) {
+    int2* range = reinterpret_cast<int2*>(scratch);
+    double* partial = reinterpret_cast<double*>(reinterpret_cast<char*>(scratch) + (((size_t)prm.n_phase * sizeof(int2) + 255) & ~size_t(255)));
+    double* sums = partial + (size_t)prm.n_phase * n_cs * 9 * kCellCap;
+    const size_t smem = (kExpBigEntries + 2 * pb_rec_stride(1) * kChordTile + 8 * 9 * 32) * sizeof(double);
+    cudaError_t e = cudaFuncSetAttribute(cell_moment_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    cell_range_kernel<<<prm.n_phase, 256, 0, st>>>(d_scene, prm, range);
+    cell_moment_kernel<<<dim3(kCellCap / 32, (unsigned)prm.n_phase, (unsigned)n_cs), 256, smem, st>>>(d_scene, prm, range, partial, n_cs);
+    cell_reduce_kernel<<<dim3(4, (unsigned)prm.n_phase), 256, 0, st>>>(prm, range, partial, sums, n_cs);
+    cell_eval_kernel<<<dim3((unsigned)((prm.n_wav_sel + 255) / 256), (unsigned)prm.n_phase), 256, 0, st>>>(d_scene, prm, range, sums);
+    *n_launch = 4;
+    return cudaGetLastError();
 }
 
 template <int S, int WPT, int THREADS = 256, bool HI = false>

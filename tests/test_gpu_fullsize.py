@@ -151,21 +151,27 @@ def test_steep_molecular_table_takes_the_per_record_form(nist_rows):
     assert np.max(np.abs(R[:, sel] - R_ref)) < 5e-13 and float((R0 - R_ref).max()) > 1e-4
 
 
-# ---- C5: columns chosen by the sigma-sorted kernel's own per-window decisions -------------------------------------
+# ---- C5: columns chosen by the kernels' own decisions ---------------------------------------------------------------
 def test_c5_regime_boundary_columns_against_oracle(nist_rows):
-    """The sorted variant of kernel (c') decides per (chord, window of 256 sorted wavelengths): order-2 expansion below
-    tau = 2.1e-5, order-8 below 0.1, skipped above 50, table exp between (pb200_transit.cu: ThinSums, ThinHi,
-    transit_tile_sorted) -- and, where a window's (or each 32-wavelength group's) sigma spread is below 1/40, one exp per chord feeding Taylor sums about the
-    window's centre (transit_tile_centre).  The
-    boundaries sit at intermediate sigma, where a "deepest + strided" pick does not look: take, for two phases, the
-    first and the last window in which each regime occurs, read back from the device's own sort order."""
+    """One absorber, many wavelengths: by default R(p, .) is tabulated on sigma cells (cell_*_kernel: Taylor sums about the
+    centre of every cell of a geometric sigma grid, the order-2 totals below "thin for every chord"); with
+    PB200_OPT_CENTRE = 2 the sigma-sorted windows of kernel (c') run, which decide per (chord, window of 256 sorted
+    wavelengths): order-2 expansion below tau = 2.1e-5, order-8 below 0.1, skipped above 50, table exp between
+    (ThinSums, ThinHi, transit_tile_sorted), and Taylor sums about the centre of narrow windows / 32-wavelength groups
+    (transit_tile_centre).  All the boundaries sit at intermediate sigma, where a "deepest + strided" pick does not look:
+    for two phases take the first, a middle and the last window of every regime (from the device's own sort order) and
+    the two ends and the middle of the first, a middle and the last sigma cell, and check BOTH paths against the oracle."""
     ctx = host.get_context(0)
     spec = workloads.get("C5")
     tr = builder.build_transit(spec, nist_rows=nist_rows)
     R = tr.sumOverChords()
     n_orb, n_wav = R.shape
-    order = ctx.last_sort_order(n_orb)
-    assert order is not None, "C5 runs the sigma-sorted windows by default"
+    assert ctx.last_sort_order(n_orb) is None, "the cell path sorts nothing"
+    with ctx.options(centre=2):
+        R_sorted = tr.sumOverChords()
+        order = ctx.last_sort_order(n_orb)
+    assert order is not None, "PB200_OPT_CENTRE = 2: C5 runs the sigma-sorted windows"
+    assert np.max(np.abs(R - R_sorted)) < 5e-14
     perm, nsig = order
     ncol = tr.getColumnDensityGrid()                               # [constituent][chord], chord = m*n_orb + p
     chi = [con.chi for con in tr.atmosphere.densityDistributionList[0].constituents]
@@ -202,6 +208,22 @@ def test_c5_regime_boundary_columns_against_oracle(nist_rows):
             for win in (idx[0], idx[len(idx) // 2], idx[-1]):
                 for pos in (win * 256, win * 256 + 128, win * 256 + 255):     # both ends (|x| = 1) and the middle of the window
                     sel.append(int(perm[p, min(pos, n_wav - 1)]))
+        # sigma cells: a in [g^k, g^(k+1)), g = (1 + 1/40)/(1 - 1/40); used from "thin for every chord" (N_max a < 0.125) upwards
+        per_octave = 1.0 / np.log2((1.0 + 1.0 / 40.0) / (1.0 - 1.0 / 40.0))
+        live = a[(a * N_hi >= thin_v) & np.isfinite(a)]
+        kk = np.floor(np.log2(live) * per_octave).astype(np.int64)
+        cells = np.unique(kk)
+        assert cells.size > 100
+        pos_of = {v: i for i, v in enumerate(a)}
+        for k in (cells[0], cells[len(cells) // 3], cells[len(cells) // 2], cells[-2], cells[-1]):
+            members = live[kk == k]
+            lo, hi = 2.0 ** (k / per_octave), 2.0 ** ((k + 1) / per_octave)
+            x = (members - 0.5 * (lo + hi)) / (0.5 * (hi - lo))
+            for target in (-1.0, 0.0, 1.0):
+                sel.append(int(perm[p, pos_of[members[np.argmin(np.abs(x - target))]]]))
+        below = a[(a * N_hi < thin_v)]
+        if below.size:
+            sel.append(int(perm[p, pos_of[below.max()]]))                      # the last wavelength that takes the order-2 totals
     sel = np.unique(np.array(sel))
     assert sel.size >= 16
     inputs = oracle_inputs(spec, nist_rows)
@@ -212,6 +234,7 @@ def test_c5_regime_boundary_columns_against_oracle(nist_rows):
     kw = dict(batch_size=None if bs >= n_c else bs, wavelength=m.wavelength[sel])
     R_ref = oracle.sum_over_chords(m, **kw)
     R0 = oracle.sum_over_chords(m, opaque_only=True, **kw)
-    ok, worst = excess_depth_ok(R[:, sel], R_ref, R0)
-    assert ok, f"C5 regime columns: worst err/bound {worst:.3g}"
-    assert np.max(np.abs(R[:, sel] - R_ref)) < 5e-13, float(np.max(np.abs(R[:, sel] - R_ref)))
+    for label, Rx in (("cells", R), ("sorted windows", R_sorted)):
+        ok, worst = excess_depth_ok(Rx[:, sel], R_ref, R0)
+        assert ok, f"C5 regime columns ({label}): worst err/bound {worst:.3g}"
+        assert np.max(np.abs(Rx[:, sel] - R_ref)) < 5e-13, (label, float(np.max(np.abs(Rx[:, sel] - R_ref))))

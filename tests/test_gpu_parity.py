@@ -475,7 +475,7 @@ def test_sigma_sorted_windows_leave_R_unchanged(name, nist_rows, golden, monkeyp
     with ctx.options(sort=1, thin=0):                                          # every active sample through the exp, sorted
         R_exp, _ = ctx.run(0, info["n_orb"], 0, info["n_wav"])
     assert np.max(np.abs(out["0"] - out["1"])) < 5e-14 and np.max(np.abs(R_exp - out["0"])) < 5e-14
-    for centre in (0, 1):     # Taylor sums about the centre of narrow windows / groups: off, whole windows only (default: 2)
+    for centre in (0, 1, 2):  # the sorted windows (the default, 3, tabulates R on sigma cells instead and sorts nothing)
         with ctx.options(sort=1, centre=centre):
             R_c, _ = ctx.run(0, info["n_orb"], 0, info["n_wav"])
         assert np.max(np.abs(R_c - out["0"])) < 5e-14, centre
@@ -522,15 +522,33 @@ def test_narrow_sorted_windows_as_taylor_sums(nist_rows):
     with ctx.options(sort=0):
         R_ref, _ = ctx.run(0, n_orb, 0, n_wav)
     R, exps = {}, {}
-    for centre in (0, 1, 2):
+    for centre in (0, 1, 2, 3):                        # 3 (default): sigma cells, no sort
         with ctx.options(sort=1, centre=centre):
             R[centre], t = ctx.run(0, n_orb, 0, n_wav)
             exps[centre] = t["exp_samples"]
+            assert (ctx.last_sort_order(n_orb) is None) == (centre == 3)
         assert np.max(np.abs(R[centre] - R_ref)) < 5e-14, centre
-    assert exps[2] <= exps[1] <= exps[0] and exps[2] < 0.5 * exps[0], exps
-    with ctx.options(sort=1):                          # a ragged tile and a phase subset through the same path
-        tile, _ = ctx.run(1, 2, 3, n_wav - 11)
-    assert np.max(np.abs(tile - R[2][1:2, 3:n_wav - 11])) < 5e-14
+    assert exps[3] < 0.5 * exps[0], exps             # cells: (chord, cell) pairs instead of samples through the exp
+    for centre in (2, 3):                              # a ragged tile and a phase subset through the same paths
+        with ctx.options(sort=1, centre=centre):
+            tile, _ = ctx.run(1, 2, 3, n_wav - 11)
+        assert np.max(np.abs(tile - R[centre][1:2, 3:n_wav - 11])) < 5e-14, centre
+    # the same scene made opaque and transparent: the cell grid follows the column densities
+    for scale in (1e6, 1e-9):
+        spec2 = workloads.get("C4s")
+        spec2["wavelength"] = list(workloads.get("C4")["wavelength"])
+        for scn in spec2["scenarios"]:
+            for key in ("Nparticles", "N", "P_0"):
+                if key in scn:
+                    scn[key] *= scale
+        tr2 = builder.build_transit(spec2, nist_rows=nist_rows)
+        sc2, keep2, info2 = scene.flatten(tr2)
+        ctx.set_scene(sc2, keep2)
+        with ctx.options(sort=0):
+            R0_, _ = ctx.run(0, info2["n_orb"], 0, info2["n_wav"])
+        with ctx.options(sort=1):
+            R1_, _ = ctx.run(0, info2["n_orb"], 0, info2["n_wav"])
+        assert np.max(np.abs(R0_ - R1_)) < 5e-14, scale
 
 
 def test_power_law_with_non_positive_exponent_is_not_culled(nist_rows):
