@@ -1,7 +1,7 @@
 #!/bin/bash
 # Round-2 ncu captures (one GPU).  Run on the GPU box from the repo root:  bash profiles/r02_capture.sh
-# Every program is run once WITHOUT ncu first (a number printed under ncu is never a bench value); reports go to
-# gpurun_out/ and are summarised in the build container with profiles/summarize.py.
+# Every program is run once WITHOUT ncu first (a number printed under ncu is never a bench value); each report is
+# summarised on the box with profiles/summarize.py (the text comes back in gpurun_out/ and is copied to profiles/).
 set -u
 O=gpurun_out
 mkdir -p $O
@@ -11,6 +11,8 @@ run() { # name, kernel regex, count, run_once arguments...
     timeout 600 python profiles/run_once.py "$@" > $O/once_$name.log 2>&1 || { echo "run_once $name failed"; tail -3 $O/once_$name.log; return; }
     timeout 900 $NCU -k regex:"$re" -c $cnt -f -o $O/r02_$name python profiles/run_once.py "$@" > $O/ncu_$name.log 2>&1
     echo "$name: rc=$? $(tail -1 $O/once_$name.log | cut -c1-200)"
+    # the reports together exceed what gpurun brings back (64 MiB): summarise here, keep the text
+    python profiles/summarize.py $O/r02_$name.ncu-rep > $O/r02_${name}_full.txt 2>/dev/null && rm -f $O/r02_$name.ncu-rep
 }
 # launch list of the bench command itself
 timeout 900 python bench.py --steps 2 --warmup 3 --cpu-seconds 0 > $O/bench_short.json 2> $O/bench_short.err
@@ -27,4 +29,4 @@ run C4_windows     "transit_kernel" 1 C4 1 sort=0
 run C2_production  "moment|column_cta|fout" 8 C2 1
 run C3_production  "transit_kernel|column_cta|compact" 6 C3 1
 run RET_batch64    "transit_kernel|column_cta|compact|lightcurve" 8 RET 1 batch=64
-ls -la $O/*.ncu-rep
+ls -la $O/r02_*_full.txt

@@ -39,6 +39,7 @@ void launch_finalize(const DevScene*, const TransitParams&, int sm_count, cudaSt
 int cell_chord_splits(int sm_count, int n_phase, int n_tiles);
 size_t cell_scratch_bytes(int n_phase, int n_cs);
 cudaError_t launch_cells(const DevScene* d_scene, const TransitParams& prm, int n_cs, void* scratch, cudaStream_t st, int* n_launch);
+void cell_bind(TransitParams& prm, void* scratch);
 void launch_sigma_lookup(const double*, const double*, int64_t, double, const double*, int64_t, double*, int,
                          cudaStream_t);
 void launch_sigma_u(const DevScene*, int n_atoms, int n_orb, int64_t wav_lo, int64_t n_wav_sel, double* out, int,
@@ -844,8 +845,10 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     prm.order = (cells || sorted) ? nullptr : order;   // compact_kernel sorts the window keys only for the kernel that reads them
     prm.winmax = reinterpret_cast<double*>(reinterpret_cast<char*>(c->scratch) + r_bytes + part_bytes + nsig_bytes + order_bytes);
     prm.perm = nullptr;
+    prm.cell_range = nullptr; prm.cell_count = nullptr;
     char* sort_base = reinterpret_cast<char*>(c->scratch) + ((r_bytes + part_bytes + nsig_bytes + order_bytes + winmax_bytes + al) & ~al);
 
+    if (cells) cell_bind(prm, sort_base);
     PB_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
     cudaStream_t sig_stream = c->stream;
     if (!c->buckets_ready && h.n_atoms > 0) {   // after the (possibly sharded + all-gathered) tables are complete on the device

@@ -623,6 +623,31 @@ __global__ void __launch_bounds__(kCompactThreads) compact_kernel(const DevScene
     // key = sum_a max_m Ncol_a(p, m) * max_{w in window} |nsig_a(p, w)| (the largest scaled tau of the window),
     // so that the long CTAs start first (bitonic network in shared memory; the order only matters for the
     // load balance, never for the results).  More than kMaxWindows windows: identity order.
+    // ---- sigma cells (one absorber): the cells this phase needs, from "thin for every chord" (N_max a < thin_v: those
+    // wavelengths take the order-2 totals above) up to the phase's largest |nsig| -------------------------------------------
+    if (prm.cell_range != nullptr) {
+        __shared__ double s_cmx[32];
+        double mx = 0.0;
+        for (int i = tid; i < prm.n_win; i += kCompactThreads) mx = fmax(mx, prm.winmax[(int64_t)blockIdx.x * prm.n_win + i]);
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, d));
+        if (lane == 0) s_cmx[wid] = mx;
+        if (tid < kCellCap / 32) prm.cell_count[blockIdx.x * (kCellCap / 32) + tid] = 0u;
+        __syncthreads();
+        if (tid == 0) {
+            for (int i = 1; i < kCompactThreads / 32; ++i) mx = fmax(mx, s_cmx[i]);
+            const double nmax = __longlong_as_double((long long)sc.nmax[p]);
+            int2 r = make_int2(0, 0);
+            const double a_thin = prm.thin_v / nmax;
+            if (nmax > 0.0 && n_tiles > 0 && mx >= a_thin && a_thin > 0.0) {
+                r.x = pb_cell_index(a_thin);
+                // (a window with a NaN cross section reports inf: every cell then; wavelengths beyond the arrays: exact sum in cell_eval_kernel)
+                const int n = (mx < __longlong_as_double(0x7ff0000000000000ll)) ? pb_cell_index(mx) - r.x + 1 : kCellCap;
+                r.y = n < 1 ? 1 : (n > kCellCap ? kCellCap : n);
+            }
+            prm.cell_range[blockIdx.x] = r;
+        }
+    }
     if (prm.order == nullptr) return;   // sigma cells / sigma-sorted windows: the launch order is not taken from here
     extern __shared__ __align__(16) unsigned char wsm[];
     double* key = reinterpret_cast<double*>(wsm);

@@ -157,7 +157,18 @@ struct TransitParams {
     double* nsig;         // [n_atoms][n_phase][n_wav_sel] -sigma_a(p, w) * 4096/ln2 (sigma_phase_kernel); with perm != NULL
                           // in the sorted order of each phase
     const int* perm;      // NULL, or [n_phase][n_wav_sel]: local wavelength index of sorted position i (pb200_sort.cu)
+    int2* cell_range;     // NULL, or [n_phase] {absolute index of the first sigma cell, number of cells} (compact_kernel -> cell_*_kernel)
+    unsigned* cell_count; // [n_phase][kCellCap / 32] arrival counters of cell_moment_kernel's chord-axis splits (zeroed by compact_kernel)
 };
+
+// Sigma cells (pb200_transit.cu): cell k holds the scaled cross sections a = |nsig| in [g^k, g^(k+1)), g = (1 + eps)/(1 - eps),
+// eps = 3/40; Taylor sums of order kCellOrder about the centre (truncation < 7.2e-16 of a chord's weight, see cell_moment_kernel)
+constexpr int kCellCap = 512;                               // cells per phase the arrays hold (g^512 = 2.6e33 in sigma)
+constexpr int kCellOrder = 12;
+constexpr int kCellSums = kCellOrder + 1;
+constexpr double kCellPerOctave = 4.612303829032796;        // 1 / log2((1 + 3/40) / (1 - 3/40))
+__device__ __forceinline__ int pb_cell_index(double a) { return (int)floor(log2(a) * kCellPerOctave); }
+__device__ __forceinline__ double pb_cell_edge(int k) { return exp2((double)k * (1.0 / kCellPerOctave)); }
 __host__ __device__ inline int64_t pb_wav_index(const TransitParams& prm, int64_t wi) {
     if (prm.cyc_block == 0) return prm.wav_lo + wi;
     return ((wi / prm.cyc_block) * prm.cyc_n + prm.cyc_rank) * prm.cyc_block + wi % prm.cyc_block;

@@ -625,52 +625,46 @@ __global__ void finalize_kernel(const DevScene* __restrict__ scp, const TransitP
 // Sigma cells (one absorber): R(p, w) = f_p(sigma(p, w)) with f_p(s) = sum_m w_m exp(-N_m s), a smooth function of the
 // cross section ALONE -- so it is tabulated once per phase on a geometric grid of sigma cells and every wavelength only
 // evaluates a polynomial.  Cell k holds the scaled cross sections a = |nsig| in [g^k, g^(k+1)), g = (1 + eps)/(1 - eps),
-// eps = 1/40: about its centre a_c = (g^k + g^(k+1))/2 with half width h = eps a_c,
+// eps = 3/40 (pb200_internal.cuh): about its centre a_c = (g^k + g^(k+1))/2 with half width h = eps a_c,
 //     w exp(-N a) = sum_k x^k [E u^k / k!],   E = w exp(-N a_c), u = -N h, x = (a - a_c)/h in [-1, 1],
-// truncated after k = 8: per chord below w (9 eps/(e (1 - eps)))^9 / 9! = 6.3e-16 w whatever its optical depth (see
-// transit_tile_centre).  cell_moment_kernel forms the nine sums A_k = sum_m E_m u_m^k / k! of every cell (ONE table exp and
-// 26 FP64 instructions per chord and cell, lane = cell, the warps of a CTA and the chord-axis splits share the chords),
-// cell_reduce_kernel adds the splits in a fixed order, cell_eval_kernel applies Horner per wavelength.  The work no longer
-// depends on the number of wavelengths: C5 has 300 306 per phase but only ~650 cells between "every chord thin"
-// (N_max a < 2.1e-5 scaled: the order-2 totals of compact_kernel) and its largest cross section.  No sort, no permutation.
+// truncated after k = 12: with tau_c = N a_c a chord's remainder is below w e^{-tau_c (1 - eps)} (tau_c eps)^13 / 13!
+// <= w (13 eps / (e (1 - eps)))^13 / 13! = 7.2e-16 w WHATEVER its optical depth (the maximum sits at tau_c = 13 / (1 - eps)).
+// (Order 8 needs eps = 1/40 for the same bound: three times the cells at 25 instead of 33 FP64 instructions per chord
+// and cell -- 2.3 times the work.)  cell_moment_kernel forms the 13 sums A_k = sum_m E_m u_m^k / k! of every cell (ONE table
+// exp per chord and cell; lane = cell, the warps of a CTA and the chord-axis splits share the chords) and the last split
+// to arrive adds the splits in a fixed order; cell_eval_kernel applies Horner per wavelength.  The work no longer depends
+// on the number of wavelengths: C5 has 300 306 per phase but ~215 cells between "every chord thin" (N_max a < 2.1e-5
+// scaled: the order-2 totals of compact_kernel, which also leaves the cell range of the phase) and its largest cross
+// section.  No sort, no permutation.
 // =====================================================================================================================
-constexpr int kCellCap = 1024;                              // cells per phase the arrays hold (g^1024 = 1.6e22 in sigma)
-constexpr double kCellPerOctave = 13.860055016436705;       // 1 / log2((1 + 1/40) / (1 - 1/40))
-__device__ __forceinline__ int pb_cell_index(double a) { return (int)floor(log2(a) * kCellPerOctave); }
-__device__ __forceinline__ double pb_cell_edge(int k) { return exp2((double)k * (1.0 / kCellPerOctave)); }
-
-// per phase: {absolute index of the first cell, number of cells}: from "thin for every chord" up to the largest |nsig|
-__global__ void __launch_bounds__(256) cell_range_kernel(const DevScene* __restrict__ scp, const TransitParams prm, int2* __restrict__ range) {
-    const DevScene& sc = *scp;
-    __shared__ double s_mx[8];
-    const int pi = blockIdx.x, p = prm.phase_lo + pi;
-    double mx = 0.0;
-    for (int i = threadIdx.x; i < prm.n_win; i += blockDim.x) mx = fmax(mx, prm.winmax[(int64_t)pi * prm.n_win + i]);   // NaN / inf windows: see below
+struct CellSums {
+    double a[kCellSums] = {};
+    // a[k] += E u^k / k!: the running power and one FMA with 1/k! per order
+    __device__ __forceinline__ void add(double E, double u) {
+        constexpr double inv_fact[kCellSums] = {1.0, 1.0, 0.5, 0.16666666666666666, 0.041666666666666664, 0.008333333333333333,
+                                                0.001388888888888889, 0.0001984126984126984, 2.48015873015873e-05,
+                                                2.7557319223985893e-06, 2.755731922398589e-07, 2.505210838544172e-08,
+                                                2.08767569878681e-09};
+        double p = E;
+        a[0] += p;
+        p *= u;
+        a[1] += p;
 #pragma unroll
-    for (int d = 16; d > 0; d >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, d));
-    if ((threadIdx.x & 31) == 0) s_mx[threadIdx.x >> 5] = mx;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        for (int i = 1; i < 8; ++i) mx = fmax(mx, s_mx[i]);
-        const double nmax = __longlong_as_double((long long)sc.nmax[p]);
-        int2 r = make_int2(0, 0);
-        const double a_thin = prm.thin_v / nmax;                       // below: thin for every chord of the phase
-        if (nmax > 0.0 && sc.n_act[p] > 0 && mx >= a_thin && a_thin > 0.0) {
-            r.x = pb_cell_index(a_thin);
-            // (a window with a NaN cross section reports inf: every cell then; wavelengths beyond the cap: exact sum in cell_eval_kernel)
-            int n = (mx < __longlong_as_double(0x7ff0000000000000ll)) ? pb_cell_index(mx) - r.x + 1 : kCellCap;
-            r.y = n < 1 ? 1 : (n > kCellCap ? kCellCap : n);
+        for (int k = 2; k < kCellSums; ++k) {
+            p *= u;
+            a[k] = fma(p, inv_fact[k], a[k]);
         }
-        range[pi] = r;
     }
-}
+};
 
-// partial[((pi * n_cs + split) * 9 + k) * kCellCap + cell]
+// partial[((pi * n_cs + split) * kCellSums + k) * kCellCap + cell];  sums[(pi * (kCellSums + 2) + k) * kCellCap + cell], rows
+// kCellSums, kCellSums + 1 of sums: the cell's centre (of nsig, <= 0) and 1 / half width for cell_eval_kernel
 __global__ void __launch_bounds__(256, 3)
-cell_moment_kernel(const DevScene* __restrict__ scp, const TransitParams prm, const int2* __restrict__ range, double* __restrict__ partial, int n_cs) {
+cell_moment_kernel(const DevScene* __restrict__ scp, const TransitParams prm, double* __restrict__ partial, double* __restrict__ sums, int n_cs) {
     const DevScene& sc = *scp;
     extern __shared__ __align__(128) double smem[];
     __shared__ uint64_t full_bar[2];
+    __shared__ int s_last;
     constexpr int NWARPS = 8;
     constexpr int R = pb_rec_stride(1);
     constexpr int kStageDoubles = R * kChordTile;
@@ -678,10 +672,11 @@ cell_moment_kernel(const DevScene* __restrict__ scp, const TransitParams prm, co
     constexpr uint32_t kRecBytes = R * sizeof(double);
     double* etab = smem;
     double* stages = smem + kExpBigEntries;
-    double* red = stages + 2 * kStageDoubles;      // [NWARPS][9][32]
+    double* red = etab;                            // [NWARPS][kCellSums][32]: after the chord loop the table's 32 KB are free
+    static_assert(NWARPS * kCellSums * 32 <= kExpBigEntries, "the warps' sums fit the exp table's memory");
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int pi = blockIdx.y, p = prm.phase_lo + pi, split = blockIdx.z;
-    const int2 rg = range[pi];
+    const int2 rg = prm.cell_range[pi];
     if ((int)blockIdx.x * 32 >= rg.y) return;      // no such cells in this phase (the same for the whole CTA)
     const int cell = blockIdx.x * 32 + lane;
     const int n_act = sc.n_act[p];
@@ -689,13 +684,14 @@ cell_moment_kernel(const DevScene* __restrict__ scp, const TransitParams prm, co
     const int tile0 = split * tps;
     int n_tiles = n_act - tile0;
     if (n_tiles > tps) n_tiles = tps;
+    const double e_lo = pb_cell_edge(rg.x + cell), e_hi = pb_cell_edge(rg.x + cell + 1);
+    const double nc = -0.5 * (e_lo + e_hi);                           // centre of the cell's nsig (<= 0)
+    const double hw = 0.5 * (e_hi - e_lo);
 
-    ThinHi hi;
+    CellSums cs;
     int n_live = 0;
     if (n_tiles > 0) {
-        const double e_lo = pb_cell_edge(rg.x + cell), e_hi = pb_cell_edge(rg.x + cell + 1);
-        const double nc = -0.5 * (e_lo + e_hi);                       // centre of the cell's nsig (<= 0)
-        const double hu = 0.5 * (e_hi - e_lo) * kExpBigC1;            // half width as an exponent
+        const double hu = hw * kExpBigC1;                             // half width as an exponent
         if (tid == 0) {
             mbar_init(&full_bar[0], 1);
             mbar_init(&full_bar[1], 1);
@@ -735,50 +731,54 @@ cell_moment_kernel(const DevScene* __restrict__ scp, const TransitParams prm, co
                     const double T = pb_exp_big_load(tab_base, __double2loint(tt));
                     double q = fma(r, w2, w1);
                     q = fma(q, r, w0);
-                    hi.add_scaled(T * q, N * hu);
+                    cs.add(T * q, N * hu);
                     ++n_live;
                 }
             }
             __syncthreads();   // stage may be refilled by the producer in the next iteration
         }
     }
-    // the warps' sums in a fixed order; a split without tiles writes zeros (cell_reduce_kernel adds every split)
+    // the warps' sums in a fixed order; a split without tiles writes zeros (the reduction below adds every split)
 #pragma unroll
-    for (int k = 0; k < 9; ++k) red[(wid * 9 + k) * 32 + lane] = hi.a[k];
+    for (int k = 0; k < kCellSums; ++k) red[(wid * kCellSums + k) * 32 + lane] = cs.a[k];
     __syncthreads();
-    for (int i = tid; i < 9 * 32; i += 256) {
+    for (int i = tid; i < kCellSums * 32; i += 256) {
         double v = red[i];
 #pragma unroll
-        for (int w = 1; w < NWARPS; ++w) v += red[w * 9 * 32 + i];
+        for (int w = 1; w < NWARPS; ++w) v += red[w * kCellSums * 32 + i];
         const int k = i >> 5, l = i & 31;
-        partial[(((int64_t)pi * n_cs + split) * 9 + k) * kCellCap + blockIdx.x * 32 + l] = v;
+        partial[(((int64_t)pi * n_cs + split) * kCellSums + k) * kCellCap + blockIdx.x * 32 + l] = v;
     }
     n_live = (int)pb_warp_sum((double)n_live);
     if (lane == 0 && n_live) atomicAdd(sc.stat + 4, (unsigned long long)n_live);
-}
-
-// sums[(pi * 9 + k) * kCellCap + cell] = sum over the chord-axis splits, fixed order
-__global__ void __launch_bounds__(256) cell_reduce_kernel(const TransitParams prm, const int2* __restrict__ range, const double* __restrict__ partial,
-                                                           double* __restrict__ sums, int n_cs) {
-    const int pi = blockIdx.y;
-    const int n_cells = range[pi].y;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 9 * kCellCap; i += gridDim.x * blockDim.x) {
-        if ((i & (kCellCap - 1)) >= ((n_cells + 31) & ~31)) continue;
+    // the last split of this (phase, cell block) to arrive adds all of them, always in split order: deterministic
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) s_last = (atomicAdd(prm.cell_count + pi * (kCellCap / 32) + blockIdx.x, 1u) == (unsigned)(n_cs - 1));
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    double* out = sums + (int64_t)pi * (kCellSums + 2) * kCellCap + blockIdx.x * 32;
+    for (int i = tid; i < kCellSums * 32; i += 256) {
+        const int k = i >> 5, l = i & 31;
         double v = 0.0;
-        for (int s = 0; s < n_cs; ++s) v += partial[((int64_t)pi * n_cs + s) * 9 * kCellCap + i];
-        sums[(int64_t)pi * 9 * kCellCap + i] = v;
+        for (int s = 0; s < n_cs; ++s) v += __ldcg(partial + (((int64_t)pi * n_cs + s) * kCellSums + k) * kCellCap + blockIdx.x * 32 + l);
+        out[k * kCellCap + l] = v;
+    }
+    if (wid == 0) {
+        out[kCellSums * kCellCap + lane] = nc;
+        out[(kCellSums + 1) * kCellCap + lane] = 1.0 / hw;
     }
 }
 
-__global__ void __launch_bounds__(256) cell_eval_kernel(const DevScene* __restrict__ scp, const TransitParams prm, const int2* __restrict__ range,
-                                                         const double* __restrict__ sums) {
+__global__ void __launch_bounds__(256) cell_eval_kernel(const DevScene* __restrict__ scp, const TransitParams prm, const double* __restrict__ sums) {
     const DevScene& sc = *scp;
     const int64_t wi = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (wi >= prm.n_wav_sel) return;
     const int pi = blockIdx.y, p = prm.phase_lo + pi;
     const double ns = __ldg(prm.nsig + (int64_t)pi * prm.n_wav_sel + wi);
     const double a = fabs(ns);
-    const int2 rg = range[pi];
+    const int2 rg = prm.cell_range[pi];
     double v;
     int k = 0;
     if (!(a < __longlong_as_double(0x7ff0000000000000ll))) {
@@ -787,14 +787,13 @@ __global__ void __launch_bounds__(256) cell_eval_kernel(const DevScene* __restri
         const double* tt = sc.thin_tot + (int64_t)p * 8;                // thin for every chord of the phase: order-2 totals
         v = fma(ns, fma(ns, tt[3], tt[1]), tt[0]);
     } else if (k < kCellCap) {
-        const double e_lo = pb_cell_edge(rg.x + k), e_hi = pb_cell_edge(rg.x + k + 1);
-        const double x = (ns + 0.5 * (e_lo + e_hi)) / (0.5 * (e_hi - e_lo));
-        const double* A = sums + (int64_t)pi * 9 * kCellCap + k;
-        double q = fma(A[8 * kCellCap], x, A[7 * kCellCap]);
+        const double* A = sums + (int64_t)pi * (kCellSums + 2) * kCellCap + k;
+        const double x = (ns - A[kCellSums * kCellCap]) * A[(kCellSums + 1) * kCellCap];
+        double q = A[kCellOrder * kCellCap];
 #pragma unroll
-        for (int j = 6; j >= 0; --j) q = fma(q, x, A[j * kCellCap]);
+        for (int j = kCellOrder - 1; j >= 0; --j) q = fma(q, x, A[j * kCellCap]);
         v = q;
-    } else {                                                            // beyond the cell arrays (tau spans > 22 decades): exact sum
+    } else {                                                            // beyond the cell arrays (tau spans > 33 decades): exact sum
         v = 0.0;
         const double* rec = sc.rec + (int64_t)p * sc.Mp * pb_rec_stride(1);
         const int64_t n_rec = (int64_t)sc.n_act[p] * kChordTile;
@@ -804,26 +803,31 @@ __global__ void __launch_bounds__(256) cell_eval_kernel(const DevScene* __restri
 }
 
 int cell_chord_splits(int sm_count, int n_phase, int n_tiles) {
-    int n_cs = (sm_count * 16 + 20 * n_phase - 1) / (20 * n_phase);     // ~20 cell blocks per phase are in use (650 cells)
+    int n_cs = (sm_count * 16 + 7 * n_phase - 1) / (7 * n_phase);       // ~7 cell blocks per phase are in use (~215 cells)
     if (n_cs > n_tiles / 2) n_cs = n_tiles / 2;
     return n_cs < 1 ? 1 : n_cs;
 }
+static size_t cell_round(size_t b) { return (b + 255) & ~size_t(255); }
 size_t cell_scratch_bytes(int n_phase, int n_cs) {
-    return ((size_t)n_phase * sizeof(int2) + 255 & ~size_t(255)) + (size_t)n_phase * (n_cs + 1) * 9 * kCellCap * sizeof(double);
+    return cell_round((size_t)n_phase * sizeof(int2)) + cell_round((size_t)n_phase * (kCellCap / 32) * sizeof(unsigned)) +
+           (size_t)n_phase * ((size_t)n_cs * kCellSums + kCellSums + 2) * kCellCap * sizeof(double);
 }
-// nsig, winmax (sigma_phase_kernel) and the records, thin totals, w0 (compact_kernel) of the run -> R
+// where compact_kernel leaves the cell ranges / finds the counters to clear: set before launch_compact
+void cell_bind(TransitParams& prm, void* scratch) {
+    prm.cell_range = reinterpret_cast<int2*>(scratch);
+    prm.cell_count = reinterpret_cast<unsigned*>(reinterpret_cast<char*>(scratch) + cell_round((size_t)prm.n_phase * sizeof(int2)));
+}
+// nsig (sigma_phase_kernel) and the records, thin totals, w0, cell ranges (compact_kernel) of the run -> R
 cudaError_t launch_cells(const DevScene* d_scene, const TransitParams& prm, int n_cs, void* scratch, cudaStream_t st, int* n_launch) {
-    int2* range = reinterpret_cast<int2*>(scratch);
-    double* partial = reinterpret_cast<double*>(reinterpret_cast<char*>(scratch) + (((size_t)prm.n_phase * sizeof(int2) + 255) & ~size_t(255)));
-    double* sums = partial + (size_t)prm.n_phase * n_cs * 9 * kCellCap;
-    const size_t smem = (kExpBigEntries + 2 * pb_rec_stride(1) * kChordTile + 8 * 9 * 32) * sizeof(double);
+    double* partial = reinterpret_cast<double*>(reinterpret_cast<char*>(scratch) + cell_round((size_t)prm.n_phase * sizeof(int2)) +
+                                                cell_round((size_t)prm.n_phase * (kCellCap / 32) * sizeof(unsigned)));
+    double* sums = partial + (size_t)prm.n_phase * n_cs * kCellSums * kCellCap;
+    const size_t smem = (kExpBigEntries + 2 * pb_rec_stride(1) * kChordTile) * sizeof(double);
     cudaError_t e = cudaFuncSetAttribute(cell_moment_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    cell_range_kernel<<<prm.n_phase, 256, 0, st>>>(d_scene, prm, range);
-    cell_moment_kernel<<<dim3(kCellCap / 32, (unsigned)prm.n_phase, (unsigned)n_cs), 256, smem, st>>>(d_scene, prm, range, partial, n_cs);
-    cell_reduce_kernel<<<dim3(4, (unsigned)prm.n_phase), 256, 0, st>>>(prm, range, partial, sums, n_cs);
-    cell_eval_kernel<<<dim3((unsigned)((prm.n_wav_sel + 255) / 256), (unsigned)prm.n_phase), 256, 0, st>>>(d_scene, prm, range, sums);
-    *n_launch = 4;
+    cell_moment_kernel<<<dim3(kCellCap / 32, (unsigned)prm.n_phase, (unsigned)n_cs), 256, smem, st>>>(d_scene, prm, partial, sums, n_cs);
+    cell_eval_kernel<<<dim3((unsigned)((prm.n_wav_sel + 255) / 256), (unsigned)prm.n_phase), 256, 0, st>>>(d_scene, prm, sums);
+    *n_launch = 2;
     return cudaGetLastError();
 }
 

@@ -187,7 +187,9 @@ def test_c5_regime_boundary_columns_against_oracle(nist_rows):
         w = np.concatenate([a, np.full(n_win * 256 - n_wav, np.nan)]).reshape(n_win, 256)
         smw, smin = np.nanmax(w, axis=1), np.nanmin(w, axis=1)
         narrow = (smw - smin) <= (smw + smin) / 40.0      # kCentreEps: Taylor sums about the window's centre (transit_tile_centre)
-        with np.errstate(invalid="ignore"):
+        import warnings
+        with np.errstate(invalid="ignore"), warnings.catch_warnings():
+            warnings.simplefilter("ignore", RuntimeWarning)
             g = w.reshape(n_win, 8, 32)                    # warp g of the CTA owns the window's g-th group of 32 sorted wavelengths
             gmx, gmn = np.nanmax(g, axis=2), np.nanmin(g, axis=2)
             by_group = np.all((gmx - gmn) <= (gmx + gmn) / 40.0, axis=1) & ~np.isnan(g).any(axis=(1, 2))
@@ -208,8 +210,8 @@ def test_c5_regime_boundary_columns_against_oracle(nist_rows):
             for win in (idx[0], idx[len(idx) // 2], idx[-1]):
                 for pos in (win * 256, win * 256 + 128, win * 256 + 255):     # both ends (|x| = 1) and the middle of the window
                     sel.append(int(perm[p, min(pos, n_wav - 1)]))
-        # sigma cells: a in [g^k, g^(k+1)), g = (1 + 1/40)/(1 - 1/40); used from "thin for every chord" (N_max a < 0.125) upwards
-        per_octave = 1.0 / np.log2((1.0 + 1.0 / 40.0) / (1.0 - 1.0 / 40.0))
+        # sigma cells: a in [g^k, g^(k+1)), g = (1 + 3/40)/(1 - 3/40); used from "thin for every chord" (N_max a < 0.125) upwards
+        per_octave = 1.0 / np.log2((1.0 + 3.0 / 40.0) / (1.0 - 3.0 / 40.0))
         live = a[(a * N_hi >= thin_v) & np.isfinite(a)]
         kk = np.floor(np.log2(live) * per_octave).astype(np.int64)
         cells = np.unique(kk)
