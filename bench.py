@@ -365,7 +365,7 @@ def parity_check(spec, tr, R, n_cols=8):
 # ------------------------------------------------------------------------------------------------
 FLOPS_MOMENT_ITEM = 33.0      # kernel (m), per (item, wavelength): d = V1 - V0 (1), fma(tc, d, V0) (2), table exp (12),
                               # Horner of 8 moments (16), e * p (1), accumulate (1)
-FLOPS_CENTRE_PAIR = 37.0      # kernel (c'), sigma cells, per (chord, cell): table exp (11), E = T q (1), u (1), nine sums (1 + 2 + 7 x 3)
+FLOPS_CENTRE_PAIR = 49.0      # kernel (c'), sigma cells, per (chord, cell): table exp (11), E = T q (1), u (1), 13 sums (1 + 2 + 11 x 3)
 FLOPS_MOMENT_BLOCK = 15.0     # kernel (m), per (chord pair, wavelength) besides its items and atoms: table exp (12) + clamp,
                               # subtract the offset sum (1), weight * exp accumulate (2)
 
@@ -547,8 +547,8 @@ def production_launch(kernel_ms, exp_samples, centre_pairs, fps, peak_tflops, wo
             "kernel_ms": kernel_ms, "exp_samples": exp_samples - centre_pairs, "centre_pairs": centre_pairs, "flops": flops,
             "achieved": ach, "frac": ach / peak_tflops,
             "traffic": recorded_traffic(workload, "cell_moment_kernel" if cells else "transit_kernel_production"),
-            "note": ("one table exp + nine Taylor sums per (chord, sigma cell), 37 flops; the per-wavelength Horner evaluation "
-                     "(9 FMAs) is not counted" if cells else
+            "note": ("one table exp + 13 Taylor sums per (chord, sigma cell), 49 flops; the per-wavelength Horner evaluation "
+                     "(12 FMAs) is not counted" if cells else
                      "flops of the samples that take the table exp only; the thin-chord expansions (4 FP64 instructions per chord "
                      "and thread) are not counted") + "; this launch is short and latency-bound, see kernels_ms and DESIGN.md"}
 
@@ -569,7 +569,7 @@ def workload_roofline(name, tr, info, timings, peak_tflops):
                              traffic=recorded_traffic(name, "transit_moment_kernel"))
     fps = executed_flops_per_sample(n_abs)
     pairs = float(np.mean([t.get("centre_pairs", 0) for t in timings]))
-    if pairs > 0.0:     # sigma cells (or narrow sorted windows): one table exp + the nine Taylor sums per (chord, cell)
+    if pairs > 0.0:     # sigma cells (or narrow sorted windows): one table exp + the Taylor sums per (chord, cell)
         flops = fps * (exp_s - pairs) + FLOPS_CENTRE_PAIR * pairs
         return fp64_roofline("cell_moment_kernel + cell_eval_kernel (c': R tabulated per phase on sigma cells), production launch",
                              flops, ms, peak_tflops, centre_pairs=pairs, flops_per_pair=FLOPS_CENTRE_PAIR,

@@ -6,8 +6,9 @@ set -u
 O=gpurun_out
 mkdir -p $O
 NCU="ncu --set full --clock-control none --import-source on"
-run() { # name, kernel regex, count, run_once arguments...
+run() { # name, kernel regex, count, run_once arguments...   (ONLY="name name" in the environment selects captures)
     local name=$1 re=$2 cnt=$3; shift 3
+    if [ -n "${ONLY:-}" ] && ! echo " $ONLY " | grep -q " $name "; then return; fi
     timeout 600 python profiles/run_once.py "$@" > $O/once_$name.log 2>&1 || { echo "run_once $name failed"; tail -3 $O/once_$name.log; return; }
     timeout 900 $NCU -k regex:"$re" -c $cnt -f -o $O/r02_$name python profiles/run_once.py "$@" > $O/ncu_$name.log 2>&1
     echo "$name: rc=$? $(tail -1 $O/once_$name.log | cut -c1-200)"
@@ -20,7 +21,7 @@ echo "bench short rc=$?"
 timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $O/r02_launches_bench_C4.csv \
     python bench.py --steps 2 --warmup 3 --cpu-seconds 0 > $O/ncu_bench.log 2>&1
 echo "bench launch list rc=$?"
-run C4_production  "cell_|transit_kernel|column_cta|compact|sigma_phase|finalize|bucket" 12 C4 1
+run C4_production  "cell_|transit_kernel|column_cta|compact|sigma_phase|finalize|bucket" 10 C4 1
 run C4_bruteforce  "transit_kernel" 1 C4 1 cull=0 mirror=0 thin=0
 run C4_kernel_a    "number_density_rows" 1 C4 1 kernel_a
 run C5_production  "cell_|transit_kernel|column_cta|compact|sigma_phase" 8 C5 1

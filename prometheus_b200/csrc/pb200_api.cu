@@ -34,7 +34,7 @@ cudaError_t launch_transit_general(const DevScene*, const DevScene& host_copy, c
                                    cudaStream_t, int* n_launch);
 void launch_sigma_phase(const DevScene*, const TransitParams&, cudaStream_t);
 void launch_bucket_build(const DevScene*, int sm_count, cudaStream_t);
-cudaError_t launch_compact(const DevScene*, const TransitParams&, bool cull, bool small, cudaStream_t);
+cudaError_t launch_compact(const DevScene*, const TransitParams&, bool cull, int chords_per_phase, cudaStream_t);
 void launch_finalize(const DevScene*, const TransitParams&, int sm_count, cudaStream_t);
 int cell_chord_splits(int sm_count, int n_phase, int n_tiles);
 size_t cell_scratch_bytes(int n_phase, int n_cs);
@@ -894,7 +894,7 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     if (!c->general_path) {   // chord records of kernel (c'), transparent chords culled
         PB_CUDA(c, cudaEventRecord(c->ev_join, c->aux));
         PB_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_join, 0));
-        PB_CUDA(c, launch_compact(c->d_scene, prm, cull, h.M <= 4096, c->stream));
+        PB_CUDA(c, launch_compact(c->d_scene, prm, cull, h.M, c->stream));
         c->launches += 1;
     }
     PB_CUDA(c, cudaGetLastError());

@@ -5,6 +5,8 @@
 // per chord in the x-sum; scenes with molecules -- column_kernel, one warp per chord, which also stores the density
 // rows kernel (m) needs.  Chord axes are a few hundred doubles and live in L1 / shared memory; the only HBM traffic is
 // the coalesced store of the result.
+#include <cooperative_groups.h>
+
 #include "pb200_internal.cuh"
 
 namespace pb200 {
@@ -690,6 +692,190 @@ __global__ void __launch_bounds__(kCompactThreads) compact_kernel(const DevScene
     for (int i = tid; i < prm.n_win; i += kCompactThreads) out[i] = idx[i];
 }
 
+// ---- the same for large sky grids whose kernel needs no window order (sigma cells, sorted windows): a CLUSTER of
+// kCompactCluster CTAs per phase.  One CTA per phase (above) walks 36 000 chords of C5 in 18 rounds of four barriers --
+// 83 us on 21 of 148 SMs.  Here CTA r of the cluster takes the r-th contiguous share of the phase's chords: pass 1 counts
+// its active chords, the counts are exchanged through distributed shared memory (cluster.sync), pass 2 packs the records
+// at base = sum of the counts of the ranks before it -- still chord order, still deterministic.  w0 and the thin totals
+// are added per CTA and then across the ranks in rank order by CTA 0, which also leaves n_act, the padding of the last
+// tile, the statistics and the cell range of the phase.
+constexpr int kCompactCluster = 8;
+constexpr int kCcThreads = 512;
+struct CompactItem { double w; int m; bool alive, active; };
+__device__ __forceinline__ CompactItem pb_compact_item(const DevScene& sc, int S, const double* s_smax, int64_t row0, int q, int n_items,
+                                                       int P, int n2) {
+    CompactItem it{0.0, q, false, false};
+    if (q >= n_items) return it;
+    double bound = 0.0;
+    if (sc.mirror) {
+        const int h = q / (P * sc.n_rho), rem = q - h * (P * sc.n_rho);
+        const int i = rem / sc.n_rho, irho = rem - i * sc.n_rho;
+        it.m = (h * n2 + i) * sc.n_rho + irho;
+        const int ip = n2 - 1 - i;
+        const double wa = sc.w_in[row0 + it.m];
+        if (ip != i) {
+            const int mb = (h * n2 + ip) * sc.n_rho + irho;
+            const double wb = sc.w_in[row0 + mb];
+            if (wa == 0.0) it.m = mb;               // Ncol of a blocked chord is not evaluated: take the mirror's
+            it.w = wa + wb;
+        } else {
+            it.w = wa;
+        }
+    } else {
+        it.w = sc.w_in[row0 + it.m];
+    }
+    for (int a = 0; a < S; ++a) bound = fma(sc.ncol[(int64_t)a * sc.n_orb * sc.Mp + row0 + it.m], s_smax[a], bound);
+    it.alive = (it.w != 0.0);
+    it.active = it.alive && !(bound < 5.5511151231257827e-17);          // 2^-54; NaN -> active
+    return it;
+}
+
+__global__ void __cluster_dims__(kCompactCluster, 1, 1) __launch_bounds__(kCcThreads)
+compact_cluster_kernel(const DevScene* __restrict__ scp, const TransitParams prm, int cull) {
+    namespace cg = cooperative_groups;
+    cg::cluster_group cluster = cg::this_cluster();
+    const DevScene& sc = *scp;
+    const int rank = (int)cluster.block_rank();
+    const int pi = blockIdx.x / kCompactCluster, p = prm.phase_lo + pi;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    constexpr int NW = kCcThreads / 32;
+    const int S = sc.n_abs, R = pb_rec_stride(S);
+    __shared__ double s_smax[kMaxConstituents];
+    __shared__ int s_warp[32];
+    __shared__ int s_cnt, s_base, s_chunk;
+    __shared__ double s_red[7][NW];
+    __shared__ double s_sums[7];
+    if (tid < S) {
+        const double v = __longlong_as_double((long long)sc.smax[(int64_t)tid * sc.n_orb + p]);
+        s_smax[tid] = (cull && v >= 0.0) ? v : __longlong_as_double(0x7ff0000000000000ll);   // negative or NaN: never cull
+    }
+    __syncthreads();
+    const int64_t row0 = (int64_t)p * sc.Mp;
+    double* rec_row = sc.rec + row0 * R;
+    const int n2 = sc.n_phi / 2, P = (n2 + 1) / 2;
+    const int n_items = sc.mirror ? 2 * P * sc.n_rho : sc.Mp;
+    const int per_cta = ((n_items + kCompactCluster * kCcThreads - 1) / (kCompactCluster * kCcThreads)) * kCcThreads;
+    const int i0 = rank * per_cta;
+    int i1 = i0 + per_cta;
+    if (i1 > n_items) i1 = n_items;
+
+    // ---- pass 1: this CTA's number of active chords ------------------------------------------------------------
+    int cnt = 0;
+    for (int q = i0 + tid; q < i1; q += kCcThreads) cnt += pb_compact_item(sc, S, s_smax, row0, q, n_items, P, n2).active ? 1 : 0;
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, d);
+    if (lane == 0) s_warp[wid] = cnt;
+    __syncthreads();
+    if (tid == 0) {
+        int t = 0;
+        for (int i = 0; i < NW; ++i) t += s_warp[i];
+        s_cnt = t;
+    }
+    cluster.sync();
+    int base0 = 0, n_rec = 0;
+    for (int r = 0; r < kCompactCluster; ++r) {
+        const int c = *cluster.map_shared_rank(&s_cnt, r);
+        if (r < rank) base0 += c;
+        n_rec += c;
+    }
+    if (tid == 0) s_base = base0;
+    __syncthreads();
+
+    // ---- pass 2: pack the records of this share in chord order ---------------------------------------------------
+    double w0 = 0.0;
+    double tt[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    for (int m0 = i0; m0 < i1; m0 += kCcThreads) {
+        const CompactItem it = pb_compact_item(sc, S, s_smax, row0, (m0 + tid < i1) ? m0 + tid : n_items, n_items, P, n2);
+        if (it.alive && !it.active) w0 += it.w;
+        const unsigned bal = __ballot_sync(0xffffffffu, it.active);
+        if (lane == 0) s_warp[wid] = __popc(bal);
+        __syncthreads();
+        if (wid == 0) {   // exclusive scan of the warp counts
+            const int c = (lane < NW) ? s_warp[lane] : 0;
+            int x = c;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int y = __shfl_up_sync(0xffffffffu, x, d);
+                if (lane >= d) x += y;
+            }
+            s_warp[lane] = x - c;
+            if (lane == 31) s_chunk = x;
+        }
+        __syncthreads();
+        const int base = s_base;
+        if (it.active) {
+            double* r = rec_row + (int64_t)(base + s_warp[wid] + __popc(bal & ((1u << lane) - 1u))) * R;
+            const double w = it.w, w1 = w * kExpBigC1, w2 = w * kExpBigC2;
+            r[0] = w; r[1] = w1; r[2] = w2;
+            for (int a = 0; a < S; ++a) r[3 + a] = sc.ncol[(int64_t)a * sc.n_orb * sc.Mp + row0 + it.m];
+            if (3 + S < R) r[3 + S] = 0.0;
+            if (S <= 2) {   // same operations as ThinSums::add of kernel (c')
+                const double N0 = r[3], N1 = (S == 2) ? r[4] : 0.0;
+                tt[0] += w;
+                tt[1] = fma(N0, w1, tt[1]);
+                tt[2] = fma(N1, w1, tt[2]);
+                const double t0 = N0 * w2, t1 = N1 * w2;
+                tt[3] = fma(t0, N0, tt[3]);
+                tt[4] = fma(t0, N1, tt[4]);
+                tt[5] = fma(t1, N1, tt[5]);
+            }
+        }
+        __syncthreads();
+        if (tid == 0) s_base = base + s_chunk;
+        __syncthreads();
+    }
+    // this CTA's sums (fixed order), then CTA 0 adds the ranks in rank order
+#pragma unroll
+    for (int k = 0; k < 7; ++k) {
+        const double v = pb_warp_sum(k == 0 ? w0 : tt[k == 0 ? 0 : k - 1]);
+        if (lane == 0) s_red[k][wid] = v;
+    }
+    __syncthreads();
+    if (tid < 7) {
+        double t = 0.0;
+        for (int i = 0; i < NW; ++i) t += s_red[tid][i];
+        s_sums[tid] = t;
+    }
+    cluster.sync();
+    if (rank == 0) {
+        const int n_tiles = (n_rec + kChordTile - 1) / kChordTile;
+        for (int i = n_rec * R + tid; i < n_tiles * kChordTile * R; i += kCcThreads) rec_row[i] = 0.0;   // padding
+        if (tid < 7) {
+            double t = 0.0;
+            for (int r = 0; r < kCompactCluster; ++r) t += cluster.map_shared_rank(s_sums, r)[tid];
+            if (tid == 0) sc.w0[p] = t; else sc.thin_tot[(int64_t)p * 8 + tid - 1] = t;
+        }
+        if (tid == 0) {
+            sc.n_act[p] = n_tiles;
+            atomicAdd(sc.stat + 1, (unsigned long long)n_tiles * kChordTile);
+        }
+        if (tid < S) sc.smax[(int64_t)tid * sc.n_orb + p] = 0ull;   // clean for the atomicMax of the next run (every rank has read it)
+        if (prm.cell_range != nullptr) {   // as in compact_kernel
+            __shared__ double s_cmx[NW];
+            double mx = 0.0;
+            for (int i = tid; i < prm.n_win; i += kCcThreads) mx = fmax(mx, prm.winmax[(int64_t)pi * prm.n_win + i]);
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, d));
+            if (lane == 0) s_cmx[wid] = mx;
+            if (tid < kCellCap / 32) prm.cell_count[pi * (kCellCap / 32) + tid] = 0u;
+            __syncthreads();
+            if (tid == 0) {
+                for (int i = 1; i < NW; ++i) mx = fmax(mx, s_cmx[i]);
+                const double nmax = __longlong_as_double((long long)sc.nmax[p]);
+                int2 rg = make_int2(0, 0);
+                const double a_thin = prm.thin_v / nmax;
+                if (nmax > 0.0 && n_tiles > 0 && mx >= a_thin && a_thin > 0.0) {
+                    rg.x = pb_cell_index(a_thin);
+                    const int n = (mx < __longlong_as_double(0x7ff0000000000000ll)) ? pb_cell_index(mx) - rg.x + 1 : kCellCap;
+                    rg.y = n < 1 ? 1 : (n > kCellCap ? kCellCap : n);
+                }
+                prm.cell_range[pi] = rg;
+            }
+        }
+    }
+    cluster.sync();   // the other ranks' shared memory stays alive until CTA 0 has read it
+}
+
 // ---- calculateNumberDensity materialised (chord-major, reference chord order) ------------------
 // out[c*n_x + ix], c = m*n_orb + p.  One warp per chord: rows are written as coalesced 8-byte stores.
 __global__ void __launch_bounds__(256)
@@ -901,7 +1087,8 @@ void launch_column(const DevScene* d_scene, int Mp, int phase_lo, int n_phase, i
     }
 }
 constexpr int kMaxWindows = 8192;
-cudaError_t launch_compact(const DevScene* d_scene, const TransitParams& prm, bool cull, bool small, cudaStream_t st) {
+cudaError_t launch_compact(const DevScene* d_scene, const TransitParams& prm, bool cull, int chords_per_phase, cudaStream_t st) {
+    const bool small = chords_per_phase <= 4096;
     int n_pow2 = 1;
     while (n_pow2 < prm.n_win) n_pow2 <<= 1;
     if (n_pow2 > kMaxWindows) n_pow2 = 0;
@@ -910,6 +1097,12 @@ cudaError_t launch_compact(const DevScene* d_scene, const TransitParams& prm, bo
         cudaError_t e = cudaFuncSetAttribute(compact_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(compact_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
+    }
+    // no window order wanted (sigma cells, sorted windows) and a large sky grid: a cluster of CTAs per phase (C5, 36 000 chords
+    // per phase; at C4's 9 000 the single CTA is as fast and the cluster launch costs more than it saves)
+    if (chords_per_phase >= (1 << 14) && prm.order == nullptr) {
+        compact_cluster_kernel<<<prm.n_phase * kCompactCluster, kCcThreads, 0, st>>>(d_scene, prm, cull ? 1 : 0);
+        return cudaGetLastError();
     }
     if (small) compact_kernel<256><<<prm.n_phase, 256, smem, st>>>(d_scene, prm, cull ? 1 : 0, n_pow2);
     else compact_kernel<1024><<<prm.n_phase, 1024, smem, st>>>(d_scene, prm, cull ? 1 : 0, n_pow2);
