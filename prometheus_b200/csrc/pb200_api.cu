@@ -38,7 +38,8 @@ cudaError_t launch_compact(const DevScene*, const TransitParams&, bool cull, int
 void launch_finalize(const DevScene*, const TransitParams&, int sm_count, cudaStream_t);
 int cell_chord_splits(int sm_count, int n_phase, int n_tiles);
 size_t cell_scratch_bytes(int n_phase, int n_cs);
-cudaError_t launch_cells(const DevScene* d_scene, const TransitParams& prm, int n_cs, void* scratch, cudaStream_t st, int* n_launch);
+cudaError_t launch_cell_moments(const DevScene* d_scene, const TransitParams& prm, int n_cs, void* scratch, cudaStream_t st);
+cudaError_t launch_cell_eval(const DevScene* d_scene, const TransitParams& prm, int n_cs, void* scratch, cudaStream_t st);
 void cell_bind(TransitParams& prm, void* scratch);
 void launch_sigma_lookup(const double*, const double*, int64_t, double, const double*, int64_t, double*, int,
                          cudaStream_t);
@@ -893,7 +894,9 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
     c->launches += 1;
     if (!c->general_path) {   // chord records of kernel (c'), transparent chords culled
         PB_CUDA(c, cudaEventRecord(c->ev_join, c->aux));
-        PB_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_join, 0));
+        // sigma cells: nothing before cell_eval_kernel reads what sigma_phase_kernel writes (the compaction and the cell
+        // sums bound sigma by the tables' maxima), so the join moves down to the evaluation
+        if (!cells) PB_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_join, 0));
         PB_CUDA(c, launch_compact(c->d_scene, prm, cull, h.M, c->stream));
         c->launches += 1;
     }
@@ -970,10 +973,13 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
         if (e != cudaSuccess) return fail(c, PB200_ERR_CUDA, "transit (general) launch: %s", cudaGetErrorString(e));
         c->launches += n_launch;
     } else if (cells) {
-        int n_launch = 0;
-        cudaError_t e = launch_cells(c->d_scene, prm, n_cs, sort_base, c->stream, &n_launch);
+        cudaError_t e = launch_cell_moments(c->d_scene, prm, n_cs, sort_base, c->stream);
+        if (e == cudaSuccess) {
+            PB_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_join, 0));
+            e = launch_cell_eval(c->d_scene, prm, n_cs, sort_base, c->stream);
+        }
         if (e != cudaSuccess) return fail(c, PB200_ERR_CUDA, "sigma cells launch: %s", cudaGetErrorString(e));
-        c->launches += n_launch;
+        c->launches += 2;
     } else {
         cudaError_t e = launch_transit(c->d_scene, h.n_abs, prm, c->stream);
         if (e != cudaSuccess) return fail(c, PB200_ERR_CUDA, "transit launch: %s", cudaGetErrorString(e));

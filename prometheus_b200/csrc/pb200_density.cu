@@ -386,14 +386,7 @@ column_cta_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, i
         // upper bound of the absorber's cross section at ANY wavelength: sum_k chi_k (10^max(tab_y_k) - offset_k) (the
         // table lookup is a convex combination of table values).  Independent of sigma_phase_kernel, which therefore
         // runs beside this kernel; compact_kernel's own test uses the run's exact maxima, which are not larger.
-        const int g = tid - 32;
-        double sm = 0.0;
-        for (int c = sc.abs_first[g]; c < sc.abs_first[g] + sc.abs_count[g]; ++c) {
-            const unsigned long long b = sc.tab_ymax[c];
-            const double ymax = (b == 0ull || b == ~0ull) ? __longlong_as_double(0x7ff0000000000000ll) : pb_from_ordered_bits(b);
-            sm += sc.cons[c].chi * (exp10(ymax) - sc.cons[c].offset);
-        }
-        s_sigmax[g] = (sm >= 0.0) ? sm * (1.0 + 1e-12) : __longlong_as_double(0x7ff0000000000000ll);   // negative or NaN: never cull
+        s_sigmax[tid - 32] = pb_abs_sigma_bound(sc, tid - 32);   // negative or NaN: +inf, never cull
     }
     __syncthreads();
     bool skip = false;
@@ -514,8 +507,9 @@ __global__ void __launch_bounds__(kCompactThreads) compact_kernel(const DevScene
     __shared__ int s_warp[32];
     __shared__ double s_part[32];
     __shared__ int s_base;
+    const bool cells = prm.cell_range != nullptr;   // sigma cells: sigma_phase_kernel runs BESIDE this kernel, the bound comes from the tables
     if (tid < S) {
-        const double v = __longlong_as_double((long long)sc.smax[(int64_t)tid * sc.n_orb + p]);
+        const double v = cells ? pb_abs_sigma_bound(sc, tid) : __longlong_as_double((long long)sc.smax[(int64_t)tid * sc.n_orb + p]);
         s_smax[tid] = (cull && v >= 0.0) ? v : __longlong_as_double(0x7ff0000000000000ll);   // negative or NaN: never cull
     }
     if (tid == 0) s_base = 0;
@@ -617,7 +611,7 @@ __global__ void __launch_bounds__(kCompactThreads) compact_kernel(const DevScene
         sc.n_act[p] = n_tiles;
         atomicAdd(sc.stat + 1, (unsigned long long)n_tiles * kChordTile);
     }
-    if (tid < S) sc.smax[(int64_t)tid * sc.n_orb + p] = 0ull;   // clean for the atomicMax of the next run
+    if (tid < S && !cells) sc.smax[(int64_t)tid * sc.n_orb + p] = 0ull;   // clean for the atomicMax of the next run
 
     // ---- order of the wavelength windows of this phase for kernel (c') -------------------------------
     // A CTA of kernel (c') owns one window; windows in a line core take the table exp on most chords, windows
@@ -628,16 +622,9 @@ __global__ void __launch_bounds__(kCompactThreads) compact_kernel(const DevScene
     // ---- sigma cells (one absorber): the cells this phase needs, from "thin for every chord" (N_max a < thin_v: those
     // wavelengths take the order-2 totals above) up to the phase's largest |nsig| -------------------------------------------
     if (prm.cell_range != nullptr) {
-        __shared__ double s_cmx[32];
-        double mx = 0.0;
-        for (int i = tid; i < prm.n_win; i += kCompactThreads) mx = fmax(mx, prm.winmax[(int64_t)blockIdx.x * prm.n_win + i]);
-#pragma unroll
-        for (int d = 16; d > 0; d >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, d));
-        if (lane == 0) s_cmx[wid] = mx;
         if (tid < kCellCap / 32) prm.cell_count[blockIdx.x * (kCellCap / 32) + tid] = 0u;
-        __syncthreads();
         if (tid == 0) {
-            for (int i = 1; i < kCompactThreads / 32; ++i) mx = fmax(mx, s_cmx[i]);
+            const double mx = pb_abs_sigma_bound(sc, 0) * kExpBigScale;   // largest |nsig| any wavelength can have
             const double nmax = __longlong_as_double((long long)sc.nmax[p]);
             int2 r = make_int2(0, 0);
             const double a_thin = prm.thin_v / nmax;
@@ -745,8 +732,9 @@ compact_cluster_kernel(const DevScene* __restrict__ scp, const TransitParams prm
     __shared__ int s_cnt, s_base, s_chunk;
     __shared__ double s_red[7][NW];
     __shared__ double s_sums[7];
+    const bool cells = prm.cell_range != nullptr;   // as in compact_kernel
     if (tid < S) {
-        const double v = __longlong_as_double((long long)sc.smax[(int64_t)tid * sc.n_orb + p]);
+        const double v = cells ? pb_abs_sigma_bound(sc, tid) : __longlong_as_double((long long)sc.smax[(int64_t)tid * sc.n_orb + p]);
         s_smax[tid] = (cull && v >= 0.0) ? v : __longlong_as_double(0x7ff0000000000000ll);   // negative or NaN: never cull
     }
     __syncthreads();
@@ -849,18 +837,11 @@ compact_cluster_kernel(const DevScene* __restrict__ scp, const TransitParams prm
             sc.n_act[p] = n_tiles;
             atomicAdd(sc.stat + 1, (unsigned long long)n_tiles * kChordTile);
         }
-        if (tid < S) sc.smax[(int64_t)tid * sc.n_orb + p] = 0ull;   // clean for the atomicMax of the next run (every rank has read it)
+        if (tid < S && !cells) sc.smax[(int64_t)tid * sc.n_orb + p] = 0ull;   // clean for the atomicMax of the next run (every rank has read it)
         if (prm.cell_range != nullptr) {   // as in compact_kernel
-            __shared__ double s_cmx[NW];
-            double mx = 0.0;
-            for (int i = tid; i < prm.n_win; i += kCcThreads) mx = fmax(mx, prm.winmax[(int64_t)pi * prm.n_win + i]);
-#pragma unroll
-            for (int d = 16; d > 0; d >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, d));
-            if (lane == 0) s_cmx[wid] = mx;
             if (tid < kCellCap / 32) prm.cell_count[pi * (kCellCap / 32) + tid] = 0u;
-            __syncthreads();
             if (tid == 0) {
-                for (int i = 1; i < NW; ++i) mx = fmax(mx, s_cmx[i]);
+                const double mx = pb_abs_sigma_bound(sc, 0) * kExpBigScale;
                 const double nmax = __longlong_as_double((long long)sc.nmax[p]);
                 int2 rg = make_int2(0, 0);
                 const double a_thin = prm.thin_v / nmax;

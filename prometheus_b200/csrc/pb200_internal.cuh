@@ -161,6 +161,18 @@ struct TransitParams {
     unsigned* cell_count; // [n_phase][kCellCap / 32] arrival counters of cell_moment_kernel's chord-axis splits (zeroed by compact_kernel)
 };
 
+// Upper bound of absorber g's cross section at ANY wavelength: sum_k chi_k (10^max(tab_y_k) - offset_k) -- the table lookup is
+// a convex combination of table values (tab_ymax: bucket_build_kernel).  +inf where a table holds a NaN or the sum is negative.
+__device__ __forceinline__ double pb_abs_sigma_bound(const DevScene& sc, int g) {
+    double sm = 0.0;
+    for (int c = sc.abs_first[g]; c < sc.abs_first[g] + sc.abs_count[g]; ++c) {
+        const unsigned long long b = sc.tab_ymax[c];
+        const double ymax = (b == 0ull || b == ~0ull) ? __longlong_as_double(0x7ff0000000000000ll) : pb_from_ordered_bits(b);
+        sm += sc.cons[c].chi * (exp10(ymax) - sc.cons[c].offset);
+    }
+    return (sm >= 0.0) ? sm * (1.0 + 1e-12) : __longlong_as_double(0x7ff0000000000000ll);
+}
+
 // Sigma cells (pb200_transit.cu): cell k holds the scaled cross sections a = |nsig| in [g^k, g^(k+1)), g = (1 + eps)/(1 - eps),
 // eps = 3/40; Taylor sums of order kCellOrder about the centre (truncation < 7.2e-16 of a chord's weight, see cell_moment_kernel)
 constexpr int kCellCap = 512;                               // cells per phase the arrays hold (g^512 = 2.6e33 in sigma)

@@ -100,7 +100,9 @@ __global__ void __launch_bounds__(256) sigma_phase_kernel(const DevScene* __rest
             bits = o > bits ? o : bits;
             ns_abs = fmax(ns_abs, __shfl_xor_sync(0xffffffffu, ns_abs, d));
         }
-        if (lane == 0 && bits) atomicMax(sc.smax + (int64_t)a * sc.n_orb + p, bits);
+        // (sigma cells: this kernel runs beside the column kernel, the compaction AND the cell sums, none of which waits for it --
+        //  they bound sigma by the tables' maxima; only cell_eval_kernel reads nsig)
+        if (lane == 0 && bits && prm.cell_range == nullptr) atomicMax(sc.smax + (int64_t)a * sc.n_orb + p, bits);
         // window maxima of |nsig_a| for the thin test / the thickness order of kernel (c')
         __syncthreads();
         if (lane == 0) s_wmax[wid] = ns_abs;
@@ -817,17 +819,24 @@ void cell_bind(TransitParams& prm, void* scratch) {
     prm.cell_range = reinterpret_cast<int2*>(scratch);
     prm.cell_count = reinterpret_cast<unsigned*>(reinterpret_cast<char*>(scratch) + cell_round((size_t)prm.n_phase * sizeof(int2)));
 }
-// nsig (sigma_phase_kernel) and the records, thin totals, w0, cell ranges (compact_kernel) of the run -> R
-cudaError_t launch_cells(const DevScene* d_scene, const TransitParams& prm, int n_cs, void* scratch, cudaStream_t st, int* n_launch) {
-    double* partial = reinterpret_cast<double*>(reinterpret_cast<char*>(scratch) + cell_round((size_t)prm.n_phase * sizeof(int2)) +
-                                                cell_round((size_t)prm.n_phase * (kCellCap / 32) * sizeof(unsigned)));
+static double* cell_partial(const TransitParams& prm, void* scratch) {
+    return reinterpret_cast<double*>(reinterpret_cast<char*>(scratch) + cell_round((size_t)prm.n_phase * sizeof(int2)) +
+                                     cell_round((size_t)prm.n_phase * (kCellCap / 32) * sizeof(unsigned)));
+}
+// the records, thin totals, w0 and cell ranges of the run (compaction) -> the cells' Taylor sums; does not need nsig
+cudaError_t launch_cell_moments(const DevScene* d_scene, const TransitParams& prm, int n_cs, void* scratch, cudaStream_t st) {
+    double* partial = cell_partial(prm, scratch);
     double* sums = partial + (size_t)prm.n_phase * n_cs * kCellSums * kCellCap;
     const size_t smem = (kExpBigEntries + 2 * pb_rec_stride(1) * kChordTile) * sizeof(double);
     cudaError_t e = cudaFuncSetAttribute(cell_moment_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     cell_moment_kernel<<<dim3(kCellCap / 32, (unsigned)prm.n_phase, (unsigned)n_cs), 256, smem, st>>>(d_scene, prm, partial, sums, n_cs);
+    return cudaGetLastError();
+}
+// nsig (sigma_phase_kernel) + the sums -> R
+cudaError_t launch_cell_eval(const DevScene* d_scene, const TransitParams& prm, int n_cs, void* scratch, cudaStream_t st) {
+    const double* sums = cell_partial(prm, scratch) + (size_t)prm.n_phase * n_cs * kCellSums * kCellCap;
     cell_eval_kernel<<<dim3((unsigned)((prm.n_wav_sel + 255) / 256), (unsigned)prm.n_phase), 256, 0, st>>>(d_scene, prm, sums);
-    *n_launch = 2;
     return cudaGetLastError();
 }
 
