@@ -641,7 +641,8 @@ def strong_scaling(name, torch, dist, ctx, flush, dev, rank, world, local, peak_
             kern = []
             st.compute_tile = pbd.tile_function(ctx, axis, world, rank, want_timing=True, sink=kern)
             ms_ng = timed(lambda: st.run_device(gather=False), steps)
-            mine = {k: float(np.mean([t[k] for t in kern[warmup:]])) for k in ("column_ms", "transit_ms", "finalize_ms")}
+            mine = {k: (float(np.mean([t[k] for t in kern[warmup:]])) if len(kern) > warmup else None)
+                    for k in ("column_ms", "transit_ms", "finalize_ms")}
             st.compute_tile = pbd.tile_function(ctx, axis, world, rank)
 
             def step():
