@@ -63,10 +63,16 @@ def main(argv):
     print(name, {k: round(v, 4) if isinstance(v, float) else v for k, v in t.items()})
     if "kernel_a" in argv:
         dens = torch.empty(info["n_chords"] * info["n_x"], dtype=torch.float64, device="cuda:0")
-        for _ in range(runs):
-            ctx.number_density_device(0, dens.data_ptr())
-        ctx.synchronize()
-        torch.cuda.synchronize()
+        ctx.set_stream(torch.cuda.current_stream().cuda_stream)
+        ms = []
+        for _ in range(runs + 3):
+            flush.zero_()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(); ctx.number_density_device(0, dens.data_ptr()); b.record()
+            torch.cuda.synchronize()
+            ms.append(a.elapsed_time(b))
+        t = float(np.mean(ms[3:]))
+        print("kernel_a", name, "ms", round(t, 4), "GB/s", round(8.0 * dens.numel() / t / 1e6, 1))
 
 
 if __name__ == "__main__":

@@ -906,7 +906,27 @@ __device__ __forceinline__ void pb_lane_rows(const ScnConst& k, const double* __
     // on the spot (a rarely taken branch after the pair, not a call inside the arithmetic)
     bool rare = false;
     if (vec) {
-        for (int ix = 2 * l8; ix < n_x; ix += 2 * kColLanes) {     // n_x is even here
+        int ix = 2 * l8;
+        if constexpr (XSH) {
+            // four samples in flight per lane (two 16-byte stores): the chain of one sample is ~24 dependent FP64 instructions
+            for (; ix + 2 * kColLanes < n_x; ix += 4 * kColLanes) {
+                const double2 xa = *reinterpret_cast<const double2*>(xs + ix), xb = *reinterpret_cast<const double2*>(xs + ix + 2 * kColLanes);
+                const double u0 = xa.x - k.cx, u1 = xa.y - k.cx, u2 = xb.x - k.cx, u3 = xb.y - k.cx;
+                const double d0 = u0 * u0, d1 = u1 * u1, d2 = u2 * u2, d3 = u3 * u3;
+                double t0 = pb_term<TYPE, true>(k, big, ltab, d0, cc, rare);
+                double t1 = pb_term<TYPE, true>(k, big, ltab, d1, cc, rare);
+                double t2 = pb_term<TYPE, true>(k, big, ltab, d2, cc, rare);
+                double t3 = pb_term<TYPE, true>(k, big, ltab, d3, cc, rare);
+                if (rare) {
+                    t0 = pb_term_exact<TYPE>(k, ltab, d0, cc); t1 = pb_term_exact<TYPE>(k, ltab, d1, cc);
+                    t2 = pb_term_exact<TYPE>(k, ltab, d2, cc); t3 = pb_term_exact<TYPE>(k, ltab, d3, cc);
+                    rare = false;
+                }
+                *reinterpret_cast<double2*>(row + ix) = make_double2(pre * t0, pre * t1);
+                *reinterpret_cast<double2*>(row + ix + 2 * kColLanes) = make_double2(pre * t2, pre * t3);
+            }
+        }
+        for (; ix < n_x; ix += 2 * kColLanes) {     // n_x is even here
             double x0, x1;
             if constexpr (XSH) { const double2 xx = *reinterpret_cast<const double2*>(xs + ix); x0 = xx.x; x1 = xx.y; }
             else { x0 = xs[ix]; x1 = xs[ix + 1]; }
@@ -940,7 +960,7 @@ __device__ __forceinline__ void pb_lane_rows_any(const ScnConst& k, const double
     }
 }
 
-__global__ void __launch_bounds__(kRowsCta, 4)
+__global__ void __launch_bounds__(kRowsCta, 3)
 number_density_rows_kernel(const DevScene* __restrict__ scp, int scenario, double* __restrict__ out, int64_t n_tiles,
                            unsigned long long* __restrict__ next_tile) {
     const DevScene& sc = *scp;
@@ -1096,7 +1116,7 @@ void launch_number_density_grid(const DevScene* d_scene, int64_t n_chords, int s
 void launch_number_density_thread(const DevScene* d_scene, int64_t n_chords, int n_x, int scenario, double* out, int sm_count,
                                   unsigned long long* next_tile, cudaStream_t st) {
     const int64_t n_tiles = (n_chords + kRowsCta - 1) / kRowsCta;
-    const int64_t slots = (int64_t)sm_count * 4;     // resident CTAs (64 registers x 256 threads)
+    const int64_t slots = (int64_t)sm_count * 3;     // resident CTAs (<= 85 registers x 256 threads)
     const int64_t ctas = n_tiles < slots ? n_tiles : slots;
     cudaMemsetAsync(next_tile, 0, sizeof(unsigned long long), st);
     const size_t smem = (kExpBigEntries + (n_x <= kRowsMaxXs ? ((n_x + 1) & ~1) : 0)) * sizeof(double);
