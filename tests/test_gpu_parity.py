@@ -533,8 +533,9 @@ def test_narrow_sorted_windows_as_taylor_sums(nist_rows):
         with ctx.options(sort=1, centre=centre):
             tile, _ = ctx.run(1, 2, 3, n_wav - 11)
         assert np.max(np.abs(tile - R[centre][1:2, 3:n_wav - 11])) < 5e-14, centre
-    # the same scene made opaque and transparent: the cell grid follows the column densities
-    for scale in (1e6, 1e-9):
+    # the same scene made opaque, transparent, and so opaque that tau spans more than the 512 cells of the arrays (2.6e33):
+    # the cell grid follows the column densities; the wavelengths beyond the arrays take the exact sum of cell_eval_kernel
+    for scale in (1e6, 1e-9, 1e31):
         spec2 = workloads.get("C4s")
         spec2["wavelength"] = list(workloads.get("C4")["wavelength"])
         for scn in spec2["scenarios"]:
