@@ -865,11 +865,15 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
         // statistics are reset by sigma_phase_kernel: no memset nodes in the run
         // sigma_phase (+ the sort) and the column kernel do not depend on each other (the column kernel bounds sigma by
         // the tables' maxima): fork -- sigma on the auxiliary stream, column on the main one -- and join before compaction
-        PB_CUDA(c, cudaEventRecord(c->ev_fork, c->stream));
-        PB_CUDA(c, cudaStreamWaitEvent(c->aux, c->ev_fork, 0));
-        sig_stream = c->aux;
-        launch_sigma_phase(c->d_scene, prm, sig_stream);
-        c->launches += 1;
+        // (sigma cells: no sigma_phase_kernel at all -- the compaction and the cell sums bound sigma by the tables' maxima,
+        //  cell_eval_kernel looks sigma(p, lambda) up where it uses it)
+        if (!cells) {
+            PB_CUDA(c, cudaEventRecord(c->ev_fork, c->stream));
+            PB_CUDA(c, cudaStreamWaitEvent(c->aux, c->ev_fork, 0));
+            sig_stream = c->aux;
+            launch_sigma_phase(c->d_scene, prm, sig_stream);
+            c->launches += 1;
+        }
         if (sorted) {
             auto take = [&](size_t bytes) { char* p0 = sort_base; sort_base += (bytes + al) & ~al; return p0; };
             double* nsig_sorted = reinterpret_cast<double*>(take((size_t)n_out * 8));
@@ -893,10 +897,10 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
                   c->general_path ? 0 : (cull ? 1 : 2));
     c->launches += 1;
     if (!c->general_path) {   // chord records of kernel (c'), transparent chords culled
-        PB_CUDA(c, cudaEventRecord(c->ev_join, c->aux));
-        // sigma cells: nothing before cell_eval_kernel reads what sigma_phase_kernel writes (the compaction and the cell
-        // sums bound sigma by the tables' maxima), so the join moves down to the evaluation
-        if (!cells) PB_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_join, 0));
+        if (!cells) {
+            PB_CUDA(c, cudaEventRecord(c->ev_join, c->aux));
+            PB_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_join, 0));
+        }
         PB_CUDA(c, launch_compact(c->d_scene, prm, cull, h.M, c->stream));
         c->launches += 1;
     }
@@ -974,10 +978,7 @@ int enqueue_run(pb200_ctx* c, int phase_lo, int phase_hi, int64_t wav_lo, int64_
         c->launches += n_launch;
     } else if (cells) {
         cudaError_t e = launch_cell_moments(c->d_scene, prm, n_cs, sort_base, c->stream);
-        if (e == cudaSuccess) {
-            PB_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_join, 0));
-            e = launch_cell_eval(c->d_scene, prm, n_cs, sort_base, c->stream);
-        }
+        if (e == cudaSuccess) e = launch_cell_eval(c->d_scene, prm, n_cs, sort_base, c->stream);
         if (e != cudaSuccess) return fail(c, PB200_ERR_CUDA, "sigma cells launch: %s", cudaGetErrorString(e));
         c->launches += 2;
     } else {

@@ -380,6 +380,8 @@ column_cta_kernel(const DevScene* __restrict__ scp, int phase_lo, int n_phase, i
         }
     }
     sc.w_in[row] = wv;
+    // run statistics (also reset by sigma_phase_kernel, which the sigma-cell route does not launch): before compaction adds to them
+    if (run_mode && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) { sc.stat[1] = 0ull; sc.stat[2] = 0ull; sc.stat[4] = 0ull; }
     if (tid < sc.n_scen) s_k[tid] = pb_scn_const(sc.scen[tid], p);   // log2(R), 1/H, ...: once per CTA, not once per thread
     if (run_mode && tid >= 64 && tid < 64 + sc.n_abs) s_abs_scn[tid - 64] = sc.cons[sc.abs_first[tid - 64]].scenario;
     if (run_mode == 1 && tid >= 32 && tid < 32 + sc.n_abs) {

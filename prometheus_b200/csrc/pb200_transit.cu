@@ -100,9 +100,7 @@ __global__ void __launch_bounds__(256) sigma_phase_kernel(const DevScene* __rest
             bits = o > bits ? o : bits;
             ns_abs = fmax(ns_abs, __shfl_xor_sync(0xffffffffu, ns_abs, d));
         }
-        // (sigma cells: this kernel runs beside the column kernel, the compaction AND the cell sums, none of which waits for it --
-        //  they bound sigma by the tables' maxima; only cell_eval_kernel reads nsig)
-        if (lane == 0 && bits && prm.cell_range == nullptr) atomicMax(sc.smax + (int64_t)a * sc.n_orb + p, bits);
+        if (lane == 0 && bits) atomicMax(sc.smax + (int64_t)a * sc.n_orb + p, bits);
         // window maxima of |nsig_a| for the thin test / the thickness order of kernel (c')
         __syncthreads();
         if (lane == 0) s_wmax[wid] = ns_abs;
@@ -778,7 +776,20 @@ __global__ void __launch_bounds__(256) cell_eval_kernel(const DevScene* __restri
     const int64_t wi = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (wi >= prm.n_wav_sel) return;
     const int pi = blockIdx.y, p = prm.phase_lo + pi;
-    const double ns = __ldg(prm.nsig + (int64_t)pi * prm.n_wav_sel + wi);
+    // (b1) -sigma(p, lambda) 4096/ln2 of the one absorber, as sigma_phase_kernel forms it (np.interp + 10**v - offset, :34-51,
+    // chi :940): looked up here, where it is used -- no nsig array, no kernel beside the column stage
+    double ns;
+    {
+        const double lam = __ldg(sc.wavelength + pb_wav_index(prm, wi));
+        const int k0 = sc.abs_first[0];
+        const double sl = __ldg(sc.scen[sc.cons[k0].scenario].shift + p) * lam;                 // :917
+        double v = 0.0;
+        for (int k = k0; k < k0 + sc.abs_count[0]; ++k) {
+            const DevConstituent& C = sc.cons[k];
+            v = fma(C.chi, exp10(pb_cons_log_sigma(C, sl)) - C.offset, v);
+        }
+        ns = -v * kExpBigScale;
+    }
     const double a = fabs(ns);
     const int2 rg = prm.cell_range[pi];
     double v;
@@ -833,7 +844,7 @@ cudaError_t launch_cell_moments(const DevScene* d_scene, const TransitParams& pr
     cell_moment_kernel<<<dim3(kCellCap / 32, (unsigned)prm.n_phase, (unsigned)n_cs), 256, smem, st>>>(d_scene, prm, partial, sums, n_cs);
     return cudaGetLastError();
 }
-// nsig (sigma_phase_kernel) + the sums -> R
+// sigma(p, lambda) looked up per wavelength + the sums -> R
 cudaError_t launch_cell_eval(const DevScene* d_scene, const TransitParams& prm, int n_cs, void* scratch, cudaStream_t st) {
     const double* sums = cell_partial(prm, scratch) + (size_t)prm.n_phase * n_cs * kCellSums * kCellCap;
     cell_eval_kernel<<<dim3((unsigned)((prm.n_wav_sel + 255) / 256), (unsigned)prm.n_phase), 256, 0, st>>>(d_scene, prm, sums);
