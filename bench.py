@@ -910,7 +910,9 @@ def run_b200(args):
                             "(phi, rho), (pi - phi, rho) -- equal column densities, the scene is symmetric in z -- share one record. "
                             "Of the remaining (`executed`) samples, those whose chord is optically thin over the warp's 256 wavelengths "
                             "(tau < 2.1e-5) are summed as a second-order expansion per chord; only `exp_samples` take the table exp. "
-                            "`off` = same steps with pb200_set_option CULL = MIRROR = THIN = 0: every unblocked sample goes through the exp"},
+                            "With one absorber and >= 8192 wavelengths per run (C4, C5) the executed samples are not walked per wavelength "
+                            "at all: R(p, .) is tabulated on sigma cells -- `exp_samples` then counts (chord, cell) pairs, one table exp "
+                            "each (DESIGN.md 6b). `off` = same steps with pb200_set_option CULL = MIRROR = THIN = 0: every unblocked sample goes through the exp"},
         "kernels_ms": {"column": column_ms, "transit": kernel_ms, "finalize": finalize_ms},
         "setup": {"seconds": t_setup, "voigt_last_table_ms": voigt["transit_ms"], "voigt_last_table_evals": voigt["samples"]},
     }
