@@ -230,6 +230,13 @@ int pb200_set_scene(pb200_ctx* ctx, const pb200_scene* scene);
    address base[i], rank r owns [r*chunk, (r+1)*chunk) (ncclAllGather in place; prometheus_b200/distributed.py).
    The reference re-reads its tables from host RAM per chunk (gasProperties.py:948-952).                      */
 int pb200_set_scene_sharded(pb200_ctx* ctx, const pb200_scene* scene, int n_ranks, int rank);
+
+/* Optional, before flattening the next scene: re-issue the host-to-device copies of the large page-locked tables of the
+   LAST pb200_set_scene at the places they had, so that the transfer runs while the host prepares the small arrays.
+   The next pb200_set_scene skips the copies that are already on the stream (same source pointer, size and place) and
+   makes every other one as usual.  The tables must not be written between this call and that pb200_set_scene.
+   No counterpart in the reference.                                                                                 */
+int pb200_prefetch_tables(pb200_ctx* ctx);
 int pb200_table_regions(pb200_ctx* ctx, int max_regions, void** base, int64_t* chunk_doubles, int* n_regions);
 
 /* ---- Transit.sumOverChords (gasProperties.py:1160-1258) ---------------------------------

@@ -30,6 +30,7 @@ def sum_over_chords(transit, max_memory_gb: float = 2.0, device: int | None = No
     """GPU replacement of `Transit.sumOverChords(self, max_memory_gb)` for any Transit-like object
     (reference: pythonScripts/gasProperties.py:1160-1258)."""
     ctx = host.get_context(device)
+    ctx.prefetch_tables()      # the sigma tables of the previous call start moving while the host flattens this one
     sc, keep, info = scene.flatten(transit)
     ctx.set_scene(sc, keep)
     R, timing = ctx.run(0, info["n_orb"], 0, info["n_wav"])

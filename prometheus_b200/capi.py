@@ -25,7 +25,7 @@ EXPORTS = [
     "pb200_voigt_profile", "pb200_molecular_sigma", "pb200_write_output", "pb200_probe_fp64",
     "pb200_set_models", "pb200_lightcurve", "pb200_run_batch",
     "pb200_host_register", "pb200_host_unregister", "pb200_run_scatter", "pb200_sync",
-    "pb200_set_scene_sharded", "pb200_table_regions", "pb200_number_density_device",
+    "pb200_set_scene_sharded", "pb200_table_regions", "pb200_number_density_device", "pb200_prefetch_tables",
     "pb200_serpens_density", "pb200_set_option", "pb200_get_option", "pb200_serpens_histogram_static",
     "pb200_last_sort_order", "pb200_optical_depth_chords", "pb200_log_table",
 ]
@@ -180,6 +180,7 @@ def load():
         "pb200_serpens_histogram_static": (C.c_int, [vp, vp, i64, vp, i32, vp, i32, vp, i32, dbl, dbl, vp]),
         "pb200_last_sort_order": (C.c_int, [vp, C.POINTER(i64), C.POINTER(C.c_int32), c_double_p]),
         "pb200_set_scene_sharded": (C.c_int, [vp, C.POINTER(Scene), i32, i32]),
+        "pb200_prefetch_tables": (C.c_int, [vp]),
         "pb200_table_regions": (C.c_int, [vp, i32, C.POINTER(vp), C.POINTER(i64), C.POINTER(i32)]),
         "pb200_host_register": (C.c_int, [vp, C.c_size_t, C.POINTER(vp)]),
         "pb200_host_unregister": (C.c_int, [vp]),
@@ -326,6 +327,10 @@ class Context:
                     ctx.set_option(k, v)
 
         return _Scope()
+
+    def prefetch_tables(self):
+        """Start the H2D copies of the last scene's large page-locked tables again (pb200_prefetch_tables)."""
+        self.check(self.lib.pb200_prefetch_tables(self.handle))
 
     def set_scene(self, scene: Scene, keep):
         self._keep = keep

@@ -137,6 +137,11 @@ struct pb200_ctx {
     bool mol_stats_pending = false;   // the last run was kernel (m) in moment form: check_oob reads [2], [3]
     bool buckets_ready = false;   // bucket indices of the sigma tables (built on the device before the first run of a scene)
     std::vector<std::pair<void*, int64_t>> regions;   // sharded uploads of the current scene: (device base, doubles per rank)
+    // pb200_prefetch_tables: the large page-locked arrays of the last pb200_set_scene (source, bytes, arena offset), and
+    // those of them whose copy a prefetch has already put on the stream for the NEXT pb200_set_scene
+    struct UpItem { const void* src; size_t bytes; size_t offset; };
+    std::vector<UpItem> last_big, prefetched;
+    void* prefetched_arena = nullptr;
     // sigma-sorted order of the last run (pb200_last_sort_order; lives in `scratch` until the next run)
     const int* last_perm = nullptr;
     const double* last_nsig_sorted = nullptr;
@@ -464,6 +469,26 @@ static int plan_derived(pb200_ctx* c) {
 
 static int set_scene_impl(pb200_ctx* c, const pb200_scene* s, int n_ranks, int rank);
 
+// Start the host-to-device copies of the large page-locked tables of the LAST scene again, at the places they had: a
+// caller that is about to flatten the same objects (Transit.sumOverChords called again -- a retrieval loop, a light curve
+// per night) lets the DMA run while the host prepares the small arrays.  The next pb200_set_scene skips every copy that
+// is already on the stream (same source pointer, size and arena offset) and makes all the others as usual, so a
+// different scene costs only the wasted transfer.  No counterpart in the reference (its tables never leave the host).
+extern "C" int pb200_prefetch_tables(pb200_ctx* c) {
+    if (!c) return PB200_ERR_INVALID;
+    if (!c->arena || c->last_big.empty()) return PB200_OK;
+    cudaError_t e = cudaSetDevice(c->device);
+    if (e != cudaSuccess) return fail(c, PB200_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e));
+    c->prefetched.clear();
+    c->prefetched_arena = c->arena;
+    for (const auto& it : c->last_big) {
+        if (!is_pinned(it.src, it.bytes) || it.offset + it.bytes > c->arena_bytes) continue;   // freed since
+        PB_CUDA(c, cudaMemcpyAsync(static_cast<char*>(c->arena) + it.offset, it.src, it.bytes, cudaMemcpyHostToDevice, c->stream));
+        c->prefetched.push_back(it);
+    }
+    return PB200_OK;
+}
+
 extern "C" int pb200_set_scene(pb200_ctx* c, const pb200_scene* s) { return set_scene_impl(c, s, 1, 0); }
 
 // As pb200_set_scene, for rank `rank` of n_ranks processes that upload the SAME scene to their GPUs: of every large
@@ -602,6 +627,7 @@ static int set_scene_impl(pb200_ctx* c, const pb200_scene* s, int n_ranks, int r
             return e;
         };
         c->regions.clear();
+        std::vector<pb200_ctx::UpItem> big_now;
         for (const auto& it : plan.items) {
             if (it.chunk) {   // this rank's slice only
                 PB_CUDA(c, flush_run());
@@ -619,8 +645,13 @@ static int set_scene_impl(pb200_ctx* c, const pb200_scene* s, int n_ranks, int r
                 c->regions.push_back({static_cast<char*>(c->arena) + it.offset, (int64_t)(it.chunk / sizeof(double))});
             } else if (it.bytes >= (64u << 10) && is_pinned(it.src, it.bytes)) {
                 PB_CUDA(c, flush_run());
-                PB_CUDA(c, cudaMemcpyAsync(static_cast<char*>(c->arena) + it.offset, it.src, it.bytes,
-                                           cudaMemcpyHostToDevice, c->stream));
+                bool done = false;   // already on the stream (pb200_prefetch_tables): same source, same size, same place
+                if (c->prefetched_arena == c->arena)
+                    for (const auto& q : c->prefetched) done = done || (q.src == it.src && q.bytes == it.bytes && q.offset == it.offset);
+                if (!done)
+                    PB_CUDA(c, cudaMemcpyAsync(static_cast<char*>(c->arena) + it.offset, it.src, it.bytes,
+                                               cudaMemcpyHostToDevice, c->stream));
+                big_now.push_back({it.src, it.bytes, it.offset});
                 run_lo = run_hi = it.offset + ((it.bytes + 255) & ~size_t(255));
             } else {
                 memcpy(static_cast<char*>(c->stage) + it.offset, it.src, it.bytes);
@@ -629,6 +660,8 @@ static int set_scene_impl(pb200_ctx* c, const pb200_scene* s, int n_ranks, int r
         }
         if (run_hi > plan.total) run_hi = plan.total;
         PB_CUDA(c, flush_run());
+        c->last_big.swap(big_now);
+        c->prefetched.clear();
     }
 
     void* A = c->arena;

@@ -82,7 +82,8 @@ class SceneBuilder:
         return capi.dptr(self.arr(a))
 
     def per_phase(self, v, n_orb):
-        return self.ptr(np.broadcast_to(np.asarray(v, dtype=np.float64), (n_orb,)))
+        v = np.asarray(v, dtype=np.float64)
+        return self.ptr(np.full(n_orb, v) if v.ndim == 0 else np.broadcast_to(v, (n_orb,)))
 
 
 def _trim_table(tx, ty, q_lo, q_hi):

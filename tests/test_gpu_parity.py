@@ -588,3 +588,30 @@ def test_options_are_per_context_and_validated(ctx):
         assert ei.value.code == -1
     with pytest.raises(capi.Pb200Error):
         ctx.check(ctx.lib.pb200_set_option(ctx.handle, 99, 0))
+
+
+def test_prefetched_tables_follow_the_host_arrays(nist_rows, golden):
+    """sum_over_chords starts the H2D copies of the previous call's page-locked sigma tables before it flattens the scene
+    (pb200_prefetch_tables); pb200_set_scene then skips exactly those copies.  The result must follow the host arrays:
+    same tables -> same bits; a table changed in place between two calls -> the new values; another scene in between ->
+    its own result, and the first scene's again afterwards."""
+    tr = builder.build_transit(workloads.get("C4s"), nist_rows=nist_rows)
+    R1 = tr.sumOverChords().copy()
+    R2 = tr.sumOverChords().copy()
+    assert np.array_equal(R1, R2)
+    con = tr.atmosphere.densityDistributionList[0].constituents[0]
+    y = con.lookupFunction.y
+    assert y.nbytes >= (64 << 10), "the table is large enough to be sent from where it lies"
+    y += np.log10(2.0)                                   # sigma doubled, in place, same array
+    R3 = tr.sumOverChords().copy()
+    assert float((R1 - R3).max()) > 1e-6 and np.all(R3 <= R1 + 1e-15)
+    tr_b = builder.build_transit(workloads.get("C1"), nist_rows=nist_rows)
+    Rb = tr_b.sumOverChords().copy()
+    g = golden("C1")
+    ok, worst = excess_depth_ok(Rb, g["R"], g["R0"])
+    assert ok, worst
+    R4 = tr.sumOverChords().copy()
+    assert np.array_equal(R3, R4)
+    y -= np.log10(2.0)
+    R5 = tr.sumOverChords().copy()
+    assert np.max(np.abs(R5 - R1)) < 1e-13
