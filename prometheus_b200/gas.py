@@ -426,6 +426,7 @@ class Transit:
         self.wavelength = self.wavelengthGrid.constructWavelengthGrid(self.atmosphere.densityDistributionList)
 
     def _upload(self, ctx):
+        ctx.prefetch_tables()      # the sigma tables of the previous call start moving while the host flattens this one
         sc, keep, info = _scene.flatten(self)
         ctx.set_scene(sc, keep)
         return info

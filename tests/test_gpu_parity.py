@@ -595,7 +595,9 @@ def test_prefetched_tables_follow_the_host_arrays(nist_rows, golden):
     (pb200_prefetch_tables); pb200_set_scene then skips exactly those copies.  The result must follow the host arrays:
     same tables -> same bits; a table changed in place between two calls -> the new values; another scene in between ->
     its own result, and the first scene's again afterwards."""
-    tr = builder.build_transit(workloads.get("C4s"), nist_rows=nist_rows)
+    spec = workloads.get("C4s")
+    spec["wavelength"] = list(workloads.get("C4")["wavelength"])      # C4's grid: a sigma table of 2.7 MB
+    tr = builder.build_transit(spec, nist_rows=nist_rows)
     R1 = tr.sumOverChords().copy()
     R2 = tr.sumOverChords().copy()
     assert np.array_equal(R1, R2)
