@@ -3,6 +3,7 @@ the FP64-pipe roofline in DESIGN.md rests on.
 
     python profiles/sass_excerpt.py > profiles/sass_transit_inner_loop.txt      (build container: cuobjdump only)
     python profiles/sass_excerpt.py moment > profiles/sass_moment_item_loop.txt (kernel (m)'s item loop, same accounting)
+    python profiles/sass_excerpt.py cells  > profiles/sass_cell_moment_loop.txt  (sigma cells: the chord loop of cell_moment_kernel)
 
 The chord loop is the innermost backward branch whose body holds 6 FP64 instructions per (chord, wavelength) sample:
 DFMA t, DADD t - magic, DFMA r, DFMA q1, DFMA q0, DFMA acc (pb200_transit.cu: transit_chords)."""
@@ -90,5 +91,31 @@ def moment():
     print("%.1f issue slots: 9 LDS per item (5 broadcast LDS.128 of the item, V pair, table entry) make issue and LSU co-limiters." % (len(body) / n_items))
 
 
+CELLS = "_ZN5pb20018cell_moment_kernelEPKNS_8DevSceneENS_13TransitParamsEPdS4_i"
+
+
+def cells():
+    print("=" * 110)
+    print("cell_moment_kernel (sigma cells): the chord loop   %s" % CELLS)
+    best = None
+    for body in loops(CELLS):
+        h = collections.Counter(opcode(t) for _, t in body)
+        fp64 = sum(v for k, v in h.items() if k in ("DFMA", "DADD", "DMUL", "DSETP"))
+        if fp64 >= 30 and (best is None or len(body) < len(best[0])):
+            best = (body, h, fp64)
+    body, h, fp64 = best
+    n = max(1, h["LDS"] // 3)        # two broadcast LDS.128 of the record + one table LDS.64 per chord
+    print("chord loop 0x%04x..0x%04x: %d chord record(s) per iteration, lane = cell" % (body[0][0], body[-1][0], n))
+    print("  issue slots %d = %d FP64 + %d other  -> per (chord, cell): %.1f slots, %.1f FP64 instructions (bench.py FLOPS_CENTRE_PAIR = 49 flops)" %
+          (len(body), fp64, len(body) - fp64, len(body) / n, fp64 / n))
+    print("  opcodes: " + ", ".join("%s %d" % kv for kv in sorted(h.items(), key=lambda kv: -kv[1])))
+    for a, t in body:
+        print("    /*%04x*/  %s" % (a, t))
+    print("=" * 110)
+    print("Reading: opaque test (DMUL + DSETP), table exp at the cell centre (DFMA magic, DADD, DFMA reduce, 2 DFMA poly, DMUL by the")
+    print("table entry), u = N h (DMUL), 13 running sums (DADD, DMUL + DADD, 11 x (DMUL + DFMA)).  ncu: FP64 pipe 67 % busy at C5.")
+
+
 if __name__ == "__main__":
-    moment() if "moment" in sys.argv[1:] else main()
+    a = sys.argv[1:]
+    moment() if "moment" in a else cells() if "cells" in a else main()
