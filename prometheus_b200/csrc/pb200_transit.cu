@@ -637,14 +637,16 @@ __global__ void finalize_kernel(const DevScene* __restrict__ scp, const TransitP
 // scaled: the order-2 totals of compact_kernel, which also leaves the cell range of the phase) and its largest cross
 // section.  No sort, no permutation.
 // =====================================================================================================================
+// 1/k!: in the constant bank, so that they are operands of the FMAs instead of immediates rebuilt (UMOV pairs) in every iteration
+static __constant__ double pb_cell_inv_fact[kCellSums] = {1.0, 1.0, 0.5, 0.16666666666666666, 0.041666666666666664, 0.008333333333333333,
+                                                          0.001388888888888889, 0.0001984126984126984, 2.48015873015873e-05,
+                                                          2.7557319223985893e-06, 2.755731922398589e-07, 2.505210838544172e-08,
+                                                          2.08767569878681e-09};
 struct CellSums {
     double a[kCellSums] = {};
     // a[k] += E u^k / k!: the running power and one FMA with 1/k! per order
     __device__ __forceinline__ void add(double E, double u) {
-        constexpr double inv_fact[kCellSums] = {1.0, 1.0, 0.5, 0.16666666666666666, 0.041666666666666664, 0.008333333333333333,
-                                                0.001388888888888889, 0.0001984126984126984, 2.48015873015873e-05,
-                                                2.7557319223985893e-06, 2.755731922398589e-07, 2.505210838544172e-08,
-                                                2.08767569878681e-09};
+        const double* __restrict__ inv_fact = pb_cell_inv_fact;
         double p = E;
         a[0] += p;
         p *= u;
