@@ -241,3 +241,26 @@ def test_lightcurve_and_batch_edge_cases(setup):
         batch.ctx.run_scatter(0, n_orb, 256, n_blocks + 2, r, full.ctypes.data, n_wav)
     batch.ctx.synchronize()
     assert np.array_equal(full, R_ref)
+
+
+def test_models_may_differ_in_temperature_and_planet_radius(nist_rows):
+    """pb200_model carries the planet radius of the model, and the T of its scenarios is honoured (ABI v4): a batch whose
+    models differ in them equals the single runs of the same objects, and the models really differ from one another.
+    (The sigma tables are the scene's: sigma_v is fixed by the template, as the header says.)"""
+    import copy
+    template = builder.build_transit(workloads.get("HYDs"), nist_rows=nist_rows)
+    variants = []
+    for f_T, f_R in ((1.0, 1.0), (1.3, 1.0), (1.0, 1.08), (0.8, 0.95)):
+        v = copy.deepcopy(template)
+        v.planet.R *= f_R
+        for dist in v.atmosphere.densityDistributionList:
+            dist.T *= f_T
+        variants.append(v)
+    batch = retrieval.RetrievalBatch(template)
+    _, R, _ = batch.run(variants, None, want_R=True)
+    batch.reset()
+    singles = [v.sumOverChords().copy() for v in variants]
+    for k in range(len(variants)):
+        assert np.max(np.abs(R[k] - singles[k])) < 5e-14, k
+    for k in range(1, len(variants)):
+        assert np.max(np.abs(singles[k] - singles[0])) > 1e-6, k        # T and R moved the transit depth
