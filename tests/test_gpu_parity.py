@@ -617,3 +617,31 @@ def test_prefetched_tables_follow_the_host_arrays(nist_rows, golden):
     y -= np.log10(2.0)
     R5 = tr.sumOverChords().copy()
     assert np.max(np.abs(R5 - R1)) < 1e-13
+
+
+def test_more_constituents_than_compiled_absorbers(nist_rows):
+    """14 atomic constituents in one scenario: with the per-scenario grouping (default) they are ONE absorber and run; with
+    PB200_OPT_GROUP = 0 they would be 14 absorbers -- more than kernel (c') is compiled for (PB200_MAX_ABSORBERS = 12) -- and
+    the run must be refused with PB200_ERR_UNSUPPORTED before any kernel sizes its shared arrays by the absorber count.
+    The context stays usable."""
+    from prometheus_b200 import scene
+    ctx = host.get_context(0)
+    spec = workloads.get("C2s")
+    names = ["NaI", "KI", "MgI", "MgII", "CaI", "CaII", "FeI", "TiI", "TiII", "SiI", "AlI", "CrI", "MnI", "NiI"]
+    spec["scenarios"][0]["molecules"] = []
+    spec["scenarios"][0]["species"] = [{"name": n, "chi": 1e-7} for n in names]
+    tr = builder.build_transit(spec, nist_rows=nist_rows)
+    sc, keep, info = scene.flatten(tr)
+    ctx.set_scene(sc, keep)
+    R, _ = ctx.run(0, info["n_orb"], 0, info["n_wav"])
+    assert np.all(np.isfinite(R)) and R.min() < 1.0
+    with ctx.options(group=0):
+        with pytest.raises(capi.Pb200Error) as err:
+            sc2, keep2, _ = scene.flatten(tr)
+            ctx.set_scene(sc2, keep2)
+            ctx.run(0, info["n_orb"], 0, info["n_wav"])
+        assert err.value.code == -4 and "absorbers" in str(err.value)
+    sc3, keep3, _ = scene.flatten(tr)
+    ctx.set_scene(sc3, keep3)
+    R3, _ = ctx.run(0, info["n_orb"], 0, info["n_wav"])
+    assert np.array_equal(R, R3)
